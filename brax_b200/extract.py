@@ -1,0 +1,201 @@
+"""Reads the static tables off a constructed reference `brax.System`.
+
+`describe(sys)` walks the objects `System.__init__` built
+(reference: brax/physics/system.py:53-84) and returns a `SystemDesc`.  Every
+number is TAKEN from the built object rather than re-derived from the config
+(SURVEY.md section 7 step 3): e.g. the collider pair list depends on quirks of
+`colliders.get` (the exhausted `parents` generator at colliders.py:935, the
+and/or precedence at :966-967) that a "clean" re-derivation would change.
+
+Works with numpy-backed systems (the reference's non-jit path) and with real
+JAX arrays (`np.asarray` handles both).  Anything outside the covered feature
+set raises `NotImplementedError` -- fail loudly, never fall back.
+"""
+from typing import Any, Dict, List
+
+import numpy as np
+
+from brax_b200.desc import SystemDesc
+
+_JOINT_KINDS = {
+    ('brax.physics.joints', 'Revolute'): 'revolute',
+    ('brax.physics.joints', 'Spherical'): 'spherical',
+    ('brax.physics.spring_joints', 'Revolute'): 'spring_revolute',
+    ('brax.physics.spring_joints', 'Universal'): 'spring_universal',
+    ('brax.physics.spring_joints', 'Spherical'): 'spring_spherical',
+}
+_PAIR_KINDS = {'capsule_plane', 'capsule_capsule', 'box_plane'}
+
+
+def _a(x) -> np.ndarray:
+  return np.asarray(x, dtype=np.float64)
+
+
+def _l(x) -> List[float]:
+  return _a(x).reshape(-1).tolist()
+
+
+def _joint_rows(joint, group: int) -> List[Dict[str, Any]]:
+  key = (type(joint).__module__, type(joint).__name__)
+  if key not in _JOINT_KINDS:
+    raise NotImplementedError('joint type %s.%s' % key)
+  kind = _JOINT_KINDS[key]
+  n = len(np.asarray(joint.body_p.idx))
+  rows = []
+  for i in range(n):
+    lim = _a(joint.limit)[i].reshape(-1, 2)
+    r = {
+        'kind': kind, 'group': group,
+        'body_p': int(np.asarray(joint.body_p.idx)[i]),
+        'body_c': int(np.asarray(joint.body_c.idx)[i]),
+        'off_p': _l(_a(joint.off_p)[i]), 'off_c': _l(_a(joint.off_c)[i]),
+        'axis_p': _l(_a(joint.axis_p)[i]), 'axis_c': _l(_a(joint.axis_c)[i]),
+        'limit': _l(lim), 'dof': int(lim.shape[0]),
+        'angular_damping': float(_a(joint.angular_damping)[i]),
+    }
+    if kind.startswith('spring_'):
+      r['stiffness'] = float(_a(joint.stiffness)[i])
+      r['spring_damping'] = float(_a(joint.spring_damping)[i])
+      r['limit_strength'] = float(_a(joint.limit_strength)[i])
+    else:
+      r['scale_pos'] = float(_a(joint.scale_pos)[i])
+      r['scale_ang'] = float(_a(joint.scale_ang)[i])
+    rows.append(r)
+  return rows
+
+
+def _match_joint(aj, i: int, joints: List[Dict[str, Any]]) -> int:
+  """Flat index of the joint an actuator row was gathered from
+  (actuators.py:43: `jp.take(joint, [joint.index[a.joint] ...])`)."""
+  bp = int(np.asarray(aj.body_p.idx)[i])
+  bc = int(np.asarray(aj.body_c.idx)[i])
+  key = (type(aj).__module__, type(aj).__name__)
+  kind = _JOINT_KINDS[key]
+  for k, j in enumerate(joints):
+    if (j['kind'] == kind and j['body_p'] == bp and j['body_c'] == bc and
+        np.array_equal(_a(j['off_p']), _a(aj.off_p)[i]) and
+        np.array_equal(_a(j['off_c']), _a(aj.off_c)[i]) and
+        np.array_equal(_a(j['axis_c']), _a(aj.axis_c)[i].reshape(-1)) and
+        np.array_equal(_a(j['axis_p']), _a(aj.axis_p)[i].reshape(-1))):
+      return k
+  raise RuntimeError('actuator joint not found among system joints')
+
+
+def _pair_rows(collider, group: int) -> List[Dict[str, Any]]:
+  cull = collider.cull
+  if type(cull).__name__ != 'Pairs':
+    raise NotImplementedError(
+        'collider cull %s (NearNeighbors is out of scope)' % type(cull).__name__)
+  fn = collider.contact_fn.__name__
+  if fn not in _PAIR_KINDS:
+    raise NotImplementedError('contact function %s is out of scope' % fn)
+  two_way = type(collider).__name__ == 'TwoWayCollider'
+  if not two_way and type(collider).__name__ != 'OneWayCollider':
+    raise NotImplementedError('collider %s' % type(collider).__name__)
+  ca, cb = cull.get()
+  ia, ib = np.asarray(ca.body.idx), np.asarray(cb.body.idx)
+  rows = []
+  for i in range(len(ia)):
+    r = {'kind': fn, 'group': group, 'two_way': two_way,
+         'body_a': int(ia[i]), 'body_b': int(ib[i]),
+         'friction_a': float(_a(ca.friction)[i]),
+         'friction_b': float(_a(cb.friction)[i]),
+         'elasticity_a': float(_a(ca.elasticity)[i]),
+         'elasticity_b': float(_a(cb.elasticity)[i]),
+         'radius_a': 0.0, 'radius_b': 0.0}
+    if fn == 'capsule_plane':
+      ends = _a(ca.end)[i].reshape(-1, 3)       # geometry.py:262-288
+      r['n_contacts'] = int(ends.shape[0])
+      r['pts'] = ends.tolist()
+      r['radius_a'] = float(_a(ca.radius)[i])
+    elif fn == 'box_plane':
+      corners = _a(ca.corner)[i].reshape(-1, 3)  # geometry.py:123-136
+      r['n_contacts'] = int(corners.shape[0])
+      r['pts'] = corners.tolist()
+    else:  # capsule_capsule, geometry.py:243-258
+      r['n_contacts'] = 1
+      r['pts'] = [_l(_a(ca.end)[i]), _l(_a(ca.pos)[i]),
+                  _l(_a(cb.end)[i]), _l(_a(cb.pos)[i])]
+      r['radius_a'] = float(_a(ca.radius)[i])
+      r['radius_b'] = float(_a(cb.radius)[i])
+    if r['n_contacts'] > 8:
+      raise NotImplementedError('more than 8 contacts per pair')
+    rows.append(r)
+  return rows
+
+
+def describe(sys, name: str = 'system', act_size: int = None) -> SystemDesc:
+  """Returns the `SystemDesc` of a constructed reference `brax.System`."""
+  cfg = sys.config
+  if type(cfg).__name__ == 'TracedConfig':
+    raise NotImplementedError(
+        'TracedConfig / per-env randomised constants are out of scope')
+  mode = cfg.dynamics_mode
+  integ = sys.integrator
+
+  bodies = []
+  for i in range(sys.num_bodies):
+    bodies.append({
+        'mass': float(_a(sys.body.mass)[i]),
+        'inv_inertia': _l(_a(sys.body.inertia)[i]),
+        'pos_mask': _l(_a(integ.pos_mask)[i]),
+        'rot_mask': _l(_a(integ.rot_mask)[i]),
+    })
+
+  joints: List[Dict[str, Any]] = []
+  for g, j in enumerate(sys.joints):
+    joints.extend(_joint_rows(j, g))
+
+  actuators = []
+  for g, a in enumerate(sys.actuators):
+    kind = {'Torque': 'torque', 'Angle': 'angle'}.get(type(a).__name__)
+    if kind is None:
+      raise NotImplementedError('actuator %s' % type(a).__name__)
+    idx = np.asarray(a.act_index).reshape(len(np.asarray(a.strength)), -1)
+    for i in range(idx.shape[0]):
+      actuators.append({
+          'kind': kind, 'group': g,
+          'joint': _match_joint(a.joint, i, joints),
+          'act_index': [int(v) for v in idx[i]],
+          'strength': float(_a(a.strength)[i]),
+      })
+
+  forces = []
+  for f in sys.forces:
+    kind = {'Thruster': 'thruster', 'Twister': 'twister'}.get(type(f).__name__)
+    if kind is None:
+      raise NotImplementedError('force %s' % type(f).__name__)
+    idx = np.asarray(f.act_index).reshape(-1, 3)
+    for i in range(idx.shape[0]):
+      forces.append({'kind': kind, 'body': int(np.asarray(f.body.idx)[i]),
+                     'act_index': [int(v) for v in idx[i]],
+                     'strength': float(_a(f.strength)[i])})
+
+  pairs = []
+  for g, c in enumerate(sys.colliders):
+    pairs.extend(_pair_rows(c, g))
+
+  if act_size is None:
+    act_size = int(sys.num_joint_dof + sys.num_forces_dof)
+  if sys.colliders:
+    c0 = sys.colliders[0]
+    erp, scale = float(c0.baumgarte_erp), float(c0.collide_scale)
+    vth = float(c0.velocity_threshold)
+  else:
+    erp = float(cfg.baumgarte_erp * cfg.substeps / cfg.dt)
+    scale = float(cfg.solver_scale_collide)
+    vth = float(np.linalg.norm(_a(integ.gravity)) * float(integ.dt) * 4.0)
+
+  qp = sys.default_qp()
+  return SystemDesc(
+      name=name, dynamics_mode=mode, substeps=int(cfg.substeps),
+      act_size=act_size, dt=float(cfg.dt), dt_sub=float(integ.dt),
+      gravity=_l(integ.gravity),
+      velocity_damping=float(integ.velocity_damping),
+      angular_damping=float(integ.angular_damping),
+      baumgarte_erp=erp, collide_scale=scale, velocity_threshold=vth,
+      num_collider_groups=len(sys.colliders),
+      bodies=bodies, joints=joints, actuators=actuators, forces=forces,
+      pairs=pairs, body_names=[b.name for b in cfg.bodies],
+      default_qp={'pos': _a(qp.pos).tolist(), 'rot': _a(qp.rot).tolist(),
+                  'vel': _a(qp.vel).tolist(), 'ang': _a(qp.ang).tolist()})

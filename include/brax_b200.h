@@ -1,0 +1,217 @@
+/*
+ * brax_b200.h -- C ABI of the B200-native Brax v1 physics step.
+ *
+ * This is the drop-in boundary for ONE path of the reference
+ * (Prasaya/brax, a fork of google/brax 0.1.1):
+ *
+ *     brax.physics.system.System.step(qp, act) -> (qp, info)
+ *         reference: brax/physics/system.py:244-247
+ *         -> _pbd_step      system.py:254-325   (dynamics_mode "pbd")
+ *         -> _spring_step   system.py:342-377   (dynamics_mode "legacy_spring")
+ *
+ * The reference has no FFI of its own (it is pure Python/JAX); these entry
+ * points are what a JAX FFI custom call / a ctypes stub / a torch wrapper binds
+ * (see INTEGRATION.md).  Plain pointers and sizes only, no torch/JAX types.
+ *
+ * Layout at the boundary is exactly what JAX hands over for a batched step
+ * (SURVEY.md 8(b)): C-contiguous float32, env-major:
+ *     pos[B][N][3] rot[B][N][4] vel[B][N][3] ang[B][N][3] act[B][A]
+ * quaternions are (w,x,y,z).  All outputs are written in full every call.
+ *
+ * There is NO CPU fallback behind these entry points: every bx_step* call
+ * launches the sm_100a kernels, and returns an error if no CUDA device exists.
+ */
+#ifndef BRAX_B200_H_
+#define BRAX_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BX_ABI_VERSION 3
+
+/* dynamics_mode (base.py:179-201) */
+#define BX_MODE_PBD 0
+#define BX_MODE_LEGACY_SPRING 1
+
+/* joint kinds.  pbd: joints.py:260 (Revolute), :322 (Spherical);
+ * legacy_spring: spring_joints.py:114 (Revolute), :160 (Universal),
+ * :226 (Spherical). */
+#define BX_JOINT_REVOLUTE 0
+#define BX_JOINT_SPHERICAL 1
+#define BX_JOINT_SPRING_REVOLUTE 2
+#define BX_JOINT_SPRING_UNIVERSAL 3
+#define BX_JOINT_SPRING_SPHERICAL 4
+
+/* actuator kinds: actuators.py:94 (Torque), :75 (Angle) */
+#define BX_ACT_TORQUE 0
+#define BX_ACT_ANGLE 1
+
+/* force kinds: forces.py:26 (Thruster), :69 (Twister) */
+#define BX_FORCE_THRUSTER 0
+#define BX_FORCE_TWISTER 1
+
+/* contact functions: colliders.py:744 capsule_plane, :805 capsule_capsule,
+ * :667 box_plane.  A sphere is a one-end capsule (colliders.py:922-929). */
+#define BX_PAIR_CAPSULE_PLANE 0
+#define BX_PAIR_CAPSULE_CAPSULE 1
+#define BX_PAIR_BOX_PLANE 2
+
+#define BX_MAX_BODIES 64
+#define BX_MAX_JOINTS 64
+#define BX_MAX_ACTUATORS 64
+#define BX_MAX_FORCES 32
+#define BX_MAX_PAIRS 64
+#define BX_MAX_CONTACTS 128 /* K: contact rows per env */
+#define BX_MAX_GROUPS 8
+
+/* One rigid body: bodies.py:39-43 and integrators.py:38-44.
+ * inv_inertia is the INVERSE diagonal inertia (bodies.py:40). */
+typedef struct bx_body {
+  float mass;
+  float inv_inertia[3];
+  float pos_mask[3]; /* 1 - frozen.position */
+  float rot_mask[3]; /* 1 - frozen.rotation; quat_mask = [1, rot_mask] */
+} bx_body;
+
+/* One joint: joints.py:38-77 / spring_joints.py:42-87.  Matrices row-major:
+ * axis_p[r*3+c] is component c of row r.  limit[d*2+{0,1}] = min,max (rad). */
+typedef struct bx_joint {
+  int32_t kind;
+  int32_t body_p, body_c;
+  int32_t group; /* index of the reference's joint group (summation order) */
+  float off_p[3], off_c[3];
+  float axis_p[9], axis_c[9];
+  float limit[6];
+  float angular_damping;
+  float scale_pos, scale_ang;                      /* pbd */
+  float stiffness, spring_damping, limit_strength; /* legacy_spring */
+} bx_joint;
+
+/* One actuator: actuators.py:31-46.  act_index[d] < 0 means "masked"
+ * (act_mask = 0, actuators.py:46,64). */
+typedef struct bx_actuator {
+  int32_t kind;
+  int32_t joint; /* index into joints[] */
+  int32_t group;
+  int32_t act_index[3];
+  float strength;
+} bx_actuator;
+
+/* One body force: forces.py:29-41, 72-84. */
+typedef struct bx_force {
+  int32_t kind;
+  int32_t body;
+  int32_t act_index[3];
+  float strength;
+} bx_force;
+
+/* One candidate collidable pair of a collider group (colliders.py:891-1023,
+ * geometry.py:86-93,126-136,246-288).  Contact rows of the system are ordered
+ * group-major, pair-major, contact-in-pair (system.py:36-43).
+ *   capsule_plane : pts[c] = capsule end c in the body-a frame (n_contacts of
+ *                   them), radius_a.
+ *   box_plane     : pts[0..7] = corners in the body-a frame.
+ *   capsule_capsule: pts[0] = end_a, pts[1] = pos_a, pts[2] = end_b,
+ *                   pts[3] = pos_b (segment half-vector and centre offset in
+ *                   each body frame), radius_a, radius_b. n_contacts = 1. */
+typedef struct bx_pair {
+  int32_t kind;
+  int32_t group;   /* collider group: averaging is per group (colliders.py:231) */
+  int32_t two_way; /* 0: OneWayCollider (b static), 1: TwoWayCollider */
+  int32_t body_a, body_b;
+  int32_t n_contacts;
+  float friction;   /* friction_a * friction_b   (colliders.py:317) */
+  float elasticity; /* elasticity_a * elasticity_b */
+  float radius_a, radius_b;
+  float pts[8][3];
+} bx_pair;
+
+/* The static description of one system; everything System.__init__ derives
+ * from the config (system.py:53-84).  Built on the host by
+ * brax_b200.extract.describe(sys) from a constructed reference System. */
+typedef struct bx_system_desc {
+  uint32_t struct_size; /* = sizeof(bx_system_desc), checked */
+  uint32_t abi_version; /* = BX_ABI_VERSION, checked */
+  int32_t dynamics_mode;
+  int32_t substeps; /* config.substeps; pbd runs substeps/2 pairs */
+  int32_t num_bodies, num_joints, num_actuators, num_forces, num_pairs;
+  int32_t num_collider_groups;
+  int32_t act_size; /* A: length of the act vector */
+  float dt_sub;     /* config.dt / config.substeps (integrators.py:45) */
+  float gravity[3];
+  float vel_damp; /* exp(velocity_damping * dt_sub) (integrators.py:89) */
+  float ang_damp; /* exp(angular_damping * dt_sub)  (integrators.py:92) */
+  float baumgarte_erp;      /* erp*substeps/dt (colliders.py:109) */
+  float collide_scale;      /* colliders.py:112 */
+  float velocity_threshold; /* |g|*h*4 (colliders.py:114) */
+  const bx_body* bodies;
+  const bx_joint* joints;
+  const bx_actuator* actuators;
+  const bx_force* forces;
+  const bx_pair* pairs;
+} bx_system_desc;
+
+typedef struct bx_system bx_system; /* opaque; owns device copies of tables */
+
+/* Device-side I/O of one batched step.  All pointers are DEVICE pointers,
+ * float32, C-contiguous.  Shapes: N bodies, A act_size, K contact rows. */
+typedef struct bx_step_io {
+  /* in  */ const float *pos, *rot, *vel, *ang, *act; /* [B,N,3|4|3|3] [B,A] */
+  /* out */ float *pos_o, *rot_o, *vel_o, *ang_o;
+  /* Info (base.py:136-153).  Any of these may be NULL to skip the write. */
+  float *contact_vel, *contact_ang;   /* info.contact  [B,N,3] x2 */
+  float *joint_vel, *joint_ang;       /* info.joint    [B,N,3] x2 */
+  float *actuator_vel, *actuator_ang; /* info.actuator [B,N,3] x2 */
+  float *contact_pos;                 /* [B,K,3] */
+  float *contact_normal;              /* [B,K,3] */
+  float *contact_penetration;         /* [B,K]   */
+} bx_step_io;
+
+/* Creates a system on CUDA device `device` (tables uploaded once).  Returns 0
+ * on success; non-zero + bx_last_error() for anything outside coverage --
+ * fail loudly, never fall back (SURVEY.md 8(b) "Errors"). */
+int bx_system_create(const bx_system_desc* desc, int device, bx_system** out);
+void bx_system_destroy(bx_system* sys);
+
+/* Number of contact rows K and bodies N, act size A of a created system. */
+int bx_system_num_contacts(const bx_system* sys);
+int bx_system_num_bodies(const bx_system* sys);
+int bx_system_act_size(const bx_system* sys);
+
+/* One System.step for B independent environments: ONE kernel launch on
+ * `stream` (a cudaStream_t passed as void*; NULL = default stream).  No host
+ * sync, no allocation: CUDA-graph capturable.  Replaces
+ * jit(vmap(System.step)) (system.py:244, envs/wrappers.py:70,80). */
+int bx_step(const bx_system* sys, int64_t num_envs, const bx_step_io* io,
+            void* stream);
+
+/* The same step with HOST buffers (pageable or pinned): copies in, launches,
+ * copies out, synchronises.  This is the call a numpy/ctypes binding of
+ * System.step makes and what bench.py's e2e number times. */
+int bx_step_host(bx_system* sys, int64_t num_envs, const bx_step_io* host_io);
+
+/* T consecutive steps in one call: act is [T,B,A]; state ping-pongs inside
+ * device scratch; Info of the LAST step is written.  Mirrors
+ * lax.scan(env.step) over actions (training/acting.py:53-74) at System level. */
+int bx_rollout(bx_system* sys, int64_t num_envs, int32_t num_steps,
+               const bx_step_io* io, void* stream);
+
+/* Kernel launch configuration (tuning knobs; defaults are chosen per system).
+ * lanes_per_env in {0=auto}; returns 0 on success. */
+int bx_system_configure(bx_system* sys, int32_t threads_per_block,
+                        int32_t reserved);
+
+/* Number of kernel launches issued through this library since load (for
+ * bench.py's gpu_launches claim). */
+int64_t bx_launch_count(void);
+
+/* Thread-local message for the last non-zero return on this thread. */
+const char* bx_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BRAX_B200_H_ */
