@@ -1,0 +1,483 @@
+// bx_api.cu -- the C ABI of include/brax_b200.h over the fused step kernel.
+//
+// bx_system_create() flattens the static description of a system
+// (what brax.System.__init__ builds, reference brax/physics/system.py:53-84)
+// into the int/float tables of bx_tables.h and uploads them once.  bx_step()
+// is one kernel launch on the caller's stream: no allocation, no host sync.
+// There is no CPU fallback: without a CUDA device every call fails loudly.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <atomic>
+#include <string>
+#include <vector>
+
+#include "../../include/brax_b200.h"
+#include "bx_tables.h"
+// single translation unit: the kernel (and BxKernelParams) is compiled here
+#include "bx_step_kernel.cu"
+
+struct bx_system {
+  BxHeader h;
+  int device;
+  int32_t* d_tab_i;
+  float* d_tab_f;
+  size_t smem_bytes;
+  int warps;  // warps per CTA (W)
+  int sm_count;
+  // scratch for bx_step_host / bx_rollout
+  float* d_scratch;
+  size_t scratch_floats;
+};
+
+static thread_local std::string g_err;
+static std::atomic<int64_t> g_launches{0};
+
+static int fail(const std::string& m) {
+  g_err = m;
+  return 1;
+}
+#define CUDA_OK(x)                                                         \
+  do {                                                                     \
+    cudaError_t e_ = (x);                                                  \
+    if (e_ != cudaSuccess)                                                 \
+      return fail(std::string(#x) + ": " + cudaGetErrorString(e_));        \
+  } while (0)
+
+extern "C" const char* bx_last_error(void) { return g_err.c_str(); }
+extern "C" int64_t bx_launch_count(void) { return g_launches.load(); }
+
+static int validate(const bx_system_desc* d) {
+  if (!d) return fail("desc is NULL");
+  if (d->struct_size != sizeof(bx_system_desc))
+    return fail("bx_system_desc size mismatch (ABI skew)");
+  if (d->abi_version != BX_ABI_VERSION) return fail("bx_system_desc abi_version mismatch");
+  if (d->dynamics_mode != BX_MODE_PBD && d->dynamics_mode != BX_MODE_LEGACY_SPRING)
+    return fail("unknown dynamics_mode");
+  if (d->num_bodies < 1 || d->num_bodies > BX_MAX_BODIES) return fail("num_bodies out of range");
+  if (d->num_joints < 0 || d->num_joints > BX_MAX_JOINTS) return fail("num_joints out of range");
+  if (d->num_actuators < 0 || d->num_actuators > BX_MAX_ACTUATORS)
+    return fail("num_actuators out of range");
+  if (d->num_forces < 0 || d->num_forces > BX_MAX_FORCES) return fail("num_forces out of range");
+  if (d->num_pairs < 0 || d->num_pairs > BX_MAX_PAIRS) return fail("num_pairs out of range");
+  if (d->num_collider_groups > BX_MAX_GROUPS) return fail("too many collider groups");
+  if (d->act_size < 1) return fail("act_size must be >= 1");
+  if (d->substeps < 1) return fail("substeps must be >= 1");
+  if (!(d->dt_sub > 0.f)) return fail("dt_sub must be positive");
+  for (int i = 0; i < d->num_joints; i++) {
+    const bx_joint& j = d->joints[i];
+    if (j.kind < BX_JOINT_REVOLUTE || j.kind > BX_JOINT_SPRING_SPHERICAL)
+      return fail("unsupported joint kind");
+    bool spring = j.kind >= BX_JOINT_SPRING_REVOLUTE;
+    if (spring != (d->dynamics_mode == BX_MODE_LEGACY_SPRING))
+      return fail("joint kind does not match dynamics_mode");
+    if (j.body_p < 0 || j.body_p >= d->num_bodies || j.body_c < 0 || j.body_c >= d->num_bodies)
+      return fail("joint body index out of range");
+  }
+  for (int i = 0; i < d->num_actuators; i++) {
+    const bx_actuator& a = d->actuators[i];
+    if (a.kind != BX_ACT_TORQUE && a.kind != BX_ACT_ANGLE) return fail("unsupported actuator kind");
+    if (a.joint < 0 || a.joint >= d->num_joints) return fail("actuator joint out of range");
+    for (int k = 0; k < 3; k++)
+      if (a.act_index[k] >= d->act_size) return fail("actuator act_index out of range");
+  }
+  for (int i = 0; i < d->num_forces; i++) {
+    const bx_force& f = d->forces[i];
+    if (f.kind != BX_FORCE_THRUSTER && f.kind != BX_FORCE_TWISTER) return fail("unsupported force kind");
+    if (f.body < 0 || f.body >= d->num_bodies) return fail("force body out of range");
+  }
+  int k = 0;
+  for (int i = 0; i < d->num_pairs; i++) {
+    const bx_pair& p = d->pairs[i];
+    if (p.kind < BX_PAIR_CAPSULE_PLANE || p.kind > BX_PAIR_BOX_PLANE)
+      return fail("unsupported collider pair kind (mesh/heightmap/clipped-plane/box-box are out of scope)");
+    if (p.body_a < 0 || p.body_a >= d->num_bodies || p.body_b < 0 || p.body_b >= d->num_bodies)
+      return fail("pair body index out of range");
+    if (p.group < 0 || p.group >= BX_MAX_GROUPS) return fail("pair group out of range");
+    if (i > 0 && p.group < d->pairs[i - 1].group) return fail("pairs must be sorted by group");
+    if (p.n_contacts < 1 || p.n_contacts > 8) return fail("pair n_contacts out of range");
+    if (p.kind == BX_PAIR_CAPSULE_CAPSULE && p.n_contacts != 1) return fail("capsule_capsule has 1 contact");
+    if (p.kind != BX_PAIR_CAPSULE_CAPSULE && p.two_way) return fail("two-way plane colliders do not exist");
+    k += p.n_contacts;
+  }
+  if (k > BX_MAX_CONTACTS) return fail("too many contact rows");
+  return 0;
+}
+
+// Flattens the description into the tables of bx_tables.h.
+static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int32_t>* ti_out,
+                         std::vector<float>* tf_out) {
+  BxHeader& h = *hh;
+  memset(&h, 0, sizeof(h));
+  std::vector<int32_t>& ti = *ti_out;
+  std::vector<float>& tf = *tf_out;
+  const int nb = d->num_bodies, nj = d->num_joints, na = d->num_actuators, nf = d->num_forces;
+  const bool spring = d->dynamics_mode == BX_MODE_LEGACY_SPRING;
+  h.mode = d->dynamics_mode;
+  h.iters = spring ? d->substeps : d->substeps / 2;  // system.py:324 / :376
+  h.nb = nb; h.nj = nj; h.na = na; h.nf = nf;
+  h.act_size = d->act_size;
+
+  // contact rows: pairs expanded, group-major / pair-major / contact-in-pair
+  struct Row { int pair, c; };
+  std::vector<Row> rows;
+  for (int i = 0; i < d->num_pairs; i++)
+    for (int c = 0; c < d->pairs[i].n_contacts; c++) rows.push_back({i, c});
+  const int nk = static_cast<int>(rows.size());
+  h.nk = nk;
+
+  // slots
+  std::vector<int> cslot(nb, -1), aslot(nb, -1);
+  int ncb = 0, nab = 0;
+  for (int i = 0; i < d->num_pairs; i++) {
+    const bx_pair& p = d->pairs[i];
+    if (cslot[p.body_a] < 0) cslot[p.body_a] = ncb++;
+    if (p.two_way && cslot[p.body_b] < 0) cslot[p.body_b] = ncb++;
+  }
+  for (int i = 0; i < na; i++) {
+    const bx_joint& j = d->joints[d->actuators[i].joint];
+    if (aslot[j.body_p] < 0) aslot[j.body_p] = nab++;
+    if (aslot[j.body_c] < 0) aslot[j.body_c] = nab++;
+  }
+  h.ncb = ncb; h.nab = nab;
+
+  // ---- float tables
+  h.fo_body = static_cast<int>(tf.size());
+  for (int b = 0; b < nb; b++) {
+    const bx_body& s = d->bodies[b];
+    float rec[BF_STRIDE] = {0};
+    rec[BF_INV_MASS] = 1.f / s.mass;
+    rec[BF_MASS] = s.mass;
+    for (int k = 0; k < 3; k++) {
+      rec[BF_INV_INERTIA + k] = s.inv_inertia[k];
+      rec[BF_POS_MASK + k] = s.pos_mask[k];
+      rec[BF_ROT_MASK + k] = s.rot_mask[k];
+    }
+    tf.insert(tf.end(), rec, rec + BF_STRIDE);
+  }
+  h.fo_joint = static_cast<int>(tf.size());
+  for (int i = 0; i < nj; i++) {
+    const bx_joint& s = d->joints[i];
+    float rec[JF_STRIDE] = {0};
+    for (int k = 0; k < 3; k++) { rec[JF_OFF_P + k] = s.off_p[k]; rec[JF_OFF_C + k] = s.off_c[k]; }
+    for (int k = 0; k < 9; k++) { rec[JF_AXIS_P + k] = s.axis_p[k]; rec[JF_AXIS_C + k] = s.axis_c[k]; }
+    for (int k = 0; k < 6; k++) rec[JF_LIMIT + k] = s.limit[k];
+    rec[JF_ANG_DAMP] = s.angular_damping;
+    rec[JF_SCALE_POS] = s.scale_pos;
+    rec[JF_SCALE_ANG] = s.scale_ang;
+    rec[JF_STIFFNESS] = s.stiffness;
+    rec[JF_SPRING_DAMP] = s.spring_damping;
+    rec[JF_LIMIT_STRENGTH] = s.limit_strength;
+    tf.insert(tf.end(), rec, rec + JF_STRIDE);
+  }
+  h.fo_act = static_cast<int>(tf.size());
+  for (int i = 0; i < na; i++) tf.push_back(d->actuators[i].strength);
+  h.fo_force = static_cast<int>(tf.size());
+  for (int i = 0; i < nf; i++) tf.push_back(d->forces[i].strength);
+  h.fo_contact = static_cast<int>(tf.size());
+  for (int k = 0; k < nk; k++) {
+    const bx_pair& p = d->pairs[rows[k].pair];
+    float rec[CF_STRIDE] = {0};
+    rec[CF_FRICTION] = p.friction;
+    rec[CF_ELASTICITY] = p.elasticity;
+    rec[CF_RADIUS_A] = p.radius_a;
+    rec[CF_RADIUS_B] = p.radius_b;
+    if (p.kind == BX_PAIR_CAPSULE_CAPSULE) {
+      for (int q = 0; q < 4; q++)
+        for (int x = 0; x < 3; x++) rec[CF_PTS + 3 * q + x] = p.pts[q][x];
+    } else {
+      for (int x = 0; x < 3; x++) rec[CF_PTS + x] = p.pts[rows[k].c][x];
+    }
+    tf.insert(tf.end(), rec, rec + CF_STRIDE);
+  }
+  h.n_floats = static_cast<int>(tf.size());
+
+  // ---- delta slots of the contact rows inside region JS
+  const int dw = spring ? 6 : 7;
+  std::vector<int> delta_off(nk);
+  int js_contacts = 0;
+  for (int k = 0; k < nk; k++) {
+    delta_off[k] = js_contacts;
+    js_contacts += d->pairs[rows[k].pair].two_way ? 2 * dw : dw;
+  }
+  int js = js_contacts;
+  if (spring) js = std::max(js, 3 * na + 12 * nj);
+  else js = std::max(js, std::max(3 * na + 3 * nj, 14 * nj));
+
+  // ---- state rows
+  int r = 0;
+  h.r_pos0 = r; r += 3 * nb;
+  h.r_rot0 = r; r += 4 * nb;
+  if (spring) { h.r_pos1 = h.r_pos0; h.r_rot1 = h.r_rot0; }
+  else { h.r_pos1 = r; r += 3 * nb; h.r_rot1 = r; r += 4 * nb; }
+  h.r_vel = r; r += 3 * nb;
+  h.r_ang = r; r += 3 * nb;
+  h.r_act = r; r += d->act_size;
+  h.r_js = r; r += js;
+  h.r_ct = r; r += 8 * nk;
+  h.r_pre = r; r += spring ? 0 : 6 * ncb;
+  h.r_ic = r; r += 6 * ncb;   // r_ic, r_ia, r_ij contiguous: zeroed together
+  h.r_ia = r; r += 3 * nab;
+  h.r_ij = r; r += spring ? 6 * nb : 0;
+  h.n_rows = r;
+
+  // ---- int tables
+  std::vector<int32_t> adj;
+  std::vector<int32_t> body_rec(nb * BI_STRIDE, 0);
+  for (int b = 0; b < nb; b++) {
+    int32_t* rec = &body_rec[b * BI_STRIDE];
+    rec[BI_CSLOT] = cslot[b];
+    rec[BI_ASLOT] = aslot[b];
+    // joints: group by group, parents then children (joints.py:93-98)
+    rec[BI_JADJ_OFF] = static_cast<int>(adj.size());
+    for (int i0 = 0; i0 < nj;) {
+      int i1 = i0;
+      while (i1 < nj && d->joints[i1].group == d->joints[i0].group) i1++;
+      for (int i = i0; i < i1; i++) if (d->joints[i].body_p == b) adj.push_back(i << 1);
+      for (int i = i0; i < i1; i++) if (d->joints[i].body_c == b) adj.push_back((i << 1) | 1);
+      i0 = i1;
+    }
+    rec[BI_JADJ_N] = static_cast<int>(adj.size()) - rec[BI_JADJ_OFF];
+    // actuators (actuators.py:67-70); bit0 = subtract
+    rec[BI_AADJ_OFF] = static_cast<int>(adj.size());
+    for (int i0 = 0; i0 < na;) {
+      int i1 = i0;
+      while (i1 < na && d->actuators[i1].group == d->actuators[i0].group) i1++;
+      for (int i = i0; i < i1; i++)
+        if (d->joints[d->actuators[i].joint].body_p == b)
+          adj.push_back((i << 2) | (d->actuators[i].kind == BX_ACT_ANGLE ? 1 : 0));
+      for (int i = i0; i < i1; i++)
+        if (d->joints[d->actuators[i].joint].body_c == b)
+          adj.push_back((i << 2) | (d->actuators[i].kind == BX_ACT_TORQUE ? 1 : 0));
+      i0 = i1;
+    }
+    rec[BI_AADJ_N] = static_cast<int>(adj.size()) - rec[BI_AADJ_OFF];
+    // forces: thrusters, then twisters (forces.py:131-136)
+    rec[BI_FADJ_OFF] = static_cast<int>(adj.size());
+    for (int kind = 0; kind < 2; kind++)
+      for (int i = 0; i < nf; i++)
+        if (d->forces[i].kind == kind && d->forces[i].body == b) adj.push_back(i);
+    rec[BI_FADJ_N] = static_cast<int>(adj.size()) - rec[BI_FADJ_OFF];
+    // contact rows: group by group, a rows then b rows (colliders.py:222-228)
+    rec[BI_CADJ_OFF] = static_cast<int>(adj.size());
+    for (int k0 = 0; k0 < nk;) {
+      int g = d->pairs[rows[k0].pair].group, k1 = k0;
+      while (k1 < nk && d->pairs[rows[k1].pair].group == g) k1++;
+      for (int k = k0; k < k1; k++)
+        if (d->pairs[rows[k].pair].body_a == b) adj.push_back((k << 4) | (g << 1));
+      for (int k = k0; k < k1; k++)
+        if (d->pairs[rows[k].pair].two_way && d->pairs[rows[k].pair].body_b == b)
+          adj.push_back((k << 4) | (g << 1) | 1);
+      k0 = k1;
+    }
+    rec[BI_CADJ_N] = static_cast<int>(adj.size()) - rec[BI_CADJ_OFF];
+  }
+  h.io_body = static_cast<int>(ti.size());
+  ti.insert(ti.end(), body_rec.begin(), body_rec.end());
+  h.io_joint = static_cast<int>(ti.size());
+  for (int i = 0; i < nj; i++) {
+    ti.push_back(d->joints[i].kind);
+    ti.push_back(d->joints[i].body_p);
+    ti.push_back(d->joints[i].body_c);
+  }
+  h.io_act = static_cast<int>(ti.size());
+  for (int i = 0; i < na; i++) {
+    const bx_actuator& a = d->actuators[i];
+    ti.push_back(a.kind); ti.push_back(a.joint);
+    for (int k = 0; k < 3; k++) ti.push_back(a.act_index[k]);
+  }
+  h.io_force = static_cast<int>(ti.size());
+  for (int i = 0; i < nf; i++) {
+    const bx_force& f = d->forces[i];
+    ti.push_back(f.kind); ti.push_back(f.body);
+    for (int k = 0; k < 3; k++) ti.push_back(f.act_index[k]);
+  }
+  h.io_contact = static_cast<int>(ti.size());
+  for (int k = 0; k < nk; k++) {
+    const bx_pair& p = d->pairs[rows[k].pair];
+    ti.push_back(p.kind); ti.push_back(p.two_way); ti.push_back(p.body_a);
+    ti.push_back(p.body_b); ti.push_back(delta_off[k]);
+  }
+  h.io_adj = static_cast<int>(ti.size());
+  ti.insert(ti.end(), adj.begin(), adj.end());
+  // output maps
+  auto body_map = [&](const std::vector<int>& slot, int base, int width, int off) {
+    int o = static_cast<int>(ti.size());
+    for (int b = 0; b < nb; b++)
+      for (int k = 0; k < 3; k++) ti.push_back(slot[b] >= 0 ? base + width * slot[b] + off + k : -1);
+    return o;
+  };
+  std::vector<int> ident(nb);
+  for (int b = 0; b < nb; b++) ident[b] = b;
+  h.m_cv = body_map(cslot, h.r_ic, 6, 0);
+  h.m_ca = body_map(cslot, h.r_ic, 6, 3);
+  h.m_aa = body_map(aslot, h.r_ia, 3, 0);
+  h.m_jv = spring ? body_map(ident, h.r_ij, 6, 0) : 0;
+  h.m_ja = spring ? body_map(ident, h.r_ij, 6, 3) : 0;
+  h.m_cp = static_cast<int>(ti.size());
+  for (int k = 0; k < nk; k++) for (int x = 0; x < 3; x++) ti.push_back(h.r_ct + 8 * k + x);
+  h.m_cn = static_cast<int>(ti.size());
+  for (int k = 0; k < nk; k++) for (int x = 0; x < 3; x++) ti.push_back(h.r_ct + 8 * k + 3 + x);
+  h.m_pen = static_cast<int>(ti.size());
+  for (int k = 0; k < nk; k++) ti.push_back(h.r_ct + 8 * k + 6);
+  h.n_ints = static_cast<int>(ti.size());
+
+  // ---- scalars
+  h.dt = d->dt_sub;
+  h.inv_dt = 1.f / d->dt_sub;
+  h.half_dt = 0.5f * d->dt_sub;
+  for (int k = 0; k < 3; k++) h.gravity[k] = d->gravity[k];
+  h.vel_damp = d->vel_damp;
+  h.ang_damp = d->ang_damp;
+  h.erp = d->baumgarte_erp;
+  h.collide_scale = d->collide_scale;
+  h.vth = d->velocity_threshold;
+  h.inv_2h = 1.f / (2.f * d->dt_sub);
+}
+
+extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_system** out) {
+  if (!out) return fail("out is NULL");
+  *out = nullptr;
+  if (validate(desc)) return 1;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail("no CUDA device: brax_b200 has no CPU fallback");
+  if (device < 0 || device >= ndev) return fail("device index out of range");
+  CUDA_OK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_OK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) return fail("brax_b200 kernels are built for sm_100a (B200) only");
+
+  bx_system* s = new bx_system();
+  std::vector<int32_t> ti;
+  std::vector<float> tf;
+  build_tables(desc, &s->h, &ti, &tf);
+  s->device = device;
+  s->sm_count = prop.multiProcessorCount;
+  s->d_scratch = nullptr;
+  s->scratch_floats = 0;
+  s->smem_bytes = (static_cast<size_t>(s->h.n_rows) * BX_ROW_STRIDE + s->h.n_floats + s->h.n_ints) * 4;
+  if (s->smem_bytes > static_cast<size_t>(prop.sharedMemPerBlockOptin)) {
+    delete s;
+    return fail("system state does not fit in shared memory (too many bodies/joints/contacts)");
+  }
+  // default warps per tile: enough to split the widest phase, capped at 8
+  int widest = std::max(std::max(s->h.nj, s->h.nk), std::max(s->h.na, 1));
+  s->warps = std::min(8, std::max(2, (widest + 1) / 2));
+  cudaError_t e1 = cudaMalloc(&s->d_tab_i, std::max<size_t>(ti.size(), 1) * 4);
+  cudaError_t e2 = cudaMalloc(&s->d_tab_f, std::max<size_t>(tf.size(), 1) * 4);
+  if (e1 != cudaSuccess || e2 != cudaSuccess) { delete s; return fail("cudaMalloc of tables failed"); }
+  CUDA_OK(cudaMemcpy(s->d_tab_i, ti.data(), ti.size() * 4, cudaMemcpyHostToDevice));
+  CUDA_OK(cudaMemcpy(s->d_tab_f, tf.data(), tf.size() * 4, cudaMemcpyHostToDevice));
+  CUDA_OK(cudaFuncSetAttribute(bx_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               prop.sharedMemPerBlockOptin));
+  *out = s;
+  return 0;
+}
+
+extern "C" void bx_system_destroy(bx_system* s) {
+  if (!s) return;
+  cudaSetDevice(s->device);
+  cudaFree(s->d_tab_i);
+  cudaFree(s->d_tab_f);
+  cudaFree(s->d_scratch);
+  delete s;
+}
+
+extern "C" int bx_system_num_contacts(const bx_system* s) { return s ? s->h.nk : -1; }
+extern "C" int bx_system_num_bodies(const bx_system* s) { return s ? s->h.nb : -1; }
+extern "C" int bx_system_act_size(const bx_system* s) { return s ? s->h.act_size : -1; }
+
+extern "C" int bx_system_configure(bx_system* s, int32_t threads_per_block, int32_t reserved) {
+  (void)reserved;
+  if (!s) return fail("system is NULL");
+  if (threads_per_block < 32 || threads_per_block > 512 || (threads_per_block & 31))
+    return fail("threads_per_block must be a multiple of 32 in [32, 512]");
+  s->warps = threads_per_block / 32;
+  return 0;
+}
+
+static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
+                  const bx_step_io* io, cudaStream_t stream) {
+  if (!s || !io) return fail("NULL argument");
+  if (num_envs <= 0) return fail("num_envs must be positive");
+  if (num_steps < 1) return fail("num_steps must be >= 1");
+  if (!io->pos || !io->rot || !io->vel || !io->ang || !io->act || !io->pos_o || !io->rot_o ||
+      !io->vel_o || !io->ang_o)
+    return fail("QP / act pointers must not be NULL");
+  BxKernelParams p;
+  p.h = s->h;
+  p.tab_i = s->d_tab_i;
+  p.tab_f = s->d_tab_f;
+  p.io = *io;
+  p.num_envs = num_envs;
+  p.num_steps = num_steps;
+  const int64_t tiles = (num_envs + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA;
+  if (tiles > 0x7fffffffLL) return fail("too many environments for one launch");
+  bx_step_kernel<<<static_cast<unsigned>(tiles), 32 * s->warps, s->smem_bytes, stream>>>(p);
+  g_launches.fetch_add(1);
+  CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int bx_step(const bx_system* s, int64_t num_envs, const bx_step_io* io, void* stream) {
+  return launch(s, num_envs, 1, io, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int bx_rollout(bx_system* s, int64_t num_envs, int32_t num_steps, const bx_step_io* io,
+                          void* stream) {
+  return launch(s, num_envs, num_steps, io, static_cast<cudaStream_t>(stream));
+}
+
+// Host-buffer step: H2D copies, one launch, D2H copies, synchronise.
+extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
+  if (!s || !hio) return fail("NULL argument");
+  if (B <= 0) return fail("num_envs must be positive");
+  CUDA_OK(cudaSetDevice(s->device));
+  const int64_t n = s->h.nb, a = s->h.act_size, k = s->h.nk;
+  // in: 13n + a ; out: 13n + 18n + 7k   (floats per env)
+  const size_t per_env = static_cast<size_t>(13 * n + a + 13 * n + 18 * n + 7 * k);
+  const size_t need = per_env * B;
+  if (need > s->scratch_floats) {
+    cudaFree(s->d_scratch);
+    s->d_scratch = nullptr;
+    s->scratch_floats = 0;
+    CUDA_OK(cudaMalloc(&s->d_scratch, need * 4));
+    s->scratch_floats = need;
+  }
+  float* cur = s->d_scratch;
+  auto take = [&](size_t per) { float* r = cur; cur += per * B; return r; };
+  bx_step_io d;
+  float* d_pos = take(3 * n); float* d_rot = take(4 * n);
+  float* d_vel = take(3 * n); float* d_ang = take(3 * n); float* d_act = take(a);
+  d.pos = d_pos; d.rot = d_rot; d.vel = d_vel; d.ang = d_ang; d.act = d_act;
+  d.pos_o = take(3 * n); d.rot_o = take(4 * n); d.vel_o = take(3 * n); d.ang_o = take(3 * n);
+  d.contact_vel = take(3 * n); d.contact_ang = take(3 * n);
+  d.joint_vel = take(3 * n); d.joint_ang = take(3 * n);
+  d.actuator_vel = take(3 * n); d.actuator_ang = take(3 * n);
+  d.contact_pos = take(3 * k); d.contact_normal = take(3 * k); d.contact_penetration = take(k);
+  cudaStream_t st = 0;
+  CUDA_OK(cudaMemcpyAsync(d_pos, hio->pos, 3 * n * B * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(cudaMemcpyAsync(d_rot, hio->rot, 4 * n * B * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(cudaMemcpyAsync(d_vel, hio->vel, 3 * n * B * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(cudaMemcpyAsync(d_ang, hio->ang, 3 * n * B * 4, cudaMemcpyHostToDevice, st));
+  CUDA_OK(cudaMemcpyAsync(d_act, hio->act, a * B * 4, cudaMemcpyHostToDevice, st));
+  if (launch(s, B, 1, &d, st)) return 1;
+  struct Out { float* h; const float* dv; size_t per; };
+  const Out outs[] = {
+      {hio->pos_o, d.pos_o, (size_t)3 * n}, {hio->rot_o, d.rot_o, (size_t)4 * n},
+      {hio->vel_o, d.vel_o, (size_t)3 * n}, {hio->ang_o, d.ang_o, (size_t)3 * n},
+      {hio->contact_vel, d.contact_vel, (size_t)3 * n}, {hio->contact_ang, d.contact_ang, (size_t)3 * n},
+      {hio->joint_vel, d.joint_vel, (size_t)3 * n}, {hio->joint_ang, d.joint_ang, (size_t)3 * n},
+      {hio->actuator_vel, d.actuator_vel, (size_t)3 * n}, {hio->actuator_ang, d.actuator_ang, (size_t)3 * n},
+      {hio->contact_pos, d.contact_pos, (size_t)3 * k}, {hio->contact_normal, d.contact_normal, (size_t)3 * k},
+      {hio->contact_penetration, d.contact_penetration, (size_t)k}};
+  for (const Out& o : outs)
+    if (o.h && o.per) CUDA_OK(cudaMemcpyAsync(o.h, o.dv, o.per * B * 4, cudaMemcpyDeviceToHost, st));
+  CUDA_OK(cudaStreamSynchronize(st));
+  return 0;
+}

@@ -1,0 +1,215 @@
+"""Host-side mirror of the reference's `brax.System` for the step path.
+
+    sys = System(desc)                      # or System.from_brax(brax_system)
+    qp, info = sys.step(qp, act)            # brax/physics/system.py:244
+
+`QP`, `P`, `Info` carry the same field names and shapes as the reference's
+flax dataclasses (brax/physics/base.py:28-153).  `step` accepts either
+
+  * torch CUDA tensors  -> `bx_step` on torch's current stream (no sync, no
+    allocation inside the library; outputs are fresh tensors), or
+  * numpy arrays (host) -> `bx_step_host` (H2D, one launch, D2H, sync),
+
+batched `[B, N, ...]` or unbatched `[N, ...]` exactly like `vmap(System.step)`
+vs `System.step`.  Only `step` runs on the GPU; `default_qp` returns the state
+the reference's `default_qp()` produced when the description was extracted.
+Everything is float32.  No CPU fallback: without the CUDA library this raises.
+"""
+import ctypes as C
+import dataclasses
+from typing import Any, Tuple
+
+import numpy as np
+
+from brax_b200 import lib as _lib
+from brax_b200.desc import CStepIO, SystemDesc
+
+
+@dataclasses.dataclass
+class P:
+  """Time derivatives (base.py:50-72)."""
+  vel: Any
+  ang: Any
+
+
+@dataclasses.dataclass
+class QP:
+  """Coordinate and time-derivative frame of every body (base.py:75-133)."""
+  pos: Any
+  rot: Any
+  vel: Any
+  ang: Any
+
+
+@dataclasses.dataclass
+class Info:
+  """Side outputs of a physics step (base.py:136-153)."""
+  contact: P
+  joint: P
+  actuator: P
+  contact_pos: Any
+  contact_normal: Any
+  contact_penetration: Any
+
+
+_OUT = (('pos_o', 3, 'n'), ('rot_o', 4, 'n'), ('vel_o', 3, 'n'),
+        ('ang_o', 3, 'n'), ('contact_vel', 3, 'n'), ('contact_ang', 3, 'n'),
+        ('joint_vel', 3, 'n'), ('joint_ang', 3, 'n'), ('actuator_vel', 3, 'n'),
+        ('actuator_ang', 3, 'n'), ('contact_pos', 3, 'k'),
+        ('contact_normal', 3, 'k'), ('contact_penetration', 0, 'k'))
+
+
+def _is_torch(x) -> bool:
+  return type(x).__module__.startswith('torch')
+
+
+class System:
+  """A brax v1 system whose `step` is the fused sm_100a kernel."""
+
+  def __init__(self, desc: SystemDesc, device: int = 0):
+    self.desc = desc
+    self.device = device
+    self.num_bodies = desc.num_bodies
+    self.num_contacts = desc.num_contacts
+    self.act_size = desc.act_size
+    self._lib = _lib.load()
+    cdesc, keep = desc.to_c()
+    handle = C.c_void_p()
+    rc = self._lib.bx_system_create(C.byref(cdesc), device, C.byref(handle))
+    del keep
+    if rc != 0:
+      raise RuntimeError('bx_system_create: ' + _lib.last_error())
+    self._h = handle
+
+  @classmethod
+  def from_brax(cls, brax_system, name: str = 'system', act_size=None,
+                device: int = 0) -> 'System':
+    """Builds from a constructed reference `brax.System` (the drop-in route)."""
+    from brax_b200.extract import describe
+    return cls(describe(brax_system, name, act_size=act_size), device)
+
+  def __del__(self):
+    h, self._h = getattr(self, '_h', None), None
+    if h:
+      try:
+        self._lib.bx_system_destroy(h)
+      except Exception:  # interpreter shutdown
+        pass
+
+  def configure(self, threads_per_block: int):
+    """Warps per 32-env tile = threads_per_block / 32 (tuning knob)."""
+    if self._lib.bx_system_configure(self._h, threads_per_block, 0) != 0:
+      raise ValueError(_lib.last_error())
+
+  # ---- state helpers ---------------------------------------------------------
+  def default_qp(self, batch: int = None, device=None) -> QP:
+    """`System.default_qp()` (system.py:112) as recorded at extraction time."""
+    d = self.desc.default_qp
+    arrs = [np.asarray(d[k], dtype=np.float32) for k in ('pos', 'rot', 'vel', 'ang')]
+    if batch is not None:
+      arrs = [np.ascontiguousarray(np.broadcast_to(a, (batch,) + a.shape)) for a in arrs]
+    if device is not None:
+      import torch
+      arrs = [torch.from_numpy(a).to(device) for a in arrs]
+    return QP(*arrs)
+
+  # ---- the step ---------------------------------------------------------------
+  def step(self, qp: QP, act) -> Tuple[QP, Info]:
+    """`System.step(qp, act) -> (qp, info)` (system.py:244-247)."""
+    if _is_torch(qp.pos):
+      return self._step_torch(qp, act, 1)
+    return self._step_numpy(qp, act)
+
+  def rollout(self, qp: QP, acts) -> Tuple[QP, Info]:
+    """T steps in ONE launch; acts is [T, B, A] (torch CUDA).  Returns the final
+    QP and the Info of the last step (lax.scan of System.step over actions)."""
+    return self._step_torch(qp, acts, int(acts.shape[0]))
+
+  def _shapes(self, pos_shape):
+    n = self.num_bodies
+    if len(pos_shape) == 2:
+      batched, b = False, 1
+    elif len(pos_shape) == 3:
+      batched, b = True, int(pos_shape[0])
+    else:
+      raise ValueError('qp.pos must be [N,3] or [B,N,3]')
+    if int(pos_shape[-2]) != n or int(pos_shape[-1]) != 3:
+      raise ValueError('qp.pos has shape %s, system has %d bodies' % (tuple(pos_shape), n))
+    return batched, b
+
+  def _wrap(self, out, batched) -> Tuple[QP, Info]:
+    if not batched:
+      out = {k: v[0] for k, v in out.items()}
+    qp = QP(out['pos_o'], out['rot_o'], out['vel_o'], out['ang_o'])
+    info = Info(P(out['contact_vel'], out['contact_ang']),
+                P(out['joint_vel'], out['joint_ang']),
+                P(out['actuator_vel'], out['actuator_ang']),
+                out['contact_pos'], out['contact_normal'],
+                out['contact_penetration'])
+    return qp, info
+
+  def _step_torch(self, qp: QP, act, steps: int):
+    import torch
+    batched, b = self._shapes(qp.pos.shape)
+    n, k, a = self.num_bodies, self.num_contacts, self.act_size
+    dev = qp.pos.device
+    if dev.type != 'cuda':
+      raise RuntimeError('torch tensors must live on a CUDA device (no CPU fallback)')
+    if dev.index is not None and dev.index != self.device:
+      raise RuntimeError('tensors are on %s, system is on cuda:%d' % (dev, self.device))
+
+    def prep(t, shape):
+      t = t.to(torch.float32).reshape(shape)
+      return t if t.is_contiguous() else t.contiguous()
+
+    ins = [prep(qp.pos, (b, n, 3)), prep(qp.rot, (b, n, 4)), prep(qp.vel, (b, n, 3)),
+           prep(qp.ang, (b, n, 3)),
+           prep(act, (steps, b, a) if steps > 1 else (b, a))]
+    out = {}
+    for name, w, dim in _OUT:
+      m = n if dim == 'n' else k
+      out[name] = torch.empty((b, m, w) if w else (b, m), dtype=torch.float32, device=dev)
+    io = CStepIO()
+    for f, t in zip(('pos', 'rot', 'vel', 'ang', 'act'), ins):
+      setattr(io, f, t.data_ptr())
+    for name, _, _ in _OUT:
+      setattr(io, name, out[name].data_ptr() if out[name].numel() else None)
+    stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    if steps > 1:
+      rc = self._lib.bx_rollout(self._h, b, steps, C.byref(io), stream)
+    else:
+      rc = self._lib.bx_step(self._h, b, C.byref(io), stream)
+    if rc != 0:
+      raise RuntimeError('bx_step: ' + _lib.last_error())
+    return self._wrap(out, batched)
+
+  def _step_numpy(self, qp: QP, act):
+    batched, b = self._shapes(np.shape(qp.pos))
+    n, k, a = self.num_bodies, self.num_contacts, self.act_size
+
+    def prep(x, shape):
+      return np.ascontiguousarray(np.asarray(x, dtype=np.float32).reshape(shape))
+
+    ins = [prep(qp.pos, (b, n, 3)), prep(qp.rot, (b, n, 4)), prep(qp.vel, (b, n, 3)),
+           prep(qp.ang, (b, n, 3)), prep(act, (b, a))]
+    out = {}
+    for name, w, dim in _OUT:
+      m = n if dim == 'n' else k
+      out[name] = np.empty((b, m, w) if w else (b, m), dtype=np.float32)
+    io = CStepIO()
+    for f, t in zip(('pos', 'rot', 'vel', 'ang', 'act'), ins):
+      setattr(io, f, t.ctypes.data)
+    for name, _, _ in _OUT:
+      setattr(io, name, out[name].ctypes.data if out[name].size else None)
+    rc = self._lib.bx_step_host(self._h, b, C.byref(io))
+    if rc != 0:
+      raise RuntimeError('bx_step_host: ' + _lib.last_error())
+    return self._wrap(out, batched)
+
+
+def load_system(name: str, device: int = 0) -> System:
+  """A system from the descriptors shipped in brax_b200/systems/ (extracted
+  from the reference's env configs by tools/gen_systems.py)."""
+  import os
+  path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'systems', name + '.json')
+  return System(SystemDesc.load(path), device)
