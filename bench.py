@@ -1,0 +1,334 @@
+"""bench.py -- env-steps/s of the fused Brax v1 `System.step` on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--env ant] [--envs 8192]
+  python bench.py --impl reference ...     # CPU arm (oracle port, all cores)
+
+A "step" is one `System.step` (all substeps) over the whole batch of
+environments with fresh U(-1,1) actions; the output state of step t is the
+input of step t+1.  Workload = BASELINE.json configs[1]: ant, 8192 envs per
+GPU, default substeps.  One JSON line is printed by rank 0.
+
+  value     env-steps/s, state resident in HBM, CUDA events around each step's
+            launch (summed), max over ranks; L2 is flushed between steps.
+  e2e       the same metric through the host-buffer C-ABI call (bx_step_host
+            via brax_b200.System.step on numpy views of pinned memory):
+            H2D of QP+act and D2H of QP+Info inside the timed region.
+  roofline  FP32-pipe bound (the path is ~50-100 flop/B): flops per
+            env-step (oracle/flops.json, counted from the oracle source) x
+            env-steps/s vs 148 SM x 128 lanes x 2 x sm clock; the HBM fraction
+            is reported beside it from the algorithmic bytes per env-step.
+  cpu_baseline  the C oracle port (float32, OpenMP over envs) on the host cores,
+            bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = 'env-steps/sec (Brax v1 System.step, all substeps)'
+UNIT = 'env-steps/s'
+SM_COUNT = 148
+FP32_LANES = 128
+
+
+def load_peaks():
+  p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+  if os.path.exists(p):
+    with open(p) as f:
+      d = json.load(f)
+    return d.get('hbm_gbs', 6650.0), d.get('sm_max_mhz', 1965.0), 'measured'
+  return 6650.0, 1965.0, 'fallback'
+
+
+def load_flops(env):
+  p = os.path.join(ROOT, 'oracle', 'flops.json')
+  if os.path.exists(p):
+    with open(p) as f:
+      d = json.load(f)
+    if env in d:
+      return d[env]
+  return None
+
+
+class ClockSampler:
+  """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+
+  def __init__(self, index):
+    self.index, self.rows, self._stop, self._t = index, [], False, None
+
+  def _run(self):
+    q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+    while not self._stop:
+      try:
+        out = subprocess.run(
+            ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + q,
+             '--format=csv,noheader,nounits'], capture_output=True, text=True,
+            timeout=5).stdout.strip()
+        if out:
+          self.rows.append([x.strip() for x in out.split(',')])
+      except Exception:
+        pass
+      time.sleep(0.1)
+
+  def __enter__(self):
+    self._t = threading.Thread(target=self._run, daemon=True)
+    self._t.start()
+    return self
+
+  def __exit__(self, *a):
+    self._stop = True
+    self._t.join(timeout=6)
+
+  def summary(self):
+    sm, mx, reasons = [], [], set()
+    names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+    for r in self.rows:
+      try:
+        sm.append(float(r[0])); mx.append(float(r[1]))
+      except Exception:
+        continue
+      for n, v in zip(names, r[2:6]):
+        if v.lower().startswith('active'):
+          reasons.add(n)
+    return {'sm_mhz': float(np.median(sm)) if sm else None,
+            'sm_max_mhz': float(max(mx)) if mx else None,
+            'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def make_state(desc, b, seed):
+  """default_qp + small velocity noise; warm-up steps then diversify it."""
+  rng = np.random.default_rng(seed)
+  d = desc.default_qp
+  pos = np.broadcast_to(np.asarray(d['pos'], np.float32), (b, desc.num_bodies, 3)).copy()
+  rot = np.broadcast_to(np.asarray(d['rot'], np.float32), (b, desc.num_bodies, 4)).copy()
+  vel = rng.uniform(-.1, .1, pos.shape).astype(np.float32)
+  ang = rng.uniform(-.1, .1, pos.shape).astype(np.float32)
+  mask_p = np.asarray([x['pos_mask'] for x in desc.bodies], np.float32)
+  mask_r = np.asarray([x['rot_mask'] for x in desc.bodies], np.float32)
+  return pos, rot, vel * mask_p, ang * mask_r
+
+
+def cpu_baseline(desc, env, b, budget_s=12.0, threads=0):
+  """Times the oracle port (float32, OpenMP over envs) on the host cores."""
+  from oracle.oracle import Oracle
+  o = Oracle(desc, np.float32)
+  cores = threads or (os.cpu_count() or 1)
+  rng = np.random.default_rng(7)
+  pos, rot, vel, ang = make_state(desc, b, 7)
+  act = rng.uniform(-1, 1, (b, desc.act_size)).astype(np.float32)
+  out = o.step(pos, rot, vel, ang, act, num_threads=cores)  # warm-up
+  t0, n = time.perf_counter(), 0
+  while True:
+    out = o.step(out['pos'], out['rot'], out['vel'], out['ang'], act, num_threads=cores)
+    n += 1
+    el = time.perf_counter() - t0
+    if el > budget_s or n >= 200:
+      break
+  return {'value': b * n / el, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+          'sample': '%s %d envs x %d steps (%.1f s), C oracle float32 + OpenMP' % (env, b, n, el)}
+
+
+def run_reference(args, desc):
+  """--impl reference: the reference's CPU implementation of the path.  JAX is
+  not installable here (no network), so this is the validated C port of the
+  reference's arithmetic on all host cores."""
+  rank = int(os.environ.get('RANK', '0'))
+  if rank != 0:
+    return
+  from oracle.oracle import Oracle
+  o = Oracle(desc, np.float32)
+  cores = os.cpu_count() or 1
+  b = args.envs  # per-step bounded sample: one GPU's shard of the workload
+  rng = np.random.default_rng(7)
+  pos, rot, vel, ang = make_state(desc, b, 7)
+  acts = rng.uniform(-1, 1, (args.steps + args.warmup, b, desc.act_size)).astype(np.float32)
+  st = {'pos': pos, 'rot': rot, 'vel': vel, 'ang': ang}
+  for i in range(args.warmup):
+    st = o.step(st['pos'], st['rot'], st['vel'], st['ang'], acts[i], num_threads=cores)
+  t0 = time.perf_counter()
+  for i in range(args.steps):
+    st = o.step(st['pos'], st['rot'], st['vel'], st['ang'], acts[args.warmup + i], num_threads=cores)
+  el = time.perf_counter() - t0
+  v = b * args.steps / el
+  sample = '%s %d envs per step (one GPU shard), C oracle float32 + OpenMP' % (args.env, b)
+  print(json.dumps({
+      'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': UNIT,
+      'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+      'ms_per_step': 1e3 * el / args.steps, 'higher_is_better': True,
+      'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+      'config': {'workload': '%s %d envs/GPU, default substeps' % (args.env, args.envs)},
+      'cpu_baseline': {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+      'e2e': {'value': v, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+  }))
+
+
+def run_gpu(args, desc):
+  import torch
+  import torch.distributed as dist
+  from brax_b200 import lib
+  from brax_b200.system import QP, System
+
+  world = int(os.environ.get('WORLD_SIZE', '1'))
+  rank = int(os.environ.get('RANK', '0'))
+  local = int(os.environ.get('LOCAL_RANK', '0'))
+  if world > 1:
+    dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+  torch.cuda.set_device(local)
+  dev = torch.device('cuda', local)
+  s = System(desc, device=local)
+  if args.threads:
+    s.configure(args.threads)
+  b, a, n, k = args.envs, desc.act_size, desc.num_bodies, desc.num_contacts
+  pos, rot, vel, ang = make_state(desc, b, 100 + rank)
+  qp = QP(*[torch.from_numpy(x).to(dev) for x in (pos, rot, vel, ang)])
+  gen = torch.Generator(device=dev)
+  gen.manual_seed(10_000 + rank)
+  total = args.steps + args.warmup
+  acts = torch.rand((total, b, a), generator=gen, device=dev) * 2 - 1
+  flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
+
+  def barrier():
+    if world > 1:
+      dist.barrier()
+    torch.cuda.synchronize()
+
+  for i in range(args.warmup):
+    qp, info = s.step(qp, acts[i])
+  barrier()
+  launches0 = lib.launch_count()
+  ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        for _ in range(args.steps)]
+  with ClockSampler(local) as clk:
+    barrier()
+    t_wall0 = time.perf_counter()
+    for i in range(args.steps):
+      flush.fill_(float(i))          # evict L2 between timed steps (not timed)
+      ev[i][0].record()
+      qp, info = s.step(qp, acts[args.warmup + i])
+      ev[i][1].record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    launches = lib.launch_count() - launches0   # kernels launched in the timed loop
+    # back-to-back (warm L2) for reference
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    q2 = qp
+    e0.record()
+    for i in range(args.steps):
+      q2, _ = s.step(q2, acts[args.warmup + i])
+    e1.record()
+    torch.cuda.synchronize()
+  ms_steps = [x.elapsed_time(y) for x, y in ev]
+  ms_total = float(sum(ms_steps))
+  ms_b2b = e0.elapsed_time(e1)
+  finite = bool(torch.isfinite(qp.pos).all().item())
+
+  # ---- e2e: host buffers through System.step (bx_step_host) ----------------
+  hq = [torch.from_numpy(x).pin_memory() for x in (pos, rot, vel, ang)]
+  hact = acts[args.warmup:].cpu().pin_memory()
+  hqp = QP(*[t.numpy() for t in hq])
+  e2e_steps = max(3, min(args.steps, 20))
+  for i in range(2):
+    hqp, hinfo = s.step(hqp, hact[i % hact.shape[0]].numpy())
+  barrier()
+  t0 = time.perf_counter()
+  for i in range(e2e_steps):
+    hqp, hinfo = s.step(hqp, hact[i % hact.shape[0]].numpy())
+  barrier()
+  t_e2e = time.perf_counter() - t0
+  h2d = 4 * b * (13 * n + a)
+  d2h = 4 * b * (13 * n + 18 * n + 7 * k)
+
+  # ---- max over ranks -----------------------------------------------------------
+  t = torch.tensor([ms_total, ms_b2b, t_e2e, t_wall], dtype=torch.float64, device=dev)
+  if world > 1:
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+  ms_total, ms_b2b, t_e2e, t_wall = [float(x) for x in t.tolist()]
+  value = world * b * args.steps / (ms_total * 1e-3)
+  value_b2b = world * b * args.steps / (ms_b2b * 1e-3)
+  e2e_value = world * b * e2e_steps / t_e2e
+
+  if rank == 0:
+    hbm_gbs, sm_max_mhz, src = load_peaks()
+    clocks = clk.summary()
+    flops = load_flops(args.env)
+    per_gpu = value / world
+    bytes_env = desc.bytes_per_env_step()
+    out = {
+        'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world,
+        'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': ms_total / args.steps, 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {
+            'workload': '%s %d envs/GPU, default substeps (%d), dynamics %s' % (
+                args.env, b, desc.substeps, desc.dynamics_mode),
+            'l2': 'flushed between timed steps (256 MiB fill outside the event pairs)',
+            'threads_per_tile': s_threads(s), 'bodies': n, 'contacts': k, 'act': a},
+        'value_back_to_back': value_b2b,
+        'wall_s_timed_loop_incl_flush': t_wall,
+        'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d,
+                'd2h_bytes_per_step': d2h, 'steps': e2e_steps},
+        'gpu_launches': int(launches),
+        'clocks': clocks, 'finite': finite,
+    }
+    hbm_ach = per_gpu * bytes_env / 1e9
+    roof_hbm = {'bound': 'hbm', 'achieved': hbm_ach, 'peak': hbm_gbs, 'unit': 'GB/s',
+                'frac': hbm_ach / hbm_gbs, 'traffic': None, 'peak_source': src,
+                'bytes_per_env_step': bytes_env}
+    if flops:
+      mhz = clocks['sm_mhz'] or sm_max_mhz
+      peak_max = SM_COUNT * FP32_LANES * 2 * sm_max_mhz * 1e6 / 1e12
+      ach = per_gpu * flops['flops'] / 1e12
+      out['roofline'] = {
+          'bound': 'fp32', 'achieved': ach, 'peak': peak_max, 'unit': 'TFLOP/s',
+          'frac': ach / peak_max, 'traffic': None,
+          'flops_per_env_step': flops['flops'],
+          'peak_at_observed_clock': SM_COUNT * FP32_LANES * 2 * mhz * 1e6 / 1e12,
+          'note': 'FP32 CUDA-core bound path (no contraction: tensor cores do not apply); '
+                  'peak = 148 SM x 128 lanes x 2 x sm_max_mhz'}
+      out['roofline_hbm'] = roof_hbm
+    else:
+      out['roofline'] = roof_hbm
+    if world == 1 and not args.no_cpu:
+      out['cpu_baseline'] = cpu_baseline(desc, args.env, min(b, 8192), budget_s=args.cpu_seconds)
+    print(json.dumps(out))
+  if world > 1:
+    dist.destroy_process_group()
+
+
+def s_threads(s):
+  return s.threads_per_tile
+
+
+def main():
+  ap = argparse.ArgumentParser()
+  ap.add_argument('--gpus', type=int, default=1)
+  ap.add_argument('--steps', type=int, default=100)
+  ap.add_argument('--warmup', type=int, default=10)
+  ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+  ap.add_argument('--env', default='ant')
+  ap.add_argument('--envs', type=int, default=8192, help='environments per GPU')
+  ap.add_argument('--threads', type=int, default=0, help='threads per 32-env tile (0 = default)')
+  ap.add_argument('--cpu-seconds', type=float, default=12.0)
+  ap.add_argument('--no-cpu', action='store_true')
+  args = ap.parse_args()
+  from brax_b200.desc import SystemDesc
+  desc = SystemDesc.load(os.path.join(ROOT, 'brax_b200', 'systems', args.env + '.json'))
+  if args.impl == 'reference':
+    run_reference(args, desc)
+  else:
+    run_gpu(args, desc)
+
+
+if __name__ == '__main__':
+  main()

@@ -80,6 +80,7 @@ class System:
     if rc != 0:
       raise RuntimeError('bx_system_create: ' + _lib.last_error())
     self._h = handle
+    self.threads_per_tile = 0  # 0 = library default
 
   @classmethod
   def from_brax(cls, brax_system, name: str = 'system', act_size=None,
@@ -100,6 +101,7 @@ class System:
     """Warps per 32-env tile = threads_per_block / 32 (tuning knob)."""
     if self._lib.bx_system_configure(self._h, threads_per_block, 0) != 0:
       raise ValueError(_lib.last_error())
+    self.threads_per_tile = threads_per_block
 
   # ---- state helpers ---------------------------------------------------------
   def default_qp(self, batch: int = None, device=None) -> QP:
