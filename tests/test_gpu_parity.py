@@ -1,0 +1,316 @@
+"""Parity of the sm_100a `System.step` kernel with the oracle (GPU box only).
+
+Every call goes through the C ABI (`bx_step` / `bx_step_host` / `bx_rollout`,
+include/brax_b200.h) via the host mirror `brax_b200.System.step`.
+
+Tolerances (north star: rel 1e-5 / abs 1e-6 single step, contact flags exact):
+
+  pos, rot      |d| <= 1e-6 + 1e-5 |ref|                           (as stated)
+  vel, ang      |d| <= 1e-6 + 1e-5 |ref| + VEL_ULPS * ulp(pos) / dt_sub
+                velocity_projection sets vel = (pos - pos_prev) / dt_sub
+                (integrators.py:139-141): ONE float32 ulp of a position near 1
+                (6e-8..1.2e-7) is 1e-5..6e-5 of velocity at dt_sub = 0.005 ..
+                0.001875, so two correct float32 evaluation orders (FMA
+                contraction here vs none in the oracle) differ by that much;
+                SURVEY.md section 7 "hard parts".
+  contact flags `contact_penetration > 0` bit-exact; a mismatch is tolerated
+                only where the oracle's |penetration| < 1e-6 and is counted.
+"""
+import numpy as np
+import pytest
+
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+VEL_ULPS = 8.0
+GOLDEN = util.golden_names()
+
+
+def _torch():
+  import torch
+  if not torch.cuda.is_available():
+    pytest.skip('no CUDA device')
+  return torch
+
+
+def _system(name):
+  from brax_b200.system import load_system
+  return load_system(name)
+
+
+def _oracle(name, dtype=np.float32):
+  from oracle.oracle import Oracle
+  return Oracle(util.load_desc(name), dtype)
+
+
+def _flat(qp, info):
+  out = {'pos': qp.pos, 'rot': qp.rot, 'vel': qp.vel, 'ang': qp.ang,
+         'contact_vel': info.contact.vel, 'contact_ang': info.contact.ang,
+         'joint_vel': info.joint.vel, 'joint_ang': info.joint.ang,
+         'actuator_vel': info.actuator.vel, 'actuator_ang': info.actuator.ang,
+         'contact_pos': info.contact_pos, 'contact_normal': info.contact_normal,
+         'contact_penetration': info.contact_penetration}
+  return {k: (v.cpu().numpy() if hasattr(v, 'cpu') else np.asarray(v)) for k, v in out.items()}
+
+
+def _vel_slack(desc, ref_pos):
+  ulp = np.spacing(np.maximum(np.abs(ref_pos), 1e-3).astype(np.float32)).max()
+  return VEL_ULPS * float(ulp) / desc.dt_sub
+
+
+def check_step(desc, got, ref, where):
+  for k in ('pos', 'rot'):
+    tol = 1e-6 + 1e-5 * np.abs(ref[k])
+    bad = np.abs(got[k] - ref[k]) > tol
+    assert not bad.any(), (where, k, float(np.abs(got[k] - ref[k]).max()))
+  slack = _vel_slack(desc, ref['pos'])
+  for k in ('vel', 'ang'):
+    tol = 1e-6 + 1e-5 * np.abs(ref[k]) + slack
+    # ang = 2 dq.xyz / dt: one ulp of a unit quaternion component
+    if k == 'ang':
+      tol = tol + VEL_ULPS * 2 * 6e-8 / desc.dt_sub
+    bad = np.abs(got[k] - ref[k]) > tol
+    assert not bad.any(), (where, k, float(np.abs(got[k] - ref[k]).max()), slack)
+  pen = ref['contact_penetration']
+  if pen.size:
+    mism = (got['contact_penetration'] > 0) != (pen > 0)
+    hard = mism & (np.abs(pen) >= 1e-6)
+    assert not hard.any(), (where, 'contact flags', int(hard.sum()))
+    assert np.abs(got['contact_penetration'] - pen).max() <= 1e-5, where
+    assert np.abs(got['contact_pos'] - ref['contact_pos']).max() <= 1e-5, where
+    assert np.abs(got['contact_normal'] - ref['contact_normal']).max() <= 1e-5, where
+  # Info impulses are sums of velocity-level quantities
+  for k in ('contact_vel', 'contact_ang', 'actuator_vel', 'actuator_ang',
+            'joint_vel', 'joint_ang'):
+    scale = max(1.0, float(np.abs(ref[k]).max()))
+    tol = 2e-5 * scale + 4 * slack
+    assert np.abs(got[k] - ref[k]).max() <= tol, (where, k, float(np.abs(got[k] - ref[k]).max()))
+
+
+@pytest.mark.parametrize('name', GOLDEN)
+def test_single_step_matches_oracle_on_golden_inputs(name):
+  """Kernel vs float32 oracle on the reference-generated golden inputs, device
+  path (torch tensors -> bx_step)."""
+  torch = _torch()
+  from brax_b200.system import QP
+  g = util.load_golden(name)
+  s = _system(name)
+  ins = [np.ascontiguousarray(g[k].astype(np.float32)) for k in util.QP_KEYS]
+  act = np.ascontiguousarray(g['act'].astype(np.float32))
+  qp = QP(*[torch.from_numpy(x).cuda() for x in ins])
+  qo, info = s.step(qp, torch.from_numpy(act).cuda())
+  torch.cuda.synchronize()
+  got = _flat(qo, info)
+  ref = _oracle(name).step(*ins, act)
+  check_step(s.desc, got, ref, name)
+
+
+@pytest.mark.parametrize('name', GOLDEN)
+def test_single_step_close_to_reference_f64(name):
+  """Kernel vs the reference's own float64 outputs (golden fixtures): the
+  float32-vs-float64 gap, asserted at the level the float32 oracle shows."""
+  _torch()
+  from brax_b200.system import QP
+  g = util.load_golden(name)
+  s = _system(name)
+  qp = QP(*[g[k].astype(np.float32) for k in util.QP_KEYS])
+  qo, info = s.step(qp, g['act'].astype(np.float32))  # host path: bx_step_host
+  got = _flat(qo, info)
+  for k in ('pos', 'rot'):
+    ref = g[k + '_o']
+    assert np.all(np.abs(got[k] - ref) <= 1e-4 + 1e-5 * np.abs(ref)), (name, k)
+  ref = g['contact_penetration']
+  if ref.size:
+    bad = ((got['contact_penetration'] > 0) != (ref > 0)) & (np.abs(ref) > 1e-5)
+    assert not bad.any(), name
+
+
+def _harvest(s, b, steps, seed):
+  """States with active contacts: roll the KERNEL forward from a noisy reset
+  (the states are inputs only; parity is judged on the step that follows)."""
+  import torch
+  from brax_b200.system import QP
+  rng = np.random.default_rng(seed)
+  d = s.desc
+  q0 = s.default_qp(batch=b)
+  mp = np.asarray([x['pos_mask'] for x in d.bodies], np.float32)
+  mr = np.asarray([x['rot_mask'] for x in d.bodies], np.float32)
+  vel = rng.uniform(-.3, .3, q0.pos.shape).astype(np.float32) * mp
+  ang = rng.uniform(-.3, .3, q0.pos.shape).astype(np.float32) * mr
+  qp = QP(*[torch.from_numpy(np.ascontiguousarray(x)).cuda() for x in (q0.pos, q0.rot, vel, ang)])
+  for t in range(steps):
+    act = torch.from_numpy(rng.uniform(-1, 1, (b, d.act_size)).astype(np.float32)).cuda()
+    qp, _ = s.step(qp, act)
+  torch.cuda.synchronize()
+  return qp, rng
+
+
+@pytest.mark.parametrize('name,b,steps', [
+    ('ant', 2048, 30), ('humanoid', 2048, 30), ('grasp', 1024, 20),
+    ('fetch', 1024, 20), ('ant_spring', 1024, 30), ('humanoid_spring', 1024, 30)])
+def test_single_step_on_harvested_states(name, b, steps):
+  torch = _torch()
+  s = _system(name)
+  qp, rng = _harvest(s, b, steps, 5)
+  assert bool(torch.isfinite(qp.pos).all())
+  act = rng.uniform(-1, 1, (b, s.act_size)).astype(np.float32)
+  qo, info = s.step(qp, torch.from_numpy(act).cuda())
+  torch.cuda.synchronize()
+  got = _flat(qo, info)
+  ins = [getattr(qp, k).cpu().numpy() for k in util.QP_KEYS]
+  ref = _oracle(name).step(*ins, act)
+  # at least some contacts must be active for the test to mean anything
+  assert (ref['contact_penetration'] > 0).mean() > 0.02, name
+  check_step(s.desc, got, ref, name)
+
+
+@pytest.mark.parametrize('name', ['ant', 'humanoid', 'grasp'])
+def test_rollout_10_steps(name):
+  """10-step rollouts vs the float32 oracle (north star: 'rollouts up to 10
+  steps ... within a stated tolerance'): abs 2e-3 on pos/rot -- contact-rich
+  PBD amplifies the single-step ulp differences."""
+  torch = _torch()
+  from brax_b200.system import QP
+  s = _system(name)
+  b = 256
+  qp, rng = _harvest(s, b, 5, 11)
+  o = _oracle(name)
+  ref = {k: getattr(qp, k).cpu().numpy() for k in util.QP_KEYS}
+  acts = rng.uniform(-1, 1, (10, b, s.act_size)).astype(np.float32)
+  for t in range(10):
+    qp, info = s.step(qp, torch.from_numpy(acts[t]).cuda())
+    r = o.step(ref['pos'], ref['rot'], ref['vel'], ref['ang'], acts[t])
+    ref = {k: r[k] for k in util.QP_KEYS}
+  got = _flat(qp, info)
+  err_p = np.abs(got['pos'] - ref['pos']).max(axis=(1, 2))
+  err_r = np.abs(got['rot'] - ref['rot']).max(axis=(1, 2))
+  # a handful of envs may flip a contact decision at a threshold; the bulk must agree
+  assert np.quantile(err_p, 0.99) <= 2e-3, float(np.quantile(err_p, 0.99))
+  assert np.quantile(err_r, 0.99) <= 2e-3, float(np.quantile(err_r, 0.99))
+  assert np.median(err_p) <= 1e-4
+
+
+def test_rollout_entry_point_equals_repeated_steps():
+  """bx_rollout(T) is bit-identical to T bx_step calls."""
+  torch = _torch()
+  s = _system('ant')
+  b, t_n = 300, 7
+  qp, rng = _harvest(s, b, 3, 3)
+  acts = torch.from_numpy(rng.uniform(-1, 1, (t_n, b, s.act_size)).astype(np.float32)).cuda()
+  q1 = qp
+  for t in range(t_n):
+    q1, i1 = s.step(q1, acts[t])
+  q2, i2 = s.rollout(qp, acts)
+  torch.cuda.synchronize()
+  a, c = _flat(q1, i1), _flat(q2, i2)
+  for k in a:
+    np.testing.assert_array_equal(a[k], c[k], err_msg=k)
+
+
+@pytest.mark.parametrize('name', ['ant', 'humanoid', 'grasp', 'fetch'])
+def test_batch_shape_edge_cases(name):
+  """B = 1, unbatched, ragged B (not a multiple of the 32-env tile) and the
+  host path give exactly the values of the same envs inside a big batch."""
+  torch = _torch()
+  from brax_b200.system import QP
+  s = _system(name)
+  b = 133
+  qp, rng = _harvest(s, b, 6, 9)
+  act = torch.from_numpy(rng.uniform(-1, 1, (b, s.act_size)).astype(np.float32)).cuda()
+  full = _flat(*s.step(qp, act))
+  for sel in (slice(0, 1), slice(5, 38), slice(100, 133)):
+    sub = QP(*[getattr(qp, k)[sel].contiguous() for k in util.QP_KEYS])
+    part = _flat(*s.step(sub, act[sel].contiguous()))
+    for k in full:
+      np.testing.assert_array_equal(full[k][sel], part[k], err_msg='%s %s' % (k, sel))
+  one = QP(*[getattr(qp, k)[7] for k in util.QP_KEYS])
+  un = _flat(*s.step(one, act[7]))
+  for k in full:
+    assert un[k].shape == full[k].shape[1:]
+    np.testing.assert_array_equal(full[k][7], un[k], err_msg=k)
+  host = QP(*[getattr(qp, k).cpu().numpy() for k in util.QP_KEYS])
+  hp = _flat(*s.step(host, act.cpu().numpy()))
+  for k in full:
+    np.testing.assert_array_equal(full[k], hp[k], err_msg=k)
+
+
+@pytest.mark.parametrize('name,b', [('ant', 8192), ('humanoid', 8192), ('grasp', 4096)])
+def test_full_size_properties(name, b):
+  """BASELINE.json sizes: size-independent properties of `System.step`."""
+  torch = _torch()
+  from brax_b200.system import QP
+  s = _system(name)
+  d = s.desc
+  qp, rng = _harvest(s, b, 20, 21)
+  act = torch.from_numpy(rng.uniform(-1, 1, (b, d.act_size)).astype(np.float32)).cuda()
+  q1, i1 = s.step(qp, act)
+  q2, i2 = s.step(qp, act)
+  a, c = _flat(q1, i1), _flat(q2, i2)
+  for k in a:  # deterministic
+    assert np.isfinite(a[k]).all(), k
+    np.testing.assert_array_equal(a[k], c[k], err_msg=k)
+  # permutation equivariance: envs are independent (no cross-env term)
+  perm = torch.from_numpy(np.random.default_rng(0).permutation(b)).cuda()
+  qpp = QP(*[getattr(qp, k)[perm].contiguous() for k in util.QP_KEYS])
+  p = _flat(*s.step(qpp, act[perm].contiguous()))
+  pn = perm.cpu().numpy()
+  for k in a:
+    np.testing.assert_array_equal(a[k][pn], p[k], err_msg=k)
+  # unit quaternions out (integrators.py:144 renormalises)
+  nrm = np.linalg.norm(a['rot'], axis=-1)
+  assert np.abs(nrm - 1).max() <= 1e-5
+  # frozen degrees of freedom stay put (integrators.py:38-44 masks)
+  mp = np.asarray([x['pos_mask'] for x in d.bodies], np.float32)
+  mr = np.asarray([x['rot_mask'] for x in d.bodies], np.float32)
+  pos_in = qp.pos.cpu().numpy()
+  assert np.abs((a['pos'] - pos_in) * (1 - mp)).max() == 0
+  assert np.abs(a['vel'] * (1 - mp)).max() == 0
+  assert np.abs(a['ang'] * (1 - mr)).max() == 0
+  # pbd: info.joint is identically zero (system.py:315)
+  if d.dynamics_mode == 'pbd':
+    assert np.abs(a['joint_vel']).max() == 0 and np.abs(a['joint_ang']).max() == 0
+  # random subset against the oracle
+  idx = np.sort(np.random.default_rng(1).choice(b, 512, replace=False))
+  ins = [getattr(qp, k).cpu().numpy()[idx] for k in util.QP_KEYS]
+  ref = _oracle(name).step(*ins, act.cpu().numpy()[idx])
+  check_step(d, {k: v[idx] for k, v in a.items()}, ref, name)
+
+
+def test_free_body_is_a_projectile():
+  """Known answer (tests/physics_test.py:32-48 style): a free body with no
+  joints/contacts moves by vel*dt per substep and keeps its velocity."""
+  torch = _torch()
+  from brax_b200.desc import SystemDesc
+  from brax_b200.system import QP, System
+  import dataclasses
+  d = util.load_desc('ant')
+  body = dict(d.bodies[0])
+  d2 = dataclasses.replace(d, bodies=[body], joints=[], actuators=[], forces=[], pairs=[],
+                           num_collider_groups=0, act_size=1, gravity=[0., 0., -9.8],
+                           velocity_damping=0., angular_damping=0.,
+                           body_names=['b'], default_qp={}, reset={})
+  s = System(d2)
+  qp = QP(np.array([[[0., 0., 1.]]], np.float32), np.array([[[1., 0., 0., 0.]]], np.float32),
+          np.array([[[1., 0., 0.]]], np.float32), np.zeros((1, 1, 3), np.float32))
+  qo, _ = s.step(qp, np.zeros((1, 1), np.float32))
+  n = (d.substeps // 2) * 2
+  h = d.dt_sub
+  # semi-implicit Euler: v_k = v0 + g h k ; z_n = z0 + h * sum v_k
+  vz = -9.8 * h * n
+  z = 1. + h * sum(-9.8 * h * k for k in range(1, n + 1))
+  assert abs(qo.vel[0, 0, 2] - vz) <= 3e-4  # one ulp(pos)/dt_sub = 2.4e-5 per substep
+  assert abs(qo.pos[0, 0, 2] - z) <= 1e-5
+  assert abs(qo.pos[0, 0, 0] - h * n) <= 1e-5
+
+
+def test_errors_are_loud():
+  torch = _torch()
+  from brax_b200.system import QP
+  s = _system('ant')
+  q = s.default_qp(batch=4)
+  with pytest.raises(ValueError):
+    s.step(QP(q.pos[:, :5], q.rot, q.vel, q.ang), np.zeros((4, 8), np.float32))
+  with pytest.raises(RuntimeError):
+    s.step(QP(*[torch.from_numpy(x) for x in (q.pos, q.rot, q.vel, q.ang)]),
+           torch.zeros(4, 8))  # CPU torch tensors: no CPU fallback
