@@ -169,7 +169,7 @@ BXD void joint_axis_angle(int kind, const float* jf, Q4 rp, Q4 rc, V3* axis,
 // Writes the torque VECTOR of actuator a to rows JS+3a and the damping torque of
 // joint j to rows JS+3(na+j); the body phase turns them into angular
 // accelerations (actuators.py:52-112, joints.py:103-128).
-__device__ __noinline__ void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
+__device__ __forceinline__ void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
   const int rrot = c.cur ? h.r_rot1 : h.r_rot0;
   for (int a = c.warp; a < h.na; a += c.nwarp) {
     const int32_t* ai = c.ti + h.io_act + a * AI_STRIDE;
@@ -294,7 +294,7 @@ BXD void velocity_projection(const BxHeader& h, const float* bf, V3 pos, V3 ppos
 // ---- phase B1 (pbd): acceleration update + kinetic step, per body ------------
 // system.py:268-274 / :287-293.  Reads pos/rot from buffer cur, writes the
 // advanced pos/rot into buffer cur^1 (buffer cur then IS qprev).
-__device__ __noinline__ void phase_body_acc_kinetic(const Ctx& c, const BxHeader& h,
+__device__ __forceinline__ void phase_body_acc_kinetic(const Ctx& c, const BxHeader& h,
                                                     bool accumulate_info) {
   const int rpos = c.cur ? h.r_pos1 : h.r_pos0, rrot = c.cur ? h.r_rot1 : h.r_rot0;
   const int npos = c.cur ? h.r_pos0 : h.r_pos1, nrot = c.cur ? h.r_rot0 : h.r_rot1;
@@ -372,7 +372,7 @@ BXD void limit_angle(V3 n, V3 n_1, V3 n_2, float lo, float hi, V3 ii_p, V3 ii_c,
 // ---- phase J (pbd): Joint.apply for every joint -> per-joint delta slots -------
 // joints.py:79-100, Revolute :270-309, Spherical :332-386.  Slot of joint j:
 // rows JS+14j .. +6 = parent (pos3, rot4), +7 .. +13 = child.
-__device__ __noinline__ void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
+__device__ __forceinline__ void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
   const int rpos = c.cur ? h.r_pos1 : h.r_pos0, rrot = c.cur ? h.r_rot1 : h.r_rot0;
   for (int j = c.warp; j < h.nj; j += c.nwarp) {
     const int32_t* ji = c.ti + h.io_joint + j * JI_STRIDE;
@@ -432,7 +432,7 @@ __device__ __noinline__ void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
 
 // ---- phase B2 (pbd): apply joint deltas (+ velocity projection in half A) ---
 // integrators.py:103-110 then :122-146; system.py:277-281 / :296-297.
-__device__ __noinline__ void phase_body_joint_update(const Ctx& c, const BxHeader& h,
+__device__ __forceinline__ void phase_body_joint_update(const Ctx& c, const BxHeader& h,
                                                      bool project) {
   const int rpos = c.cur ? h.r_pos1 : h.r_pos0, rrot = c.cur ? h.r_rot1 : h.r_rot0;
   const int ppos = c.cur ? h.r_pos0 : h.r_pos1, prot = c.cur ? h.r_rot0 : h.r_rot1;
@@ -546,7 +546,7 @@ BXD Contact contact_fn(const Ctx& c, const BxHeader& h, int kind, const float* c
 // colliders.py:198-240, OneWay :306-377, TwoWay :495-582.  Row k keeps its
 // contact (pos3 normal3 pen dlambda) in rows CT+8k and its deltas (a: pos3 rot4
 // [, b: pos3 rot4]) in rows JS+delta_off(k).
-__device__ __noinline__ void phase_contacts_position(const Ctx& c, const BxHeader& h) {
+__device__ __forceinline__ void phase_contacts_position(const Ctx& c, const BxHeader& h) {
   const int rpos = c.cur ? h.r_pos1 : h.r_pos0, rrot = c.cur ? h.r_rot1 : h.r_rot0;
   const int ppos = c.cur ? h.r_pos0 : h.r_pos1, prot = c.cur ? h.r_rot0 : h.r_rot1;
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
@@ -671,7 +671,7 @@ BXD void gather_contact_deltas(const Ctx& c, const BxHeader& h, const int32_t* b
 
 // ---- phase B3 (pbd): apply contact deltas, keep qp_right_before's velocities,
 // velocity projection.  system.py:299-307.
-__device__ __noinline__ void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
+__device__ __forceinline__ void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
   const int rpos = c.cur ? h.r_pos1 : h.r_pos0, rrot = c.cur ? h.r_rot1 : h.r_rot0;
   const int ppos = c.cur ? h.r_pos0 : h.r_pos1, prot = c.cur ? h.r_rot0 : h.r_rot1;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
@@ -703,7 +703,7 @@ __device__ __noinline__ void phase_body_contact_update(const Ctx& c, const BxHea
 // ---- phase C2 (pbd): _velocity_contact for every contact row ------------------
 // colliders.py:155-196, OneWay :379-442, TwoWay :584-658.  Deltas (a: vel3 ang3
 // [, b: vel3 ang3]) go to rows JS+delta_off(k).
-__device__ __noinline__ void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
+__device__ __forceinline__ void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
   const int rpos = c.cur ? h.r_pos1 : h.r_pos0;
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
     const int32_t* ci = c.ti + h.io_contact + k * CI_STRIDE;
@@ -784,7 +784,7 @@ __device__ __noinline__ void phase_contacts_velocity(const Ctx& c, const BxHeade
 
 // ---- phase B4: velocity-level contact update + Info.contact -----------------
 // integrators.py:97-101; system.py:313,315 (pbd) / :365,367 (legacy_spring).
-__device__ __noinline__ void phase_body_velocity_update(const Ctx& c, const BxHeader& h,
+__device__ __forceinline__ void phase_body_velocity_update(const Ctx& c, const BxHeader& h,
                                                         float eps) {
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
@@ -809,7 +809,7 @@ BXD void body_impulse(float mass, V3 inv_i, V3 bpos, V3 imp, V3 at, V3* dvel, V3
 }
 
 // phase S1: kinetic step for every body, in place (system.py:352).
-__device__ __noinline__ void phase_body_kinetic(const Ctx& c, const BxHeader& h) {
+__device__ __forceinline__ void phase_body_kinetic(const Ctx& c, const BxHeader& h) {
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const float* bf = c.tf + h.fo_body + b * BF_STRIDE;
     V3 pos = ld3(c, h.r_pos0 + 3 * b);
@@ -822,7 +822,7 @@ __device__ __noinline__ void phase_body_kinetic(const Ctx& c, const BxHeader& h)
 
 // phase S2: spring joints (spring_joints.py:89-303) -> slot rows
 // JS+3na+12j: parent vel3 ang3, child vel3 ang3.
-__device__ __noinline__ void phase_joints_spring(const Ctx& c, const BxHeader& h) {
+__device__ __forceinline__ void phase_joints_spring(const Ctx& c, const BxHeader& h) {
   for (int j = c.warp; j < h.nj; j += c.nwarp) {
     const int32_t* ji = c.ti + h.io_joint + j * JI_STRIDE;
     const float* jf = c.tf + h.fo_joint + j * JF_STRIDE;
@@ -880,7 +880,7 @@ __device__ __noinline__ void phase_joints_spring(const Ctx& c, const BxHeader& h
 
 // phase S3: acceleration update from joints + actuators + forces; Info.joint and
 // Info.actuator accumulation (system.py:356-359,367).
-__device__ __noinline__ void phase_body_acc_spring(const Ctx& c, const BxHeader& h) {
+__device__ __forceinline__ void phase_body_acc_spring(const Ctx& c, const BxHeader& h) {
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
     const float* bf = c.tf + h.fo_body + b * BF_STRIDE;
@@ -913,7 +913,7 @@ __device__ __noinline__ void phase_body_acc_spring(const Ctx& c, const BxHeader&
 
 // phase S4: contact_fn + velocity-level _contact (colliders.py:116-153,
 // OneWay :267-304, TwoWay :449-493).
-__device__ __noinline__ void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
+__device__ __forceinline__ void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
     const int32_t* ci = c.ti + h.io_contact + k * CI_STRIDE;
     const float* cf = c.tf + h.fo_contact + k * CF_STRIDE;
