@@ -373,7 +373,11 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   if (e1 != cudaSuccess || e2 != cudaSuccess) { delete s; return fail("cudaMalloc of tables failed"); }
   CUDA_OK(cudaMemcpy(s->d_tab_i, ti.data(), ti.size() * 4, cudaMemcpyHostToDevice));
   CUDA_OK(cudaMemcpy(s->d_tab_f, tf.data(), tf.size() * 4, cudaMemcpyHostToDevice));
-  CUDA_OK(cudaFuncSetAttribute(bx_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  CUDA_OK(cudaFuncSetAttribute(bx_step_kernel<BX_MODE_PBD>,
+                               cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               prop.sharedMemPerBlockOptin));
+  CUDA_OK(cudaFuncSetAttribute(bx_step_kernel<BX_MODE_LEGACY_SPRING>,
+                               cudaFuncAttributeMaxDynamicSharedMemorySize,
                                prop.sharedMemPerBlockOptin));
   *out = s;
   return 0;
@@ -418,7 +422,10 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   p.num_steps = num_steps;
   const int64_t tiles = (num_envs + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA;
   if (tiles > 0x7fffffffLL) return fail("too many environments for one launch");
-  bx_step_kernel<<<static_cast<unsigned>(tiles), 32 * s->warps, s->smem_bytes, stream>>>(p);
+  if (s->h.mode == BX_MODE_PBD)
+    bx_step_kernel<BX_MODE_PBD><<<static_cast<unsigned>(tiles), 32 * s->warps, s->smem_bytes, stream>>>(p);
+  else
+    bx_step_kernel<BX_MODE_LEGACY_SPRING><<<static_cast<unsigned>(tiles), 32 * s->warps, s->smem_bytes, stream>>>(p);
   g_launches.fetch_add(1);
   CUDA_OK(cudaGetLastError());
   return 0;

