@@ -237,7 +237,7 @@ def run_gpu(args, desc):
   hq = [torch.from_numpy(x).pin_memory() for x in (pos, rot, vel, ang)]
   hact = acts[args.warmup:].cpu().pin_memory()
   hqp = QP(*[t.numpy() for t in hq])
-  e2e_steps = max(3, min(args.steps, 20))
+  e2e_steps = 1 if args.no_e2e else max(3, min(args.steps, 20))
   for i in range(2):
     hqp, hinfo = s.step(hqp, hact[i % hact.shape[0]].numpy())
   barrier()
@@ -321,6 +321,7 @@ def main():
   ap.add_argument('--threads', type=int, default=0, help='threads per 32-env tile (0 = default)')
   ap.add_argument('--cpu-seconds', type=float, default=12.0)
   ap.add_argument('--no-cpu', action='store_true')
+  ap.add_argument('--no-e2e', action='store_true')
   args = ap.parse_args()
   from brax_b200.desc import SystemDesc
   desc = SystemDesc.load(os.path.join(ROOT, 'brax_b200', 'systems', args.env + '.json'))

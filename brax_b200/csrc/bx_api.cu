@@ -365,9 +365,11 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
     delete s;
     return fail("system state does not fit in shared memory (too many bodies/joints/contacts)");
   }
-  // default warps per tile: enough to split the widest phase, capped at 8
-  int widest = std::max(std::max(s->h.nj, s->h.nk), std::max(s->h.na, 1));
-  s->warps = std::min(8, std::max(2, (widest + 1) / 2));
+  // default warps per tile (measured on B200, profiles/): one warp per joint /
+  // per two contact rows; between 9 and 12 warps the 114-register kernel would
+  // drop to one CTA per SM without shortening any phase, so stay at 8 there.
+  int widest = std::max(std::max(s->h.nj, (s->h.nk + 1) / 2), std::max(s->h.na, 2));
+  s->warps = widest <= 8 ? widest : (widest <= 12 ? 8 : 16);
   cudaError_t e1 = cudaMalloc(&s->d_tab_i, std::max<size_t>(ti.size(), 1) * 4);
   cudaError_t e2 = cudaMalloc(&s->d_tab_f, std::max<size_t>(tf.size(), 1) * 4);
   if (e1 != cudaSuccess || e2 != cudaSuccess) { delete s; return fail("cudaMalloc of tables failed"); }

@@ -27,7 +27,20 @@
 static int omp_get_max_threads_wrap(void) { return omp_get_max_threads(); }
 #endif
 
-#ifdef BXO_DOUBLE
+#ifdef BXO_COUNT
+/* operation-counting build (C++): see oracle/flopcount.hpp */
+#include "flopcount.hpp"
+double bxo_counters[CNT_N];
+typedef CR R;
+#define FN(n) n##_cnt
+#define SQRT cr_sqrt
+#define SIN cr_sin
+#define COS cr_cos
+#define ATAN2 cr_atan2
+#define ACOS cr_acos
+#define FABS cr_fabs
+#define _Thread_local thread_local
+#elif defined(BXO_DOUBLE)
 typedef double R;
 #define FN(n) n##_f64
 #define SQRT sqrt
@@ -1500,3 +1513,10 @@ int FN(bxo_pair_contacts)(const osys* s, int pair_index, const R* pos, const R* 
   }
   return 0;
 }
+
+#ifdef BXO_COUNT
+/* C-linkage entry of the counting build (oracle/count_flops.py) */
+extern "C" int bxo_step_count(const osys* s, int64_t num_envs, const oio* io) {
+  return FN(bxo_step)(s, num_envs, io, 1);
+}
+#endif
