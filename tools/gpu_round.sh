@@ -6,7 +6,7 @@ O=gpurun_out/$TAG
 mkdir -p $O
 nvidia-smi -L > $O/gpu.txt 2>&1; nproc >> $O/gpu.txt
 python -c "import jax; print('jax', jax.__version__)" >> $O/gpu.txt 2>&1
-timeout 900 python -m pytest tests -m gpu -q -x --timeout 600 > $O/pytest.log 2>&1; echo "pytest rc=$?" >> $O/pytest.log
+timeout 900 python -m pytest tests -m gpu -q --timeout 600 > $O/pytest.log 2>&1; echo "pytest rc=$?" >> $O/pytest.log
 timeout 300 python tools/parity_report.py > $O/parity.txt 2>&1
 timeout 120 python __graft_entry__.py smoke > $O/smoke.log 2>&1; echo "smoke rc=$?" >> $O/smoke.log
 timeout 300 python bench.py > $O/bench_ant.json 2> $O/bench_ant.err
