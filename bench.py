@@ -36,6 +36,9 @@ sys.path.insert(0, ROOT)
 METRIC = 'env-steps/sec (Brax v1 System.step, all substeps)'
 UNIT = 'env-steps/s'
 SM_COUNT = 148
+# dram__bytes_read.sum + dram__bytes_write.sum of one bx_step_kernel launch at the
+# bench workload, from the committed `ncu --set full` capture (profiles/); bytes.
+NCU_TRAFFIC = {'ant': 4664576}
 FP32_LANES = 128
 
 
@@ -250,10 +253,9 @@ def run_gpu(args, desc):
   d2h = 4 * b * (13 * n + 18 * n + 7 * k)
 
   # ---- max over ranks -----------------------------------------------------------
-  t = torch.tensor([ms_total, ms_b2b, t_e2e, t_wall], dtype=torch.float64, device=dev)
-  if world > 1:
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-  ms_total, ms_b2b, t_e2e, t_wall = [float(x) for x in t.tolist()]
+  from brax_b200 import shard
+  ms_total, ms_b2b, t_e2e, t_wall = shard.reduce_stats(
+      [ms_total, ms_b2b, t_e2e, t_wall], ['max'] * 4, device=dev)
   value = world * b * args.steps / (ms_total * 1e-3)
   value_b2b = world * b * args.steps / (ms_b2b * 1e-3)
   e2e_value = world * b * e2e_steps / t_e2e
@@ -281,24 +283,26 @@ def run_gpu(args, desc):
         'gpu_launches': int(launches),
         'clocks': clocks, 'finite': finite,
     }
+    # dominant (only) kernel: bx_step_kernel, one launch per step; its average
+    # duration IS ms_per_step (CUDA events bracket each launch on its stream).
     hbm_ach = per_gpu * bytes_env / 1e9
-    roof_hbm = {'bound': 'hbm', 'achieved': hbm_ach, 'peak': hbm_gbs, 'unit': 'GB/s',
-                'frac': hbm_ach / hbm_gbs, 'traffic': None, 'peak_source': src,
-                'bytes_per_env_step': bytes_env}
+    out['roofline'] = {
+        'bound': 'hbm', 'achieved': hbm_ach, 'peak': hbm_gbs, 'unit': 'GB/s',
+        'frac': hbm_ach / hbm_gbs, 'traffic': NCU_TRAFFIC.get(args.env),
+        'peak_source': src, 'bytes_per_env_step': bytes_env,
+        'bytes_per_launch': bytes_env * b,
+        'note': 'schema roofline (HBM). The kernel is NOT HBM-bound: it is FP32-pipe / '
+                'instruction-issue bound (~60 flop/B), see roofline_fp32'}
     if flops:
       mhz = clocks['sm_mhz'] or sm_max_mhz
       peak_max = SM_COUNT * FP32_LANES * 2 * sm_max_mhz * 1e6 / 1e12
       ach = per_gpu * flops['flops'] / 1e12
-      out['roofline'] = {
+      out['roofline_fp32'] = {
           'bound': 'fp32', 'achieved': ach, 'peak': peak_max, 'unit': 'TFLOP/s',
-          'frac': ach / peak_max, 'traffic': None,
-          'flops_per_env_step': flops['flops'],
+          'frac': ach / peak_max, 'flops_per_env_step': flops['flops'],
           'peak_at_observed_clock': SM_COUNT * FP32_LANES * 2 * mhz * 1e6 / 1e12,
-          'note': 'FP32 CUDA-core bound path (no contraction: tensor cores do not apply); '
-                  'peak = 148 SM x 128 lanes x 2 x sm_max_mhz'}
-      out['roofline_hbm'] = roof_hbm
-    else:
-      out['roofline'] = roof_hbm
+          'note': 'flops = exact add+mul+div+sqrt+trig count of the oracle (oracle/flops.json); '
+                  'peak = 148 SM x 128 lanes x 2 (FMA) x sm_max_mhz; tensor cores do not apply'}
     if world == 1 and not args.no_cpu:
       out['cpu_baseline'] = cpu_baseline(desc, args.env, min(b, 8192), budget_s=args.cpu_seconds)
     print(json.dumps(out))
