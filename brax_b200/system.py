@@ -97,6 +97,11 @@ class System:
       except Exception:  # interpreter shutdown
         pass
 
+  @property
+  def handle(self) -> int:
+    """The `bx_system*` as an integer (FFI attribute)."""
+    return int(self._h.value)
+
   def configure(self, threads_per_block: int):
     """Warps per 32-env tile = threads_per_block / 32 (tuning knob)."""
     if self._lib.bx_system_configure(self._h, threads_per_block, 0) != 0:
