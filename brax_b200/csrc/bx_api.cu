@@ -24,7 +24,7 @@ struct bx_system {
   BxHeader h;
   int device;
   int32_t* d_tab_i;
-  float* d_tab_f;
+  float4* d_tab_f;
   size_t smem_bytes;
   int warps;  // warps per CTA (W)
   int sm_count;
@@ -113,13 +113,19 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   BxHeader& h = *hh;
   memset(&h, 0, sizeof(h));
   std::vector<int32_t>& ti = *ti_out;
-  std::vector<float>& tf = *tf_out;
+  std::vector<float>& tf = *tf_out;  // 4 floats per quad
   const int nb = d->num_bodies, nj = d->num_joints, na = d->num_actuators, nf = d->num_forces;
   const bool spring = d->dynamics_mode == BX_MODE_LEGACY_SPRING;
+  const int bqn = spring ? BX_BODY_QUADS_SPRING : BX_BODY_QUADS_PBD;
   h.mode = d->dynamics_mode;
   h.iters = spring ? d->substeps : d->substeps / 2;  // system.py:324 / :376
   h.nb = nb; h.nj = nj; h.na = na; h.nf = nf;
   h.act_size = d->act_size;
+  auto quad = [&](float x, float y, float z, float w) {
+    tf.push_back(x); tf.push_back(y); tf.push_back(z); tf.push_back(w);
+  };
+  auto nquads = [&]() { return static_cast<int>(tf.size() / 4); };
+  auto align4 = [&]() { while (ti.size() & 3) ti.push_back(0); };
 
   // contact rows: pairs expanded, group-major / pair-major / contact-in-pair
   struct Row { int pair, c; };
@@ -144,87 +150,69 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   }
   h.ncb = ncb; h.nab = nab;
 
-  // ---- float tables
-  h.fo_body = static_cast<int>(tf.size());
+  // ---- float4 tables
+  h.fo_body = nquads();
   for (int b = 0; b < nb; b++) {
     const bx_body& s = d->bodies[b];
-    float rec[BF_STRIDE] = {0};
-    rec[BF_INV_MASS] = 1.f / s.mass;
-    rec[BF_MASS] = s.mass;
-    for (int k = 0; k < 3; k++) {
-      rec[BF_INV_INERTIA + k] = s.inv_inertia[k];
-      rec[BF_POS_MASK + k] = s.pos_mask[k];
-      rec[BF_ROT_MASK + k] = s.rot_mask[k];
-    }
-    tf.insert(tf.end(), rec, rec + BF_STRIDE);
+    quad(1.f / s.mass, s.mass, 0.f, 0.f);
+    quad(s.inv_inertia[0], s.inv_inertia[1], s.inv_inertia[2], 0.f);
+    quad(s.pos_mask[0], s.pos_mask[1], s.pos_mask[2], 0.f);
+    quad(s.rot_mask[0], s.rot_mask[1], s.rot_mask[2], 0.f);
   }
-  h.fo_joint = static_cast<int>(tf.size());
+  h.fo_joint = nquads();
   for (int i = 0; i < nj; i++) {
     const bx_joint& s = d->joints[i];
-    float rec[JF_STRIDE] = {0};
-    for (int k = 0; k < 3; k++) { rec[JF_OFF_P + k] = s.off_p[k]; rec[JF_OFF_C + k] = s.off_c[k]; }
-    for (int k = 0; k < 9; k++) { rec[JF_AXIS_P + k] = s.axis_p[k]; rec[JF_AXIS_C + k] = s.axis_c[k]; }
-    for (int k = 0; k < 6; k++) rec[JF_LIMIT + k] = s.limit[k];
-    rec[JF_ANG_DAMP] = s.angular_damping;
-    rec[JF_SCALE_POS] = s.scale_pos;
-    rec[JF_SCALE_ANG] = s.scale_ang;
-    rec[JF_STIFFNESS] = s.stiffness;
-    rec[JF_SPRING_DAMP] = s.spring_damping;
-    rec[JF_LIMIT_STRENGTH] = s.limit_strength;
-    tf.insert(tf.end(), rec, rec + JF_STRIDE);
+    quad(s.off_p[0], s.off_p[1], s.off_p[2], s.angular_damping);
+    quad(s.off_c[0], s.off_c[1], s.off_c[2], s.scale_pos);
+    const float wp[3] = {s.scale_ang, s.stiffness, s.spring_damping};
+    const float wc[3] = {s.limit_strength, 0.f, 0.f};
+    for (int r = 0; r < 3; r++) quad(s.axis_p[3 * r], s.axis_p[3 * r + 1], s.axis_p[3 * r + 2], wp[r]);
+    for (int r = 0; r < 3; r++) quad(s.axis_c[3 * r], s.axis_c[3 * r + 1], s.axis_c[3 * r + 2], wc[r]);
+    quad(s.limit[0], s.limit[1], s.limit[2], s.limit[3]);
+    quad(s.limit[4], s.limit[5], 0.f, 0.f);
   }
-  h.fo_act = static_cast<int>(tf.size());
-  for (int i = 0; i < na; i++) tf.push_back(d->actuators[i].strength);
-  h.fo_force = static_cast<int>(tf.size());
-  for (int i = 0; i < nf; i++) tf.push_back(d->forces[i].strength);
-  h.fo_contact = static_cast<int>(tf.size());
+  h.fo_act = nquads();
+  for (int i = 0; i < na; i++) quad(d->actuators[i].strength, 0.f, 0.f, 0.f);
+  h.fo_force = nquads();
+  for (int i = 0; i < nf; i++) quad(d->forces[i].strength, 0.f, 0.f, 0.f);
+  h.fo_contact = nquads();
   for (int k = 0; k < nk; k++) {
     const bx_pair& p = d->pairs[rows[k].pair];
-    float rec[CF_STRIDE] = {0};
-    rec[CF_FRICTION] = p.friction;
-    rec[CF_ELASTICITY] = p.elasticity;
-    rec[CF_RADIUS_A] = p.radius_a;
-    rec[CF_RADIUS_B] = p.radius_b;
+    quad(p.friction, p.elasticity, p.radius_a, p.radius_b);
     if (p.kind == BX_PAIR_CAPSULE_CAPSULE) {
-      for (int q = 0; q < 4; q++)
-        for (int x = 0; x < 3; x++) rec[CF_PTS + 3 * q + x] = p.pts[q][x];
+      for (int q = 0; q < 4; q++) quad(p.pts[q][0], p.pts[q][1], p.pts[q][2], 0.f);
     } else {
-      for (int x = 0; x < 3; x++) rec[CF_PTS + x] = p.pts[rows[k].c][x];
+      const float* pt = p.pts[rows[k].c];
+      quad(pt[0], pt[1], pt[2], 0.f);
+      for (int q = 0; q < 3; q++) quad(0.f, 0.f, 0.f, 0.f);
     }
-    tf.insert(tf.end(), rec, rec + CF_STRIDE);
   }
-  h.n_floats = static_cast<int>(tf.size());
+  h.n_fquads = nquads();
 
-  // ---- delta slots of the contact rows inside region JS
-  const int dw = spring ? 6 : 7;
+  // ---- delta slots (quads) of the contact rows inside region JS
   std::vector<int> delta_off(nk);
   int js_contacts = 0;
   for (int k = 0; k < nk; k++) {
     delta_off[k] = js_contacts;
-    js_contacts += d->pairs[rows[k].pair].two_way ? 2 * dw : dw;
+    js_contacts += d->pairs[rows[k].pair].two_way ? 4 : 2;
   }
-  int js = js_contacts;
-  if (spring) js = std::max(js, 3 * na + 12 * nj);
-  else js = std::max(js, std::max(3 * na + 3 * nj, 14 * nj));
+  // pbd: torque slots (na + nj) and joint delta slots (4 nj) are never live together
+  int js = spring ? std::max(js_contacts, na + 4 * nj)
+                  : std::max(js_contacts, std::max(na + nj, 4 * nj));
 
-  // ---- state rows
-  int r = 0;
-  h.r_pos0 = r; r += 3 * nb;
-  h.r_rot0 = r; r += 4 * nb;
-  if (spring) { h.r_pos1 = h.r_pos0; h.r_rot1 = h.r_rot0; }
-  else { h.r_pos1 = r; r += 3 * nb; h.r_rot1 = r; r += 4 * nb; }
-  h.r_vel = r; r += 3 * nb;
-  h.r_ang = r; r += 3 * nb;
-  h.r_act = r; r += d->act_size;
-  h.r_js = r; r += js;
-  h.r_ct = r; r += 8 * nk;
-  h.r_pre = r; r += spring ? 0 : 6 * ncb;
-  h.r_ic = r; r += 6 * ncb;   // r_ic, r_ia, r_ij contiguous: zeroed together
-  h.r_ia = r; r += 3 * nab;
-  h.r_ij = r; r += spring ? 6 * nb : 0;
-  h.n_rows = r;
+  // ---- state quad rows
+  int r = nb * bqn;
+  h.q_act = r; r += (d->act_size + 3) / 4;
+  h.q_js = r; r += js;
+  h.q_ct = r; r += 2 * nk;
+  h.q_pre = r; r += spring ? 0 : 2 * ncb;
+  h.q_ic = r; r += 2 * ncb;   // q_ic, q_ia, q_ij contiguous: zeroed together
+  h.q_ia = r; r += nab;
+  h.q_ij = r; r += spring ? 2 * nb : 0;
+  h.n_quads = r;
+  h.n_zero = r - h.q_ic;
 
-  // ---- int tables
+  // ---- int tables (every record 16-byte aligned)
   std::vector<int32_t> adj;
   std::vector<int32_t> body_rec(nb * BI_STRIDE, 0);
   for (int b = 0; b < nb; b++) {
@@ -277,52 +265,98 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   }
   h.io_body = static_cast<int>(ti.size());
   ti.insert(ti.end(), body_rec.begin(), body_rec.end());
+  align4();
   h.io_joint = static_cast<int>(ti.size());
   for (int i = 0; i < nj; i++) {
     ti.push_back(d->joints[i].kind);
     ti.push_back(d->joints[i].body_p);
     ti.push_back(d->joints[i].body_c);
+    ti.push_back(0);
   }
   h.io_act = static_cast<int>(ti.size());
   for (int i = 0; i < na; i++) {
     const bx_actuator& a = d->actuators[i];
     ti.push_back(a.kind); ti.push_back(a.joint);
     for (int k = 0; k < 3; k++) ti.push_back(a.act_index[k]);
+    for (int k = 0; k < 3; k++) ti.push_back(0);
   }
   h.io_force = static_cast<int>(ti.size());
   for (int i = 0; i < nf; i++) {
     const bx_force& f = d->forces[i];
     ti.push_back(f.kind); ti.push_back(f.body);
     for (int k = 0; k < 3; k++) ti.push_back(f.act_index[k]);
+    for (int k = 0; k < 3; k++) ti.push_back(0);
   }
   h.io_contact = static_cast<int>(ti.size());
   for (int k = 0; k < nk; k++) {
     const bx_pair& p = d->pairs[rows[k].pair];
     ti.push_back(p.kind); ti.push_back(p.two_way); ti.push_back(p.body_a);
     ti.push_back(p.body_b); ti.push_back(delta_off[k]);
+    for (int q = 0; q < 3; q++) ti.push_back(0);
   }
   h.io_adj = static_cast<int>(ti.size());
   ti.insert(ti.end(), adj.begin(), adj.end());
-  // output maps
-  auto body_map = [&](const std::vector<int>& slot, int base, int width, int off) {
-    int o = static_cast<int>(ti.size());
-    for (int b = 0; b < nb; b++)
-      for (int k = 0; k < 3; k++) ti.push_back(slot[b] >= 0 ? base + width * slot[b] + off + k : -1);
-    return o;
+
+  // ---- I/O segments: element r of an env -> shared float index of (quad row, comp)
+  const int RF = BX_QSTRIDE * 4;  // floats per quad row
+  auto seg = [&](int nper, float fill, const std::vector<int>& map) {
+    BxSeg sgm;
+    sgm.nper = nper;
+    sgm.map = static_cast<int>(ti.size());
+    sgm.magic = nper > 1 ? static_cast<uint32_t>((0x100000000ULL + nper - 1) / nper) : 0u;
+    sgm.fill = fill;
+    ti.insert(ti.end(), map.begin(), map.end());
+    return sgm;
   };
-  std::vector<int> ident(nb);
+  // per-body vector field with `w` components at quad (bqn*b + off); rot is stored (w,x,y,z)
+  auto body_field = [&](int off, int w) {
+    std::vector<int> m;
+    for (int b = 0; b < nb; b++)
+      for (int x = 0; x < w; x++) m.push_back((bqn * b + off) * RF + x);
+    return m;
+  };
+  auto slot_field = [&](const std::vector<int>& slot, int base, int per, int off) {
+    std::vector<int> m;
+    for (int b = 0; b < nb; b++)
+      for (int x = 0; x < 3; x++) m.push_back(slot[b] >= 0 ? (base + per * slot[b] + off) * RF + x : -1);
+    return m;
+  };
+  const int vel_off = bqn - 2, ang_off = bqn - 1;
+  h.seg_in[0] = seg(3 * nb, 0.f, body_field(0, 3));
+  h.seg_in[1] = seg(4 * nb, 0.f, body_field(1, 4));
+  h.seg_in[2] = seg(3 * nb, 0.f, body_field(vel_off, 3));
+  h.seg_in[3] = seg(3 * nb, 0.f, body_field(ang_off, 3));
+  {
+    std::vector<int> m;
+    for (int i = 0; i < d->act_size; i++) m.push_back((h.q_act + (i >> 2)) * RF + (i & 3));
+    h.seg_in[4] = seg(d->act_size, 0.f, m);
+  }
+  std::vector<int> ident(nb), none(3 * nb, -1);
   for (int b = 0; b < nb; b++) ident[b] = b;
-  h.m_cv = body_map(cslot, h.r_ic, 6, 0);
-  h.m_ca = body_map(cslot, h.r_ic, 6, 3);
-  h.m_aa = body_map(aslot, h.r_ia, 3, 0);
-  h.m_jv = spring ? body_map(ident, h.r_ij, 6, 0) : 0;
-  h.m_ja = spring ? body_map(ident, h.r_ij, 6, 3) : 0;
-  h.m_cp = static_cast<int>(ti.size());
-  for (int k = 0; k < nk; k++) for (int x = 0; x < 3; x++) ti.push_back(h.r_ct + 8 * k + x);
-  h.m_cn = static_cast<int>(ti.size());
-  for (int k = 0; k < nk; k++) for (int x = 0; x < 3; x++) ti.push_back(h.r_ct + 8 * k + 3 + x);
-  h.m_pen = static_cast<int>(ti.size());
-  for (int k = 0; k < nk; k++) ti.push_back(h.r_ct + 8 * k + 6);
+  h.seg_out[0] = h.seg_in[0];
+  h.seg_out[1] = h.seg_in[1];
+  h.seg_out[2] = h.seg_in[2];
+  h.seg_out[3] = h.seg_in[3];
+  h.seg_out[4] = seg(3 * nb, 0.f, slot_field(cslot, h.q_ic, 2, 0));   // contact.vel
+  h.seg_out[5] = seg(3 * nb, 0.f, slot_field(cslot, h.q_ic, 2, 1));   // contact.ang
+  h.seg_out[6] = seg(3 * nb, 0.f, spring ? slot_field(ident, h.q_ij, 2, 0) : none);  // joint.vel
+  h.seg_out[7] = seg(3 * nb, 0.f, spring ? slot_field(ident, h.q_ij, 2, 1) : none);  // joint.ang
+  h.seg_out[8] = seg(3 * nb, 0.f, none);                               // actuator.vel
+  h.seg_out[9] = seg(3 * nb, 0.f, slot_field(aslot, h.q_ia, 1, 0));   // actuator.ang
+  {
+    std::vector<int> mp, mn, me;
+    for (int k = 0; k < nk; k++) {
+      for (int x = 0; x < 3; x++) {
+        mp.push_back((h.q_ct + 2 * k) * RF + x);
+        mn.push_back((h.q_ct + 2 * k + 1) * RF + x);
+      }
+      me.push_back((h.q_ct + 2 * k) * RF + 3);
+    }
+    h.seg_out[10] = seg(3 * nk, 0.f, mp);
+    h.seg_out[11] = seg(3 * nk, 0.f, mn);
+    h.seg_out[12] = seg(nk, 0.f, me);
+  }
+  align4();
   h.n_ints = static_cast<int>(ti.size());
 
   // ---- scalars
@@ -360,7 +394,8 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   s->sm_count = prop.multiProcessorCount;
   s->d_scratch = nullptr;
   s->scratch_floats = 0;
-  s->smem_bytes = (static_cast<size_t>(s->h.n_rows) * BX_ROW_STRIDE + s->h.n_floats + s->h.n_ints) * 4;
+  s->smem_bytes = (static_cast<size_t>(s->h.n_quads) * BX_QSTRIDE + s->h.n_fquads) * 16 +
+                  static_cast<size_t>(s->h.n_ints) * 4;
   if (s->smem_bytes > static_cast<size_t>(prop.sharedMemPerBlockOptin)) {
     delete s;
     return fail("system state does not fit in shared memory (too many bodies/joints/contacts)");
@@ -419,7 +454,12 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   p.h = s->h;
   p.tab_i = s->d_tab_i;
   p.tab_f = s->d_tab_f;
-  p.io = *io;
+  p.in[0] = io->pos; p.in[1] = io->rot; p.in[2] = io->vel; p.in[3] = io->ang; p.in[4] = io->act;
+  float* const outs[BX_SEG_OUT] = {
+      io->pos_o, io->rot_o, io->vel_o, io->ang_o, io->contact_vel, io->contact_ang,
+      io->joint_vel, io->joint_ang, io->actuator_vel, io->actuator_ang,
+      io->contact_pos, io->contact_normal, io->contact_penetration};
+  for (int i = 0; i < BX_SEG_OUT; i++) p.out[i] = outs[i];
   p.num_envs = num_envs;
   p.num_steps = num_steps;
   const int64_t tiles = (num_envs + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA;

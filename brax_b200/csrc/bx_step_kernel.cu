@@ -12,10 +12,11 @@
 //     32 environments between them (warp w takes items w, w+W, ...), phases are
 //     separated by __syncthreads();
 //   * the whole QP state of the tile, the per-joint / per-contact deltas and the
-//     Info accumulators live in shared memory for the entire substep loop, laid
-//     out [row][env] with a 33-float row stride: compute accesses (row*33+lane)
-//     and the transposing global I/O (consecutive rows, same env) are both
-//     bank-conflict free;
+//     Info accumulators live in shared memory for the entire substep loop as
+//     float4 "quads" laid out [quad row][env] (row stride 33 quads): a 3-vector
+//     or a quaternion of one env is ONE 128-bit LDS/STS, conflict-free across
+//     the 32 lanes, and the transposing global I/O is conflict-free too;
+//   * the static tables are float4 / int4 records read with 128-bit broadcasts;
 //   * HBM is touched once on the way in and once on the way out, with
 //     coalesced 128-bit loads/stores of the boundary layout [B,N,3|4].
 // FP32 CUDA-core bound by design; tensor cores do not apply (no contraction).
@@ -29,117 +30,101 @@
 struct BxKernelParams {
   BxHeader h;
   const int32_t* tab_i;
-  const float* tab_f;
-  bx_step_io io;
+  const float4* tab_f;
+  const float* in[BX_SEG_IN];  // pos rot vel ang act
+  float* out[BX_SEG_OUT];      // order of bx_step_io's outputs
   int64_t num_envs;
   int32_t num_steps;  // >1: rollout, act is [T,B,A]
 };
 
-#define RS BX_ROW_STRIDE
+#define QS BX_QSTRIDE
 
 struct Ctx {
-  float* st;         // shared state base + lane
-  const float* tf;   // float tables (shared)
-  const int32_t* ti; // int tables (shared)
-  int warp, nwarp, lane;
-  int cur;           // ping-pong index of the current pos/rot buffer
+  float4* q;          // shared state base + lane
+  const float4* tf;   // float4 tables (shared)
+  const int32_t* ti;  // int tables (shared)
+  int warp, nwarp;
+  int cur;            // ping-pong index of the current pos/rot quads (pbd)
 };
 
-#define ROW(c, r) ((c).st[(r) * RS])
+// body block layout (quads): pbd {pos0 rot0 pos1 rot1 vel ang}, spring {pos rot vel ang}
+template <int MODE> struct Lay {
+  static constexpr int BQ = MODE == BX_MODE_PBD ? BX_BODY_QUADS_PBD : BX_BODY_QUADS_SPRING;
+  static constexpr int VEL = BQ - 2, ANG = BQ - 1;
+};
 
-BXD V3 ld3(const Ctx& c, int r) { return v3(ROW(c, r), ROW(c, r + 1), ROW(c, r + 2)); }
-BXD Q4 ld4(const Ctx& c, int r) {
-  return q4(ROW(c, r), ROW(c, r + 1), ROW(c, r + 2), ROW(c, r + 3));
+#define QROW(c, r) ((c).q[(r) * QS])
+
+BXD V3 f3(float4 t) { return v3(t.x, t.y, t.z); }
+BXD V3 ldv(const Ctx& c, int r) { return f3(QROW(c, r)); }
+BXD Q4 ldq(const Ctx& c, int r) { float4 t = QROW(c, r); return q4(t.x, t.y, t.z, t.w); }
+BXD void stv(const Ctx& c, int r, V3 v) { QROW(c, r) = make_float4(v.x, v.y, v.z, 0.f); }
+BXD void stv4(const Ctx& c, int r, V3 v, float w) { QROW(c, r) = make_float4(v.x, v.y, v.z, w); }
+BXD void stq(const Ctx& c, int r, Q4 q) { QROW(c, r) = make_float4(q.w, q.x, q.y, q.z); }
+BXD float act_at(const Ctx& c, const BxHeader& h, int i) {
+  return reinterpret_cast<const float*>(&QROW(c, h.q_act + (i >> 2)))[i & 3];
 }
-BXD void st3(const Ctx& c, int r, V3 v) { ROW(c, r) = v.x; ROW(c, r + 1) = v.y; ROW(c, r + 2) = v.z; }
-BXD void st4(const Ctx& c, int r, Q4 q) {
-  ROW(c, r) = q.w; ROW(c, r + 1) = q.x; ROW(c, r + 2) = q.y; ROW(c, r + 3) = q.z;
-}
-BXD V3 tf3(const float* t) { return v3(t[0], t[1], t[2]); }
+BXD int4 ldi4(const int32_t* p) { return *reinterpret_cast<const int4*>(p); }
 
 // ---- global <-> shared transposing I/O ---------------------------------------
-// g: [B, nper] row-major; this CTA owns envs [env0, env0+nenv).  Element
-// (e, r) goes to shared row (row0 + r), env slot e.
-__device__ void load_rows(float* sm, const float* __restrict__ g, int64_t env0,
-                          int nenv, int nper, int row0) {
-  const float* src = g + env0 * nper;
-  int total = nenv * nper;
-  if ((total & 3) == 0 && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
-    const float4* s4 = reinterpret_cast<const float4*>(src);
+// g: [B, nper] row-major; this CTA owns envs [env0, env0+nenv).  Element (e, r)
+// lives at shared float index map[r] + 4*e (map[r] < 0: constant `fill`).
+template <bool LOAD>
+__device__ __noinline__ void io_segment(float* smf, const int32_t* ti, BxSeg sg, float* g,
+                                        int64_t env0, int nenv) {
+  if (g == nullptr || sg.nper == 0) return;
+  const int nper = sg.nper;
+  float* base = g + env0 * nper;
+  const int32_t* map = ti + sg.map;
+  const int total = nenv * nper;
+  if ((total & 3) == 0 && ((reinterpret_cast<uintptr_t>(base) & 15) == 0)) {
+    float4* b4 = reinterpret_cast<float4*>(base);
     for (int i = threadIdx.x; i < (total >> 2); i += blockDim.x) {
-      float4 v = __ldg(s4 + i);
-      float vv[4] = {v.x, v.y, v.z, v.w};
-      int idx = i << 2;
-      int e = idx / nper, r = idx - e * nper;
-#pragma unroll
-      for (int k = 0; k < 4; k++) {
-        sm[(row0 + r) * RS + e] = vv[k];
-        if (++r == nper) { r = 0; e++; }
-      }
-    }
-  } else {
-    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-      int e = idx / nper, r = idx - e * nper;
-      sm[(row0 + r) * RS + e] = __ldg(src + idx);
-    }
-  }
-}
-
-// map == nullptr: element (e, r) comes from row (row0 + r); otherwise from row
-// map[r], or 0 when map[r] < 0.
-__device__ void store_rows(const float* sm, float* __restrict__ g, int64_t env0,
-                           int nenv, int nper, int row0, const int32_t* map) {
-  if (g == nullptr) return;
-  float* dst = g + env0 * nper;
-  int total = nenv * nper;
-  if ((total & 3) == 0 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-    float4* d4 = reinterpret_cast<float4*>(dst);
-    for (int i = threadIdx.x; i < (total >> 2); i += blockDim.x) {
+      const int idx = i << 2;
+      int e = sg.magic ? static_cast<int>(__umulhi(static_cast<unsigned>(idx), sg.magic)) : idx;
+      int r = idx - e * nper;
       float vv[4];
-      int idx = i << 2;
-      int e = idx / nper, r = idx - e * nper;
+      if (LOAD) {
+        float4 v = __ldg(b4 + i);
+        vv[0] = v.x; vv[1] = v.y; vv[2] = v.z; vv[3] = v.w;
+      }
 #pragma unroll
       for (int k = 0; k < 4; k++) {
-        int row = map ? map[r] : row0 + r;
-        vv[k] = row >= 0 ? sm[row * RS + e] : 0.f;
+        const int m = map[r];
+        if (LOAD) { if (m >= 0) smf[m + 4 * e] = vv[k]; }
+        else vv[k] = m >= 0 ? smf[m + 4 * e] : sg.fill;
         if (++r == nper) { r = 0; e++; }
       }
-      d4[i] = make_float4(vv[0], vv[1], vv[2], vv[3]);
+      if (!LOAD) b4[i] = make_float4(vv[0], vv[1], vv[2], vv[3]);
     }
   } else {
     for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-      int e = idx / nper, r = idx - e * nper;
-      int row = map ? map[r] : row0 + r;
-      dst[idx] = row >= 0 ? sm[row * RS + e] : 0.f;
+      const int e = sg.magic ? static_cast<int>(__umulhi(static_cast<unsigned>(idx), sg.magic)) : idx;
+      const int r = idx - e * nper;
+      const int m = map[r];
+      if (LOAD) { if (m >= 0) smf[m + 4 * e] = __ldg(base + idx); }
+      else base[idx] = m >= 0 ? smf[m + 4 * e] : sg.fill;
     }
   }
-}
-
-__device__ void store_const(float* __restrict__ g, int64_t env0, int nenv, int nper,
-                            float value) {
-  if (g == nullptr) return;
-  float* dst = g + env0 * nper;
-  int total = nenv * nper;
-  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) dst[idx] = value;
 }
 
 // ---- joints: axis / angle -------------------------------------------------
 // Revolute.axis_angle joints.py:311-319 (spring_joints.py:150-157)
-BXD void axis_angle_revolute(const float* jf, Q4 rp, Q4 rc, V3* axis, float* angle) {
-  V3 ax = rotate(tf3(jf + JF_AXIS_P), rp);
-  V3 ref_p = rotate(tf3(jf + JF_AXIS_P + 6), rp);
-  V3 ref_c = rotate(tf3(jf + JF_AXIS_C + 6), rc);
+BXD void axis_angle_revolute(const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
+  V3 ax = rotate(f3(jq[JQ_AXIS_P]), rp);
+  V3 ref_p = rotate(f3(jq[JQ_AXIS_P + 2]), rp);
+  V3 ref_c = rotate(f3(jq[JQ_AXIS_C + 2]), rc);
   axis[0] = ax;
   angle[0] = signed_angle(ax, ref_p, ref_c);
 }
 
 // Spherical.axis_angle joints.py:388-415 (spring_joints.py:212-224, 276-303)
-BXD void axis_angle_spherical(const float* jf, Q4 rp, Q4 rc, V3* axis, float* angle) {
-  V3 a1p = rotate(tf3(jf + JF_AXIS_P), rp);
-  V3 a2p = rotate(tf3(jf + JF_AXIS_P + 3), rp);
-  V3 a1c = rotate(tf3(jf + JF_AXIS_C), rc);
-  V3 a2c = rotate(tf3(jf + JF_AXIS_C + 3), rc);
-  V3 a3c = rotate(tf3(jf + JF_AXIS_C + 6), rc);
+BXD void axis_angle_spherical(const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
+  V3 a1p = rotate(f3(jq[JQ_AXIS_P]), rp);
+  V3 a2p = rotate(f3(jq[JQ_AXIS_P + 1]), rp);
+  V3 a1c = rotate(f3(jq[JQ_AXIS_C]), rc);
+  V3 a2c = rotate(f3(jq[JQ_AXIS_C + 1]), rc);
+  V3 a3c = rotate(f3(jq[JQ_AXIS_C + 2]), rc);
   V3 lon = cross(a3c, a1p);
   lon = vdiv(lon, 1e-10f + safe_norm(lon));
   float psi = signed_angle(a1p, a2p, lon);
@@ -157,82 +142,85 @@ BXD int joint_dof(int kind) {
              : (kind == BX_JOINT_SPRING_UNIVERSAL ? 2 : 3);
 }
 
-BXD void joint_axis_angle(int kind, const float* jf, Q4 rp, Q4 rc, V3* axis,
-                          float* angle) {
+BXD void joint_axis_angle(int kind, const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
   if (kind == BX_JOINT_REVOLUTE || kind == BX_JOINT_SPRING_REVOLUTE)
-    axis_angle_revolute(jf, rp, rc, axis, angle);
+    axis_angle_revolute(jq, rp, rc, axis, angle);
   else
-    axis_angle_spherical(jf, rp, rc, axis, angle);
+    axis_angle_spherical(jq, rp, rc, axis, angle);
 }
 
 // ---- phase T: actuator torques and joint damping torques -------------------
-// Writes the torque VECTOR of actuator a to rows JS+3a and the damping torque of
-// joint j to rows JS+3(na+j); the body phase turns them into angular
+// Writes the torque VECTOR of actuator a to quad JS+a and the damping torque of
+// joint j to quad JS+na+j; the body phase turns them into angular
 // accelerations (actuators.py:52-112, joints.py:103-128).
-__device__ __forceinline__ void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
-  const int rrot = c.cur ? h.r_rot1 : h.r_rot0;
+template <int MODE>
+BXD void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
+  typedef Lay<MODE> L;
+  const int ro = MODE == BX_MODE_PBD ? 2 * c.cur + 1 : 1;
   for (int a = c.warp; a < h.na; a += c.nwarp) {
-    const int32_t* ai = c.ti + h.io_act + a * AI_STRIDE;
-    const int j = ai[AI_JOINT];
-    const int32_t* ji = c.ti + h.io_joint + j * JI_STRIDE;
-    const float* jf = c.tf + h.fo_joint + j * JF_STRIDE;
-    const int kind = ji[JI_KIND];
-    Q4 rp = ld4(c, rrot + 4 * ji[JI_BODY_P]);
-    Q4 rc = ld4(c, rrot + 4 * ji[JI_BODY_C]);
+    const int4 ai = ldi4(c.ti + h.io_act + a * AI_STRIDE);  // kind, joint, idx0, idx1
+    const int idx2 = c.ti[h.io_act + a * AI_STRIDE + 4];
+    const int j = ai.y;
+    const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
+    const float4* jq = c.tf + h.fo_joint + j * JQ_STRIDE;
+    const int kind = ji.x;
+    Q4 rp = ldq(c, L::BQ * ji.y + ro);
+    Q4 rc = ldq(c, L::BQ * ji.z + ro);
     V3 axis[3];
     float angle[3];
-    joint_axis_angle(kind, jf, rp, rc, axis, angle);
-    const float strength = c.tf[h.fo_act + a];
+    joint_axis_angle(kind, jq, rp, rc, axis, angle);
+    const float strength = c.tf[h.fo_act + a].x;
     const int dof = joint_dof(kind);
+    const float4 l01 = jq[JQ_LIMIT], l2 = jq[JQ_LIMIT + 1];
+    const float lo[3] = {l01.x, l01.z, l2.x}, hi[3] = {l01.y, l01.w, l2.y};
+    const int aidx[3] = {ai.z, ai.w, idx2};
     V3 tq = v3(0.f, 0.f, 0.f);
 #pragma unroll
     for (int d = 0; d < 3; d++) {
       if (d < dof) {
-        int idx = ai[AI_IDX + d];
+        int idx = aidx[d];
         // take(act, idx, mode=clip) * act_mask  (actuators.py:64)
         float m = idx >= 0 ? 1.f : 0.f;
         idx = min(max(idx, 0), h.act_size - 1);
-        float av = ROW(c, h.r_act + idx) * m;
-        float lo = jf[JF_LIMIT + 2 * d], hi = jf[JF_LIMIT + 2 * d + 1];
+        float av = act_at(c, h, idx) * m;
         float t;
-        if (ai[AI_KIND] == BX_ACT_TORQUE) {
+        if (ai.x == BX_ACT_TORQUE) {
           t = av * strength * -1.f;
-          t = angle[d] < lo ? 0.f : t;
-          t = angle[d] > hi ? 0.f : t;
+          t = angle[d] < lo[d] ? 0.f : t;
+          t = angle[d] > hi[d] ? 0.f : t;
         } else {
-          float tgt = clipf(av * 3.14159265358979323846f / 180.f, lo, hi);
+          float tgt = clipf(av * 3.14159265358979323846f / 180.f, lo[d], hi[d]);
           t = (tgt - angle[d]) * strength;
         }
         tq = tq + axis[d] * t;
       }
     }
-    st3(c, h.r_js + 3 * a, tq);
+    stv(c, h.q_js + a, tq);
   }
   if (damp) {
     for (int j = c.warp; j < h.nj; j += c.nwarp) {
-      const int32_t* ji = c.ti + h.io_joint + j * JI_STRIDE;
-      const float* jf = c.tf + h.fo_joint + j * JF_STRIDE;
-      V3 ap = ld3(c, h.r_ang + 3 * ji[JI_BODY_P]);
-      V3 ac = ld3(c, h.r_ang + 3 * ji[JI_BODY_C]);
-      V3 tq = (-1.f * jf[JF_ANG_DAMP]) * (ap - ac);
-      st3(c, h.r_js + 3 * (h.na + j), tq);
+      const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
+      const float damping = c.tf[h.fo_joint + j * JQ_STRIDE + JQ_OFF_P].w;
+      V3 ap = ldv(c, L::BQ * ji.y + L::ANG);
+      V3 ac = ldv(c, L::BQ * ji.z + L::ANG);
+      V3 tq = (-1.f * damping) * (ap - ac);
+      stv(c, h.q_js + h.na + j, tq);
     }
   }
 }
 
 // Sum of the angular accelerations of body b from actuators (dp_a), joint
 // damping (dp_j) and forces (dp_f); system.py:268-271.
-BXD void body_accels(const Ctx& c, const BxHeader& h, int b, const int32_t* bi,
-                     const float* bf, bool damp, V3* dpa_ang, V3* dpj_ang,
-                     V3* dpf_vel, V3* dpf_ang) {
-  V3 inv_i = tf3(bf + BF_INV_INERTIA);
+BXD void body_accels(const Ctx& c, const BxHeader& h, const int32_t* bi, const float4* bq,
+                     bool damp, V3* dpa_ang, V3* dpj_ang, V3* dpf_vel, V3* dpf_ang) {
+  V3 inv_i = f3(bq[BQ_INV_INERTIA]);
   V3 dpa = v3(0.f, 0.f, 0.f), dpj = v3(0.f, 0.f, 0.f);
   {
     const int32_t* adj = c.ti + h.io_adj + bi[BI_AADJ_OFF];
     const int n = bi[BI_AADJ_N];
     for (int i = 0; i < n; i++) {
       int e = adj[i];
-      V3 t = inv_i * ld3(c, h.r_js + 3 * (e >> 2));
+      V3 t = inv_i * ldv(c, h.q_js + (e >> 2));
       // Torque: parent +, child -; Angle: parent -, child + (actuators.py:88-89,109-110)
       dpa = (e & 1) ? dpa - t : dpa + t;
     }
@@ -242,7 +230,7 @@ BXD void body_accels(const Ctx& c, const BxHeader& h, int b, const int32_t* bi,
     const int n = bi[BI_JADJ_N];
     for (int i = 0; i < n; i++) {
       int e = adj[i];
-      V3 t = inv_i * ld3(c, h.r_js + 3 * (h.na + (e >> 1)));
+      V3 t = inv_i * ldv(c, h.q_js + h.na + (e >> 1));
       dpj = (e & 1) ? dpj - t : dpj + t;
     }
   }
@@ -253,11 +241,11 @@ BXD void body_accels(const Ctx& c, const BxHeader& h, int b, const int32_t* bi,
     for (int i = 0; i < n; i++) {
       int f = adj[i];
       const int32_t* fi = c.ti + h.io_force + f * FI_STRIDE;
-      float strength = c.tf[h.fo_force + f];
-      V3 a = v3(ROW(c, h.r_act + min(max(fi[FI_IDX], 0), h.act_size - 1)),
-                ROW(c, h.r_act + min(max(fi[FI_IDX + 1], 0), h.act_size - 1)),
-                ROW(c, h.r_act + min(max(fi[FI_IDX + 2], 0), h.act_size - 1)));
-      V3 d = vdiv(a * strength, bf[BF_MASS]);  // forces.py:44,87
+      float strength = c.tf[h.fo_force + f].x;
+      V3 a = v3(act_at(c, h, min(max(fi[FI_IDX], 0), h.act_size - 1)),
+                act_at(c, h, min(max(fi[FI_IDX + 1], 0), h.act_size - 1)),
+                act_at(c, h, min(max(fi[FI_IDX + 2], 0), h.act_size - 1)));
+      V3 d = vdiv(a * strength, bq[BQ_MASS].y);  // forces.py:44,87
       if (fi[FI_KIND] == BX_FORCE_THRUSTER) fv = fv + d; else fa = fa + d;
     }
   }
@@ -266,8 +254,7 @@ BXD void body_accels(const Ctx& c, const BxHeader& h, int b, const int32_t* bi,
 
 // ---- integrator pieces (per body) -------------------------------------------
 // Euler.kinetic integrators.py:50-68
-BXD void kinetic(const BxHeader& h, const float* bf, V3 vel, V3 ang, V3* pos, Q4* rot) {
-  V3 pm = tf3(bf + BF_POS_MASK), rm = tf3(bf + BF_ROT_MASK);
+BXD void kinetic(const BxHeader& h, V3 pm, V3 rm, V3 vel, V3 ang, V3* pos, Q4* rot) {
   *pos = *pos + (vel * h.dt) * pm;
   V3 w = (ang * rm) * h.half_dt;
   Q4 r = *rot + quat_mul(q4(0.f, w.x, w.y, w.z), *rot);
@@ -277,9 +264,8 @@ BXD void kinetic(const BxHeader& h, const float* bf, V3 vel, V3 ang, V3* pos, Q4
 }
 
 // Euler.velocity_projection integrators.py:122-146
-BXD void velocity_projection(const BxHeader& h, const float* bf, V3 pos, V3 ppos,
-                             Q4 prot, Q4* rot, V3* vel, V3* ang) {
-  V3 pm = tf3(bf + BF_POS_MASK), rm = tf3(bf + BF_ROT_MASK);
+BXD void velocity_projection(const BxHeader& h, V3 pm, V3 rm, V3 pos, V3 ppos, Q4 prot, Q4* rot,
+                             V3* vel, V3* ang) {
   Q4 r = *rot;
   float n = bx_sqrt(r.w * r.w + r.x * r.x + r.y * r.y + r.z * r.z);
   float rn = bx_rcp(n);
@@ -296,31 +282,31 @@ BXD void velocity_projection(const BxHeader& h, const float* bf, V3 pos, V3 ppos
 // ---- phase B1 (pbd): acceleration update + kinetic step, per body ------------
 // system.py:268-274 / :287-293.  Reads pos/rot from buffer cur, writes the
 // advanced pos/rot into buffer cur^1 (buffer cur then IS qprev).
-__device__ __forceinline__ void phase_body_acc_kinetic(const Ctx& c, const BxHeader& h,
-                                                    bool accumulate_info) {
-  const int rpos = c.cur ? h.r_pos1 : h.r_pos0, rrot = c.cur ? h.r_rot1 : h.r_rot0;
-  const int npos = c.cur ? h.r_pos0 : h.r_pos1, nrot = c.cur ? h.r_rot0 : h.r_rot1;
+BXD void phase_body_acc_kinetic(const Ctx& c, const BxHeader& h, bool accumulate_info) {
+  typedef Lay<BX_MODE_PBD> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
-    const float* bf = c.tf + h.fo_body + b * BF_STRIDE;
+    const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
+    const int r0 = L::BQ * b;
     V3 dpa, dpj, fv, fa;
-    body_accels(c, h, b, bi, bf, true, &dpa, &dpj, &fv, &fa);
+    body_accels(c, h, bi, bq, true, &dpa, &dpj, &fv, &fa);
     V3 acc_ang = (dpa + fa) + dpj;
-    V3 vel = ld3(c, h.r_vel + 3 * b), ang = ld3(c, h.r_ang + 3 * b);
+    V3 vel = ldv(c, r0 + L::VEL), ang = ldv(c, r0 + L::ANG);
     V3 g = v3(h.gravity[0], h.gravity[1], h.gravity[2]);
+    V3 pm = f3(bq[BQ_POS_MASK]), rm = f3(bq[BQ_ROT_MASK]);
     // Euler.update acc branch integrators.py:87-95
-    vel = (h.vel_damp * vel + (fv + g) * h.dt) * tf3(bf + BF_POS_MASK);
-    ang = (h.ang_damp * ang + acc_ang * h.dt) * tf3(bf + BF_ROT_MASK);
-    V3 pos = ld3(c, rpos + 3 * b);
-    Q4 rot = ld4(c, rrot + 4 * b);
-    kinetic(h, bf, vel, ang, &pos, &rot);
-    st3(c, h.r_vel + 3 * b, vel);
-    st3(c, h.r_ang + 3 * b, ang);
-    st3(c, npos + 3 * b, pos);
-    st4(c, nrot + 4 * b, rot);
+    vel = (h.vel_damp * vel + (fv + g) * h.dt) * pm;
+    ang = (h.ang_damp * ang + acc_ang * h.dt) * rm;
+    V3 pos = ldv(c, r0 + 2 * c.cur);
+    Q4 rot = ldq(c, r0 + 2 * c.cur + 1);
+    kinetic(h, pm, rm, vel, ang, &pos, &rot);
+    stv(c, r0 + L::VEL, vel);
+    stv(c, r0 + L::ANG, ang);
+    stv(c, r0 + 2 * (c.cur ^ 1), pos);
+    stq(c, r0 + 2 * (c.cur ^ 1) + 1, rot);
     if (accumulate_info && bi[BI_ASLOT] >= 0) {  // info.actuator += dp_a (system.py:315)
-      int r = h.r_ia + 3 * bi[BI_ASLOT];
-      st3(c, r, ld3(c, r) + dpa);
+      int r = h.q_ia + bi[BI_ASLOT];
+      stv(c, r, ldv(c, r) + dpa);
     }
   }
 }
@@ -373,32 +359,35 @@ BXD void limit_angle(V3 n, V3 n_1, V3 n_2, float lo, float hi, V3 ii_p, V3 ii_c,
 
 // ---- phase J (pbd): Joint.apply for every joint -> per-joint delta slots -------
 // joints.py:79-100, Revolute :270-309, Spherical :332-386.  Slot of joint j:
-// rows JS+14j .. +6 = parent (pos3, rot4), +7 .. +13 = child.
-__device__ __forceinline__ void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
-  const int rpos = c.cur ? h.r_pos1 : h.r_pos0, rrot = c.cur ? h.r_rot1 : h.r_rot0;
+// quads JS+4j .. +3 = parent dpos, parent drot, child dpos, child drot.
+BXD void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
+  typedef Lay<BX_MODE_PBD> L;
   for (int j = c.warp; j < h.nj; j += c.nwarp) {
-    const int32_t* ji = c.ti + h.io_joint + j * JI_STRIDE;
-    const float* jf = c.tf + h.fo_joint + j * JF_STRIDE;
-    const int bp = ji[JI_BODY_P], bc = ji[JI_BODY_C];
-    const float* bfp = c.tf + h.fo_body + bp * BF_STRIDE;
-    const float* bfc = c.tf + h.fo_body + bc * BF_STRIDE;
-    V3 pos_p = ld3(c, rpos + 3 * bp), pos_c = ld3(c, rpos + 3 * bc);
-    Q4 rp = ld4(c, rrot + 4 * bp), rc = ld4(c, rrot + 4 * bc);
-    V3 ii_p = tf3(bfp + BF_INV_INERTIA), ii_c = tf3(bfc + BF_INV_INERTIA);
-    V3 wp = pos_p + rotate(tf3(jf + JF_OFF_P), rp);
-    V3 wc = pos_c + rotate(tf3(jf + JF_OFF_C), rc);
+    const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
+    const float4* jq = c.tf + h.fo_joint + j * JQ_STRIDE;
+    const int bp = ji.y, bc = ji.z;
+    const float4* bqp = c.tf + h.fo_body + bp * BQ_STRIDE;
+    const float4* bqc = c.tf + h.fo_body + bc * BQ_STRIDE;
+    V3 pos_p = ldv(c, L::BQ * bp + 2 * c.cur), pos_c = ldv(c, L::BQ * bc + 2 * c.cur);
+    Q4 rp = ldq(c, L::BQ * bp + 2 * c.cur + 1), rc = ldq(c, L::BQ * bc + 2 * c.cur + 1);
+    V3 ii_p = f3(bqp[BQ_INV_INERTIA]), ii_c = f3(bqc[BQ_INV_INERTIA]);
+    const float4 mp = bqp[BQ_MASS], mc = bqc[BQ_MASS];
+    const float4 j0 = jq[JQ_OFF_P], j1 = jq[JQ_OFF_C];
+    const float4 ap0 = jq[JQ_AXIS_P];
+    V3 wp = pos_p + rotate(f3(j0), rp);
+    V3 wc = pos_c + rotate(f3(j1), rc);
     DQ dp, dc;
-    position_update(wp, wc, pos_p, pos_c, rp, rc, bfp[BF_INV_MASS], bfc[BF_INV_MASS],
-                    bfp[BF_MASS], bfc[BF_MASS], ii_p, ii_c, jf[JF_SCALE_POS], &dp, &dc);
-    const float sa = jf[JF_SCALE_ANG];
-    if (ji[JI_KIND] == BX_JOINT_REVOLUTE) {
-      V3 axis = rotate(tf3(jf + JF_AXIS_P), rp);
-      V3 ref_p = rotate(tf3(jf + JF_AXIS_P + 6), rp);
-      V3 ref_c = rotate(tf3(jf + JF_AXIS_C + 6), rc);
+    position_update(wp, wc, pos_p, pos_c, rp, rc, mp.x, mc.x, mp.y, mc.y, ii_p, ii_c, j1.w, &dp, &dc);
+    const float sa = ap0.w;
+    const float4 l01 = jq[JQ_LIMIT];
+    if (ji.x == BX_JOINT_REVOLUTE) {
+      V3 axis = rotate(f3(ap0), rp);
+      V3 ref_p = rotate(f3(jq[JQ_AXIS_P + 2]), rp);
+      V3 ref_c = rotate(f3(jq[JQ_AXIS_C + 2]), rc);
       float psi = signed_angle(axis, ref_p, ref_c);
-      V3 axis_c = rotate(tf3(jf + JF_AXIS_C), rc);
+      V3 axis_c = rotate(f3(jq[JQ_AXIS_C]), rc);
       V3 dq_1 = cross(axis, axis_c);
-      float ph = clipf(psi, jf[JF_LIMIT], jf[JF_LIMIT + 1]);
+      float ph = clipf(psi, l01.x, l01.y);
       V3 n1 = rotate(ref_p, quat_rot_axis(axis, ph));
       V3 dq_2 = cross(n1, ref_c);
       Q4 p1, c1, p2, c2;
@@ -407,11 +396,12 @@ __device__ __forceinline__ void phase_joints_pbd(const Ctx& c, const BxHeader& h
       dp.rot = dp.rot + (p1 + p2);
       dc.rot = dc.rot + (c1 + c2);
     } else {
-      V3 a1p = rotate(tf3(jf + JF_AXIS_P), rp);
-      V3 a2p = rotate(tf3(jf + JF_AXIS_P + 3), rp);
-      V3 a1c = rotate(tf3(jf + JF_AXIS_C), rc);
-      V3 a2c = rotate(tf3(jf + JF_AXIS_C + 3), rc);
-      V3 a3c = rotate(tf3(jf + JF_AXIS_C + 6), rc);
+      const float4 l2 = jq[JQ_LIMIT + 1];
+      V3 a1p = rotate(f3(ap0), rp);
+      V3 a2p = rotate(f3(jq[JQ_AXIS_P + 1]), rp);
+      V3 a1c = rotate(f3(jq[JQ_AXIS_C]), rc);
+      V3 a2c = rotate(f3(jq[JQ_AXIS_C + 1]), rc);
+      V3 a3c = rotate(f3(jq[JQ_AXIS_C + 2]), rc);
       V3 lon = cross(a3c, a1p);
       lon = vdiv(lon, 1e-6f + safe_norm(lon));
       V3 xz = dot(a1p, a1c) * a1c + dot(a1p, a2c) * a2c;
@@ -420,49 +410,49 @@ __device__ __forceinline__ void phase_joints_pbd(const Ctx& c, const BxHeader& h
       a2n = vdiv(a2n, 1e-6f + safe_norm(a2n));
       float sg = signf(dot(a1p, a3c));
       Q4 p1, c1, p2, c2, p3, c3;
-      limit_angle(a1p, a2p, lon, jf[JF_LIMIT], jf[JF_LIMIT + 1], ii_p, ii_c, rp, rc, sa, &p1, &c1);
-      limit_angle((-a2n) * sg, a1p, xz, jf[JF_LIMIT + 2], jf[JF_LIMIT + 3], ii_p, ii_c, rp, rc, sa, &p2, &c2);
-      limit_angle(a3c, lon, a2c, jf[JF_LIMIT + 4], jf[JF_LIMIT + 5], ii_p, ii_c, rp, rc, sa, &p3, &c3);
+      limit_angle(a1p, a2p, lon, l01.x, l01.y, ii_p, ii_c, rp, rc, sa, &p1, &c1);
+      limit_angle((-a2n) * sg, a1p, xz, l01.z, l01.w, ii_p, ii_c, rp, rc, sa, &p2, &c2);
+      limit_angle(a3c, lon, a2c, l2.x, l2.y, ii_p, ii_c, rp, rc, sa, &p3, &c3);
       dp.rot = dp.rot + ((p1 + p2) + p3);
       dc.rot = dc.rot + ((c1 + c2) + c3);
     }
-    const int r = h.r_js + 14 * j;
-    st3(c, r, dp.pos); st4(c, r + 3, dp.rot);
-    st3(c, r + 7, dc.pos); st4(c, r + 10, dc.rot);
+    const int r = h.q_js + 4 * j;
+    stv(c, r, dp.pos); stq(c, r + 1, dp.rot);
+    stv(c, r + 2, dc.pos); stq(c, r + 3, dc.rot);
   }
 }
 
 // ---- phase B2 (pbd): apply joint deltas (+ velocity projection in half A) ---
 // integrators.py:103-110 then :122-146; system.py:277-281 / :296-297.
-__device__ __forceinline__ void phase_body_joint_update(const Ctx& c, const BxHeader& h,
-                                                     bool project) {
-  const int rpos = c.cur ? h.r_pos1 : h.r_pos0, rrot = c.cur ? h.r_rot1 : h.r_rot0;
-  const int ppos = c.cur ? h.r_pos0 : h.r_pos1, prot = c.cur ? h.r_rot0 : h.r_rot1;
+BXD void phase_body_joint_update(const Ctx& c, const BxHeader& h, bool project) {
+  typedef Lay<BX_MODE_PBD> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
-    const float* bf = c.tf + h.fo_body + b * BF_STRIDE;
+    const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
+    const int r0 = L::BQ * b, rc_ = r0 + 2 * c.cur, rp_ = r0 + 2 * (c.cur ^ 1);
     V3 dpos = v3(0.f, 0.f, 0.f);
     Q4 drot = q4(0.f, 0.f, 0.f, 0.f);
-    const int32_t* adj = c.ti + h.io_adj + bi[BI_JADJ_OFF];
-    const int n = bi[BI_JADJ_N];
+    const int4 b0 = ldi4(bi);  // cslot aslot jadj_off jadj_n
+    const int32_t* adj = c.ti + h.io_adj + b0.z;
+    const int n = b0.w;
     for (int i = 0; i < n; i++) {
       int e = adj[i];
-      int r = h.r_js + 14 * (e >> 1) + 7 * (e & 1);
-      dpos = dpos + ld3(c, r);
-      drot = drot + ld4(c, r + 3);
+      int r = h.q_js + 4 * (e >> 1) + 2 * (e & 1);
+      dpos = dpos + ldv(c, r);
+      drot = drot + ldq(c, r + 1);
     }
-    V3 rm = tf3(bf + BF_ROT_MASK);
-    V3 pos = ld3(c, rpos + 3 * b) + dpos * tf3(bf + BF_POS_MASK);
-    Q4 rot = ld4(c, rrot + 4 * b);
+    V3 pm = f3(bq[BQ_POS_MASK]), rm = f3(bq[BQ_ROT_MASK]);
+    V3 pos = ldv(c, rc_) + dpos * pm;
+    Q4 rot = ldq(c, rc_ + 1);
     rot = q4(rot.w + drot.w, rot.x + drot.x * rm.x, rot.y + drot.y * rm.y, rot.z + drot.z * rm.z);
     if (project) {
       V3 vel, ang;
-      velocity_projection(h, bf, pos, ld3(c, ppos + 3 * b), ld4(c, prot + 4 * b), &rot, &vel, &ang);
-      st3(c, h.r_vel + 3 * b, vel);
-      st3(c, h.r_ang + 3 * b, ang);
+      velocity_projection(h, pm, rm, pos, ldv(c, rp_), ldq(c, rp_ + 1), &rot, &vel, &ang);
+      stv(c, r0 + L::VEL, vel);
+      stv(c, r0 + L::ANG, ang);
     }
-    st3(c, rpos + 3 * b, pos);
-    st4(c, rrot + 4 * b, rot);
+    stv(c, rc_, pos);
+    stq(c, rc_ + 1, rot);
   }
 }
 
@@ -514,25 +504,26 @@ BXD float w_of(float inv_mass, V3 inv_i, V3 r, V3 n) {
 
 // contact function of one contact row (colliders.py:667-680 box_plane,
 // :744-759 capsule_plane, :805-819 capsule_capsule).
-BXD Contact contact_fn(const Ctx& c, const BxHeader& h, int kind, const float* cf,
-                       V3 pa, Q4 ra, V3 va, V3 wa, V3 pb, Q4 rb, V3 vb, V3 wb) {
+BXD Contact contact_fn(int kind, const float4* cq, V3 pa, Q4 ra, V3 va, V3 wa, V3 pb, Q4 rb,
+                       V3 vb, V3 wb) {
   Contact ct;
+  const float4 mat = cq[CQ_MAT];
   if (kind == BX_PAIR_CAPSULE_CAPSULE) {
-    V3 ca = pa + rotate(tf3(cf + CF_PTS + 3), ra), ea = rotate(tf3(cf + CF_PTS), ra);
-    V3 cb = pb + rotate(tf3(cf + CF_PTS + 9), rb), eb = rotate(tf3(cf + CF_PTS + 6), rb);
+    V3 ca = pa + rotate(f3(cq[CQ_PTS + 1]), ra), ea = rotate(f3(cq[CQ_PTS]), ra);
+    V3 cb = pb + rotate(f3(cq[CQ_PTS + 3]), rb), eb = rotate(f3(cq[CQ_PTS + 2]), rb);
     V3 best_a, best_b;
     closest_seg_seg(ca + ea, ca - ea, cb + eb, cb - eb, &best_a, &best_b);
     V3 pv = best_a - best_b;
     float dist = safe_norm(pv);
     ct.normal = vdiv(pv, 1e-6f + dist);
-    ct.pen = cf[CF_RADIUS_A] + cf[CF_RADIUS_B] - dist;
+    ct.pen = mat.z + mat.w - dist;
     ct.pos = vdiv(best_a + best_b, 2.f);
     ct.vel = (va + cross(wa, ct.pos - pa)) - (vb + cross(wb, ct.pos - pb));
   } else {
     V3 n = rotate(v3(0.f, 0.f, 1.f), rb);
-    V3 off = rotate(tf3(cf + CF_PTS), ra);
+    V3 off = rotate(f3(cq[CQ_PTS]), ra);
     if (kind == BX_PAIR_CAPSULE_PLANE) {
-      ct.pos = (pa + off) - n * cf[CF_RADIUS_A];
+      ct.pos = (pa + off) - n * mat.z;
       ct.vel = va + cross(wa, ct.pos - pa);
     } else {  // box corner: QP.to_world base.py:112-125
       ct.pos = pa + off;
@@ -546,28 +537,29 @@ BXD Contact contact_fn(const Ctx& c, const BxHeader& h, int kind, const float* c
 
 // ---- phase C1 (pbd): contact_fn + _position_contact for every contact row ------
 // colliders.py:198-240, OneWay :306-377, TwoWay :495-582.  Row k keeps its
-// contact (pos3 normal3 pen dlambda) in rows CT+8k and its deltas (a: pos3 rot4
-// [, b: pos3 rot4]) in rows JS+delta_off(k).
-__device__ __forceinline__ void phase_contacts_position(const Ctx& c, const BxHeader& h) {
-  const int rpos = c.cur ? h.r_pos1 : h.r_pos0, rrot = c.cur ? h.r_rot1 : h.r_rot0;
-  const int ppos = c.cur ? h.r_pos0 : h.r_pos1, prot = c.cur ? h.r_rot0 : h.r_rot1;
+// contact in quads CT+2k = {pos, pen}, {normal, dlambda} and its deltas
+// (a: dpos, drot [, b: dpos, drot]) in quads JS+delta_off(k).
+BXD void phase_contacts_position(const Ctx& c, const BxHeader& h) {
+  typedef Lay<BX_MODE_PBD> L;
+  const int co = 2 * c.cur, po = 2 * (c.cur ^ 1);
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
-    const int32_t* ci = c.ti + h.io_contact + k * CI_STRIDE;
-    const float* cf = c.tf + h.fo_contact + k * CF_STRIDE;
-    const int a = ci[CI_BODY_A], b = ci[CI_BODY_B];
-    const bool two_way = ci[CI_TWO_WAY] != 0;
-    const float* bfa = c.tf + h.fo_body + a * BF_STRIDE;
-    const float* bfb = c.tf + h.fo_body + b * BF_STRIDE;
-    V3 pa = ld3(c, rpos + 3 * a), pb = ld3(c, rpos + 3 * b);
-    Q4 ra = ld4(c, rrot + 4 * a), rb = ld4(c, rrot + 4 * b);
-    Contact ct = contact_fn(c, h, ci[CI_KIND], cf, pa, ra, ld3(c, h.r_vel + 3 * a),
-                            ld3(c, h.r_ang + 3 * a), pb, rb, ld3(c, h.r_vel + 3 * b),
-                            ld3(c, h.r_ang + 3 * b));
-    V3 iia = tf3(bfa + BF_INV_INERTIA);
-    const float ima = bfa[BF_INV_MASS], ma = bfa[BF_MASS];
+    const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);  // kind two_way a b
+    const int rd = h.q_js + c.ti[h.io_contact + k * CI_STRIDE + CI_DELTA_OFF];
+    const float4* cq = c.tf + h.fo_contact + k * CQ_STRIDE;
+    const int a = ci.z, b = ci.w;
+    const bool two_way = ci.y != 0;
+    const float4* bqa = c.tf + h.fo_body + a * BQ_STRIDE;
+    const int ra0 = L::BQ * a, rb0 = L::BQ * b;
+    V3 pa = ldv(c, ra0 + co), pb = ldv(c, rb0 + co);
+    Q4 ra = ldq(c, ra0 + co + 1), rb = ldq(c, rb0 + co + 1);
+    Contact ct = contact_fn(ci.x, cq, pa, ra, ldv(c, ra0 + L::VEL), ldv(c, ra0 + L::ANG), pb, rb,
+                            ldv(c, rb0 + L::VEL), ldv(c, rb0 + L::ANG));
+    V3 iia = f3(bqa[BQ_INV_INERTIA]);
+    const float4 ma4 = bqa[BQ_MASS];
+    const float ima = ma4.x, ma = ma4.y;
+    const float friction = cq[CQ_MAT].x;
     const float cs = h.collide_scale;
     V3 n = ct.normal;
-    const int rd = h.r_js + ci[CI_DELTA_OFF];
     float dl_out;
     if (!two_way) {
       V3 pos_c = ct.pos + n * ct.pen;
@@ -582,22 +574,24 @@ __device__ __forceinline__ void phase_contacts_position(const Ctx& c, const BxHe
       Q4 drot = cs * (.5f * vec_quat_mul(iia * cross(rp, p), ra));
       // static friction
       V3 r1 = rotate(rp, qconj(ra));
-      V3 p1bar = ld3(c, ppos + 3 * a) + rotate(r1, ld4(c, prot + 4 * a));
+      V3 p1bar = ldv(c, ra0 + po) + rotate(r1, ldq(c, ra0 + po + 1));
       V3 deltap = ct.pos - p1bar;
       V3 dpt = deltap - dot(deltap, n) * n;
       float c2 = safe_norm(dpt);
       V3 n2 = vdiv(dpt, c2 + 1e-6f);
       float w1t = w_of(ima, iia, rp, n2);
       float dlt = bx_div(-c2, w1t + 0.f);
-      float sm = fabsf(dlt) < fabsf(cf[CF_FRICTION] * dl) ? 1.f : 0.f;
+      float sm = fabsf(dlt) < fabsf(friction * dl) ? 1.f : 0.f;
       V3 pt = ((dlt * n2) * sm) * cm;
       dpos = dpos + cs * vdiv(pt, ma);
       drot = drot + cs * (.5f * vec_quat_mul(iia * cross(rp, pt), ra));
-      st3(c, rd, dpos); st4(c, rd + 3, drot);
+      stv(c, rd, dpos); stq(c, rd + 1, drot);
       dl_out = dl * cm;
     } else {
-      V3 iib = tf3(bfb + BF_INV_INERTIA);
-      const float imb = bfb[BF_INV_MASS], mb = bfb[BF_MASS];
+      const float4* bqb = c.tf + h.fo_body + b * BQ_STRIDE;
+      V3 iib = f3(bqb[BQ_INV_INERTIA]);
+      const float4 mb4 = bqb[BQ_MASS];
+      const float imb = mb4.x, mb = mb4.y;
       V3 half = vdiv(n * ct.pen, 2.f);
       V3 rp = (ct.pos - half) - pa, rc = (ct.pos + half) - pb;
       float cc = -ct.pen;
@@ -611,8 +605,8 @@ __device__ __forceinline__ void phase_contacts_position(const Ctx& c, const BxHe
       // static friction
       V3 xa = ct.pos - pa, xb = ct.pos - pb;
       V3 r1 = rotate(xa, qconj(ra)), r2 = rotate(xb, qconj(rb));
-      V3 p1bar = ld3(c, ppos + 3 * a) + rotate(r1, ld4(c, prot + 4 * a));
-      V3 p2bar = ld3(c, ppos + 3 * b) + rotate(r2, ld4(c, prot + 4 * b));
+      V3 p1bar = ldv(c, ra0 + po) + rotate(r1, ldq(c, ra0 + po + 1));
+      V3 p2bar = ldv(c, rb0 + po) + rotate(r2, ldq(c, rb0 + po + 1));
       V3 deltap = (ct.pos - p1bar) - (ct.pos - p2bar);
       V3 dpt = deltap - dot(deltap, n) * n;
       float c2 = safe_norm(dpt);
@@ -625,150 +619,148 @@ __device__ __forceinline__ void phase_contacts_position(const Ctx& c, const BxHe
       dpb = dpb + cs * vdiv(-pt, mb);
       dra = dra + cs * (.5f * vec_quat_mul(iia * cross(xa, pt), ra));
       drb = drb + cs * (.5f * vec_quat_mul(iib * cross(xb, -pt), rb));
-      st3(c, rd, dpa); st4(c, rd + 3, dra);
-      st3(c, rd + 7, dpb); st4(c, rd + 10, drb);
+      stv(c, rd, dpa); stq(c, rd + 1, dra);
+      stv(c, rd + 2, dpb); stq(c, rd + 3, drb);
       dl_out = dl;  // un-masked (colliders.py:580)
     }
-    const int rc_ = h.r_ct + 8 * k;
-    st3(c, rc_, ct.pos); st3(c, rc_ + 3, ct.normal);
-    ROW(c, rc_ + 6) = ct.pen;
-    ROW(c, rc_ + 7) = dl_out;
+    const int rc_ = h.q_ct + 2 * k;
+    stv4(c, rc_, ct.pos, ct.pen);
+    stv4(c, rc_ + 1, ct.normal, dl_out);
   }
 }
 
 // Per-body scatter-and-average of the contact rows' deltas, one collider group
 // at a time (colliders.py:187-196, 231-240): sum rows, count rows with any
 // non-zero linear part, divide by (eps + count), then sum over groups.
-// W = 7 (Q deltas: pos3 rot4) or 6 (P deltas: vel3 ang3).
-template <int W>
-BXD void gather_contact_deltas(const Ctx& c, const BxHeader& h, const int32_t* bi,
-                               float eps, float* out) {
-#pragma unroll
-  for (int q = 0; q < W; q++) out[q] = 0.f;
-  const int32_t* adj = c.ti + h.io_adj + bi[BI_CADJ_OFF];
-  const int n = bi[BI_CADJ_N];
+// Each side of a row holds two quads: linear part (xyz) and a second part
+// (rot wxyz for Q deltas; ang xyz + 0 for P deltas).
+BXD void gather_contact_deltas(const Ctx& c, const BxHeader& h, int cadj_off, int n, float eps,
+                               float4* lin_out, float4* sec_out) {
+  float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), so = lo;
+  const int32_t* adj = c.ti + h.io_adj + cadj_off;
   int i = 0;
   while (i < n) {
     const int g = (adj[i] >> 1) & 7;
-    float s[W];
-#pragma unroll
-    for (int q = 0; q < W; q++) s[q] = 0.f;
+    float4 ls = make_float4(0.f, 0.f, 0.f, 0.f), ss = ls;
     float cnt = 0.f;
     for (; i < n && ((adj[i] >> 1) & 7) == g; i++) {
       const int e = adj[i];
-      const int32_t* ci = c.ti + h.io_contact + (e >> 4) * CI_STRIDE;
-      const int r = h.r_js + ci[CI_DELTA_OFF] + (e & 1) * W;
-      float v[W];
-#pragma unroll
-      for (int q = 0; q < W; q++) v[q] = ROW(c, r + q);
-      cnt += (v[0] != 0.f || v[1] != 0.f || v[2] != 0.f) ? 1.f : 0.f;
-#pragma unroll
-      for (int q = 0; q < W; q++) s[q] += v[q];
+      const int r = h.q_js + c.ti[h.io_contact + (e >> 4) * CI_STRIDE + CI_DELTA_OFF] + 2 * (e & 1);
+      const float4 l = QROW(c, r), s = QROW(c, r + 1);
+      cnt += (l.x != 0.f || l.y != 0.f || l.z != 0.f) ? 1.f : 0.f;
+      ls.x += l.x; ls.y += l.y; ls.z += l.z;
+      ss.x += s.x; ss.y += s.y; ss.z += s.z; ss.w += s.w;
     }
     const float d = eps + cnt, rd = bx_rcp(d);
-#pragma unroll
-    for (int q = 0; q < W; q++) out[q] += bx_mul_rcp(s[q], d, rd);
+    lo.x += bx_mul_rcp(ls.x, d, rd); lo.y += bx_mul_rcp(ls.y, d, rd); lo.z += bx_mul_rcp(ls.z, d, rd);
+    so.x += bx_mul_rcp(ss.x, d, rd); so.y += bx_mul_rcp(ss.y, d, rd);
+    so.z += bx_mul_rcp(ss.z, d, rd); so.w += bx_mul_rcp(ss.w, d, rd);
   }
+  *lin_out = lo; *sec_out = so;
 }
 
 // ---- phase B3 (pbd): apply contact deltas, keep qp_right_before's velocities,
 // velocity projection.  system.py:299-307.
-__device__ __forceinline__ void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
-  const int rpos = c.cur ? h.r_pos1 : h.r_pos0, rrot = c.cur ? h.r_rot1 : h.r_rot0;
-  const int ppos = c.cur ? h.r_pos0 : h.r_pos1, prot = c.cur ? h.r_rot0 : h.r_rot1;
+BXD void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
+  typedef Lay<BX_MODE_PBD> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
-    const float* bf = c.tf + h.fo_body + b * BF_STRIDE;
-    V3 pos = ld3(c, rpos + 3 * b);
-    Q4 rot = ld4(c, rrot + 4 * b);
-    if (bi[BI_CADJ_N] > 0) {
-      float d[7];
-      gather_contact_deltas<7>(c, h, bi, 1e-6f, d);
-      V3 rm = tf3(bf + BF_ROT_MASK);
-      pos = pos + v3(d[0], d[1], d[2]) * tf3(bf + BF_POS_MASK);
-      rot = q4(rot.w + d[3], rot.x + d[4] * rm.x, rot.y + d[5] * rm.y, rot.z + d[6] * rm.z);
-      st3(c, rpos + 3 * b, pos);
+    const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
+    const int r0 = L::BQ * b, rc_ = r0 + 2 * c.cur, rp_ = r0 + 2 * (c.cur ^ 1);
+    const int cslot = bi[BI_CSLOT], cadj_off = bi[BI_CADJ_OFF], cadj_n = bi[BI_CADJ_N];
+    V3 pm = f3(bq[BQ_POS_MASK]), rm = f3(bq[BQ_ROT_MASK]);
+    V3 pos = ldv(c, rc_);
+    Q4 rot = ldq(c, rc_ + 1);
+    if (cadj_n > 0) {
+      float4 dl, dr;  // dr is stored (w,x,y,z)
+      gather_contact_deltas(c, h, cadj_off, cadj_n, 1e-6f, &dl, &dr);
+      pos = pos + f3(dl) * pm;
+      rot = q4(rot.w + dr.x, rot.x + dr.y * rm.x, rot.y + dr.z * rm.y, rot.z + dr.w * rm.z);
+      stv(c, rc_, pos);
     }
-    if (bi[BI_CSLOT] >= 0) {  // qp_right_before.vel / .ang (system.py:306)
-      const int r = h.r_pre + 6 * bi[BI_CSLOT];
-      st3(c, r, ld3(c, h.r_vel + 3 * b));
-      st3(c, r + 3, ld3(c, h.r_ang + 3 * b));
+    if (cslot >= 0) {  // qp_right_before.vel / .ang (system.py:306)
+      const int r = h.q_pre + 2 * cslot;
+      QROW(c, r) = QROW(c, r0 + L::VEL);
+      QROW(c, r + 1) = QROW(c, r0 + L::ANG);
     }
     V3 vel, ang;
-    velocity_projection(h, bf, pos, ld3(c, ppos + 3 * b), ld4(c, prot + 4 * b), &rot, &vel, &ang);
-    st3(c, h.r_vel + 3 * b, vel);
-    st3(c, h.r_ang + 3 * b, ang);
-    st4(c, rrot + 4 * b, rot);
+    velocity_projection(h, pm, rm, pos, ldv(c, rp_), ldq(c, rp_ + 1), &rot, &vel, &ang);
+    stv(c, r0 + L::VEL, vel);
+    stv(c, r0 + L::ANG, ang);
+    stq(c, rc_ + 1, rot);
   }
 }
 
 // ---- phase C2 (pbd): _velocity_contact for every contact row ------------------
-// colliders.py:155-196, OneWay :379-442, TwoWay :584-658.  Deltas (a: vel3 ang3
-// [, b: vel3 ang3]) go to rows JS+delta_off(k).
-__device__ __forceinline__ void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
-  const int rpos = c.cur ? h.r_pos1 : h.r_pos0;
+// colliders.py:155-196, OneWay :379-442, TwoWay :584-658.  Deltas (a: dvel, dang
+// [, b: dvel, dang]) go to quads JS+delta_off(k).
+BXD void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
+  typedef Lay<BX_MODE_PBD> L;
+  const int co = 2 * c.cur;
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
-    const int32_t* ci = c.ti + h.io_contact + k * CI_STRIDE;
-    const float* cf = c.tf + h.fo_contact + k * CF_STRIDE;
-    const int a = ci[CI_BODY_A], b = ci[CI_BODY_B];
-    const bool two_way = ci[CI_TWO_WAY] != 0;
-    const int32_t* bia = c.ti + h.io_body + a * BI_STRIDE;
-    const float* bfa = c.tf + h.fo_body + a * BF_STRIDE;
-    const int rc_ = h.r_ct + 8 * k;
-    V3 cpos = ld3(c, rc_), n = ld3(c, rc_ + 3);
-    const float pen = ROW(c, rc_ + 6), dlambda = ROW(c, rc_ + 7);
-    V3 pa = ld3(c, rpos + 3 * a);
+    const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);
+    const int rd = h.q_js + c.ti[h.io_contact + k * CI_STRIDE + CI_DELTA_OFF];
+    const float4 mat = c.tf[h.fo_contact + k * CQ_STRIDE + CQ_MAT];
+    const int a = ci.z, b = ci.w;
+    const bool two_way = ci.y != 0;
+    const float4* bqa = c.tf + h.fo_body + a * BQ_STRIDE;
+    const int ra0 = L::BQ * a;
+    const float4 c0 = QROW(c, h.q_ct + 2 * k), c1 = QROW(c, h.q_ct + 2 * k + 1);
+    V3 cpos = f3(c0), n = f3(c1);
+    const float pen = c0.w, dlambda = c1.w;
+    V3 pa = ldv(c, ra0 + co);
     V3 ra = cpos - pa;
-    V3 iia = tf3(bfa + BF_INV_INERTIA);
-    const float ima = bfa[BF_INV_MASS], ma = bfa[BF_MASS];
-    const int rpre_a = h.r_pre + 6 * bia[BI_CSLOT];
-    const int rd = h.r_js + ci[CI_DELTA_OFF];
+    V3 iia = f3(bqa[BQ_INV_INERTIA]);
+    const float4 ma4 = bqa[BQ_MASS];
+    const float ima = ma4.x, ma = ma4.y;
+    const int rpre_a = h.q_pre + 2 * c.ti[h.io_body + a * BI_STRIDE + BI_CSLOT];
     const float stat = pen > 0.f ? 1.f : 0.f;
     if (!two_way) {
-      V3 rel = ld3(c, h.r_vel + 3 * a) + cross(ld3(c, h.r_ang + 3 * a), ra);
+      V3 rel = ldv(c, ra0 + L::VEL) + cross(ldv(c, ra0 + L::ANG), ra);
       float v_n = dot(rel, n);
       V3 v_t = rel - n * v_n;
       float vtn = safe_norm(v_t);
       V3 vdir = vdiv(v_t, 1e-6f + vtn);
-      float lim = (cf[CF_FRICTION] * fabsf(dlambda)) * h.inv_2h;
+      float lim = (mat.x * fabsf(dlambda)) * h.inv_2h;
       V3 dvel = (-vdir) * fminf(lim, vtn);
       V3 angw = cross(ra, vdir);
       float w = ima + dot(angw, angw);  // no inertia here (colliders.py:405-406)
       V3 p_dyn = vdiv(dvel, w + 1e-6f);
       // restitution; qp_right_before has the same pos as now
-      V3 rel_old = ld3(c, rpre_a) + cross(ld3(c, rpre_a + 3), ra);
+      V3 rel_old = ldv(c, rpre_a) + cross(ldv(c, rpre_a + 1), ra);
       float v_n_old = dot(rel_old, n);
-      V3 dx = n * (-v_n - fminf(cf[CF_ELASTICITY] * v_n_old, 0.f));
+      V3 dx = n * (-v_n - fminf(mat.y * v_n_old, 0.f));
       float cc = safe_norm(dx);
       V3 n2 = vdiv(dx, cc + 1e-6f);
       float w1 = w_of(ima, iia, ra, n2);
       float dlr = bx_div(cc, w1 + 1e-6f);
       float sink = v_n_old <= -h.vth ? 1.f : 0.f;
       V3 p = (((dlr * n2) * sink) + p_dyn) * stat;
-      st3(c, rd, vdiv(p, ma));
-      st3(c, rd + 3, cross(iia * ra, p));
+      stv(c, rd, vdiv(p, ma));
+      stv(c, rd + 1, cross(iia * ra, p));
     } else {
-      const int32_t* bib = c.ti + h.io_body + b * BI_STRIDE;
-      const float* bfb = c.tf + h.fo_body + b * BF_STRIDE;
-      V3 iib = tf3(bfb + BF_INV_INERTIA);
-      const float imb = bfb[BF_INV_MASS], mb = bfb[BF_MASS];
-      const int rpre_b = h.r_pre + 6 * bib[BI_CSLOT];
-      V3 pb = ld3(c, rpos + 3 * b);
+      const float4* bqb = c.tf + h.fo_body + b * BQ_STRIDE;
+      const int rb0 = L::BQ * b;
+      V3 iib = f3(bqb[BQ_INV_INERTIA]);
+      const float4 mb4 = bqb[BQ_MASS];
+      const float imb = mb4.x, mb = mb4.y;
+      const int rpre_b = h.q_pre + 2 * c.ti[h.io_body + b * BI_STRIDE + BI_CSLOT];
+      V3 pb = ldv(c, rb0 + co);
       V3 rb = cpos - pb;
-      V3 rel = (ld3(c, h.r_vel + 3 * a) + cross(ld3(c, h.r_ang + 3 * a), ra)) -
-               (ld3(c, h.r_vel + 3 * b) + cross(ld3(c, h.r_ang + 3 * b), rb));
+      V3 rel = (ldv(c, ra0 + L::VEL) + cross(ldv(c, ra0 + L::ANG), ra)) -
+               (ldv(c, rb0 + L::VEL) + cross(ldv(c, rb0 + L::ANG), rb));
       float v_n = dot(rel, n);
       V3 v_t = rel - n * v_n;
       float vtn = safe_norm(v_t);
       V3 vdir = vdiv(v_t, 1e-6f + vtn);
-      float lim = (cf[CF_FRICTION] * fabsf(dlambda)) * h.inv_2h;
+      float lim = (mat.x * fabsf(dlambda)) * h.inv_2h;
       V3 dvel = (-vdir) * fminf(lim, vtn);
       float w1 = w_of(ima, iia, ra, vdir), w2 = w_of(imb, iib, rb, vdir);
       V3 p_dyn = vdiv(dvel, w1 + w2 + 1e-6f);
-      V3 rel_old = (ld3(c, rpre_a) + cross(ld3(c, rpre_a + 3), ra)) -
-                   (ld3(c, rpre_b) + cross(ld3(c, rpre_b + 3), rb));
+      V3 rel_old = (ldv(c, rpre_a) + cross(ldv(c, rpre_a + 1), ra)) -
+                   (ldv(c, rpre_b) + cross(ldv(c, rpre_b + 1), rb));
       float v_n_old = dot(rel_old, n);
-      V3 dx = n * (-v_n - fminf(cf[CF_ELASTICITY] * v_n_old, 0.f));
+      V3 dx = n * (-v_n - fminf(mat.y * v_n_old, 0.f));
       V3 rc2 = (cpos + n * pen) - pb;
       float cc = safe_norm(dx);
       V3 n2 = vdiv(dx, cc + 1e-6f);
@@ -776,30 +768,33 @@ __device__ __forceinline__ void phase_contacts_velocity(const Ctx& c, const BxHe
       float dlr = bx_div(cc, w1r + w2r + 1e-6f);
       float sink = v_n_old <= 0.f ? 1.f : 0.f;
       V3 p = (((dlr * n2) * sink) + p_dyn) * stat;
-      st3(c, rd, vdiv(p, ma));
-      st3(c, rd + 3, cross(iia * ra, p));
-      st3(c, rd + 6, vdiv(-p, mb));
-      st3(c, rd + 9, cross(iib * rb, -p));
+      stv(c, rd, vdiv(p, ma));
+      stv(c, rd + 1, cross(iia * ra, p));
+      stv(c, rd + 2, vdiv(-p, mb));
+      stv(c, rd + 3, cross(iib * rb, -p));
     }
   }
 }
 
 // ---- phase B4: velocity-level contact update + Info.contact -----------------
 // integrators.py:97-101; system.py:313,315 (pbd) / :365,367 (legacy_spring).
-__device__ __forceinline__ void phase_body_velocity_update(const Ctx& c, const BxHeader& h,
-                                                        float eps) {
+template <int MODE>
+BXD void phase_body_velocity_update(const Ctx& c, const BxHeader& h, float eps) {
+  typedef Lay<MODE> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
-    if (bi[BI_CADJ_N] == 0) continue;
-    const float* bf = c.tf + h.fo_body + b * BF_STRIDE;
-    float d[6];
-    gather_contact_deltas<6>(c, h, bi, eps, d);
-    V3 dv = v3(d[0], d[1], d[2]), da = v3(d[3], d[4], d[5]);
-    st3(c, h.r_vel + 3 * b, (ld3(c, h.r_vel + 3 * b) + dv) * tf3(bf + BF_POS_MASK));
-    st3(c, h.r_ang + 3 * b, (ld3(c, h.r_ang + 3 * b) + da) * tf3(bf + BF_ROT_MASK));
-    const int r = h.r_ic + 6 * bi[BI_CSLOT];
-    st3(c, r, ld3(c, r) + dv);
-    st3(c, r + 3, ld3(c, r + 3) + da);
+    const int cadj_n = bi[BI_CADJ_N];
+    if (cadj_n == 0) continue;
+    const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
+    const int r0 = L::BQ * b;
+    float4 dl, ds;
+    gather_contact_deltas(c, h, bi[BI_CADJ_OFF], cadj_n, eps, &dl, &ds);
+    V3 dv = f3(dl), da = f3(ds);
+    stv(c, r0 + L::VEL, (ldv(c, r0 + L::VEL) + dv) * f3(bq[BQ_POS_MASK]));
+    stv(c, r0 + L::ANG, (ldv(c, r0 + L::ANG) + da) * f3(bq[BQ_ROT_MASK]));
+    const int r = h.q_ic + 2 * bi[BI_CSLOT];
+    stv(c, r, ldv(c, r) + dv);
+    stv(c, r + 1, ldv(c, r + 1) + da);
   }
 }
 
@@ -811,58 +806,66 @@ BXD void body_impulse(float mass, V3 inv_i, V3 bpos, V3 imp, V3 at, V3* dvel, V3
 }
 
 // phase S1: kinetic step for every body, in place (system.py:352).
-__device__ __forceinline__ void phase_body_kinetic(const Ctx& c, const BxHeader& h) {
+BXD void phase_body_kinetic(const Ctx& c, const BxHeader& h) {
+  typedef Lay<BX_MODE_LEGACY_SPRING> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
-    const float* bf = c.tf + h.fo_body + b * BF_STRIDE;
-    V3 pos = ld3(c, h.r_pos0 + 3 * b);
-    Q4 rot = ld4(c, h.r_rot0 + 4 * b);
-    kinetic(h, bf, ld3(c, h.r_vel + 3 * b), ld3(c, h.r_ang + 3 * b), &pos, &rot);
-    st3(c, h.r_pos0 + 3 * b, pos);
-    st4(c, h.r_rot0 + 4 * b, rot);
+    const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
+    const int r0 = L::BQ * b;
+    V3 pos = ldv(c, r0);
+    Q4 rot = ldq(c, r0 + 1);
+    kinetic(h, f3(bq[BQ_POS_MASK]), f3(bq[BQ_ROT_MASK]), ldv(c, r0 + L::VEL), ldv(c, r0 + L::ANG),
+            &pos, &rot);
+    stv(c, r0, pos);
+    stq(c, r0 + 1, rot);
   }
 }
 
-// phase S2: spring joints (spring_joints.py:89-303) -> slot rows
-// JS+3na+12j: parent vel3 ang3, child vel3 ang3.
-__device__ __forceinline__ void phase_joints_spring(const Ctx& c, const BxHeader& h) {
+// phase S2: spring joints (spring_joints.py:89-303) -> slot quads
+// JS+na+4j: parent dvel, dang, child dvel, dang.
+BXD void phase_joints_spring(const Ctx& c, const BxHeader& h) {
+  typedef Lay<BX_MODE_LEGACY_SPRING> L;
   for (int j = c.warp; j < h.nj; j += c.nwarp) {
-    const int32_t* ji = c.ti + h.io_joint + j * JI_STRIDE;
-    const float* jf = c.tf + h.fo_joint + j * JF_STRIDE;
-    const int kind = ji[JI_KIND], bp = ji[JI_BODY_P], bc = ji[JI_BODY_C];
-    const float* bfp = c.tf + h.fo_body + bp * BF_STRIDE;
-    const float* bfc = c.tf + h.fo_body + bc * BF_STRIDE;
-    V3 pos_p = ld3(c, h.r_pos0 + 3 * bp), pos_c = ld3(c, h.r_pos0 + 3 * bc);
-    Q4 rp = ld4(c, h.r_rot0 + 4 * bp), rc = ld4(c, h.r_rot0 + 4 * bc);
-    V3 ang_p = ld3(c, h.r_ang + 3 * bp), ang_c = ld3(c, h.r_ang + 3 * bc);
-    V3 ii_p = tf3(bfp + BF_INV_INERTIA), ii_c = tf3(bfc + BF_INV_INERTIA);
+    const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
+    const float4* jq = c.tf + h.fo_joint + j * JQ_STRIDE;
+    const int kind = ji.x, bp = ji.y, bc = ji.z;
+    const float4* bqp = c.tf + h.fo_body + bp * BQ_STRIDE;
+    const float4* bqc = c.tf + h.fo_body + bc * BQ_STRIDE;
+    const int rp0 = L::BQ * bp, rc0 = L::BQ * bc;
+    V3 pos_p = ldv(c, rp0), pos_c = ldv(c, rc0);
+    Q4 rp = ldq(c, rp0 + 1), rc = ldq(c, rc0 + 1);
+    V3 ang_p = ldv(c, rp0 + L::ANG), ang_c = ldv(c, rc0 + L::ANG);
+    V3 ii_p = f3(bqp[BQ_INV_INERTIA]), ii_c = f3(bqc[BQ_INV_INERTIA]);
+    const float4 j0 = jq[JQ_OFF_P], j1 = jq[JQ_OFF_C];
+    const float stiffness = jq[JQ_AXIS_P + 1].w, spring_damp = jq[JQ_AXIS_P + 2].w;
+    const float ang_damp = j0.w, ls = jq[JQ_AXIS_C].w;
     // QP.to_world base.py:112-125
-    V3 op = rotate(tf3(jf + JF_OFF_P), rp), oc = rotate(tf3(jf + JF_OFF_C), rc);
+    V3 op = rotate(f3(j0), rp), oc = rotate(f3(j1), rc);
     V3 wp = pos_p + op, wc = pos_c + oc;
-    V3 vp = ld3(c, h.r_vel + 3 * bp) + cross(ang_p, op);
-    V3 vc = ld3(c, h.r_vel + 3 * bc) + cross(ang_c, oc);
-    V3 imp = (wp - wc) * jf[JF_STIFFNESS] + jf[JF_SPRING_DAMP] * (vp - vc);
+    V3 vp = ldv(c, rp0 + L::VEL) + cross(ang_p, op);
+    V3 vc = ldv(c, rc0 + L::VEL) + cross(ang_c, oc);
+    V3 imp = (wp - wc) * stiffness + spring_damp * (vp - vc);
     V3 dvp, dap, dvc, dac;
-    body_impulse(bfp[BF_MASS], ii_p, pos_p, -imp, wp, &dvp, &dap);
-    body_impulse(bfc[BF_MASS], ii_c, pos_c, imp, wc, &dvc, &dac);
+    body_impulse(bqp[BQ_MASS].y, ii_p, pos_p, -imp, wp, &dvp, &dap);
+    body_impulse(bqc[BQ_MASS].y, ii_c, pos_c, imp, wc, &dvc, &dac);
     V3 axis[3];
     float angle[3], dang[3];
-    joint_axis_angle(kind, jf, rp, rc, axis, angle);
+    joint_axis_angle(kind, jq, rp, rc, axis, angle);
     const int dof = joint_dof(kind);
+    const float4 l01 = jq[JQ_LIMIT], l2 = jq[JQ_LIMIT + 1];
+    const float lo[3] = {l01.x, l01.z, l2.x}, hi[3] = {l01.y, l01.w, l2.y};
 #pragma unroll
     for (int d = 0; d < 3; d++) {
-      float lo = jf[JF_LIMIT + 2 * d], hi = jf[JF_LIMIT + 2 * d + 1];
       float v = 0.f;
       if (d < dof) {
-        v = angle[d] < lo ? lo - angle[d] : 0.f;
-        v = angle[d] > hi ? hi - angle[d] : v;
+        v = angle[d] < lo[d] ? lo[d] - angle[d] : 0.f;
+        v = angle[d] > hi[d] ? hi[d] - angle[d] : v;
       }
       dang[d] = v;
     }
-    const float ls = jf[JF_LIMIT_STRENGTH];
     V3 tq;
     if (kind == BX_JOINT_SPRING_REVOLUTE) {  // spring_joints.py:127-148
-      V3 axis_c = rotate(tf3(jf + JF_AXIS_C), rc);
-      tq = jf[JF_STIFFNESS] * cross(axis[0], axis_c);
+      V3 axis_c = rotate(f3(jq[JQ_AXIS_C]), rc);
+      tq = stiffness * cross(axis[0], axis_c);
       tq = tq - (ls * axis[0]) * dang[0];
     } else if (kind == BX_JOINT_SPRING_UNIVERSAL) {  // :178-210
       V3 proj = axis[1] - dot(axis[1], axis[0]) * axis[0];
@@ -872,63 +875,68 @@ __device__ __forceinline__ void phase_joints_spring(const Ctx& c, const BxHeader
     } else {  // spring Spherical :249-274
       tq = (-ls) * ((axis[0] * dang[0] + axis[1] * dang[1]) + axis[2] * dang[2]);
     }
-    tq = tq - jf[JF_ANG_DAMP] * (ang_p - ang_c);
+    tq = tq - ang_damp * (ang_p - ang_c);
     dap = dap + ii_p * tq;
     dac = dac + (-ii_c) * tq;
-    const int r = h.r_js + 3 * h.na + 12 * j;
-    st3(c, r, dvp); st3(c, r + 3, dap); st3(c, r + 6, dvc); st3(c, r + 9, dac);
+    const int r = h.q_js + h.na + 4 * j;
+    stv(c, r, dvp); stv(c, r + 1, dap); stv(c, r + 2, dvc); stv(c, r + 3, dac);
   }
 }
 
 // phase S3: acceleration update from joints + actuators + forces; Info.joint and
 // Info.actuator accumulation (system.py:356-359,367).
-__device__ __forceinline__ void phase_body_acc_spring(const Ctx& c, const BxHeader& h) {
+BXD void phase_body_acc_spring(const Ctx& c, const BxHeader& h) {
+  typedef Lay<BX_MODE_LEGACY_SPRING> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
-    const float* bf = c.tf + h.fo_body + b * BF_STRIDE;
+    const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
+    const int r0 = L::BQ * b;
     V3 dpa, unused, fv, fa;
-    body_accels(c, h, b, bi, bf, false, &dpa, &unused, &fv, &fa);
+    body_accels(c, h, bi, bq, false, &dpa, &unused, &fv, &fa);
     V3 jv = v3(0.f, 0.f, 0.f), ja = v3(0.f, 0.f, 0.f);
     const int32_t* adj = c.ti + h.io_adj + bi[BI_JADJ_OFF];
     const int n = bi[BI_JADJ_N];
     for (int i = 0; i < n; i++) {
       int e = adj[i];
-      int r = h.r_js + 3 * h.na + 12 * (e >> 1) + 6 * (e & 1);
-      jv = jv + ld3(c, r);
-      ja = ja + ld3(c, r + 3);
+      int r = h.q_js + h.na + 4 * (e >> 1) + 2 * (e & 1);
+      jv = jv + ldv(c, r);
+      ja = ja + ldv(c, r + 1);
     }
     V3 g = v3(h.gravity[0], h.gravity[1], h.gravity[2]);
     V3 acc_v = jv + fv, acc_a = (ja + dpa) + fa;
-    V3 vel = (h.vel_damp * ld3(c, h.r_vel + 3 * b) + (acc_v + g) * h.dt) * tf3(bf + BF_POS_MASK);
-    V3 ang = (h.ang_damp * ld3(c, h.r_ang + 3 * b) + acc_a * h.dt) * tf3(bf + BF_ROT_MASK);
-    st3(c, h.r_vel + 3 * b, vel);
-    st3(c, h.r_ang + 3 * b, ang);
-    const int rj = h.r_ij + 6 * b;
-    st3(c, rj, ld3(c, rj) + jv);
-    st3(c, rj + 3, ld3(c, rj + 3) + ja);
+    V3 vel = (h.vel_damp * ldv(c, r0 + L::VEL) + (acc_v + g) * h.dt) * f3(bq[BQ_POS_MASK]);
+    V3 ang = (h.ang_damp * ldv(c, r0 + L::ANG) + acc_a * h.dt) * f3(bq[BQ_ROT_MASK]);
+    stv(c, r0 + L::VEL, vel);
+    stv(c, r0 + L::ANG, ang);
+    const int rj = h.q_ij + 2 * b;
+    stv(c, rj, ldv(c, rj) + jv);
+    stv(c, rj + 1, ldv(c, rj + 1) + ja);
     if (bi[BI_ASLOT] >= 0) {
-      int r = h.r_ia + 3 * bi[BI_ASLOT];
-      st3(c, r, ld3(c, r) + dpa);
+      int r = h.q_ia + bi[BI_ASLOT];
+      stv(c, r, ldv(c, r) + dpa);
     }
   }
 }
 
 // phase S4: contact_fn + velocity-level _contact (colliders.py:116-153,
 // OneWay :267-304, TwoWay :449-493).
-__device__ __forceinline__ void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
+BXD void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
+  typedef Lay<BX_MODE_LEGACY_SPRING> L;
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
-    const int32_t* ci = c.ti + h.io_contact + k * CI_STRIDE;
-    const float* cf = c.tf + h.fo_contact + k * CF_STRIDE;
-    const int a = ci[CI_BODY_A], b = ci[CI_BODY_B];
-    const bool two_way = ci[CI_TWO_WAY] != 0;
-    const float* bfa = c.tf + h.fo_body + a * BF_STRIDE;
-    const float* bfb = c.tf + h.fo_body + b * BF_STRIDE;
-    V3 pa = ld3(c, h.r_pos0 + 3 * a), pb = ld3(c, h.r_pos0 + 3 * b);
-    Contact ct = contact_fn(c, h, ci[CI_KIND], cf, pa, ld4(c, h.r_rot0 + 4 * a),
-                            ld3(c, h.r_vel + 3 * a), ld3(c, h.r_ang + 3 * a), pb,
-                            ld4(c, h.r_rot0 + 4 * b), ld3(c, h.r_vel + 3 * b),
-                            ld3(c, h.r_ang + 3 * b));
-    V3 iia = tf3(bfa + BF_INV_INERTIA), iib = tf3(bfb + BF_INV_INERTIA);
+    const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);
+    const int rd = h.q_js + c.ti[h.io_contact + k * CI_STRIDE + CI_DELTA_OFF];
+    const float4* cq = c.tf + h.fo_contact + k * CQ_STRIDE;
+    const int a = ci.z, b = ci.w;
+    const bool two_way = ci.y != 0;
+    const float4* bqa = c.tf + h.fo_body + a * BQ_STRIDE;
+    const float4* bqb = c.tf + h.fo_body + b * BQ_STRIDE;
+    const int ra0 = L::BQ * a, rb0 = L::BQ * b;
+    V3 pa = ldv(c, ra0), pb = ldv(c, rb0);
+    Contact ct = contact_fn(ci.x, cq, pa, ldq(c, ra0 + 1), ldv(c, ra0 + L::VEL), ldv(c, ra0 + L::ANG),
+                            pb, ldq(c, rb0 + 1), ldv(c, rb0 + L::VEL), ldv(c, rb0 + L::ANG));
+    const float4 mat = cq[CQ_MAT];
+    V3 iia = f3(bqa[BQ_INV_INERTIA]), iib = f3(bqb[BQ_INV_INERTIA]);
+    const float mass_a = bqa[BQ_MASS].y, mass_b = bqb[BQ_MASS].y;
     V3 n = ct.normal;
     V3 ra = ct.pos - pa, rb = ct.pos - pb;
     float baum = h.erp * ct.pen;
@@ -938,92 +946,99 @@ __device__ __forceinline__ void phase_contacts_spring(const Ctx& c, const BxHead
     if (two_way) {
       V3 c2 = cross(iib * cross(rb, n), rb);
       ang = dot(n, c1 + c2);
-      denom = bx_div(1.f, bfa[BF_MASS]) + bx_div(1.f, bfb[BF_MASS]) + ang;
+      denom = bx_div(1.f, mass_a) + bx_div(1.f, mass_b) + ang;
     } else {
       ang = dot(n, c1);
-      denom = bx_div(1.f, bfa[BF_MASS]) + ang;
+      denom = bx_div(1.f, mass_a) + ang;
     }
-    float imp = bx_div(-1.f * (1.f + cf[CF_ELASTICITY]) * nv + baum, denom);
+    float imp = bx_div(-1.f * (1.f + mat.y) * nv + baum, denom);
     V3 vd = ct.vel - nv * n;
     float nvd = safe_norm(vd);
-    float impd = fminf(bx_div(nvd, denom), cf[CF_FRICTION] * imp);
+    float impd = fminf(bx_div(nvd, denom), mat.x * imp);
     V3 dir = vdiv(vd, 1e-6f + nvd);
     float apn = (ct.pen > 0.f && nv < 0.f && imp > 0.f) ? 1.f : 0.f;
     float apd = apn * (nvd > 0.01f ? 1.f : 0.f);
     V3 dvn, dan, dvd, dad;
-    body_impulse(bfa[BF_MASS], iia, pa, imp * n, ct.pos, &dvn, &dan);
-    body_impulse(bfa[BF_MASS], iia, pa, (-impd) * dir, ct.pos, &dvd, &dad);
-    const int rd = h.r_js + ci[CI_DELTA_OFF];
-    st3(c, rd, dvn * apn + dvd * apd);
-    st3(c, rd + 3, dan * apn + dad * apd);
+    body_impulse(mass_a, iia, pa, imp * n, ct.pos, &dvn, &dan);
+    body_impulse(mass_a, iia, pa, (-impd) * dir, ct.pos, &dvd, &dad);
+    stv(c, rd, dvn * apn + dvd * apd);
+    stv(c, rd + 1, dan * apn + dad * apd);
     if (two_way) {
-      body_impulse(bfb[BF_MASS], iib, pb, (-imp) * n, ct.pos, &dvn, &dan);
-      body_impulse(bfb[BF_MASS], iib, pb, impd * dir, ct.pos, &dvd, &dad);
-      st3(c, rd + 6, dvn * apn + dvd * apd);
-      st3(c, rd + 9, dan * apn + dad * apd);
+      body_impulse(mass_b, iib, pb, (-imp) * n, ct.pos, &dvn, &dan);
+      body_impulse(mass_b, iib, pb, impd * dir, ct.pos, &dvd, &dad);
+      stv(c, rd + 2, dvn * apn + dvd * apd);
+      stv(c, rd + 3, dan * apn + dad * apd);
     }
-    const int rc_ = h.r_ct + 8 * k;
-    st3(c, rc_, ct.pos); st3(c, rc_ + 3, ct.normal);
-    ROW(c, rc_ + 6) = ct.pen;
+    const int rc_ = h.q_ct + 2 * k;
+    stv4(c, rc_, ct.pos, ct.pen);
+    stv4(c, rc_ + 1, ct.normal, 0.f);
   }
 }
 
 // ============================== the kernel ====================================
-extern __shared__ __align__(16) float bx_smem[];
-
-__device__ __forceinline__ void zero_rows(float* sm, int row0, int nrows) {
-  for (int i = threadIdx.x; i < nrows * RS; i += blockDim.x) sm[row0 * RS + i] = 0.f;
-}
+extern __shared__ __align__(16) float4 bx_smem[];
 
 // blockDim.x = 32 * W (W warps share one tile of 32 environments).
 template <int MODE>
 __global__ void __launch_bounds__(512, 1)
 bx_step_kernel(const __grid_constant__ BxKernelParams p) {
+  typedef Lay<MODE> L;
   const BxHeader& h = p.h;
-  float* sm = bx_smem;
-  float* tf = sm + h.n_rows * RS;
-  int32_t* ti = reinterpret_cast<int32_t*>(tf + h.n_floats);
+  float4* sq = bx_smem;
+  float4* tf = sq + h.n_quads * QS;
+  int32_t* ti = reinterpret_cast<int32_t*>(tf + h.n_fquads);
+  float* smf = reinterpret_cast<float*>(sq);
   const int64_t env0 = static_cast<int64_t>(blockIdx.x) * BX_ENVS_PER_CTA;
   const int nenv = static_cast<int>((p.num_envs - env0) < BX_ENVS_PER_CTA ? (p.num_envs - env0) : BX_ENVS_PER_CTA);
 
-  for (int i = threadIdx.x; i < h.n_floats; i += blockDim.x) tf[i] = __ldg(p.tab_f + i);
+  for (int i = threadIdx.x; i < h.n_fquads; i += blockDim.x) tf[i] = __ldg(p.tab_f + i);
   for (int i = threadIdx.x; i < h.n_ints; i += blockDim.x) ti[i] = __ldg(p.tab_i + i);
   if (nenv < BX_ENVS_PER_CTA) {
     // partial tile: give the idle env slots a benign state (identity rotations)
-    for (int i = threadIdx.x; i < h.n_rows * RS; i += blockDim.x) sm[i] = 0.f;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = threadIdx.x; i < h.n_quads * QS; i += blockDim.x) sq[i] = z;
     __syncthreads();
-    for (int i = threadIdx.x; i < h.nb * BX_ENVS_PER_CTA; i += blockDim.x) {
-      int b = i / BX_ENVS_PER_CTA, e = i - b * BX_ENVS_PER_CTA;
-      sm[(h.r_rot0 + 4 * b) * RS + e] = 1.f;
+    const int nrot = MODE == BX_MODE_PBD ? 2 : 1;
+    for (int i = threadIdx.x; i < h.nb * nrot * BX_ENVS_PER_CTA; i += blockDim.x) {
+      const int br = i / BX_ENVS_PER_CTA, e = i - br * BX_ENVS_PER_CTA;
+      const int b = br / nrot, which = br - b * nrot;
+      sq[(L::BQ * b + 2 * which + 1) * QS + e] = make_float4(1.f, 0.f, 0.f, 0.f);
     }
-    __syncthreads();
   }
-  load_rows(sm, p.io.pos, env0, nenv, 3 * h.nb, h.r_pos0);
-  load_rows(sm, p.io.rot, env0, nenv, 4 * h.nb, h.r_rot0);
-  load_rows(sm, p.io.vel, env0, nenv, 3 * h.nb, h.r_vel);
-  load_rows(sm, p.io.ang, env0, nenv, 3 * h.nb, h.r_ang);
+  __syncthreads();
+  for (int s = 0; s < 4; s++)
+    io_segment<true>(smf, ti, h.seg_in[s], const_cast<float*>(p.in[s]), env0, nenv);
 
   Ctx c;
-  c.lane = threadIdx.x & 31;
   c.warp = threadIdx.x >> 5;
   c.nwarp = blockDim.x >> 5;
-  c.st = sm + c.lane;
+  c.q = sq + (threadIdx.x & 31);
   c.tf = tf;
   c.ti = ti;
   c.cur = 0;
 
   for (int step = 0; step < p.num_steps; step++) {
     __syncthreads();
-    load_rows(sm, p.io.act + static_cast<int64_t>(step) * p.num_envs * h.act_size, env0,
-              nenv, h.act_size, h.r_act);
+    io_segment<true>(smf, ti, h.seg_in[4],
+                     const_cast<float*>(p.in[4]) + static_cast<int64_t>(step) * p.num_envs * h.act_size,
+                     env0, nenv);
     // zero_info (system.py:76-84): Info accumulators start at 0 every step
-    zero_rows(sm, h.r_ic, 6 * h.ncb + 3 * h.nab + (MODE == BX_MODE_LEGACY_SPRING ? 6 * h.nb : 0));
+    {
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int i = threadIdx.x; i < h.n_zero * QS; i += blockDim.x) sq[h.q_ic * QS + i] = z;
+      if (h.iters == 0)  // contact_penetration = -1 (system.py:84)
+        for (int i = threadIdx.x; i < h.nk * QS; i += blockDim.x) {
+          const int k = i / QS, e = i - k * QS;
+          sq[(h.q_ct + 2 * k) * QS + e] = make_float4(0.f, 0.f, 0.f, -1.f);
+          sq[(h.q_ct + 2 * k + 1) * QS + e] = z;
+        }
+    }
     __syncthreads();
     if constexpr (MODE == BX_MODE_PBD) {
       for (int it = 0; it < h.iters; it++) {
 #pragma unroll 1
         for (int half = 0; half < 2; half++) {
-          phase_torques(c, h, true);
+          phase_torques<MODE>(c, h, true);
           __syncthreads();
           phase_body_acc_kinetic(c, h, half == 1);
           c.cur ^= 1;
@@ -1039,7 +1054,7 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
             __syncthreads();
             phase_contacts_velocity(c, h);
             __syncthreads();
-            phase_body_velocity_update(c, h, 1e-6f);
+            phase_body_velocity_update<MODE>(c, h, 1e-6f);
             __syncthreads();
           }
         }
@@ -1048,45 +1063,22 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
       for (int it = 0; it < h.iters; it++) {
         phase_body_kinetic(c, h);
         __syncthreads();
-        phase_torques(c, h, false);
+        phase_torques<MODE>(c, h, false);
         phase_joints_spring(c, h);
         __syncthreads();
         phase_body_acc_spring(c, h);
         __syncthreads();
         phase_contacts_spring(c, h);
         __syncthreads();
-        phase_body_velocity_update(c, h, 1e-8f);
+        phase_body_velocity_update<MODE>(c, h, 1e-8f);
         // same warp<->body mapping as phase_body_kinetic: no barrier needed
       }
     }
   }
   __syncthreads();
 
-  const int rpos = c.cur ? h.r_pos1 : h.r_pos0, rrot = c.cur ? h.r_rot1 : h.r_rot0;
-  store_rows(sm, p.io.pos_o, env0, nenv, 3 * h.nb, rpos, nullptr);
-  store_rows(sm, p.io.rot_o, env0, nenv, 4 * h.nb, rrot, nullptr);
-  store_rows(sm, p.io.vel_o, env0, nenv, 3 * h.nb, h.r_vel, nullptr);
-  store_rows(sm, p.io.ang_o, env0, nenv, 3 * h.nb, h.r_ang, nullptr);
-  store_rows(sm, p.io.contact_vel, env0, nenv, 3 * h.nb, 0, ti + h.m_cv);
-  store_rows(sm, p.io.contact_ang, env0, nenv, 3 * h.nb, 0, ti + h.m_ca);
-  store_rows(sm, p.io.actuator_ang, env0, nenv, 3 * h.nb, 0, ti + h.m_aa);
-  store_const(p.io.actuator_vel, env0, nenv, 3 * h.nb, 0.f);
-  if constexpr (MODE == BX_MODE_LEGACY_SPRING) {
-    store_rows(sm, p.io.joint_vel, env0, nenv, 3 * h.nb, 0, ti + h.m_jv);
-    store_rows(sm, p.io.joint_ang, env0, nenv, 3 * h.nb, 0, ti + h.m_ja);
-  } else {
-    store_const(p.io.joint_vel, env0, nenv, 3 * h.nb, 0.f);
-    store_const(p.io.joint_ang, env0, nenv, 3 * h.nb, 0.f);
-  }
-  if (h.nk > 0) {
-    if (h.iters > 0) {
-      store_rows(sm, p.io.contact_pos, env0, nenv, 3 * h.nk, 0, ti + h.m_cp);
-      store_rows(sm, p.io.contact_normal, env0, nenv, 3 * h.nk, 0, ti + h.m_cn);
-      store_rows(sm, p.io.contact_penetration, env0, nenv, h.nk, 0, ti + h.m_pen);
-    } else {  // zero_info: penetration = -1 (system.py:84)
-      store_const(p.io.contact_pos, env0, nenv, 3 * h.nk, 0.f);
-      store_const(p.io.contact_normal, env0, nenv, 3 * h.nk, 0.f);
-      store_const(p.io.contact_penetration, env0, nenv, h.nk, -1.f);
-    }
-  }
+  // outputs: the pos/rot maps point at buffer 0; buffer `cur` holds the result
+  const int cur_shift = (MODE == BX_MODE_PBD && c.cur) ? 2 * QS * 4 : 0;
+  for (int s = 0; s < BX_SEG_OUT; s++)
+    io_segment<false>(smf + (s < 2 ? cur_shift : 0), ti, h.seg_out[s], p.out[s], env0, nenv);
 }

@@ -1,10 +1,11 @@
 // bx_tables.h -- flat device-side "program" of one system.
 //
-// bx_system_create() (bx_api.cu) flattens a bx_system_desc into one int32 and
-// one float32 array (uploaded once); the step kernel copies both into shared
-// memory at CTA start.  Every index in here is static per system, so inside the
-// kernel all table reads are warp-uniform (one warp = 32 environments working
-// on the same joint / body / contact row).
+// bx_system_create() (bx_api.cu) flattens a bx_system_desc into one float4
+// table and one int32 table (uploaded once); the step kernel copies both into
+// shared memory at CTA start.  Every index in here is static per system, so
+// inside the kernel all table reads are warp-uniform 128-bit shared-memory
+// broadcasts (one warp = 32 environments working on the same joint / body /
+// contact row).
 //
 // Reference anchors for what each record holds: joints.py:38-77,
 // spring_joints.py:42-87, actuators.py:31-46, forces.py:29-41,
@@ -14,42 +15,33 @@
 
 #include <stdint.h>
 
-// ---- float records (strides in floats) ------------------------------------
+// ---- float4 records (strides in quads = float4) --------------------------
 enum {
-  // body
-  BF_INV_MASS = 0,  // 1/mass (float32 division on the host, as jnp does)
-  BF_MASS = 1,
-  BF_INV_INERTIA = 2,  // [3]
-  BF_POS_MASK = 5,     // [3]
-  BF_ROT_MASK = 8,     // [3]
-  BF_STRIDE = 11,
+  // body: 4 quads
+  BQ_MASS = 0,         // {1/mass (float32 division on the host, as jnp does), mass, 0, 0}
+  BQ_INV_INERTIA = 1,  // {ix, iy, iz, 0}
+  BQ_POS_MASK = 2,     // {x, y, z, 0}
+  BQ_ROT_MASK = 3,     // {x, y, z, 0}
+  BQ_STRIDE = 4,
 
-  // joint
-  JF_OFF_P = 0,    // [3]
-  JF_OFF_C = 3,    // [3]
-  JF_AXIS_P = 6,   // [9] row-major
-  JF_AXIS_C = 15,  // [9]
-  JF_LIMIT = 24,   // [3][2]
-  JF_ANG_DAMP = 30,
-  JF_SCALE_POS = 31,
-  JF_SCALE_ANG = 32,
-  JF_STIFFNESS = 33,
-  JF_SPRING_DAMP = 34,
-  JF_LIMIT_STRENGTH = 35,
-  JF_STRIDE = 37,
+  // joint: 10 quads
+  JQ_OFF_P = 0,   // {off_p, angular_damping}
+  JQ_OFF_C = 1,   // {off_c, scale_pos}
+  JQ_AXIS_P = 2,  // rows 0..2: {axis_p[r], w}; w = scale_ang, stiffness, spring_damping
+  JQ_AXIS_C = 5,  // rows 0..2: {axis_c[r], w}; w = limit_strength, 0, 0
+  JQ_LIMIT = 8,   // {lo0, hi0, lo1, hi1}, {lo2, hi2, 0, 0}
+  JQ_STRIDE = 10,
 
-  // contact row (one per contact, pairs expanded)
-  CF_FRICTION = 0,
-  CF_ELASTICITY = 1,
-  CF_RADIUS_A = 2,
-  CF_RADIUS_B = 3,
-  CF_PTS = 4,  // capsule_plane / box_plane: [3]; capsule_capsule: [4][3]
-  CF_STRIDE = 17,
+  // actuator / force: 1 quad {strength, 0, 0, 0}
+  // contact row (one per contact, pairs expanded): 5 quads
+  CQ_MAT = 0,  // {friction, elasticity, radius_a, radius_b}
+  CQ_PTS = 1,  // capsule_plane / box_plane: pts[0]; capsule_capsule: pts[0..3]
+  CQ_STRIDE = 5,
 };
 
-// ---- int records (strides in ints) -----------------------------------------
+// ---- int records (strides in ints; every record is 16-byte aligned) --------
 enum {
-  // body
+  // body: 3 x int4
   BI_CSLOT = 0,     // slot in the collider-body regions (PRE, INFO_C) or -1
   BI_ASLOT = 1,     // slot in the actuated-body region (INFO_A) or -1
   BI_JADJ_OFF = 2,  // joint adjacency: entries (j << 1 | side), side 1 = child
@@ -60,33 +52,44 @@ enum {
   BI_FADJ_N = 7,
   BI_CADJ_OFF = 8,  // contact adjacency: (row << 4 | group << 1 | side)
   BI_CADJ_N = 9,
-  BI_STRIDE = 10,
+  BI_STRIDE = 12,
 
-  // joint
+  // joint: int4 {kind, body_p, body_c, 0}
   JI_KIND = 0,
   JI_BODY_P = 1,
   JI_BODY_C = 2,
-  JI_STRIDE = 3,
+  JI_STRIDE = 4,
 
-  // actuator
+  // actuator: 2 x int4 {kind, joint, idx0, idx1} {idx2, 0, 0, 0}
   AI_KIND = 0,
   AI_JOINT = 1,
   AI_IDX = 2,  // [3], -1 = masked
-  AI_STRIDE = 5,
+  AI_STRIDE = 8,
 
-  // force
+  // force: 2 x int4
   FI_KIND = 0,
   FI_BODY = 1,
   FI_IDX = 2,  // [3]
-  FI_STRIDE = 5,
+  FI_STRIDE = 8,
 
-  // contact row
+  // contact row: 2 x int4 {kind, two_way, body_a, body_b} {delta_quad, 0, 0, 0}
   CI_KIND = 0,
   CI_TWO_WAY = 1,
   CI_BODY_A = 2,
   CI_BODY_B = 3,
-  CI_DELTA_OFF = 4,  // row offset of this contact's delta slot in region JS
-  CI_STRIDE = 5,
+  CI_DELTA_OFF = 4,  // quad offset of this contact's delta slot in region JS
+  CI_STRIDE = 8,
+};
+
+// Global <-> shared I/O segment: global array g[B][nper]; element (e, r) lives at
+// shared float index map[r] + 4 * e (map[r] < 0: the element is a constant).
+#define BX_SEG_IN 5    // pos rot vel ang act
+#define BX_SEG_OUT 13  // pos rot vel ang + 6 Info P + contact pos/normal/pen
+struct BxSeg {
+  int32_t nper;   // floats per environment
+  int32_t map;    // offset of map[nper] in the int table
+  uint32_t magic; // ceil(2^32 / nper): e = umulhi(idx, magic) for idx < 2^20
+  float fill;     // value of elements with map[r] < 0
 };
 
 // Header: lives in the kernel parameter (constant bank), not in shared memory.
@@ -98,17 +101,15 @@ struct BxHeader {
   int32_t ncb;  // bodies that appear in a collider (slots for PRE/INFO_C)
   int32_t nab;  // bodies that appear in an actuated joint (slots for INFO_A)
   // table sizes / offsets
-  int32_t n_ints, n_floats;
+  int32_t n_ints, n_fquads;
   int32_t io_body, io_joint, io_act, io_force, io_contact, io_adj;  // int offs
-  int32_t fo_body, fo_joint, fo_act, fo_force, fo_contact;          // float offs
-  // state rows (row index; each row is 33 floats = 32 envs + 1 pad)
-  int32_t r_pos0, r_pos1, r_rot0, r_rot1, r_vel, r_ang;
-  int32_t r_act, r_js, r_ct, r_pre, r_ic, r_ia, r_ij;
-  int32_t n_rows;
-  // output maps (offsets into the int table; entry = state row or -1 for 0):
-  // contact_vel[3N] contact_ang[3N] actuator_ang[3N] joint_vel[3N] joint_ang[3N]
-  // contact_pos[3K] contact_normal[3K] contact_penetration[K]
-  int32_t m_cv, m_ca, m_aa, m_jv, m_ja, m_cp, m_cn, m_pen;
+  int32_t fo_body, fo_joint, fo_act, fo_force, fo_contact;          // quad offs
+  // state quad rows (each row = 32 env slots x float4, + 1 pad quad)
+  int32_t q_act, q_js, q_ct, q_pre, q_ic, q_ia, q_ij;
+  int32_t n_quads;
+  int32_t n_zero;  // quads from q_ic to zero at the start of every step
+  BxSeg seg_in[BX_SEG_IN];
+  BxSeg seg_out[BX_SEG_OUT];
   // scalars
   float dt, inv_dt, half_dt;
   float gravity[3];
@@ -117,7 +118,10 @@ struct BxHeader {
   float inv_2h;  // 1 / (2*dt_sub), colliders.py:399
 };
 
-#define BX_ROW_STRIDE 33  // 32 env slots + 1 pad word (bank-conflict-free I/O)
+#define BX_QSTRIDE 33  // quads per row: 32 env slots + 1 pad (conflict-free transposing I/O)
 #define BX_ENVS_PER_CTA 32
+// body block: pbd {pos0 rot0 pos1 rot1 vel ang}, legacy_spring {pos rot vel ang}
+#define BX_BODY_QUADS_PBD 6
+#define BX_BODY_QUADS_SPRING 4
 
 #endif  // BX_TABLES_H_
