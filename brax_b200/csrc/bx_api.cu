@@ -35,6 +35,10 @@ struct bx_system {
 
 static thread_local std::string g_err;
 static std::atomic<int64_t> g_launches{0};
+static long long* g_dbg = nullptr;  // BX_PHASE_TIMING builds: device buffer of 16 counters
+#ifdef BX_PHASE_TIMING
+extern "C" void bx_debug_set_buffer(long long* d) { g_dbg = d; }
+#endif
 
 static int fail(const std::string& m) {
   g_err = m;
@@ -189,16 +193,74 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   }
   h.n_fquads = nquads();
 
-  // ---- delta slots (quads) of the contact rows inside region JS
-  std::vector<int> delta_off(nk);
-  int js_contacts = 0;
-  for (int k = 0; k < nk; k++) {
-    delta_off[k] = js_contacts;
-    js_contacts += d->pairs[rows[k].pair].two_way ? 4 : 2;
+  // ---- per-body slot lists inside region JS (see bx_tables.h "Slots") ---------
+  // Lists of one barrier interval are packed from quad 0; different intervals
+  // reuse the region.  Order inside a list = the reference's summation order.
+  std::vector<int> a_base(nb, 0), a_n(nb, 0), d_base(nb, 0), d_n(nb, 0), j_base(nb, 0), j_n(nb, 0);
+  std::vector<int> act_slot_p(na), act_slot_c(na), dslot_p(nj), dslot_c(nj), jslot_p(nj), jslot_c(nj);
+  int t_quads = 0;  // interval T: actuator lists, then (pbd) damping lists
+  for (int b = 0; b < nb; b++) {
+    a_base[b] = t_quads;
+    // actuators.py:67-70: group by group, parents then children
+    for (int i0 = 0; i0 < na;) {
+      int i1 = i0;
+      while (i1 < na && d->actuators[i1].group == d->actuators[i0].group) i1++;
+      for (int i = i0; i < i1; i++)
+        if (d->joints[d->actuators[i].joint].body_p == b) act_slot_p[i] = t_quads++;
+      for (int i = i0; i < i1; i++)
+        if (d->joints[d->actuators[i].joint].body_c == b) act_slot_c[i] = t_quads++;
+      i0 = i1;
+    }
+    a_n[b] = t_quads - a_base[b];
   }
-  // pbd: torque slots (na + nj) and joint delta slots (4 nj) are never live together
-  int js = spring ? std::max(js_contacts, na + 4 * nj)
-                  : std::max(js_contacts, std::max(na + nj, 4 * nj));
+  if (!spring) {
+    for (int b = 0; b < nb; b++) {
+      d_base[b] = t_quads;
+      // joints.py:93-98 / :103-128: group by group, parents then children
+      for (int i0 = 0; i0 < nj;) {
+        int i1 = i0;
+        while (i1 < nj && d->joints[i1].group == d->joints[i0].group) i1++;
+        for (int i = i0; i < i1; i++) if (d->joints[i].body_p == b) dslot_p[i] = t_quads++;
+        for (int i = i0; i < i1; i++) if (d->joints[i].body_c == b) dslot_c[i] = t_quads++;
+        i0 = i1;
+      }
+      d_n[b] = t_quads - d_base[b];
+    }
+  }
+  // interval J (pbd: own interval from quad 0; spring: same interval as T, after it)
+  int j_quads = spring ? t_quads : 0;
+  for (int b = 0; b < nb; b++) {
+    j_base[b] = j_quads;
+    for (int i0 = 0; i0 < nj;) {
+      int i1 = i0;
+      while (i1 < nj && d->joints[i1].group == d->joints[i0].group) i1++;
+      for (int i = i0; i < i1; i++) if (d->joints[i].body_p == b) { jslot_p[i] = j_quads; j_quads += 2; }
+      for (int i = i0; i < i1; i++) if (d->joints[i].body_c == b) { jslot_c[i] = j_quads; j_quads += 2; }
+      i0 = i1;
+    }
+    j_n[b] = (j_quads - j_base[b]) / 2;
+  }
+  // contact intervals: per body, per collider group, a rows then b rows
+  // (colliders.py:222-228)
+  std::vector<int> cslot_a(nk, 0), cslot_b(nk, 0);
+  std::vector<std::vector<int>> cgroups(nb);  // (base, count) pairs
+  int c_quads = 0;
+  for (int b = 0; b < nb; b++) {
+    for (int k0 = 0; k0 < nk;) {
+      int g = d->pairs[rows[k0].pair].group, k1 = k0;
+      while (k1 < nk && d->pairs[rows[k1].pair].group == g) k1++;
+      const int base = c_quads;
+      for (int k = k0; k < k1; k++)
+        if (d->pairs[rows[k].pair].body_a == b) { cslot_a[k] = c_quads; c_quads += 2; }
+      for (int k = k0; k < k1; k++)
+        if (d->pairs[rows[k].pair].two_way && d->pairs[rows[k].pair].body_b == b) {
+          cslot_b[k] = c_quads; c_quads += 2;
+        }
+      if (c_quads > base) { cgroups[b].push_back(base); cgroups[b].push_back((c_quads - base) / 2); }
+      k0 = k1;
+    }
+  }
+  const int js = std::max(std::max(t_quads, j_quads), c_quads);
 
   // ---- state quad rows
   int r = nb * bqn;
@@ -219,49 +281,18 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
     int32_t* rec = &body_rec[b * BI_STRIDE];
     rec[BI_CSLOT] = cslot[b];
     rec[BI_ASLOT] = aslot[b];
-    // joints: group by group, parents then children (joints.py:93-98)
-    rec[BI_JADJ_OFF] = static_cast<int>(adj.size());
-    for (int i0 = 0; i0 < nj;) {
-      int i1 = i0;
-      while (i1 < nj && d->joints[i1].group == d->joints[i0].group) i1++;
-      for (int i = i0; i < i1; i++) if (d->joints[i].body_p == b) adj.push_back(i << 1);
-      for (int i = i0; i < i1; i++) if (d->joints[i].body_c == b) adj.push_back((i << 1) | 1);
-      i0 = i1;
-    }
-    rec[BI_JADJ_N] = static_cast<int>(adj.size()) - rec[BI_JADJ_OFF];
-    // actuators (actuators.py:67-70); bit0 = subtract
-    rec[BI_AADJ_OFF] = static_cast<int>(adj.size());
-    for (int i0 = 0; i0 < na;) {
-      int i1 = i0;
-      while (i1 < na && d->actuators[i1].group == d->actuators[i0].group) i1++;
-      for (int i = i0; i < i1; i++)
-        if (d->joints[d->actuators[i].joint].body_p == b)
-          adj.push_back((i << 2) | (d->actuators[i].kind == BX_ACT_ANGLE ? 1 : 0));
-      for (int i = i0; i < i1; i++)
-        if (d->joints[d->actuators[i].joint].body_c == b)
-          adj.push_back((i << 2) | (d->actuators[i].kind == BX_ACT_TORQUE ? 1 : 0));
-      i0 = i1;
-    }
-    rec[BI_AADJ_N] = static_cast<int>(adj.size()) - rec[BI_AADJ_OFF];
+    rec[BI_A_BASE] = a_base[b]; rec[BI_A_N] = a_n[b];
+    rec[BI_D_BASE] = d_base[b]; rec[BI_D_N] = d_n[b];
+    rec[BI_J_BASE] = j_base[b]; rec[BI_J_N] = j_n[b];
     // forces: thrusters, then twisters (forces.py:131-136)
-    rec[BI_FADJ_OFF] = static_cast<int>(adj.size());
+    rec[BI_F_OFF] = static_cast<int>(adj.size());
     for (int kind = 0; kind < 2; kind++)
       for (int i = 0; i < nf; i++)
         if (d->forces[i].kind == kind && d->forces[i].body == b) adj.push_back(i);
-    rec[BI_FADJ_N] = static_cast<int>(adj.size()) - rec[BI_FADJ_OFF];
-    // contact rows: group by group, a rows then b rows (colliders.py:222-228)
-    rec[BI_CADJ_OFF] = static_cast<int>(adj.size());
-    for (int k0 = 0; k0 < nk;) {
-      int g = d->pairs[rows[k0].pair].group, k1 = k0;
-      while (k1 < nk && d->pairs[rows[k1].pair].group == g) k1++;
-      for (int k = k0; k < k1; k++)
-        if (d->pairs[rows[k].pair].body_a == b) adj.push_back((k << 4) | (g << 1));
-      for (int k = k0; k < k1; k++)
-        if (d->pairs[rows[k].pair].two_way && d->pairs[rows[k].pair].body_b == b)
-          adj.push_back((k << 4) | (g << 1) | 1);
-      k0 = k1;
-    }
-    rec[BI_CADJ_N] = static_cast<int>(adj.size()) - rec[BI_CADJ_OFF];
+    rec[BI_F_N] = static_cast<int>(adj.size()) - rec[BI_F_OFF];
+    rec[BI_CG_OFF] = static_cast<int>(adj.size());
+    adj.insert(adj.end(), cgroups[b].begin(), cgroups[b].end());
+    rec[BI_CG_N] = static_cast<int>(cgroups[b].size() / 2);
   }
   h.io_body = static_cast<int>(ti.size());
   ti.insert(ti.end(), body_rec.begin(), body_rec.end());
@@ -272,13 +303,15 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
     ti.push_back(d->joints[i].body_p);
     ti.push_back(d->joints[i].body_c);
     ti.push_back(0);
+    ti.push_back(spring ? 0 : dslot_p[i]); ti.push_back(spring ? 0 : dslot_c[i]);
+    ti.push_back(jslot_p[i]); ti.push_back(jslot_c[i]);
   }
   h.io_act = static_cast<int>(ti.size());
   for (int i = 0; i < na; i++) {
     const bx_actuator& a = d->actuators[i];
     ti.push_back(a.kind); ti.push_back(a.joint);
     for (int k = 0; k < 3; k++) ti.push_back(a.act_index[k]);
-    for (int k = 0; k < 3; k++) ti.push_back(0);
+    ti.push_back(act_slot_p[i]); ti.push_back(act_slot_c[i]); ti.push_back(0);
   }
   h.io_force = static_cast<int>(ti.size());
   for (int i = 0; i < nf; i++) {
@@ -291,8 +324,8 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   for (int k = 0; k < nk; k++) {
     const bx_pair& p = d->pairs[rows[k].pair];
     ti.push_back(p.kind); ti.push_back(p.two_way); ti.push_back(p.body_a);
-    ti.push_back(p.body_b); ti.push_back(delta_off[k]);
-    for (int q = 0; q < 3; q++) ti.push_back(0);
+    ti.push_back(p.body_b); ti.push_back(cslot_a[k]); ti.push_back(cslot_b[k]);
+    ti.push_back(0); ti.push_back(0);
   }
   h.io_adj = static_cast<int>(ti.size());
   ti.insert(ti.end(), adj.begin(), adj.end());
@@ -302,6 +335,14 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   auto seg = [&](int nper, float fill, const std::vector<int>& map) {
     BxSeg sgm;
     sgm.nper = nper;
+    bool all_const = true;
+    for (int v : map) all_const = all_const && v < 0;
+    if (all_const) {  // constant segment: no map, the kernel does a plain fill
+      sgm.map = -1;
+      sgm.magic = 0;
+      sgm.fill = fill;
+      return sgm;
+    }
     sgm.map = static_cast<int>(ti.size());
     sgm.magic = nper > 1 ? static_cast<uint32_t>((0x100000000ULL + nper - 1) / nper) : 0u;
     sgm.fill = fill;
@@ -372,6 +413,30 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   h.inv_2h = 1.f / (2.f * d->dt_sub);
 }
 
+// One instantiation per (dynamics mode, launch bounds); the launch picks the
+// smallest bound that holds the configured CTA size.
+typedef void (*bx_kernel_fn)(const BxKernelParams);
+static bx_kernel_fn pick_kernel(int mode, int threads) {
+  if (mode == BX_MODE_PBD) {
+    if (threads <= 256) return bx_step_kernel<BX_MODE_PBD, 256, 2>;
+    if (threads <= 320) return bx_step_kernel<BX_MODE_PBD, 320, 2>;
+    if (threads <= 384) return bx_step_kernel<BX_MODE_PBD, 384, 2>;
+    return bx_step_kernel<BX_MODE_PBD, 512, 1>;
+  }
+  if (threads <= 256) return bx_step_kernel<BX_MODE_LEGACY_SPRING, 256, 2>;
+  if (threads <= 320) return bx_step_kernel<BX_MODE_LEGACY_SPRING, 320, 2>;
+  if (threads <= 384) return bx_step_kernel<BX_MODE_LEGACY_SPRING, 384, 2>;
+  return bx_step_kernel<BX_MODE_LEGACY_SPRING, 512, 1>;
+}
+static int set_smem_attr(int bytes) {
+  const int sizes[4] = {256, 320, 384, 512};
+  for (int mode = 0; mode < 2; mode++)
+    for (int i = 0; i < 4; i++)
+      CUDA_OK(cudaFuncSetAttribute(pick_kernel(mode, sizes[i]),
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  return 0;
+}
+
 extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_system** out) {
   if (!out) return fail("out is NULL");
   *out = nullptr;
@@ -400,22 +465,34 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
     delete s;
     return fail("system state does not fit in shared memory (too many bodies/joints/contacts)");
   }
-  // default warps per tile (measured on B200, profiles/): one warp per joint /
-  // per two contact rows; between 9 and 12 warps the 114-register kernel would
-  // drop to one CTA per SM without shortening any phase, so stay at 8 there.
-  int widest = std::max(std::max(s->h.nj, (s->h.nk + 1) / 2), std::max(s->h.na, 2));
-  s->warps = widest <= 8 ? widest : (widest <= 12 ? 8 : 16);
+  // default warps per tile: minimise the critical path of one half-substep,
+  // sum over phases of ceil(items / W) * (measured cycles of one item, in k-cycles,
+  // tools/phase_timing.py), times a penalty for the register budget that W implies
+  // (10 warps: 102 regs; 12: 85 regs; 16: one tile per SM).
+  {
+    bool spherical = false;
+    for (int i = 0; i < desc->num_joints; i++)
+      spherical = spherical || (desc->joints[i].kind != BX_JOINT_REVOLUTE &&
+                                desc->joints[i].kind != BX_JOINT_SPRING_REVOLUTE);
+    const double cj = spherical ? 6.7 : 2.3, ca = spherical ? 4.0 : 1.7, cb = 3.56, ck = 1.07;
+    const int cand[5] = {4, 8, 10, 12, 16};
+    const double pen[5] = {1.0, 1.0, 1.03, 1.3, 1.5};
+    double best = 1e30;
+    s->warps = 8;
+    auto rounds = [](int n, int w) { return (n + w - 1) / w; };
+    for (int i = 0; i < 5; i++) {
+      const int w = cand[i];
+      const double cost = pen[i] * (rounds(s->h.nj, w) * cj + rounds(s->h.na, w) * ca +
+                                    rounds(s->h.nb, w) * cb + rounds(s->h.nk, w) * ck);
+      if (cost < best - 1e-9) { best = cost; s->warps = w; }
+    }
+  }
   cudaError_t e1 = cudaMalloc(&s->d_tab_i, std::max<size_t>(ti.size(), 1) * 4);
   cudaError_t e2 = cudaMalloc(&s->d_tab_f, std::max<size_t>(tf.size(), 1) * 4);
   if (e1 != cudaSuccess || e2 != cudaSuccess) { delete s; return fail("cudaMalloc of tables failed"); }
   CUDA_OK(cudaMemcpy(s->d_tab_i, ti.data(), ti.size() * 4, cudaMemcpyHostToDevice));
   CUDA_OK(cudaMemcpy(s->d_tab_f, tf.data(), tf.size() * 4, cudaMemcpyHostToDevice));
-  CUDA_OK(cudaFuncSetAttribute(bx_step_kernel<BX_MODE_PBD>,
-                               cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               prop.sharedMemPerBlockOptin));
-  CUDA_OK(cudaFuncSetAttribute(bx_step_kernel<BX_MODE_LEGACY_SPRING>,
-                               cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               prop.sharedMemPerBlockOptin));
+  if (set_smem_attr(static_cast<int>(prop.sharedMemPerBlockOptin))) { delete s; return 1; }
   *out = s;
   return 0;
 }
@@ -462,12 +539,11 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   for (int i = 0; i < BX_SEG_OUT; i++) p.out[i] = outs[i];
   p.num_envs = num_envs;
   p.num_steps = num_steps;
+  p.dbg = g_dbg;
   const int64_t tiles = (num_envs + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA;
   if (tiles > 0x7fffffffLL) return fail("too many environments for one launch");
-  if (s->h.mode == BX_MODE_PBD)
-    bx_step_kernel<BX_MODE_PBD><<<static_cast<unsigned>(tiles), 32 * s->warps, s->smem_bytes, stream>>>(p);
-  else
-    bx_step_kernel<BX_MODE_LEGACY_SPRING><<<static_cast<unsigned>(tiles), 32 * s->warps, s->smem_bytes, stream>>>(p);
+  pick_kernel(s->h.mode, 32 * s->warps)<<<static_cast<unsigned>(tiles), 32 * s->warps,
+                                          s->smem_bytes, stream>>>(p);
   g_launches.fetch_add(1);
   CUDA_OK(cudaGetLastError());
   return 0;

@@ -35,7 +35,25 @@ struct BxKernelParams {
   float* out[BX_SEG_OUT];      // order of bx_step_io's outputs
   int64_t num_envs;
   int32_t num_steps;  // >1: rollout, act is [T,B,A]
+  long long* dbg;     // BX_PHASE_TIMING builds only: cycles per phase of CTA 0
 };
+
+// Phase timing (tools/phase_timing.py builds with -DBX_PHASE_TIMING): thread 0
+// of CTA 0 accumulates the cycles between consecutive barriers per phase id.
+#ifdef BX_PHASE_TIMING
+#define PT_INIT() long long pt_last = clock64()
+#define PT(i)                                                        \
+  do {                                                               \
+    if (p.dbg && blockIdx.x == 0 && threadIdx.x == 0) {              \
+      long long t_ = clock64();                                      \
+      p.dbg[i] += t_ - pt_last;                                      \
+      pt_last = t_;                                                  \
+    }                                                                \
+  } while (0)
+#else
+#define PT_INIT()
+#define PT(i)
+#endif
 
 #define QS BX_QSTRIDE
 
@@ -69,42 +87,117 @@ BXD int4 ldi4(const int32_t* p) { return *reinterpret_cast<const int4*>(p); }
 // ---- global <-> shared transposing I/O ---------------------------------------
 // g: [B, nper] row-major; this CTA owns envs [env0, env0+nenv).  Element (e, r)
 // lives at shared float index map[r] + 4*e (map[r] < 0: constant `fill`).
+BXD void seg_locate(const BxSeg& sg, int idx, int* e, int* r) {
+  *e = sg.magic ? static_cast<int>(__umulhi(static_cast<unsigned>(idx), sg.magic)) : idx;
+  *r = idx - *e * sg.nper;
+}
+
+// scalar fallback (ragged tiles / unaligned pointers)
 template <bool LOAD>
-__device__ __noinline__ void io_segment(float* smf, const int32_t* ti, BxSeg sg, float* g,
-                                        int64_t env0, int nenv) {
-  if (g == nullptr || sg.nper == 0) return;
-  const int nper = sg.nper;
-  float* base = g + env0 * nper;
+__device__ __noinline__ void io_segment_scalar(float* smf, const int32_t* ti, BxSeg sg, float* g,
+                                               int64_t env0, int nenv) {
+  float* base = g + env0 * sg.nper;
   const int32_t* map = ti + sg.map;
-  const int total = nenv * nper;
-  if ((total & 3) == 0 && ((reinterpret_cast<uintptr_t>(base) & 15) == 0)) {
-    float4* b4 = reinterpret_cast<float4*>(base);
-    for (int i = threadIdx.x; i < (total >> 2); i += blockDim.x) {
-      const int idx = i << 2;
-      int e = sg.magic ? static_cast<int>(__umulhi(static_cast<unsigned>(idx), sg.magic)) : idx;
-      int r = idx - e * nper;
-      float vv[4];
-      if (LOAD) {
-        float4 v = __ldg(b4 + i);
-        vv[0] = v.x; vv[1] = v.y; vv[2] = v.z; vv[3] = v.w;
+  const int total = nenv * sg.nper;
+  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    int e, r;
+    seg_locate(sg, idx, &e, &r);
+    const int m = sg.map >= 0 ? map[r] : -1;
+    if (LOAD) { if (m >= 0) smf[m + 4 * e] = __ldg(base + idx); }
+    else base[idx] = m >= 0 ? smf[m + 4 * e] : sg.fill;
+  }
+}
+
+BXD bool seg_vector_ok(const BxSeg& sg, const float* g, int64_t env0, int nenv) {
+  return ((nenv * sg.nper) & 3) == 0 &&
+         ((reinterpret_cast<uintptr_t>(g + env0 * sg.nper) & 15) == 0);
+}
+
+// Loads NSEG input segments: all global loads of a thread are issued before the
+// first shared-memory scatter, so the HBM round trips of the segments overlap.
+template <int NSEG>
+__device__ __noinline__ void load_segments(float* smf, const int32_t* ti, const BxSeg* segs,
+                                           const float* const* ptrs, int64_t env0, int nenv) {
+  bool vec = true;
+#pragma unroll
+  for (int s = 0; s < NSEG; s++) vec = vec && seg_vector_ok(segs[s], ptrs[s], env0, nenv);
+  if (!vec) {
+#pragma unroll
+    for (int s = 0; s < NSEG; s++)
+      if (segs[s].nper) io_segment_scalar<true>(smf, ti, segs[s], const_cast<float*>(ptrs[s]), env0, nenv);
+    return;
+  }
+  int cnt[NSEG], total = 0;
+#pragma unroll
+  for (int s = 0; s < NSEG; s++) { cnt[s] = (nenv * segs[s].nper) >> 2; total += cnt[s]; }
+  const int nt = blockDim.x;
+  for (int c0 = threadIdx.x; c0 < total; c0 += 4 * nt) {
+    float4 v[4];
+    int seg_of[4], loc[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      int c = c0 + u * nt, sidx = -1;
+      if (c < total) {
+#pragma unroll
+        for (int s = 0; s < NSEG; s++) {
+          if (sidx < 0) { if (c < cnt[s]) sidx = s; else c -= cnt[s]; }
+        }
+#pragma unroll
+        for (int s = 0; s < NSEG; s++)
+          if (sidx == s)
+            v[u] = __ldg(reinterpret_cast<const float4*>(ptrs[s] + env0 * segs[s].nper) + c);
       }
+      seg_of[u] = sidx; loc[u] = c;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      if (seg_of[u] < 0) continue;
+      BxSeg sg = segs[0];
+#pragma unroll
+      for (int s = 1; s < NSEG; s++) if (seg_of[u] == s) sg = segs[s];
+      const int32_t* map = ti + sg.map;
+      int e, r;
+      seg_locate(sg, loc[u] << 2, &e, &r);
+      const float vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
       for (int k = 0; k < 4; k++) {
         const int m = map[r];
-        if (LOAD) { if (m >= 0) smf[m + 4 * e] = vv[k]; }
-        else vv[k] = m >= 0 ? smf[m + 4 * e] : sg.fill;
-        if (++r == nper) { r = 0; e++; }
+        if (m >= 0) smf[m + 4 * e] = vv[k];
+        if (++r == sg.nper) { r = 0; e++; }
       }
-      if (!LOAD) b4[i] = make_float4(vv[0], vv[1], vv[2], vv[3]);
     }
-  } else {
-    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-      const int e = sg.magic ? static_cast<int>(__umulhi(static_cast<unsigned>(idx), sg.magic)) : idx;
-      const int r = idx - e * nper;
+  }
+}
+
+// Stores one output segment (128-bit coalesced stores; constant segments are a
+// plain fill).
+__device__ __noinline__ void store_segment(const float* smf, const int32_t* ti, BxSeg sg, float* g,
+                                           int64_t env0, int nenv) {
+  if (g == nullptr || sg.nper == 0) return;
+  if (!seg_vector_ok(sg, g, env0, nenv)) {
+    io_segment_scalar<false>(const_cast<float*>(smf), ti, sg, g, env0, nenv);
+    return;
+  }
+  float4* b4 = reinterpret_cast<float4*>(g + env0 * sg.nper);
+  const int n4 = (nenv * sg.nper) >> 2;
+  if (sg.map < 0) {  // constant output (e.g. info.joint in pbd)
+    const float4 f = make_float4(sg.fill, sg.fill, sg.fill, sg.fill);
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) b4[i] = f;
+    return;
+  }
+  const int32_t* map = ti + sg.map;
+#pragma unroll 2
+  for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+    int e, r;
+    seg_locate(sg, i << 2, &e, &r);
+    float vv[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
       const int m = map[r];
-      if (LOAD) { if (m >= 0) smf[m + 4 * e] = __ldg(base + idx); }
-      else base[idx] = m >= 0 ? smf[m + 4 * e] : sg.fill;
+      vv[k] = m >= 0 ? smf[m + 4 * e] : sg.fill;
+      if (++r == sg.nper) { r = 0; e++; }
     }
+    b4[i] = make_float4(vv[0], vv[1], vv[2], vv[3]);
   }
 }
 
@@ -158,8 +251,9 @@ BXD void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
   typedef Lay<MODE> L;
   const int ro = MODE == BX_MODE_PBD ? 2 * c.cur + 1 : 1;
   for (int a = c.warp; a < h.na; a += c.nwarp) {
-    const int4 ai = ldi4(c.ti + h.io_act + a * AI_STRIDE);  // kind, joint, idx0, idx1
-    const int idx2 = c.ti[h.io_act + a * AI_STRIDE + 4];
+    const int4 ai = ldi4(c.ti + h.io_act + a * AI_STRIDE);      // kind, joint, idx0, idx1
+    const int4 ai2 = ldi4(c.ti + h.io_act + a * AI_STRIDE + 4);  // idx2, slot_p, slot_c
+    const int idx2 = ai2.x;
     const int j = ai.y;
     const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
     const float4* jq = c.tf + h.fo_joint + j * JQ_STRIDE;
@@ -195,16 +289,24 @@ BXD void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
         tq = tq + axis[d] * t;
       }
     }
-    stv(c, h.q_js + a, tq);
+    // signed I^-1 tau straight into the two bodies' actuator lists.  Torque:
+    // parent +, child -; Angle: parent -, child + (actuators.py:88-89,109-110)
+    V3 tp = f3(c.tf[h.fo_body + ji.y * BQ_STRIDE + BQ_INV_INERTIA]) * tq;
+    V3 tc = f3(c.tf[h.fo_body + ji.z * BQ_STRIDE + BQ_INV_INERTIA]) * tq;
+    const bool angle_act = ai.x == BX_ACT_ANGLE;
+    stv(c, h.q_js + ai2.y, angle_act ? -tp : tp);
+    stv(c, h.q_js + ai2.z, angle_act ? tc : -tc);
   }
   if (damp) {
     for (int j = c.warp; j < h.nj; j += c.nwarp) {
       const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
+      const int4 js = ldi4(c.ti + h.io_joint + j * JI_STRIDE + 4);  // dslot_p dslot_c jslot_p jslot_c
       const float damping = c.tf[h.fo_joint + j * JQ_STRIDE + JQ_OFF_P].w;
       V3 ap = ldv(c, L::BQ * ji.y + L::ANG);
       V3 ac = ldv(c, L::BQ * ji.z + L::ANG);
       V3 tq = (-1.f * damping) * (ap - ac);
-      stv(c, h.q_js + h.na + j, tq);
+      stv(c, h.q_js + js.x, f3(c.tf[h.fo_body + ji.y * BQ_STRIDE + BQ_INV_INERTIA]) * tq);
+      stv(c, h.q_js + js.y, -(f3(c.tf[h.fo_body + ji.z * BQ_STRIDE + BQ_INV_INERTIA]) * tq));
     }
   }
 }
@@ -213,31 +315,20 @@ BXD void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
 // damping (dp_j) and forces (dp_f); system.py:268-271.
 BXD void body_accels(const Ctx& c, const BxHeader& h, const int32_t* bi, const float4* bq,
                      bool damp, V3* dpa_ang, V3* dpj_ang, V3* dpf_vel, V3* dpf_ang) {
-  V3 inv_i = f3(bq[BQ_INV_INERTIA]);
   V3 dpa = v3(0.f, 0.f, 0.f), dpj = v3(0.f, 0.f, 0.f);
   {
-    const int32_t* adj = c.ti + h.io_adj + bi[BI_AADJ_OFF];
-    const int n = bi[BI_AADJ_N];
-    for (int i = 0; i < n; i++) {
-      int e = adj[i];
-      V3 t = inv_i * ldv(c, h.q_js + (e >> 2));
-      // Torque: parent +, child -; Angle: parent -, child + (actuators.py:88-89,109-110)
-      dpa = (e & 1) ? dpa - t : dpa + t;
-    }
+    const int4 b0 = ldi4(bi);  // cslot aslot a_base a_n
+    const int r = h.q_js + b0.z;
+    for (int i = 0; i < b0.w; i++) dpa = dpa + ldv(c, r + i);
   }
   if (damp) {
-    const int32_t* adj = c.ti + h.io_adj + bi[BI_JADJ_OFF];
-    const int n = bi[BI_JADJ_N];
-    for (int i = 0; i < n; i++) {
-      int e = adj[i];
-      V3 t = inv_i * ldv(c, h.q_js + h.na + (e >> 1));
-      dpj = (e & 1) ? dpj - t : dpj + t;
-    }
+    const int r = h.q_js + bi[BI_D_BASE], n = bi[BI_D_N];
+    for (int i = 0; i < n; i++) dpj = dpj + ldv(c, r + i);
   }
   V3 fv = v3(0.f, 0.f, 0.f), fa = v3(0.f, 0.f, 0.f);
   {
-    const int32_t* adj = c.ti + h.io_adj + bi[BI_FADJ_OFF];
-    const int n = bi[BI_FADJ_N];
+    const int32_t* adj = c.ti + h.io_adj + bi[BI_F_OFF];
+    const int n = bi[BI_F_N];
     for (int i = 0; i < n; i++) {
       int f = adj[i];
       const int32_t* fi = c.ti + h.io_force + f * FI_STRIDE;
@@ -416,9 +507,9 @@ BXD void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
       dp.rot = dp.rot + ((p1 + p2) + p3);
       dc.rot = dc.rot + ((c1 + c2) + c3);
     }
-    const int r = h.q_js + 4 * j;
-    stv(c, r, dp.pos); stq(c, r + 1, dp.rot);
-    stv(c, r + 2, dc.pos); stq(c, r + 3, dc.rot);
+    const int4 js = ldi4(c.ti + h.io_joint + j * JI_STRIDE + 4);  // dslot_p dslot_c jslot_p jslot_c
+    stv(c, h.q_js + js.z, dp.pos); stq(c, h.q_js + js.z + 1, dp.rot);
+    stv(c, h.q_js + js.w, dc.pos); stq(c, h.q_js + js.w + 1, dc.rot);
   }
 }
 
@@ -432,14 +523,10 @@ BXD void phase_body_joint_update(const Ctx& c, const BxHeader& h, bool project) 
     const int r0 = L::BQ * b, rc_ = r0 + 2 * c.cur, rp_ = r0 + 2 * (c.cur ^ 1);
     V3 dpos = v3(0.f, 0.f, 0.f);
     Q4 drot = q4(0.f, 0.f, 0.f, 0.f);
-    const int4 b0 = ldi4(bi);  // cslot aslot jadj_off jadj_n
-    const int32_t* adj = c.ti + h.io_adj + b0.z;
-    const int n = b0.w;
-    for (int i = 0; i < n; i++) {
-      int e = adj[i];
-      int r = h.q_js + 4 * (e >> 1) + 2 * (e & 1);
-      dpos = dpos + ldv(c, r);
-      drot = drot + ldq(c, r + 1);
+    const int jr = h.q_js + bi[BI_J_BASE], jn = bi[BI_J_N];
+    for (int i = 0; i < jn; i++) {
+      dpos = dpos + ldv(c, jr + 2 * i);
+      drot = drot + ldq(c, jr + 2 * i + 1);
     }
     V3 pm = f3(bq[BQ_POS_MASK]), rm = f3(bq[BQ_ROT_MASK]);
     V3 pos = ldv(c, rc_) + dpos * pm;
@@ -544,7 +631,8 @@ BXD void phase_contacts_position(const Ctx& c, const BxHeader& h) {
   const int co = 2 * c.cur, po = 2 * (c.cur ^ 1);
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
     const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);  // kind two_way a b
-    const int rd = h.q_js + c.ti[h.io_contact + k * CI_STRIDE + CI_DELTA_OFF];
+    const int4 cs4 = ldi4(c.ti + h.io_contact + k * CI_STRIDE + 4);  // slot_a slot_b
+    const int rd = h.q_js + cs4.x, rdb = h.q_js + cs4.y;
     const float4* cq = c.tf + h.fo_contact + k * CQ_STRIDE;
     const int a = ci.z, b = ci.w;
     const bool two_way = ci.y != 0;
@@ -620,7 +708,7 @@ BXD void phase_contacts_position(const Ctx& c, const BxHeader& h) {
       dra = dra + cs * (.5f * vec_quat_mul(iia * cross(xa, pt), ra));
       drb = drb + cs * (.5f * vec_quat_mul(iib * cross(xb, -pt), rb));
       stv(c, rd, dpa); stq(c, rd + 1, dra);
-      stv(c, rd + 2, dpb); stq(c, rd + 3, drb);
+      stv(c, rdb, dpb); stq(c, rdb + 1, drb);
       dl_out = dl;  // un-masked (colliders.py:580)
     }
     const int rc_ = h.q_ct + 2 * k;
@@ -634,19 +722,16 @@ BXD void phase_contacts_position(const Ctx& c, const BxHeader& h) {
 // non-zero linear part, divide by (eps + count), then sum over groups.
 // Each side of a row holds two quads: linear part (xyz) and a second part
 // (rot wxyz for Q deltas; ang xyz + 0 for P deltas).
-BXD void gather_contact_deltas(const Ctx& c, const BxHeader& h, int cadj_off, int n, float eps,
+BXD void gather_contact_deltas(const Ctx& c, const BxHeader& h, int cg_off, int cg_n, float eps,
                                float4* lin_out, float4* sec_out) {
   float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), so = lo;
-  const int32_t* adj = c.ti + h.io_adj + cadj_off;
-  int i = 0;
-  while (i < n) {
-    const int g = (adj[i] >> 1) & 7;
+  const int32_t* cg = c.ti + h.io_adj + cg_off;
+  for (int g = 0; g < cg_n; g++) {
+    const int base = h.q_js + cg[2 * g], n = cg[2 * g + 1];
     float4 ls = make_float4(0.f, 0.f, 0.f, 0.f), ss = ls;
     float cnt = 0.f;
-    for (; i < n && ((adj[i] >> 1) & 7) == g; i++) {
-      const int e = adj[i];
-      const int r = h.q_js + c.ti[h.io_contact + (e >> 4) * CI_STRIDE + CI_DELTA_OFF] + 2 * (e & 1);
-      const float4 l = QROW(c, r), s = QROW(c, r + 1);
+    for (int i = 0; i < n; i++) {
+      const float4 l = QROW(c, base + 2 * i), s = QROW(c, base + 2 * i + 1);
       cnt += (l.x != 0.f || l.y != 0.f || l.z != 0.f) ? 1.f : 0.f;
       ls.x += l.x; ls.y += l.y; ls.z += l.z;
       ss.x += s.x; ss.y += s.y; ss.z += s.z; ss.w += s.w;
@@ -667,7 +752,7 @@ BXD void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
     const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
     const int r0 = L::BQ * b, rc_ = r0 + 2 * c.cur, rp_ = r0 + 2 * (c.cur ^ 1);
-    const int cslot = bi[BI_CSLOT], cadj_off = bi[BI_CADJ_OFF], cadj_n = bi[BI_CADJ_N];
+    const int cslot = bi[BI_CSLOT], cadj_off = bi[BI_CG_OFF], cadj_n = bi[BI_CG_N];
     V3 pm = f3(bq[BQ_POS_MASK]), rm = f3(bq[BQ_ROT_MASK]);
     V3 pos = ldv(c, rc_);
     Q4 rot = ldq(c, rc_ + 1);
@@ -699,7 +784,8 @@ BXD void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
   const int co = 2 * c.cur;
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
     const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);
-    const int rd = h.q_js + c.ti[h.io_contact + k * CI_STRIDE + CI_DELTA_OFF];
+    const int4 cs4 = ldi4(c.ti + h.io_contact + k * CI_STRIDE + 4);  // slot_a slot_b
+    const int rd = h.q_js + cs4.x, rdb = h.q_js + cs4.y;
     const float4 mat = c.tf[h.fo_contact + k * CQ_STRIDE + CQ_MAT];
     const int a = ci.z, b = ci.w;
     const bool two_way = ci.y != 0;
@@ -770,8 +856,8 @@ BXD void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
       V3 p = (((dlr * n2) * sink) + p_dyn) * stat;
       stv(c, rd, vdiv(p, ma));
       stv(c, rd + 1, cross(iia * ra, p));
-      stv(c, rd + 2, vdiv(-p, mb));
-      stv(c, rd + 3, cross(iib * rb, -p));
+      stv(c, rdb, vdiv(-p, mb));
+      stv(c, rdb + 1, cross(iib * rb, -p));
     }
   }
 }
@@ -783,12 +869,12 @@ BXD void phase_body_velocity_update(const Ctx& c, const BxHeader& h, float eps) 
   typedef Lay<MODE> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
-    const int cadj_n = bi[BI_CADJ_N];
+    const int cadj_n = bi[BI_CG_N];
     if (cadj_n == 0) continue;
     const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
     const int r0 = L::BQ * b;
     float4 dl, ds;
-    gather_contact_deltas(c, h, bi[BI_CADJ_OFF], cadj_n, eps, &dl, &ds);
+    gather_contact_deltas(c, h, bi[BI_CG_OFF], cadj_n, eps, &dl, &ds);
     V3 dv = f3(dl), da = f3(ds);
     stv(c, r0 + L::VEL, (ldv(c, r0 + L::VEL) + dv) * f3(bq[BQ_POS_MASK]));
     stv(c, r0 + L::ANG, (ldv(c, r0 + L::ANG) + da) * f3(bq[BQ_ROT_MASK]));
@@ -878,8 +964,9 @@ BXD void phase_joints_spring(const Ctx& c, const BxHeader& h) {
     tq = tq - ang_damp * (ang_p - ang_c);
     dap = dap + ii_p * tq;
     dac = dac + (-ii_c) * tq;
-    const int r = h.q_js + h.na + 4 * j;
-    stv(c, r, dvp); stv(c, r + 1, dap); stv(c, r + 2, dvc); stv(c, r + 3, dac);
+    const int4 js = ldi4(c.ti + h.io_joint + j * JI_STRIDE + 4);  // - - jslot_p jslot_c
+    stv(c, h.q_js + js.z, dvp); stv(c, h.q_js + js.z + 1, dap);
+    stv(c, h.q_js + js.w, dvc); stv(c, h.q_js + js.w + 1, dac);
   }
 }
 
@@ -894,13 +981,10 @@ BXD void phase_body_acc_spring(const Ctx& c, const BxHeader& h) {
     V3 dpa, unused, fv, fa;
     body_accels(c, h, bi, bq, false, &dpa, &unused, &fv, &fa);
     V3 jv = v3(0.f, 0.f, 0.f), ja = v3(0.f, 0.f, 0.f);
-    const int32_t* adj = c.ti + h.io_adj + bi[BI_JADJ_OFF];
-    const int n = bi[BI_JADJ_N];
-    for (int i = 0; i < n; i++) {
-      int e = adj[i];
-      int r = h.q_js + h.na + 4 * (e >> 1) + 2 * (e & 1);
-      jv = jv + ldv(c, r);
-      ja = ja + ldv(c, r + 1);
+    const int jr = h.q_js + bi[BI_J_BASE], jn = bi[BI_J_N];
+    for (int i = 0; i < jn; i++) {
+      jv = jv + ldv(c, jr + 2 * i);
+      ja = ja + ldv(c, jr + 2 * i + 1);
     }
     V3 g = v3(h.gravity[0], h.gravity[1], h.gravity[2]);
     V3 acc_v = jv + fv, acc_a = (ja + dpa) + fa;
@@ -924,7 +1008,8 @@ BXD void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_LEGACY_SPRING> L;
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
     const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);
-    const int rd = h.q_js + c.ti[h.io_contact + k * CI_STRIDE + CI_DELTA_OFF];
+    const int4 cs4 = ldi4(c.ti + h.io_contact + k * CI_STRIDE + 4);  // slot_a slot_b
+    const int rd = h.q_js + cs4.x, rdb = h.q_js + cs4.y;
     const float4* cq = c.tf + h.fo_contact + k * CQ_STRIDE;
     const int a = ci.z, b = ci.w;
     const bool two_way = ci.y != 0;
@@ -966,8 +1051,8 @@ BXD void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
     if (two_way) {
       body_impulse(mass_b, iib, pb, (-imp) * n, ct.pos, &dvn, &dan);
       body_impulse(mass_b, iib, pb, impd * dir, ct.pos, &dvd, &dad);
-      stv(c, rd + 2, dvn * apn + dvd * apd);
-      stv(c, rd + 3, dan * apn + dad * apd);
+      stv(c, rdb, dvn * apn + dvd * apd);
+      stv(c, rdb + 1, dan * apn + dad * apd);
     }
     const int rc_ = h.q_ct + 2 * k;
     stv4(c, rc_, ct.pos, ct.pen);
@@ -978,9 +1063,11 @@ BXD void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
 // ============================== the kernel ====================================
 extern __shared__ __align__(16) float4 bx_smem[];
 
-// blockDim.x = 32 * W (W warps share one tile of 32 environments).
-template <int MODE>
-__global__ void __launch_bounds__(512, 1)
+// blockDim.x = 32 * W (W warps share one tile of 32 environments).  MAXT / MINB
+// are the launch bounds: the register budget is what keeps two tiles per SM
+// resident (256 threads: 128 regs, 320: 102, 384: 85).
+template <int MODE, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB)
 bx_step_kernel(const __grid_constant__ BxKernelParams p) {
   typedef Lay<MODE> L;
   const BxHeader& h = p.h;
@@ -991,6 +1078,7 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
   const int64_t env0 = static_cast<int64_t>(blockIdx.x) * BX_ENVS_PER_CTA;
   const int nenv = static_cast<int>((p.num_envs - env0) < BX_ENVS_PER_CTA ? (p.num_envs - env0) : BX_ENVS_PER_CTA);
 
+  PT_INIT();
   for (int i = threadIdx.x; i < h.n_fquads; i += blockDim.x) tf[i] = __ldg(p.tab_f + i);
   for (int i = threadIdx.x; i < h.n_ints; i += blockDim.x) ti[i] = __ldg(p.tab_i + i);
   if (nenv < BX_ENVS_PER_CTA) {
@@ -1006,8 +1094,8 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
     }
   }
   __syncthreads();
-  for (int s = 0; s < 4; s++)
-    io_segment<true>(smf, ti, h.seg_in[s], const_cast<float*>(p.in[s]), env0, nenv);
+  PT(0);
+  load_segments<4>(smf, ti, h.seg_in, p.in, env0, nenv);
 
   Ctx c;
   c.warp = threadIdx.x >> 5;
@@ -1019,9 +1107,10 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
 
   for (int step = 0; step < p.num_steps; step++) {
     __syncthreads();
-    io_segment<true>(smf, ti, h.seg_in[4],
-                     const_cast<float*>(p.in[4]) + static_cast<int64_t>(step) * p.num_envs * h.act_size,
-                     env0, nenv);
+    {
+      const float* act = p.in[4] + static_cast<int64_t>(step) * p.num_envs * h.act_size;
+      load_segments<1>(smf, ti, h.seg_in + 4, &act, env0, nenv);
+    }
     // zero_info (system.py:76-84): Info accumulators start at 0 every step
     {
       const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1034,28 +1123,29 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
         }
     }
     __syncthreads();
+    PT(1);
     if constexpr (MODE == BX_MODE_PBD) {
       for (int it = 0; it < h.iters; it++) {
 #pragma unroll 1
         for (int half = 0; half < 2; half++) {
           phase_torques<MODE>(c, h, true);
-          __syncthreads();
+          __syncthreads(); PT(2);
           phase_body_acc_kinetic(c, h, half == 1);
           c.cur ^= 1;
-          __syncthreads();
+          __syncthreads(); PT(3);
           phase_joints_pbd(c, h);
-          __syncthreads();
+          __syncthreads(); PT(4);
           phase_body_joint_update(c, h, half == 0);
-          __syncthreads();
+          __syncthreads(); PT(5);
           if (half == 1) {
             phase_contacts_position(c, h);
-            __syncthreads();
+            __syncthreads(); PT(6);
             phase_body_contact_update(c, h);
-            __syncthreads();
+            __syncthreads(); PT(7);
             phase_contacts_velocity(c, h);
-            __syncthreads();
+            __syncthreads(); PT(8);
             phase_body_velocity_update<MODE>(c, h, 1e-6f);
-            __syncthreads();
+            __syncthreads(); PT(9);
           }
         }
       }
@@ -1077,8 +1167,10 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
   }
   __syncthreads();
 
+  PT(10);
   // outputs: the pos/rot maps point at buffer 0; buffer `cur` holds the result
   const int cur_shift = (MODE == BX_MODE_PBD && c.cur) ? 2 * QS * 4 : 0;
   for (int s = 0; s < BX_SEG_OUT; s++)
-    io_segment<false>(smf + (s < 2 ? cur_shift : 0), ti, h.seg_out[s], p.out[s], env0, nenv);
+    store_segment(smf + (s < 2 ? cur_shift : 0), ti, h.seg_out[s], p.out[s], env0, nenv);
+  PT(11);
 }

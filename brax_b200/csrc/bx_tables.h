@@ -40,30 +40,43 @@ enum {
 };
 
 // ---- int records (strides in ints; every record is 16-byte aligned) --------
+// "Slots" are quad rows relative to region JS.  Every producer (actuator, joint,
+// contact row) writes its per-body contribution straight into the consuming
+// body's slot LIST; the lists are contiguous and laid out in the reference's
+// summation order (joints.py:93-98, actuators.py:67-70, colliders.py:222-228),
+// so a body sums its list with independent, address-known loads.
 enum {
   // body: 3 x int4
-  BI_CSLOT = 0,     // slot in the collider-body regions (PRE, INFO_C) or -1
-  BI_ASLOT = 1,     // slot in the actuated-body region (INFO_A) or -1
-  BI_JADJ_OFF = 2,  // joint adjacency: entries (j << 1 | side), side 1 = child
-  BI_JADJ_N = 3,
-  BI_AADJ_OFF = 4,  // actuator adjacency: (a << 2 | negate << 1 | side)
-  BI_AADJ_N = 5,
-  BI_FADJ_OFF = 6,  // force adjacency: force index
-  BI_FADJ_N = 7,
-  BI_CADJ_OFF = 8,  // contact adjacency: (row << 4 | group << 1 | side)
-  BI_CADJ_N = 9,
+  BI_CSLOT = 0,   // slot in the collider-body regions (PRE, INFO_C) or -1
+  BI_ASLOT = 1,   // slot in the actuated-body region (INFO_A) or -1
+  BI_A_BASE = 2,  // actuator list: a_n quads (signed I^-1 tau)
+  BI_A_N = 3,
+  BI_D_BASE = 4,  // joint-damping list: d_n quads (pbd)
+  BI_D_N = 5,
+  BI_J_BASE = 6,  // joint list: j_n entries of 2 quads (pbd: dpos, drot; spring: dvel, dang)
+  BI_J_N = 7,
+  BI_F_OFF = 8,   // force adjacency (offset into the adj table), force indices
+  BI_F_N = 9,
+  BI_CG_OFF = 10,  // contact groups of this body: cg_n pairs (base, count) in the adj
+  BI_CG_N = 11,    // table; each entry = 2 quads (linear part, second part)
   BI_STRIDE = 12,
 
-  // joint: int4 {kind, body_p, body_c, 0}
+  // joint: 2 x int4 {kind, body_p, body_c, 0} {dslot_p, dslot_c, jslot_p, jslot_c}
   JI_KIND = 0,
   JI_BODY_P = 1,
   JI_BODY_C = 2,
-  JI_STRIDE = 4,
+  JI_DSLOT_P = 4,
+  JI_DSLOT_C = 5,
+  JI_JSLOT_P = 6,
+  JI_JSLOT_C = 7,
+  JI_STRIDE = 8,
 
-  // actuator: 2 x int4 {kind, joint, idx0, idx1} {idx2, 0, 0, 0}
+  // actuator: 2 x int4 {kind, joint, idx0, idx1} {idx2, slot_p, slot_c, 0}
   AI_KIND = 0,
   AI_JOINT = 1,
   AI_IDX = 2,  // [3], -1 = masked
+  AI_SLOT_P = 5,
+  AI_SLOT_C = 6,
   AI_STRIDE = 8,
 
   // force: 2 x int4
@@ -72,12 +85,13 @@ enum {
   FI_IDX = 2,  // [3]
   FI_STRIDE = 8,
 
-  // contact row: 2 x int4 {kind, two_way, body_a, body_b} {delta_quad, 0, 0, 0}
+  // contact row: 2 x int4 {kind, two_way, body_a, body_b} {slot_a, slot_b, 0, 0}
   CI_KIND = 0,
   CI_TWO_WAY = 1,
   CI_BODY_A = 2,
   CI_BODY_B = 3,
-  CI_DELTA_OFF = 4,  // quad offset of this contact's delta slot in region JS
+  CI_SLOT_A = 4,
+  CI_SLOT_B = 5,
   CI_STRIDE = 8,
 };
 
