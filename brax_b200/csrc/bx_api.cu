@@ -260,7 +260,17 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
       k0 = k1;
     }
   }
-  const int js = std::max(std::max(t_quads, j_quads), c_quads);
+  int js = std::max(std::max(t_quads, j_quads), c_quads);
+  {
+    // region JS doubles as the staging buffer of the bulk-copy I/O: it must hold
+    // the largest output span of a tile, and JS..end must hold all input spans.
+    const int row_floats = BX_QSTRIDE * 4;
+    const int max_out = 32 * std::max(4 * nb, 3 * nk);
+    js = std::max(js, (max_out + row_floats - 1) / row_floats);
+    const int in_floats = 32 * (13 * nb + d->act_size);
+    const int tail = 2 * nk + (spring ? 0 : 2 * ncb) + 2 * ncb + nab + (spring ? 2 * nb : 0);
+    js = std::max(js, (in_floats + row_floats - 1) / row_floats - tail);
+  }
 
   // ---- state quad rows
   int r = nb * bqn;
@@ -460,7 +470,7 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   s->d_scratch = nullptr;
   s->scratch_floats = 0;
   s->smem_bytes = (static_cast<size_t>(s->h.n_quads) * BX_QSTRIDE + s->h.n_fquads) * 16 +
-                  static_cast<size_t>(s->h.n_ints) * 4;
+                  static_cast<size_t>(s->h.n_ints) * 4 + 16 /* mbarrier */;
   if (s->smem_bytes > static_cast<size_t>(prop.sharedMemPerBlockOptin)) {
     delete s;
     return fail("system state does not fit in shared memory (too many bodies/joints/contacts)");
@@ -476,7 +486,7 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
                                 desc->joints[i].kind != BX_JOINT_SPRING_REVOLUTE);
     const double cj = spherical ? 6.7 : 2.3, ca = spherical ? 4.0 : 1.7, cb = 3.56, ck = 1.07;
     const int cand[5] = {4, 8, 10, 12, 16};
-    const double pen[5] = {1.0, 1.0, 1.03, 1.3, 1.5};
+    const double pen[5] = {1.0, 1.0, 1.03, 2.0, 1.5};
     double best = 1e30;
     s->warps = 8;
     auto rounds = [](int n, int w) { return (n + w - 1) / w; };

@@ -108,86 +108,82 @@ __device__ __noinline__ void io_segment_scalar(float* smf, const int32_t* ti, Bx
   }
 }
 
-BXD bool seg_vector_ok(const BxSeg& sg, const float* g, int64_t env0, int nenv) {
-  return ((nenv * sg.nper) & 3) == 0 &&
-         ((reinterpret_cast<uintptr_t>(g + env0 * sg.nper) & 15) == 0);
+// ---- bulk asynchronous copies (TMA engine, no tensor map needed: every span of
+// a 32-env tile is contiguous in HBM) ------------------------------------------
+BXD uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+BXD void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+BXD void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+BXD void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "BX_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra BX_DONE;\n\t"
+      "bra BX_WAIT;\n\t"
+      "BX_DONE:\n\t}" ::"r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+}
+BXD void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+BXD void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
+               "r"(smem_u32(smem_src)), "r"(bytes)
+               : "memory");
+}
+BXD void bulk_commit_wait_read() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+BXD void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+BXD bool span_bulk_ok(const BxSeg& sg, const float* g, int64_t env0) {
+  return (reinterpret_cast<uintptr_t>(g + env0 * sg.nper) & 15) == 0;
 }
 
-// Loads NSEG input segments: all global loads of a thread are issued before the
-// first shared-memory scatter, so the HBM round trips of the segments overlap.
-template <int NSEG>
-__device__ __noinline__ void load_segments(float* smf, const int32_t* ti, const BxSeg* segs,
-                                           const float* const* ptrs, int64_t env0, int nenv) {
-  bool vec = true;
+// One WARP moves one whole segment of a full tile, four consecutive elements per
+// lane and iteration (128-bit on the global / staging side).  All warps run this
+// same small loop on different segments at once.
+// staging (global layout [env][nper]) -> state quads
+BXD void unstage_warp(float* smf, const int32_t* ti, const BxSeg& sg, const float* stage, int lane) {
+  const int32_t* map = ti + sg.map;
+  const int n4 = BX_ENVS_PER_CTA / 4 * sg.nper;
+  const float4* st4 = reinterpret_cast<const float4*>(stage);
+#pragma unroll 1
+  for (int i = lane; i < n4; i += 32) {
+    int e, r;
+    seg_locate(sg, i << 2, &e, &r);
+    const float4 v = st4[i];
+    const float vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-  for (int s = 0; s < NSEG; s++) vec = vec && seg_vector_ok(segs[s], ptrs[s], env0, nenv);
-  if (!vec) {
-#pragma unroll
-    for (int s = 0; s < NSEG; s++)
-      if (segs[s].nper) io_segment_scalar<true>(smf, ti, segs[s], const_cast<float*>(ptrs[s]), env0, nenv);
-    return;
-  }
-  int cnt[NSEG], total = 0;
-#pragma unroll
-  for (int s = 0; s < NSEG; s++) { cnt[s] = (nenv * segs[s].nper) >> 2; total += cnt[s]; }
-  const int nt = blockDim.x;
-  for (int c0 = threadIdx.x; c0 < total; c0 += 4 * nt) {
-    float4 v[4];
-    int seg_of[4], loc[4];
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-      int c = c0 + u * nt, sidx = -1;
-      if (c < total) {
-#pragma unroll
-        for (int s = 0; s < NSEG; s++) {
-          if (sidx < 0) { if (c < cnt[s]) sidx = s; else c -= cnt[s]; }
-        }
-#pragma unroll
-        for (int s = 0; s < NSEG; s++)
-          if (sidx == s)
-            v[u] = __ldg(reinterpret_cast<const float4*>(ptrs[s] + env0 * segs[s].nper) + c);
-      }
-      seg_of[u] = sidx; loc[u] = c;
-    }
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-      if (seg_of[u] < 0) continue;
-      BxSeg sg = segs[0];
-#pragma unroll
-      for (int s = 1; s < NSEG; s++) if (seg_of[u] == s) sg = segs[s];
-      const int32_t* map = ti + sg.map;
-      int e, r;
-      seg_locate(sg, loc[u] << 2, &e, &r);
-      const float vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-#pragma unroll
-      for (int k = 0; k < 4; k++) {
-        const int m = map[r];
-        if (m >= 0) smf[m + 4 * e] = vv[k];
-        if (++r == sg.nper) { r = 0; e++; }
-      }
+    for (int k = 0; k < 4; k++) {
+      const int m = map[r];
+      if (m >= 0) smf[m + 4 * e] = vv[k];
+      if (++r == sg.nper) { r = 0; e++; }
     }
   }
 }
-
-// Stores one output segment (128-bit coalesced stores; constant segments are a
-// plain fill).
-__device__ __noinline__ void store_segment(const float* smf, const int32_t* ti, BxSeg sg, float* g,
-                                           int64_t env0, int nenv) {
-  if (g == nullptr || sg.nper == 0) return;
-  if (!seg_vector_ok(sg, g, env0, nenv)) {
-    io_segment_scalar<false>(const_cast<float*>(smf), ti, sg, g, env0, nenv);
-    return;
-  }
-  float4* b4 = reinterpret_cast<float4*>(g + env0 * sg.nper);
-  const int n4 = (nenv * sg.nper) >> 2;
-  if (sg.map < 0) {  // constant output (e.g. info.joint in pbd)
+// state quads -> global (coalesced 128-bit stores); constant segments are a fill
+BXD void store_warp(const float* smf, const int32_t* ti, const BxSeg& sg, float* gspan, int lane) {
+  const int n4 = BX_ENVS_PER_CTA / 4 * sg.nper;
+  float4* g4 = reinterpret_cast<float4*>(gspan);
+  if (sg.map < 0) {
     const float4 f = make_float4(sg.fill, sg.fill, sg.fill, sg.fill);
-    for (int i = threadIdx.x; i < n4; i += blockDim.x) b4[i] = f;
+    for (int i = lane; i < n4; i += 32) g4[i] = f;
     return;
   }
   const int32_t* map = ti + sg.map;
-#pragma unroll 2
-  for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+#pragma unroll 1
+  for (int i = lane; i < n4; i += 32) {
     int e, r;
     seg_locate(sg, i << 2, &e, &r);
     float vv[4];
@@ -197,7 +193,7 @@ __device__ __noinline__ void store_segment(const float* smf, const int32_t* ti, 
       vv[k] = m >= 0 ? smf[m + 4 * e] : sg.fill;
       if (++r == sg.nper) { r = 0; e++; }
     }
-    b4[i] = make_float4(vv[0], vv[1], vv[2], vv[3]);
+    g4[i] = make_float4(vv[0], vv[1], vv[2], vv[3]);
   }
 }
 
@@ -1079,9 +1075,34 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
   const int nenv = static_cast<int>((p.num_envs - env0) < BX_ENVS_PER_CTA ? (p.num_envs - env0) : BX_ENVS_PER_CTA);
 
   PT_INIT();
-  for (int i = threadIdx.x; i < h.n_fquads; i += blockDim.x) tf[i] = __ldg(p.tab_f + i);
-  for (int i = threadIdx.x; i < h.n_ints; i += blockDim.x) ti[i] = __ldg(p.tab_i + i);
-  if (nenv < BX_ENVS_PER_CTA) {
+  // ---- stage in: ONE wave of bulk async copies (tables + the five input spans of
+  // this tile), one mbarrier, then the transposition staging -> state quads.
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(ti + h.n_ints);
+  float* stage = smf + h.q_js * QS * 4;  // JS.. regions are dead outside the substep loop
+  const bool full = nenv == BX_ENVS_PER_CTA;
+  bool in_bulk = full;
+#pragma unroll
+  for (int s = 0; s < BX_SEG_IN; s++) in_bulk = in_bulk && span_bulk_ok(h.seg_in[s], p.in[s], env0);
+  uint32_t phase = 0;
+  if (threadIdx.x == 0) mbar_init(mbar, 1);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t bytes = h.n_fquads * 16 + h.n_ints * 4;
+    if (in_bulk)
+      for (int s = 0; s < BX_SEG_IN; s++) bytes += 4 * BX_ENVS_PER_CTA * h.seg_in[s].nper;
+    mbar_expect_tx(mbar, bytes);
+    bulk_g2s(tf, p.tab_f, h.n_fquads * 16, mbar);
+    bulk_g2s(ti, p.tab_i, h.n_ints * 4, mbar);
+    if (in_bulk) {
+      int off = 0;
+      for (int s = 0; s < BX_SEG_IN; s++) {
+        const int n = BX_ENVS_PER_CTA * h.seg_in[s].nper;
+        if (n) bulk_g2s(stage + off, p.in[s] + env0 * h.seg_in[s].nper, 4 * n, mbar);
+        off += n;
+      }
+    }
+  }
+  if (!full) {
     // partial tile: give the idle env slots a benign state (identity rotations)
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int i = threadIdx.x; i < h.n_quads * QS; i += blockDim.x) sq[i] = z;
@@ -1092,10 +1113,23 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
       const int b = br / nrot, which = br - b * nrot;
       sq[(L::BQ * b + 2 * which + 1) * QS + e] = make_float4(1.f, 0.f, 0.f, 0.f);
     }
+    __syncthreads();
   }
-  __syncthreads();
+  mbar_wait(mbar, phase);
+  phase ^= 1;
   PT(0);
-  load_segments<4>(smf, ti, h.seg_in, p.in, env0, nenv);
+  if (in_bulk) {
+    for (int s = threadIdx.x >> 5; s < BX_SEG_IN; s += blockDim.x >> 5) {
+      int off = 0;
+      for (int t = 0; t < s; t++) off += BX_ENVS_PER_CTA * h.seg_in[t].nper;
+      unstage_warp(smf, ti, h.seg_in[s], stage + off, threadIdx.x & 31);
+    }
+  } else {
+#pragma unroll 1
+    for (int s = 0; s < BX_SEG_IN; s++)
+      if (h.seg_in[s].nper)
+        io_segment_scalar<true>(smf, ti, h.seg_in[s], const_cast<float*>(p.in[s]), env0, nenv);
+  }
 
   Ctx c;
   c.warp = threadIdx.x >> 5;
@@ -1107,9 +1141,22 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
 
   for (int step = 0; step < p.num_steps; step++) {
     __syncthreads();
-    {
+    if (step > 0) {  // rollout: the actions of step t (step 0 came with the state)
       const float* act = p.in[4] + static_cast<int64_t>(step) * p.num_envs * h.act_size;
-      load_segments<1>(smf, ti, h.seg_in + 4, &act, env0, nenv);
+      const BxSeg sg = h.seg_in[4];
+      if (full && span_bulk_ok(sg, act, env0)) {
+        if (threadIdx.x == 0) {
+          fence_async_smem();
+          mbar_expect_tx(mbar, 4 * BX_ENVS_PER_CTA * sg.nper);
+          bulk_g2s(stage, act + env0 * sg.nper, 4 * BX_ENVS_PER_CTA * sg.nper, mbar);
+        }
+        mbar_wait(mbar, phase);
+        phase ^= 1;
+        if (threadIdx.x < 32) unstage_warp(smf, ti, sg, stage, threadIdx.x);
+      } else {
+        io_segment_scalar<true>(smf, ti, sg, const_cast<float*>(act), env0, nenv);
+      }
+      __syncthreads();
     }
     // zero_info (system.py:76-84): Info accumulators start at 0 every step
     {
@@ -1168,9 +1215,24 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
   __syncthreads();
 
   PT(10);
-  // outputs: the pos/rot maps point at buffer 0; buffer `cur` holds the result
+  // ---- out: each warp transposes whole segments straight to HBM with coalesced
+  // 128-bit stores.  The pos/rot maps point at buffer 0; buffer `cur` holds the
+  // result.
   const int cur_shift = (MODE == BX_MODE_PBD && c.cur) ? 2 * QS * 4 : 0;
+  bool out_vec = full;
+#pragma unroll
   for (int s = 0; s < BX_SEG_OUT; s++)
-    store_segment(smf + (s < 2 ? cur_shift : 0), ti, h.seg_out[s], p.out[s], env0, nenv);
+    out_vec = out_vec && (p.out[s] == nullptr || span_bulk_ok(h.seg_out[s], p.out[s], env0));
+  if (out_vec) {
+    for (int s = c.warp; s < BX_SEG_OUT; s += c.nwarp)
+      if (p.out[s] != nullptr && h.seg_out[s].nper > 0)
+        store_warp(smf + (s < 2 ? cur_shift : 0), ti, h.seg_out[s],
+                   p.out[s] + env0 * h.seg_out[s].nper, threadIdx.x & 31);
+  } else {
+#pragma unroll 1
+    for (int s = 0; s < BX_SEG_OUT; s++)
+      if (p.out[s] != nullptr && h.seg_out[s].nper > 0)
+        io_segment_scalar<false>(smf + (s < 2 ? cur_shift : 0), ti, h.seg_out[s], p.out[s], env0, nenv);
+  }
   PT(11);
 }

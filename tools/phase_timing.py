@@ -42,8 +42,8 @@ for a in acts[20:]:
   q, _ = s.step(q, a)
 torch.cuda.synchronize()
 v = dbg.cpu().numpy() / n
-names = ['tables', 'load', 'T', 'B1', 'J', 'B2', 'C1', 'B3', 'C2', 'B4', 'tail', 'store']
-tot = v[:12].sum()
+names = ['tables', 'load', 'T', 'B1', 'J', 'B2', 'C1', 'B3', 'C2', 'B4', 'tail', 'store', 'stage', 'flush']
+tot = v[:14].sum()
 print('%s B=%d: %.0f cycles/step (%.1f us @1.965GHz)' % (name, b, tot, tot / 1965))
 for nm, x in zip(names, v):
   print('  %-7s %8.0f  %5.1f%%' % (nm, x, 100 * x / tot))
