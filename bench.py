@@ -311,7 +311,7 @@ def run_gpu(args, desc):
 
 
 def s_threads(s):
-  return s.threads_per_tile
+  return int(s._lib.bx_system_threads(s._h))
 
 
 def main():

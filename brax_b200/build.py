@@ -9,29 +9,46 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libbrax_b200.so')
-SOURCES = ['bx_api.cu']  # single translation unit (includes bx_step_kernel.cu)
-DEPS = ['bx_api.cu', 'bx_step_kernel.cu', 'bx_math.cuh', 'bx_tables.h',
+DEPS = ['bx_api.cu', 'bx_kernels.cu', 'bx_step_kernel.cuh', 'bx_params.h', 'bx_math.cuh', 'bx_tables.h',
         os.path.join('..', '..', 'include', 'brax_b200.h')]
+# (launch bound threads, min blocks per SM): one kernel translation unit each
+BOUNDS = [(256, 2), (320, 2), (512, 1)]
 
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3',
-              '-std=c++17', '-shared', '-Xcompiler', '-fPIC']
+              '-std=c++17', '-Xcompiler', '-fPIC']
 
 
-def stale() -> bool:
-  if not os.path.exists(LIB):
+def stale(lib=None) -> bool:
+  lib = lib or LIB
+  if not os.path.exists(lib):
     return True
-  t = os.path.getmtime(LIB)
+  t = os.path.getmtime(lib)
   return any(os.path.getmtime(os.path.join(CSRC, d)) > t for d in DEPS)
 
 
-def build(force: bool = False, verbose: bool = False, extra=()) -> str:
-  if force or stale():
-    nvcc = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
-    cmd = [nvcc] + NVCC_FLAGS + list(extra) + (
-        ['-Xptxas', '-v'] if verbose else []) + [
-            os.path.join(CSRC, s) for s in SOURCES] + ['-o', LIB]
-    subprocess.check_call(cmd)
-  return LIB
+def build(force: bool = False, verbose: bool = False, extra=(), out: str = None) -> str:
+  """Compiles bx_api.cu + one bx_kernels.cu object per launch bound (in
+  parallel) and links them into the shared library."""
+  out = out or LIB
+  if not (force or stale(out)):
+    return out
+  nvcc = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
+  objdir = os.path.join(HERE, 'csrc', '_obj' + ('' if out == LIB else '_' + os.path.basename(out)))
+  os.makedirs(objdir, exist_ok=True)
+  common = [nvcc] + NVCC_FLAGS + list(extra) + (['-Xptxas', '-v'] if verbose else [])
+  jobs = [(common + ['-c', os.path.join(CSRC, 'bx_api.cu'), '-o', os.path.join(objdir, 'bx_api.o')])]
+  objs = [os.path.join(objdir, 'bx_api.o')]
+  for maxt, minb in BOUNDS:
+    o = os.path.join(objdir, 'bx_kernels_%d.o' % maxt)
+    objs.append(o)
+    jobs.append(common + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-c',
+                          os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
+  procs = [subprocess.Popen(j) for j in jobs]
+  rcs = [p.wait() for p in procs]
+  if any(rcs):
+    raise subprocess.CalledProcessError(max(rcs), 'nvcc')
+  subprocess.check_call([nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', out] + objs)
+  return out
 
 
 if __name__ == '__main__':

@@ -16,9 +16,8 @@
 #include <vector>
 
 #include "../../include/brax_b200.h"
+#include "bx_params.h"
 #include "bx_tables.h"
-// single translation unit: the kernel (and BxKernelParams) is compiled here
-#include "bx_step_kernel.cu"
 
 struct bx_system {
   BxHeader h;
@@ -27,6 +26,7 @@ struct bx_system {
   float4* d_tab_f;
   size_t smem_bytes;
   int warps;  // warps per CTA (W)
+  int jc, cc; // joint / contact class of the kernel variant (bx_params.h)
   int sm_count;
   // scratch for bx_step_host / bx_rollout
   float* d_scratch;
@@ -423,27 +423,18 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   h.inv_2h = 1.f / (2.f * d->dt_sub);
 }
 
-// One instantiation per (dynamics mode, launch bounds); the launch picks the
-// smallest bound that holds the configured CTA size.
-typedef void (*bx_kernel_fn)(const BxKernelParams);
-static bx_kernel_fn pick_kernel(int mode, int threads) {
-  if (mode == BX_MODE_PBD) {
-    if (threads <= 256) return bx_step_kernel<BX_MODE_PBD, 256, 2>;
-    if (threads <= 320) return bx_step_kernel<BX_MODE_PBD, 320, 2>;
-    if (threads <= 384) return bx_step_kernel<BX_MODE_PBD, 384, 2>;
-    return bx_step_kernel<BX_MODE_PBD, 512, 1>;
-  }
-  if (threads <= 256) return bx_step_kernel<BX_MODE_LEGACY_SPRING, 256, 2>;
-  if (threads <= 320) return bx_step_kernel<BX_MODE_LEGACY_SPRING, 320, 2>;
-  if (threads <= 384) return bx_step_kernel<BX_MODE_LEGACY_SPRING, 384, 2>;
-  return bx_step_kernel<BX_MODE_LEGACY_SPRING, 512, 1>;
+// The kernels live in one translation unit per launch bound (bx_kernels.cu); the
+// launch picks the smallest bound that holds the configured CTA size.
+static cudaError_t launch_variant(int mode, int jc, int cc, unsigned grid, int threads, size_t smem,
+                                  cudaStream_t stream, const BxKernelParams& p) {
+  if (threads <= 256) return bx_launch_256(mode, jc, cc, grid, threads, smem, stream, p);
+  if (threads <= 320) return bx_launch_320(mode, jc, cc, grid, threads, smem, stream, p);
+  return bx_launch_512(mode, jc, cc, grid, threads, smem, stream, p);
 }
 static int set_smem_attr(int bytes) {
-  const int sizes[4] = {256, 320, 384, 512};
-  for (int mode = 0; mode < 2; mode++)
-    for (int i = 0; i < 4; i++)
-      CUDA_OK(cudaFuncSetAttribute(pick_kernel(mode, sizes[i]),
-                                   cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  CUDA_OK(bx_set_smem_256(bytes));
+  CUDA_OK(bx_set_smem_320(bytes));
+  CUDA_OK(bx_set_smem_512(bytes));
   return 0;
 }
 
@@ -465,6 +456,18 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   std::vector<int32_t> ti;
   std::vector<float> tf;
   build_tables(desc, &s->h, &ti, &tf);
+  {
+    bool rev = false, other = false, sph_only = desc->num_joints > 0;
+    for (int i = 0; i < desc->num_joints; i++) {
+      const int k = desc->joints[i].kind;
+      if (k == BX_JOINT_REVOLUTE || k == BX_JOINT_SPRING_REVOLUTE) rev = true; else other = true;
+      if (k != BX_JOINT_SPHERICAL) sph_only = false;
+    }
+    s->jc = !other ? BX_JC_REVOLUTE : ((sph_only && !rev) ? BX_JC_SPHERICAL : BX_JC_ALL);
+    s->cc = BX_CC_PLANE;
+    for (int i = 0; i < desc->num_pairs; i++)
+      if (desc->pairs[i].two_way || desc->pairs[i].kind == BX_PAIR_CAPSULE_CAPSULE) s->cc = BX_CC_ALL;
+  }
   s->device = device;
   s->sm_count = prop.multiProcessorCount;
   s->d_scratch = nullptr;
@@ -552,10 +555,10 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   p.dbg = g_dbg;
   const int64_t tiles = (num_envs + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA;
   if (tiles > 0x7fffffffLL) return fail("too many environments for one launch");
-  pick_kernel(s->h.mode, 32 * s->warps)<<<static_cast<unsigned>(tiles), 32 * s->warps,
-                                          s->smem_bytes, stream>>>(p);
+  cudaError_t le = launch_variant(s->h.mode, s->jc, s->cc, static_cast<unsigned>(tiles), 32 * s->warps,
+                                  s->smem_bytes, stream, p);
   g_launches.fetch_add(1);
-  CUDA_OK(cudaGetLastError());
+  CUDA_OK(le);
   return 0;
 }
 
@@ -567,6 +570,39 @@ extern "C" int bx_rollout(bx_system* s, int64_t num_envs, int32_t num_steps, con
                           void* stream) {
   return launch(s, num_envs, num_steps, io, static_cast<cudaStream_t>(stream));
 }
+
+// Times the candidate CTA sizes on the caller's own buffers and keeps the fastest
+// (outputs are overwritten by every trial: call it before a real step).
+extern "C" int bx_system_autotune(bx_system* s, int64_t num_envs, const bx_step_io* io, void* stream) {
+  if (!s || !io) return fail("NULL argument");
+  CUDA_OK(cudaSetDevice(s->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaEvent_t e0, e1;
+  CUDA_OK(cudaEventCreate(&e0));
+  CUDA_OK(cudaEventCreate(&e1));
+  const int cand[4] = {8, 10, 12, 16};
+  const int keep = s->warps;
+  float best = 1e30f;
+  int best_w = keep;
+  for (int i = 0; i < 4; i++) {
+    s->warps = cand[i];
+    if (launch(s, num_envs, 1, io, st)) { s->warps = keep; return 1; }  // warm-up
+    CUDA_OK(cudaEventRecord(e0, st));
+    for (int r = 0; r < 3; r++)
+      if (launch(s, num_envs, 1, io, st)) { s->warps = keep; return 1; }
+    CUDA_OK(cudaEventRecord(e1, st));
+    CUDA_OK(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+    if (ms < best) { best = ms; best_w = cand[i]; }
+  }
+  s->warps = best_w;
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  return 0;
+}
+
+extern "C" int bx_system_threads(const bx_system* s) { return s ? 32 * s->warps : -1; }
 
 // Host-buffer step: H2D copies, one launch, D2H copies, synchronise.
 extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {

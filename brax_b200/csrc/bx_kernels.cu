@@ -1,0 +1,50 @@
+// bx_kernels.cu -- instantiates the step kernel for ONE launch bound
+// (compiled once per bound: -DBX_TU_MAXT=256|320|512 -DBX_TU_MINB=2|2|1) and
+// exports its launcher.  Variants: dynamics mode x joint class x contact class
+// (bx_params.h); a system runs the variant that contains only its own features.
+#include "bx_step_kernel.cuh"
+
+#ifndef BX_TU_MAXT
+#error "compile with -DBX_TU_MAXT=<threads> -DBX_TU_MINB=<blocks per SM>"
+#endif
+
+#define BX_CAT_(a, b) a##b
+#define BX_CAT(a, b) BX_CAT_(a, b)
+
+typedef void (*bx_kernel_fn)(const BxKernelParams);
+
+template <int MODE>
+static bx_kernel_fn pick(int jc, int cc) {
+#define BX_K(JM, CM) bx_step_kernel<MODE, (JM) | (CM) | BXF_COMMON, BX_TU_MAXT, BX_TU_MINB>
+  if (cc == BX_CC_PLANE) {
+    if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC0);
+    if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC0);
+    return BX_K(BXF_JC2, BXF_CC0);
+  }
+  if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC1);
+  if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC1);
+  return BX_K(BXF_JC2, BXF_CC1);
+#undef BX_K
+}
+
+static bx_kernel_fn pick_any(int mode, int jc, int cc) {
+  return mode == BX_MODE_PBD ? pick<BX_MODE_PBD>(jc, cc) : pick<BX_MODE_LEGACY_SPRING>(jc, cc);
+}
+
+cudaError_t BX_CAT(bx_launch_, BX_TU_MAXT)(int mode, int jc, int cc, unsigned grid, int threads,
+                                           size_t smem, cudaStream_t stream,
+                                           const BxKernelParams& p) {
+  pick_any(mode, jc, cc)<<<grid, threads, smem, stream>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t BX_CAT(bx_set_smem_, BX_TU_MAXT)(int bytes) {
+  for (int mode = 0; mode < 2; mode++)
+    for (int jc = 0; jc < BX_NUM_JC; jc++)
+      for (int cc = 0; cc < BX_NUM_CC; cc++) {
+        cudaError_t e = cudaFuncSetAttribute(pick_any(mode, jc, cc),
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e != cudaSuccess) return e;
+      }
+  return cudaSuccess;
+}

@@ -1,0 +1,56 @@
+// bx_params.h -- kernel parameter block, feature masks and the launcher
+// interface between bx_api.cu (host API) and the kernel translation units.
+#ifndef BX_PARAMS_H_
+#define BX_PARAMS_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "bx_tables.h"
+
+struct BxKernelParams {
+  BxHeader h;
+  const int32_t* tab_i;
+  const float4* tab_f;
+  const float* in[BX_SEG_IN];  // pos rot vel ang act
+  float* out[BX_SEG_OUT];      // order of bx_step_io's outputs
+  int64_t num_envs;
+  int32_t num_steps;  // >1: rollout, act is [T,B,A]
+  long long* dbg;     // BX_PHASE_TIMING builds only: cycles per phase of CTA 0
+};
+
+
+// Feature mask of a kernel variant: code for features a system does not use is
+// compiled out (smaller instruction footprint of the substep loop).
+enum {
+  BXF_REVOLUTE = 1, BXF_SPHERICAL = 2, BXF_UNIVERSAL = 4,
+  BXF_ONE_WAY = 8, BXF_TWO_WAY = 16,
+  BXF_CAPSULE_PLANE = 32, BXF_CAPSULE_CAPSULE = 64, BXF_BOX_PLANE = 128,
+  BXF_TORQUE = 256, BXF_ANGLE = 512, BXF_FORCES = 1024,
+  BXF_ALL = 2047
+};
+// Kernel variants are instantiated per (dynamics mode, joint class, contact
+// class, launch bound).  Classes are the feature sets of the reference's envs:
+// all-revolute (ant, fetch), all-spherical (humanoid, grasp: joints.py:418-474
+// "sphericalize"), anything; plane contacts only (one-way capsule/box vs plane)
+// or everything.
+enum { BX_JC_REVOLUTE = 0, BX_JC_SPHERICAL = 1, BX_JC_ALL = 2, BX_NUM_JC = 3 };
+enum { BX_CC_PLANE = 0, BX_CC_ALL = 1, BX_NUM_CC = 2 };
+#define BXF_COMMON (BXF_TORQUE | BXF_ANGLE | BXF_FORCES)
+#define BXF_JC0 BXF_REVOLUTE
+#define BXF_JC1 BXF_SPHERICAL
+#define BXF_JC2 (BXF_REVOLUTE | BXF_SPHERICAL | BXF_UNIVERSAL)
+#define BXF_CC0 (BXF_ONE_WAY | BXF_CAPSULE_PLANE | BXF_BOX_PLANE)
+#define BXF_CC1 (BXF_ONE_WAY | BXF_TWO_WAY | BXF_CAPSULE_PLANE | BXF_CAPSULE_CAPSULE | BXF_BOX_PLANE)
+
+// One translation unit per launch bound (bx_kernels.cu compiled with
+// -DBX_TU_MAXT=.. -DBX_TU_MINB=..) exports these two functions.
+#define BX_LAUNCHER_DECL(maxt)                                                              \
+  cudaError_t bx_launch_##maxt(int mode, int jc, int cc, unsigned grid, int threads,        \
+                               size_t smem, cudaStream_t stream, const BxKernelParams& p); \
+  cudaError_t bx_set_smem_##maxt(int bytes);
+BX_LAUNCHER_DECL(256)
+BX_LAUNCHER_DECL(320)
+BX_LAUNCHER_DECL(512)
+
+#endif  // BX_PARAMS_H_

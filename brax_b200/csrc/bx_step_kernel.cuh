@@ -25,18 +25,7 @@
 
 #include "../../include/brax_b200.h"
 #include "bx_math.cuh"
-#include "bx_tables.h"
-
-struct BxKernelParams {
-  BxHeader h;
-  const int32_t* tab_i;
-  const float4* tab_f;
-  const float* in[BX_SEG_IN];  // pos rot vel ang act
-  float* out[BX_SEG_OUT];      // order of bx_step_io's outputs
-  int64_t num_envs;
-  int32_t num_steps;  // >1: rollout, act is [T,B,A]
-  long long* dbg;     // BX_PHASE_TIMING builds only: cycles per phase of CTA 0
-};
+#include "bx_params.h"
 
 // Phase timing (tools/phase_timing.py builds with -DBX_PHASE_TIMING): thread 0
 // of CTA 0 accumulates the cycles between consecutive barriers per phase id.
@@ -57,6 +46,12 @@ struct BxKernelParams {
 
 #define QS BX_QSTRIDE
 
+// Inside Kern<FEAT> the mask is the template parameter.
+#define BX_FEAT FEAT
+// "is x the case?" with the answer folded at compile time when the mask decides it
+#define BXF_IS(cond, yes_mask, no_mask) \
+  ((BX_FEAT & (no_mask)) == 0 ? true : ((BX_FEAT & (yes_mask)) == 0 ? false : (cond)))
+
 struct Ctx {
   float4* q;          // shared state base + lane
   const float4* tf;   // float4 tables (shared)
@@ -73,28 +68,35 @@ template <int MODE> struct Lay {
 
 #define QROW(c, r) ((c).q[(r) * QS])
 
-BXD V3 f3(float4 t) { return v3(t.x, t.y, t.z); }
-BXD V3 ldv(const Ctx& c, int r) { return f3(QROW(c, r)); }
-BXD Q4 ldq(const Ctx& c, int r) { float4 t = QROW(c, r); return q4(t.x, t.y, t.z, t.w); }
-BXD void stv(const Ctx& c, int r, V3 v) { QROW(c, r) = make_float4(v.x, v.y, v.z, 0.f); }
-BXD void stv4(const Ctx& c, int r, V3 v, float w) { QROW(c, r) = make_float4(v.x, v.y, v.z, w); }
-BXD void stq(const Ctx& c, int r, Q4 q) { QROW(c, r) = make_float4(q.w, q.x, q.y, q.z); }
-BXD float act_at(const Ctx& c, const BxHeader& h, int i) {
+extern __shared__ __align__(16) float4 bx_smem[];
+
+// All device code of the step lives in Kern<FEAT>: FEAT (a BXF_* mask) folds the
+// feature tests at compile time.
+#define BXS static __device__ __forceinline__
+template <int FEAT>
+struct Kern {
+BXS V3 f3(float4 t) { return v3(t.x, t.y, t.z); }
+BXS V3 ldv(const Ctx& c, int r) { return f3(QROW(c, r)); }
+BXS Q4 ldq(const Ctx& c, int r) { float4 t = QROW(c, r); return q4(t.x, t.y, t.z, t.w); }
+BXS void stv(const Ctx& c, int r, V3 v) { QROW(c, r) = make_float4(v.x, v.y, v.z, 0.f); }
+BXS void stv4(const Ctx& c, int r, V3 v, float w) { QROW(c, r) = make_float4(v.x, v.y, v.z, w); }
+BXS void stq(const Ctx& c, int r, Q4 q) { QROW(c, r) = make_float4(q.w, q.x, q.y, q.z); }
+BXS float act_at(const Ctx& c, const BxHeader& h, int i) {
   return reinterpret_cast<const float*>(&QROW(c, h.q_act + (i >> 2)))[i & 3];
 }
-BXD int4 ldi4(const int32_t* p) { return *reinterpret_cast<const int4*>(p); }
+BXS int4 ldi4(const int32_t* p) { return *reinterpret_cast<const int4*>(p); }
 
 // ---- global <-> shared transposing I/O ---------------------------------------
 // g: [B, nper] row-major; this CTA owns envs [env0, env0+nenv).  Element (e, r)
 // lives at shared float index map[r] + 4*e (map[r] < 0: constant `fill`).
-BXD void seg_locate(const BxSeg& sg, int idx, int* e, int* r) {
+BXS void seg_locate(const BxSeg& sg, int idx, int* e, int* r) {
   *e = sg.magic ? static_cast<int>(__umulhi(static_cast<unsigned>(idx), sg.magic)) : idx;
   *r = idx - *e * sg.nper;
 }
 
 // scalar fallback (ragged tiles / unaligned pointers)
 template <bool LOAD>
-__device__ __noinline__ void io_segment_scalar(float* smf, const int32_t* ti, BxSeg sg, float* g,
+static __device__ __noinline__ void io_segment_scalar(float* smf, const int32_t* ti, BxSeg sg, float* g,
                                                int64_t env0, int nenv) {
   float* base = g + env0 * sg.nper;
   const int32_t* map = ti + sg.map;
@@ -110,16 +112,16 @@ __device__ __noinline__ void io_segment_scalar(float* smf, const int32_t* ti, Bx
 
 // ---- bulk asynchronous copies (TMA engine, no tensor map needed: every span of
 // a 32-env tile is contiguous in HBM) ------------------------------------------
-BXD uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
-BXD void mbar_init(uint64_t* bar, int count) {
+BXS uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+BXS void mbar_init(uint64_t* bar, int count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
-BXD void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+BXS void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
 }
-BXD void mbar_wait(uint64_t* bar, uint32_t parity) {
+BXS void mbar_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "BX_WAIT:\n\t"
@@ -129,24 +131,24 @@ BXD void mbar_wait(uint64_t* bar, uint32_t parity) {
       "BX_DONE:\n\t}" ::"r"(smem_u32(bar)), "r"(parity)
       : "memory");
 }
-BXD void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+BXS void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                    smem_u32(smem_dst)),
                "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
-BXD void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes) {
+BXS void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
                "r"(smem_u32(smem_src)), "r"(bytes)
                : "memory");
 }
-BXD void bulk_commit_wait_read() {
+BXS void bulk_commit_wait_read() {
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
   asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
-BXD void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+BXS void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-BXD bool span_bulk_ok(const BxSeg& sg, const float* g, int64_t env0) {
+BXS bool span_bulk_ok(const BxSeg& sg, const float* g, int64_t env0) {
   return (reinterpret_cast<uintptr_t>(g + env0 * sg.nper) & 15) == 0;
 }
 
@@ -154,7 +156,7 @@ BXD bool span_bulk_ok(const BxSeg& sg, const float* g, int64_t env0) {
 // lane and iteration (128-bit on the global / staging side).  All warps run this
 // same small loop on different segments at once.
 // staging (global layout [env][nper]) -> state quads
-BXD void unstage_warp(float* smf, const int32_t* ti, const BxSeg& sg, const float* stage, int lane) {
+BXS void unstage_warp(float* smf, const int32_t* ti, const BxSeg& sg, const float* stage, int lane) {
   const int32_t* map = ti + sg.map;
   const int n4 = BX_ENVS_PER_CTA / 4 * sg.nper;
   const float4* st4 = reinterpret_cast<const float4*>(stage);
@@ -173,7 +175,7 @@ BXD void unstage_warp(float* smf, const int32_t* ti, const BxSeg& sg, const floa
   }
 }
 // state quads -> global (coalesced 128-bit stores); constant segments are a fill
-BXD void store_warp(const float* smf, const int32_t* ti, const BxSeg& sg, float* gspan, int lane) {
+BXS void store_warp(const float* smf, const int32_t* ti, const BxSeg& sg, float* gspan, int lane) {
   const int n4 = BX_ENVS_PER_CTA / 4 * sg.nper;
   float4* g4 = reinterpret_cast<float4*>(gspan);
   if (sg.map < 0) {
@@ -199,7 +201,7 @@ BXD void store_warp(const float* smf, const int32_t* ti, const BxSeg& sg, float*
 
 // ---- joints: axis / angle -------------------------------------------------
 // Revolute.axis_angle joints.py:311-319 (spring_joints.py:150-157)
-BXD void axis_angle_revolute(const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
+BXS void axis_angle_revolute(const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
   V3 ax = rotate(f3(jq[JQ_AXIS_P]), rp);
   V3 ref_p = rotate(f3(jq[JQ_AXIS_P + 2]), rp);
   V3 ref_c = rotate(f3(jq[JQ_AXIS_C + 2]), rc);
@@ -208,7 +210,7 @@ BXD void axis_angle_revolute(const float4* jq, Q4 rp, Q4 rc, V3* axis, float* an
 }
 
 // Spherical.axis_angle joints.py:388-415 (spring_joints.py:212-224, 276-303)
-BXD void axis_angle_spherical(const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
+BXS void axis_angle_spherical(const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
   V3 a1p = rotate(f3(jq[JQ_AXIS_P]), rp);
   V3 a2p = rotate(f3(jq[JQ_AXIS_P + 1]), rp);
   V3 a1c = rotate(f3(jq[JQ_AXIS_C]), rc);
@@ -225,14 +227,16 @@ BXD void axis_angle_spherical(const float4* jq, Q4 rp, Q4 rc, V3* axis, float* a
   angle[0] = psi; angle[1] = theta; angle[2] = phi;
 }
 
-BXD int joint_dof(int kind) {
-  return (kind == BX_JOINT_REVOLUTE || kind == BX_JOINT_SPRING_REVOLUTE)
+BXS int joint_dof(int kind) {
+  return BXF_IS(kind == BX_JOINT_REVOLUTE || kind == BX_JOINT_SPRING_REVOLUTE, BXF_REVOLUTE,
+                BXF_SPHERICAL | BXF_UNIVERSAL)
              ? 1
-             : (kind == BX_JOINT_SPRING_UNIVERSAL ? 2 : 3);
+             : (BXF_IS(kind == BX_JOINT_SPRING_UNIVERSAL, BXF_UNIVERSAL, BXF_SPHERICAL) ? 2 : 3);
 }
 
-BXD void joint_axis_angle(int kind, const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
-  if (kind == BX_JOINT_REVOLUTE || kind == BX_JOINT_SPRING_REVOLUTE)
+BXS void joint_axis_angle(int kind, const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
+  if (BXF_IS(kind == BX_JOINT_REVOLUTE || kind == BX_JOINT_SPRING_REVOLUTE, BXF_REVOLUTE,
+             BXF_SPHERICAL | BXF_UNIVERSAL))
     axis_angle_revolute(jq, rp, rc, axis, angle);
   else
     axis_angle_spherical(jq, rp, rc, axis, angle);
@@ -243,7 +247,7 @@ BXD void joint_axis_angle(int kind, const float4* jq, Q4 rp, Q4 rc, V3* axis, fl
 // joint j to quad JS+na+j; the body phase turns them into angular
 // accelerations (actuators.py:52-112, joints.py:103-128).
 template <int MODE>
-BXD void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
+BXS void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
   typedef Lay<MODE> L;
   const int ro = MODE == BX_MODE_PBD ? 2 * c.cur + 1 : 1;
   for (int a = c.warp; a < h.na; a += c.nwarp) {
@@ -274,7 +278,7 @@ BXD void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
         idx = min(max(idx, 0), h.act_size - 1);
         float av = act_at(c, h, idx) * m;
         float t;
-        if (ai.x == BX_ACT_TORQUE) {
+        if (BXF_IS(ai.x == BX_ACT_TORQUE, BXF_TORQUE, BXF_ANGLE)) {
           t = av * strength * -1.f;
           t = angle[d] < lo[d] ? 0.f : t;
           t = angle[d] > hi[d] ? 0.f : t;
@@ -289,7 +293,7 @@ BXD void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
     // parent +, child -; Angle: parent -, child + (actuators.py:88-89,109-110)
     V3 tp = f3(c.tf[h.fo_body + ji.y * BQ_STRIDE + BQ_INV_INERTIA]) * tq;
     V3 tc = f3(c.tf[h.fo_body + ji.z * BQ_STRIDE + BQ_INV_INERTIA]) * tq;
-    const bool angle_act = ai.x == BX_ACT_ANGLE;
+    const bool angle_act = BXF_IS(ai.x == BX_ACT_ANGLE, BXF_ANGLE, BXF_TORQUE);
     stv(c, h.q_js + ai2.y, angle_act ? -tp : tp);
     stv(c, h.q_js + ai2.z, angle_act ? tc : -tc);
   }
@@ -309,7 +313,7 @@ BXD void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
 
 // Sum of the angular accelerations of body b from actuators (dp_a), joint
 // damping (dp_j) and forces (dp_f); system.py:268-271.
-BXD void body_accels(const Ctx& c, const BxHeader& h, const int32_t* bi, const float4* bq,
+BXS void body_accels(const Ctx& c, const BxHeader& h, const int32_t* bi, const float4* bq,
                      bool damp, V3* dpa_ang, V3* dpj_ang, V3* dpf_vel, V3* dpf_ang) {
   V3 dpa = v3(0.f, 0.f, 0.f), dpj = v3(0.f, 0.f, 0.f);
   {
@@ -322,7 +326,7 @@ BXD void body_accels(const Ctx& c, const BxHeader& h, const int32_t* bi, const f
     for (int i = 0; i < n; i++) dpj = dpj + ldv(c, r + i);
   }
   V3 fv = v3(0.f, 0.f, 0.f), fa = v3(0.f, 0.f, 0.f);
-  {
+  if (BX_FEAT & BXF_FORCES) {
     const int32_t* adj = c.ti + h.io_adj + bi[BI_F_OFF];
     const int n = bi[BI_F_N];
     for (int i = 0; i < n; i++) {
@@ -341,7 +345,7 @@ BXD void body_accels(const Ctx& c, const BxHeader& h, const int32_t* bi, const f
 
 // ---- integrator pieces (per body) -------------------------------------------
 // Euler.kinetic integrators.py:50-68
-BXD void kinetic(const BxHeader& h, V3 pm, V3 rm, V3 vel, V3 ang, V3* pos, Q4* rot) {
+BXS void kinetic(const BxHeader& h, V3 pm, V3 rm, V3 vel, V3 ang, V3* pos, Q4* rot) {
   *pos = *pos + (vel * h.dt) * pm;
   V3 w = (ang * rm) * h.half_dt;
   Q4 r = *rot + quat_mul(q4(0.f, w.x, w.y, w.z), *rot);
@@ -351,7 +355,7 @@ BXD void kinetic(const BxHeader& h, V3 pm, V3 rm, V3 vel, V3 ang, V3* pos, Q4* r
 }
 
 // Euler.velocity_projection integrators.py:122-146
-BXD void velocity_projection(const BxHeader& h, V3 pm, V3 rm, V3 pos, V3 ppos, Q4 prot, Q4* rot,
+BXS void velocity_projection(const BxHeader& h, V3 pm, V3 rm, V3 pos, V3 ppos, Q4 prot, Q4* rot,
                              V3* vel, V3* ang) {
   Q4 r = *rot;
   float n = bx_sqrt(r.w * r.w + r.x * r.x + r.y * r.y + r.z * r.z);
@@ -369,7 +373,7 @@ BXD void velocity_projection(const BxHeader& h, V3 pm, V3 rm, V3 pos, V3 ppos, Q
 // ---- phase B1 (pbd): acceleration update + kinetic step, per body ------------
 // system.py:268-274 / :287-293.  Reads pos/rot from buffer cur, writes the
 // advanced pos/rot into buffer cur^1 (buffer cur then IS qprev).
-BXD void phase_body_acc_kinetic(const Ctx& c, const BxHeader& h, bool accumulate_info) {
+BXS void phase_body_acc_kinetic(const Ctx& c, const BxHeader& h, bool accumulate_info) {
   typedef Lay<BX_MODE_PBD> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
@@ -402,7 +406,7 @@ BXD void phase_body_acc_kinetic(const Ctx& c, const BxHeader& h, bool accumulate
 struct DQ { V3 pos; Q4 rot; };
 
 // Joint.apply_angle_update joints.py:130-152 (rot parts only; pos parts are 0)
-BXD void angle_update(V3 dq, V3 ii_p, V3 ii_c, Q4 rp, Q4 rc, float scale_ang,
+BXS void angle_update(V3 dq, V3 ii_p, V3 ii_c, Q4 rp, Q4 rc, float scale_ang,
                       Q4* out_p, Q4* out_c) {
   float th = safe_norm(dq);
   V3 n = vdiv(dq, th + 1e-6f);
@@ -414,7 +418,7 @@ BXD void angle_update(V3 dq, V3 ii_p, V3 ii_c, Q4 rp, Q4 rc, float scale_ang,
 }
 
 // Joint.apply_position_update joints.py:154-195
-BXD void position_update(V3 wp, V3 wc, V3 pos_p, V3 pos_c, Q4 rp, Q4 rc,
+BXS void position_update(V3 wp, V3 wc, V3 pos_p, V3 pos_c, Q4 rp, Q4 rc,
                          float im_p, float im_c, float m_p, float m_c, V3 ii_p,
                          V3 ii_c, float scale_pos, DQ* dp, DQ* dc) {
   V3 dx = wp - wc;
@@ -433,7 +437,7 @@ BXD void position_update(V3 wp, V3 wc, V3 pos_p, V3 pos_c, Q4 rp, Q4 rc,
 }
 
 // limit_angle closure of Spherical.apply_reduced joints.py:343-354
-BXD void limit_angle(V3 n, V3 n_1, V3 n_2, float lo, float hi, V3 ii_p, V3 ii_c,
+BXS void limit_angle(V3 n, V3 n_1, V3 n_2, float lo, float hi, V3 ii_p, V3 ii_c,
                      Q4 rp, Q4 rc, float scale_ang, Q4* out_p, Q4* out_c) {
   float ph = signed_angle(n, n_1, n_2);
   float mask = ph < lo ? 1.f : 0.f;
@@ -447,7 +451,7 @@ BXD void limit_angle(V3 n, V3 n_1, V3 n_2, float lo, float hi, V3 ii_p, V3 ii_c,
 // ---- phase J (pbd): Joint.apply for every joint -> per-joint delta slots -------
 // joints.py:79-100, Revolute :270-309, Spherical :332-386.  Slot of joint j:
 // quads JS+4j .. +3 = parent dpos, parent drot, child dpos, child drot.
-BXD void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
+BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_PBD> L;
   for (int j = c.warp; j < h.nj; j += c.nwarp) {
     const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
@@ -467,7 +471,7 @@ BXD void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
     position_update(wp, wc, pos_p, pos_c, rp, rc, mp.x, mc.x, mp.y, mc.y, ii_p, ii_c, j1.w, &dp, &dc);
     const float sa = ap0.w;
     const float4 l01 = jq[JQ_LIMIT];
-    if (ji.x == BX_JOINT_REVOLUTE) {
+    if (BXF_IS(ji.x == BX_JOINT_REVOLUTE, BXF_REVOLUTE, BXF_SPHERICAL)) {
       V3 axis = rotate(f3(ap0), rp);
       V3 ref_p = rotate(f3(jq[JQ_AXIS_P + 2]), rp);
       V3 ref_c = rotate(f3(jq[JQ_AXIS_C + 2]), rc);
@@ -511,7 +515,7 @@ BXD void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
 
 // ---- phase B2 (pbd): apply joint deltas (+ velocity projection in half A) ---
 // integrators.py:103-110 then :122-146; system.py:277-281 / :296-297.
-BXD void phase_body_joint_update(const Ctx& c, const BxHeader& h, bool project) {
+BXS void phase_body_joint_update(const Ctx& c, const BxHeader& h, bool project) {
   typedef Lay<BX_MODE_PBD> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
@@ -543,7 +547,7 @@ BXD void phase_body_joint_update(const Ctx& c, const BxHeader& h, bool project) 
 struct Contact { V3 pos, vel, normal; float pen; };
 
 // geometry.py:360-374
-BXD V3 closest_segment_point_and_dist(V3 a, V3 b, V3 pt, float* d2) {
+BXS V3 closest_segment_point_and_dist(V3 a, V3 b, V3 pt, float* d2) {
   V3 ab = b - a;
   float t = bx_div(dot(pt - a, ab), dot(ab, ab) + 1e-6f);
   V3 p = a + clipf(t, 0.f, 1.f) * ab;
@@ -553,7 +557,7 @@ BXD V3 closest_segment_point_and_dist(V3 a, V3 b, V3 pt, float* d2) {
 }
 
 // geometry.py:394-459 closest_segment_to_segment_points
-BXD void closest_seg_seg(V3 a0, V3 a1, V3 b0, V3 b1, V3* best_a, V3* best_b) {
+BXS void closest_seg_seg(V3 a0, V3 a1, V3 b0, V3 b1, V3* best_a, V3* best_b) {
   V3 dir_a = a1 - a0;
   float len_a = safe_norm(dir_a);
   len_a += 1e-6f * (len_a == 0.f ? 1.f : 0.f);
@@ -580,18 +584,19 @@ BXD void closest_seg_seg(V3 a0, V3 a1, V3 b0, V3 b1, V3* best_a, V3* best_b) {
   *best_b = first ? bb : nb;
 }
 
-BXD float w_of(float inv_mass, V3 inv_i, V3 r, V3 n) {
+BXS float w_of(float inv_mass, V3 inv_i, V3 r, V3 n) {
   V3 cr = cross(r, n);
   return inv_mass + dot(cr, inv_i * cr);
 }
 
 // contact function of one contact row (colliders.py:667-680 box_plane,
 // :744-759 capsule_plane, :805-819 capsule_capsule).
-BXD Contact contact_fn(int kind, const float4* cq, V3 pa, Q4 ra, V3 va, V3 wa, V3 pb, Q4 rb,
+BXS Contact contact_fn(int kind, const float4* cq, V3 pa, Q4 ra, V3 va, V3 wa, V3 pb, Q4 rb,
                        V3 vb, V3 wb) {
   Contact ct;
   const float4 mat = cq[CQ_MAT];
-  if (kind == BX_PAIR_CAPSULE_CAPSULE) {
+  if (BXF_IS(kind == BX_PAIR_CAPSULE_CAPSULE, BXF_CAPSULE_CAPSULE,
+             BXF_CAPSULE_PLANE | BXF_BOX_PLANE)) {
     V3 ca = pa + rotate(f3(cq[CQ_PTS + 1]), ra), ea = rotate(f3(cq[CQ_PTS]), ra);
     V3 cb = pb + rotate(f3(cq[CQ_PTS + 3]), rb), eb = rotate(f3(cq[CQ_PTS + 2]), rb);
     V3 best_a, best_b;
@@ -605,7 +610,7 @@ BXD Contact contact_fn(int kind, const float4* cq, V3 pa, Q4 ra, V3 va, V3 wa, V
   } else {
     V3 n = rotate(v3(0.f, 0.f, 1.f), rb);
     V3 off = rotate(f3(cq[CQ_PTS]), ra);
-    if (kind == BX_PAIR_CAPSULE_PLANE) {
+    if (BXF_IS(kind == BX_PAIR_CAPSULE_PLANE, BXF_CAPSULE_PLANE, BXF_BOX_PLANE)) {
       ct.pos = (pa + off) - n * mat.z;
       ct.vel = va + cross(wa, ct.pos - pa);
     } else {  // box corner: QP.to_world base.py:112-125
@@ -622,7 +627,7 @@ BXD Contact contact_fn(int kind, const float4* cq, V3 pa, Q4 ra, V3 va, V3 wa, V
 // colliders.py:198-240, OneWay :306-377, TwoWay :495-582.  Row k keeps its
 // contact in quads CT+2k = {pos, pen}, {normal, dlambda} and its deltas
 // (a: dpos, drot [, b: dpos, drot]) in quads JS+delta_off(k).
-BXD void phase_contacts_position(const Ctx& c, const BxHeader& h) {
+BXS void phase_contacts_position(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_PBD> L;
   const int co = 2 * c.cur, po = 2 * (c.cur ^ 1);
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
@@ -631,7 +636,7 @@ BXD void phase_contacts_position(const Ctx& c, const BxHeader& h) {
     const int rd = h.q_js + cs4.x, rdb = h.q_js + cs4.y;
     const float4* cq = c.tf + h.fo_contact + k * CQ_STRIDE;
     const int a = ci.z, b = ci.w;
-    const bool two_way = ci.y != 0;
+    const bool two_way = BXF_IS(ci.y != 0, BXF_TWO_WAY, BXF_ONE_WAY);
     const float4* bqa = c.tf + h.fo_body + a * BQ_STRIDE;
     const int ra0 = L::BQ * a, rb0 = L::BQ * b;
     V3 pa = ldv(c, ra0 + co), pb = ldv(c, rb0 + co);
@@ -718,7 +723,7 @@ BXD void phase_contacts_position(const Ctx& c, const BxHeader& h) {
 // non-zero linear part, divide by (eps + count), then sum over groups.
 // Each side of a row holds two quads: linear part (xyz) and a second part
 // (rot wxyz for Q deltas; ang xyz + 0 for P deltas).
-BXD void gather_contact_deltas(const Ctx& c, const BxHeader& h, int cg_off, int cg_n, float eps,
+BXS void gather_contact_deltas(const Ctx& c, const BxHeader& h, int cg_off, int cg_n, float eps,
                                float4* lin_out, float4* sec_out) {
   float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), so = lo;
   const int32_t* cg = c.ti + h.io_adj + cg_off;
@@ -742,7 +747,7 @@ BXD void gather_contact_deltas(const Ctx& c, const BxHeader& h, int cg_off, int 
 
 // ---- phase B3 (pbd): apply contact deltas, keep qp_right_before's velocities,
 // velocity projection.  system.py:299-307.
-BXD void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
+BXS void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_PBD> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
@@ -775,7 +780,7 @@ BXD void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
 // ---- phase C2 (pbd): _velocity_contact for every contact row ------------------
 // colliders.py:155-196, OneWay :379-442, TwoWay :584-658.  Deltas (a: dvel, dang
 // [, b: dvel, dang]) go to quads JS+delta_off(k).
-BXD void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
+BXS void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_PBD> L;
   const int co = 2 * c.cur;
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
@@ -784,7 +789,7 @@ BXD void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
     const int rd = h.q_js + cs4.x, rdb = h.q_js + cs4.y;
     const float4 mat = c.tf[h.fo_contact + k * CQ_STRIDE + CQ_MAT];
     const int a = ci.z, b = ci.w;
-    const bool two_way = ci.y != 0;
+    const bool two_way = BXF_IS(ci.y != 0, BXF_TWO_WAY, BXF_ONE_WAY);
     const float4* bqa = c.tf + h.fo_body + a * BQ_STRIDE;
     const int ra0 = L::BQ * a;
     const float4 c0 = QROW(c, h.q_ct + 2 * k), c1 = QROW(c, h.q_ct + 2 * k + 1);
@@ -861,7 +866,7 @@ BXD void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
 // ---- phase B4: velocity-level contact update + Info.contact -----------------
 // integrators.py:97-101; system.py:313,315 (pbd) / :365,367 (legacy_spring).
 template <int MODE>
-BXD void phase_body_velocity_update(const Ctx& c, const BxHeader& h, float eps) {
+BXS void phase_body_velocity_update(const Ctx& c, const BxHeader& h, float eps) {
   typedef Lay<MODE> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
@@ -882,13 +887,13 @@ BXD void phase_body_velocity_update(const Ctx& c, const BxHeader& h, float eps) 
 
 // ======================= legacy_spring (system.py:342-377) =====================
 // Body.impulse bodies.py:46-59
-BXD void body_impulse(float mass, V3 inv_i, V3 bpos, V3 imp, V3 at, V3* dvel, V3* dang) {
+BXS void body_impulse(float mass, V3 inv_i, V3 bpos, V3 imp, V3 at, V3* dvel, V3* dang) {
   *dvel = vdiv(imp, mass);
   *dang = inv_i * cross(at - bpos, imp);
 }
 
 // phase S1: kinetic step for every body, in place (system.py:352).
-BXD void phase_body_kinetic(const Ctx& c, const BxHeader& h) {
+BXS void phase_body_kinetic(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_LEGACY_SPRING> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
@@ -904,7 +909,7 @@ BXD void phase_body_kinetic(const Ctx& c, const BxHeader& h) {
 
 // phase S2: spring joints (spring_joints.py:89-303) -> slot quads
 // JS+na+4j: parent dvel, dang, child dvel, dang.
-BXD void phase_joints_spring(const Ctx& c, const BxHeader& h) {
+BXS void phase_joints_spring(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_LEGACY_SPRING> L;
   for (int j = c.warp; j < h.nj; j += c.nwarp) {
     const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
@@ -945,11 +950,11 @@ BXD void phase_joints_spring(const Ctx& c, const BxHeader& h) {
       dang[d] = v;
     }
     V3 tq;
-    if (kind == BX_JOINT_SPRING_REVOLUTE) {  // spring_joints.py:127-148
+    if (BXF_IS(kind == BX_JOINT_SPRING_REVOLUTE, BXF_REVOLUTE, BXF_SPHERICAL | BXF_UNIVERSAL)) {  // spring_joints.py:127-148
       V3 axis_c = rotate(f3(jq[JQ_AXIS_C]), rc);
       tq = stiffness * cross(axis[0], axis_c);
       tq = tq - (ls * axis[0]) * dang[0];
-    } else if (kind == BX_JOINT_SPRING_UNIVERSAL) {  // :178-210
+    } else if (BXF_IS(kind == BX_JOINT_SPRING_UNIVERSAL, BXF_UNIVERSAL, BXF_SPHERICAL)) {  // :178-210
       V3 proj = axis[1] - dot(axis[1], axis[0]) * axis[0];
       proj = vdiv(proj, safe_norm(proj));
       tq = (ls / 5.f) * cross(proj, axis[1]);
@@ -968,7 +973,7 @@ BXD void phase_joints_spring(const Ctx& c, const BxHeader& h) {
 
 // phase S3: acceleration update from joints + actuators + forces; Info.joint and
 // Info.actuator accumulation (system.py:356-359,367).
-BXD void phase_body_acc_spring(const Ctx& c, const BxHeader& h) {
+BXS void phase_body_acc_spring(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_LEGACY_SPRING> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
@@ -1000,7 +1005,7 @@ BXD void phase_body_acc_spring(const Ctx& c, const BxHeader& h) {
 
 // phase S4: contact_fn + velocity-level _contact (colliders.py:116-153,
 // OneWay :267-304, TwoWay :449-493).
-BXD void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
+BXS void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_LEGACY_SPRING> L;
   for (int k = c.warp; k < h.nk; k += c.nwarp) {
     const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);
@@ -1008,7 +1013,7 @@ BXD void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
     const int rd = h.q_js + cs4.x, rdb = h.q_js + cs4.y;
     const float4* cq = c.tf + h.fo_contact + k * CQ_STRIDE;
     const int a = ci.z, b = ci.w;
-    const bool two_way = ci.y != 0;
+    const bool two_way = BXF_IS(ci.y != 0, BXF_TWO_WAY, BXF_ONE_WAY);
     const float4* bqa = c.tf + h.fo_body + a * BQ_STRIDE;
     const float4* bqb = c.tf + h.fo_body + b * BQ_STRIDE;
     const int ra0 = L::BQ * a, rb0 = L::BQ * b;
@@ -1057,14 +1062,9 @@ BXD void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
 }
 
 // ============================== the kernel ====================================
-extern __shared__ __align__(16) float4 bx_smem[];
-
-// blockDim.x = 32 * W (W warps share one tile of 32 environments).  MAXT / MINB
-// are the launch bounds: the register budget is what keeps two tiles per SM
-// resident (256 threads: 128 regs, 320: 102, 384: 85).
-template <int MODE, int MAXT, int MINB>
-__global__ void __launch_bounds__(MAXT, MINB)
-bx_step_kernel(const __grid_constant__ BxKernelParams p) {
+// The whole step of one tile of 32 environments (called by bx_step_kernel below).
+template <int MODE>
+static __device__ __forceinline__ void run(const BxKernelParams& p) {
   typedef Lay<MODE> L;
   const BxHeader& h = p.h;
   float4* sq = bx_smem;
@@ -1235,4 +1235,14 @@ bx_step_kernel(const __grid_constant__ BxKernelParams p) {
         io_segment_scalar<false>(smf + (s < 2 ? cur_shift : 0), ti, h.seg_out[s], p.out[s], env0, nenv);
   }
   PT(11);
+}
+};  // struct Kern
+
+// blockDim.x = 32 * W (W warps share one tile of 32 environments).  MAXT / MINB
+// are the launch bounds: the register budget is what keeps two tiles per SM
+// resident (256 threads: 128 regs, 320: 102 regs).
+template <int MODE, int FEAT, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB)
+bx_step_kernel(const __grid_constant__ BxKernelParams p) {
+  Kern<FEAT>::template run<MODE>(p);
 }

@@ -9,11 +9,12 @@ import os
 from brax_b200 import desc as _desc
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, 'libbrax_b200.so')
+LIB_PATH = os.environ.get('BRAX_B200_LIB') or os.path.join(HERE, 'libbrax_b200.so')
 
 SYMBOLS = ('bx_system_create', 'bx_system_destroy', 'bx_system_num_contacts',
            'bx_system_num_bodies', 'bx_system_act_size', 'bx_step',
            'bx_step_host', 'bx_rollout', 'bx_system_configure',
+           'bx_system_autotune', 'bx_system_threads',
            'bx_launch_count', 'bx_last_error')
 
 _lib = None
@@ -48,6 +49,10 @@ def load():
   lib.bx_rollout.restype = C.c_int
   lib.bx_system_configure.argtypes = [P, C.c_int32, C.c_int32]
   lib.bx_system_configure.restype = C.c_int
+  lib.bx_system_autotune.argtypes = [P, C.c_int64, C.POINTER(_desc.CStepIO), P]
+  lib.bx_system_autotune.restype = C.c_int
+  lib.bx_system_threads.argtypes = [P]
+  lib.bx_system_threads.restype = C.c_int
   lib.bx_launch_count.argtypes = []
   lib.bx_launch_count.restype = C.c_int64
   lib.bx_last_error.argtypes = []

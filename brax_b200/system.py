@@ -81,6 +81,8 @@ class System:
       raise RuntimeError('bx_system_create: ' + _lib.last_error())
     self._h = handle
     self.threads_per_tile = 0  # 0 = library default
+    self._tuned = set()        # batch sizes bx_system_autotune has seen
+    self.autotune = True
 
   @classmethod
   def from_brax(cls, brax_system, name: str = 'system', act_size=None,
@@ -107,6 +109,7 @@ class System:
     if self._lib.bx_system_configure(self._h, threads_per_block, 0) != 0:
       raise ValueError(_lib.last_error())
     self.threads_per_tile = threads_per_block
+    self.autotune = False
 
   # ---- state helpers ---------------------------------------------------------
   def default_qp(self, batch: int = None, device=None) -> QP:
@@ -182,6 +185,11 @@ class System:
     for name, _, _ in _OUT:
       setattr(io, name, out[name].data_ptr() if out[name].numel() else None)
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    if self.autotune and steps == 1 and b >= 1024 and b not in self._tuned:
+      # first call at this batch size: time the candidate CTA sizes once
+      self._tuned.add(b)
+      if self._lib.bx_system_autotune(self._h, b, C.byref(io), stream) != 0:
+        raise RuntimeError('bx_system_autotune: ' + _lib.last_error())
     if steps > 1:
       rc = self._lib.bx_rollout(self._h, b, steps, C.byref(io), stream)
     else:

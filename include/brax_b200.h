@@ -204,6 +204,15 @@ int bx_rollout(bx_system* sys, int64_t num_envs, int32_t num_steps,
 int bx_system_configure(bx_system* sys, int32_t threads_per_block,
                         int32_t reserved);
 
+/* Picks the CTA size (warps per 32-env tile) by timing the candidates on the
+ * caller's own device buffers for this batch size (about 16 launches + one
+ * synchronise; outputs are overwritten, inputs untouched).  Optional: without
+ * it a cost model chooses.  Like XLA's autotuning of a jitted computation. */
+int bx_system_autotune(bx_system* sys, int64_t num_envs, const bx_step_io* io,
+                       void* stream);
+/* Threads per CTA currently configured. */
+int bx_system_threads(const bx_system* sys);
+
 /* Number of kernel launches issued through this library since load (for
  * bench.py's gpu_launches claim). */
 int64_t bx_launch_count(void);

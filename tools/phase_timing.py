@@ -13,12 +13,10 @@ sys.path.insert(0, ROOT)
 from brax_b200 import build as bb, lib as bl  # noqa: E402
 
 out = os.path.join(ROOT, 'build', 'libbrax_b200_pt.so')
-if '--build-only' in sys.argv or not os.path.exists(out):
-  os.makedirs(os.path.dirname(out), exist_ok=True)
-  subprocess.check_call(['/usr/local/cuda/bin/nvcc'] + bb.NVCC_FLAGS + ['-DBX_PHASE_TIMING',
-                        os.path.join(bb.CSRC, 'bx_api.cu'), '-o', out])
-  if '--build-only' in sys.argv:
-    sys.exit(0)
+os.makedirs(os.path.dirname(out), exist_ok=True)
+bb.build(extra=['-DBX_PHASE_TIMING'], out=out, force='--build-only' in sys.argv)
+if '--build-only' in sys.argv:
+  sys.exit(0)
 bl.LIB_PATH = out
 from brax_b200.system import load_system  # noqa: E402
 
