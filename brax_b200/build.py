@@ -33,7 +33,8 @@ def build(force: bool = False, verbose: bool = False, extra=(), out: str = None)
   if not (force or stale(out)):
     return out
   nvcc = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
-  objdir = os.path.join(HERE, 'csrc', '_obj' + ('' if out == LIB else '_' + os.path.basename(out)))
+  import tempfile
+  objdir = os.path.join(tempfile.gettempdir(), 'brax_b200_obj_' + os.path.basename(out))
   os.makedirs(objdir, exist_ok=True)
   common = [nvcc] + NVCC_FLAGS + list(extra) + (['-Xptxas', '-v'] if verbose else [])
   jobs = [(common + ['-c', os.path.join(CSRC, 'bx_api.cu'), '-o', os.path.join(objdir, 'bx_api.o')])]
