@@ -237,20 +237,27 @@ def run_gpu(args, desc):
   finite = bool(torch.isfinite(qp.pos).all().item())
 
   # ---- e2e: host buffers through System.step (bx_step_host) ----------------
-  hq = [torch.from_numpy(x).pin_memory() for x in (pos, rot, vel, ang)]
-  hact = acts[args.warmup:].cpu().pin_memory()
-  hqp = QP(*[t.numpy() for t in hq])
-  e2e_steps = 1 if args.no_e2e else max(3, min(args.steps, 20))
-  for i in range(2):
-    hqp, hinfo = s.step(hqp, hact[i % hact.shape[0]].numpy())
+  # Inputs start in page-locked host memory, every step uploads QP + act, steps,
+  # and downloads QP + Info into page-locked host memory (two HostBuffers sets
+  # ping-pong so a step's outputs are the next step's inputs, like a host-side
+  # rollout loop of the reference's numpy path).
+  hb = [s.host_buffers(b), s.host_buffers(b)]
+  for dst, src in zip((hb[0].out['pos_o'], hb[0].out['rot_o'], hb[0].out['vel_o'], hb[0].out['ang_o']),
+                      (pos, rot, vel, ang)):
+    dst[...] = src
+  hact = acts[args.warmup:].cpu().pin_memory().numpy()
+  hqp = QP(hb[0].out['pos_o'], hb[0].out['rot_o'], hb[0].out['vel_o'], hb[0].out['ang_o'])
+  e2e_steps = 1 if args.no_e2e else max(3, min(args.steps, 50))
+  for i in range(3):
+    hqp, hinfo = s.step(hqp, hact[i % hact.shape[0]], out=hb[(i + 1) % 2])
   barrier()
   t0 = time.perf_counter()
   for i in range(e2e_steps):
-    hqp, hinfo = s.step(hqp, hact[i % hact.shape[0]].numpy())
+    hqp, hinfo = s.step(hqp, hact[i % hact.shape[0]], out=hb[i % 2])
   barrier()
   t_e2e = time.perf_counter() - t0
-  h2d = 4 * b * (13 * n + a)
-  d2h = 4 * b * (13 * n + 18 * n + 7 * k)
+  e2e_finite = bool(np.isfinite(hqp.pos).all())
+  h2d, d2h = s.host_transfer_bytes(b)
 
   # ---- max over ranks -----------------------------------------------------------
   from brax_b200 import shard
@@ -279,7 +286,8 @@ def run_gpu(args, desc):
         'value_back_to_back': value_b2b,
         'wall_s_timed_loop_incl_flush': t_wall,
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d,
-                'd2h_bytes_per_step': d2h, 'steps': e2e_steps},
+                'd2h_bytes_per_step': d2h, 'steps': e2e_steps, 'finite': e2e_finite,
+                'path': 'System.step(numpy QP, out=HostBuffers) -> bx_step_host: chunked H2D/step/D2H pipeline on 3 streams, page-locked buffers'},
         'gpu_launches': int(launches),
         'clocks': clocks, 'finite': finite,
     }

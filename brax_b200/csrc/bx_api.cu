@@ -19,6 +19,8 @@
 #include "bx_params.h"
 #include "bx_tables.h"
 
+#define BX_HOST_STREAMS 3
+
 struct bx_system {
   BxHeader h;
   int device;
@@ -31,6 +33,7 @@ struct bx_system {
   // scratch for bx_step_host / bx_rollout
   float* d_scratch;
   size_t scratch_floats;
+  cudaStream_t streams[BX_HOST_STREAMS];
 };
 
 static thread_local std::string g_err;
@@ -472,6 +475,7 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   s->sm_count = prop.multiProcessorCount;
   s->d_scratch = nullptr;
   s->scratch_floats = 0;
+  for (int i = 0; i < BX_HOST_STREAMS; i++) s->streams[i] = nullptr;
   s->smem_bytes = (static_cast<size_t>(s->h.n_quads) * BX_QSTRIDE + s->h.n_fquads) * 16 +
                   static_cast<size_t>(s->h.n_ints) * 4 + 16 /* mbarrier */;
   if (s->smem_bytes > static_cast<size_t>(prop.sharedMemPerBlockOptin)) {
@@ -516,6 +520,8 @@ extern "C" void bx_system_destroy(bx_system* s) {
   cudaFree(s->d_tab_i);
   cudaFree(s->d_tab_f);
   cudaFree(s->d_scratch);
+  for (int i = 0; i < BX_HOST_STREAMS; i++)
+    if (s->streams[i]) cudaStreamDestroy(s->streams[i]);
   delete s;
 }
 
@@ -608,9 +614,63 @@ extern "C" int bx_system_threads(const bx_system* s) { return s ? 32 * s->warps 
 extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
   if (!s || !hio) return fail("NULL argument");
   if (B <= 0) return fail("num_envs must be positive");
+  if (!hio->pos || !hio->rot || !hio->vel || !hio->ang || !hio->act || !hio->pos_o || !hio->rot_o ||
+      !hio->vel_o || !hio->ang_o)
+    return fail("QP / act pointers must not be NULL");
   CUDA_OK(cudaSetDevice(s->device));
   const int64_t n = s->h.nb, a = s->h.act_size, k = s->h.nk;
   // in: 13n + a ; out: 13n + 18n + 7k   (floats per env)
+  for (int i = 0; i < BX_HOST_STREAMS; i++)
+    if (!s->streams[i]) CUDA_OK(cudaStreamCreateWithFlags(&s->streams[i], cudaStreamNonBlocking));
+  {
+    // Zero-copy path: when every buffer is page-locked (bx_host_alloc,
+    // cudaHostRegister, torch pin_memory) the kernel works on the host memory
+    // directly -- each tile pulls its input spans over PCIe with bulk async copies
+    // and pushes its outputs with coalesced 128-bit stores, so upload, compute and
+    // download of different tiles overlap inside ONE launch.
+    const float* hin[BX_SEG_IN] = {hio->pos, hio->rot, hio->vel, hio->ang, hio->act};
+    float* hout[BX_SEG_OUT] = {hio->pos_o, hio->rot_o, hio->vel_o, hio->ang_o, hio->contact_vel,
+                               hio->contact_ang, hio->joint_vel, hio->joint_ang, hio->actuator_vel,
+                               hio->actuator_ang, hio->contact_pos, hio->contact_normal,
+                               hio->contact_penetration};
+    const void* din[BX_SEG_IN];
+    void* dout[BX_SEG_OUT];
+    bool pinned = true;
+    auto dev_ptr = [&](const void* hp, const void** dp) {
+      cudaPointerAttributes at;
+      if (cudaPointerGetAttributes(&at, hp) != cudaSuccess) { cudaGetLastError(); return false; }
+      if (at.type != cudaMemoryTypeHost || at.devicePointer == nullptr) return false;
+      *dp = at.devicePointer;
+      return true;
+    };
+    for (int i = 0; i < BX_SEG_IN && pinned; i++) pinned = dev_ptr(hin[i], &din[i]);
+    for (int i = 0; i < BX_SEG_OUT && pinned; i++) {
+      dout[i] = nullptr;
+      const bool constant = i >= 4 && s->h.seg_out[i].map < 0;
+      if (hout[i] && s->h.seg_out[i].nper > 0 && !constant)
+        pinned = dev_ptr(hout[i], const_cast<const void**>(&dout[i]));
+    }
+    if (pinned) {
+      bx_step_io d;
+      memset(&d, 0, sizeof(d));
+      d.pos = (const float*)din[0]; d.rot = (const float*)din[1]; d.vel = (const float*)din[2];
+      d.ang = (const float*)din[3]; d.act = (const float*)din[4];
+      float** dp[BX_SEG_OUT] = {&d.pos_o, &d.rot_o, &d.vel_o, &d.ang_o, &d.contact_vel, &d.contact_ang,
+                                &d.joint_vel, &d.joint_ang, &d.actuator_vel, &d.actuator_ang,
+                                &d.contact_pos, &d.contact_normal, &d.contact_penetration};
+      for (int i = 0; i < BX_SEG_OUT; i++) *dp[i] = static_cast<float*>(dout[i]);
+      cudaStream_t st = s->streams[0];
+      if (launch(s, B, 1, &d, st)) return 1;
+      for (int i = 4; i < BX_SEG_OUT; i++)
+        if (hout[i] && s->h.seg_out[i].nper > 0 && s->h.seg_out[i].map < 0) {
+          const float f = s->h.seg_out[i].fill;
+          const size_t cnt = static_cast<size_t>(s->h.seg_out[i].nper) * B;
+          if (f == 0.f) memset(hout[i], 0, cnt * 4); else std::fill(hout[i], hout[i] + cnt, f);
+        }
+      CUDA_OK(cudaStreamSynchronize(st));
+      return 0;
+    }
+  }
   const size_t per_env = static_cast<size_t>(13 * n + a + 13 * n + 18 * n + 7 * k);
   const size_t need = per_env * B;
   if (need > s->scratch_floats) {
@@ -622,33 +682,83 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
   }
   float* cur = s->d_scratch;
   auto take = [&](size_t per) { float* r = cur; cur += per * B; return r; };
-  bx_step_io d;
-  float* d_pos = take(3 * n); float* d_rot = take(4 * n);
-  float* d_vel = take(3 * n); float* d_ang = take(3 * n); float* d_act = take(a);
-  d.pos = d_pos; d.rot = d_rot; d.vel = d_vel; d.ang = d_ang; d.act = d_act;
-  d.pos_o = take(3 * n); d.rot_o = take(4 * n); d.vel_o = take(3 * n); d.ang_o = take(3 * n);
-  d.contact_vel = take(3 * n); d.contact_ang = take(3 * n);
-  d.joint_vel = take(3 * n); d.joint_ang = take(3 * n);
-  d.actuator_vel = take(3 * n); d.actuator_ang = take(3 * n);
-  d.contact_pos = take(3 * k); d.contact_normal = take(3 * k); d.contact_penetration = take(k);
-  cudaStream_t st = 0;
-  CUDA_OK(cudaMemcpyAsync(d_pos, hio->pos, 3 * n * B * 4, cudaMemcpyHostToDevice, st));
-  CUDA_OK(cudaMemcpyAsync(d_rot, hio->rot, 4 * n * B * 4, cudaMemcpyHostToDevice, st));
-  CUDA_OK(cudaMemcpyAsync(d_vel, hio->vel, 3 * n * B * 4, cudaMemcpyHostToDevice, st));
-  CUDA_OK(cudaMemcpyAsync(d_ang, hio->ang, 3 * n * B * 4, cudaMemcpyHostToDevice, st));
-  CUDA_OK(cudaMemcpyAsync(d_act, hio->act, a * B * 4, cudaMemcpyHostToDevice, st));
-  if (launch(s, B, 1, &d, st)) return 1;
-  struct Out { float* h; const float* dv; size_t per; };
-  const Out outs[] = {
-      {hio->pos_o, d.pos_o, (size_t)3 * n}, {hio->rot_o, d.rot_o, (size_t)4 * n},
-      {hio->vel_o, d.vel_o, (size_t)3 * n}, {hio->ang_o, d.ang_o, (size_t)3 * n},
-      {hio->contact_vel, d.contact_vel, (size_t)3 * n}, {hio->contact_ang, d.contact_ang, (size_t)3 * n},
-      {hio->joint_vel, d.joint_vel, (size_t)3 * n}, {hio->joint_ang, d.joint_ang, (size_t)3 * n},
-      {hio->actuator_vel, d.actuator_vel, (size_t)3 * n}, {hio->actuator_ang, d.actuator_ang, (size_t)3 * n},
-      {hio->contact_pos, d.contact_pos, (size_t)3 * k}, {hio->contact_normal, d.contact_normal, (size_t)3 * k},
-      {hio->contact_penetration, d.contact_penetration, (size_t)k}};
-  for (const Out& o : outs)
-    if (o.h && o.per) CUDA_OK(cudaMemcpyAsync(o.h, o.dv, o.per * B * 4, cudaMemcpyDeviceToHost, st));
-  CUDA_OK(cudaStreamSynchronize(st));
+  // device arrays, in the order of the kernel's segments
+  const size_t in_per[BX_SEG_IN] = {(size_t)3 * n, (size_t)4 * n, (size_t)3 * n, (size_t)3 * n, (size_t)a};
+  const float* h_in[BX_SEG_IN] = {hio->pos, hio->rot, hio->vel, hio->ang, hio->act};
+  float* d_in[BX_SEG_IN];
+  for (int i = 0; i < BX_SEG_IN; i++) d_in[i] = take(in_per[i]);
+  const size_t out_per[BX_SEG_OUT] = {(size_t)3 * n, (size_t)4 * n, (size_t)3 * n, (size_t)3 * n,
+                                      (size_t)3 * n, (size_t)3 * n, (size_t)3 * n, (size_t)3 * n,
+                                      (size_t)3 * n, (size_t)3 * n, (size_t)3 * k, (size_t)3 * k, (size_t)k};
+  float* h_out[BX_SEG_OUT] = {hio->pos_o, hio->rot_o, hio->vel_o, hio->ang_o, hio->contact_vel,
+                              hio->contact_ang, hio->joint_vel, hio->joint_ang, hio->actuator_vel,
+                              hio->actuator_ang, hio->contact_pos, hio->contact_normal,
+                              hio->contact_penetration};
+  float* d_out[BX_SEG_OUT];
+  for (int i = 0; i < BX_SEG_OUT; i++) d_out[i] = take(out_per[i]);
+  // Pipeline: the batch is cut into chunks (multiples of the 32-env tile); chunk
+  // c's H2D, kernel and D2H run on stream c % 3, so the upload of one chunk, the
+  // step of another and the download of a third overlap (PCIe is full duplex).
+  // Outputs that are constants of the dynamics mode (info.joint / info.actuator.vel
+  // in pbd) are not transferred: the host fills them while the GPU works.
+  int64_t chunk = ((B + 3) / 4 + 31) / 32 * 32;
+  if (chunk < 1024) chunk = std::min<int64_t>(B, 1024);
+  int ci = 0;
+  for (int64_t e0 = 0; e0 < B; e0 += chunk, ci++) {
+    const int64_t nb_ = std::min<int64_t>(chunk, B - e0);
+    cudaStream_t st = s->streams[ci % BX_HOST_STREAMS];
+    bx_step_io d;
+    memset(&d, 0, sizeof(d));
+    for (int i = 0; i < BX_SEG_IN; i++)
+      CUDA_OK(cudaMemcpyAsync(d_in[i] + e0 * in_per[i], h_in[i] + e0 * in_per[i], in_per[i] * nb_ * 4,
+                              cudaMemcpyHostToDevice, st));
+    d.pos = d_in[0] + e0 * in_per[0]; d.rot = d_in[1] + e0 * in_per[1];
+    d.vel = d_in[2] + e0 * in_per[2]; d.ang = d_in[3] + e0 * in_per[3];
+    d.act = d_in[4] + e0 * in_per[4];
+    float** dp[BX_SEG_OUT] = {&d.pos_o, &d.rot_o, &d.vel_o, &d.ang_o, &d.contact_vel, &d.contact_ang,
+                              &d.joint_vel, &d.joint_ang, &d.actuator_vel, &d.actuator_ang,
+                              &d.contact_pos, &d.contact_normal, &d.contact_penetration};
+    for (int i = 0; i < BX_SEG_OUT; i++) {
+      const bool constant = s->h.seg_out[i].map < 0;
+      *dp[i] = (i < 4 || (h_out[i] && out_per[i] && !constant)) ? d_out[i] + e0 * out_per[i] : nullptr;
+    }
+    if (launch(s, nb_, 1, &d, st)) return 1;
+    for (int i = 0; i < BX_SEG_OUT; i++)
+      if (*dp[i] && h_out[i])
+        CUDA_OK(cudaMemcpyAsync(h_out[i] + e0 * out_per[i], *dp[i], out_per[i] * nb_ * 4,
+                                cudaMemcpyDeviceToHost, st));
+  }
+  for (int i = 4; i < BX_SEG_OUT; i++)
+    if (h_out[i] && out_per[i] && s->h.seg_out[i].map < 0) {
+      const float f = s->h.seg_out[i].fill;
+      if (f == 0.f) memset(h_out[i], 0, out_per[i] * B * 4);
+      else std::fill(h_out[i], h_out[i] + out_per[i] * B, f);
+    }
+  for (int i = 0; i < BX_HOST_STREAMS; i++) CUDA_OK(cudaStreamSynchronize(s->streams[i]));
   return 0;
 }
+
+// Bytes bx_step_host moves over PCIe for `num_envs` environments (constant
+// outputs are filled on the host and not counted).
+extern "C" int bx_host_transfer_bytes(const bx_system* s, int64_t B, int64_t* h2d, int64_t* d2h) {
+  if (!s) return fail("NULL argument");
+  const int64_t n = s->h.nb, a = s->h.act_size;
+  if (h2d) *h2d = 4 * B * (13 * n + a);
+  int64_t o = 0;
+  for (int i = 0; i < BX_SEG_OUT; i++)
+    if (i < 4 || s->h.seg_out[i].map >= 0) o += s->h.seg_out[i].nper;
+  if (d2h) *d2h = 4 * B * o;
+  return 0;
+}
+
+// Page-locked host memory for bx_step_host buffers (pageable memory works too,
+// at a fraction of the PCIe rate).
+extern "C" void* bx_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+    fail("cudaHostAlloc failed");
+    return nullptr;
+  }
+  return p;
+}
+extern "C" void bx_host_free(void* p) { if (p) cudaFreeHost(p); }

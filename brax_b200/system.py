@@ -59,6 +59,48 @@ _OUT = (('pos_o', 3, 'n'), ('rot_o', 4, 'n'), ('vel_o', 3, 'n'),
         ('contact_normal', 3, 'k'), ('contact_penetration', 0, 'k'))
 
 
+class HostBuffers:
+  """Page-locked host arrays for the host path of `System.step` (bx_host_alloc).
+
+  `out` holds one array per output of the step; `qp()` / `act` are optional
+  pinned input arrays a caller can fill in place.  Passing `out=bufs` to
+  `System.step` writes the results into these arrays (they are overwritten by
+  the next call that uses the same HostBuffers)."""
+
+  def __init__(self, system: 'System', batch: int):
+    self._lib = system._lib
+    self._ptrs = []
+    n, k, a = system.num_bodies, system.num_contacts, system.act_size
+
+    def arr(shape):
+      count = int(np.prod(shape))
+      p = self._lib.bx_host_alloc(max(count, 1) * 4)
+      if not p:
+        raise MemoryError('bx_host_alloc: ' + _lib.last_error())
+      self._ptrs.append(p)
+      return np.ctypeslib.as_array((C.c_float * max(count, 1)).from_address(p))[:count].reshape(shape)
+
+    self.out = {}
+    for name, w, dim in _OUT:
+      m = n if dim == 'n' else k
+      self.out[name] = arr((batch, m, w) if w else (batch, m))
+    self.pos, self.rot = arr((batch, n, 3)), arr((batch, n, 4))
+    self.vel, self.ang = arr((batch, n, 3)), arr((batch, n, 3))
+    self.act = arr((batch, a))
+    self.batch = batch
+
+  def qp(self) -> 'QP':
+    return QP(self.pos, self.rot, self.vel, self.ang)
+
+  def __del__(self):
+    for p in getattr(self, '_ptrs', []):
+      try:
+        self._lib.bx_host_free(p)
+      except Exception:
+        pass
+    self._ptrs = []
+
+
 def _is_torch(x) -> bool:
   return type(x).__module__.startswith('torch')
 
@@ -124,11 +166,24 @@ class System:
     return QP(*arrs)
 
   # ---- the step ---------------------------------------------------------------
-  def step(self, qp: QP, act) -> Tuple[QP, Info]:
-    """`System.step(qp, act) -> (qp, info)` (system.py:244-247)."""
+  def step(self, qp: QP, act, out: 'HostBuffers' = None) -> Tuple[QP, Info]:
+    """`System.step(qp, act) -> (qp, info)` (system.py:244-247).
+
+    out: optional `HostBuffers` (host path only): results are written into its
+    page-locked arrays instead of freshly allocated pageable ones."""
     if _is_torch(qp.pos):
       return self._step_torch(qp, act, 1)
-    return self._step_numpy(qp, act)
+    return self._step_numpy(qp, act, out)
+
+  def host_buffers(self, batch: int) -> HostBuffers:
+    """Page-locked arrays for `step(..., out=...)` at this batch size."""
+    return HostBuffers(self, batch)
+
+  def host_transfer_bytes(self, batch: int):
+    """(h2d, d2h) bytes one host-path step moves over PCIe."""
+    h2d, d2h = C.c_int64(), C.c_int64()
+    self._lib.bx_host_transfer_bytes(self._h, batch, C.byref(h2d), C.byref(d2h))
+    return int(h2d.value), int(d2h.value)
 
   def rollout(self, qp: QP, acts) -> Tuple[QP, Info]:
     """T steps in ONE launch; acts is [T, B, A] (torch CUDA).  Returns the final
@@ -198,7 +253,7 @@ class System:
       raise RuntimeError('bx_step: ' + _lib.last_error())
     return self._wrap(out, batched)
 
-  def _step_numpy(self, qp: QP, act):
+  def _step_numpy(self, qp: QP, act, bufs: 'HostBuffers' = None):
     batched, b = self._shapes(np.shape(qp.pos))
     n, k, a = self.num_bodies, self.num_contacts, self.act_size
 
@@ -207,10 +262,15 @@ class System:
 
     ins = [prep(qp.pos, (b, n, 3)), prep(qp.rot, (b, n, 4)), prep(qp.vel, (b, n, 3)),
            prep(qp.ang, (b, n, 3)), prep(act, (b, a))]
-    out = {}
-    for name, w, dim in _OUT:
-      m = n if dim == 'n' else k
-      out[name] = np.empty((b, m, w) if w else (b, m), dtype=np.float32)
+    if bufs is not None:
+      if bufs.batch != b:
+        raise ValueError('HostBuffers are for batch %d, step has %d' % (bufs.batch, b))
+      out = dict(bufs.out)
+    else:
+      out = {}
+      for name, w, dim in _OUT:
+        m = n if dim == 'n' else k
+        out[name] = np.empty((b, m, w) if w else (b, m), dtype=np.float32)
     io = CStepIO()
     for f, t in zip(('pos', 'rot', 'vel', 'ang', 'act'), ins):
       setattr(io, f, t.ctypes.data)

@@ -24,6 +24,7 @@
 #ifndef BRAX_B200_H_
 #define BRAX_B200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -189,9 +190,18 @@ int bx_step(const bx_system* sys, int64_t num_envs, const bx_step_io* io,
             void* stream);
 
 /* The same step with HOST buffers (pageable or pinned): copies in, launches,
- * copies out, synchronises.  This is the call a numpy/ctypes binding of
+ * copies out, synchronises; the batch is pipelined in chunks over three streams
+ * so upload, step and download overlap.  This is the call a numpy/ctypes binding of
  * System.step makes and what bench.py's e2e number times. */
 int bx_step_host(bx_system* sys, int64_t num_envs, const bx_step_io* host_io);
+
+/* PCIe bytes one bx_step_host call moves (outputs that are constants of the
+ * dynamics mode are filled on the host, not transferred). */
+int bx_host_transfer_bytes(const bx_system* sys, int64_t num_envs, int64_t* h2d,
+                           int64_t* d2h);
+/* Page-locked host memory for bx_step_host buffers (pageable works, slower). */
+void* bx_host_alloc(size_t bytes);
+void bx_host_free(void* p);
 
 /* T consecutive steps in one call: act is [T,B,A]; state ping-pongs inside
  * device scratch; Info of the LAST step is written.  Mirrors

@@ -352,3 +352,34 @@ def test_errors_are_loud():
   with pytest.raises(RuntimeError):
     s.step(QP(*[torch.from_numpy(x) for x in (q.pos, q.rot, q.vel, q.ang)]),
            torch.zeros(4, 8))  # CPU torch tensors: no CPU fallback
+
+
+def test_host_path_pinned_buffers_and_chunking():
+  """bx_step_host (chunked 3-stream pipeline, page-locked HostBuffers, constant
+  outputs filled on the host) is bit-identical to the device path."""
+  torch = _torch()
+  from brax_b200.system import QP
+  for name, b in (('ant', 5000), ('humanoid_spring', 1500)):
+    s = _system(name)
+    qp, rng = _harvest(s, b, 4, 17)
+    act = rng.uniform(-1, 1, (b, s.act_size)).astype(np.float32)
+    dev = _flat(*s.step(qp, torch.from_numpy(act).cuda()))
+    hb = s.host_buffers(b)
+    for k in util.QP_KEYS:
+      getattr(hb, k)[...] = getattr(qp, k).cpu().numpy()
+    hb.act[...] = act
+    for v in hb.out.values():
+      v.fill(np.nan)
+    host = _flat(*s.step(hb.qp(), hb.act, out=hb))  # page-locked: zero-copy launch
+    for k in dev:
+      np.testing.assert_array_equal(dev[k], host[k], err_msg='%s %s' % (name, k))
+    pageable = QP(*[np.array(getattr(hb, k)) for k in util.QP_KEYS])
+    host2 = _flat(*s.step(pageable, np.array(hb.act)))  # pageable: chunked copy pipeline
+    for k in dev:
+      np.testing.assert_array_equal(dev[k], host2[k], err_msg='%s %s pageable' % (name, k))
+    h2d, d2h = s.host_transfer_bytes(b)
+    n, a, kk = s.num_bodies, s.act_size, s.num_contacts
+    assert h2d == 4 * b * (13 * n + a)
+    assert d2h <= 4 * b * (31 * n + 7 * kk)
+    if s.desc.dynamics_mode == 'pbd':  # info.joint (2 x 3N) + info.actuator.vel (3N) stay on the host
+      assert d2h == 4 * b * (31 * n + 7 * kk - 9 * n)
