@@ -38,7 +38,7 @@ UNIT = 'env-steps/s'
 SM_COUNT = 148
 # dram__bytes_read.sum + dram__bytes_write.sum of one bx_step_kernel launch at the
 # bench workload, from the committed `ncu --set full` capture (profiles/); bytes.
-NCU_TRAFFIC = {'ant': 4664576}
+NCU_TRAFFIC = {'ant': 4603904}
 FP32_LANES = 128
 
 
