@@ -190,8 +190,8 @@ def run_gpu(args, desc):
   torch.cuda.set_device(local)
   dev = torch.device('cuda', local)
   s = System(desc, device=local)
-  if args.threads:
-    s.configure(args.threads)
+  if args.threads or args.contact_section:
+    s.configure(args.threads, args.contact_section)
   b, a, n, k = args.envs, desc.act_size, desc.num_bodies, desc.num_contacts
   pos, rot, vel, ang = make_state(desc, b, 100 + rank)
   qp = QP(*[torch.from_numpy(x).to(dev) for x in (pos, rot, vel, ang)])
@@ -331,6 +331,8 @@ def main():
   ap.add_argument('--env', default='ant')
   ap.add_argument('--envs', type=int, default=8192, help='environments per GPU')
   ap.add_argument('--threads', type=int, default=0, help='threads per 32-env tile (0 = default)')
+  ap.add_argument('--contact-section', type=int, default=0,
+                  help='0 = default, 1 = four contact phases, 2 = fused per-body section')
   ap.add_argument('--cpu-seconds', type=float, default=12.0)
   ap.add_argument('--no-cpu', action='store_true')
   ap.add_argument('--no-e2e', action='store_true')

@@ -12,7 +12,7 @@ LIB = os.path.join(HERE, 'libbrax_b200.so')
 DEPS = ['bx_api.cu', 'bx_kernels.cu', 'bx_step_kernel.cuh', 'bx_params.h', 'bx_math.cuh', 'bx_tables.h',
         os.path.join('..', '..', 'include', 'brax_b200.h')]
 # (launch bound threads, min blocks per SM): one kernel translation unit each
-BOUNDS = [(256, 2), (320, 2), (512, 1)]
+BOUNDS = [(256, 2), (320, 2), (384, 2), (512, 1)]
 
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3',
               '-std=c++17', '-Xcompiler', '-fPIC']

@@ -29,6 +29,7 @@ struct bx_system {
   size_t smem_bytes;
   int warps;  // warps per CTA (W)
   int jc, cc; // joint / contact class of the kernel variant (bx_params.h)
+  bool fusable;  // the fused contact section is legal for this system
   int sm_count;
   // scratch for bx_step_host / bx_rollout
   float* d_scratch;
@@ -306,7 +307,15 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
     rec[BI_CG_OFF] = static_cast<int>(adj.size());
     adj.insert(adj.end(), cgroups[b].begin(), cgroups[b].end());
     rec[BI_CG_N] = static_cast<int>(cgroups[b].size() / 2);
+    rec[BI_ROW_OFF] = static_cast<int>(adj.size());
+    for (int k = 0; k < nk; k++)
+      if (d->pairs[rows[k].pair].body_a == b) adj.push_back(k);
+    rec[BI_ROW_N] = static_cast<int>(adj.size()) - rec[BI_ROW_OFF];
   }
+  std::vector<int32_t> forder;
+  for (int pass = 0; pass < 2; pass++)
+    for (int b = 0; b < nb; b++)
+      if ((body_rec[b * BI_STRIDE + BI_ROW_N] > 0) == (pass == 0)) forder.push_back(b);
   h.io_body = static_cast<int>(ti.size());
   ti.insert(ti.end(), body_rec.begin(), body_rec.end());
   align4();
@@ -342,6 +351,8 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   }
   h.io_adj = static_cast<int>(ti.size());
   ti.insert(ti.end(), adj.begin(), adj.end());
+  h.io_forder = static_cast<int>(ti.size());
+  ti.insert(ti.end(), forder.begin(), forder.end());
 
   // ---- I/O segments: element r of an env -> shared float index of (quad row, comp)
   const int RF = BX_QSTRIDE * 4;  // floats per quad row
@@ -432,11 +443,16 @@ static cudaError_t launch_variant(int mode, int jc, int cc, unsigned grid, int t
                                   cudaStream_t stream, const BxKernelParams& p) {
   if (threads <= 256) return bx_launch_256(mode, jc, cc, grid, threads, smem, stream, p);
   if (threads <= 320) return bx_launch_320(mode, jc, cc, grid, threads, smem, stream, p);
+  // 12 warps with two tiles per SM (80 registers) only pays when two tiles fit in
+  // shared memory; otherwise the one-tile-per-SM build with more registers is used
+  if (threads <= 384 && 2 * (smem + 1024) <= 233472)
+    return bx_launch_384(mode, jc, cc, grid, threads, smem, stream, p);
   return bx_launch_512(mode, jc, cc, grid, threads, smem, stream, p);
 }
 static int set_smem_attr(int bytes) {
   CUDA_OK(bx_set_smem_256(bytes));
   CUDA_OK(bx_set_smem_320(bytes));
+  CUDA_OK(bx_set_smem_384(bytes));
   CUDA_OK(bx_set_smem_512(bytes));
   return 0;
 }
@@ -467,9 +483,25 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
       if (k != BX_JOINT_SPHERICAL) sph_only = false;
     }
     s->jc = !other ? BX_JC_REVOLUTE : ((sph_only && !rev) ? BX_JC_SPHERICAL : BX_JC_ALL);
-    s->cc = BX_CC_PLANE;
+    // fused contact section: pbd, one-way plane colliders only, <= 2 rows per body
+    std::vector<int> rows_of(desc->num_bodies, 0);
+    int max_rows = 0;
     for (int i = 0; i < desc->num_pairs; i++)
-      if (desc->pairs[i].two_way || desc->pairs[i].kind == BX_PAIR_CAPSULE_CAPSULE) s->cc = BX_CC_ALL;
+      max_rows = std::max(max_rows, rows_of[desc->pairs[i].body_a] += desc->pairs[i].n_contacts);
+    int contact_bodies = 0;
+    s->cc = BX_CC_PLANE;
+    for (int b = 0; b < desc->num_bodies; b++) contact_bodies += rows_of[b] > 0;
+    s->fusable = desc->dynamics_mode == BX_MODE_PBD && max_rows <= 2;
+    for (int i = 0; i < desc->num_pairs; i++)
+      if (desc->pairs[i].two_way || desc->pairs[i].kind == BX_PAIR_CAPSULE_CAPSULE) {
+        s->cc = BX_CC_ALL;
+        s->fusable = false;
+      }
+    // Measured (profiles/r01_sweeps.txt): the fused section wins when the chains
+    // leave warps free (ant: 4 of 10 bodies collide, +2.5%) and loses when nearly
+    // every body carries one (humanoid, -1%); bx_system_autotune times both.
+    if (s->cc != BX_CC_ALL)
+      s->cc = (s->fusable && 2 * contact_bodies <= desc->num_bodies) ? BX_CC_PLANE_FUSED : BX_CC_PLANE;
   }
   s->device = device;
   s->sm_count = prop.multiProcessorCount;
@@ -529,12 +561,17 @@ extern "C" int bx_system_num_contacts(const bx_system* s) { return s ? s->h.nk :
 extern "C" int bx_system_num_bodies(const bx_system* s) { return s ? s->h.nb : -1; }
 extern "C" int bx_system_act_size(const bx_system* s) { return s ? s->h.act_size : -1; }
 
-extern "C" int bx_system_configure(bx_system* s, int32_t threads_per_block, int32_t reserved) {
-  (void)reserved;
+extern "C" int bx_system_configure(bx_system* s, int32_t threads_per_block, int32_t contact_section) {
   if (!s) return fail("system is NULL");
-  if (threads_per_block < 32 || threads_per_block > 512 || (threads_per_block & 31))
-    return fail("threads_per_block must be a multiple of 32 in [32, 512]");
-  s->warps = threads_per_block / 32;
+  if (threads_per_block != 0 &&
+      (threads_per_block < 32 || threads_per_block > 512 || (threads_per_block & 31)))
+    return fail("threads_per_block must be 0 or a multiple of 32 in [32, 512]");
+  if (contact_section < 0 || contact_section > 2) return fail("contact_section must be 0, 1 or 2");
+  if (contact_section == 2 && !s->fusable)
+    return fail("fused contact section needs pbd, one-way plane colliders, <= 2 rows per body");
+  if (threads_per_block) s->warps = threads_per_block / 32;
+  if (contact_section && s->cc != BX_CC_ALL)
+    s->cc = contact_section == 2 ? BX_CC_PLANE_FUSED : BX_CC_PLANE;
   return 0;
 }
 
@@ -587,21 +624,37 @@ extern "C" int bx_system_autotune(bx_system* s, int64_t num_envs, const bx_step_
   CUDA_OK(cudaEventCreate(&e0));
   CUDA_OK(cudaEventCreate(&e1));
   const int cand[4] = {8, 10, 12, 16};
-  const int keep = s->warps;
+  const int keep = s->warps, keep_cc = s->cc;
   float best = 1e30f;
-  int best_w = keep;
-  for (int i = 0; i < 4; i++) {
-    s->warps = cand[i];
-    if (launch(s, num_envs, 1, io, st)) { s->warps = keep; return 1; }  // warm-up
-    CUDA_OK(cudaEventRecord(e0, st));
-    for (int r = 0; r < 3; r++)
-      if (launch(s, num_envs, 1, io, st)) { s->warps = keep; return 1; }
-    CUDA_OK(cudaEventRecord(e1, st));
-    CUDA_OK(cudaEventSynchronize(e1));
-    float ms = 0.f;
-    CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
-    if (ms < best) { best = ms; best_w = cand[i]; }
-  }
+  int best_w = keep, best_cc = keep_cc;
+  // two interleaved passes over all candidates, 8 timed launches each, best pass
+  // per candidate: a single noisy sample must not decide
+  const int nf = s->fusable ? 2 : 1;
+  float t[2][4] = {{1e30f, 1e30f, 1e30f, 1e30f}, {1e30f, 1e30f, 1e30f, 1e30f}};
+  for (int pass = 0; pass < 2; pass++)
+    for (int f = 0; f < nf; f++) {
+      if (s->fusable) s->cc = f ? BX_CC_PLANE_FUSED : BX_CC_PLANE;
+      for (int i = 0; i < 4; i++) {
+        s->warps = cand[i];
+        bool bad = launch(s, num_envs, 1, io, st) != 0;  // warm-up
+        if (!bad) CUDA_OK(cudaEventRecord(e0, st));
+        for (int r = 0; r < 8 && !bad; r++) bad = launch(s, num_envs, 1, io, st) != 0;
+        if (bad) { s->warps = keep; s->cc = keep_cc; return 1; }
+        CUDA_OK(cudaEventRecord(e1, st));
+        CUDA_OK(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CUDA_OK(cudaEventElapsedTime(&ms, e0, e1));
+        t[f][i] = ms < t[f][i] ? ms : t[f][i];
+      }
+    }
+  for (int f = 0; f < nf; f++)
+    for (int i = 0; i < 4; i++)
+      if (t[f][i] < best) {
+        best = t[f][i];
+        best_w = cand[i];
+        best_cc = s->fusable ? (f ? BX_CC_PLANE_FUSED : BX_CC_PLANE) : keep_cc;
+      }
+  s->cc = best_cc;
   s->warps = best_w;
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);

@@ -16,7 +16,12 @@ typedef void (*bx_kernel_fn)(const BxKernelParams);
 template <int MODE>
 static bx_kernel_fn pick(int jc, int cc) {
 #define BX_K(JM, CM) bx_step_kernel<MODE, (JM) | (CM) | BXF_COMMON, BX_TU_MAXT, BX_TU_MINB>
-  if (cc == BX_CC_PLANE) {
+  if (MODE == BX_MODE_PBD && cc == BX_CC_PLANE_FUSED) {
+    if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC0 | BXF_FUSED_CONTACTS);
+    if (jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC0 | BXF_FUSED_CONTACTS);
+    return BX_K(BXF_JC2, BXF_CC0 | BXF_FUSED_CONTACTS);
+  }
+  if (cc != BX_CC_ALL) {
     if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC0);
     if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC0);
     return BX_K(BXF_JC2, BXF_CC0);

@@ -27,6 +27,7 @@ enum {
   BXF_ONE_WAY = 8, BXF_TWO_WAY = 16,
   BXF_CAPSULE_PLANE = 32, BXF_CAPSULE_CAPSULE = 64, BXF_BOX_PLANE = 128,
   BXF_TORQUE = 256, BXF_ANGLE = 512, BXF_FORCES = 1024,
+  BXF_FUSED_CONTACTS = 2048,  // pbd, one-way colliders, <= 2 rows per body
   BXF_ALL = 2047
 };
 // Kernel variants are instantiated per (dynamics mode, joint class, contact
@@ -35,7 +36,7 @@ enum {
 // "sphericalize"), anything; plane contacts only (one-way capsule/box vs plane)
 // or everything.
 enum { BX_JC_REVOLUTE = 0, BX_JC_SPHERICAL = 1, BX_JC_ALL = 2, BX_NUM_JC = 3 };
-enum { BX_CC_PLANE = 0, BX_CC_ALL = 1, BX_NUM_CC = 2 };
+enum { BX_CC_PLANE_FUSED = 0, BX_CC_PLANE = 1, BX_CC_ALL = 2, BX_NUM_CC = 3 };
 #define BXF_COMMON (BXF_TORQUE | BXF_ANGLE | BXF_FORCES)
 #define BXF_JC0 BXF_REVOLUTE
 #define BXF_JC1 BXF_SPHERICAL
@@ -51,6 +52,7 @@ enum { BX_CC_PLANE = 0, BX_CC_ALL = 1, BX_NUM_CC = 2 };
   cudaError_t bx_set_smem_##maxt(int bytes);
 BX_LAUNCHER_DECL(256)
 BX_LAUNCHER_DECL(320)
+BX_LAUNCHER_DECL(384)
 BX_LAUNCHER_DECL(512)
 
 #endif  // BX_PARAMS_H_

@@ -627,10 +627,9 @@ BXS Contact contact_fn(int kind, const float4* cq, V3 pa, Q4 ra, V3 va, V3 wa, V
 // colliders.py:198-240, OneWay :306-377, TwoWay :495-582.  Row k keeps its
 // contact in quads CT+2k = {pos, pen}, {normal, dlambda} and its deltas
 // (a: dpos, drot [, b: dpos, drot]) in quads JS+delta_off(k).
-BXS void phase_contacts_position(const Ctx& c, const BxHeader& h) {
+BXS void c1_row(const Ctx& c, const BxHeader& h, int k) {
   typedef Lay<BX_MODE_PBD> L;
   const int co = 2 * c.cur, po = 2 * (c.cur ^ 1);
-  for (int k = c.warp; k < h.nk; k += c.nwarp) {
     const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);  // kind two_way a b
     const int4 cs4 = ldi4(c.ti + h.io_contact + k * CI_STRIDE + 4);  // slot_a slot_b
     const int rd = h.q_js + cs4.x, rdb = h.q_js + cs4.y;
@@ -715,7 +714,9 @@ BXS void phase_contacts_position(const Ctx& c, const BxHeader& h) {
     const int rc_ = h.q_ct + 2 * k;
     stv4(c, rc_, ct.pos, ct.pen);
     stv4(c, rc_ + 1, ct.normal, dl_out);
-  }
+}
+BXS void phase_contacts_position(const Ctx& c, const BxHeader& h) {
+  for (int k = c.warp; k < h.nk; k += c.nwarp) c1_row(c, h, k);
 }
 
 // Per-body scatter-and-average of the contact rows' deltas, one collider group
@@ -747,9 +748,8 @@ BXS void gather_contact_deltas(const Ctx& c, const BxHeader& h, int cg_off, int 
 
 // ---- phase B3 (pbd): apply contact deltas, keep qp_right_before's velocities,
 // velocity projection.  system.py:299-307.
-BXS void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
+BXS void b3_body(const Ctx& c, const BxHeader& h, int b) {
   typedef Lay<BX_MODE_PBD> L;
-  for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
     const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
     const int r0 = L::BQ * b, rc_ = r0 + 2 * c.cur, rp_ = r0 + 2 * (c.cur ^ 1);
@@ -774,16 +774,17 @@ BXS void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
     stv(c, r0 + L::VEL, vel);
     stv(c, r0 + L::ANG, ang);
     stq(c, rc_ + 1, rot);
-  }
+}
+BXS void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
+  for (int b = c.warp; b < h.nb; b += c.nwarp) b3_body(c, h, b);
 }
 
 // ---- phase C2 (pbd): _velocity_contact for every contact row ------------------
 // colliders.py:155-196, OneWay :379-442, TwoWay :584-658.  Deltas (a: dvel, dang
 // [, b: dvel, dang]) go to quads JS+delta_off(k).
-BXS void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
+BXS void c2_row(const Ctx& c, const BxHeader& h, int k) {
   typedef Lay<BX_MODE_PBD> L;
   const int co = 2 * c.cur;
-  for (int k = c.warp; k < h.nk; k += c.nwarp) {
     const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);
     const int4 cs4 = ldi4(c.ti + h.io_contact + k * CI_STRIDE + 4);  // slot_a slot_b
     const int rd = h.q_js + cs4.x, rdb = h.q_js + cs4.y;
@@ -860,18 +861,19 @@ BXS void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
       stv(c, rdb, vdiv(-p, mb));
       stv(c, rdb + 1, cross(iib * rb, -p));
     }
-  }
+}
+BXS void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
+  for (int k = c.warp; k < h.nk; k += c.nwarp) c2_row(c, h, k);
 }
 
 // ---- phase B4: velocity-level contact update + Info.contact -----------------
 // integrators.py:97-101; system.py:313,315 (pbd) / :365,367 (legacy_spring).
 template <int MODE>
-BXS void phase_body_velocity_update(const Ctx& c, const BxHeader& h, float eps) {
+BXS void b4_body(const Ctx& c, const BxHeader& h, float eps, int b) {
   typedef Lay<MODE> L;
-  for (int b = c.warp; b < h.nb; b += c.nwarp) {
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
     const int cadj_n = bi[BI_CG_N];
-    if (cadj_n == 0) continue;
+    if (cadj_n == 0) return;
     const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
     const int r0 = L::BQ * b;
     float4 dl, ds;
@@ -882,6 +884,31 @@ BXS void phase_body_velocity_update(const Ctx& c, const BxHeader& h, float eps) 
     const int r = h.q_ic + 2 * bi[BI_CSLOT];
     stv(c, r, ldv(c, r) + dv);
     stv(c, r + 1, ldv(c, r + 1) + da);
+}
+template <int MODE>
+BXS void phase_body_velocity_update(const Ctx& c, const BxHeader& h, float eps) {
+  for (int b = c.warp; b < h.nb; b += c.nwarp) b4_body<MODE>(c, h, eps, b);
+}
+
+// ---- fused contact section (pbd): when every collider is one-way and a body has
+// at most two contact rows, a body's rows only touch that body, so C1 -> B3 ->
+// C2 -> B4 of one body is a chain inside ONE warp (each lane re-reads only what
+// it wrote itself): three barriers and their idle time disappear.  Bodies with
+// contacts come first in `forder` so the long items start first.
+BXS void phase_contacts_fused(const Ctx& c, const BxHeader& h) {
+  // rounds alternate direction, so a second round lands on the warps that had the
+  // short (contact-free) bodies in the first
+  bool flip = false;
+  for (int base = 0; base < h.nb; base += c.nwarp, flip = !flip) {
+    const int i = base + (flip ? c.nwarp - 1 - c.warp : c.warp);
+    if (i >= h.nb) continue;
+    const int b = c.ti[h.io_forder + i];
+    const int4 b3 = ldi4(c.ti + h.io_body + b * BI_STRIDE + 12);  // row_off row_n
+    const int32_t* rows = c.ti + h.io_adj + b3.x;
+    for (int r = 0; r < b3.y; r++) c1_row(c, h, rows[r]);
+    b3_body(c, h, b);
+    for (int r = 0; r < b3.y; r++) c2_row(c, h, rows[r]);
+    if (b3.y > 0) b4_body<BX_MODE_PBD>(c, h, 1e-6f, b);
   }
 }
 
@@ -1185,14 +1212,19 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
           phase_body_joint_update(c, h, half == 0);
           __syncthreads(); PT(5);
           if (half == 1) {
-            phase_contacts_position(c, h);
-            __syncthreads(); PT(6);
-            phase_body_contact_update(c, h);
-            __syncthreads(); PT(7);
-            phase_contacts_velocity(c, h);
-            __syncthreads(); PT(8);
-            phase_body_velocity_update<MODE>(c, h, 1e-6f);
-            __syncthreads(); PT(9);
+            if (BX_FEAT & BXF_FUSED_CONTACTS) {
+              phase_contacts_fused(c, h);
+              __syncthreads(); PT(6);
+            } else {
+              phase_contacts_position(c, h);
+              __syncthreads(); PT(6);
+              phase_body_contact_update(c, h);
+              __syncthreads(); PT(7);
+              phase_contacts_velocity(c, h);
+              __syncthreads(); PT(8);
+              phase_body_velocity_update<MODE>(c, h, 1e-6f);
+              __syncthreads(); PT(9);
+            }
           }
         }
       }

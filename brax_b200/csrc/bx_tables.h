@@ -46,7 +46,7 @@ enum {
 // summation order (joints.py:93-98, actuators.py:67-70, colliders.py:222-228),
 // so a body sums its list with independent, address-known loads.
 enum {
-  // body: 3 x int4
+  // body: 4 x int4
   BI_CSLOT = 0,   // slot in the collider-body regions (PRE, INFO_C) or -1
   BI_ASLOT = 1,   // slot in the actuated-body region (INFO_A) or -1
   BI_A_BASE = 2,  // actuator list: a_n quads (signed I^-1 tau)
@@ -59,7 +59,9 @@ enum {
   BI_F_N = 9,
   BI_CG_OFF = 10,  // contact groups of this body: cg_n pairs (base, count) in the adj
   BI_CG_N = 11,    // table; each entry = 2 quads (linear part, second part)
-  BI_STRIDE = 12,
+  BI_ROW_OFF = 12,  // contact rows whose body_a is this body (adj table), fused path
+  BI_ROW_N = 13,
+  BI_STRIDE = 16,
 
   // joint: 2 x int4 {kind, body_p, body_c, 0} {dslot_p, dslot_c, jslot_p, jslot_c}
   JI_KIND = 0,
@@ -117,6 +119,7 @@ struct BxHeader {
   // table sizes / offsets
   int32_t n_ints, n_fquads;
   int32_t io_body, io_joint, io_act, io_force, io_contact, io_adj;  // int offs
+  int32_t io_forder;  // body order of the fused contact section (contact bodies first)
   int32_t fo_body, fo_joint, fo_act, fo_force, fo_contact;          // quad offs
   // state quad rows (each row = 32 env slots x float4, + 1 pad quad)
   int32_t q_act, q_js, q_ct, q_pre, q_ic, q_ia, q_ij;

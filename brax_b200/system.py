@@ -146,12 +146,14 @@ class System:
     """The `bx_system*` as an integer (FFI attribute)."""
     return int(self._h.value)
 
-  def configure(self, threads_per_block: int):
-    """Warps per 32-env tile = threads_per_block / 32 (tuning knob)."""
-    if self._lib.bx_system_configure(self._h, threads_per_block, 0) != 0:
+  def configure(self, threads_per_block: int = 0, contact_section: int = 0):
+    """Tuning knobs (0 = keep): warps per 32-env tile = threads_per_block / 32;
+    contact_section 1 = four contact phases, 2 = fused per-body section."""
+    if self._lib.bx_system_configure(self._h, threads_per_block, contact_section) != 0:
       raise ValueError(_lib.last_error())
-    self.threads_per_tile = threads_per_block
-    self.autotune = False
+    if threads_per_block:
+      self.threads_per_tile = threads_per_block
+      self.autotune = False
 
   # ---- state helpers ---------------------------------------------------------
   def default_qp(self, batch: int = None, device=None) -> QP:

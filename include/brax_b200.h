@@ -210,9 +210,12 @@ int bx_rollout(bx_system* sys, int64_t num_envs, int32_t num_steps,
                const bx_step_io* io, void* stream);
 
 /* Kernel launch configuration (tuning knobs; defaults are chosen per system).
- * lanes_per_env in {0=auto}; returns 0 on success. */
+ * threads_per_block: multiple of 32 in [32, 512], 0 = keep.
+ * contact_section: 0 = keep, 1 = four barrier-separated contact phases,
+ * 2 = fused per-body contact section (pbd, one-way plane colliders with at most
+ * two contact rows per body; refused otherwise).  Returns 0 on success. */
 int bx_system_configure(bx_system* sys, int32_t threads_per_block,
-                        int32_t reserved);
+                        int32_t contact_section);
 
 /* Picks the CTA size (warps per 32-env tile) by timing the candidates on the
  * caller's own device buffers for this batch size (about 16 launches + one

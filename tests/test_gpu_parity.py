@@ -111,21 +111,26 @@ def check_step(name, ins, act, got, strict_frac=0.90):
     assert not (err > OUTLIER_BOUND * tol).any(), (name, k, float(err.max()))
     bad_env |= over
     stats[k] = float((err <= base).mean())
-  assert bad_env.sum() <= allowed, (name, 'envs outside tolerance', int(bad_env.sum()), b)
-  stats['outlier_envs'] = int(bad_env.sum())
-  # the tolerance as literally stated holds for (nearly) all pos/rot elements
-  for k in ('pos', 'rot'):
-    assert stats[k] >= strict_frac, (name, k, stats[k])
   pen, pen64 = ref['contact_penetration'], r64['contact_penetration']
   if pen.size:
     mism = (got['contact_penetration'] > 0) != (pen > 0)
     hard = mism & (np.abs(pen) >= 1e-6) & (np.abs(pen64) >= 1e-6)
     assert not hard.any(), (name, 'contact flags', int(hard.sum()))
-    # body-level flag: any(info.contact.vel != 0)  
+    # body-level flag: any(info.contact.vel != 0)  (SURVEY.md 8(c)).  The impulse of
+    # an active contact is itself gated by float compares (normal-velocity sign,
+    # static friction, `sinking`: colliders.py:366,430), so besides |pen| ~ 0 an env
+    # may flip at one of those; such an env spends the same outlier budget as above.
     fg = np.any(got['contact_vel'] != 0, axis=-1)
     fr = np.any(ref['contact_vel'] != 0, axis=-1)
     near = (np.abs(pen) < 1e-5).any(axis=-1, keepdims=True)
-    assert not ((fg != fr) & ~near).any(), (name, 'contact impulse flags')
+    flag_env = ((fg != fr) & ~near).any(axis=-1)
+    stats['flag_envs'] = int(flag_env.sum())
+    bad_env |= flag_env
+  assert bad_env.sum() <= allowed, (name, 'envs outside tolerance', int(bad_env.sum()), b)
+  stats['outlier_envs'] = int(bad_env.sum())
+  # the tolerance as literally stated holds for (nearly) all pos/rot elements
+  for k in ('pos', 'rot'):
+    assert stats[k] >= strict_frac, (name, k, stats[k])
   return ref, stats
 
 
@@ -202,6 +207,31 @@ def test_single_step_on_harvested_states(name, b, steps):
   ref, _ = check_step(name, ins, act, got)
   # at least some contacts must be active for the test to mean anything
   assert (ref['contact_penetration'] > 0).mean() > 0.02, name
+
+
+@pytest.mark.parametrize('name', ['ant', 'humanoid'])
+def test_contact_section_variants(name):
+  """Both schedules of the contact section (four barrier-separated phases /
+  fused per-body chains, bx_system_configure) hold parity on contact-rich
+  states, and grasp (two-way colliders) refuses the fused one."""
+  torch = _torch()
+  from brax_b200.system import load_system
+  s = load_system(name)
+  qp, rng = _harvest(s, 1024, 30, 9)
+  act = rng.uniform(-1, 1, (1024, s.act_size)).astype(np.float32)
+  ins = [getattr(qp, k).cpu().numpy() for k in util.QP_KEYS]
+  outs = []
+  for section in (1, 2):
+    s.configure(contact_section=section)
+    qo, info = s.step(qp, torch.from_numpy(act).cuda())
+    torch.cuda.synchronize()
+    outs.append(_flat(qo, info))
+    check_step(name, ins, act, outs[-1])
+  # same arithmetic in the same order: the two schedules agree to the bit
+  for k in outs[0]:
+    np.testing.assert_array_equal(outs[0][k], outs[1][k], err_msg=k)
+  with pytest.raises(ValueError):
+    load_system('grasp').configure(contact_section=2)
 
 
 @pytest.mark.parametrize('name', ['ant', 'humanoid', 'grasp'])
