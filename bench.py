@@ -9,7 +9,11 @@ input of step t+1.  Workload = BASELINE.json configs[1]: ant, 8192 envs per
 GPU, default substeps.  One JSON line is printed by rank 0.
 
   value     env-steps/s, state resident in HBM, CUDA events around each step's
-            launch (summed), max over ranks; L2 is flushed between steps.
+            launch (summed), max over ranks.  Inputs larger than L2: the timed
+            steps rotate over enough independent env batches (>= 2 x L2 of state)
+            that every step reads cold state.  `value_l2_flushed` is the same
+            measurement on ONE batch with the whole L2 (kernel code included)
+            evicted by a 256 MiB fill before every step.
   e2e       the same metric through the host-buffer C-ABI call (bx_step_host
             via brax_b200.System.step on numpy views of pinned memory):
             H2D of QP+act and D2H of QP+Info inside the timed region.
@@ -36,6 +40,7 @@ sys.path.insert(0, ROOT)
 METRIC = 'env-steps/sec (Brax v1 System.step, all substeps)'
 UNIT = 'env-steps/s'
 SM_COUNT = 148
+L2_BYTES = 126 * 1000 * 1000  # B200 L2 (B200_PROFILING.md)
 # dram__bytes_read.sum + dram__bytes_write.sum of one bx_step_kernel launch at the
 # bench workload, from the committed `ncu --set full` capture (profiles/); bytes.
 NCU_TRAFFIC = {'ant': 4603904}
@@ -192,6 +197,7 @@ def run_gpu(args, desc):
   s = System(desc, device=local)
   if args.threads or args.contact_section:
     s.configure(args.threads, args.contact_section)
+  s.autotune = bool(args.autotune)
   b, a, n, k = args.envs, desc.act_size, desc.num_bodies, desc.num_contacts
   pos, rot, vel, ang = make_state(desc, b, 100 + rank)
   qp = QP(*[torch.from_numpy(x).to(dev) for x in (pos, rot, vel, ang)])
@@ -200,30 +206,57 @@ def run_gpu(args, desc):
   total = args.steps + args.warmup
   acts = torch.rand((total, b, a), generator=gen, device=dev) * 2 - 1
   flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
+  spin_cycles = int(400e-6 * 1.9e9)  # ~400 us, longer than the host needs to enqueue one step
 
   def barrier():
     if world > 1:
       dist.barrier()
     torch.cuda.synchronize()
 
-  for i in range(args.warmup):
-    qp, info = s.step(qp, acts[i])
+  # Working set larger than L2: the timed loop rotates over `nsets` independent env
+  # batches, so the state a step reads was written nsets steps earlier with
+  # >= 2 x L2 of other traffic in between (cold data; kernel code and the system's
+  # tables stay L2-resident, as in any real stepping loop).
+  bytes_set = b * desc.bytes_per_env_step()
+  nsets = max(2, -(-2 * L2_BYTES // bytes_set))
+  qps = [QP(qp.pos.clone(), qp.rot.clone(), qp.vel.clone(), qp.ang.clone()) for _ in range(nsets)]
+  for i in range(max(args.warmup, 0)):
+    qps[i % nsets], info = s.step(qps[i % nsets], acts[i])
+  for j in range(nsets):            # untimed: every set leaves its start state once
+    qps[j], info = s.step(qps[j], acts[j % total])
   barrier()
-  launches0 = lib.launch_count()
-  ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-        for _ in range(args.steps)]
+
+  def event_pairs():
+    return [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            for _ in range(args.steps)]
+
+  ev, ev_fl = event_pairs(), event_pairs()
   with ClockSampler(local) as clk:
     barrier()
+    launches0 = lib.launch_count()
     t_wall0 = time.perf_counter()
     for i in range(args.steps):
-      flush.fill_(float(i))          # evict L2 between timed steps (not timed)
+      # a spin kernel holds the stream while the host enqueues events and step, so
+      # an event pair times device work only (no host enqueue gap)
+      torch.cuda._sleep(spin_cycles)
+      j = i % nsets
       ev[i][0].record()
-      qp, info = s.step(qp, acts[args.warmup + i])
+      qps[j], info = s.step(qps[j], acts[args.warmup + i])
       ev[i][1].record()
     barrier()
     t_wall = time.perf_counter() - t_wall0
     launches = lib.launch_count() - launches0   # kernels launched in the timed loop
-    # back-to-back (warm L2) for reference
+    qp = qps[0]
+    # secondary: one env batch, whole L2 evicted (code and tables included)
+    # before every step by a 256 MiB fill outside the event pair
+    for i in range(args.steps):
+      torch.cuda._sleep(spin_cycles)
+      flush.fill_(float(i))
+      ev_fl[i][0].record()
+      qp, info = s.step(qp, acts[args.warmup + i])
+      ev_fl[i][1].record()
+    barrier()
+    # back-to-back from Python (host enqueue rate included), for reference
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     q2 = qp
     e0.record()
@@ -233,6 +266,7 @@ def run_gpu(args, desc):
     torch.cuda.synchronize()
   ms_steps = [x.elapsed_time(y) for x, y in ev]
   ms_total = float(sum(ms_steps))
+  ms_flushed = float(sum(x.elapsed_time(y) for x, y in ev_fl))
   ms_b2b = e0.elapsed_time(e1)
   finite = bool(torch.isfinite(qp.pos).all().item())
 
@@ -261,10 +295,11 @@ def run_gpu(args, desc):
 
   # ---- max over ranks -----------------------------------------------------------
   from brax_b200 import shard
-  ms_total, ms_b2b, t_e2e, t_wall = shard.reduce_stats(
-      [ms_total, ms_b2b, t_e2e, t_wall], ['max'] * 4, device=dev)
+  ms_total, ms_b2b, t_e2e, t_wall, ms_flushed = shard.reduce_stats(
+      [ms_total, ms_b2b, t_e2e, t_wall, ms_flushed], ['max'] * 5, device=dev)
   value = world * b * args.steps / (ms_total * 1e-3)
   value_b2b = world * b * args.steps / (ms_b2b * 1e-3)
+  value_flushed = world * b * args.steps / (ms_flushed * 1e-3)
   e2e_value = world * b * e2e_steps / t_e2e
 
   if rank == 0:
@@ -281,10 +316,16 @@ def run_gpu(args, desc):
         'config': {
             'workload': '%s %d envs/GPU, default substeps (%d), dynamics %s' % (
                 args.env, b, desc.substeps, desc.dynamics_mode),
-            'l2': 'flushed between timed steps (256 MiB fill outside the event pairs)',
+            'l2': 'inputs larger than L2: the timed steps rotate over %d independent env batches '
+                  '(%.0f MB working set vs 126 MB L2), so each step reads state last touched %d '
+                  'steps earlier; every step is enqueued behind a ~400 us spin kernel so its event '
+                  'pair holds device time only' % (nsets, nsets * bytes_set / 1e6, nsets),
+            'env_batches': nsets,
             'threads_per_tile': s_threads(s), 'bodies': n, 'contacts': k, 'act': a},
+        'value_l2_flushed': value_flushed,
+        'ms_per_step_l2_flushed': ms_flushed / args.steps,
         'value_back_to_back': value_b2b,
-        'wall_s_timed_loop_incl_flush': t_wall,
+        'wall_s_timed_loop_incl_spin': t_wall,
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d,
                 'd2h_bytes_per_step': d2h, 'steps': e2e_steps, 'finite': e2e_finite,
                 'path': 'System.step(numpy QP, out=HostBuffers) -> bx_step_host: chunked H2D/step/D2H pipeline on 3 streams, page-locked buffers'},
@@ -333,6 +374,7 @@ def main():
   ap.add_argument('--threads', type=int, default=0, help='threads per 32-env tile (0 = default)')
   ap.add_argument('--contact-section', type=int, default=0,
                   help='0 = default, 1 = four contact phases, 2 = fused per-body section')
+  ap.add_argument('--autotune', action='store_true', help='time CTA sizes on the first step')
   ap.add_argument('--cpu-seconds', type=float, default=12.0)
   ap.add_argument('--no-cpu', action='store_true')
   ap.add_argument('--no-e2e', action='store_true')

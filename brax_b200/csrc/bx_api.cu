@@ -457,6 +457,26 @@ static int set_smem_attr(int bytes) {
   return 0;
 }
 
+static size_t tile_bytes(const BxHeader& h) {
+  return (static_cast<size_t>(h.n_quads) * BX_QSTRIDE + h.n_fquads) * 16 +
+         static_cast<size_t>(h.n_ints) * 4 + 16 /* mbarrier */;
+}
+
+extern "C" int bx_desc_tile_bytes(const bx_system_desc* desc, int64_t* bytes, int32_t* rows) {
+  if (validate(desc)) return 1;
+  BxHeader h;
+  std::vector<int32_t> ti;
+  std::vector<float> tf;
+  build_tables(desc, &h, &ti, &tf);
+  if (bytes) *bytes = static_cast<int64_t>(tile_bytes(h));
+  if (rows) {
+    const int v[8] = {h.q_act, h.q_js - h.q_act, h.q_ct - h.q_js, h.q_pre - h.q_ct,
+                      h.q_ic - h.q_pre, h.q_ia - h.q_ic, h.q_ij - h.q_ia, h.n_quads - h.q_ij};
+    for (int i = 0; i < 8; i++) rows[i] = v[i];
+  }
+  return 0;
+}
+
 extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_system** out) {
   if (!out) return fail("out is NULL");
   *out = nullptr;
@@ -508,8 +528,7 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   s->d_scratch = nullptr;
   s->scratch_floats = 0;
   for (int i = 0; i < BX_HOST_STREAMS; i++) s->streams[i] = nullptr;
-  s->smem_bytes = (static_cast<size_t>(s->h.n_quads) * BX_QSTRIDE + s->h.n_fquads) * 16 +
-                  static_cast<size_t>(s->h.n_ints) * 4 + 16 /* mbarrier */;
+  s->smem_bytes = tile_bytes(s->h);
   if (s->smem_bytes > static_cast<size_t>(prop.sharedMemPerBlockOptin)) {
     delete s;
     return fail("system state does not fit in shared memory (too many bodies/joints/contacts)");
@@ -517,7 +536,7 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   // default warps per tile: minimise the critical path of one half-substep,
   // sum over phases of ceil(items / W) * (measured cycles of one item, in k-cycles,
   // tools/phase_timing.py), times a penalty for the register budget that W implies
-  // (10 warps: 102 regs; 12: 85 regs; 16: one tile per SM).
+  // (10 warps: 96 regs; 12: 80 regs; 16: one tile per SM); profiles/r01_sweeps.txt.
   {
     bool spherical = false;
     for (int i = 0; i < desc->num_joints; i++)
@@ -525,7 +544,10 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
                                 desc->joints[i].kind != BX_JOINT_SPRING_REVOLUTE);
     const double cj = spherical ? 6.7 : 2.3, ca = spherical ? 4.0 : 1.7, cb = 3.56, ck = 1.07;
     const int cand[5] = {4, 8, 10, 12, 16};
-    const double pen[5] = {1.0, 1.0, 1.03, 2.0, 1.5};
+    // 12 warps: two tiles per SM at 80 registers when shared memory allows (spherical
+    // joint code spills there: humanoid -4%), else the one-tile-per-SM build
+    const bool two_fit = 2 * (s->smem_bytes + 1024) <= 233472;
+    const double pen[5] = {1.0, 1.0, 1.03, two_fit ? (spherical ? 1.3 : 1.06) : 2.0, 1.7};
     double best = 1e30;
     s->warps = 8;
     auto rounds = [](int n, int w) { return (n + w - 1) / w; };

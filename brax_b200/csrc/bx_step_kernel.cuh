@@ -30,7 +30,12 @@
 // Phase timing (tools/phase_timing.py builds with -DBX_PHASE_TIMING): thread 0
 // of CTA 0 accumulates the cycles between consecutive barriers per phase id.
 #ifdef BX_PHASE_TIMING
-#define PT_INIT() long long pt_last = clock64()
+// dbg[0..15]: phase cycles of CTA 0; dbg[16 + 4 * cta ..]: {smid, start ns, end ns, cycles}
+#define PT_INIT()                                                                  \
+  long long pt_last = clock64();                                                   \
+  const long long pt_c0 = pt_last;                                                 \
+  long long pt_g0;                                                                 \
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(pt_g0))
 #define PT(i)                                                        \
   do {                                                               \
     if (p.dbg && blockIdx.x == 0 && threadIdx.x == 0) {              \
@@ -39,9 +44,21 @@
       pt_last = t_;                                                  \
     }                                                                \
   } while (0)
+#define PT_DONE()                                                                  \
+  do {                                                                             \
+    if (p.dbg && threadIdx.x == 0 && blockIdx.x < 4096) {                          \
+      long long g1_;                                                               \
+      unsigned sm_;                                                                \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1_));                      \
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(sm_));                             \
+      long long* r_ = p.dbg + 16 + 4 * blockIdx.x;                                 \
+      r_[0] = sm_; r_[1] = pt_g0; r_[2] = g1_; r_[3] = clock64() - pt_c0;          \
+    }                                                                              \
+  } while (0)
 #else
 #define PT_INIT()
 #define PT(i)
+#define PT_DONE()
 #endif
 
 #define QS BX_QSTRIDE
@@ -1267,6 +1284,7 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
         io_segment_scalar<false>(smf + (s < 2 ? cur_shift : 0), ti, h.seg_out[s], p.out[s], env0, nenv);
   }
   PT(11);
+  PT_DONE();
 }
 };  // struct Kern
 

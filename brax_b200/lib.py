@@ -15,7 +15,7 @@ SYMBOLS = ('bx_system_create', 'bx_system_destroy', 'bx_system_num_contacts',
            'bx_system_num_bodies', 'bx_system_act_size', 'bx_step',
            'bx_step_host', 'bx_rollout', 'bx_system_configure',
            'bx_system_autotune', 'bx_system_threads', 'bx_host_transfer_bytes',
-           'bx_host_alloc', 'bx_host_free',
+           'bx_host_alloc', 'bx_host_free', 'bx_desc_tile_bytes',
            'bx_launch_count', 'bx_last_error')
 
 _lib = None
@@ -56,6 +56,9 @@ def load():
   lib.bx_system_threads.restype = C.c_int
   lib.bx_host_transfer_bytes.argtypes = [P, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
   lib.bx_host_transfer_bytes.restype = C.c_int
+  lib.bx_desc_tile_bytes.argtypes = [C.POINTER(_desc.CSystemDesc), C.POINTER(C.c_int64),
+                                     C.POINTER(C.c_int32)]
+  lib.bx_desc_tile_bytes.restype = C.c_int
   lib.bx_host_alloc.argtypes = [C.c_size_t]
   lib.bx_host_alloc.restype = C.c_void_p
   lib.bx_host_free.argtypes = [C.c_void_p]

@@ -105,6 +105,21 @@ def _is_torch(x) -> bool:
   return type(x).__module__.startswith('torch')
 
 
+def tile_bytes(desc: SystemDesc):
+  """(shared-memory bytes of one 32-env tile, quad rows per region) of a system;
+  needs no device (bx_desc_tile_bytes)."""
+  lib = _lib.load()
+  cdesc, keep = desc.to_c()
+  nbytes = C.c_int64()
+  rows = (C.c_int32 * 8)()
+  rc = lib.bx_desc_tile_bytes(C.byref(cdesc), C.byref(nbytes), rows)
+  del keep
+  if rc != 0:
+    raise ValueError('bx_desc_tile_bytes: ' + _lib.last_error())
+  names = ('bodies', 'act', 'slots', 'contact_rows', 'pre', 'info_contact', 'info_actuator', 'info_joint')
+  return int(nbytes.value), dict(zip(names, list(rows)))
+
+
 class System:
   """A brax v1 system whose `step` is the fused sm_100a kernel."""
 
@@ -124,7 +139,12 @@ class System:
     self._h = handle
     self.threads_per_tile = 0  # 0 = library default
     self._tuned = set()        # batch sizes bx_system_autotune has seen
-    self.autotune = True
+    # opt-in: time the candidate CTA sizes on the first big step (bx_system_autotune);
+    # the per-system default is calibrated against sweeps (profiles/r01_sweeps.txt) and
+    # a one-shot timing on a cold device picked worse configurations in practice
+    self.autotune = False
+    self._plans = {}           # batch -> output slicing plan
+    self._io = CStepIO()
 
   @classmethod
   def from_brax(cls, brax_system, name: str = 'system', act_size=None,
@@ -215,32 +235,56 @@ class System:
                 out['contact_penetration'])
     return qp, info
 
+  def _out_plan(self, b):
+    """Per batch size: the 13 outputs as slices of ONE allocation (each slice
+    starts on a 16-byte boundary so the kernel's vector stores apply)."""
+    plan = self._plans.get(b)
+    if plan is None:
+      n, k = self.num_bodies, self.num_contacts
+      shapes, offs, off = [], [], 0
+      for _, w, dim in _OUT:
+        m = n if dim == 'n' else k
+        shapes.append((b, m, w) if w else (b, m))
+        offs.append(off)
+        off += -(-(b * m * max(w, 1)) // 4) * 4
+      plan = self._plans[b] = (shapes, offs, max(off, 4))
+    return plan
+
   def _step_torch(self, qp: QP, act, steps: int):
     import torch
     batched, b = self._shapes(qp.pos.shape)
-    n, k, a = self.num_bodies, self.num_contacts, self.act_size
+    n, a = self.num_bodies, self.act_size
     dev = qp.pos.device
     if dev.type != 'cuda':
       raise RuntimeError('torch tensors must live on a CUDA device (no CPU fallback)')
     if dev.index is not None and dev.index != self.device:
       raise RuntimeError('tensors are on %s, system is on cuda:%d' % (dev, self.device))
+    f32 = torch.float32
 
-    def prep(t, shape):
-      t = t.to(torch.float32).reshape(shape)
-      return t if t.is_contiguous() else t.contiguous()
+    def prep(t, numel):
+      # the common case (float32, contiguous, right size) costs two attribute reads
+      if t.dtype is not f32:
+        t = t.to(f32)
+      if not t.is_contiguous():
+        t = t.contiguous()
+      if t.numel() != numel:
+        raise ValueError('tensor has %d elements, expected %d' % (t.numel(), numel))
+      return t
 
-    ins = [prep(qp.pos, (b, n, 3)), prep(qp.rot, (b, n, 4)), prep(qp.vel, (b, n, 3)),
-           prep(qp.ang, (b, n, 3)),
-           prep(act, (steps, b, a) if steps > 1 else (b, a))]
+    ins = (prep(qp.pos, b * n * 3), prep(qp.rot, b * n * 4), prep(qp.vel, b * n * 3),
+           prep(qp.ang, b * n * 3), prep(act, steps * b * a))
+    shapes, offs, total = self._out_plan(b)
+    flat = torch.empty(total, dtype=f32, device=dev)
+    base = flat.data_ptr()
+    io = self._io
+    io.pos, io.rot, io.vel, io.ang, io.act = [t.data_ptr() for t in ins]
     out = {}
-    for name, w, dim in _OUT:
-      m = n if dim == 'n' else k
-      out[name] = torch.empty((b, m, w) if w else (b, m), dtype=torch.float32, device=dev)
-    io = CStepIO()
-    for f, t in zip(('pos', 'rot', 'vel', 'ang', 'act'), ins):
-      setattr(io, f, t.data_ptr())
-    for name, _, _ in _OUT:
-      setattr(io, name, out[name].data_ptr() if out[name].numel() else None)
+    for (name, _, _), shape, off in zip(_OUT, shapes, offs):
+      cnt = 1
+      for d in shape:
+        cnt *= d
+      out[name] = flat[off:off + cnt].view(shape)
+      setattr(io, name, base + 4 * off if cnt else None)
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     if self.autotune and steps == 1 and b >= 1024 and b not in self._tuned:
       # first call at this batch size: time the candidate CTA sizes once

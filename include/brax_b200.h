@@ -203,6 +203,13 @@ int bx_host_transfer_bytes(const bx_system* sys, int64_t num_envs, int64_t* h2d,
 void* bx_host_alloc(size_t bytes);
 void bx_host_free(void* p);
 
+/* Shared-memory footprint of one 32-environment tile of this system, without a
+ * device (sizing / diagnostics): bytes = state rows + tables; rows[8] = quad rows
+ * of {bodies, act, slot lists + staging, contact rows, pre-velocities,
+ * info.contact, info.actuator, info.joint}.  Two tiles share an SM when
+ * 2 * (bytes + 1024) <= 233472. */
+int bx_desc_tile_bytes(const bx_system_desc* desc, int64_t* bytes, int32_t* rows);
+
 /* T consecutive steps in one call: act is [T,B,A]; state ping-pongs inside
  * device scratch; Info of the LAST step is written.  Mirrors
  * lax.scan(env.step) over actions (training/acting.py:53-74) at System level. */

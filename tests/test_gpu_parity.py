@@ -234,6 +234,21 @@ def test_contact_section_variants(name):
     load_system('grasp').configure(contact_section=2)
 
 
+def test_autotune_changes_schedule_not_results():
+  """bx_system_autotune (opt-in) only re-maps work items to warps: the step it
+  leaves configured gives bit-identical results to the default configuration."""
+  torch = _torch()
+  from brax_b200.system import load_system
+  s0, s1 = load_system('ant'), load_system('ant')
+  s1.autotune = True
+  qp, rng = _harvest(s0, 2048, 10, 3)
+  act = torch.from_numpy(rng.uniform(-1, 1, (2048, s0.act_size)).astype(np.float32)).cuda()
+  a, b = _flat(*s0.step(qp, act)), _flat(*s1.step(qp, act))
+  assert 2048 in s1._tuned
+  for k in a:
+    np.testing.assert_array_equal(a[k], b[k], err_msg=k)
+
+
 @pytest.mark.parametrize('name', ['ant', 'humanoid', 'grasp'])
 def test_rollout_10_steps(name):
   """10-step rollouts vs the float32 oracle (north star: 'rollouts up to 10
