@@ -67,12 +67,42 @@ def load_flops(env):
 
 
 class ClockSampler:
-  """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+  """Samples SM clocks / throttle reasons while the timed region runs: NVML in a
+  thread (every ~2 ms, no process spawn, so the host enqueue loop is not
+  disturbed); `nvidia-smi` polling only if NVML cannot be loaded."""
 
   def __init__(self, index):
     self.index, self.rows, self._stop, self._t = index, [], False, None
+    self.source = 'nvml'
+
+  def _run_nvml(self):
+    import pynvml as nv
+    nv.nvmlInit()
+    try:
+      import torch
+      uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+      hnd = nv.nvmlDeviceGetHandleByUUID(('GPU-' + uuid).encode())
+    except Exception:
+      hnd = nv.nvmlDeviceGetHandleByIndex(self.index)
+    mx = nv.nvmlDeviceGetMaxClockInfo(hnd, nv.NVML_CLOCK_SM)
+    bits = [(getattr(nv, 'nvmlClocksEventReasonHwSlowdown', 0x8), 'hw_slowdown'),
+            (getattr(nv, 'nvmlClocksEventReasonHwThermalSlowdown', 0x40), 'hw_thermal_slowdown'),
+            (getattr(nv, 'nvmlClocksEventReasonSwThermalSlowdown', 0x20), 'sw_thermal_slowdown'),
+            (getattr(nv, 'nvmlClocksEventReasonSwPowerCap', 0x4), 'sw_power_cap')]
+    get_reasons = getattr(nv, 'nvmlDeviceGetCurrentClocksEventReasons', None) or \
+        nv.nvmlDeviceGetCurrentClocksThrottleReasons
+    while not self._stop:
+      sm = nv.nvmlDeviceGetClockInfo(hnd, nv.NVML_CLOCK_SM)
+      r = get_reasons(hnd)
+      self.rows.append([str(sm), str(mx)] + ['Active' if r & bit else 'Not Active' for bit, _ in bits])
+      time.sleep(0.002)
 
   def _run(self):
+    try:
+      self._run_nvml()
+      return
+    except Exception:
+      self.source = 'nvidia-smi'
     q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
          'clocks_event_reasons.hw_thermal_slowdown,'
          'clocks_event_reasons.sw_thermal_slowdown,'
@@ -111,7 +141,7 @@ class ClockSampler:
           reasons.add(n)
     return {'sm_mhz': float(np.median(sm)) if sm else None,
             'sm_max_mhz': float(max(mx)) if mx else None,
-            'reasons': sorted(reasons), 'samples': len(sm)}
+            'reasons': sorted(reasons), 'samples': len(sm), 'source': self.source}
 
 
 def make_state(desc, b, seed):
@@ -206,7 +236,10 @@ def run_gpu(args, desc):
   total = args.steps + args.warmup
   acts = torch.rand((total, b, a), generator=gen, device=dev) * 2 - 1
   flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
-  spin_cycles = int(400e-6 * 1.9e9)  # ~400 us, longer than the host needs to enqueue one step
+  # timed steps are enqueued in chunks behind a spin kernel that outlasts the host's
+  # enqueue time for the chunk (~0.15 ms per step), well inside the launch queue depth
+  CHUNK = 128
+  spin_cycles = int((20e-3 + 0.25e-3 * min(args.steps, CHUNK)) * 1.9e9)
 
   def barrier():
     if world > 1:
@@ -235,10 +268,11 @@ def run_gpu(args, desc):
     barrier()
     launches0 = lib.launch_count()
     t_wall0 = time.perf_counter()
+    # a spin kernel holds the stream while the host enqueues a chunk of timed steps and
+    # their event pairs, so the pairs hold device time only (no host enqueue gaps)
     for i in range(args.steps):
-      # a spin kernel holds the stream while the host enqueues events and step, so
-      # an event pair times device work only (no host enqueue gap)
-      torch.cuda._sleep(spin_cycles)
+      if i % CHUNK == 0:
+        torch.cuda._sleep(spin_cycles)
       j = i % nsets
       ev[i][0].record()
       qps[j], info = s.step(qps[j], acts[args.warmup + i])
@@ -246,27 +280,30 @@ def run_gpu(args, desc):
     barrier()
     t_wall = time.perf_counter() - t_wall0
     launches = lib.launch_count() - launches0   # kernels launched in the timed loop
-    qp = qps[0]
-    # secondary: one env batch, whole L2 evicted (code and tables included)
-    # before every step by a 256 MiB fill outside the event pair
-    for i in range(args.steps):
-      torch.cuda._sleep(spin_cycles)
-      flush.fill_(float(i))
-      ev_fl[i][0].record()
-      qp, info = s.step(qp, acts[args.warmup + i])
-      ev_fl[i][1].record()
-    barrier()
-    # back-to-back from Python (host enqueue rate included), for reference
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    q2 = qp
-    e0.record()
-    for i in range(args.steps):
-      q2, _ = s.step(q2, acts[args.warmup + i])
-    e1.record()
-    torch.cuda.synchronize()
+  qp = qps[0]
+  # secondary: one env batch, whole L2 evicted (code and tables included)
+  # before every step by a 256 MiB fill outside the event pair
+  for i in range(args.steps):
+    if i % CHUNK == 0:
+      torch.cuda._sleep(2 * spin_cycles)
+    flush.fill_(float(i))
+    ev_fl[i][0].record()
+    qp, info = s.step(qp, acts[args.warmup + i])
+    ev_fl[i][1].record()
+  barrier()
+  # back-to-back from Python (host enqueue rate included), for reference
+  e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  q2 = qp
+  e0.record()
+  for i in range(args.steps):
+    q2, _ = s.step(q2, acts[args.warmup + i])
+  e1.record()
+  torch.cuda.synchronize()
   ms_steps = [x.elapsed_time(y) for x, y in ev]
   ms_total = float(sum(ms_steps))
-  ms_flushed = float(sum(x.elapsed_time(y) for x, y in ev_fl))
+  ms_sorted = sorted(ms_steps)
+  ms_fl_steps = sorted(x.elapsed_time(y) for x, y in ev_fl)
+  ms_flushed = float(sum(ms_fl_steps))
   ms_b2b = e0.elapsed_time(e1)
   finite = bool(torch.isfinite(qp.pos).all().item())
 
@@ -312,18 +349,20 @@ def run_gpu(args, desc):
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world,
         'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': ms_total / args.steps, 'higher_is_better': True,
+        'ms_per_step_min_median_max': [ms_sorted[0], ms_sorted[len(ms_sorted) // 2], ms_sorted[-1]],
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
         'config': {
             'workload': '%s %d envs/GPU, default substeps (%d), dynamics %s' % (
                 args.env, b, desc.substeps, desc.dynamics_mode),
             'l2': 'inputs larger than L2: the timed steps rotate over %d independent env batches '
                   '(%.0f MB working set vs 126 MB L2), so each step reads state last touched %d '
-                  'steps earlier; every step is enqueued behind a ~400 us spin kernel so its event '
-                  'pair holds device time only' % (nsets, nsets * bytes_set / 1e6, nsets),
+                  'steps earlier; timed steps are enqueued in chunks of 128 behind a spin kernel so the event '
+                  'pairs hold device time only' % (nsets, nsets * bytes_set / 1e6, nsets),
             'env_batches': nsets,
             'threads_per_tile': s_threads(s), 'bodies': n, 'contacts': k, 'act': a},
         'value_l2_flushed': value_flushed,
         'ms_per_step_l2_flushed': ms_flushed / args.steps,
+        'ms_l2_flushed_min_median_max': [ms_fl_steps[0], ms_fl_steps[len(ms_fl_steps) // 2], ms_fl_steps[-1]],
         'value_back_to_back': value_b2b,
         'wall_s_timed_loop_incl_spin': t_wall,
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d,

@@ -30,7 +30,9 @@
 // Phase timing (tools/phase_timing.py builds with -DBX_PHASE_TIMING): thread 0
 // of CTA 0 accumulates the cycles between consecutive barriers per phase id.
 #ifdef BX_PHASE_TIMING
-// dbg[0..15]: phase cycles of CTA 0; dbg[16 + 4 * cta ..]: {smid, start ns, end ns, cycles}
+// dbg[0..15]: phase cycles of CTA 0 (barrier to barrier); dbg[16..31]: of those, the
+// cycles warp 0 was busy before it arrived at the barrier; dbg[32 + 4 * cta ..]:
+// {smid, start ns, end ns, cycles}
 #define PT_INIT()                                                                  \
   long long pt_last = clock64();                                                   \
   const long long pt_c0 = pt_last;                                                 \
@@ -44,6 +46,10 @@
       pt_last = t_;                                                  \
     }                                                                \
   } while (0)
+#define PTA(i)                                                       \
+  do {                                                               \
+    if (p.dbg && blockIdx.x == 0 && threadIdx.x == 0) p.dbg[16 + (i)] += clock64() - pt_last; \
+  } while (0)
 #define PT_DONE()                                                                  \
   do {                                                                             \
     if (p.dbg && threadIdx.x == 0 && blockIdx.x < 4096) {                          \
@@ -51,13 +57,14 @@
       unsigned sm_;                                                                \
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g1_));                      \
       asm volatile("mov.u32 %0, %%smid;" : "=r"(sm_));                             \
-      long long* r_ = p.dbg + 16 + 4 * blockIdx.x;                                 \
+      long long* r_ = p.dbg + 32 + 4 * blockIdx.x;                                 \
       r_[0] = sm_; r_[1] = pt_g0; r_[2] = g1_; r_[3] = clock64() - pt_c0;          \
     }                                                                              \
   } while (0)
 #else
 #define PT_INIT()
 #define PT(i)
+#define PTA(i)
 #define PT_DONE()
 #endif
 
@@ -315,7 +322,13 @@ BXS void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
     stv(c, h.q_js + ai2.z, angle_act ? tc : -tc);
   }
   if (damp) {
-    for (int j = c.warp; j < h.nj; j += c.nwarp) {
+    // the damping items are short: when the last actuator round leaves warps idle,
+    // those warps take them (up to 4 each) instead of lengthening the busy ones
+    const int rem = h.na % c.nwarp, n_idle = rem ? c.nwarp - rem : 0;
+    const bool on_idle = n_idle > 0 && h.nj <= 4 * n_idle;
+    const int j0 = on_idle ? (c.warp >= rem ? c.warp - rem : h.nj) : c.warp;
+    const int jstep = on_idle ? n_idle : c.nwarp;
+    for (int j = j0; j < h.nj; j += jstep) {
       const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
       const int4 js = ldi4(c.ti + h.io_joint + j * JI_STRIDE + 4);  // dslot_p dslot_c jslot_p jslot_c
       const float damping = c.tf[h.fo_joint + j * JQ_STRIDE + JQ_OFF_P].w;
@@ -1220,27 +1233,27 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
 #pragma unroll 1
         for (int half = 0; half < 2; half++) {
           phase_torques<MODE>(c, h, true);
-          __syncthreads(); PT(2);
+          PTA(2); __syncthreads(); PT(2);
           phase_body_acc_kinetic(c, h, half == 1);
           c.cur ^= 1;
-          __syncthreads(); PT(3);
+          PTA(3); __syncthreads(); PT(3);
           phase_joints_pbd(c, h);
-          __syncthreads(); PT(4);
+          PTA(4); __syncthreads(); PT(4);
           phase_body_joint_update(c, h, half == 0);
-          __syncthreads(); PT(5);
+          PTA(5); __syncthreads(); PT(5);
           if (half == 1) {
             if (BX_FEAT & BXF_FUSED_CONTACTS) {
               phase_contacts_fused(c, h);
-              __syncthreads(); PT(6);
+              PTA(6); __syncthreads(); PT(6);
             } else {
               phase_contacts_position(c, h);
-              __syncthreads(); PT(6);
+              PTA(6); __syncthreads(); PT(6);
               phase_body_contact_update(c, h);
-              __syncthreads(); PT(7);
+              PTA(7); __syncthreads(); PT(7);
               phase_contacts_velocity(c, h);
-              __syncthreads(); PT(8);
+              PTA(8); __syncthreads(); PT(8);
               phase_body_velocity_update<MODE>(c, h, 1e-6f);
-              __syncthreads(); PT(9);
+              PTA(9); __syncthreads(); PT(9);
             }
           }
         }

@@ -1,9 +1,11 @@
 """Attributes an ncu source-page CSV (SASS rows) to the kernel's phase functions.
 
-usage: python tools/phase_profile.py SRC.csv [kernel-substring]
-SASS address -> source line comes from `nvdisasm -g` on the cubin inside
+usage: python tools/phase_profile.py SRC.csv KERNEL_REGEX [--lines N] [--ops]
+  KERNEL_REGEX selects the .text section, e.g. 'ILi0ELi\\d+ELi320ELi2E' ; with
+  several matches the candidates are listed.
+SASS address -> source line comes from `nvdisasm -g` on the cubins inside
 brax_b200/libbrax_b200.so (must be the build that was profiled); a line of
-bx_math.cuh is charged to the last bx_step_kernel.cu line seen before it.
+bx_math.cuh is charged to the last bx_step_kernel.cuh line seen before it.
 """
 import collections
 import csv
@@ -15,17 +17,19 @@ import tempfile
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 src_csv = sys.argv[1]
-kern = sys.argv[2] if len(sys.argv) > 2 else 'ILi0EE'
-cu = os.path.join(ROOT, 'brax_b200', 'csrc', 'bx_step_kernel.cu')
+kern = re.compile(sys.argv[2])
+nlines = int(sys.argv[sys.argv.index('--lines') + 1]) if '--lines' in sys.argv else 0
+cuh = os.path.join(ROOT, 'brax_b200', 'csrc', 'bx_step_kernel.cuh')
+src_lines = open(cuh).read().splitlines()
 
-# function line ranges of the .cu file
 funcs = []
-for i, line in enumerate(open(cu), 1):
-  m = re.match(r'^(?:template.*\n)?(?:BXD|__device__|extern|__global__|static)[^;]*?\b(\w+)\s*\(', line)
-  if m and not line.startswith(' '):
+for i, line in enumerate(src_lines, 1):
+  m = re.match(r'^(?:BXS|BXD|__device__|static)\s[^;]*?\b(\w+)\s*\($', line) or \
+      re.match(r'^(?:BXS|BXD|__device__|static)\s[^;]*?\b(\w+)\s*\(', line)
+  if m:
     funcs.append((i, m.group(1)))
-  elif re.match(r'^bx_step_kernel\(', line):
-    funcs.append((i, 'bx_step_kernel'))
+
+
 def func_of(ln):
   name = '?'
   for start, n in funcs:
@@ -33,23 +37,39 @@ def func_of(ln):
       name = n
   return name
 
-td = tempfile.mkdtemp()
-subprocess.check_call(['cuobjdump', '-xelf', 'all', os.path.join(ROOT, 'brax_b200', 'libbrax_b200.so')],
-                      cwd=td, stdout=subprocess.DEVNULL)
-cubin = [f for f in os.listdir(td) if f.endswith('.cubin')][0]
-dis = subprocess.run(['nvdisasm', '-g', '-c', os.path.join(td, cubin)], capture_output=True, text=True).stdout
-addr_line, on, cur = {}, False, 0
-for l in dis.splitlines():
-  if l.startswith('.text.'):
-    on = kern in l
-  if not on:
-    continue
-  m = re.search(r'//## File ".*bx_step_kernel\.cu", line (\d+)', l)
-  if m:
-    cur = int(m.group(1))
-  m = re.match(r'\s+/\*([0-9a-f]{4,6})\*/', l)
-  if m:
-    addr_line[int(m.group(1), 16)] = cur
+
+# the kernel objects of the last build (brax_b200/build.py keeps them in the temp dir);
+# every launch-bound TU has its own cubin, extracted into its own directory
+objdir = os.path.join(tempfile.gettempdir(), 'brax_b200_obj_libbrax_b200.so')
+cubins = []
+for o in sorted(f for f in os.listdir(objdir) if f.startswith('bx_kernels_') and f.endswith('.o')):
+  td = tempfile.mkdtemp()
+  subprocess.check_call(['cuobjdump', '-xelf', 'all', os.path.join(objdir, o)], cwd=td, stdout=subprocess.DEVNULL)
+  cubins += [os.path.join(td, f) for f in os.listdir(td) if f.endswith('.cubin')]
+addr_line, addr_op, found = {}, {}, []
+for cubin in cubins:
+  dis = subprocess.run(['nvdisasm', '-g', '-c', cubin], capture_output=True, text=True).stdout
+  on, cur = False, 0
+  for l in dis.splitlines():
+    if l.startswith('.text.'):
+      on = bool(kern.search(l))
+      if on:
+        found.append(l.strip())
+    if not on:
+      continue
+    m = re.search(r'//## File ".*bx_step_kernel\.cuh", line (\d+)', l)
+    if m:
+      cur = int(m.group(1))
+    m = re.match(r'\s+/\*([0-9a-f]{4,6})\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)', l)
+    if m:
+      addr_line[int(m.group(1), 16)] = cur
+      addr_op[int(m.group(1), 16)] = m.group(2)
+if len(found) != 1:
+  print('kernel regex matched %d sections:' % len(found))
+  for f in found[:20]:
+    print(' ', f)
+  sys.exit(1)
+print('kernel', found[0])
 
 rows = list(csv.reader(open(src_csv)))
 hdr, data = rows[1], rows[2:]
@@ -57,6 +77,8 @@ iA, iE, iS = hdr.index('Address'), hdr.index('Instructions Executed'), hdr.index
 stall_cols = [i for i, h in enumerate(hdr) if h.startswith('stall_') and 'Not Issued' not in h]
 base = None
 agg = collections.defaultdict(lambda: [0, 0, collections.Counter()])
+by_line = collections.defaultdict(lambda: [0, 0])
+ops = collections.Counter()
 tot_e = tot_s = 0
 for r in data:
   if len(r) < len(hdr):
@@ -64,9 +86,12 @@ for r in data:
   a = int(r[iA], 16) if r[iA].startswith('0x') else int(r[iA])
   if base is None:
     base = a
-  f = func_of(addr_line.get(a - base, 0))
+  ln = addr_line.get(a - base, 0)
+  f = func_of(ln)
   e, s = int(r[iE] or 0), int(r[iS] or 0)
   agg[f][0] += e; agg[f][1] += s
+  by_line[ln][0] += e; by_line[ln][1] += s
+  ops[addr_op.get(a - base, '?').split('.')[0]] += e
   for i in stall_cols:
     v = int(r[i] or 0)
     if v:
@@ -76,3 +101,12 @@ print('%-28s %7s %7s  top stalls' % ('function', 'inst%', 'samp%'))
 for f, (e, s, st) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
   print('%-28s %6.1f%% %6.1f%%  %s' % (f, 100 * e / tot_e, 100 * s / max(tot_s, 1),
         ' '.join('%s:%d' % kv for kv in st.most_common(4))))
+if '--ops' in sys.argv:
+  print('\nopcode mix (warp instructions executed):')
+  for op, n in ops.most_common(24):
+    print('  %-10s %5.1f%%' % (op, 100 * n / tot_e))
+if nlines:
+  print('\ntop source lines by samples:')
+  for ln, (e, s) in sorted(by_line.items(), key=lambda kv: -kv[1][1])[:nlines]:
+    text = src_lines[ln - 1].strip() if 0 < ln <= len(src_lines) else ''
+    print('  %5d %-22s inst %4.1f%% samp %4.1f%%  %s' % (ln, func_of(ln), 100 * e / tot_e, 100 * s / max(tot_s, 1), text[:70]))

@@ -26,7 +26,7 @@ s = load_system(name)
 if len(sys.argv) > 3:
   s.configure(int(sys.argv[3]), int(sys.argv[4]) if len(sys.argv) > 4 else 0)
 lib = bl.load()
-dbg = torch.zeros(16 + 4 * 4096, dtype=torch.int64, device='cuda')
+dbg = torch.zeros(32 + 4 * 4096, dtype=torch.int64, device='cuda')
 lib.bx_debug_set_buffer.argtypes = [C.c_void_p]
 q = s.default_qp(batch=b, device='cuda')
 rng = np.random.default_rng(0)
@@ -43,12 +43,12 @@ v = dbg.cpu().numpy() / n
 names = ['tables', 'load', 'T', 'B1', 'J', 'B2', 'C1|fused', 'B3', 'C2', 'B4', 'tail', 'store', 'stage', 'flush']
 tot = v[:14].sum()
 print('%s B=%d: %.0f cycles/step (%.1f us @1.965GHz)' % (name, b, tot, tot / 1965))
-for nm, x in zip(names, v):
-  print('  %-7s %8.0f  %5.1f%%' % (nm, x, 100 * x / tot))
+for i, (nm, x) in enumerate(zip(names, v)):
+  print('  %-9s %8.0f  %5.1f%%   warp 0 busy %8.0f' % (nm, x, 100 * x / tot, v[16 + i]))
 
 # per-CTA records of the LAST launch: tiles per SM, duration by co-residency, start skew
 ntile = min((b + 31) // 32, 4096)
-rec = dbg.cpu().numpy()[16:16 + 4 * ntile].reshape(ntile, 4)
+rec = dbg.cpu().numpy()[32:32 + 4 * ntile].reshape(ntile, 4)
 sm, t0, t1, cyc = rec[:, 0], rec[:, 1], rec[:, 2], rec[:, 3]
 start = t0.min()
 per_sm = np.bincount(sm.astype(np.int64))
@@ -70,7 +70,7 @@ for a in acts[:10]:
   e1.record()
   evs.append((e0, e1))
 torch.cuda.synchronize()
-rec = dbg.cpu().numpy()[16:16 + 4 * ntile].reshape(ntile, 4)
+rec = dbg.cpu().numpy()[32:32 + 4 * ntile].reshape(ntile, 4)
 print('event-timed launch: median %.1f us; CTA span of the last one %.1f us' % (
     1e3 * np.median([x.elapsed_time(y) for x, y in evs]), (rec[:, 2].max() - rec[:, 1].min()) / 1e3))
 # two launches back to back inside one event pair: (pair - single) = steady-state cost
