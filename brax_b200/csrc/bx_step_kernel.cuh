@@ -42,13 +42,24 @@
   do {                                                               \
     if (p.dbg && blockIdx.x == 0 && threadIdx.x == 0) {              \
       long long t_ = clock64();                                      \
-      p.dbg[i] += t_ - pt_last;                                      \
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.dbg + (i)), static_cast<unsigned long long>(t_ - pt_last)); \
       pt_last = t_;                                                  \
     }                                                                \
   } while (0)
 #define PTA(i)                                                       \
   do {                                                               \
-    if (p.dbg && blockIdx.x == 0 && threadIdx.x == 0) p.dbg[16 + (i)] += clock64() - pt_last; \
+    if (p.dbg && blockIdx.x == 0 && threadIdx.x == 0)                \
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.dbg + 16 + (i)), static_cast<unsigned long long>(clock64() - pt_last)); \
+  } while (0)
+#define BX_PTM_BASE (32 + 4 * 4096)
+#define PTM0(c) do { if ((c).dbg && threadIdx.x == 0 && blockIdx.x == 0) (c).mark = clock64(); } while (0)
+#define PTM(c, slot)                                                  \
+  do {                                                                \
+    if ((c).dbg && threadIdx.x == 0 && blockIdx.x == 0) {             \
+      long long t_ = clock64();                                       \
+      atomicAdd(reinterpret_cast<unsigned long long*>((c).dbg + BX_PTM_BASE + (c).moff + (slot)), static_cast<unsigned long long>(t_ - (c).mark)); \
+      (c).mark = t_;                                                  \
+    }                                                                 \
   } while (0)
 #define PT_DONE()                                                                  \
   do {                                                                             \
@@ -65,6 +76,8 @@
 #define PT_INIT()
 #define PT(i)
 #define PTA(i)
+#define PTM0(c)
+#define PTM(c, slot)
 #define PT_DONE()
 #endif
 
@@ -82,6 +95,11 @@ struct Ctx {
   const int32_t* ti;  // int tables (shared)
   int warp, nwarp;
   int cur;            // ping-pong index of the current pos/rot quads (pbd)
+#ifdef BX_PHASE_TIMING
+  long long* dbg;     // within-item markers (PTM): dbg[BX_PTM_BASE + slot]
+  mutable long long mark;
+  int moff;           // marker slot offset (experiments)
+#endif
 };
 
 // body block layout (quads): pbd {pos0 rot0 pos1 rot1 vel ang}, spring {pos rot vel ang}
@@ -349,16 +367,19 @@ BXS void body_accels(const Ctx& c, const BxHeader& h, const int32_t* bi, const f
   {
     const int4 b0 = ldi4(bi);  // cslot aslot a_base a_n
     const int r = h.q_js + b0.z;
+#pragma unroll 1
     for (int i = 0; i < b0.w; i++) dpa = dpa + ldv(c, r + i);
   }
   if (damp) {
     const int r = h.q_js + bi[BI_D_BASE], n = bi[BI_D_N];
+#pragma unroll 1
     for (int i = 0; i < n; i++) dpj = dpj + ldv(c, r + i);
   }
   V3 fv = v3(0.f, 0.f, 0.f), fa = v3(0.f, 0.f, 0.f);
   if (BX_FEAT & BXF_FORCES) {
     const int32_t* adj = c.ti + h.io_adj + bi[BI_F_OFF];
     const int n = bi[BI_F_N];
+#pragma unroll 1
     for (int i = 0; i < n; i++) {
       int f = adj[i];
       const int32_t* fi = c.ti + h.io_force + f * FI_STRIDE;
@@ -406,12 +427,14 @@ BXS void velocity_projection(const BxHeader& h, V3 pm, V3 rm, V3 pos, V3 ppos, Q
 BXS void phase_body_acc_kinetic(const Ctx& c, const BxHeader& h, bool accumulate_info) {
   typedef Lay<BX_MODE_PBD> L;
   for (int b = c.warp; b < h.nb; b += c.nwarp) {
+    PTM0(c);
     const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
     const float4* bq = c.tf + h.fo_body + b * BQ_STRIDE;
     const int r0 = L::BQ * b;
     V3 dpa, dpj, fv, fa;
     body_accels(c, h, bi, bq, true, &dpa, &dpj, &fv, &fa);
     V3 acc_ang = (dpa + fa) + dpj;
+    PTM(c, 0);
     V3 vel = ldv(c, r0 + L::VEL), ang = ldv(c, r0 + L::ANG);
     V3 g = v3(h.gravity[0], h.gravity[1], h.gravity[2]);
     V3 pm = f3(bq[BQ_POS_MASK]), rm = f3(bq[BQ_ROT_MASK]);
@@ -420,11 +443,14 @@ BXS void phase_body_acc_kinetic(const Ctx& c, const BxHeader& h, bool accumulate
     ang = (h.ang_damp * ang + acc_ang * h.dt) * rm;
     V3 pos = ldv(c, r0 + 2 * c.cur);
     Q4 rot = ldq(c, r0 + 2 * c.cur + 1);
+    PTM(c, 1);
     kinetic(h, pm, rm, vel, ang, &pos, &rot);
+    PTM(c, 2);
     stv(c, r0 + L::VEL, vel);
     stv(c, r0 + L::ANG, ang);
     stv(c, r0 + 2 * (c.cur ^ 1), pos);
     stq(c, r0 + 2 * (c.cur ^ 1) + 1, rot);
+    PTM(c, 3);
     if (accumulate_info && bi[BI_ASLOT] >= 0) {  // info.actuator += dp_a (system.py:315)
       int r = h.q_ia + bi[BI_ASLOT];
       stv(c, r, ldv(c, r) + dpa);
@@ -484,6 +510,7 @@ BXS void limit_angle(V3 n, V3 n_1, V3 n_2, float lo, float hi, V3 ii_p, V3 ii_c,
 BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_PBD> L;
   for (int j = c.warp; j < h.nj; j += c.nwarp) {
+    PTM0(c);
     const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
     const float4* jq = c.tf + h.fo_joint + j * JQ_STRIDE;
     const int bp = ji.y, bc = ji.z;
@@ -497,8 +524,10 @@ BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
     const float4 ap0 = jq[JQ_AXIS_P];
     V3 wp = pos_p + rotate(f3(j0), rp);
     V3 wc = pos_c + rotate(f3(j1), rc);
+    PTM(c, 4);
     DQ dp, dc;
     position_update(wp, wc, pos_p, pos_c, rp, rc, mp.x, mc.x, mp.y, mc.y, ii_p, ii_c, j1.w, &dp, &dc);
+    PTM(c, 5);
     const float sa = ap0.w;
     const float4 l01 = jq[JQ_LIMIT];
     if (BXF_IS(ji.x == BX_JOINT_REVOLUTE, BXF_REVOLUTE, BXF_SPHERICAL)) {
@@ -506,16 +535,19 @@ BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
       V3 ref_p = rotate(f3(jq[JQ_AXIS_P + 2]), rp);
       V3 ref_c = rotate(f3(jq[JQ_AXIS_C + 2]), rc);
       float psi = signed_angle(axis, ref_p, ref_c);
+      PTM(c, 6);
       V3 axis_c = rotate(f3(jq[JQ_AXIS_C]), rc);
       V3 dq_1 = cross(axis, axis_c);
       float ph = clipf(psi, l01.x, l01.y);
       V3 n1 = rotate(ref_p, quat_rot_axis(axis, ph));
       V3 dq_2 = cross(n1, ref_c);
+      PTM(c, 7);
       Q4 p1, c1, p2, c2;
       angle_update(dq_1, ii_p, ii_c, rp, rc, sa, &p1, &c1);
       angle_update(dq_2, ii_p, ii_c, rp, rc, sa, &p2, &c2);
       dp.rot = dp.rot + (p1 + p2);
       dc.rot = dc.rot + (c1 + c2);
+      PTM(c, 8);
     } else {
       const float4 l2 = jq[JQ_LIMIT + 1];
       V3 a1p = rotate(f3(ap0), rp);
@@ -540,6 +572,7 @@ BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
     const int4 js = ldi4(c.ti + h.io_joint + j * JI_STRIDE + 4);  // dslot_p dslot_c jslot_p jslot_c
     stv(c, h.q_js + js.z, dp.pos); stq(c, h.q_js + js.z + 1, dp.rot);
     stv(c, h.q_js + js.w, dc.pos); stq(c, h.q_js + js.w + 1, dc.rot);
+    PTM(c, 9);
   }
 }
 
@@ -554,6 +587,7 @@ BXS void phase_body_joint_update(const Ctx& c, const BxHeader& h, bool project) 
     V3 dpos = v3(0.f, 0.f, 0.f);
     Q4 drot = q4(0.f, 0.f, 0.f, 0.f);
     const int jr = h.q_js + bi[BI_J_BASE], jn = bi[BI_J_N];
+#pragma unroll 1
     for (int i = 0; i < jn; i++) {
       dpos = dpos + ldv(c, jr + 2 * i);
       drot = drot + ldq(c, jr + 2 * i + 1);
@@ -758,10 +792,12 @@ BXS void gather_contact_deltas(const Ctx& c, const BxHeader& h, int cg_off, int 
                                float4* lin_out, float4* sec_out) {
   float4 lo = make_float4(0.f, 0.f, 0.f, 0.f), so = lo;
   const int32_t* cg = c.ti + h.io_adj + cg_off;
+#pragma unroll 1
   for (int g = 0; g < cg_n; g++) {
     const int base = h.q_js + cg[2 * g], n = cg[2 * g + 1];
     float4 ls = make_float4(0.f, 0.f, 0.f, 0.f), ss = ls;
     float cnt = 0.f;
+#pragma unroll 1
     for (int i = 0; i < n; i++) {
       const float4 l = QROW(c, base + 2 * i), s = QROW(c, base + 2 * i + 1);
       cnt += (l.x != 0.f || l.y != 0.f || l.z != 0.f) ? 1.f : 0.f;
@@ -935,8 +971,10 @@ BXS void phase_contacts_fused(const Ctx& c, const BxHeader& h) {
     const int b = c.ti[h.io_forder + i];
     const int4 b3 = ldi4(c.ti + h.io_body + b * BI_STRIDE + 12);  // row_off row_n
     const int32_t* rows = c.ti + h.io_adj + b3.x;
+#pragma unroll 1
     for (int r = 0; r < b3.y; r++) c1_row(c, h, rows[r]);
     b3_body(c, h, b);
+#pragma unroll 1
     for (int r = 0; r < b3.y; r++) c2_row(c, h, rows[r]);
     if (b3.y > 0) b4_body<BX_MODE_PBD>(c, h, 1e-6f, b);
   }
@@ -1040,6 +1078,7 @@ BXS void phase_body_acc_spring(const Ctx& c, const BxHeader& h) {
     body_accels(c, h, bi, bq, false, &dpa, &unused, &fv, &fa);
     V3 jv = v3(0.f, 0.f, 0.f), ja = v3(0.f, 0.f, 0.f);
     const int jr = h.q_js + bi[BI_J_BASE], jn = bi[BI_J_N];
+#pragma unroll 1
     for (int i = 0; i < jn; i++) {
       jv = jv + ldv(c, jr + 2 * i);
       ja = ja + ldv(c, jr + 2 * i + 1);
@@ -1195,6 +1234,11 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
   c.tf = tf;
   c.ti = ti;
   c.cur = 0;
+#ifdef BX_PHASE_TIMING
+  c.dbg = p.dbg;
+  c.mark = 0;
+  c.moff = 0;
+#endif
 
   for (int step = 0; step < p.num_steps; step++) {
     __syncthreads();
@@ -1235,12 +1279,19 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
           phase_torques<MODE>(c, h, true);
           PTA(2); __syncthreads(); PT(2);
           phase_body_acc_kinetic(c, h, half == 1);
+#ifdef BX_EXPERIMENT_TWICE  // same phase again, instruction cache warm: timing only
+          __syncthreads();
+          c.moff = 16;
+          phase_body_acc_kinetic(c, h, half == 1);
+          c.moff = 0;
+#endif
           c.cur ^= 1;
           PTA(3); __syncthreads(); PT(3);
           phase_joints_pbd(c, h);
           PTA(4); __syncthreads(); PT(4);
           phase_body_joint_update(c, h, half == 0);
           PTA(5); __syncthreads(); PT(5);
+#ifndef BX_EXPERIMENT_NO_CONTACTS
           if (half == 1) {
             if (BX_FEAT & BXF_FUSED_CONTACTS) {
               phase_contacts_fused(c, h);
@@ -1256,6 +1307,7 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
               PTA(9); __syncthreads(); PT(9);
             }
           }
+#endif
         }
       }
     } else {

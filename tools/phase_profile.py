@@ -30,6 +30,22 @@ for i, line in enumerate(src_lines, 1):
     funcs.append((i, m.group(1)))
 
 
+math_h = os.path.join(ROOT, 'brax_b200', 'csrc', 'bx_math.cuh')
+mfuncs = []
+for i, line in enumerate(open(math_h).read().splitlines(), 1):
+  m = re.match(r'^(?:BXD|__device__|static)\s[^;]*?\b(\w+)\s*\(', line)
+  if m:
+    mfuncs.append((i, m.group(1)))
+
+
+def mfunc_of(ln):
+  name = '?'
+  for start, n in mfuncs:
+    if start <= ln:
+      name = n
+  return 'math:' + name
+
+
 def func_of(ln):
   name = '?'
   for start, n in funcs:
@@ -46,7 +62,8 @@ for o in sorted(f for f in os.listdir(objdir) if f.startswith('bx_kernels_') and
   td = tempfile.mkdtemp()
   subprocess.check_call(['cuobjdump', '-xelf', 'all', os.path.join(objdir, o)], cwd=td, stdout=subprocess.DEVNULL)
   cubins += [os.path.join(td, f) for f in os.listdir(td) if f.endswith('.cubin')]
-addr_line, addr_op, found = {}, {}, []
+addr_line, addr_op, addr_math, found = {}, {}, {}, []
+curm = None
 for cubin in cubins:
   dis = subprocess.run(['nvdisasm', '-g', '-c', cubin], capture_output=True, text=True).stdout
   on, cur = False, 0
@@ -60,10 +77,15 @@ for cubin in cubins:
     m = re.search(r'//## File ".*bx_step_kernel\.cuh", line (\d+)', l)
     if m:
       cur = int(m.group(1))
+      curm = None
+    m = re.search(r'//## File ".*bx_math\.cuh", line (\d+)', l)
+    if m:
+      curm = mfunc_of(int(m.group(1)))
     m = re.match(r'\s+/\*([0-9a-f]{4,6})\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)', l)
     if m:
       addr_line[int(m.group(1), 16)] = cur
       addr_op[int(m.group(1), 16)] = m.group(2)
+      addr_math[int(m.group(1), 16)] = curm
 if len(found) != 1:
   print('kernel regex matched %d sections:' % len(found))
   for f in found[:20]:
@@ -101,6 +123,11 @@ print('%-28s %7s %7s  top stalls' % ('function', 'inst%', 'samp%'))
 for f, (e, s, st) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
   print('%-28s %6.1f%% %6.1f%%  %s' % (f, 100 * e / tot_e, 100 * s / max(tot_s, 1),
         ' '.join('%s:%d' % kv for kv in st.most_common(4))))
+if '--static' in sys.argv:
+  st = collections.Counter(addr_math.get(a) or func_of(l) for a, l in addr_line.items())
+  print('\nstatic SASS instructions by function (total %d = %d KB):' % (len(addr_line), len(addr_line) * 16 // 1024))
+  for f, n in st.most_common(40):
+    print('  %-28s %5d  %5.1f KB' % (f, n, n * 16 / 1024))
 if '--ops' in sys.argv:
   print('\nopcode mix (warp instructions executed):')
   for op, n in ops.most_common(24):

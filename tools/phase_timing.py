@@ -14,7 +14,10 @@ from brax_b200 import build as bb, lib as bl  # noqa: E402
 
 out = os.path.join(ROOT, 'build', 'libbrax_b200_pt.so')
 os.makedirs(os.path.dirname(out), exist_ok=True)
-bb.build(extra=['-DBX_PHASE_TIMING'], out=out, force='--build-only' in sys.argv)
+if os.environ.get('BX_PT_LIB'):   # a prebuilt timing library (experiments)
+  out = os.path.join(ROOT, os.environ['BX_PT_LIB'])
+else:
+  bb.build(extra=['-DBX_PHASE_TIMING'], out=out, force='--build-only' in sys.argv)
 if '--build-only' in sys.argv:
   sys.exit(0)
 bl.LIB_PATH = out
@@ -26,7 +29,7 @@ s = load_system(name)
 if len(sys.argv) > 3:
   s.configure(int(sys.argv[3]), int(sys.argv[4]) if len(sys.argv) > 4 else 0)
 lib = bl.load()
-dbg = torch.zeros(32 + 4 * 4096, dtype=torch.int64, device='cuda')
+dbg = torch.zeros(32 + 4 * 4096 + 64, dtype=torch.int64, device='cuda')
 lib.bx_debug_set_buffer.argtypes = [C.c_void_p]
 q = s.default_qp(batch=b, device='cuda')
 rng = np.random.default_rng(0)
@@ -46,6 +49,9 @@ print('%s B=%d: %.0f cycles/step (%.1f us @1.965GHz)' % (name, b, tot, tot / 196
 for i, (nm, x) in enumerate(zip(names, v)):
   print('  %-9s %8.0f  %5.1f%%   warp 0 busy %8.0f' % (nm, x, 100 * x / tot, v[16 + i]))
 
+mk = v[32 + 4 * 4096:]
+if mk.any():
+  print('within-item markers (warp 0, cycles/step):', [int(x) for x in mk[:16]], [int(x) for x in mk[16:32]])
 # per-CTA records of the LAST launch: tiles per SM, duration by co-residency, start skew
 ntile = min((b + 31) // 32, 4096)
 rec = dbg.cpu().numpy()[32:32 + 4 * ntile].reshape(ntile, 4)
