@@ -43,7 +43,8 @@ SM_COUNT = 148
 L2_BYTES = 126 * 1000 * 1000  # B200 L2 (B200_PROFILING.md)
 # dram__bytes_read.sum + dram__bytes_write.sum of one bx_step_kernel launch at the
 # bench workload, from the committed `ncu --set full` capture (profiles/); bytes.
-NCU_TRAFFIC = {'ant': 4603904}
+# (reads only: the 11.3 MB of outputs were still in L2 when the kernel ended)
+NCU_TRAFFIC = {'ant': 4592128}
 FP32_LANES = 128
 
 
@@ -337,6 +338,7 @@ def run_gpu(args, desc):
   value = world * b * args.steps / (ms_total * 1e-3)
   value_b2b = world * b * args.steps / (ms_b2b * 1e-3)
   value_flushed = world * b * args.steps / (ms_flushed * 1e-3)
+  value_flushed_median = world * b / (ms_fl_steps[len(ms_fl_steps) // 2] * 1e-3)
   e2e_value = world * b * e2e_steps / t_e2e
 
   if rank == 0:
@@ -361,13 +363,16 @@ def run_gpu(args, desc):
             'env_batches': nsets,
             'threads_per_tile': s_threads(s), 'bodies': n, 'contacts': k, 'act': a},
         'value_l2_flushed': value_flushed,
+        'value_l2_flushed_median_step': value_flushed_median,
         'ms_per_step_l2_flushed': ms_flushed / args.steps,
         'ms_l2_flushed_min_median_max': [ms_fl_steps[0], ms_fl_steps[len(ms_fl_steps) // 2], ms_fl_steps[-1]],
         'value_back_to_back': value_b2b,
         'wall_s_timed_loop_incl_spin': t_wall,
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d,
                 'd2h_bytes_per_step': d2h, 'steps': e2e_steps, 'finite': e2e_finite,
-                'path': 'System.step(numpy QP, out=HostBuffers) -> bx_step_host: chunked H2D/step/D2H pipeline on 3 streams, page-locked buffers'},
+                'path': 'System.step(numpy QP on page-locked HostBuffers, out=HostBuffers) -> bx_step_host: '
+                        'one launch working on the mapped host memory (tiles pull inputs / push outputs '
+                        'over PCIe); pageable callers get the chunked 3-stream copy pipeline'},
         'gpu_launches': int(launches),
         'clocks': clocks, 'finite': finite,
     }

@@ -18,5 +18,5 @@ CMD="python bench.py --steps 3 --warmup 3 --no-cpu"
 $CMD > $O/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $O/launches.csv $CMD > $O/ncu1.log 2>&1
 $CMD > $O/plain2.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:bx_step -s 3 -c 1 -o $O/prof $CMD > $O/ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:bx_step -s 25 -c 1 -o $O/prof $CMD > $O/ncu2.log 2>&1
 tail -3 $O/pytest.log; cat $O/smoke.log | tail -2; cat $O/bench_ant.json
