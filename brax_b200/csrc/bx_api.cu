@@ -116,12 +116,14 @@ static int validate(const bx_system_desc* d) {
 }
 
 // Flattens the description into the tables of bx_tables.h.
-static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int32_t>* ti_out,
-                         std::vector<float>* tf_out) {
+static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<int32_t>* ti_out,
+                           std::vector<float>* tf_out, int rows_per_item) {
   BxHeader& h = *hh;
   memset(&h, 0, sizeof(h));
   std::vector<int32_t>& ti = *ti_out;
   std::vector<float>& tf = *tf_out;  // 4 floats per quad
+  ti.clear();
+  tf.clear();
   const int nb = d->num_bodies, nj = d->num_joints, na = d->num_actuators, nf = d->num_forces;
   const bool spring = d->dynamics_mode == BX_MODE_LEGACY_SPRING;
   const int bqn = spring ? BX_BODY_QUADS_SPRING : BX_BODY_QUADS_PBD;
@@ -142,6 +144,19 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
     for (int c = 0; c < d->pairs[i].n_contacts; c++) rows.push_back({i, c});
   const int nk = static_cast<int>(rows.size());
   h.nk = nk;
+  // contact items: up to rows_per_item consecutive rows of one pair share one
+  // slot-list entry per side
+  std::vector<int> item_k0, item_n, item_of(nk, 0);
+  for (int k = 0; k < nk;) {
+    int n = 1;
+    while (n < rows_per_item && k + n < nk && rows[k + n].pair == rows[k].pair) n++;
+    for (int r = 0; r < n; r++) item_of[k + r] = static_cast<int>(item_k0.size());
+    item_k0.push_back(k);
+    item_n.push_back(n);
+    k += n;
+  }
+  const int nci = static_cast<int>(item_k0.size());
+  h.nci = nci;
 
   // slots
   std::vector<int> cslot(nb, -1), aslot(nb, -1);
@@ -246,25 +261,26 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   }
   // contact intervals: per body, per collider group, a rows then b rows
   // (colliders.py:222-228)
-  std::vector<int> cslot_a(nk, 0), cslot_b(nk, 0);
-  std::vector<std::vector<int>> cgroups(nb);  // (base, count) pairs
+  std::vector<int> cslot_a(nci, 0), cslot_b(nci, 0);
+  std::vector<std::vector<int>> cgroups(nb);  // (base, entries) pairs
   int c_quads = 0;
+  auto pair_of_item = [&](int i) -> const bx_pair& { return d->pairs[rows[item_k0[i]].pair]; };
   for (int b = 0; b < nb; b++) {
-    for (int k0 = 0; k0 < nk;) {
-      int g = d->pairs[rows[k0].pair].group, k1 = k0;
-      while (k1 < nk && d->pairs[rows[k1].pair].group == g) k1++;
+    for (int i0 = 0; i0 < nci;) {
+      int g = pair_of_item(i0).group, i1 = i0;
+      while (i1 < nci && pair_of_item(i1).group == g) i1++;
       const int base = c_quads;
-      for (int k = k0; k < k1; k++)
-        if (d->pairs[rows[k].pair].body_a == b) { cslot_a[k] = c_quads; c_quads += 2; }
-      for (int k = k0; k < k1; k++)
-        if (d->pairs[rows[k].pair].two_way && d->pairs[rows[k].pair].body_b == b) {
-          cslot_b[k] = c_quads; c_quads += 2;
-        }
+      for (int i = i0; i < i1; i++)
+        if (pair_of_item(i).body_a == b) { cslot_a[i] = c_quads; c_quads += 2; }
+      for (int i = i0; i < i1; i++)
+        if (pair_of_item(i).two_way && pair_of_item(i).body_b == b) { cslot_b[i] = c_quads; c_quads += 2; }
       if (c_quads > base) { cgroups[b].push_back(base); cgroups[b].push_back((c_quads - base) / 2); }
-      k0 = k1;
+      i0 = i1;
     }
   }
   int js = std::max(std::max(t_quads, j_quads), c_quads);
+  const int cd_rows = spring ? 0 : (nk + 3) / 4;
+  const int ct_rows = nk + d->num_pairs + cd_rows;
   {
     // region JS doubles as the staging buffer of the bulk-copy I/O: it must hold
     // the largest output span of a tile, and JS..end must hold all input spans.
@@ -272,7 +288,7 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
     const int max_out = 32 * std::max(4 * nb, 3 * nk);
     js = std::max(js, (max_out + row_floats - 1) / row_floats);
     const int in_floats = 32 * (13 * nb + d->act_size);
-    const int tail = 2 * nk + (spring ? 0 : 2 * ncb) + 2 * ncb + nab + (spring ? 2 * nb : 0);
+    const int tail = ct_rows + (spring ? 0 : 2 * ncb) + 2 * ncb + nab + (spring ? 2 * nb : 0);
     js = std::max(js, (in_floats + row_floats - 1) / row_floats - tail);
   }
 
@@ -280,7 +296,9 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   int r = nb * bqn;
   h.q_act = r; r += (d->act_size + 3) / 4;
   h.q_js = r; r += js;
-  h.q_ct = r; r += 2 * nk;
+  h.q_ct = r; r += nk;
+  h.q_cn = r; r += d->num_pairs;
+  h.q_cd = r; r += cd_rows;
   h.q_pre = r; r += spring ? 0 : 2 * ncb;
   h.q_ic = r; r += 2 * ncb;   // q_ic, q_ia, q_ij contiguous: zeroed together
   h.q_ia = r; r += nab;
@@ -308,8 +326,8 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
     adj.insert(adj.end(), cgroups[b].begin(), cgroups[b].end());
     rec[BI_CG_N] = static_cast<int>(cgroups[b].size() / 2);
     rec[BI_ROW_OFF] = static_cast<int>(adj.size());
-    for (int k = 0; k < nk; k++)
-      if (d->pairs[rows[k].pair].body_a == b) adj.push_back(k);
+    for (int i = 0; i < nci; i++)
+      if (pair_of_item(i).body_a == b) adj.push_back(i);
     rec[BI_ROW_N] = static_cast<int>(adj.size()) - rec[BI_ROW_OFF];
   }
   std::vector<int32_t> forder;
@@ -346,9 +364,12 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   for (int k = 0; k < nk; k++) {
     const bx_pair& p = d->pairs[rows[k].pair];
     ti.push_back(p.kind); ti.push_back(p.two_way); ti.push_back(p.body_a);
-    ti.push_back(p.body_b); ti.push_back(cslot_a[k]); ti.push_back(cslot_b[k]);
-    ti.push_back(0); ti.push_back(0);
+    ti.push_back(p.body_b); ti.push_back(cslot_a[item_of[k]]); ti.push_back(cslot_b[item_of[k]]);
+    ti.push_back(rows[k].pair); ti.push_back(0);
   }
+  h.io_citem = static_cast<int>(ti.size());
+  for (int i = 0; i < nci; i++) { ti.push_back(item_k0[i]); ti.push_back(item_n[i]); }
+  align4();
   h.io_adj = static_cast<int>(ti.size());
   ti.insert(ti.end(), adj.begin(), adj.end());
   h.io_forder = static_cast<int>(ti.size());
@@ -412,10 +433,10 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
     std::vector<int> mp, mn, me;
     for (int k = 0; k < nk; k++) {
       for (int x = 0; x < 3; x++) {
-        mp.push_back((h.q_ct + 2 * k) * RF + x);
-        mn.push_back((h.q_ct + 2 * k + 1) * RF + x);
+        mp.push_back((h.q_ct + k) * RF + x);
+        mn.push_back((h.q_cn + rows[k].pair) * RF + x);
       }
-      me.push_back((h.q_ct + 2 * k) * RF + 3);
+      me.push_back((h.q_ct + k) * RF + 3);
     }
     h.seg_out[10] = seg(3 * nk, 0.f, mp);
     h.seg_out[11] = seg(3 * nk, 0.f, mn);
@@ -435,6 +456,23 @@ static void build_tables(const bx_system_desc* d, BxHeader* hh, std::vector<int3
   h.collide_scale = d->collide_scale;
   h.vth = d->velocity_threshold;
   h.inv_2h = 1.f / (2.f * d->dt_sub);
+}
+
+static size_t tile_bytes(const BxHeader& h);
+
+// Rows per contact item: 1 (every row its own slot-list entry: most parallelism,
+// the reference's exact summation order) unless pairing the rows is what lets two
+// tiles share an SM (fetch: 8 box corners per collider).
+static void build_tables(const bx_system_desc* d, BxHeader* h, std::vector<int32_t>* ti,
+                         std::vector<float>* tf) {
+  build_tables_g(d, h, ti, tf, 1);
+  auto two_fit = [](const BxHeader& x) { return 2 * (tile_bytes(x) + 1024) <= 233472; };
+  if (two_fit(*h)) return;
+  BxHeader h2;
+  std::vector<int32_t> ti2;
+  std::vector<float> tf2;
+  build_tables_g(d, &h2, &ti2, &tf2, 2);
+  if (two_fit(h2)) { *h = h2; ti->swap(ti2); tf->swap(tf2); }
 }
 
 // The kernels live in one translation unit per launch bound (bx_kernels.cu); the
@@ -554,7 +592,8 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
     for (int i = 0; i < 5; i++) {
       const int w = cand[i];
       const double cost = pen[i] * (rounds(s->h.nj, w) * cj + rounds(s->h.na, w) * ca +
-                                    rounds(s->h.nb, w) * cb + rounds(s->h.nk, w) * ck);
+                                    rounds(s->h.nb, w) * cb +
+                                    rounds(s->h.nci, w) * ck * (s->h.nci ? s->h.nk / s->h.nci : 1));
       if (cost < best - 1e-9) { best = cost; s->warps = w; }
     }
   }

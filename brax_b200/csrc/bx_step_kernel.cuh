@@ -610,6 +610,31 @@ BXS void phase_body_joint_update(const Ctx& c, const BxHeader& h, bool project) 
 // ---- contacts -----------------------------------------------------------------
 struct Contact { V3 pos, vel, normal; float pen; };
 
+// One contact ITEM = 1 or 2 consecutive rows of one collider pair (bx_tables.h).  Its
+// rows add their per-body deltas here in row order; the item then writes ONE entry per
+// side into the body's slot list: {linear xyz, rows with a non-zero linear part},
+// {second part}.  (The row count replaces the `any(x != 0)` test of the gather,
+// colliders.py:187-196.)
+struct CAcc {
+  float4 la, sa, lb, sb;
+};
+BXS CAcc cacc_zero() {
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  CAcc a; a.la = z; a.sa = z; a.lb = z; a.sb = z;
+  return a;
+}
+BXS void cacc_add(float4& l, float4& s2, V3 lin, float4 sec) {
+  l.x += lin.x; l.y += lin.y; l.z += lin.z;
+  l.w += (lin.x != 0.f || lin.y != 0.f || lin.z != 0.f) ? 1.f : 0.f;
+  s2.x += sec.x; s2.y += sec.y; s2.z += sec.z; s2.w += sec.w;
+}
+BXS float4 wxyz(Q4 q) { return make_float4(q.w, q.x, q.y, q.z); }
+BXS float4 xyz0(V3 v) { return make_float4(v.x, v.y, v.z, 0.f); }
+// scalar k of a packed scalar region (4 per quad row)
+BXS float& scalar_at(const Ctx& c, int row0, int k) {
+  return reinterpret_cast<float*>(&QROW(c, row0 + (k >> 2)))[k & 3];
+}
+
 // geometry.py:360-374
 BXS V3 closest_segment_point_and_dist(V3 a, V3 b, V3 pt, float* d2) {
   V3 ab = b - a;
@@ -691,12 +716,11 @@ BXS Contact contact_fn(int kind, const float4* cq, V3 pa, Q4 ra, V3 va, V3 wa, V
 // colliders.py:198-240, OneWay :306-377, TwoWay :495-582.  Row k keeps its
 // contact in quads CT+2k = {pos, pen}, {normal, dlambda} and its deltas
 // (a: dpos, drot [, b: dpos, drot]) in quads JS+delta_off(k).
-BXS void c1_row(const Ctx& c, const BxHeader& h, int k) {
+BXS void c1_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
   typedef Lay<BX_MODE_PBD> L;
   const int co = 2 * c.cur, po = 2 * (c.cur ^ 1);
     const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);  // kind two_way a b
-    const int4 cs4 = ldi4(c.ti + h.io_contact + k * CI_STRIDE + 4);  // slot_a slot_b
-    const int rd = h.q_js + cs4.x, rdb = h.q_js + cs4.y;
+    const int pair_row = c.ti[h.io_contact + k * CI_STRIDE + CI_PAIR];
     const float4* cq = c.tf + h.fo_contact + k * CQ_STRIDE;
     const int a = ci.z, b = ci.w;
     const bool two_way = BXF_IS(ci.y != 0, BXF_TWO_WAY, BXF_ONE_WAY);
@@ -737,7 +761,7 @@ BXS void c1_row(const Ctx& c, const BxHeader& h, int k) {
       V3 pt = ((dlt * n2) * sm) * cm;
       dpos = dpos + cs * vdiv(pt, ma);
       drot = drot + cs * (.5f * vec_quat_mul(iia * cross(rp, pt), ra));
-      stv(c, rd, dpos); stq(c, rd + 1, drot);
+      cacc_add(acc.la, acc.sa, dpos, wxyz(drot));
       dl_out = dl * cm;
     } else {
       const float4* bqb = c.tf + h.fo_body + b * BQ_STRIDE;
@@ -771,16 +795,33 @@ BXS void c1_row(const Ctx& c, const BxHeader& h, int k) {
       dpb = dpb + cs * vdiv(-pt, mb);
       dra = dra + cs * (.5f * vec_quat_mul(iia * cross(xa, pt), ra));
       drb = drb + cs * (.5f * vec_quat_mul(iib * cross(xb, -pt), rb));
-      stv(c, rd, dpa); stq(c, rd + 1, dra);
-      stv(c, rdb, dpb); stq(c, rdb + 1, drb);
+      cacc_add(acc.la, acc.sa, dpa, wxyz(dra));
+      cacc_add(acc.lb, acc.sb, dpb, wxyz(drb));
       dl_out = dl;  // un-masked (colliders.py:580)
     }
-    const int rc_ = h.q_ct + 2 * k;
-    stv4(c, rc_, ct.pos, ct.pen);
-    stv4(c, rc_ + 1, ct.normal, dl_out);
+    stv4(c, h.q_ct + k, ct.pos, ct.pen);
+    stv(c, h.q_cn + pair_row, ct.normal);  // the same for every row of the pair
+    scalar_at(c, h.q_cd, k) = dl_out;
+}
+// writes the entry (entries) of one item into the slot lists of its bodies
+BXS void cacc_store(const Ctx& c, const BxHeader& h, int k0, const CAcc& acc) {
+  const int4 cs4 = ldi4(c.ti + h.io_contact + k0 * CI_STRIDE + 4);  // slot_a slot_b pair .
+  QROW(c, h.q_js + cs4.x) = acc.la;
+  QROW(c, h.q_js + cs4.x + 1) = acc.sa;
+  if (BXF_IS(c.ti[h.io_contact + k0 * CI_STRIDE + CI_TWO_WAY] != 0, BXF_TWO_WAY, BXF_ONE_WAY)) {
+    QROW(c, h.q_js + cs4.y) = acc.lb;
+    QROW(c, h.q_js + cs4.y + 1) = acc.sb;
+  }
+}
+BXS void c1_item(const Ctx& c, const BxHeader& h, int item) {
+  const int2 it = *reinterpret_cast<const int2*>(c.ti + h.io_citem + 2 * item);  // first row, rows
+  CAcc acc = cacc_zero();
+#pragma unroll 1
+  for (int r = 0; r < it.y; r++) c1_row(c, h, it.x + r, acc);
+  cacc_store(c, h, it.x, acc);
 }
 BXS void phase_contacts_position(const Ctx& c, const BxHeader& h) {
-  for (int k = c.warp; k < h.nk; k += c.nwarp) c1_row(c, h, k);
+  for (int i = c.warp; i < h.nci; i += c.nwarp) c1_item(c, h, i);
 }
 
 // Per-body scatter-and-average of the contact rows' deltas, one collider group
@@ -800,7 +841,7 @@ BXS void gather_contact_deltas(const Ctx& c, const BxHeader& h, int cg_off, int 
 #pragma unroll 1
     for (int i = 0; i < n; i++) {
       const float4 l = QROW(c, base + 2 * i), s = QROW(c, base + 2 * i + 1);
-      cnt += (l.x != 0.f || l.y != 0.f || l.z != 0.f) ? 1.f : 0.f;
+      cnt += l.w;  // rows of this entry with a non-zero linear part
       ls.x += l.x; ls.y += l.y; ls.z += l.z;
       ss.x += s.x; ss.y += s.y; ss.z += s.z; ss.w += s.w;
     }
@@ -848,20 +889,19 @@ BXS void phase_body_contact_update(const Ctx& c, const BxHeader& h) {
 // ---- phase C2 (pbd): _velocity_contact for every contact row ------------------
 // colliders.py:155-196, OneWay :379-442, TwoWay :584-658.  Deltas (a: dvel, dang
 // [, b: dvel, dang]) go to quads JS+delta_off(k).
-BXS void c2_row(const Ctx& c, const BxHeader& h, int k) {
+BXS void c2_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
   typedef Lay<BX_MODE_PBD> L;
   const int co = 2 * c.cur;
     const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);
-    const int4 cs4 = ldi4(c.ti + h.io_contact + k * CI_STRIDE + 4);  // slot_a slot_b
-    const int rd = h.q_js + cs4.x, rdb = h.q_js + cs4.y;
+    const int pair_row = c.ti[h.io_contact + k * CI_STRIDE + CI_PAIR];
     const float4 mat = c.tf[h.fo_contact + k * CQ_STRIDE + CQ_MAT];
     const int a = ci.z, b = ci.w;
     const bool two_way = BXF_IS(ci.y != 0, BXF_TWO_WAY, BXF_ONE_WAY);
     const float4* bqa = c.tf + h.fo_body + a * BQ_STRIDE;
     const int ra0 = L::BQ * a;
-    const float4 c0 = QROW(c, h.q_ct + 2 * k), c1 = QROW(c, h.q_ct + 2 * k + 1);
-    V3 cpos = f3(c0), n = f3(c1);
-    const float pen = c0.w, dlambda = c1.w;
+    const float4 c0 = QROW(c, h.q_ct + k);
+    V3 cpos = f3(c0), n = ldv(c, h.q_cn + pair_row);
+    const float pen = c0.w, dlambda = scalar_at(c, h.q_cd, k);
     V3 pa = ldv(c, ra0 + co);
     V3 ra = cpos - pa;
     V3 iia = f3(bqa[BQ_INV_INERTIA]);
@@ -890,8 +930,7 @@ BXS void c2_row(const Ctx& c, const BxHeader& h, int k) {
       float dlr = bx_div(cc, w1 + 1e-6f);
       float sink = v_n_old <= -h.vth ? 1.f : 0.f;
       V3 p = (((dlr * n2) * sink) + p_dyn) * stat;
-      stv(c, rd, vdiv(p, ma));
-      stv(c, rd + 1, cross(iia * ra, p));
+      cacc_add(acc.la, acc.sa, vdiv(p, ma), xyz0(cross(iia * ra, p)));
     } else {
       const float4* bqb = c.tf + h.fo_body + b * BQ_STRIDE;
       const int rb0 = L::BQ * b;
@@ -922,14 +961,19 @@ BXS void c2_row(const Ctx& c, const BxHeader& h, int k) {
       float dlr = bx_div(cc, w1r + w2r + 1e-6f);
       float sink = v_n_old <= 0.f ? 1.f : 0.f;
       V3 p = (((dlr * n2) * sink) + p_dyn) * stat;
-      stv(c, rd, vdiv(p, ma));
-      stv(c, rd + 1, cross(iia * ra, p));
-      stv(c, rdb, vdiv(-p, mb));
-      stv(c, rdb + 1, cross(iib * rb, -p));
+      cacc_add(acc.la, acc.sa, vdiv(p, ma), xyz0(cross(iia * ra, p)));
+      cacc_add(acc.lb, acc.sb, vdiv(-p, mb), xyz0(cross(iib * rb, -p)));
     }
 }
+BXS void c2_item(const Ctx& c, const BxHeader& h, int item) {
+  const int2 it = *reinterpret_cast<const int2*>(c.ti + h.io_citem + 2 * item);
+  CAcc acc = cacc_zero();
+#pragma unroll 1
+  for (int r = 0; r < it.y; r++) c2_row(c, h, it.x + r, acc);
+  cacc_store(c, h, it.x, acc);
+}
 BXS void phase_contacts_velocity(const Ctx& c, const BxHeader& h) {
-  for (int k = c.warp; k < h.nk; k += c.nwarp) c2_row(c, h, k);
+  for (int i = c.warp; i < h.nci; i += c.nwarp) c2_item(c, h, i);
 }
 
 // ---- phase B4: velocity-level contact update + Info.contact -----------------
@@ -969,13 +1013,13 @@ BXS void phase_contacts_fused(const Ctx& c, const BxHeader& h) {
     const int i = base + (flip ? c.nwarp - 1 - c.warp : c.warp);
     if (i >= h.nb) continue;
     const int b = c.ti[h.io_forder + i];
-    const int4 b3 = ldi4(c.ti + h.io_body + b * BI_STRIDE + 12);  // row_off row_n
+    const int4 b3 = ldi4(c.ti + h.io_body + b * BI_STRIDE + 12);  // item_off item_n
     const int32_t* rows = c.ti + h.io_adj + b3.x;
 #pragma unroll 1
-    for (int r = 0; r < b3.y; r++) c1_row(c, h, rows[r]);
+    for (int r = 0; r < b3.y; r++) c1_item(c, h, rows[r]);
     b3_body(c, h, b);
 #pragma unroll 1
-    for (int r = 0; r < b3.y; r++) c2_row(c, h, rows[r]);
+    for (int r = 0; r < b3.y; r++) c2_item(c, h, rows[r]);
     if (b3.y > 0) b4_body<BX_MODE_PBD>(c, h, 1e-6f, b);
   }
 }
@@ -1101,12 +1145,11 @@ BXS void phase_body_acc_spring(const Ctx& c, const BxHeader& h) {
 
 // phase S4: contact_fn + velocity-level _contact (colliders.py:116-153,
 // OneWay :267-304, TwoWay :449-493).
-BXS void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
+BXS void spring_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
   typedef Lay<BX_MODE_LEGACY_SPRING> L;
-  for (int k = c.warp; k < h.nk; k += c.nwarp) {
+  {
     const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);
-    const int4 cs4 = ldi4(c.ti + h.io_contact + k * CI_STRIDE + 4);  // slot_a slot_b
-    const int rd = h.q_js + cs4.x, rdb = h.q_js + cs4.y;
+    const int pair_row = c.ti[h.io_contact + k * CI_STRIDE + CI_PAIR];
     const float4* cq = c.tf + h.fo_contact + k * CQ_STRIDE;
     const int a = ci.z, b = ci.w;
     const bool two_way = BXF_IS(ci.y != 0, BXF_TWO_WAY, BXF_ONE_WAY);
@@ -1143,17 +1186,23 @@ BXS void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
     V3 dvn, dan, dvd, dad;
     body_impulse(mass_a, iia, pa, imp * n, ct.pos, &dvn, &dan);
     body_impulse(mass_a, iia, pa, (-impd) * dir, ct.pos, &dvd, &dad);
-    stv(c, rd, dvn * apn + dvd * apd);
-    stv(c, rd + 1, dan * apn + dad * apd);
+    cacc_add(acc.la, acc.sa, dvn * apn + dvd * apd, xyz0(dan * apn + dad * apd));
     if (two_way) {
       body_impulse(mass_b, iib, pb, (-imp) * n, ct.pos, &dvn, &dan);
       body_impulse(mass_b, iib, pb, impd * dir, ct.pos, &dvd, &dad);
-      stv(c, rdb, dvn * apn + dvd * apd);
-      stv(c, rdb + 1, dan * apn + dad * apd);
+      cacc_add(acc.lb, acc.sb, dvn * apn + dvd * apd, xyz0(dan * apn + dad * apd));
     }
-    const int rc_ = h.q_ct + 2 * k;
-    stv4(c, rc_, ct.pos, ct.pen);
-    stv4(c, rc_ + 1, ct.normal, 0.f);
+    stv4(c, h.q_ct + k, ct.pos, ct.pen);
+    stv(c, h.q_cn + pair_row, ct.normal);
+  }
+}
+BXS void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
+  for (int i = c.warp; i < h.nci; i += c.nwarp) {
+    const int2 it = *reinterpret_cast<const int2*>(c.ti + h.io_citem + 2 * i);
+    CAcc acc = cacc_zero();
+#pragma unroll 1
+    for (int r = 0; r < it.y; r++) spring_row(c, h, it.x + r, acc);
+    cacc_store(c, h, it.x, acc);
   }
 }
 
@@ -1264,11 +1313,8 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
       const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int i = threadIdx.x; i < h.n_zero * QS; i += blockDim.x) sq[h.q_ic * QS + i] = z;
       if (h.iters == 0)  // contact_penetration = -1 (system.py:84)
-        for (int i = threadIdx.x; i < h.nk * QS; i += blockDim.x) {
-          const int k = i / QS, e = i - k * QS;
-          sq[(h.q_ct + 2 * k) * QS + e] = make_float4(0.f, 0.f, 0.f, -1.f);
-          sq[(h.q_ct + 2 * k + 1) * QS + e] = z;
-        }
+        for (int i = threadIdx.x; i < (h.q_pre - h.q_ct) * QS; i += blockDim.x)
+          sq[h.q_ct * QS + i] = i < h.nk * QS ? make_float4(0.f, 0.f, 0.f, -1.f) : z;
     }
     __syncthreads();
     PT(1);

@@ -59,7 +59,7 @@ enum {
   BI_F_N = 9,
   BI_CG_OFF = 10,  // contact groups of this body: cg_n pairs (base, count) in the adj
   BI_CG_N = 11,    // table; each entry = 2 quads (linear part, second part)
-  BI_ROW_OFF = 12,  // contact rows whose body_a is this body (adj table), fused path
+  BI_ROW_OFF = 12,  // contact items whose body_a is this body (adj table), fused path
   BI_ROW_N = 13,
   BI_STRIDE = 16,
 
@@ -87,13 +87,16 @@ enum {
   FI_IDX = 2,  // [3]
   FI_STRIDE = 8,
 
-  // contact row: 2 x int4 {kind, two_way, body_a, body_b} {slot_a, slot_b, 0, 0}
+  // contact row: 2 x int4 {kind, two_way, body_a, body_b} {slot_a, slot_b, pair, 0}.
+  // slot_a / slot_b are those of the row's ITEM (1 or 2 consecutive rows of one pair
+  // that share one slot-list entry per side); `pair` is the row of the pair's normal.
   CI_KIND = 0,
   CI_TWO_WAY = 1,
   CI_BODY_A = 2,
   CI_BODY_B = 3,
   CI_SLOT_A = 4,
   CI_SLOT_B = 5,
+  CI_PAIR = 6,
   CI_STRIDE = 8,
 };
 
@@ -113,6 +116,7 @@ struct BxHeader {
   int32_t mode;      // BX_MODE_*
   int32_t iters;     // pbd: substeps/2 ; legacy_spring: substeps
   int32_t nb, nj, na, nf, nk;  // bodies, joints, actuators, forces, contact rows
+  int32_t nci;       // contact items (1 or 2 rows each); io_citem: {first row, rows} per item
   int32_t act_size;
   int32_t ncb;  // bodies that appear in a collider (slots for PRE/INFO_C)
   int32_t nab;  // bodies that appear in an actuated joint (slots for INFO_A)
@@ -120,9 +124,12 @@ struct BxHeader {
   int32_t n_ints, n_fquads;
   int32_t io_body, io_joint, io_act, io_force, io_contact, io_adj;  // int offs
   int32_t io_forder;  // body order of the fused contact section (contact bodies first)
+  int32_t io_citem;
   int32_t fo_body, fo_joint, fo_act, fo_force, fo_contact;          // quad offs
   // state quad rows (each row = 32 env slots x float4, + 1 pad quad)
-  int32_t q_act, q_js, q_ct, q_pre, q_ic, q_ia, q_ij;
+  // q_ct: one quad {pos, penetration} per contact row; q_cn: one quad {normal} per
+  // collider pair; q_cd: dlambda of the rows, 4 per quad (pbd)
+  int32_t q_act, q_js, q_ct, q_cn, q_cd, q_pre, q_ic, q_ia, q_ij;
   int32_t n_quads;
   int32_t n_zero;  // quads from q_ic to zero at the start of every step
   BxSeg seg_in[BX_SEG_IN];
