@@ -76,7 +76,7 @@ ACCUMULATORS = ('contact_vel', 'contact_ang', 'joint_vel', 'joint_ang',
                 'actuator_vel', 'actuator_ang')
 
 
-def check_step(name, ins, act, got, strict_frac=0.90):
+def check_step(name, ins, act, got, strict_frac=0.90, outlier_frac=OUTLIER_FRAC):
   """Kernel output `got` vs the float32 oracle, with the float64 oracle run on
   the same inputs measuring how ill-conditioned each env's step is in float32.
 
@@ -89,7 +89,7 @@ def check_step(name, ins, act, got, strict_frac=0.90):
   ref = _oracle(name, np.float32).step(*ins, act)
   r64 = _oracle(name, np.float64).step(*ins, act)
   b = ref['pos'].shape[0]
-  allowed = int(OUTLIER_FRAC * b) if b >= 200 else 0
+  allowed = int(outlier_frac * b) if b >= 200 else 0
   stats = {}
   vel_floor = VEL_ULPS * 6e-8 / util.load_desc(name).dt_sub
   bad_env = np.zeros(b, bool)
@@ -193,7 +193,9 @@ def _harvest(s, b, steps, seed):
 
 @pytest.mark.parametrize('name,b,steps', [
     ('ant', 2048, 30), ('humanoid', 2048, 30), ('grasp', 1024, 20),
-    ('fetch', 1024, 20), ('ant_spring', 1024, 30), ('humanoid_spring', 1024, 30)])
+    ('fetch', 1024, 20), ('ant_spring', 1024, 30), ('humanoid_spring', 1024, 30),
+    # two rows per contact item (pbd and legacy_spring), many rows per body, two-way pairs
+    ('fetch_spring', 1024, 20), ('humanoid_standup', 1024, 20), ('half_cheetah', 1024, 6)])
 def test_single_step_on_harvested_states(name, b, steps):
   torch = _torch()
   s = _system(name)
@@ -204,7 +206,11 @@ def test_single_step_on_harvested_states(name, b, steps):
   torch.cuda.synchronize()
   got = _flat(qo, info)
   ins = [getattr(qp, k).cpu().numpy() for k in util.QP_KEYS]
-  ref, _ = check_step(name, ins, act, got)
+  # half_cheetah under random torques spins at hundreds of rad/s: two float32 builds of
+  # the ORACLE (multiply-adds fused or not) already disagree beyond the policy in 3.1 %
+  # of such envs (tools/fma_conditioning.py, profiles/r01_float32_conditioning.txt)
+  frac = 0.06 if name == 'half_cheetah' else OUTLIER_FRAC
+  ref, _ = check_step(name, ins, act, got, outlier_frac=frac)
   # at least some contacts must be active for the test to mean anything
   assert (ref['contact_penetration'] > 0).mean() > 0.02, name
 
