@@ -300,6 +300,21 @@ def run_gpu(args, desc):
     q2, _ = s.step(q2, acts[args.warmup + i])
   e1.record()
   torch.cuda.synchronize()
+  # "next" row N2: T steps per launch (bx_rollout, actions [T,B,A]); the
+  # state stays in shared memory between the steps of a launch.  Reported beside value.
+  roll_t = min(10, args.steps)
+  n_roll = max(1, args.steps // roll_t)
+  er = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_roll)]
+  q3, _ = s.rollout(qps[0], acts[:roll_t])   # warm-up of the multi-step launch
+  torch.cuda._sleep(spin_cycles)
+  for i in range(n_roll):
+    j = i % nsets
+    a0 = args.warmup + (i * roll_t) % max(1, args.steps - roll_t + 1)
+    er[i][0].record()
+    qps[j], _ = s.rollout(qps[j], acts[a0:a0 + roll_t])
+    er[i][1].record()
+  barrier()
+  ms_roll = float(sum(x.elapsed_time(y) for x, y in er))
   ms_steps = [x.elapsed_time(y) for x, y in ev]
   ms_total = float(sum(ms_steps))
   ms_sorted = sorted(ms_steps)
@@ -333,8 +348,8 @@ def run_gpu(args, desc):
 
   # ---- max over ranks -----------------------------------------------------------
   from brax_b200 import shard
-  ms_total, ms_b2b, t_e2e, t_wall, ms_flushed = shard.reduce_stats(
-      [ms_total, ms_b2b, t_e2e, t_wall, ms_flushed], ['max'] * 5, device=dev)
+  ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll = shard.reduce_stats(
+      [ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll], ['max'] * 6, device=dev)
   value = world * b * args.steps / (ms_total * 1e-3)
   value_b2b = world * b * args.steps / (ms_b2b * 1e-3)
   value_flushed = world * b * args.steps / (ms_flushed * 1e-3)
@@ -367,6 +382,9 @@ def run_gpu(args, desc):
         'ms_per_step_l2_flushed': ms_flushed / args.steps,
         'ms_l2_flushed_min_median_max': [ms_fl_steps[0], ms_fl_steps[len(ms_fl_steps) // 2], ms_fl_steps[-1]],
         'value_back_to_back': value_b2b,
+        'rollout': {'steps_per_launch': roll_t, 'launches': n_roll,
+                    'value': world * b * roll_t * n_roll / (ms_roll * 1e-3), 'unit': UNIT,
+                    'ms_per_step': ms_roll / (roll_t * n_roll)},
         'wall_s_timed_loop_incl_spin': t_wall,
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d,
                 'd2h_bytes_per_step': d2h, 'steps': e2e_steps, 'finite': e2e_finite,
