@@ -70,13 +70,14 @@ def load_flops(env):
 class ClockSampler:
   """Samples SM clocks / throttle reasons while the timed region runs: NVML in a
   thread (every ~2 ms, no process spawn, so the host enqueue loop is not
-  disturbed); `nvidia-smi` polling only if NVML cannot be loaded."""
+  disturbed), plus one sample on entry and one on exit taken by the caller's
+  thread.  `nvidia-smi` (one call on exit) only if NVML cannot be loaded."""
 
   def __init__(self, index):
     self.index, self.rows, self._stop, self._t = index, [], False, None
-    self.source = 'nvml'
+    self.source, self._nv, self._hnd = 'nvml', None, None
 
-  def _run_nvml(self):
+  def _init_nvml(self):
     import pynvml as nv
     nv.nvmlInit()
     try:
@@ -85,49 +86,65 @@ class ClockSampler:
       hnd = nv.nvmlDeviceGetHandleByUUID(('GPU-' + uuid).encode())
     except Exception:
       hnd = nv.nvmlDeviceGetHandleByIndex(self.index)
-    mx = nv.nvmlDeviceGetMaxClockInfo(hnd, nv.NVML_CLOCK_SM)
-    bits = [(getattr(nv, 'nvmlClocksEventReasonHwSlowdown', 0x8), 'hw_slowdown'),
-            (getattr(nv, 'nvmlClocksEventReasonHwThermalSlowdown', 0x40), 'hw_thermal_slowdown'),
-            (getattr(nv, 'nvmlClocksEventReasonSwThermalSlowdown', 0x20), 'sw_thermal_slowdown'),
-            (getattr(nv, 'nvmlClocksEventReasonSwPowerCap', 0x4), 'sw_power_cap')]
-    get_reasons = getattr(nv, 'nvmlDeviceGetCurrentClocksEventReasons', None) or \
+    self._mx = nv.nvmlDeviceGetMaxClockInfo(hnd, nv.NVML_CLOCK_SM)
+    self._bits = [getattr(nv, 'nvmlClocksEventReasonHwSlowdown', 0x8),
+                  getattr(nv, 'nvmlClocksEventReasonHwThermalSlowdown', 0x40),
+                  getattr(nv, 'nvmlClocksEventReasonSwThermalSlowdown', 0x20),
+                  getattr(nv, 'nvmlClocksEventReasonSwPowerCap', 0x4)]
+    self._reasons = getattr(nv, 'nvmlDeviceGetCurrentClocksEventReasons', None) or \
         nv.nvmlDeviceGetCurrentClocksThrottleReasons
-    while not self._stop:
-      sm = nv.nvmlDeviceGetClockInfo(hnd, nv.NVML_CLOCK_SM)
-      r = get_reasons(hnd)
-      self.rows.append([str(sm), str(mx)] + ['Active' if r & bit else 'Not Active' for bit, _ in bits])
-      time.sleep(0.002)
+    self._nv, self._hnd = nv, hnd
+
+  def _sample(self):
+    sm = self._nv.nvmlDeviceGetClockInfo(self._hnd, self._nv.NVML_CLOCK_SM)
+    r = self._reasons(self._hnd)
+    self.rows.append([str(sm), str(self._mx)] + ['Active' if r & bit else 'Not Active' for bit in self._bits])
 
   def _run(self):
-    try:
-      self._run_nvml()
-      return
-    except Exception:
-      self.source = 'nvidia-smi'
+    while not self._stop:
+      try:
+        self._sample()
+      except Exception:
+        pass
+      time.sleep(0.002)
+
+  def _smi_once(self):
     q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
          'clocks_event_reasons.hw_thermal_slowdown,'
          'clocks_event_reasons.sw_thermal_slowdown,'
          'clocks_event_reasons.sw_power_cap')
-    while not self._stop:
-      try:
-        out = subprocess.run(
-            ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + q,
-             '--format=csv,noheader,nounits'], capture_output=True, text=True,
-            timeout=5).stdout.strip()
-        if out:
-          self.rows.append([x.strip() for x in out.split(',')])
-      except Exception:
-        pass
-      time.sleep(0.1)
+    try:
+      out = subprocess.run(
+          ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + q,
+           '--format=csv,noheader,nounits'], capture_output=True, text=True,
+          timeout=10).stdout.strip()
+      if out:
+        self.rows.append([x.strip() for x in out.split(',')])
+    except Exception:
+      pass
 
   def __enter__(self):
-    self._t = threading.Thread(target=self._run, daemon=True)
-    self._t.start()
+    try:
+      self._init_nvml()
+      self._sample()
+      self._t = threading.Thread(target=self._run, daemon=True)
+      self._t.start()
+    except Exception:
+      self._nv, self.source = None, 'nvidia-smi'
     return self
 
   def __exit__(self, *a):
     self._stop = True
-    self._t.join(timeout=6)
+    if self._t is not None:
+      self._t.join(timeout=2)
+    if self._nv is not None:
+      try:
+        self._sample()
+      except Exception:
+        pass
+    if not self.rows:
+      self.source = 'nvidia-smi'
+      self._smi_once()
 
   def summary(self):
     sm, mx, reasons = [], [], set()

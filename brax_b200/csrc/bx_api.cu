@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -637,7 +638,7 @@ extern "C" int bx_system_configure(bx_system* s, int32_t threads_per_block, int3
 }
 
 static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
-                  const bx_step_io* io, cudaStream_t stream) {
+                  const bx_step_io* io, cudaStream_t stream, uint32_t stagger_ns = 0) {
   if (!s || !io) return fail("NULL argument");
   if (num_envs <= 0) return fail("num_envs must be positive");
   if (num_steps < 1) return fail("num_steps must be >= 1");
@@ -656,6 +657,7 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   for (int i = 0; i < BX_SEG_OUT; i++) p.out[i] = outs[i];
   p.num_envs = num_envs;
   p.num_steps = num_steps;
+  p.stagger_ns = stagger_ns;
   p.dbg = g_dbg;
   const int64_t tiles = (num_envs + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA;
   if (tiles > 0x7fffffffLL) return fail("too many environments for one launch");
@@ -774,7 +776,17 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
                                 &d.contact_pos, &d.contact_normal, &d.contact_penetration};
       for (int i = 0; i < BX_SEG_OUT; i++) *dp[i] = static_cast<float*>(dout[i]);
       cudaStream_t st = s->streams[0];
-      if (launch(s, B, 1, &d, st)) return 1;
+      // One wave of tiles (all resident together): stagger their starts over the time
+      // the larger transfer direction needs at 60 GB/s (measured flat optimum 45-100,
+      // profiles/r01_sweeps.txt), see bx_step_kernel.cuh.
+      uint32_t stagger_ns = 0;
+      if ((B + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA <= 2 * static_cast<int64_t>(s->sm_count)) {
+        int64_t h2d = 0, d2h = 0;
+        bx_host_transfer_bytes(s, B, &h2d, &d2h);
+        static const double gbps = getenv("BX_HOST_STAGGER_GBPS") ? atof(getenv("BX_HOST_STAGGER_GBPS")) : 60.0;
+        if (gbps > 0) stagger_ns = static_cast<uint32_t>(static_cast<double>(std::max(h2d, d2h)) / gbps);
+      }
+      if (launch(s, B, 1, &d, st, stagger_ns)) return 1;
       for (int i = 4; i < BX_SEG_OUT; i++)
         if (hout[i] && s->h.seg_out[i].nper > 0 && s->h.seg_out[i].map < 0) {
           const float f = s->h.seg_out[i].fill;

@@ -16,6 +16,9 @@ struct BxKernelParams {
   float* out[BX_SEG_OUT];      // order of bx_step_io's outputs
   int64_t num_envs;
   int32_t num_steps;  // >1: rollout, act is [T,B,A]
+  // host path only (bx_step_host on mapped host memory): tile i starts i/grid of
+  // this many nanoseconds late, so the tiles' PCIe reads and writes overlap (else 0)
+  uint32_t stagger_ns;
   long long* dbg;     // BX_PHASE_TIMING builds only: cycles per phase of CTA 0
 };
 

@@ -1220,6 +1220,23 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
   const int nenv = static_cast<int>((p.num_envs - env0) < BX_ENVS_PER_CTA ? (p.num_envs - env0) : BX_ENVS_PER_CTA);
 
   PT_INIT();
+  if (p.stagger_ns) {
+    // All tiles of a small batch are resident at once and would move in lock step:
+    // every tile reading over PCIe, then every tile writing.  Spreading the starts
+    // over the transfer time keeps both directions of the link busy together.
+    if (threadIdx.x == 0) {
+      const unsigned long long wait =
+          static_cast<unsigned long long>(blockIdx.x) * p.stagger_ns / gridDim.x;
+      unsigned long long t0, t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+      for (;;) {
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 >= wait) break;
+        __nanosleep(static_cast<unsigned>(wait - (t - t0) < 1000ull ? wait - (t - t0) : 1000ull));
+      }
+    }
+    __syncthreads();
+  }
   // ---- stage in: ONE wave of bulk async copies (tables + the five input spans of
   // this tile), one mbarrier, then the transposition staging -> state quads.
   uint64_t* mbar = reinterpret_cast<uint64_t*>(ti + h.n_ints);

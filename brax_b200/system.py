@@ -81,9 +81,11 @@ class HostBuffers:
       return np.ctypeslib.as_array((C.c_float * max(count, 1)).from_address(p))[:count].reshape(shape)
 
     self.out = {}
+    self.out_ptr = {}   # name -> address (None for empty outputs), read by System.step
     for name, w, dim in _OUT:
       m = n if dim == 'n' else k
       self.out[name] = arr((batch, m, w) if w else (batch, m))
+      self.out_ptr[name] = self._ptrs[-1] if self.out[name].size else None
     self.pos, self.rot = arr((batch, n, 3)), arr((batch, n, 4))
     self.vel, self.ang = arr((batch, n, 3)), arr((batch, n, 3))
     self.act = arr((batch, a))
@@ -303,25 +305,30 @@ class System:
     batched, b = self._shapes(np.shape(qp.pos))
     n, k, a = self.num_bodies, self.num_contacts, self.act_size
 
-    def prep(x, shape):
-      return np.ascontiguousarray(np.asarray(x, dtype=np.float32).reshape(shape))
+    def prep(x, numel):
+      # float32 C-contiguous arrays of the right size pass through untouched
+      if not (isinstance(x, np.ndarray) and x.dtype == np.float32 and x.flags.c_contiguous):
+        x = np.ascontiguousarray(np.asarray(x, dtype=np.float32))
+      if x.size != numel:
+        raise ValueError('array has %d elements, expected %d' % (x.size, numel))
+      return x
 
-    ins = [prep(qp.pos, (b, n, 3)), prep(qp.rot, (b, n, 4)), prep(qp.vel, (b, n, 3)),
-           prep(qp.ang, (b, n, 3)), prep(act, (b, a))]
+    ins = (prep(qp.pos, b * n * 3), prep(qp.rot, b * n * 4), prep(qp.vel, b * n * 3),
+           prep(qp.ang, b * n * 3), prep(act, b * a))
+    io = self._io
+    io.pos, io.rot, io.vel, io.ang, io.act = [t.__array_interface__['data'][0] for t in ins]
     if bufs is not None:
       if bufs.batch != b:
         raise ValueError('HostBuffers are for batch %d, step has %d' % (bufs.batch, b))
       out = dict(bufs.out)
+      for name, ptr in bufs.out_ptr.items():
+        setattr(io, name, ptr)
     else:
       out = {}
       for name, w, dim in _OUT:
         m = n if dim == 'n' else k
         out[name] = np.empty((b, m, w) if w else (b, m), dtype=np.float32)
-    io = CStepIO()
-    for f, t in zip(('pos', 'rot', 'vel', 'ang', 'act'), ins):
-      setattr(io, f, t.ctypes.data)
-    for name, _, _ in _OUT:
-      setattr(io, name, out[name].ctypes.data if out[name].size else None)
+        setattr(io, name, out[name].__array_interface__['data'][0] if out[name].size else None)
     rc = self._lib.bx_step_host(self._h, b, C.byref(io))
     if rc != 0:
       raise RuntimeError('bx_step_host: ' + _lib.last_error())
