@@ -1514,6 +1514,32 @@ int FN(bxo_pair_contacts)(const osys* s, int pair_index, const R* pos, const R* 
   return 0;
 }
 
+/* Joint.angle_vel (joints.py:197-226) for every joint, BEFORE the free_dofs
+ * selection of :219-225: angle_out / vel_out are [B, nj, 3], the slots beyond a
+ * joint's dof stay 0.  vel_d = dot(ang_p - ang_c, axis_d) (:212). */
+int FN(bxo_angle_vel)(const osys* s, int64_t num_envs, const R* rot, const R* ang,
+                      R* angle_out, R* vel_out) {
+  for (int64_t e = 0; e < num_envs; e++) {
+    const R* re = rot + e * s->nb * 4;
+    const R* ae = ang + e * s->nb * 3;
+    for (int i = 0; i < s->nj; i++) {
+      const ojoint* j = &s->joints[i];
+      R axis[3][3] = {{0}}, angle[3] = {0, 0, 0};
+      joint_axis_angle(s, j, re + 4 * j->body_p, re + 4 * j->body_c, axis, angle);
+      const int dof = joint_dof(j);
+      R* ao = angle_out + (e * s->nj + i) * 3;
+      R* vo = vel_out + (e * s->nj + i) * 3;
+      for (int d = 0; d < 3; d++) {
+        R dw[3];
+        for (int k = 0; k < 3; k++) dw[k] = ae[3 * j->body_p + k] - ae[3 * j->body_c + k];
+        ao[d] = d < dof ? angle[d] : C(0);
+        vo[d] = d < dof ? dot3(dw, axis[d]) : C(0);
+      }
+    }
+  }
+  return 0;
+}
+
 #ifdef BXO_COUNT
 /* C-linkage entry of the counting build (oracle/count_flops.py) */
 extern "C" int bxo_step_count(const osys* s, int64_t num_envs, const oio* io) {

@@ -183,6 +183,23 @@ class Oracle:
     self._sys = s
     self._keep = (bodies, joints, acts, forces, pairs)
 
+  def angle_vel(self, rot, ang):
+    """`Joint.angle_vel` of every joint (joints.py:197-226), before the free_dofs
+    selection: (angle [B,nj,3], vel [B,nj,3]); slots beyond a joint's dof are 0."""
+    d, dt = self.desc, self.dtype
+    n, nj = d.num_bodies, len(d.joints)
+    rot = np.ascontiguousarray(np.asarray(rot, dtype=dt).reshape(-1, n, 4))
+    b = rot.shape[0]
+    ang = np.ascontiguousarray(np.asarray(ang, dtype=dt).reshape(b, n, 3))
+    angle, vel = np.zeros((b, nj, 3), dt), np.zeros((b, nj, 3), dt)
+    fn = getattr(self._lib, 'bxo_angle_vel' + ('_f32' if dt == np.float32 else '_f64'))
+    fn.restype = C.c_int
+    rc = fn(C.byref(self._sys), C.c_int64(b), C.c_void_p(rot.ctypes.data), C.c_void_p(ang.ctypes.data),
+            C.c_void_p(angle.ctypes.data), C.c_void_p(vel.ctypes.data))
+    if rc != 0:
+      raise RuntimeError('bxo_angle_vel failed')
+    return angle, vel
+
   def step(self, pos, rot, vel, ang, act, num_threads: int = 0):
     """One batched step.  Inputs [B,N,3|4|3|3], [B,A] (or unbatched)."""
     d, dt = self.desc, self.dtype
