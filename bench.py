@@ -332,6 +332,21 @@ def run_gpu(args, desc):
     er[i][1].record()
   barrier()
   ms_roll = float(sum(x.elapsed_time(y) for x, y in er))
+  # "next" row N1, first piece: Joint.angle_vel of the new state as a kernel epilogue
+  # (what every env's _get_obs asks for after the step); same timing method as `value`.
+  ea = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+  for j in range(nsets):   # untimed: the allocator sees the larger output block of every set once
+    qps[j], _, _ = s.step(qps[j], acts[j % total], angle_vel=True)
+  barrier()
+  for i in range(args.steps):
+    if i % CHUNK == 0:
+      torch.cuda._sleep(spin_cycles)
+    j = i % nsets
+    ea[i][0].record()
+    qps[j], _, js = s.step(qps[j], acts[args.warmup + i], angle_vel=True)
+    ea[i][1].record()
+  barrier()
+  ms_av = float(sum(x.elapsed_time(y) for x, y in ea))
   ms_steps = [x.elapsed_time(y) for x, y in ev]
   ms_total = float(sum(ms_steps))
   ms_sorted = sorted(ms_steps)
@@ -365,8 +380,8 @@ def run_gpu(args, desc):
 
   # ---- max over ranks -----------------------------------------------------------
   from brax_b200 import shard
-  ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll = shard.reduce_stats(
-      [ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll], ['max'] * 6, device=dev)
+  ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll, ms_av = shard.reduce_stats(
+      [ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll, ms_av], ['max'] * 7, device=dev)
   value = world * b * args.steps / (ms_total * 1e-3)
   value_b2b = world * b * args.steps / (ms_b2b * 1e-3)
   value_flushed = world * b * args.steps / (ms_flushed * 1e-3)
@@ -399,6 +414,9 @@ def run_gpu(args, desc):
         'ms_per_step_l2_flushed': ms_flushed / args.steps,
         'ms_l2_flushed_min_median_max': [ms_fl_steps[0], ms_fl_steps[len(ms_fl_steps) // 2], ms_fl_steps[-1]],
         'value_back_to_back': value_b2b,
+        'with_angle_vel_epilogue': {'value': world * b * args.steps / (ms_av * 1e-3), 'unit': UNIT,
+                                    'ms_per_step': ms_av / args.steps,
+                                    'extra_bytes_per_env_step': 24 * len(desc.joints)},
         'rollout': {'steps_per_launch': roll_t, 'launches': n_roll,
                     'value': world * b * roll_t * n_roll / (ms_roll * 1e-3), 'unit': UNIT,
                     'ms_per_step': ms_roll / (roll_t * n_roll)},

@@ -291,6 +291,7 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     const int in_floats = 32 * (13 * nb + d->act_size);
     const int tail = ct_rows + (spring ? 0 : 2 * ncb) + 2 * ncb + nab + (spring ? 2 * nb : 0);
     js = std::max(js, (in_floats + row_floats - 1) / row_floats - tail);
+    js = std::max(js, 2 * nj);  // angle_vel epilogue: {angles}, {velocities} per joint
   }
 
   // ---- state quad rows
@@ -442,6 +443,16 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     h.seg_out[10] = seg(3 * nk, 0.f, mp);
     h.seg_out[11] = seg(3 * nk, 0.f, mn);
     h.seg_out[12] = seg(nk, 0.f, me);
+  }
+  {  // angle_vel epilogue rows live in JS (dead after the last substep)
+    std::vector<int> ma, mv;
+    for (int i = 0; i < nj; i++)
+      for (int x = 0; x < 3; x++) {
+        ma.push_back((h.q_js + 2 * i) * RF + x);
+        mv.push_back((h.q_js + 2 * i + 1) * RF + x);
+      }
+    h.seg_out[13] = seg(3 * nj, 0.f, ma);
+    h.seg_out[14] = seg(3 * nj, 0.f, mv);
   }
   align4();
   h.n_ints = static_cast<int>(ti.size());
@@ -653,7 +664,8 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   float* const outs[BX_SEG_OUT] = {
       io->pos_o, io->rot_o, io->vel_o, io->ang_o, io->contact_vel, io->contact_ang,
       io->joint_vel, io->joint_ang, io->actuator_vel, io->actuator_ang,
-      io->contact_pos, io->contact_normal, io->contact_penetration};
+      io->contact_pos, io->contact_normal, io->contact_penetration,
+      io->joint_angle, io->joint_velocity};
   for (int i = 0; i < BX_SEG_OUT; i++) p.out[i] = outs[i];
   p.num_envs = num_envs;
   p.num_steps = num_steps;
@@ -748,7 +760,7 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
     float* hout[BX_SEG_OUT] = {hio->pos_o, hio->rot_o, hio->vel_o, hio->ang_o, hio->contact_vel,
                                hio->contact_ang, hio->joint_vel, hio->joint_ang, hio->actuator_vel,
                                hio->actuator_ang, hio->contact_pos, hio->contact_normal,
-                               hio->contact_penetration};
+                               hio->contact_penetration, hio->joint_angle, hio->joint_velocity};
     const void* din[BX_SEG_IN];
     void* dout[BX_SEG_OUT];
     bool pinned = true;
@@ -773,7 +785,8 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
       d.ang = (const float*)din[3]; d.act = (const float*)din[4];
       float** dp[BX_SEG_OUT] = {&d.pos_o, &d.rot_o, &d.vel_o, &d.ang_o, &d.contact_vel, &d.contact_ang,
                                 &d.joint_vel, &d.joint_ang, &d.actuator_vel, &d.actuator_ang,
-                                &d.contact_pos, &d.contact_normal, &d.contact_penetration};
+                                &d.contact_pos, &d.contact_normal, &d.contact_penetration,
+                                &d.joint_angle, &d.joint_velocity};
       for (int i = 0; i < BX_SEG_OUT; i++) *dp[i] = static_cast<float*>(dout[i]);
       cudaStream_t st = s->streams[0];
       // One wave of tiles (all resident together): stagger their starts over the time
@@ -797,7 +810,7 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
       return 0;
     }
   }
-  const size_t per_env = static_cast<size_t>(13 * n + a + 13 * n + 18 * n + 7 * k);
+  const size_t per_env = static_cast<size_t>(13 * n + a + 13 * n + 18 * n + 7 * k + 6 * s->h.nj);
   const size_t need = per_env * B;
   if (need > s->scratch_floats) {
     cudaFree(s->d_scratch);
@@ -815,11 +828,12 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
   for (int i = 0; i < BX_SEG_IN; i++) d_in[i] = take(in_per[i]);
   const size_t out_per[BX_SEG_OUT] = {(size_t)3 * n, (size_t)4 * n, (size_t)3 * n, (size_t)3 * n,
                                       (size_t)3 * n, (size_t)3 * n, (size_t)3 * n, (size_t)3 * n,
-                                      (size_t)3 * n, (size_t)3 * n, (size_t)3 * k, (size_t)3 * k, (size_t)k};
+                                      (size_t)3 * n, (size_t)3 * n, (size_t)3 * k, (size_t)3 * k, (size_t)k,
+                                      (size_t)3 * s->h.nj, (size_t)3 * s->h.nj};
   float* h_out[BX_SEG_OUT] = {hio->pos_o, hio->rot_o, hio->vel_o, hio->ang_o, hio->contact_vel,
                               hio->contact_ang, hio->joint_vel, hio->joint_ang, hio->actuator_vel,
                               hio->actuator_ang, hio->contact_pos, hio->contact_normal,
-                              hio->contact_penetration};
+                              hio->contact_penetration, hio->joint_angle, hio->joint_velocity};
   float* d_out[BX_SEG_OUT];
   for (int i = 0; i < BX_SEG_OUT; i++) d_out[i] = take(out_per[i]);
   // Pipeline: the batch is cut into chunks (multiples of the 32-env tile); chunk
@@ -843,7 +857,8 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
     d.act = d_in[4] + e0 * in_per[4];
     float** dp[BX_SEG_OUT] = {&d.pos_o, &d.rot_o, &d.vel_o, &d.ang_o, &d.contact_vel, &d.contact_ang,
                               &d.joint_vel, &d.joint_ang, &d.actuator_vel, &d.actuator_ang,
-                              &d.contact_pos, &d.contact_normal, &d.contact_penetration};
+                              &d.contact_pos, &d.contact_normal, &d.contact_penetration,
+                              &d.joint_angle, &d.joint_velocity};
     for (int i = 0; i < BX_SEG_OUT; i++) {
       const bool constant = s->h.seg_out[i].map < 0;
       *dp[i] = (i < 4 || (h_out[i] && out_per[i] && !constant)) ? d_out[i] + e0 * out_per[i] : nullptr;
@@ -871,7 +886,7 @@ extern "C" int bx_host_transfer_bytes(const bx_system* s, int64_t B, int64_t* h2
   const int64_t n = s->h.nb, a = s->h.act_size;
   if (h2d) *h2d = 4 * B * (13 * n + a);
   int64_t o = 0;
-  for (int i = 0; i < BX_SEG_OUT; i++)
+  for (int i = 0; i < 13; i++)  // the step's own outputs; the optional angle_vel epilogue adds 24 J bytes/env
     if (i < 4 || s->h.seg_out[i].map >= 0) o += s->h.seg_out[i].nper;
   if (d2h) *d2h = 4 * B * o;
   return 0;

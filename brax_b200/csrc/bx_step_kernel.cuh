@@ -1206,6 +1206,34 @@ BXS void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
   }
 }
 
+// ---- optional epilogue: Joint.angle_vel of the new state ----------------------
+// joints.py:197-226 before the free_dofs selection (the host mirror applies it):
+// angles of the joint's dofs and vel_d = dot(ang_p - ang_c, axis_d), written to
+// quads JS+2j = {angle0..2}, JS+2j+1 = {vel0..2} (JS is dead after the last substep).
+template <int MODE>
+BXS void phase_angle_vel(const Ctx& c, const BxHeader& h) {
+  typedef Lay<MODE> L;
+  const int ro = MODE == BX_MODE_PBD ? 2 * c.cur + 1 : 1;
+  for (int j = c.warp; j < h.nj; j += c.nwarp) {
+    const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
+    const float4* jq = c.tf + h.fo_joint + j * JQ_STRIDE;
+    Q4 rp = ldq(c, L::BQ * ji.y + ro), rc = ldq(c, L::BQ * ji.z + ro);
+    V3 axis[3];
+    float angle[3];
+    joint_axis_angle(ji.x, jq, rp, rc, axis, angle);
+    V3 dw = ldv(c, L::BQ * ji.y + L::ANG) - ldv(c, L::BQ * ji.z + L::ANG);
+    const int dof = joint_dof(ji.x);
+    float a[3], v[3];
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+      a[d] = d < dof ? angle[d] : 0.f;
+      v[d] = d < dof ? dot(dw, axis[d]) : 0.f;
+    }
+    QROW(c, h.q_js + 2 * j) = make_float4(a[0], a[1], a[2], 0.f);
+    QROW(c, h.q_js + 2 * j + 1) = make_float4(v[0], v[1], v[2], 0.f);
+  }
+}
+
 // ============================== the kernel ====================================
 // The whole step of one tile of 32 environments (called by bx_step_kernel below).
 template <int MODE>
@@ -1390,6 +1418,10 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
     }
   }
   __syncthreads();
+  if (p.out[13] != nullptr || p.out[14] != nullptr) {
+    phase_angle_vel<MODE>(c, h);
+    __syncthreads();
+  }
 
   PT(10);
   // ---- out: each warp transposes whole segments straight to HBM with coalesced

@@ -103,7 +103,7 @@ enum {
 // Global <-> shared I/O segment: global array g[B][nper]; element (e, r) lives at
 // shared float index map[r] + 4 * e (map[r] < 0: the element is a constant).
 #define BX_SEG_IN 5    // pos rot vel ang act
-#define BX_SEG_OUT 13  // pos rot vel ang + 6 Info P + contact pos/normal/pen
+#define BX_SEG_OUT 15  // pos rot vel ang + 6 Info P + contact pos/normal/pen + joint angle/velocity
 struct BxSeg {
   int32_t nper;   // floats per environment
   int32_t map;    // offset of map[nper] in the int table

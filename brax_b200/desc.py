@@ -20,7 +20,7 @@ from typing import Any, Dict, List
 
 import numpy as np
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 MODE = {'pbd': 0, 'legacy_spring': 1}
 JOINT_KIND = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
@@ -87,7 +87,8 @@ class CStepIO(C.Structure):
   _fields_ = [(n, C.c_void_p) for n in (
       'pos', 'rot', 'vel', 'ang', 'act', 'pos_o', 'rot_o', 'vel_o', 'ang_o',
       'contact_vel', 'contact_ang', 'joint_vel', 'joint_ang', 'actuator_vel',
-      'actuator_ang', 'contact_pos', 'contact_normal', 'contact_penetration')]
+      'actuator_ang', 'contact_pos', 'contact_normal', 'contact_penetration',
+      'joint_angle', 'joint_velocity')]
 
 
 def _f(x):

@@ -51,6 +51,9 @@ def _joint_rows(joint, group: int) -> List[Dict[str, Any]]:
         'off_p': _l(_a(joint.off_p)[i]), 'off_c': _l(_a(joint.off_c)[i]),
         'axis_p': _l(_a(joint.axis_p)[i]), 'axis_c': _l(_a(joint.axis_c)[i]),
         'limit': _l(lim), 'dof': int(lim.shape[0]),
+        # dofs of this joint that `Joint.angle_vel` reports (joints.py:219-225, :430-437)
+        'free_dofs': int(joint.free_dofs[i]) if getattr(joint, 'free_dofs', None) is not None
+                     else int(lim.shape[0]),
         'angular_damping': float(_a(joint.angular_damping)[i]),
     }
     if kind.startswith('spring_'):

@@ -57,6 +57,17 @@ _OUT = (('pos_o', 3, 'n'), ('rot_o', 4, 'n'), ('vel_o', 3, 'n'),
         ('joint_vel', 3, 'n'), ('joint_ang', 3, 'n'), ('actuator_vel', 3, 'n'),
         ('actuator_ang', 3, 'n'), ('contact_pos', 3, 'k'),
         ('contact_normal', 3, 'k'), ('contact_penetration', 0, 'k'))
+# optional epilogue: Joint.angle_vel of the new state, [B, J, 3] each
+_OUT_AV = (('joint_angle', 3, 'j'), ('joint_velocity', 3, 'j'))
+
+
+@dataclasses.dataclass
+class JointState:
+  """`Joint.angle_vel` of every joint (joints.py:197-226) before the free_dofs
+  selection: angle / vel are [B, J, 3] (or [J, 3]), slots beyond a joint's dof are 0.
+  `System.angle_vel_groups` turns it into what the reference's envs consume."""
+  angle: Any
+  vel: Any
 
 
 class HostBuffers:
@@ -85,6 +96,10 @@ class HostBuffers:
     for name, w, dim in _OUT:
       m = n if dim == 'n' else k
       self.out[name] = arr((batch, m, w) if w else (batch, m))
+      self.out_ptr[name] = self._ptrs[-1] if self.out[name].size else None
+    nj = len(system.desc.joints)
+    for name, w, _ in _OUT_AV:
+      self.out[name] = arr((batch, nj, w))
       self.out_ptr[name] = self._ptrs[-1] if self.out[name].size else None
     self.pos, self.rot = arr((batch, n, 3)), arr((batch, n, 4))
     self.vel, self.ang = arr((batch, n, 3)), arr((batch, n, 3))
@@ -190,14 +205,33 @@ class System:
     return QP(*arrs)
 
   # ---- the step ---------------------------------------------------------------
-  def step(self, qp: QP, act, out: 'HostBuffers' = None) -> Tuple[QP, Info]:
+  def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False):
     """`System.step(qp, act) -> (qp, info)` (system.py:244-247).
 
     out: optional `HostBuffers` (host path only): results are written into its
-    page-locked arrays instead of freshly allocated pageable ones."""
+    page-locked arrays instead of freshly allocated pageable ones.
+    angle_vel: also return `Joint.angle_vel` of the new state as a third value
+    (`JointState`), computed in the same launch -- what every env's `_get_obs`
+    asks for right after the step (envs/ant.py:259, envs/humanoid.py:285)."""
     if _is_torch(qp.pos):
-      return self._step_torch(qp, act, 1)
-    return self._step_numpy(qp, act, out)
+      return self._step_torch(qp, act, 1, angle_vel)
+    return self._step_numpy(qp, act, out, angle_vel)
+
+  def angle_vel_groups(self, js: JointState):
+    """[(angle, vel) per joint group] exactly as `[j.angle_vel(qp) for j in
+    sys.joints]`: per group the joints' first free_dofs dofs, flattened
+    (joints.py:216-225)."""
+    groups = {}
+    for i, j in enumerate(self.desc.joints):
+      groups.setdefault(j['group'], []).append((i, int(j.get('free_dofs', j['dof']))))
+    cat = np.concatenate
+    if _is_torch(js.angle):
+      import torch
+      cat = lambda xs, axis: torch.cat(xs, dim=axis)  # noqa: E731
+    res = []
+    for g in sorted(groups):
+      res.append(tuple(cat([x[..., i, :f] for i, f in groups[g]], -1) for x in (js.angle, js.vel)))
+    return res
 
   def host_buffers(self, batch: int) -> HostBuffers:
     """Page-locked arrays for `step(..., out=...)` at this batch size."""
@@ -212,7 +246,7 @@ class System:
   def rollout(self, qp: QP, acts) -> Tuple[QP, Info]:
     """T steps in ONE launch; acts is [T, B, A] (torch CUDA).  Returns the final
     QP and the Info of the last step (lax.scan of System.step over actions)."""
-    return self._step_torch(qp, acts, int(acts.shape[0]))
+    return self._step_torch(qp, acts, int(acts.shape[0]), False)
 
   def _shapes(self, pos_shape):
     n = self.num_bodies
@@ -235,24 +269,27 @@ class System:
                 P(out['actuator_vel'], out['actuator_ang']),
                 out['contact_pos'], out['contact_normal'],
                 out['contact_penetration'])
+    if 'joint_angle' in out:
+      return qp, info, JointState(out['joint_angle'], out['joint_velocity'])
     return qp, info
 
-  def _out_plan(self, b):
-    """Per batch size: the 13 outputs as slices of ONE allocation (each slice
+  def _out_plan(self, b, av):
+    """Per batch size: the outputs as slices of ONE allocation (each slice
     starts on a 16-byte boundary so the kernel's vector stores apply)."""
-    plan = self._plans.get(b)
+    plan = self._plans.get((b, av))
     if plan is None:
-      n, k = self.num_bodies, self.num_contacts
-      shapes, offs, off = [], [], 0
-      for _, w, dim in _OUT:
-        m = n if dim == 'n' else k
+      dims = {'n': self.num_bodies, 'k': self.num_contacts, 'j': len(self.desc.joints)}
+      names, shapes, offs, off = [], [], [], 0
+      for name, w, dim in (_OUT + _OUT_AV if av else _OUT):
+        m = dims[dim]
+        names.append(name)
         shapes.append((b, m, w) if w else (b, m))
         offs.append(off)
         off += -(-(b * m * max(w, 1)) // 4) * 4
-      plan = self._plans[b] = (shapes, offs, max(off, 4))
+      plan = self._plans[(b, av)] = (names, shapes, offs, max(off, 4))
     return plan
 
-  def _step_torch(self, qp: QP, act, steps: int):
+  def _step_torch(self, qp: QP, act, steps: int, av: bool = False):
     import torch
     batched, b = self._shapes(qp.pos.shape)
     n, a = self.num_bodies, self.act_size
@@ -275,13 +312,14 @@ class System:
 
     ins = (prep(qp.pos, b * n * 3), prep(qp.rot, b * n * 4), prep(qp.vel, b * n * 3),
            prep(qp.ang, b * n * 3), prep(act, steps * b * a))
-    shapes, offs, total = self._out_plan(b)
+    names, shapes, offs, total = self._out_plan(b, av)
     flat = torch.empty(total, dtype=f32, device=dev)
     base = flat.data_ptr()
     io = self._io
     io.pos, io.rot, io.vel, io.ang, io.act = [t.data_ptr() for t in ins]
+    io.joint_angle = io.joint_velocity = None
     out = {}
-    for (name, _, _), shape, off in zip(_OUT, shapes, offs):
+    for name, shape, off in zip(names, shapes, offs):
       cnt = 1
       for d in shape:
         cnt *= d
@@ -301,7 +339,7 @@ class System:
       raise RuntimeError('bx_step: ' + _lib.last_error())
     return self._wrap(out, batched)
 
-  def _step_numpy(self, qp: QP, act, bufs: 'HostBuffers' = None):
+  def _step_numpy(self, qp: QP, act, bufs: 'HostBuffers' = None, av: bool = False):
     batched, b = self._shapes(np.shape(qp.pos))
     n, k, a = self.num_bodies, self.num_contacts, self.act_size
 
@@ -323,10 +361,15 @@ class System:
       out = dict(bufs.out)
       for name, ptr in bufs.out_ptr.items():
         setattr(io, name, ptr)
+      if not av:
+        io.joint_angle = io.joint_velocity = None
+        del out['joint_angle'], out['joint_velocity']
     else:
       out = {}
-      for name, w, dim in _OUT:
-        m = n if dim == 'n' else k
+      io.joint_angle = io.joint_velocity = None
+      dims = {'n': n, 'k': k, 'j': len(self.desc.joints)}
+      for name, w, dim in (_OUT + _OUT_AV if av else _OUT):
+        m = dims[dim]
         out[name] = np.empty((b, m, w) if w else (b, m), dtype=np.float32)
         setattr(io, name, out[name].__array_interface__['data'][0] if out[name].size else None)
     rc = self._lib.bx_step_host(self._h, b, C.byref(io))

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BX_ABI_VERSION 3
+#define BX_ABI_VERSION 4
 
 /* dynamics_mode (base.py:179-201) */
 #define BX_MODE_PBD 0
@@ -169,6 +169,11 @@ typedef struct bx_step_io {
   float *contact_pos;                 /* [B,K,3] */
   float *contact_normal;              /* [B,K,3] */
   float *contact_penetration;         /* [B,K]   */
+  /* Optional epilogue (both NULL = skipped): Joint.angle_vel of the NEW state for
+   * every joint (joints.py:197-226, what every env's _get_obs calls right after the
+   * step, envs/ant.py:259), before the free_dofs selection: [B,J,3], slots beyond a
+   * joint's dof are 0.  J = num_joints in descriptor order. */
+  float *joint_angle, *joint_velocity;
 } bx_step_io;
 
 /* Creates a system on CUDA device `device` (tables uploaded once).  Returns 0

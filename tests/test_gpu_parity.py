@@ -25,6 +25,8 @@ further floor of VEL_ULPS * 6e-8 / dt_sub: velocity_projection computes
 Contact flags `contact_penetration > 0` are bit-exact
 except where the oracles' |penetration| < 1e-6.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -213,6 +215,49 @@ def test_single_step_on_harvested_states(name, b, steps):
   ref, _ = check_step(name, ins, act, got, outlier_frac=frac)
   # at least some contacts must be active for the test to mean anything
   assert (ref['contact_penetration'] > 0).mean() > 0.02, name
+
+
+@pytest.mark.parametrize('name', GOLDEN)
+def test_angle_vel_epilogue(name):
+  """`step(..., angle_vel=True)`: Joint.angle_vel of the new state from the same
+  launch.  Checked against the float32 oracle's angle_vel
+  (pinned to the reference in tests/test_oracle_golden.py) evaluated on the
+  kernel's own output state, so only the epilogue is judged here; QP and Info
+  must not change when the epilogue is on; the free_dofs selection must give the
+  reference's per-group layout."""
+  torch = _torch()
+  from brax_b200.system import QP
+  from tests.test_oracle_golden import angle_tol, select_free
+  g = util.load_golden(name)
+  av = np.load(os.path.join(util.GOLDEN, name + '_angle_vel.npz'))
+  s = _system(name)
+  ins = [np.ascontiguousarray(g[k].astype(np.float32)) for k in util.QP_KEYS]
+  act = torch.from_numpy(np.ascontiguousarray(g['act'].astype(np.float32))).cuda()
+  qp = QP(*[torch.from_numpy(x).cuda() for x in ins])
+  q0, i0 = s.step(qp, act)
+  q1, i1, js = s.step(qp, act, angle_vel=True)
+  torch.cuda.synchronize()
+  a, b = _flat(q0, i0), _flat(q1, i1)
+  for k in a:
+    np.testing.assert_array_equal(a[k], b[k], err_msg=k)
+  angle, vel = js.angle.cpu().numpy(), js.vel.cpu().numpy()
+  oa, ov = _oracle(name, np.float32).angle_vel(b['rot'], b['ang'])
+  o64a, _ = _oracle(name, np.float64).angle_vel(b['rot'], b['ang'])
+  assert (np.abs(angle - oa) <= 2 * angle_tol(o64a, av['dof'])).all(), float(np.abs(angle - oa).max())
+  scale = 1.0 + np.abs(b['ang']).reshape(b['ang'].shape[0], -1).max(axis=1)[:, None, None]
+  assert (np.abs(vel - ov) <= 2e-5 * scale).all(), float(np.abs(vel - ov).max())
+  # reference layout: [j.angle_vel(qp) for j in sys.joints], concatenated
+  groups = s.angle_vel_groups(js)
+  flat_a = torch.cat([x for x, _ in groups], dim=-1).cpu().numpy()
+  np.testing.assert_array_equal(flat_a, select_free(angle, av['dof'], av['free']))
+  assert flat_a.shape[-1] == av['flat_angle'].shape[-1]
+  # and it is the reference's value up to the state difference of one step
+  assert np.abs(flat_a - av['flat_angle']).max() < 5e-3
+  # host path, page-locked buffers
+  hb = s.host_buffers(ins[0].shape[0])
+  q2, i2, js2 = s.step(QP(*ins), g['act'].astype(np.float32), out=hb, angle_vel=True)
+  np.testing.assert_array_equal(js2.angle, angle)
+  np.testing.assert_array_equal(js2.vel, vel)
 
 
 @pytest.mark.parametrize('name', ['ant', 'humanoid'])
