@@ -95,6 +95,7 @@ struct Ctx {
   const int32_t* ti;  // int tables (shared)
   int warp, nwarp;
   int cur;            // ping-pong index of the current pos/rot quads (pbd)
+  int damp_j0, damp_step;  // this warp's joint-damping items (phase T), set once per launch
 #ifdef BX_PHASE_TIMING
   long long* dbg;     // within-item markers (PTM): dbg[BX_PTM_BASE + slot]
   mutable long long mark;
@@ -340,13 +341,7 @@ BXS void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
     stv(c, h.q_js + ai2.z, angle_act ? tc : -tc);
   }
   if (damp) {
-    // the damping items are short: when the last actuator round leaves warps idle,
-    // those warps take them (up to 4 each) instead of lengthening the busy ones
-    const int rem = h.na % c.nwarp, n_idle = rem ? c.nwarp - rem : 0;
-    const bool on_idle = n_idle > 0 && h.nj <= 4 * n_idle;
-    const int j0 = on_idle ? (c.warp >= rem ? c.warp - rem : h.nj) : c.warp;
-    const int jstep = on_idle ? n_idle : c.nwarp;
-    for (int j = j0; j < h.nj; j += jstep) {
+    for (int j = c.damp_j0; j < h.nj; j += c.damp_step) {
       const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
       const int4 js = ldi4(c.ti + h.io_joint + j * JI_STRIDE + 4);  // dslot_p dslot_c jslot_p jslot_c
       const float damping = c.tf[h.fo_joint + j * JQ_STRIDE + JQ_OFF_P].w;
@@ -1328,6 +1323,14 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
   c.tf = tf;
   c.ti = ti;
   c.cur = 0;
+  {
+    // the damping items of phase T are short: when the last actuator round leaves
+    // warps idle, those warps take them (up to 4 each) instead of the busy ones
+    const int rem = h.na % c.nwarp, n_idle = rem ? c.nwarp - rem : 0;
+    const bool on_idle = n_idle > 0 && h.nj <= 4 * n_idle;
+    c.damp_j0 = on_idle ? (c.warp >= rem ? c.warp - rem : h.nj) : c.warp;
+    c.damp_step = on_idle ? n_idle : c.nwarp;
+  }
 #ifdef BX_PHASE_TIMING
   c.dbg = p.dbg;
   c.mark = 0;
