@@ -175,6 +175,12 @@ def make_state(desc, b, seed):
   return pos, rot, vel * mask_p, ang * mask_r
 
 
+def workload_name(args, desc):
+  """config.workload, identical on both arms (b200 / --impl reference)."""
+  return '%s %d envs/GPU, default substeps (%d), dynamics %s' % (
+      args.env, args.envs, desc.substeps, desc.dynamics_mode)
+
+
 def cpu_baseline(desc, env, b, budget_s=12.0, threads=0):
   """Times the oracle port (float32, OpenMP over envs) on the host cores."""
   from oracle.oracle import Oracle
@@ -223,7 +229,7 @@ def run_reference(args, desc):
       'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
       'ms_per_step': 1e3 * el / args.steps, 'higher_is_better': True,
       'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-      'config': {'workload': '%s %d envs/GPU, default substeps' % (args.env, args.envs)},
+      'config': {'workload': workload_name(args, desc)},
       'cpu_baseline': {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
       'e2e': {'value': v, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
   }))
@@ -401,8 +407,7 @@ def run_gpu(args, desc):
         'ms_per_step_min_median_max': [ms_sorted[0], ms_sorted[len(ms_sorted) // 2], ms_sorted[-1]],
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
         'config': {
-            'workload': '%s %d envs/GPU, default substeps (%d), dynamics %s' % (
-                args.env, b, desc.substeps, desc.dynamics_mode),
+            'workload': workload_name(args, desc),
             'l2': 'inputs larger than L2: the timed steps rotate over %d independent env batches '
                   '(%.0f MB working set vs 126 MB L2), so each step reads state last touched %d '
                   'steps earlier; timed steps are enqueued in chunks of 128 behind a spin kernel so the event '

@@ -1,0 +1,186 @@
+"""Host-side mirror of the reference's `brax.envs` for the envs whose whole
+`Env.step` runs as the fused kernel's epilogue ("next" row N1 of SURVEY.md 8(f)).
+
+    env = envs.Ant(use_contact_forces=True)        # brax/envs/ant.py:173-196
+    env = envs.Humanoid()                          # brax/envs/humanoid.py:200-221
+    state = env.reset(batch=8192, device='cuda')   # default_qp (+ noise on the velocities)
+    state = env.step(state, action)                # ONE launch: physics + obs/reward/done/metrics
+
+`State` carries the reference's fields (brax/envs/env.py:28-37): qp, obs, reward,
+done, metrics (dict, the reference's keys in the reference's order), info.
+`env.sys` is the `brax_b200.System` (so `env.sys.step` stays available).
+
+What runs on the GPU: `sys.step` and, in the same launch, everything the
+reference computes after it in `Ant.step` / `Humanoid.step` (ant.py:222-281,
+humanoid.py:246-340).  What does not: `reset`'s forward kinematics
+(`default_qp(joint_angle=...)`, system.py:112-242, row N3) -- `reset` here starts
+from the recorded `default_qp()` and perturbs velocities only; wrappers and
+agents are callers and stay reference code.  No CPU fallback.
+"""
+import ctypes as C
+import dataclasses
+from typing import Any, Dict, Tuple
+
+import numpy as np
+
+from brax_b200 import system as _system
+from brax_b200.desc import MAX_ACTUATORS, MAX_JOINTS, SystemDesc
+
+ENV_KIND = {'ant': 1, 'humanoid': 2}
+
+ANT_METRICS = ('reward_forward', 'reward_survive', 'reward_ctrl', 'reward_contact', 'x_position',
+               'y_position', 'distance_from_origin', 'x_velocity', 'y_velocity', 'forward_reward')
+HUMANOID_METRICS = ('forward_reward', 'reward_linvel', 'reward_quadctrl', 'reward_alive', 'x_position',
+                    'y_position', 'distance_from_origin', 'x_velocity', 'y_velocity')
+
+
+class CEnvDesc(C.Structure):
+  """bx_env_desc (include/brax_b200.h)."""
+  _fields_ = [('struct_size', C.c_uint32), ('kind', C.c_int32), ('dt', C.c_float),
+              ('forward_reward_weight', C.c_float), ('ctrl_cost_weight', C.c_float),
+              ('contact_cost_weight', C.c_float), ('healthy_reward', C.c_float),
+              ('healthy_z_min', C.c_float), ('healthy_z_max', C.c_float),
+              ('terminate_when_unhealthy', C.c_int32), ('use_contact_forces', C.c_int32),
+              ('exclude_current_positions', C.c_int32),
+              ('joint_free_dofs', C.c_int32 * MAX_JOINTS),
+              ('actuator_width', C.c_int32 * MAX_ACTUATORS)]
+
+
+@dataclasses.dataclass
+class EnvDesc:
+  """Constructor arguments of a reference env that enter `Env.step`."""
+  kind: str
+  forward_reward_weight: float = 1.0
+  ctrl_cost_weight: float = 0.5
+  contact_cost_weight: float = 0.0
+  healthy_reward: float = 1.0
+  terminate_when_unhealthy: bool = True
+  healthy_z_range: Tuple[float, float] = (0.2, 1.0)
+  use_contact_forces: bool = False
+  exclude_current_positions: bool = True
+
+  def metric_names(self):
+    return ANT_METRICS if self.kind == 'ant' else HUMANOID_METRICS
+
+  def obs_size(self, desc: SystemDesc) -> int:
+    nd = sum(int(j.get('free_dofs', j['dof'])) for j in desc.joints)
+    n = (1 if self.exclude_current_positions else 3) + 4 + nd + 6 + nd
+    if self.kind == 'ant':
+      return n + (6 * desc.num_bodies if self.use_contact_forces else 0)
+    return n + 15 * (desc.num_bodies - 1) + sum(len(a['act_index']) for a in desc.actuators)
+
+  def to_c(self, desc: SystemDesc) -> CEnvDesc:
+    c = CEnvDesc()
+    c.struct_size = C.sizeof(CEnvDesc)
+    c.kind = ENV_KIND[self.kind]
+    c.dt = desc.dt
+    c.forward_reward_weight = self.forward_reward_weight
+    c.ctrl_cost_weight = self.ctrl_cost_weight
+    c.contact_cost_weight = self.contact_cost_weight
+    c.healthy_reward = self.healthy_reward
+    c.healthy_z_min, c.healthy_z_max = self.healthy_z_range
+    c.terminate_when_unhealthy = int(self.terminate_when_unhealthy)
+    c.use_contact_forces = int(self.use_contact_forces)
+    c.exclude_current_positions = int(self.exclude_current_positions)
+    for i, j in enumerate(desc.joints):
+      c.joint_free_dofs[i] = int(j.get('free_dofs', j['dof']))
+    for i, a in enumerate(desc.actuators):
+      c.actuator_width[i] = len(a['act_index'])
+    return c
+
+
+@dataclasses.dataclass
+class State:
+  """Environment state (brax/envs/env.py:28-37)."""
+  qp: Any
+  obs: Any
+  reward: Any
+  done: Any
+  metrics: Dict[str, Any] = dataclasses.field(default_factory=dict)
+  info: Dict[str, Any] = dataclasses.field(default_factory=dict)
+
+  def replace(self, **kw):
+    return dataclasses.replace(self, **kw)
+
+
+class Env:
+  """Common part of the mirrored envs: a `System` with the env epilogue switched on."""
+
+  def __init__(self, system_name: str, env: EnvDesc, device: int = 0):
+    self.env = env
+    self.sys = _system.load_system(system_name, device)
+    self.sys.set_env(env)
+    self.observation_size = env.obs_size(self.sys.desc)
+    self.action_size = self.sys.act_size
+
+  def reset(self, batch: int = None, device=None, rng=None, velocity_noise: float = 0.0) -> State:
+    """Initial state from the recorded `default_qp()`.  The reference draws joint
+    angles and runs forward kinematics (ant.py:198-204, system.py:112-242: row N3,
+    not built); here only body velocities can be perturbed.  obs is that of a zero
+    step (filled by the first `step`), reward = done = 0 and zero metrics as in the
+    reference's reset (ant.py:206-220)."""
+    qp = self.sys.default_qp(batch=batch)
+    if velocity_noise:
+      rng = rng or np.random.default_rng(0)
+      d = self.sys.desc
+      mp = np.asarray([x['pos_mask'] for x in d.bodies], np.float32)
+      mr = np.asarray([x['rot_mask'] for x in d.bodies], np.float32)
+      qp.vel = (rng.uniform(-velocity_noise, velocity_noise, qp.pos.shape).astype(np.float32) * mp)
+      qp.ang = (rng.uniform(-velocity_noise, velocity_noise, qp.pos.shape).astype(np.float32) * mr)
+    lead = qp.pos.shape[:-2]
+    zeros = lambda *s: np.zeros(lead + s, np.float32)  # noqa: E731
+    obs, rew, done = zeros(self.observation_size), zeros(), zeros()
+    met = {k: zeros() for k in self.env.metric_names()}
+    if device is not None:
+      import torch
+      to = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(device)  # noqa: E731
+      qp = _system.QP(*[to(getattr(qp, k)) for k in ('pos', 'rot', 'vel', 'ang')])
+      obs, rew, done = to(obs), to(rew), to(done)
+      met = {k: to(v) for k, v in met.items()}
+    return State(qp, obs, rew, done, met)
+
+  def step(self, state: State, action) -> State:
+    """`Env.step(state, action)` (ant.py:222, humanoid.py:246): one kernel launch."""
+    qp, info, eo = self.sys.step(state.qp, action, env=True)
+    names = self.env.metric_names()
+    metrics = dict(state.metrics)
+    metrics.update({k: eo['metrics'][..., i] for i, k in enumerate(names)})
+    return State(qp, eo['obs'], eo['reward'], eo['done'], metrics, dict(state.info, physics=info))
+
+
+class Ant(Env):
+  """brax/envs/ant.py:26-281 (constructor arguments and defaults :173-196)."""
+
+  def __init__(self, ctrl_cost_weight=0.5, use_contact_forces=False, contact_cost_weight=5e-4,
+               healthy_reward=1.0, terminate_when_unhealthy=True, healthy_z_range=(0.2, 1.0),
+               reset_noise_scale=0.1, exclude_current_positions_from_observation=True,
+               legacy_spring=False, device: int = 0):
+    self._reset_noise_scale = reset_noise_scale
+    super().__init__('ant_spring' if legacy_spring else 'ant', EnvDesc(
+        'ant', 1.0, ctrl_cost_weight, contact_cost_weight, healthy_reward, terminate_when_unhealthy,
+        tuple(healthy_z_range), use_contact_forces, exclude_current_positions_from_observation), device)
+
+
+class Humanoid(Env):
+  """brax/envs/humanoid.py:26-340 (constructor arguments and defaults :200-221)."""
+
+  def __init__(self, forward_reward_weight=1.25, ctrl_cost_weight=0.1, healthy_reward=5.0,
+               terminate_when_unhealthy=True, healthy_z_range=(0.8, 2.1), reset_noise_scale=1e-2,
+               exclude_current_positions_from_observation=True, legacy_spring=False, device: int = 0):
+    self._reset_noise_scale = reset_noise_scale
+    super().__init__('humanoid_spring' if legacy_spring else 'humanoid', EnvDesc(
+        'humanoid', forward_reward_weight, ctrl_cost_weight, 0.0, healthy_reward, terminate_when_unhealthy,
+        tuple(healthy_z_range), False, exclude_current_positions_from_observation), device)
+
+
+_ENVS = {'ant': Ant, 'humanoid': Humanoid}
+
+
+def create(env_name: str, **kwargs) -> Env:
+  """`envs.create(name)` for the mirrored envs.  'ant' is registered with
+  use_contact_forces=True as in this fork (brax/envs/__init__.py:45)."""
+  if env_name not in _ENVS:
+    raise KeyError('env %r has no fused epilogue (available: %s)' % (env_name, sorted(_ENVS)))
+  if env_name == 'ant':
+    kwargs.setdefault('use_contact_forces', True)
+  return _ENVS[env_name](**kwargs)

@@ -1,0 +1,77 @@
+"""Pins the env-epilogue oracle (oracle/env_oracle.py) against the reference.
+
+tests/golden/<variant>_env.npz hold obs / reward / done / metrics of the
+UNMODIFIED reference `Ant.step` / `Humanoid.step` (brax/envs/ant.py:222-281,
+brax/envs/humanoid.py:246-340) on numpy float64 for the very steps stored in
+tests/golden/<system>_steps.npz (oracle/gen_golden_env.py).  Fed with the stored
+physics outputs, the float64 evaluation of the oracle must reproduce them to
+rounding; chained behind the C oracle (physics + angle_vel) it must too.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from brax_b200 import envs
+from oracle import env_oracle
+from oracle.oracle import Oracle
+from tests import util
+
+# variant -> (system golden, EnvDesc as the reference constructs it)
+VARIANTS = {
+    'ant': ('ant', envs.EnvDesc('ant', 1.0, 0.5, 5e-4, 1.0, True, (0.2, 1.0), True, True)),
+    'ant_nocfrc': ('ant', envs.EnvDesc('ant', 1.0, 0.5, 5e-4, 1.0, True, (0.2, 1.0), False, True)),
+    'ant_spring': ('ant_spring', envs.EnvDesc('ant', 1.0, 0.5, 5e-4, 1.0, True, (0.2, 1.0), True, True)),
+    'humanoid': ('humanoid', envs.EnvDesc('humanoid', 1.25, 0.1, 0.0, 5.0, True, (0.8, 2.1), False, True)),
+    'humanoid_spring': ('humanoid_spring',
+                        envs.EnvDesc('humanoid', 1.25, 0.1, 0.0, 5.0, True, (0.8, 2.1), False, True)),
+}
+
+
+def env_golden(variant):
+  return np.load(os.path.join(util.GOLDEN, variant + '_env.npz'))
+
+
+@pytest.mark.parametrize('variant', sorted(VARIANTS))
+def test_env_oracle_f64_matches_reference(variant):
+  sysname, env = VARIANTS[variant]
+  g, e = util.load_golden(sysname), env_golden(variant)
+  av = np.load(os.path.join(util.GOLDEN, sysname + '_angle_vel.npz'))
+  desc = util.load_desc(sysname)
+  assert list(e['metric_names']) == list(env.metric_names())
+  assert e['obs'].shape[1] == env.obs_size(desc)
+  assert abs(float(e['dt']) - desc.dt) < 1e-15
+  out = {k: g[k + '_o'] for k in util.QP_KEYS}
+  out.update(contact_vel=g['contact_vel'], contact_ang=g['contact_ang'])
+  r = env_oracle.env_epilogue(desc, env, g['pos'], out, g['act'], av['flat_angle'], av['flat_vel'], np.float64)
+  for k in ('obs', 'reward', 'done', 'metrics'):
+    np.testing.assert_allclose(r[k], e[k], rtol=0, atol=1e-10, err_msg=k)
+
+
+@pytest.mark.parametrize('variant', sorted(VARIANTS))
+def test_env_oracle_chain_matches_reference(variant):
+  """C oracle (step + angle_vel) -> env oracle, float64 end to end, and the float32
+  chain (the CUDA path's checker) within float32 rounding of the reference."""
+  sysname, env = VARIANTS[variant]
+  g, e = util.load_golden(sysname), env_golden(variant)
+  desc = util.load_desc(sysname)
+  for dtype, tol in ((np.float64, 1e-9), (np.float32, None)):
+    o = Oracle(desc, dtype)
+    out = o.step(g['pos'], g['rot'], g['vel'], g['ang'], g['act'])
+    fa, fv = env_oracle.flat_angle_vel(desc, *o.angle_vel(out['rot'], out['ang']))
+    r = env_oracle.env_epilogue(desc, env, g['pos'], out, g['act'], fa, fv, dtype)
+    if tol is not None:
+      for k in ('obs', 'reward', 'done', 'metrics'):
+        np.testing.assert_allclose(r[k], e[k], rtol=0, atol=tol, err_msg=k)
+    else:
+      np.testing.assert_array_equal(r['done'], e['done'])
+      # velocities are position differences over dt (ant.py:226): ulp(pos)/dt of float32
+      np.testing.assert_allclose(r['reward'], e['reward'], rtol=1e-4, atol=5e-3)
+      assert np.quantile(np.abs(r['obs'] - e['obs']), 0.99) < 1e-3
+
+
+def test_obs_sizes():
+  assert VARIANTS['ant'][1].obs_size(util.load_desc('ant')) == 87
+  assert VARIANTS['ant_nocfrc'][1].obs_size(util.load_desc('ant')) == 27
+  assert VARIANTS['humanoid'][1].obs_size(util.load_desc('humanoid')) == 240
+  assert VARIANTS['humanoid_spring'][1].obs_size(util.load_desc('humanoid_spring')) == 227
