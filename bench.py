@@ -353,6 +353,33 @@ def run_gpu(args, desc):
     ea[i][1].record()
   barrier()
   ms_av = float(sum(x.elapsed_time(y) for x, y in ea))
+  # "next" row N1: the whole Env.step (sys.step + obs / reward / done / metrics of
+  # envs/ant.py:222-281, envs/humanoid.py:246-340) as ONE launch; same timing method.
+  ms_env, env_obs = 0.0, 0
+  env_name = args.env[:-len('_spring')] if args.env.endswith('_spring') else args.env
+  if env_name in ('ant', 'humanoid'):
+    from brax_b200 import envs as bx_envs
+    from brax_b200.envs import State
+    kw = dict(use_contact_forces=True) if env_name == 'ant' else {}   # the fork's registration
+    env = bx_envs.create(env_name, legacy_spring=args.env.endswith('_spring'), device=local, **kw)
+    if args.threads or args.contact_section:
+      env.sys.configure(args.threads, args.contact_section)
+    env_obs = env.observation_size
+    sts = [State(q, None, None, None) for q in qps]
+    for j in range(nsets):
+      sts[j] = env.step(sts[j], acts[j % total])
+    barrier()
+    ee = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for i in range(args.steps):
+      if i % CHUNK == 0:
+        torch.cuda._sleep(spin_cycles)
+      j = i % nsets
+      ee[i][0].record()
+      sts[j] = env.step(sts[j], acts[args.warmup + i])
+      ee[i][1].record()
+    barrier()
+    ms_env = float(sum(x.elapsed_time(y) for x, y in ee))
+    qps = [st.qp for st in sts]
   ms_steps = [x.elapsed_time(y) for x, y in ev]
   ms_total = float(sum(ms_steps))
   ms_sorted = sorted(ms_steps)
@@ -386,8 +413,8 @@ def run_gpu(args, desc):
 
   # ---- max over ranks -----------------------------------------------------------
   from brax_b200 import shard
-  ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll, ms_av = shard.reduce_stats(
-      [ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll, ms_av], ['max'] * 7, device=dev)
+  ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll, ms_av, ms_env = shard.reduce_stats(
+      [ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll, ms_av, ms_env], ['max'] * 8, device=dev)
   value = world * b * args.steps / (ms_total * 1e-3)
   value_b2b = world * b * args.steps / (ms_b2b * 1e-3)
   value_flushed = world * b * args.steps / (ms_flushed * 1e-3)
@@ -422,6 +449,10 @@ def run_gpu(args, desc):
         'with_angle_vel_epilogue': {'value': world * b * args.steps / (ms_av * 1e-3), 'unit': UNIT,
                                     'ms_per_step': ms_av / args.steps,
                                     'extra_bytes_per_env_step': 24 * len(desc.joints)},
+        'env_step': ({'value': world * b * args.steps / (ms_env * 1e-3), 'unit': UNIT,
+                      'ms_per_step': ms_env / args.steps, 'obs_size': env_obs,
+                      'what': 'full Env.step (sys.step + obs/reward/done/metrics) in one launch',
+                      'extra_bytes_per_env_step': 4 * (env_obs + 12)} if ms_env > 0 else None),
         'rollout': {'steps_per_launch': roll_t, 'launches': n_roll,
                     'value': world * b * roll_t * n_roll / (ms_roll * 1e-3), 'unit': UNIT,
                     'ms_per_step': ms_roll / (roll_t * n_roll)},

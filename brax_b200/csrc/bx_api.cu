@@ -113,8 +113,25 @@ static int validate(const bx_system_desc* d) {
     k += p.n_contacts;
   }
   if (k > BX_MAX_CONTACTS) return fail("too many contact rows");
+  if (d->env) {
+    const bx_env_desc& e = *d->env;
+    if (e.struct_size != sizeof(bx_env_desc)) return fail("bx_env_desc size mismatch (ABI skew)");
+    if (e.kind != BX_ENV_ANT && e.kind != BX_ENV_HUMANOID)
+      return fail("unsupported env kind (fused epilogues exist for ant and humanoid)");
+    if (!(e.dt > 0.f)) return fail("env dt must be positive");
+    if (e.kind == BX_ENV_HUMANOID && d->num_bodies < 2) return fail("humanoid epilogue needs >= 2 bodies");
+    for (int i = 0; i < d->num_joints; i++)
+      if (e.joint_free_dofs[i] < 0 || e.joint_free_dofs[i] > 3) return fail("joint_free_dofs out of range");
+    for (int i = 0; i < d->num_actuators; i++)
+      if (e.actuator_width[i] < 1 || e.actuator_width[i] > 3) return fail("actuator_width out of range");
+  }
   return 0;
 }
+
+// The outputs of bx_step_io in segment order (pos_o is the first of BX_SEG_OUT pointers).
+static_assert(sizeof(bx_step_io) == (BX_SEG_IN + BX_SEG_OUT) * sizeof(void*), "bx_step_io vs segments");
+static float* const* io_outs(const bx_step_io* io) { return &io->pos_o; }
+static float** io_outs(bx_step_io* io) { return &io->pos_o; }
 
 // Flattens the description into the tables of bx_tables.h.
 static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<int32_t>* ti_out,
@@ -292,6 +309,8 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     const int tail = ct_rows + (spring ? 0 : 2 * ncb) + 2 * ncb + nab + (spring ? 2 * nb : 0);
     js = std::max(js, (in_floats + row_floats - 1) / row_floats - tail);
     js = std::max(js, 2 * nj);  // angle_vel epilogue: {angles}, {velocities} per joint
+    if (d->env)  // env epilogue rows follow the angle_vel rows (bx_tables.h EQ_*)
+      js = std::max(js, 2 * nj + EQ_X + (d->env->kind == BX_ENV_ANT ? 2 * nb : 5 * (nb - 1) + na));
   }
 
   // ---- state quad rows
@@ -305,8 +324,10 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
   h.q_ic = r; r += 2 * ncb;   // q_ic, q_ia, q_ij contiguous: zeroed together
   h.q_ia = r; r += nab;
   h.q_ij = r; r += spring ? 2 * nb : 0;
-  h.n_quads = r;
   h.n_zero = r - h.q_ic;
+  h.q_ep = r; r += d->env ? 1 : 0;  // survives the substeps: reference point before the step
+  h.q_env = h.q_js + 2 * nj;
+  h.n_quads = r;
 
   // ---- int tables (every record 16-byte aligned)
   std::vector<int32_t> adj;
@@ -453,6 +474,55 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
       }
     h.seg_out[13] = seg(3 * nj, 0.f, ma);
     h.seg_out[14] = seg(3 * nj, 0.f, mv);
+  }
+  for (int i = BX_SEG_ENV; i < BX_SEG_OUT; i++) h.seg_out[i] = seg(0, 0.f, std::vector<int>());
+  if (d->env) {
+    // obs: what _get_obs concatenates (envs/ant.py:257-281, envs/humanoid.py:281-330),
+    // every element an address of a row written by phase_angle_vel / phase_env
+    const bx_env_desc& e = *d->env;
+    const int E = h.q_env;
+    std::vector<int> m;
+    auto row3 = [&](int row, int x0 = 0, int n = 3) { for (int x = x0; x < x0 + n; x++) m.push_back(row * RF + x); };
+    auto joints_part = [&](int which) {
+      for (int i = 0; i < nj; i++) row3(h.q_js + 2 * i + which, 0, e.joint_free_dofs[i]);
+    };
+    if (e.exclude_current_positions) row3(E + EQ_TORSO_POS, 2, 1); else row3(E + EQ_TORSO_POS);
+    row3(E + EQ_TORSO_ROT, 0, 4);
+    joints_part(0);
+    row3(bqn * 0 + vel_off);
+    row3(bqn * 0 + ang_off);
+    joints_part(1);
+    int nmetrics = 10;
+    if (e.kind == BX_ENV_ANT) {
+      if (e.use_contact_forces)
+        for (int which = 0; which < 2; which++)
+          for (int b = 0; b < nb; b++) row3(E + EQ_X + 2 * b + which);
+    } else {
+      nmetrics = 9;
+      for (int b = 0; b < nb - 1; b++)
+        for (int rr = 0; rr < 3; rr++) row3(E + EQ_X + 5 * b + rr);
+      for (int b = 0; b < nb - 1; b++) row3(E + EQ_X + 5 * b + 3);
+      for (int b = 0; b < nb - 1; b++) row3(E + EQ_X + 5 * b + 4);
+      for (int i = 0; i < na; i++) row3(E + EQ_X + 5 * (nb - 1) + i, 0, e.actuator_width[i]);
+    }
+    h.seg_out[BX_SEG_ENV] = seg(static_cast<int>(m.size()), 0.f, m);
+    h.seg_out[BX_SEG_ENV + 1] = seg(1, 0.f, std::vector<int>{(E + EQ_S0) * RF + 0});
+    h.seg_out[BX_SEG_ENV + 2] = seg(1, 0.f, std::vector<int>{(E + EQ_S0) * RF + 1});
+    std::vector<int> mm;
+    for (int i = 0; i < nmetrics; i++) mm.push_back((E + EQ_S0) * RF + ((2 + i) >> 2) * RF + ((2 + i) & 3));
+    h.seg_out[BX_SEG_ENV + 3] = seg(nmetrics, 0.f, mm);
+    h.env_kind = e.kind;
+    h.env_flags = (e.use_contact_forces ? 1 : 0) | (e.terminate_when_unhealthy ? 2 : 0);
+    h.env_dt = e.dt;
+    h.env_wf = e.forward_reward_weight;
+    h.env_wc = e.ctrl_cost_weight;
+    h.env_wcc = e.contact_cost_weight;
+    h.env_hr = e.healthy_reward;
+    h.env_zmin = e.healthy_z_min;
+    h.env_zmax = e.healthy_z_max;
+    float msum = 0.f;  // jp.sum(mass[:-1]) in float32
+    for (int b = 0; b < nb - 1; b++) msum += d->bodies[b].mass;
+    h.env_msum = msum;
   }
   align4();
   h.n_ints = static_cast<int>(ti.size());
@@ -633,6 +703,8 @@ extern "C" void bx_system_destroy(bx_system* s) {
 extern "C" int bx_system_num_contacts(const bx_system* s) { return s ? s->h.nk : -1; }
 extern "C" int bx_system_num_bodies(const bx_system* s) { return s ? s->h.nb : -1; }
 extern "C" int bx_system_act_size(const bx_system* s) { return s ? s->h.act_size : -1; }
+extern "C" int bx_system_obs_size(const bx_system* s) { return s ? s->h.seg_out[BX_SEG_ENV].nper : -1; }
+extern "C" int bx_system_num_metrics(const bx_system* s) { return s ? s->h.seg_out[BX_SEG_ENV + 3].nper : -1; }
 
 extern "C" int bx_system_configure(bx_system* s, int32_t threads_per_block, int32_t contact_section) {
   if (!s) return fail("system is NULL");
@@ -661,19 +733,18 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   p.tab_i = s->d_tab_i;
   p.tab_f = s->d_tab_f;
   p.in[0] = io->pos; p.in[1] = io->rot; p.in[2] = io->vel; p.in[3] = io->ang; p.in[4] = io->act;
-  float* const outs[BX_SEG_OUT] = {
-      io->pos_o, io->rot_o, io->vel_o, io->ang_o, io->contact_vel, io->contact_ang,
-      io->joint_vel, io->joint_ang, io->actuator_vel, io->actuator_ang,
-      io->contact_pos, io->contact_normal, io->contact_penetration,
-      io->joint_angle, io->joint_velocity};
-  for (int i = 0; i < BX_SEG_OUT; i++) p.out[i] = outs[i];
+  for (int i = 0; i < BX_SEG_OUT; i++) p.out[i] = io_outs(io)[i];
+  if (!s->h.env_kind && (io->obs || io->reward || io->done || io->metrics))
+    return fail("obs/reward/done/metrics need a system created with desc.env");
   p.num_envs = num_envs;
   p.num_steps = num_steps;
   p.stagger_ns = stagger_ns;
   p.dbg = g_dbg;
   const int64_t tiles = (num_envs + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA;
   if (tiles > 0x7fffffffLL) return fail("too many environments for one launch");
-  cudaError_t le = launch_variant(s->h.mode, s->jc, s->cc, static_cast<unsigned>(tiles), 32 * s->warps,
+  // systems with an env epilogue run the builds that contain it; all others the plain ones
+  cudaError_t le = launch_variant(s->h.mode, s->jc, s->cc | (s->h.env_kind ? BX_CC_ENV : 0),
+                                  static_cast<unsigned>(tiles), 32 * s->warps,
                                   s->smem_bytes, stream, p);
   g_launches.fetch_add(1);
   CUDA_OK(le);
@@ -746,8 +817,8 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
       !hio->vel_o || !hio->ang_o)
     return fail("QP / act pointers must not be NULL");
   CUDA_OK(cudaSetDevice(s->device));
-  const int64_t n = s->h.nb, a = s->h.act_size, k = s->h.nk;
-  // in: 13n + a ; out: 13n + 18n + 7k   (floats per env)
+  const int64_t n = s->h.nb, a = s->h.act_size;
+  // in: 13n + a ; out: the segments' nper (floats per env)
   for (int i = 0; i < BX_HOST_STREAMS; i++)
     if (!s->streams[i]) CUDA_OK(cudaStreamCreateWithFlags(&s->streams[i], cudaStreamNonBlocking));
   {
@@ -757,10 +828,7 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
     // and pushes its outputs with coalesced 128-bit stores, so upload, compute and
     // download of different tiles overlap inside ONE launch.
     const float* hin[BX_SEG_IN] = {hio->pos, hio->rot, hio->vel, hio->ang, hio->act};
-    float* hout[BX_SEG_OUT] = {hio->pos_o, hio->rot_o, hio->vel_o, hio->ang_o, hio->contact_vel,
-                               hio->contact_ang, hio->joint_vel, hio->joint_ang, hio->actuator_vel,
-                               hio->actuator_ang, hio->contact_pos, hio->contact_normal,
-                               hio->contact_penetration, hio->joint_angle, hio->joint_velocity};
+    float* const* hout = io_outs(hio);
     const void* din[BX_SEG_IN];
     void* dout[BX_SEG_OUT];
     bool pinned = true;
@@ -783,11 +851,7 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
       memset(&d, 0, sizeof(d));
       d.pos = (const float*)din[0]; d.rot = (const float*)din[1]; d.vel = (const float*)din[2];
       d.ang = (const float*)din[3]; d.act = (const float*)din[4];
-      float** dp[BX_SEG_OUT] = {&d.pos_o, &d.rot_o, &d.vel_o, &d.ang_o, &d.contact_vel, &d.contact_ang,
-                                &d.joint_vel, &d.joint_ang, &d.actuator_vel, &d.actuator_ang,
-                                &d.contact_pos, &d.contact_normal, &d.contact_penetration,
-                                &d.joint_angle, &d.joint_velocity};
-      for (int i = 0; i < BX_SEG_OUT; i++) *dp[i] = static_cast<float*>(dout[i]);
+      for (int i = 0; i < BX_SEG_OUT; i++) io_outs(&d)[i] = static_cast<float*>(dout[i]);
       cudaStream_t st = s->streams[0];
       // One wave of tiles (all resident together): stagger their starts over the time
       // the larger transfer direction needs at 60 GB/s (measured flat optimum 45-100,
@@ -810,7 +874,8 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
       return 0;
     }
   }
-  const size_t per_env = static_cast<size_t>(13 * n + a + 13 * n + 18 * n + 7 * k + 6 * s->h.nj);
+  size_t per_env = static_cast<size_t>(13 * n + a);
+  for (int i = 0; i < BX_SEG_OUT; i++) per_env += s->h.seg_out[i].nper;
   const size_t need = per_env * B;
   if (need > s->scratch_floats) {
     cudaFree(s->d_scratch);
@@ -826,14 +891,9 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
   const float* h_in[BX_SEG_IN] = {hio->pos, hio->rot, hio->vel, hio->ang, hio->act};
   float* d_in[BX_SEG_IN];
   for (int i = 0; i < BX_SEG_IN; i++) d_in[i] = take(in_per[i]);
-  const size_t out_per[BX_SEG_OUT] = {(size_t)3 * n, (size_t)4 * n, (size_t)3 * n, (size_t)3 * n,
-                                      (size_t)3 * n, (size_t)3 * n, (size_t)3 * n, (size_t)3 * n,
-                                      (size_t)3 * n, (size_t)3 * n, (size_t)3 * k, (size_t)3 * k, (size_t)k,
-                                      (size_t)3 * s->h.nj, (size_t)3 * s->h.nj};
-  float* h_out[BX_SEG_OUT] = {hio->pos_o, hio->rot_o, hio->vel_o, hio->ang_o, hio->contact_vel,
-                              hio->contact_ang, hio->joint_vel, hio->joint_ang, hio->actuator_vel,
-                              hio->actuator_ang, hio->contact_pos, hio->contact_normal,
-                              hio->contact_penetration, hio->joint_angle, hio->joint_velocity};
+  size_t out_per[BX_SEG_OUT];
+  for (int i = 0; i < BX_SEG_OUT; i++) out_per[i] = static_cast<size_t>(s->h.seg_out[i].nper);
+  float* const* h_out = io_outs(hio);
   float* d_out[BX_SEG_OUT];
   for (int i = 0; i < BX_SEG_OUT; i++) d_out[i] = take(out_per[i]);
   // Pipeline: the batch is cut into chunks (multiples of the 32-env tile); chunk
@@ -855,18 +915,15 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
     d.pos = d_in[0] + e0 * in_per[0]; d.rot = d_in[1] + e0 * in_per[1];
     d.vel = d_in[2] + e0 * in_per[2]; d.ang = d_in[3] + e0 * in_per[3];
     d.act = d_in[4] + e0 * in_per[4];
-    float** dp[BX_SEG_OUT] = {&d.pos_o, &d.rot_o, &d.vel_o, &d.ang_o, &d.contact_vel, &d.contact_ang,
-                              &d.joint_vel, &d.joint_ang, &d.actuator_vel, &d.actuator_ang,
-                              &d.contact_pos, &d.contact_normal, &d.contact_penetration,
-                              &d.joint_angle, &d.joint_velocity};
+    float** dp = io_outs(&d);
     for (int i = 0; i < BX_SEG_OUT; i++) {
       const bool constant = s->h.seg_out[i].map < 0;
-      *dp[i] = (i < 4 || (h_out[i] && out_per[i] && !constant)) ? d_out[i] + e0 * out_per[i] : nullptr;
+      dp[i] = (i < 4 || (h_out[i] && out_per[i] && !constant)) ? d_out[i] + e0 * out_per[i] : nullptr;
     }
     if (launch(s, nb_, 1, &d, st)) return 1;
     for (int i = 0; i < BX_SEG_OUT; i++)
-      if (*dp[i] && h_out[i])
-        CUDA_OK(cudaMemcpyAsync(h_out[i] + e0 * out_per[i], *dp[i], out_per[i] * nb_ * 4,
+      if (dp[i] && h_out[i])
+        CUDA_OK(cudaMemcpyAsync(h_out[i] + e0 * out_per[i], dp[i], out_per[i] * nb_ * 4,
                                 cudaMemcpyDeviceToHost, st));
   }
   for (int i = 4; i < BX_SEG_OUT; i++)

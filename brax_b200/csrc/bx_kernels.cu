@@ -13,9 +13,9 @@
 
 typedef void (*bx_kernel_fn)(const BxKernelParams);
 
-template <int MODE>
+template <int MODE, int ENV>
 static bx_kernel_fn pick(int jc, int cc) {
-#define BX_K(JM, CM) bx_step_kernel<MODE, (JM) | (CM) | BXF_COMMON, BX_TU_MAXT, BX_TU_MINB>
+#define BX_K(JM, CM) bx_step_kernel<MODE, (JM) | (CM) | BXF_COMMON | ENV, BX_TU_MAXT, BX_TU_MINB>
   if (MODE == BX_MODE_PBD && cc == BX_CC_PLANE_FUSED) {
     if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC0 | BXF_FUSED_CONTACTS);
     if (jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC0 | BXF_FUSED_CONTACTS);
@@ -33,7 +33,11 @@ static bx_kernel_fn pick(int jc, int cc) {
 }
 
 static bx_kernel_fn pick_any(int mode, int jc, int cc) {
-  return mode == BX_MODE_PBD ? pick<BX_MODE_PBD>(jc, cc) : pick<BX_MODE_LEGACY_SPRING>(jc, cc);
+  if (cc & BX_CC_ENV) {
+    cc &= ~BX_CC_ENV;
+    return mode == BX_MODE_PBD ? pick<BX_MODE_PBD, BXF_ENV>(jc, cc) : pick<BX_MODE_LEGACY_SPRING, BXF_ENV>(jc, cc);
+  }
+  return mode == BX_MODE_PBD ? pick<BX_MODE_PBD, 0>(jc, cc) : pick<BX_MODE_LEGACY_SPRING, 0>(jc, cc);
 }
 
 cudaError_t BX_CAT(bx_launch_, BX_TU_MAXT)(int mode, int jc, int cc, unsigned grid, int threads,
@@ -46,10 +50,11 @@ cudaError_t BX_CAT(bx_launch_, BX_TU_MAXT)(int mode, int jc, int cc, unsigned gr
 cudaError_t BX_CAT(bx_set_smem_, BX_TU_MAXT)(int bytes) {
   for (int mode = 0; mode < 2; mode++)
     for (int jc = 0; jc < BX_NUM_JC; jc++)
-      for (int cc = 0; cc < BX_NUM_CC; cc++) {
-        cudaError_t e = cudaFuncSetAttribute(pick_any(mode, jc, cc),
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        if (e != cudaSuccess) return e;
-      }
+      for (int cc = 0; cc < BX_NUM_CC; cc++)
+        for (int env = 0; env < 2; env++) {
+          cudaError_t e = cudaFuncSetAttribute(pick_any(mode, jc, cc | (env ? BX_CC_ENV : 0)),
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+          if (e != cudaSuccess) return e;
+        }
   return cudaSuccess;
 }

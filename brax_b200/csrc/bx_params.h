@@ -31,8 +31,10 @@ enum {
   BXF_CAPSULE_PLANE = 32, BXF_CAPSULE_CAPSULE = 64, BXF_BOX_PLANE = 128,
   BXF_TORQUE = 256, BXF_ANGLE = 512, BXF_FORCES = 1024,
   BXF_FUSED_CONTACTS = 2048,  // pbd, one-way colliders, <= 2 rows per body
+  BXF_ENV = 4096,             // env epilogue compiled in (systems created with desc.env)
   BXF_ALL = 2047
 };
+#define BX_CC_ENV 8  // or-ed into the contact class passed to bx_launch_*: env-epilogue build
 // Kernel variants are instantiated per (dynamics mode, joint class, contact
 // class, launch bound).  Classes are the feature sets of the reference's envs:
 // all-revolute (ant, fetch), all-spherical (humanoid, grasp: joints.py:418-474

@@ -218,17 +218,20 @@ BXS void unstage_warp(float* smf, const int32_t* ti, const BxSeg& sg, const floa
   }
 }
 // state quads -> global (coalesced 128-bit stores); constant segments are a fill
-BXS void store_warp(const float* smf, const int32_t* ti, const BxSeg& sg, float* gspan, int lane) {
+// (lane, stride) = (lane, 32): one warp moves the segment; (threadIdx.x, blockDim.x): the
+// whole CTA shares it (long segments: the env epilogue's obs)
+BXS void store_warp(const float* smf, const int32_t* ti, const BxSeg& sg, float* gspan, int lane,
+                    int stride = 32) {
   const int n4 = BX_ENVS_PER_CTA / 4 * sg.nper;
   float4* g4 = reinterpret_cast<float4*>(gspan);
   if (sg.map < 0) {
     const float4 f = make_float4(sg.fill, sg.fill, sg.fill, sg.fill);
-    for (int i = lane; i < n4; i += 32) g4[i] = f;
+    for (int i = lane; i < n4; i += stride) g4[i] = f;
     return;
   }
   const int32_t* map = ti + sg.map;
 #pragma unroll 1
-  for (int i = lane; i < n4; i += 32) {
+  for (int i = lane; i < n4; i += stride) {
     int e, r;
     seg_locate(sg, i << 2, &e, &r);
     float vv[4];
@@ -1229,6 +1232,119 @@ BXS void phase_angle_vel(const Ctx& c, const BxHeader& h) {
   }
 }
 
+// ---- optional epilogue: the reference's Env.step after sys.step -----------------
+// envs/ant.py:222-281 (Ant.step, _get_obs), envs/humanoid.py:246-340 (Humanoid.step,
+// _get_obs, _center_of_mass).  Rows q_env + EQ_* (bx_tables.h) receive everything
+// the obs / reward / done / metrics segments point at; the joint angles come from
+// phase_angle_vel's rows.  lane = env as everywhere.
+template <int MODE>
+BXS V3 env_com(const Ctx& c, const BxHeader& h, int po) {  // humanoid.py:332-334
+  typedef Lay<MODE> L;
+  V3 s = v3(0.f, 0.f, 0.f);
+  for (int b = 0; b < h.nb - 1; b++)
+    s = s + c.tf[h.fo_body + b * BQ_STRIDE + BQ_MASS].y * ldv(c, L::BQ * b + po);
+  return vdiv(s, h.env_msum);
+}
+// reference point before the step: torso position (ant.py:226) / centre of mass
+// (humanoid.py:250); one warp, at the start of every step
+template <int MODE>
+static __device__ __noinline__ void phase_env_before(const Ctx c, const BxHeader& h) {
+  typedef Lay<MODE> L;
+  const int po = MODE == BX_MODE_PBD ? 2 * c.cur : 0;
+  stv(c, h.q_ep, h.env_kind == BX_ENV_ANT ? ldv(c, L::BQ * 0 + po) : env_com<MODE>(c, h, po));
+}
+template <int MODE>
+static __device__ __noinline__ void phase_env(const Ctx c, const BxHeader& h) {
+  typedef Lay<MODE> L;
+  const int po = MODE == BX_MODE_PBD ? 2 * c.cur : 0;
+  const int E = h.q_env;
+  const bool scalar_warp = c.warp == c.nwarp - 1;
+  float ctrl = 0.f, contact = 0.f;
+  V3 ref = v3(0.f, 0.f, 0.f);  // torso position (ant) / centre of mass (humanoid) after the step
+  if (h.env_kind == BX_ENV_ANT) {
+    if (h.env_flags & 1)  // cfrc = clip(info.contact, -1, 1)  (ant.py:271-279)
+      for (int b = c.warp; b < h.nb; b += c.nwarp) {
+        const int cs = c.ti[h.io_body + b * BI_STRIDE + BI_CSLOT];
+        V3 v = v3(0.f, 0.f, 0.f), w = v;
+        if (cs >= 0) { v = ldv(c, h.q_ic + 2 * cs); w = ldv(c, h.q_ic + 2 * cs + 1); }
+        stv(c, E + EQ_X + 2 * b, v3(clipf(v.x, -1.f, 1.f), clipf(v.y, -1.f, 1.f), clipf(v.z, -1.f, 1.f)));
+        stv(c, E + EQ_X + 2 * b + 1, v3(clipf(w.x, -1.f, 1.f), clipf(w.y, -1.f, 1.f), clipf(w.z, -1.f, 1.f)));
+      }
+    if (scalar_warp) {
+      ref = ldv(c, L::BQ * 0 + po);
+      for (int b = 0; b < h.nb; b++) {  // contact_cost (ant.py:237-238)
+        const int cs = c.ti[h.io_body + b * BI_STRIDE + BI_CSLOT];
+        if (cs < 0) continue;
+        const V3 v = ldv(c, h.q_ic + 2 * cs);
+        const float x = clipf(v.x, -1.f, 1.f), y = clipf(v.y, -1.f, 1.f), z = clipf(v.z, -1.f, 1.f);
+        contact += x * x;
+        contact += y * y;
+        contact += z * z;
+      }
+      contact *= h.env_wcc;
+    }
+  } else {
+    ref = env_com<MODE>(c, h, po);
+    // com_vals (humanoid.py:301-308); Body.inertia is the INVERSE inertia (bodies.py:40)
+    for (int b = c.warp; b < h.nb - 1; b += c.nwarp) {
+      const float4 bm = c.tf[h.fo_body + b * BQ_STRIDE + BQ_MASS];
+      const float4 ii = c.tf[h.fo_body + b * BQ_STRIDE + BQ_INV_INERTIA];
+      const V3 d = ldv(c, L::BQ * b + po) - ref;
+      const V3 vel = ldv(c, L::BQ * b + L::VEL);
+      const float nrm = bx_sqrt(d.x * d.x + d.y * d.y + d.z * d.z);
+      const float n2 = nrm * nrm;  // jp.norm(d) ** 2
+      const float mn = bm.y * n2;
+      const int r0 = E + EQ_X + 5 * b;
+      stv(c, r0 + 0, v3(mn + (ii.x - d.x * d.x), -(d.x * d.y), -(d.x * d.z)));
+      stv(c, r0 + 1, v3(-(d.y * d.x), mn + (ii.y - d.y * d.y), -(d.y * d.z)));
+      stv(c, r0 + 2, v3(-(d.z * d.x), -(d.z * d.y), mn + (ii.z - d.z * d.z)));
+      stv(c, r0 + 3, vdiv(bm.y * vel, h.env_msum));
+      stv(c, r0 + 4, vdiv(cross(d, vel), 1e-7f + n2));
+    }
+    // qfrc_actuator = take(action, act_index, clip) * strength (humanoid.py:314-319):
+    // masked slots (-1) clamp to action[0], as jp.take does
+    for (int i = c.warp; i < h.na; i += c.nwarp) {
+      const int32_t* ai = c.ti + h.io_act + i * AI_STRIDE;
+      const float st = c.tf[h.fo_act + i].x;
+      float q[3];
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const int idx = ai[AI_IDX + k];
+        q[k] = act_at(c, h, idx < 0 ? 0 : idx) * st;
+      }
+      stv(c, E + EQ_X + 5 * (h.nb - 1) + i, v3(q[0], q[1], q[2]));
+    }
+  }
+  if (!scalar_warp) return;
+  const V3 p0 = ldv(c, L::BQ * 0 + po);
+  QROW(c, E + EQ_TORSO_POS) = QROW(c, L::BQ * 0 + po);
+  QROW(c, E + EQ_TORSO_ROT) = QROW(c, L::BQ * 0 + po + 1);
+  const V3 velocity = vdiv(ref - ldv(c, h.q_ep), h.env_dt);  // ant.py:226, humanoid.py:252
+  const float forward = h.env_kind == BX_ENV_ANT ? velocity.x : h.env_wf * velocity.x;
+  float healthy = p0.z < h.env_zmin ? 0.f : 1.f;             // ant.py:229-231
+  healthy = p0.z > h.env_zmax ? 0.f : healthy;
+  const bool term = (h.env_flags & 2) != 0;
+  const float hr = term ? h.env_hr : h.env_hr * healthy;
+  for (int i = 0; i < h.act_size; i++) {
+    const float a = act_at(c, h, i);
+    ctrl += a * a;
+  }
+  ctrl *= h.env_wc;
+  const float dist = bx_sqrt(ref.x * ref.x + ref.y * ref.y + ref.z * ref.z);
+  const float done = term ? 1.f - healthy : 0.f;
+  if (h.env_kind == BX_ENV_ANT) {
+    const float reward = forward + hr - ctrl - contact;        // ant.py:240
+    QROW(c, E + EQ_S0) = make_float4(reward, done, forward, hr);
+    QROW(c, E + EQ_S1) = make_float4(-ctrl, -contact, ref.x, ref.y);
+    QROW(c, E + EQ_S2) = make_float4(dist, velocity.x, velocity.y, forward);
+  } else {
+    const float reward = forward + hr - ctrl;                  // humanoid.py:265
+    QROW(c, E + EQ_S0) = make_float4(reward, done, forward, forward);
+    QROW(c, E + EQ_S1) = make_float4(-ctrl, hr, ref.x, ref.y);
+    QROW(c, E + EQ_S2) = make_float4(dist, velocity.x, velocity.y, 0.f);
+  }
+}
+
 // ============================== the kernel ====================================
 // The whole step of one tile of 32 environments (called by bx_step_kernel below).
 template <int MODE>
@@ -1337,6 +1453,8 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
   c.moff = 0;
 #endif
 
+  const bool env_on = (BX_FEAT & BXF_ENV) != 0 && h.env_kind != BX_ENV_NONE && (p.out[BX_SEG_ENV] != nullptr || p.out[BX_SEG_ENV + 1] != nullptr ||
+                                                    p.out[BX_SEG_ENV + 2] != nullptr || p.out[BX_SEG_ENV + 3] != nullptr);
   for (int step = 0; step < p.num_steps; step++) {
     __syncthreads();
     if (step > 0) {  // rollout: the actions of step t (step 0 came with the state)
@@ -1363,6 +1481,7 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
       if (h.iters == 0)  // contact_penetration = -1 (system.py:84)
         for (int i = threadIdx.x; i < (h.q_pre - h.q_ct) * QS; i += blockDim.x)
           sq[h.q_ct * QS + i] = i < h.nk * QS ? make_float4(0.f, 0.f, 0.f, -1.f) : z;
+      if (env_on && c.warp == c.nwarp - 1) phase_env_before<MODE>(c, h);
     }
     __syncthreads();
     PT(1);
@@ -1419,9 +1538,40 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
         // same warp<->body mapping as phase_body_kinetic: no barrier needed
       }
     }
+    if (env_on) {
+      // Env.step's epilogue of THIS step (every step of a rollout): obs / reward / done /
+      // metrics [T,B,...]
+      __syncthreads();
+      phase_angle_vel<MODE>(c, h);  // writes rows only the stores read: no barrier before phase_env
+      phase_env<MODE>(c, h);
+      __syncthreads();
+      auto env_ptr = [&](int s) -> float* {
+        return p.out[s] == nullptr ? nullptr
+            : p.out[s] + static_cast<int64_t>(step) * p.num_envs * h.seg_out[s].nper;
+      };
+      bool vec = full;
+#pragma unroll
+      for (int s = BX_SEG_ENV; s < BX_SEG_OUT; s++)
+        vec = vec && (p.out[s] == nullptr || span_bulk_ok(h.seg_out[s], env_ptr(s), env0));
+      if (vec) {
+        // obs is long (87 .. 240 floats per env): the whole CTA shares it; the three short
+        // segments go to the last warps
+        if (p.out[BX_SEG_ENV] != nullptr)
+          store_warp(smf, ti, h.seg_out[BX_SEG_ENV], env_ptr(BX_SEG_ENV) + env0 * h.seg_out[BX_SEG_ENV].nper,
+                     threadIdx.x, blockDim.x);
+        for (int s = BX_SEG_ENV + 1 + (c.nwarp - 1 - c.warp); s < BX_SEG_OUT; s += c.nwarp)
+          if (p.out[s] != nullptr)
+            store_warp(smf, ti, h.seg_out[s], env_ptr(s) + env0 * h.seg_out[s].nper, threadIdx.x & 31);
+      } else {
+#pragma unroll 1
+        for (int s = BX_SEG_ENV; s < BX_SEG_OUT; s++)
+          if (p.out[s] != nullptr)
+            io_segment_scalar<false>(smf, ti, h.seg_out[s], env_ptr(s), env0, nenv);
+      }
+    }
   }
   __syncthreads();
-  if (p.out[13] != nullptr || p.out[14] != nullptr) {
+  if (!env_on && (p.out[13] != nullptr || p.out[14] != nullptr)) {
     phase_angle_vel<MODE>(c, h);
     __syncthreads();
   }
@@ -1433,16 +1583,16 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
   const int cur_shift = (MODE == BX_MODE_PBD && c.cur) ? 2 * QS * 4 : 0;
   bool out_vec = full;
 #pragma unroll
-  for (int s = 0; s < BX_SEG_OUT; s++)
+  for (int s = 0; s < BX_SEG_OUT_STEP; s++)
     out_vec = out_vec && (p.out[s] == nullptr || span_bulk_ok(h.seg_out[s], p.out[s], env0));
   if (out_vec) {
-    for (int s = c.warp; s < BX_SEG_OUT; s += c.nwarp)
+    for (int s = c.warp; s < BX_SEG_OUT_STEP; s += c.nwarp)
       if (p.out[s] != nullptr && h.seg_out[s].nper > 0)
         store_warp(smf + (s < 2 ? cur_shift : 0), ti, h.seg_out[s],
                    p.out[s] + env0 * h.seg_out[s].nper, threadIdx.x & 31);
   } else {
 #pragma unroll 1
-    for (int s = 0; s < BX_SEG_OUT; s++)
+    for (int s = 0; s < BX_SEG_OUT_STEP; s++)
       if (p.out[s] != nullptr && h.seg_out[s].nper > 0)
         io_segment_scalar<false>(smf + (s < 2 ? cur_shift : 0), ti, h.seg_out[s], p.out[s], env0, nenv);
   }

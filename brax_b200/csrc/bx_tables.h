@@ -103,7 +103,9 @@ enum {
 // Global <-> shared I/O segment: global array g[B][nper]; element (e, r) lives at
 // shared float index map[r] + 4 * e (map[r] < 0: the element is a constant).
 #define BX_SEG_IN 5    // pos rot vel ang act
-#define BX_SEG_OUT 15  // pos rot vel ang + 6 Info P + contact pos/normal/pen + joint angle/velocity
+#define BX_SEG_OUT_STEP 15  // pos rot vel ang + 6 Info P + contact pos/normal/pen + joint angle/velocity
+#define BX_SEG_OUT 19       // ... + env epilogue: obs, reward, done, metrics (written every step of a rollout)
+#define BX_SEG_ENV BX_SEG_OUT_STEP
 struct BxSeg {
   int32_t nper;   // floats per environment
   int32_t map;    // offset of map[nper] in the int table
@@ -140,7 +142,34 @@ struct BxHeader {
   float vel_damp, ang_damp;
   float erp, collide_scale, vth;
   float inv_2h;  // 1 / (2*dt_sub), colliders.py:399
+  // ---- env epilogue (optional; env_kind 0 = none): what Ant.step / Humanoid.step
+  // compute after sys.step (envs/ant.py:222-281, envs/humanoid.py:246-340)
+  int32_t env_kind;    // BX_ENV_*
+  int32_t env_flags;   // bit 0 use_contact_forces, bit 1 terminate_when_unhealthy
+  int32_t q_ep;        // persistent row: reference point BEFORE the step (torso pos / centre of mass)
+  int32_t q_env;       // first env row (inside JS, after the angle_vel rows): layout EQ_* below
+  float env_dt;        // config.dt
+  float env_wf, env_wc, env_wcc, env_hr;  // forward / ctrl / contact weights, healthy_reward
+  float env_zmin, env_zmax;
+  float env_msum;      // humanoid: sum of the masses of bodies [0, nb-1) (float32 sum on the host)
 };
+
+// env rows relative to q_env
+enum {
+  EQ_TORSO_POS = 0,  // {pos of body 0}
+  EQ_TORSO_ROT = 1,  // {rot of body 0 (w,x,y,z)}
+  EQ_S0 = 2,         // {reward, done, metric 0, metric 1}
+  EQ_S1 = 3,         // {metric 2..5}
+  EQ_S2 = 4,         // {metric 6..9}
+  EQ_X = 5,          // ant: per body {clip(contact.vel)}, {clip(contact.ang)} (2 rows);
+                     // humanoid: per body b < nb-1 {com_inr rows 0..2}, {com_vel}, {com_ang} (5 rows),
+                     // then one row per actuator {act[idx] * strength}
+};
+#ifndef BX_ENV_NONE  // also in include/brax_b200.h
+#define BX_ENV_NONE 0
+#define BX_ENV_ANT 1
+#define BX_ENV_HUMANOID 2
+#endif
 
 #define BX_QSTRIDE 33  // quads per row: 32 env slots + 1 pad (conflict-free transposing I/O)
 #define BX_ENVS_PER_CTA 32

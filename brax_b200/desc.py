@@ -20,7 +20,7 @@ from typing import Any, Dict, List
 
 import numpy as np
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 MODE = {'pbd': 0, 'legacy_spring': 1}
 JOINT_KIND = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
@@ -80,7 +80,8 @@ class CSystemDesc(C.Structure):
               ('collide_scale', C.c_float), ('velocity_threshold', C.c_float),
               ('bodies', C.POINTER(CBody)), ('joints', C.POINTER(CJoint)),
               ('actuators', C.POINTER(CActuator)),
-              ('forces', C.POINTER(CForce)), ('pairs', C.POINTER(CPair))]
+              ('forces', C.POINTER(CForce)), ('pairs', C.POINTER(CPair)),
+              ('env', C.c_void_p)]
 
 
 class CStepIO(C.Structure):
@@ -88,7 +89,7 @@ class CStepIO(C.Structure):
       'pos', 'rot', 'vel', 'ang', 'act', 'pos_o', 'rot_o', 'vel_o', 'ang_o',
       'contact_vel', 'contact_ang', 'joint_vel', 'joint_ang', 'actuator_vel',
       'actuator_ang', 'contact_pos', 'contact_normal', 'contact_penetration',
-      'joint_angle', 'joint_velocity')]
+      'joint_angle', 'joint_velocity', 'obs', 'reward', 'done', 'metrics')]
 
 
 def _f(x):
@@ -185,8 +186,9 @@ class SystemDesc:
         raise ValueError('unsupported collider pair %r' % p['kind'])
 
   # ---- C packing -----------------------------------------------------------
-  def to_c(self):
-    """Returns (CSystemDesc, keepalive) with float32-rounded tables."""
+  def to_c(self, env=None):
+    """Returns (CSystemDesc, keepalive) with float32-rounded tables.  env: optional
+    `brax_b200.envs.EnvDesc` (the env epilogue, bx_env_desc)."""
     self.validate()
     bodies = (CBody * max(1, self.num_bodies))()
     for i, b in enumerate(self.bodies):
@@ -259,4 +261,6 @@ class SystemDesc:
     d.actuators = C.cast(acts, C.POINTER(CActuator))
     d.forces = C.cast(forces, C.POINTER(CForce))
     d.pairs = C.cast(pairs, C.POINTER(CPair))
-    return d, (bodies, joints, acts, forces, pairs)
+    cenv = env.to_c(self) if env is not None else None
+    d.env = C.cast(C.pointer(cenv), C.c_void_p) if cenv is not None else None
+    return d, (bodies, joints, acts, forces, pairs, cenv)

@@ -108,8 +108,7 @@ class Env:
 
   def __init__(self, system_name: str, env: EnvDesc, device: int = 0):
     self.env = env
-    self.sys = _system.load_system(system_name, device)
-    self.sys.set_env(env)
+    self.sys = _system.load_system(system_name, device, env)
     self.observation_size = env.obs_size(self.sys.desc)
     self.action_size = self.sys.act_size
 

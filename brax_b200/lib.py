@@ -12,7 +12,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get('BRAX_B200_LIB') or os.path.join(HERE, 'libbrax_b200.so')
 
 SYMBOLS = ('bx_system_create', 'bx_system_destroy', 'bx_system_num_contacts',
-           'bx_system_num_bodies', 'bx_system_act_size', 'bx_step',
+           'bx_system_num_bodies', 'bx_system_act_size', 'bx_system_obs_size',
+           'bx_system_num_metrics', 'bx_step',
            'bx_step_host', 'bx_rollout', 'bx_system_configure',
            'bx_system_autotune', 'bx_system_threads', 'bx_host_transfer_bytes',
            'bx_host_alloc', 'bx_host_free', 'bx_desc_tile_bytes',
@@ -38,7 +39,7 @@ def load():
   lib.bx_system_destroy.argtypes = [P]
   lib.bx_system_destroy.restype = None
   for f in ('bx_system_num_contacts', 'bx_system_num_bodies',
-            'bx_system_act_size'):
+            'bx_system_act_size', 'bx_system_obs_size', 'bx_system_num_metrics'):
     getattr(lib, f).argtypes = [P]
     getattr(lib, f).restype = C.c_int
   lib.bx_step.argtypes = [P, C.c_int64, C.POINTER(_desc.CStepIO), P]

@@ -59,6 +59,8 @@ _OUT = (('pos_o', 3, 'n'), ('rot_o', 4, 'n'), ('vel_o', 3, 'n'),
         ('contact_normal', 3, 'k'), ('contact_penetration', 0, 'k'))
 # optional epilogue: Joint.angle_vel of the new state, [B, J, 3] each
 _OUT_AV = (('joint_angle', 3, 'j'), ('joint_velocity', 3, 'j'))
+# optional env epilogue (systems created with an EnvDesc): Env.step's outputs
+_OUT_ENV = (('obs', 1, 'o'), ('reward', 0, 'one'), ('done', 0, 'one'), ('metrics', 1, 'm'))
 
 
 @dataclasses.dataclass
@@ -101,6 +103,11 @@ class HostBuffers:
     for name, w, _ in _OUT_AV:
       self.out[name] = arr((batch, nj, w))
       self.out_ptr[name] = self._ptrs[-1] if self.out[name].size else None
+    if system.env is not None:
+      for name, shape in (('obs', (batch, system.obs_size)), ('reward', (batch,)), ('done', (batch,)),
+                          ('metrics', (batch, system.num_metrics))):
+        self.out[name] = arr(shape)
+        self.out_ptr[name] = self._ptrs[-1]
     self.pos, self.rot = arr((batch, n, 3)), arr((batch, n, 4))
     self.vel, self.ang = arr((batch, n, 3)), arr((batch, n, 3))
     self.act = arr((batch, a))
@@ -122,11 +129,12 @@ def _is_torch(x) -> bool:
   return type(x).__module__.startswith('torch')
 
 
-def tile_bytes(desc: SystemDesc):
-  """(shared-memory bytes of one 32-env tile, quad rows per region) of a system;
-  needs no device (bx_desc_tile_bytes)."""
+def tile_bytes(desc: SystemDesc, env=None):
+  """(shared-memory bytes of one 32-env tile, quad rows per region) of a system
+  (with the env epilogue of `env`, an EnvDesc, if given); needs no device
+  (bx_desc_tile_bytes)."""
   lib = _lib.load()
-  cdesc, keep = desc.to_c()
+  cdesc, keep = desc.to_c(env)
   nbytes = C.c_int64()
   rows = (C.c_int32 * 8)()
   rc = lib.bx_desc_tile_bytes(C.byref(cdesc), C.byref(nbytes), rows)
@@ -140,14 +148,17 @@ def tile_bytes(desc: SystemDesc):
 class System:
   """A brax v1 system whose `step` is the fused sm_100a kernel."""
 
-  def __init__(self, desc: SystemDesc, device: int = 0):
+  def __init__(self, desc: SystemDesc, device: int = 0, env=None):
+    """env: optional `brax_b200.envs.EnvDesc`; the step can then also return what
+    the reference's `Env.step` computes after `sys.step` (`step(..., env=True)`)."""
     self.desc = desc
+    self.env = env
     self.device = device
     self.num_bodies = desc.num_bodies
     self.num_contacts = desc.num_contacts
     self.act_size = desc.act_size
     self._lib = _lib.load()
-    cdesc, keep = desc.to_c()
+    cdesc, keep = desc.to_c(env)
     handle = C.c_void_p()
     rc = self._lib.bx_system_create(C.byref(cdesc), device, C.byref(handle))
     del keep
@@ -162,6 +173,10 @@ class System:
     self.autotune = False
     self._plans = {}           # batch -> output slicing plan
     self._io = CStepIO()
+    self.obs_size = self._lib.bx_system_obs_size(self._h) if env is not None else 0
+    self.num_metrics = self._lib.bx_system_num_metrics(self._h) if env is not None else 0
+    if env is not None and self.obs_size != env.obs_size(desc):
+      raise RuntimeError('obs size: library %d, EnvDesc %d' % (self.obs_size, env.obs_size(desc)))
 
   @classmethod
   def from_brax(cls, brax_system, name: str = 'system', act_size=None,
@@ -205,17 +220,22 @@ class System:
     return QP(*arrs)
 
   # ---- the step ---------------------------------------------------------------
-  def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False):
+  def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False, env: bool = False):
     """`System.step(qp, act) -> (qp, info)` (system.py:244-247).
 
     out: optional `HostBuffers` (host path only): results are written into its
     page-locked arrays instead of freshly allocated pageable ones.
-    angle_vel: also return `Joint.angle_vel` of the new state as a third value
+    angle_vel: also return `Joint.angle_vel` of the new state as a further value
     (`JointState`), computed in the same launch -- what every env's `_get_obs`
-    asks for right after the step (envs/ant.py:259, envs/humanoid.py:285)."""
+    asks for right after the step (envs/ant.py:259, envs/humanoid.py:285).
+    env: (systems built with an EnvDesc) also return, last, a dict with what the
+    reference's `Env.step` computes after `sys.step` -- obs [B,O], reward [B],
+    done [B], metrics [B,M] (envs/ant.py:222-281, envs/humanoid.py:246-340)."""
+    if env and self.env is None:
+      raise ValueError('this System was built without an EnvDesc')
     if _is_torch(qp.pos):
-      return self._step_torch(qp, act, 1, angle_vel)
-    return self._step_numpy(qp, act, out, angle_vel)
+      return self._step_torch(qp, act, 1, angle_vel, env)
+    return self._step_numpy(qp, act, out, angle_vel, env)
 
   def angle_vel_groups(self, js: JointState):
     """[(angle, vel) per joint group] exactly as `[j.angle_vel(qp) for j in
@@ -243,10 +263,14 @@ class System:
     self._lib.bx_host_transfer_bytes(self._h, batch, C.byref(h2d), C.byref(d2h))
     return int(h2d.value), int(d2h.value)
 
-  def rollout(self, qp: QP, acts) -> Tuple[QP, Info]:
+  def rollout(self, qp: QP, acts, env: bool = False):
     """T steps in ONE launch; acts is [T, B, A] (torch CUDA).  Returns the final
-    QP and the Info of the last step (lax.scan of System.step over actions)."""
-    return self._step_torch(qp, acts, int(acts.shape[0]), False)
+    QP and the Info of the last step (lax.scan of System.step over actions); with
+    env=True also the env epilogue of EVERY step: obs [T,B,O], reward / done [T,B],
+    metrics [T,B,M]."""
+    if env and self.env is None:
+      raise ValueError('this System was built without an EnvDesc')
+    return self._step_torch(qp, acts, int(acts.shape[0]), False, env)
 
   def _shapes(self, pos_shape):
     n = self.num_bodies
@@ -260,7 +284,22 @@ class System:
       raise ValueError('qp.pos has shape %s, system has %d bodies' % (tuple(pos_shape), n))
     return batched, b
 
-  def _wrap(self, out, batched) -> Tuple[QP, Info]:
+  def _specs(self, b, av, env, steps=1):
+    """[(name, shape)] of the outputs of one call."""
+    dims = {'n': self.num_bodies, 'k': self.num_contacts, 'j': len(self.desc.joints)}
+    specs = [(name, (b, dims[dim], w) if w else (b, dims[dim])) for name, w, dim in (_OUT + _OUT_AV if av else _OUT)]
+    if env:
+      lead = (steps, b) if steps > 1 else (b,)
+      specs += [('obs', lead + (self.obs_size,)), ('reward', lead), ('done', lead),
+                ('metrics', lead + (self.num_metrics,))]
+    return specs
+
+  def _wrap(self, out, batched, steps=1):
+    env_out = None
+    if 'obs' in out:
+      env_out = {k: out.pop(k) for k in ('obs', 'reward', 'done', 'metrics')}
+      if not batched:
+        env_out = {k: (v[:, 0] if steps > 1 else v[0]) for k, v in env_out.items()}
     if not batched:
       out = {k: v[0] for k, v in out.items()}
     qp = QP(out['pos_o'], out['rot_o'], out['vel_o'], out['ang_o'])
@@ -269,27 +308,33 @@ class System:
                 P(out['actuator_vel'], out['actuator_ang']),
                 out['contact_pos'], out['contact_normal'],
                 out['contact_penetration'])
+    res = (qp, info)
     if 'joint_angle' in out:
-      return qp, info, JointState(out['joint_angle'], out['joint_velocity'])
-    return qp, info
+      res += (JointState(out['joint_angle'], out['joint_velocity']),)
+    if env_out is not None:
+      res += (env_out,)
+    return res
 
-  def _out_plan(self, b, av):
+  def _out_plan(self, b, av, env=False, steps=1):
     """Per batch size: the outputs as slices of ONE allocation (each slice
     starts on a 16-byte boundary so the kernel's vector stores apply)."""
-    plan = self._plans.get((b, av))
+    key = (b, av, env, steps)
+    plan = self._plans.get(key)
     if plan is None:
-      dims = {'n': self.num_bodies, 'k': self.num_contacts, 'j': len(self.desc.joints)}
       names, shapes, offs, off = [], [], [], 0
-      for name, w, dim in (_OUT + _OUT_AV if av else _OUT):
-        m = dims[dim]
+      for name, shape in self._specs(b, av, env, steps):
         names.append(name)
-        shapes.append((b, m, w) if w else (b, m))
+        shapes.append(shape)
         offs.append(off)
-        off += -(-(b * m * max(w, 1)) // 4) * 4
-      plan = self._plans[(b, av)] = (names, shapes, offs, max(off, 4))
+        off += -(-int(np.prod(shape)) // 4) * 4
+      plan = self._plans[key] = (names, shapes, offs, max(off, 4))
     return plan
 
-  def _step_torch(self, qp: QP, act, steps: int, av: bool = False):
+  def _clear_optional(self, io):
+    io.joint_angle = io.joint_velocity = None
+    io.obs = io.reward = io.done = io.metrics = None
+
+  def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False):
     import torch
     batched, b = self._shapes(qp.pos.shape)
     n, a = self.num_bodies, self.act_size
@@ -312,12 +357,12 @@ class System:
 
     ins = (prep(qp.pos, b * n * 3), prep(qp.rot, b * n * 4), prep(qp.vel, b * n * 3),
            prep(qp.ang, b * n * 3), prep(act, steps * b * a))
-    names, shapes, offs, total = self._out_plan(b, av)
+    names, shapes, offs, total = self._out_plan(b, av, env, steps)
     flat = torch.empty(total, dtype=f32, device=dev)
     base = flat.data_ptr()
     io = self._io
     io.pos, io.rot, io.vel, io.ang, io.act = [t.data_ptr() for t in ins]
-    io.joint_angle = io.joint_velocity = None
+    self._clear_optional(io)
     out = {}
     for name, shape, off in zip(names, shapes, offs):
       cnt = 1
@@ -337,11 +382,11 @@ class System:
       rc = self._lib.bx_step(self._h, b, C.byref(io), stream)
     if rc != 0:
       raise RuntimeError('bx_step: ' + _lib.last_error())
-    return self._wrap(out, batched)
+    return self._wrap(out, batched, steps)
 
-  def _step_numpy(self, qp: QP, act, bufs: 'HostBuffers' = None, av: bool = False):
+  def _step_numpy(self, qp: QP, act, bufs: 'HostBuffers' = None, av: bool = False, env: bool = False):
     batched, b = self._shapes(np.shape(qp.pos))
-    n, k, a = self.num_bodies, self.num_contacts, self.act_size
+    n, a = self.num_bodies, self.act_size
 
     def prep(x, numel):
       # float32 C-contiguous arrays of the right size pass through untouched
@@ -355,22 +400,18 @@ class System:
            prep(qp.ang, b * n * 3), prep(act, b * a))
     io = self._io
     io.pos, io.rot, io.vel, io.ang, io.act = [t.__array_interface__['data'][0] for t in ins]
+    self._clear_optional(io)
     if bufs is not None:
       if bufs.batch != b:
         raise ValueError('HostBuffers are for batch %d, step has %d' % (bufs.batch, b))
-      out = dict(bufs.out)
-      for name, ptr in bufs.out_ptr.items():
-        setattr(io, name, ptr)
-      if not av:
-        io.joint_angle = io.joint_velocity = None
-        del out['joint_angle'], out['joint_velocity']
+      want = set(name for name, _ in self._specs(b, av, env))
+      out = {k: v for k, v in bufs.out.items() if k in want}
+      for name in out:
+        setattr(io, name, bufs.out_ptr[name])
     else:
       out = {}
-      io.joint_angle = io.joint_velocity = None
-      dims = {'n': n, 'k': k, 'j': len(self.desc.joints)}
-      for name, w, dim in (_OUT + _OUT_AV if av else _OUT):
-        m = dims[dim]
-        out[name] = np.empty((b, m, w) if w else (b, m), dtype=np.float32)
+      for name, shape in self._specs(b, av, env):
+        out[name] = np.empty(shape, dtype=np.float32)
         setattr(io, name, out[name].__array_interface__['data'][0] if out[name].size else None)
     rc = self._lib.bx_step_host(self._h, b, C.byref(io))
     if rc != 0:
@@ -378,9 +419,9 @@ class System:
     return self._wrap(out, batched)
 
 
-def load_system(name: str, device: int = 0) -> System:
+def load_system(name: str, device: int = 0, env=None) -> System:
   """A system from the descriptors shipped in brax_b200/systems/ (extracted
   from the reference's env configs by tools/gen_systems.py)."""
   import os
   path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'systems', name + '.json')
-  return System(SystemDesc.load(path), device)
+  return System(SystemDesc.load(path), device, env)

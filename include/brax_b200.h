@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BX_ABI_VERSION 4
+#define BX_ABI_VERSION 5
 
 /* dynamics_mode (base.py:179-201) */
 #define BX_MODE_PBD 0
@@ -130,6 +130,38 @@ typedef struct bx_pair {
   float pts[8][3];
 } bx_pair;
 
+/* Optional env epilogue ("next" row N1): everything the reference's Env.step computes
+ * AFTER sys.step, evaluated by the same launch from the state still in shared memory.
+ *   BX_ENV_ANT       brax/envs/ant.py:222-281       (Ant.step, _get_obs)
+ *   BX_ENV_HUMANOID  brax/envs/humanoid.py:246-340  (Humanoid.step, _get_obs, _center_of_mass)
+ * The fields are the envs' constructor arguments (ant.py:173-196, humanoid.py:200-221).
+ * Body 0 is the torso; the centre of mass runs over bodies [0, N-1) (humanoid.py:332-334).
+ * obs layout (floats per env, bx_system_obs_size):
+ *   ant:      [pos0.z | pos0.xyz] rot0 joint_angle[D]  vel0 ang0 joint_vel[D]
+ *             [clip(info.contact.vel)[N,3] clip(info.contact.ang)[N,3]]   (use_contact_forces)
+ *   humanoid: [pos0.z | pos0.xyz] rot0 joint_angle[D]  vel0 ang0 joint_vel[D]
+ *             com_inr[N-1,3,3] com_vel[N-1,3] com_ang[N-1,3] qfrc_actuator[sum of actuator_width]
+ *   D = sum of joint_free_dofs.  metrics (bx_system_num_metrics) in the order of the
+ *   reference's dict: ant.py:244-255 (10), humanoid.py:267-277 (9). */
+#define BX_ENV_NONE 0
+#define BX_ENV_ANT 1
+#define BX_ENV_HUMANOID 2
+typedef struct bx_env_desc {
+  uint32_t struct_size; /* = sizeof(bx_env_desc), checked */
+  int32_t kind;
+  float dt;             /* config.dt: velocity = (after - before) / dt (ant.py:226) */
+  float forward_reward_weight; /* humanoid.py:253; ant: 1 */
+  float ctrl_cost_weight;
+  float contact_cost_weight;   /* ant.py:237-238 */
+  float healthy_reward;
+  float healthy_z_min, healthy_z_max;
+  int32_t terminate_when_unhealthy;
+  int32_t use_contact_forces;        /* ant.py:271-279 */
+  int32_t exclude_current_positions; /* ..._from_observation */
+  int32_t joint_free_dofs[BX_MAX_JOINTS];   /* dofs of joint i that Joint.angle_vel returns (joints.py:216-225) */
+  int32_t actuator_width[BX_MAX_ACTUATORS]; /* act_index.shape[-1] of actuator i's group (humanoid.py:314-319) */
+} bx_env_desc;
+
 /* The static description of one system; everything System.__init__ derives
  * from the config (system.py:53-84).  Built on the host by
  * brax_b200.extract.describe(sys) from a constructed reference System. */
@@ -153,6 +185,7 @@ typedef struct bx_system_desc {
   const bx_actuator* actuators;
   const bx_force* forces;
   const bx_pair* pairs;
+  const bx_env_desc* env; /* optional env epilogue, NULL = none */
 } bx_system_desc;
 
 typedef struct bx_system bx_system; /* opaque; owns device copies of tables */
@@ -174,6 +207,10 @@ typedef struct bx_step_io {
    * step, envs/ant.py:259), before the free_dofs selection: [B,J,3], slots beyond a
    * joint's dof are 0.  J = num_joints in descriptor order. */
   float *joint_angle, *joint_velocity;
+  /* Optional env epilogue (systems created with desc.env; all NULL = skipped): the
+   * reference's Env.step outputs, State.obs [B,O], State.reward [B], State.done [B],
+   * State.metrics as [B,M].  With bx_rollout they are [T,B,...]: written every step. */
+  float *obs, *reward, *done, *metrics;
 } bx_step_io;
 
 /* Creates a system on CUDA device `device` (tables uploaded once).  Returns 0
@@ -186,6 +223,9 @@ void bx_system_destroy(bx_system* sys);
 int bx_system_num_contacts(const bx_system* sys);
 int bx_system_num_bodies(const bx_system* sys);
 int bx_system_act_size(const bx_system* sys);
+/* Env epilogue sizes: O floats of obs per env, M metrics (0 without desc.env). */
+int bx_system_obs_size(const bx_system* sys);
+int bx_system_num_metrics(const bx_system* sys);
 
 /* One System.step for B independent environments: ONE kernel launch on
  * `stream` (a cudaStream_t passed as void*; NULL = default stream).  No host

@@ -14,6 +14,7 @@ import pytest
 
 from brax_b200 import build as bx_build
 from brax_b200 import desc as bx_desc
+from brax_b200 import envs as bx_envs
 from brax_b200 import lib as bx_lib
 from tests import util
 
@@ -52,9 +53,9 @@ def test_struct_sizes_match_header():
 #include <stdio.h>
 #include "brax_b200.h"
 int main(void) {
-  printf("%zu %zu %zu %zu %zu %zu %zu %d\n", sizeof(bx_body), sizeof(bx_joint),
+  printf("%zu %zu %zu %zu %zu %zu %zu %zu %d\n", sizeof(bx_body), sizeof(bx_joint),
          sizeof(bx_actuator), sizeof(bx_force), sizeof(bx_pair),
-         sizeof(bx_system_desc), sizeof(bx_step_io), BX_ABI_VERSION);
+         sizeof(bx_system_desc), sizeof(bx_step_io), sizeof(bx_env_desc), BX_ABI_VERSION);
   return 0;
 }'''
   import tempfile
@@ -66,7 +67,7 @@ int main(void) {
     got = [int(x) for x in subprocess.check_output([exe]).split()]
   want = [C.sizeof(c) for c in (bx_desc.CBody, bx_desc.CJoint, bx_desc.CActuator,
                                 bx_desc.CForce, bx_desc.CPair,
-                                bx_desc.CSystemDesc, bx_desc.CStepIO)]
+                                bx_desc.CSystemDesc, bx_desc.CStepIO, bx_envs.CEnvDesc)]
   assert got[:-1] == want
   assert got[-1] == bx_desc.ABI_VERSION
 
@@ -104,6 +105,35 @@ def test_create_rejects_uncovered_features(lib):
   cdesc.joints[0].body_c = 99
   rc, msg = _create(lib, cdesc)
   assert rc != 0 and 'out of range' in msg
+
+
+def test_create_rejects_bad_env_desc(lib):
+  """The optional env epilogue (bx_env_desc) is validated before any device is touched."""
+  env = bx_envs.EnvDesc('ant', use_contact_forces=True)
+  cdesc, keep = util.load_desc('ant').to_c(env)
+  keep[-1].struct_size = 12
+  rc, msg = _create(lib, cdesc)
+  assert rc != 0 and 'bx_env_desc size mismatch' in msg
+  cdesc, keep = util.load_desc('ant').to_c(env)
+  keep[-1].kind = 9
+  rc, msg = _create(lib, cdesc)
+  assert rc != 0 and 'unsupported env kind' in msg
+  cdesc, keep = util.load_desc('ant').to_c(env)
+  keep[-1].joint_free_dofs[0] = 5
+  rc, msg = _create(lib, cdesc)
+  assert rc != 0 and 'joint_free_dofs' in msg
+
+
+def test_tile_bytes_with_env_epilogue(lib):
+  """The env rows grow the tile; ant and humanoid still fit two tiles per SM."""
+  from brax_b200 import system as bx_system
+  for name, env in (('ant', bx_envs.EnvDesc('ant', use_contact_forces=True)),
+                    ('humanoid', bx_envs.EnvDesc('humanoid'))):
+    d = util.load_desc(name)
+    plain, _ = bx_system.tile_bytes(d)
+    with_env, _ = bx_system.tile_bytes(d, env)
+    assert plain <= with_env
+    assert 2 * (with_env + 1024) <= 233472, (name, with_env)
 
 
 def test_no_cpu_fallback(lib):

@@ -1,0 +1,218 @@
+"""Parity of the fused env epilogue ("next" row N1) with the oracle (GPU box only).
+
+`brax_b200.envs.Ant / Humanoid .step` = ONE launch of the step kernel that also
+writes what the reference's `Env.step` computes after `sys.step`: obs, reward,
+done, metrics (brax/envs/ant.py:222-281, brax/envs/humanoid.py:246-340).  Checked
+against the float32 oracle chain (C physics oracle -> oracle/env_oracle.py, pinned
+to the reference by tests/test_env_oracle.py) under the same policy as the physics
+parity tests: |kernel - o32| <= 1e-6 + 1e-5 |o32| + GAP_MULT * gap(env) + velocity
+floor, gap = max |o32 - o64| of that env (measured float32 conditioning).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from tests import util
+from tests.test_env_oracle import VARIANTS, env_golden
+from tests.test_gpu_parity import GAP_MULT, OUTLIER_FRAC, VEL_ULPS, _harvest, _torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _env(variant, device=0):
+  from brax_b200 import envs
+  sysname, e = VARIANTS[variant]
+  kw = dict(use_contact_forces=e.use_contact_forces) if e.kind == 'ant' else {}
+  cls = envs.Ant if e.kind == 'ant' else envs.Humanoid
+  env = cls(legacy_spring=sysname.endswith('_spring'), device=device, **kw)
+  assert env.env == e  # the mirrored constructor defaults ARE the reference's
+  return sysname, env
+
+
+def _oracle_chain(sysname, envdesc, ins, act, dtype):
+  from oracle import env_oracle
+  from oracle.oracle import Oracle
+  desc = util.load_desc(sysname)
+  o = Oracle(desc, dtype)
+  out = o.step(*ins, act)
+  fa, fv = env_oracle.flat_angle_vel(desc, *o.angle_vel(out['rot'], out['ang']))
+  return env_oracle.env_epilogue(desc, envdesc, ins[0], out, act, fa, fv, dtype)
+
+
+def check_env(sysname, envdesc, ins, act, got, outlier_frac=OUTLIER_FRAC):
+  r32 = _oracle_chain(sysname, envdesc, ins, act, np.float32)
+  r64 = _oracle_chain(sysname, envdesc, ins, act, np.float64)
+  b = r32['obs'].shape[0]
+  allowed = int(outlier_frac * b) if b >= 200 else 0
+  floor = VEL_ULPS * 6e-8 / util.load_desc(sysname).dt_sub
+  bad = np.zeros(b, bool)
+  for k in ('obs', 'reward', 'metrics'):
+    g, r = got[k].reshape(b, -1), r32[k].reshape(b, -1)
+    assert np.isfinite(g).all(), k
+    gap = np.abs(r.astype(np.float64) - r64[k].reshape(b, -1)).max(axis=1, keepdims=True)
+    tol = 1e-6 + 1e-5 * np.abs(r) + GAP_MULT * gap + floor
+    over = np.abs(g - r) > tol
+    assert not (np.abs(g - r) > 100 * tol).any(), (k, float(np.abs(g - r).max()))
+    bad |= over.any(axis=1)
+  # done is a float compare of the torso height with the healthy range: exact unless
+  # the height sits within rounding of a bound
+  z = r64['obs'][:, 0]
+  near = np.minimum(np.abs(z - envdesc.healthy_z_range[0]), np.abs(z - envdesc.healthy_z_range[1])) < 1e-5
+  assert ((got['done'] == r32['done']) | near).all()
+  assert bad.sum() <= allowed, ('envs outside tolerance', int(bad.sum()), b)
+  return r32
+
+
+@pytest.mark.parametrize('variant', sorted(VARIANTS))
+def test_env_step_on_golden_inputs(variant):
+  """Host path (numpy in, numpy out) on the reference's own stored steps; also
+  close to the reference's float64 obs / reward (tests/golden/*_env.npz)."""
+  _torch()
+  from brax_b200.envs import State
+  from brax_b200.system import QP
+  sysname, env = _env(variant)
+  g, e = util.load_golden(sysname), env_golden(variant)
+  ins = [g[k].astype(np.float32) for k in util.QP_KEYS]
+  act = g['act'].astype(np.float32)
+  st = env.step(State(QP(*ins), None, None, None), act)
+  got = {'obs': st.obs, 'reward': st.reward, 'done': st.done,
+         'metrics': np.stack([st.metrics[k] for k in env.env.metric_names()], -1)}
+  assert st.obs.shape == e['obs'].shape and st.obs.shape[1] == env.observation_size
+  check_env(sysname, env.env, ins, act, got)
+  np.testing.assert_array_equal(st.done, e['done'])
+  np.testing.assert_allclose(st.reward, e['reward'], rtol=1e-4, atol=5e-3)
+  assert np.quantile(np.abs(st.obs - e['obs']), 0.99) < 1e-3
+  # the physics outputs of the env step are those of the plain step
+  qp2, _ = env.sys.step(QP(*ins), act)
+  np.testing.assert_array_equal(qp2.pos, st.qp.pos)
+
+
+@pytest.mark.parametrize('variant,b,steps', [('ant', 2048, 30), ('humanoid', 2048, 30),
+                                             ('ant_spring', 1024, 20), ('humanoid_spring', 1024, 20)])
+def test_env_step_on_harvested_states(variant, b, steps):
+  """Device path (torch tensors) on states with active contacts."""
+  torch = _torch()
+  from brax_b200.envs import State
+  sysname, env = _env(variant)
+  qp, rng = _harvest(env.sys, b, steps, 7)
+  act = rng.uniform(-1, 1, (b, env.action_size)).astype(np.float32)
+  st = env.step(State(qp, None, None, None), torch.from_numpy(act).cuda())
+  torch.cuda.synchronize()
+  got = {'obs': st.obs.cpu().numpy(), 'reward': st.reward.cpu().numpy(), 'done': st.done.cpu().numpy(),
+         'metrics': torch.stack([st.metrics[k] for k in env.env.metric_names()], -1).cpu().numpy()}
+  ins = [getattr(qp, k).cpu().numpy() for k in util.QP_KEYS]
+  r32 = check_env(sysname, env.env, ins, act, got)
+  if env.env.kind == 'ant':
+    assert (np.abs(r32['obs'][:, 27:]) > 0).mean() > 0.02  # contact forces are live
+
+
+def test_env_rollout_equals_repeated_steps():
+  """bx_rollout writes the env outputs of EVERY step: [T,B,...] bit-identical to T
+  env steps; ragged and unbatched shapes equal the same envs inside a big batch."""
+  torch = _torch()
+  from brax_b200.envs import State
+  from brax_b200.system import QP
+  _, env = _env('ant')
+  b, t_n = 300, 6   # ragged: 300 = 9 tiles + 12 envs; rows of step t start unaligned
+  qp, rng = _harvest(env.sys, b, 3, 3)
+  acts = torch.from_numpy(rng.uniform(-1, 1, (t_n, b, env.action_size)).astype(np.float32)).cuda()
+  st, obs, rew, done, met = State(qp, None, None, None), [], [], [], []
+  for t in range(t_n):
+    st = env.step(st, acts[t])
+    obs.append(st.obs); rew.append(st.reward); done.append(st.done)
+    met.append(torch.stack([st.metrics[k] for k in env.env.metric_names()], -1))
+  q2, i2, eo = env.sys.rollout(qp, acts, env=True)
+  torch.cuda.synchronize()
+  assert torch.equal(q2.pos, st.qp.pos) and torch.equal(q2.ang, st.qp.ang)
+  assert torch.equal(eo['obs'], torch.stack(obs)) and torch.equal(eo['reward'], torch.stack(rew))
+  assert torch.equal(eo['done'], torch.stack(done)) and torch.equal(eo['metrics'], torch.stack(met))
+  # unbatched call == env 5 of the batch
+  one = env.step(State(QP(*[getattr(qp, k)[5] for k in util.QP_KEYS]), None, None, None), acts[0, 5])
+  assert one.obs.shape == (env.observation_size,) and one.reward.shape == ()
+  assert torch.equal(one.obs, obs[0][5]) and torch.equal(one.reward, rew[0][5])
+
+
+def test_env_outputs_need_an_env_system():
+  _torch()
+  from brax_b200.system import load_system
+  s = load_system('ant')
+  with pytest.raises(ValueError):
+    s.step(s.default_qp(batch=4), np.zeros((4, 8), np.float32), env=True)
+
+
+@pytest.mark.parametrize('variant,b', [('ant', 1024), ('humanoid', 1024)])
+def test_1000_step_statistics(variant, b):
+  """North star: 'reward/energy statistics over 1000-step rollouts are compared
+  within a stated tolerance'.  1000 env steps of B envs on the GPU (10 launches of
+  100 steps through bx_rollout, env epilogue every step) against the float32 oracle
+  chain run over the same actions from the same start.  Single trajectories are
+  chaotic (contact-rich PBD amplifies ulps), so the POPULATION is compared: mean
+  reward per step, mean torso height, mean kinetic energy and the fraction of
+  unhealthy env-steps over all B x 1000 samples agree within 2 % of the oracle's
+  value (or 3 standard errors of the mean across envs, whichever is larger), and the
+  first 10 steps agree per env (rollout tolerance of test_rollout_10_steps)."""
+  torch = _torch()
+  from oracle import env_oracle
+  from oracle.oracle import Oracle
+  sysname, env = _env(variant)
+  desc = util.load_desc(sysname)
+  t_n, chunk = 1000, 100
+  rng = np.random.default_rng(2024)
+  st0 = env.reset(batch=b, rng=rng, velocity_noise=0.1)
+  acts = rng.uniform(-1, 1, (t_n, b, env.action_size)).astype(np.float32)
+  mass = np.asarray([x['mass'] for x in desc.bodies], np.float32)
+  live = np.asarray([x['pos_mask'][2] for x in desc.bodies], np.float32)  # skip the frozen floor
+
+  def energy(vel):
+    return 0.5 * np.sum(mass[None, :, None] * live[None, :, None] * np.square(vel), axis=(-1, -2))
+
+  # GPU: 10 launches x 100 steps
+  from brax_b200.system import QP
+  qp = QP(*[torch.from_numpy(np.ascontiguousarray(getattr(st0.qp, k))).cuda() for k in util.QP_KEYS])
+  g_rew, g_z, g_e, g_done, g_first = [], [], [], [], None
+  tz = 0 if env.env.exclude_current_positions else 2
+  for c0 in range(0, t_n, chunk):
+    a = torch.from_numpy(acts[c0:c0 + chunk]).cuda()
+    # energy needs the velocities of every step: step-by-step inside the chunk would be
+    # 1000 launches; instead take z / reward / done from the per-step env outputs and
+    # the energy at the chunk ends
+    qp, _, eo = env.sys.rollout(qp, a, env=True)
+    g_rew.append(eo['reward'].cpu().numpy()); g_z.append(eo['obs'][..., tz].cpu().numpy())
+    g_done.append(eo['done'].cpu().numpy()); g_e.append(energy(qp.vel.cpu().numpy()))
+    if g_first is None:
+      g_first = eo['obs'][9].cpu().numpy()
+  g_rew, g_z, g_done = np.concatenate(g_rew), np.concatenate(g_z), np.concatenate(g_done)
+  assert np.isfinite(g_rew).all() and np.isfinite(g_z).all()
+
+  # oracle: the same 1000 steps on the host cores
+  o = Oracle(desc, np.float32)
+  cur = {k: np.ascontiguousarray(getattr(st0.qp, k), np.float32) for k in util.QP_KEYS}
+  o_rew, o_z, o_done, o_e, o_first = np.empty((t_n, b), np.float32), np.empty((t_n, b), np.float32), \
+      np.empty((t_n, b), np.float32), [], None
+  for t in range(t_n):
+    out = o.step(cur['pos'], cur['rot'], cur['vel'], cur['ang'], acts[t], num_threads=os.cpu_count() or 1)
+    fa, fv = env_oracle.flat_angle_vel(desc, *o.angle_vel(out['rot'], out['ang']))
+    r = env_oracle.env_epilogue(desc, env.env, cur['pos'], out, acts[t], fa, fv, np.float32)
+    o_rew[t], o_z[t], o_done[t] = r['reward'], r['obs'][:, tz], r['done']
+    if t == 9:
+      o_first = r['obs']
+    if (t + 1) % chunk == 0:
+      o_e.append(energy(out['vel']))
+    cur = {k: out[k] for k in util.QP_KEYS}
+
+  # the first 10 steps agree per env
+  err = np.abs(g_first - o_first).max(axis=1)
+  assert np.quantile(err, 0.99) <= 5e-2 and np.median(err) <= 2e-3, (float(np.quantile(err, 0.99)), float(np.median(err)))
+
+  def close(name, g, r):
+    # per-env means -> population mean and its standard error
+    gm, rm = g.mean(axis=0), r.mean(axis=0)
+    se = np.sqrt(gm.var() / b + rm.var() / b)
+    tol = max(0.02 * abs(rm.mean()), 3.0 * se)
+    assert abs(gm.mean() - rm.mean()) <= tol, (variant, name, float(gm.mean()), float(rm.mean()), float(tol))
+
+  close('reward', g_rew, o_rew)
+  close('torso_z', g_z, o_z)
+  close('unhealthy', g_done, o_done)
+  close('kinetic_energy', np.stack(g_e), np.stack(o_e))
