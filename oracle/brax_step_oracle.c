@@ -1485,6 +1485,9 @@ int FN(bxo_step)(const osys* s, int64_t num_envs, const oio* io, int num_threads
   return 0;
 }
 
+/* math.rotate (math.py:25-40) for the reference's known-answer test math_test.py:25-37. */
+void FN(bxo_rotate)(const R* v, const R* q, R* out) { rotate(v, q, out); }
+
 /* contact_fn of pair `pair_index` evaluated on one env's QP (unbatched
  * [N,3|4] arrays); out: n_contacts rows of pos[3] vel[3] normal[3] pen.
  * For the reference's collider known-answer tests (colliders_test.py:54-135). */

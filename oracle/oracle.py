@@ -247,6 +247,16 @@ class Oracle:
                   C.c_void_p(ba.ctypes.data), C.c_void_p(bb.ctypes.data))
     return ba, bb
 
+  def rotate(self, vec, quat):
+    """math.rotate (math.py:25-40)."""
+    dt = self.dtype
+    v = np.ascontiguousarray(np.asarray(vec, dtype=dt))
+    q = np.ascontiguousarray(np.asarray(quat, dtype=dt))
+    out = np.empty(3, dt)
+    getattr(self._lib, 'bxo_rotate' + ('_f32' if dt == np.float32 else '_f64'))(
+        C.c_void_p(v.ctypes.data), C.c_void_p(q.ctypes.data), C.c_void_p(out.ctypes.data))
+    return out
+
   def pair_contacts(self, pair_index, pos, rot, vel=None, ang=None):
     """Contact rows [C,10] = pos3 vel3 normal3 pen of one collidable pair."""
     d, dt = self.desc, self.dtype
