@@ -234,8 +234,9 @@ def test_cuda_path_passes_reference_test(case):
   o32 = run_oracle(desc, g, np.float32)
   report = {k: float(np.abs(got[k] - o32[k]).max()) for k in util.QP_KEYS}
   print(case, 'max |cuda - o32|', report)
-  for k in ('pos', 'rot'):
-    np.testing.assert_allclose(got[k], o32[k], rtol=0, atol=2e-3 * max(1.0, np.abs(o32[k]).max()), err_msg=k)
+  # measured: <= 4.4e-4 (pos) / 5.2e-5 (rot) on every non-chaotic case; the pendulum's bob rings
+  for k, tol in (('pos', 2e-3), ('rot', 5e-3 if case.startswith(CHAOTIC_PREFIXES) else 1e-3)):
+    np.testing.assert_allclose(got[k], o32[k], rtol=0, atol=tol * max(1.0, np.abs(o32[k]).max()), err_msg=k)
   if not case.startswith(CHAOTIC_PREFIXES):
     for k in ('vel', 'ang'):
       np.testing.assert_allclose(got[k], o32[k], rtol=2e-2, atol=2e-2, err_msg=k)
