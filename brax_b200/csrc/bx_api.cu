@@ -743,7 +743,9 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   const int64_t tiles = (num_envs + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA;
   if (tiles > 0x7fffffffLL) return fail("too many environments for one launch");
   // systems with an env epilogue run the builds that contain it; all others the plain ones
-  cudaError_t le = launch_variant(s->h.mode, s->jc, s->cc | (s->h.env_kind ? BX_CC_ENV : 0),
+  // BX_PDL=0 switches programmatic dependent launch off (A/B, debugging)
+  static const int pdl = (getenv("BX_PDL") && atoi(getenv("BX_PDL")) == 0) ? 0 : BX_CC_PDL;
+  cudaError_t le = launch_variant(s->h.mode, s->jc, s->cc | (s->h.env_kind ? BX_CC_ENV : 0) | pdl,
                                   static_cast<unsigned>(tiles), 32 * s->warps,
                                   s->smem_bytes, stream, p);
   g_launches.fetch_add(1);

@@ -33,6 +33,7 @@ static bx_kernel_fn pick(int jc, int cc) {
 }
 
 static bx_kernel_fn pick_any(int mode, int jc, int cc) {
+  cc &= ~BX_CC_PDL;
   if (cc & BX_CC_ENV) {
     cc &= ~BX_CC_ENV;
     return mode == BX_MODE_PBD ? pick<BX_MODE_PBD, BXF_ENV>(jc, cc) : pick<BX_MODE_LEGACY_SPRING, BXF_ENV>(jc, cc);
@@ -43,8 +44,21 @@ static bx_kernel_fn pick_any(int mode, int jc, int cc) {
 cudaError_t BX_CAT(bx_launch_, BX_TU_MAXT)(int mode, int jc, int cc, unsigned grid, int threads,
                                            size_t smem, cudaStream_t stream,
                                            const BxKernelParams& p) {
-  pick_any(mode, jc, cc)<<<grid, threads, smem, stream>>>(p);
-  return cudaGetLastError();
+  if (!(cc & BX_CC_PDL)) {
+    pick_any(mode, jc, cc)<<<grid, threads, smem, stream>>>(p);
+    return cudaGetLastError();
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(threads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, pick_any(mode, jc, cc), p);
 }
 
 cudaError_t BX_CAT(bx_set_smem_, BX_TU_MAXT)(int bytes) {

@@ -35,6 +35,10 @@ enum {
   BXF_ALL = 2047
 };
 #define BX_CC_ENV 8  // or-ed into the contact class passed to bx_launch_*: env-epilogue build
+// or-ed in as well: launch with programmatic stream serialization (programmatic dependent
+// launch): the CTAs of this launch may become resident, load the static tables and park at
+// griddepcontrol.wait while the previous kernel of the stream drains
+#define BX_CC_PDL 16
 // Kernel variants are instantiated per (dynamics mode, joint class, contact
 // class, launch bound).  Classes are the feature sets of the reference's envs:
 // all-revolute (ant, fetch), all-spherical (humanoid, grasp: joints.py:418-474

@@ -148,7 +148,7 @@ static __device__ __noinline__ void io_segment_scalar(float* smf, const int32_t*
     int e, r;
     seg_locate(sg, idx, &e, &r);
     const int m = sg.map >= 0 ? map[r] : -1;
-    if (LOAD) { if (m >= 0) smf[m + 4 * e] = __ldg(base + idx); }
+    if (LOAD) { if (m >= 0) smf[m + 4 * e] = base[idx]; }  // plain load: with PDL the producer may still run at CTA start
     else base[idx] = m >= 0 ? smf[m + 4 * e] : sg.fill;
   }
 }
@@ -190,6 +190,11 @@ BXS void bulk_commit_wait_read() {
   asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 BXS void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// Programmatic dependent launch (no-ops for a normally serialized launch): the next kernel of
+// the stream may start launching once every CTA of this grid has passed pdl_trigger; a CTA of
+// that kernel may touch what this grid wrote only after pdl_wait (= this grid complete, flushed).
+BXS void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+BXS void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 BXS bool span_bulk_ok(const BxSeg& sg, const float* g, int64_t env0) {
   return (reinterpret_cast<uintptr_t>(g + env0 * sg.nper) & 15) == 0;
@@ -1359,6 +1364,7 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
   const int nenv = static_cast<int>((p.num_envs - env0) < BX_ENVS_PER_CTA ? (p.num_envs - env0) : BX_ENVS_PER_CTA);
 
   PT_INIT();
+  pdl_trigger();
   if (p.stagger_ns) {
     // All tiles of a small batch are resident at once and would move in lock step:
     // every tile reading over PCIe, then every tile writing.  Spreading the starts
@@ -1392,8 +1398,9 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
     if (in_bulk)
       for (int s = 0; s < BX_SEG_IN; s++) bytes += 4 * BX_ENVS_PER_CTA * h.seg_in[s].nper;
     mbar_expect_tx(mbar, bytes);
-    bulk_g2s(tf, p.tab_f, h.n_fquads * 16, mbar);
+    bulk_g2s(tf, p.tab_f, h.n_fquads * 16, mbar);  // static tables: not produced by a kernel
     bulk_g2s(ti, p.tab_i, h.n_ints * 4, mbar);
+    pdl_wait();  // the inputs may be the previous launch's outputs
     if (in_bulk) {
       int off = 0;
       for (int s = 0; s < BX_SEG_IN; s++) {
@@ -1403,6 +1410,7 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
       }
     }
   }
+  if (threadIdx.x != 0) pdl_wait();  // every thread that will read or write global memory
   if (!full) {
     // partial tile: give the idle env slots a benign state (identity rotations)
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);

@@ -480,3 +480,54 @@ def test_host_path_pinned_buffers_and_chunking():
     assert d2h <= 4 * b * (31 * n + 7 * kk)
     if s.desc.dynamics_mode == 'pbd':  # info.joint (2 x 3N) + info.actuator.vel (3N) stay on the host
       assert d2h == 4 * b * (31 * n + 7 * kk - 9 * n)
+
+
+def test_dependent_launch_chain_is_ordered():
+  """Launches use programmatic stream serialization (the next launch's CTAs may become
+  resident and load tables while this one drains); the chain step N -> N+1 must still see
+  complete outputs: 40 eager steps at the BASELINE batch == one 40-step bx_rollout, bitwise."""
+  torch = _torch()
+  s = _system('ant')
+  b, t_n = 8192, 40
+  qp, rng = _harvest(s, b, 2, 17)
+  acts = torch.from_numpy(rng.uniform(-1, 1, (t_n, b, s.act_size)).astype(np.float32)).cuda()
+  q1 = qp
+  for t in range(t_n):
+    q1, i1 = s.step(q1, acts[t])
+  q2, i2 = s.rollout(qp, acts)
+  torch.cuda.synchronize()
+  a, c = _flat(q1, i1), _flat(q2, i2)
+  for k in a:
+    np.testing.assert_array_equal(a[k], c[k], err_msg=k)
+
+
+def test_cuda_graph_capture():
+  """bx_step neither allocates nor synchronises: a chain of steps captures into a CUDA
+  graph and replays to the eager result (SURVEY.md 8(b) 'CUDA-graph capturable')."""
+  torch = _torch()
+  from brax_b200.system import QP
+  s = _system('humanoid')
+  b, t_n = 1024, 5
+  qp, rng = _harvest(s, b, 2, 23)
+  acts = torch.from_numpy(rng.uniform(-1, 1, (t_n, b, s.act_size)).astype(np.float32)).cuda()
+  q1 = qp
+  for t in range(t_n):
+    q1, i1 = s.step(q1, acts[t])
+  torch.cuda.synchronize()
+  static_in = QP(*[getattr(qp, k).clone() for k in util.QP_KEYS])
+  side = torch.cuda.Stream()
+  side.wait_stream(torch.cuda.current_stream())
+  with torch.cuda.stream(side):   # warm-up on the capture stream
+    s.step(static_in, acts[0])
+  torch.cuda.current_stream().wait_stream(side)
+  g = torch.cuda.CUDAGraph()
+  with torch.cuda.graph(g):
+    q2 = static_in
+    for t in range(t_n):
+      q2, i2 = s.step(q2, acts[t])
+  for _ in range(2):   # replays are idempotent: static inputs are never written
+    g.replay()
+  torch.cuda.synchronize()
+  a, c = _flat(q1, i1), _flat(q2, i2)
+  for k in a:
+    np.testing.assert_array_equal(a[k], c[k], err_msg=k)
