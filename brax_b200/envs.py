@@ -26,12 +26,15 @@ import numpy as np
 from brax_b200 import system as _system
 from brax_b200.desc import MAX_ACTUATORS, MAX_JOINTS, SystemDesc
 
-ENV_KIND = {'ant': 1, 'humanoid': 2}
+ENV_KIND = {'ant': 1, 'humanoid': 2, 'fetch': 3, 'grasp': 4}
 
 ANT_METRICS = ('reward_forward', 'reward_survive', 'reward_ctrl', 'reward_contact', 'x_position',
                'y_position', 'distance_from_origin', 'x_velocity', 'y_velocity', 'forward_reward')
 HUMANOID_METRICS = ('forward_reward', 'reward_linvel', 'reward_quadctrl', 'reward_alive', 'x_position',
                     'y_position', 'distance_from_origin', 'x_velocity', 'y_velocity')
+FETCH_METRICS = ('hits', 'weightedHits', 'movingToTarget', 'torsoIsUp', 'torsoHeight')
+GRASP_METRICS = ('hits', 'touchingObject', 'movingToObject', 'movingObjectToTarget', 'closeToObject')
+MAX_ACT = 64
 
 
 class CEnvDesc(C.Structure):
@@ -43,7 +46,10 @@ class CEnvDesc(C.Structure):
               ('terminate_when_unhealthy', C.c_int32), ('use_contact_forces', C.c_int32),
               ('exclude_current_positions', C.c_int32),
               ('joint_free_dofs', C.c_int32 * MAX_JOINTS),
-              ('actuator_width', C.c_int32 * MAX_ACTUATORS)]
+              ('actuator_width', C.c_int32 * MAX_ACTUATORS),
+              ('ref_body', C.c_int32), ('target_body', C.c_int32), ('object_body', C.c_int32),
+              ('hand_body', C.c_int32), ('touch_bodies', C.c_int32 * 4), ('target_radius', C.c_float),
+              ('act_min', C.c_float * MAX_ACT), ('act_range', C.c_float * MAX_ACT)]
 
 
 @dataclasses.dataclass
@@ -58,11 +64,26 @@ class EnvDesc:
   healthy_z_range: Tuple[float, float] = (0.2, 1.0)
   use_contact_forces: bool = False
   exclude_current_positions: bool = True
+  # fetch / grasp (fetch.py:28-34, grasp.py:32-54): body indices, target radius and, for
+  # grasp, the affine map of the [-1,1] action (`_min_act`, `_range_act`)
+  ref_body: int = 0         # torso (fetch) / palm (grasp): origin of the egocentric frame
+  target_body: int = 0
+  object_body: int = 0
+  hand_body: int = 0
+  touch_bodies: Tuple[int, ...] = (0, 0, 0, 0)
+  target_radius: float = 0.0
+  act_min: Tuple[float, ...] = ()
+  act_range: Tuple[float, ...] = ()
 
   def metric_names(self):
-    return ANT_METRICS if self.kind == 'ant' else HUMANOID_METRICS
+    return {'ant': ANT_METRICS, 'humanoid': HUMANOID_METRICS, 'fetch': FETCH_METRICS,
+            'grasp': GRASP_METRICS}[self.kind]
 
   def obs_size(self, desc: SystemDesc) -> int:
+    if self.kind == 'fetch':
+      return 10 + 7 * desc.num_bodies
+    if self.kind == 'grasp':
+      return 20 + 7 * desc.num_bodies
     nd = sum(int(j.get('free_dofs', j['dof'])) for j in desc.joints)
     n = (1 if self.exclude_current_positions else 3) + 4 + nd + 6 + nd
     if self.kind == 'ant':
@@ -86,7 +107,44 @@ class EnvDesc:
       c.joint_free_dofs[i] = int(j.get('free_dofs', j['dof']))
     for i, a in enumerate(desc.actuators):
       c.actuator_width[i] = len(a['act_index'])
+    c.ref_body, c.target_body = self.ref_body, self.target_body
+    c.object_body, c.hand_body = self.object_body, self.hand_body
+    c.touch_bodies[:] = list(self.touch_bodies)
+    c.target_radius = self.target_radius
+    if self.kind == 'grasp':
+      if len(self.act_min) != desc.act_size or len(self.act_range) != desc.act_size:
+        raise ValueError('grasp: act_min / act_range must have act_size entries')
+      for i in range(desc.act_size):
+        c.act_min[i], c.act_range[i] = self.act_min[i], self.act_range[i]
     return c
+
+
+def fetch_desc(desc: SystemDesc) -> EnvDesc:
+  """EnvDesc of `Fetch` (fetch.py:28-34): torso / target indices by body name, radius 2."""
+  names = desc.body_names
+  return EnvDesc('fetch', ref_body=names.index('Torso'), target_body=names.index('Target'), target_radius=2.0)
+
+
+def grasp_desc(desc: SystemDesc) -> EnvDesc:
+  """EnvDesc of `Grasp` (grasp.py:32-54).  The action map: per joint dof the angle limits in
+  DEGREES as they stand in `sys.config.joints` after `joints.get` sphericalized them (three per
+  joint, zeros appended, joints.py:431-433), then the palm target box."""
+  names = desc.body_names
+  if desc.dynamics_mode != 'pbd':
+    # legacy_spring keeps 1/2/3-dof joints: the env lists the limits in CONFIG joint order, the
+    # descriptor holds the joints grouped by dof (joints.py:465-474) -- not recoverable here
+    raise NotImplementedError('grasp env epilogue: pbd only')
+  lo, rng = [], []
+  for j in desc.joints:
+    lim = np.asarray(j['limit'], np.float64).reshape(-1, 2) * 180.0 / np.pi
+    lo += [float(x) for x in lim[:, 0]]
+    rng += [float(x) for x in lim[:, 1] - lim[:, 0]]
+  lo += [-10.0, -10.0, 3.5]
+  rng += [20.0, 20.0, 10.0]
+  return EnvDesc('grasp', ref_body=names.index('HandPalm'), target_body=names.index('Target'),
+                 object_body=names.index('Object'), hand_body=names.index('HandThumbProximal'),
+                 touch_bodies=(3, 9, 12, 15),   # grasp.py:116, as written there
+                 target_radius=1.1, act_min=tuple(lo), act_range=tuple(rng))
 
 
 @dataclasses.dataclass

@@ -4,6 +4,11 @@ AFTER `sys.step` inside `Env.step` -- obs, reward, done, metrics.
   ant       brax/envs/ant.py:222-281       (Ant.step :222-256, _get_obs :257-281)
   humanoid  brax/envs/humanoid.py:246-340  (Humanoid.step :246-279, _get_obs :281-330,
                                             _center_of_mass :332-334)
+  fetch     brax/envs/fetch.py:54-122      (Fetch.step :54-96, _get_obs :98-122)
+  grasp     brax/envs/grasp.py:73-186      (Grasp.step :73-138 incl. the action map and palm
+                                            move BEFORE sys.step = env_prologue, _get_obs :144-186)
+The random target teleport on a hit (fetch.py:88-93, grasp.py:131-136) draws from the JAX
+PRNG and stays with the caller; `hits` is among the metrics.
 
 Pinned to the reference: tests/test_oracle_golden.py feeds it the physics outputs
 stored in tests/golden/<sys>_steps.npz / <sys>_angle_vel.npz and compares with
@@ -31,6 +36,50 @@ def flat_angle_vel(desc, angle, vel):
   ia = np.asarray([c[0] for c in cols], int)
   da = np.asarray([c[1] for c in cols], int)
   return angle[:, ia, da], vel[:, ia, da]
+
+
+def _rotate(v, q):
+  """math.rotate (math.py:25-40), batched: v [...,3], q [...,4] (w,x,y,z)."""
+  s, u = q[..., :1], q[..., 1:]
+  r = 2 * (np.sum(u * v, axis=-1, keepdims=True) * u) + (s * s - np.sum(u * u, axis=-1, keepdims=True)) * v
+  return r + 2 * s * np.cross(u, v)
+
+
+def _inv_rotate(v, q):
+  """math.inv_rotate (math.py:43-53): rotate by quat_inv(q) = q * [1,-1,-1,-1] (math.py:190-199)."""
+  return _rotate(v, q * np.asarray([1, -1, -1, -1], q.dtype))
+
+
+def _norm(x):
+  return np.sqrt(np.sum(np.square(x), axis=-1))
+
+
+def env_prologue(desc, env, pos, act, dtype=np.float32):
+  """What `Env.step` does BEFORE `sys.step`: (pos, act) -> (pos', act').  Identity except
+  for grasp (grasp.py:75-85): the [-1,1] action is mapped onto the joint ranges (+ the palm
+  target box) and the frozen palm is moved towards its target, at most 0.15 * 2 per step."""
+  dt = np.dtype(dtype).type
+  pos, act = np.array(pos, dtype), np.asarray(act, dtype)
+  if env.kind != 'grasp':
+    return pos, act
+  act = np.asarray(env.act_min, dtype) + np.asarray(env.act_range, dtype) * ((act + dt(1)) / dt(2.))
+  target = act[:, -3:]
+  palm = pos[:, env.ref_body]
+  nrm = _norm(target - palm)
+  scale = np.where(nrm > dt(2.0), dt(2.) / np.where(nrm > 0, nrm, dt(1)), dt(1.0)).astype(dtype)
+  pos[:, env.ref_body] = palm + scale[:, None] * (target - palm) * dt(.15)
+  return pos, act
+
+
+def _egocentric(env, pos, rot, vel, cvel, dt):
+  """Shared by fetch / grasp _get_obs: positions and velocities of all bodies in the frame
+  of the reference body, contact flags (fetch.py:103-117, grasp.py:147-150,176-178)."""
+  b = pos.shape[0]
+  q = rot[:, env.ref_body][:, None, :]
+  pos_local = _inv_rotate(pos - pos[:, env.ref_body][:, None, :], np.broadcast_to(q, rot.shape))
+  vel_local = _inv_rotate(vel, np.broadcast_to(q, rot.shape))
+  contacts = np.where(np.sum(np.square(cvel), axis=-1) > dt(0.00001), dt(1), dt(0)).astype(pos.dtype)
+  return pos_local, vel_local, contacts
 
 
 def _healthy(env, z, dt):
@@ -104,6 +153,64 @@ def env_epilogue(desc, env, pos_before, out, act, flat_angle, flat_vel, dtype=np
                                         com_ang[:, :-1].reshape(b, -1)] + qfrc, axis=-1)
     metrics = np.stack([forward, forward, -ctrl, hr, com_a[:, 0], com_a[:, 1],
                         np.sqrt(np.sum(np.square(com_a), axis=-1)), velocity[:, 0], velocity[:, 1]], axis=-1)
+  elif env.kind == 'fetch':
+    cvel = np.asarray(out['contact_vel'], dtype)
+    ti, gi = env.ref_body, env.target_body
+    pos_local, vel_local, contacts = _egocentric(env, pos, rot, vel, cvel, dt)
+    ex = np.broadcast_to(np.asarray([1., 0., 0.], dtype), (b, 3))
+    ez = np.broadcast_to(np.asarray([0., 0., 1.], dtype), (b, 3))
+    torso_fwd, torso_up = _rotate(ex, rot[:, ti]), _rotate(ez, rot[:, ti])
+    tl = pos_local[:, gi]
+    tl_mag = _norm(tl)[:, None]
+    obs = np.concatenate([torso_fwd, torso_up, tl_mag, tl / (dt(1e-6) + tl_mag), pos_local.reshape(b, -1),
+                          vel_local.reshape(b, -1), contacts], axis=-1)
+    torso_delta = pos[:, ti] - pos0[:, ti]                          # fetch.py:59-63
+    target_rel = pos[:, gi] - pos[:, ti]
+    target_dist = _norm(target_rel)
+    target_dir = target_rel / (dt(1e-6) + target_dist)[:, None]
+    moving = dt(.1) * np.sum(torso_delta * target_dir, axis=-1)
+    is_up = dt(.1) * cdt * np.sum(torso_up * ez, axis=-1)
+    height = dt(.1) * cdt * pos[:, 0, 2]
+    facing = np.sum(target_dir * torso_fwd, axis=-1)
+    hit = np.where(target_dist < dt(env.target_radius), dt(1), dt(0)).astype(dtype)
+    weighted = hit * facing
+    reward = height + moving + is_up + weighted                     # fetch.py:81
+    done = np.zeros(b, dtype)
+    metrics = np.stack([hit, weighted, moving, is_up, height], axis=-1)
+  elif env.kind == 'grasp':
+    cvel = np.asarray(out['contact_vel'], dtype)
+    pi, oi, gi, hi = env.ref_body, env.object_body, env.target_body, env.hand_body
+    pos_local, vel_local, contacts = _egocentric(env, pos, rot, vel, cvel, dt)
+
+    def mag_dir(x):
+      m = _norm(x)[:, None]
+      return m, x / (dt(1e-6) + m)
+
+    ol_mag, ol_dir = mag_dir(pos_local[:, oi])
+    tl_mag, tl_dir = mag_dir(pos_local[:, gi])
+    hand_to_obj = pos[:, oi] - pos[:, pi]
+    _, h2o_dir = mag_dir(hand_to_obj)
+    hand_vel = vel[:, hi]
+    heading = np.sum(h2o_dir * hand_vel, axis=-1, keepdims=True)
+    o2t_mag, o2t_dir = mag_dir(pos[:, gi] - pos[:, oi])
+    obj_heading = np.sum(o2t_dir * vel[:, oi], axis=-1, keepdims=True)
+    obs = np.concatenate([ol_mag, ol_dir, tl_mag, tl_dir, pos_local.reshape(b, -1), vel_local.reshape(b, -1),
+                          hand_to_obj, hand_vel, heading, o2t_mag, o2t_dir, obj_heading, contacts], axis=-1)
+    object_rel = pos[:, oi] - pos[:, pi]                             # grasp.py:91-100
+    object_dist = _norm(object_rel)
+    planar = _norm(object_rel * np.asarray([1., 1., 0.], dtype))
+    object_dir = object_rel / (dt(1e-6) + object_dist)[:, None]
+    moving_to_object = dt(.1) * cdt * np.sum(hand_vel * object_dir, axis=-1)
+    close = dt(.1) * cdt * dt(1.) / (dt(1.) + planar)
+    target_rel = pos[:, gi] - pos[:, oi]                             # grasp.py:103-109
+    target_dist = _norm(target_rel)
+    target_dir = target_rel / (dt(1e-6) + target_dist)[:, None]
+    moving_to_target = dt(1.5) * cdt * np.sum(vel[:, oi] * target_dir, axis=-1)
+    touching = dt(0.2) * cdt * np.sum(contacts[:, list(env.touch_bodies)], axis=-1)   # grasp.py:112-116
+    hit = np.where(target_dist < dt(env.target_radius), dt(1), dt(0)).astype(dtype)
+    reward = moving_to_object + close + touching + dt(5.) * hit + moving_to_target      # grasp.py:121
+    done = np.zeros(b, dtype)
+    metrics = np.stack([hit, touching, moving_to_object, moving_to_target, close], axis=-1)
   else:
     raise ValueError('no env epilogue for kind %r' % env.kind)
   return {'obs': obs.astype(dtype), 'reward': reward.astype(dtype), 'done': done.astype(dtype),

@@ -40,6 +40,11 @@ VARIANTS = {
     'ant_spring': ('ant_spring', 'ant', 'Ant', dict(use_contact_forces=True, legacy_spring=True)),
     'humanoid': ('humanoid', 'humanoid', 'Humanoid', dict()),
     'humanoid_spring': ('humanoid_spring', 'humanoid', 'Humanoid', dict(legacy_spring=True)),
+    # egocentric envs; their random target teleport on a hit (JAX PRNG) is the caller's.  Grasp
+    # maps the action and moves the palm BEFORE sys.step, so its physics is not that of the
+    # stored system golden: the step's output QP is stored here as well.
+    'fetch': ('fetch', 'fetch', 'Fetch', dict()),
+    'grasp': ('grasp', 'grasp', 'Grasp', dict()),
 }
 
 
@@ -65,12 +70,16 @@ def main(names):
     g = np.load(os.path.join(out_dir, sysname + '_steps.npz'))
     steps = g['pos'].shape[0]
     obs, rew, done, met, names_m = [], [], [], [], None
+    qpo = {k: [] for k in ('pos', 'rot', 'vel', 'ang')}
     for t in range(steps):
       qp = brax.QP(pos=g['pos'][t], rot=g['rot'][t], vel=g['vel'][t], ang=g['ang'][t])
-      st = benv.State(qp=qp, obs=np.zeros(1), reward=np.zeros(()), done=np.zeros(()), metrics={})
+      st = benv.State(qp=qp, obs=np.zeros(1), reward=np.zeros(()), done=np.zeros(()), metrics={},
+                      info={'rng': np.array([1, 2], dtype='uint32')})
       st2 = e.step(st, g['act'][t])
-      # same physics as the stored system golden
-      np.testing.assert_allclose(np.asarray(st2.qp.pos, np.float64), g['pos_o'][t], rtol=0, atol=1e-12)
+      if modname != 'grasp':  # same physics as the stored system golden
+        np.testing.assert_allclose(np.asarray(st2.qp.pos, np.float64)[:12], g['pos_o'][t][:12], rtol=0, atol=1e-12)
+      for k in qpo:
+        qpo[k].append(np.asarray(getattr(st2.qp, k), np.float64))
       obs.append(np.asarray(st2.obs, np.float64))
       rew.append(float(st2.reward))
       done.append(float(st2.done))
@@ -80,7 +89,10 @@ def main(names):
     np.savez_compressed(os.path.join(out_dir, name + '_env.npz'), obs=np.stack(obs),
                         reward=np.asarray(rew), done=np.asarray(done), metrics=np.asarray(met),
                         metric_names=np.asarray(names_m), system=np.asarray(sysname),
-                        dt=np.asarray(float(e.sys.config.dt)))
+                        dt=np.asarray(float(e.sys.config.dt)),
+                        **{'qp_' + k: np.stack(v) for k, v in qpo.items()},
+                        **({'act_min': np.asarray(e._min_act, np.float64), 'act_range': np.asarray(e._range_act, np.float64)}
+                           if modname == 'grasp' else {}))
     print('%-16s %3d steps, obs %d, metrics %s' % (name, steps, obs[0].shape[0], names_m))
 
 

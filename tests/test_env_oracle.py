@@ -25,6 +25,8 @@ VARIANTS = {
     'humanoid': ('humanoid', envs.EnvDesc('humanoid', 1.25, 0.1, 0.0, 5.0, True, (0.8, 2.1), False, True)),
     'humanoid_spring': ('humanoid_spring',
                         envs.EnvDesc('humanoid', 1.25, 0.1, 0.0, 5.0, True, (0.8, 2.1), False, True)),
+    'fetch': ('fetch', envs.fetch_desc(util.load_desc('fetch'))),
+    'grasp': ('grasp', envs.grasp_desc(util.load_desc('grasp'))),
 }
 
 
@@ -32,7 +34,7 @@ def env_golden(variant):
   return np.load(os.path.join(util.GOLDEN, variant + '_env.npz'))
 
 
-@pytest.mark.parametrize('variant', sorted(VARIANTS))
+@pytest.mark.parametrize('variant', [v for v in sorted(VARIANTS) if not v.startswith('grasp')])
 def test_env_oracle_f64_matches_reference(variant):
   sysname, env = VARIANTS[variant]
   g, e = util.load_golden(sysname), env_golden(variant)
@@ -55,14 +57,22 @@ def test_env_oracle_chain_matches_reference(variant):
   sysname, env = VARIANTS[variant]
   g, e = util.load_golden(sysname), env_golden(variant)
   desc = util.load_desc(sysname)
+  if env.kind == 'grasp':  # the affine action map derived from the descriptor == the env's own
+    np.testing.assert_allclose(env.act_min, e['act_min'], rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(env.act_range, e['act_range'], rtol=1e-12, atol=1e-12)
   for dtype, tol in ((np.float64, 1e-9), (np.float32, None)):
     o = Oracle(desc, dtype)
-    out = o.step(g['pos'], g['rot'], g['vel'], g['ang'], g['act'])
+    pos_in, act_in = env_oracle.env_prologue(desc, env, g['pos'], g['act'], dtype)   # grasp.py:75-85
+    out = o.step(pos_in, g['rot'], g['vel'], g['ang'], act_in)
     fa, fv = env_oracle.flat_angle_vel(desc, *o.angle_vel(out['rot'], out['ang']))
     r = env_oracle.env_epilogue(desc, env, g['pos'], out, g['act'], fa, fv, dtype)
     if tol is not None:
       for k in ('obs', 'reward', 'done', 'metrics'):
         np.testing.assert_allclose(r[k], e[k], rtol=0, atol=tol, err_msg=k)
+      if 'qp_pos' in e:   # the step's output QP (a hit teleports the target afterwards: caller's)
+        hit = e['metrics'][:, 0] > 0
+        for k in util.QP_KEYS:
+          np.testing.assert_allclose(out[k][~hit], e['qp_' + k][~hit], rtol=0, atol=1e-9, err_msg=k)
     else:
       np.testing.assert_array_equal(r['done'], e['done'])
       # velocities are position differences over dt (ant.py:226): ulp(pos)/dt of float32
@@ -75,3 +85,5 @@ def test_obs_sizes():
   assert VARIANTS['ant_nocfrc'][1].obs_size(util.load_desc('ant')) == 27
   assert VARIANTS['humanoid'][1].obs_size(util.load_desc('humanoid')) == 240
   assert VARIANTS['humanoid_spring'][1].obs_size(util.load_desc('humanoid_spring')) == 227
+  assert VARIANTS['fetch'][1].obs_size(util.load_desc('fetch')) == 101
+  assert VARIANTS['grasp'][1].obs_size(util.load_desc('grasp')) == 132
