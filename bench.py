@@ -383,7 +383,7 @@ def run_gpu(args, desc):
   # envs/ant.py:222-281, envs/humanoid.py:246-340) as ONE launch; same timing method.
   ms_env, env_obs = 0.0, 0
   env_name = args.env[:-len('_spring')] if args.env.endswith('_spring') else args.env
-  if env_name in ('ant', 'humanoid'):
+  if env_name in ('ant', 'humanoid', 'fetch', 'grasp') and args.env != 'grasp_spring':
     from brax_b200 import envs as bx_envs
     from brax_b200.envs import State
     kw = dict(use_contact_forces=True) if env_name == 'ant' else {}   # the fork's registration
@@ -391,6 +391,11 @@ def run_gpu(args, desc):
     if args.threads or args.contact_section:
       env.sys.configure(args.threads, args.contact_section)
     env_obs = env.observation_size
+    if env_name in ('fetch', 'grasp'):
+      # targets away from the robot, as after the reference's reset (no teleports in the timed loop)
+      far = torch.tensor([8.0, 3.0, 1.0], device=dev)
+      for q in qps:
+        q.pos[:, env.env.target_body] = q.pos[:, env.env.object_body if env_name == 'grasp' else env.env.ref_body] + far
     sts = [State(q, None, None, None) for q in qps]
     for j in range(nsets):
       sts[j] = env.step(sts[j], acts[j % total])

@@ -116,8 +116,19 @@ static int validate(const bx_system_desc* d) {
   if (d->env) {
     const bx_env_desc& e = *d->env;
     if (e.struct_size != sizeof(bx_env_desc)) return fail("bx_env_desc size mismatch (ABI skew)");
-    if (e.kind != BX_ENV_ANT && e.kind != BX_ENV_HUMANOID)
-      return fail("unsupported env kind (fused epilogues exist for ant and humanoid)");
+    if (e.kind < BX_ENV_ANT || e.kind > BX_ENV_GRASP)
+      return fail("unsupported env kind (fused epilogues exist for ant, humanoid, fetch and grasp)");
+    if (e.kind == BX_ENV_FETCH || e.kind == BX_ENV_GRASP) {
+      const int idx[8] = {e.ref_body, e.target_body, e.kind == BX_ENV_GRASP ? e.object_body : 0,
+                          e.kind == BX_ENV_GRASP ? e.hand_body : 0,
+                          e.kind == BX_ENV_GRASP ? e.touch_bodies[0] : 0, e.kind == BX_ENV_GRASP ? e.touch_bodies[1] : 0,
+                          e.kind == BX_ENV_GRASP ? e.touch_bodies[2] : 0, e.kind == BX_ENV_GRASP ? e.touch_bodies[3] : 0};
+      for (int i = 0; i < 8; i++)
+        if (idx[i] < 0 || idx[i] >= d->num_bodies) return fail("env body index out of range");
+      if (e.kind == BX_ENV_GRASP && d->dynamics_mode != BX_MODE_PBD) return fail("grasp env epilogue: pbd only");
+      if (e.kind == BX_ENV_GRASP && (d->act_size > BX_MAX_ACT || d->act_size < 3))
+        return fail("grasp env epilogue: act_size out of range");
+    }
     if (!(e.dt > 0.f)) return fail("env dt must be positive");
     if (e.kind == BX_ENV_HUMANOID && d->num_bodies < 2) return fail("humanoid epilogue needs >= 2 bodies");
     for (int i = 0; i < d->num_joints; i++)
@@ -228,6 +239,19 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
       for (int q = 0; q < 3; q++) quad(0.f, 0.f, 0.f, 0.f);
     }
   }
+  if (d->env && d->env->kind == BX_ENV_GRASP) {  // action map: min quads, then range quads
+    h.fo_envact = nquads();
+    const int nq = (d->act_size + 3) / 4;
+    for (int pass = 0; pass < 2; pass++)
+      for (int q = 0; q < nq; q++) {
+        float v[4];
+        for (int x = 0; x < 4; x++) {
+          const int i = 4 * q + x;
+          v[x] = i < d->act_size ? (pass ? d->env->act_range[i] : d->env->act_min[i]) : 0.f;
+        }
+        quad(v[0], v[1], v[2], v[3]);
+      }
+  }
   h.n_fquads = nquads();
 
   // ---- per-body slot lists inside region JS (see bx_tables.h "Slots") ---------
@@ -309,8 +333,13 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     const int tail = ct_rows + (spring ? 0 : 2 * ncb) + 2 * ncb + nab + (spring ? 2 * nb : 0);
     js = std::max(js, (in_floats + row_floats - 1) / row_floats - tail);
     js = std::max(js, 2 * nj);  // angle_vel epilogue: {angles}, {velocities} per joint
-    if (d->env)  // env epilogue rows follow the angle_vel rows (bx_tables.h EQ_*)
-      js = std::max(js, 2 * nj + EQ_X + (d->env->kind == BX_ENV_ANT ? 2 * nb : 5 * (nb - 1) + na));
+    if (d->env) {  // env epilogue rows follow the angle_vel rows (bx_tables.h EQ_*)
+      const int k = d->env->kind;
+      int extra = k == BX_ENV_ANT ? 2 * nb : (k == BX_ENV_HUMANOID ? 5 * (nb - 1) + na : 0);
+      if (k == BX_ENV_FETCH || k == BX_ENV_GRASP)  // flags + vectors (+ local rows where no dead body rows exist)
+        extra = (nb + 3) / 4 + EV_COUNT + (spring ? 2 * nb : 0);
+      js = std::max(js, 2 * nj + EQ_X + extra);
+    }
   }
 
   // ---- state quad rows
@@ -325,7 +354,8 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
   h.q_ia = r; r += nab;
   h.q_ij = r; r += spring ? 2 * nb : 0;
   h.n_zero = r - h.q_ic;
-  h.q_ep = r; r += d->env ? 1 : 0;  // survives the substeps: reference point before the step
+  // survives the substeps: reference point before the step (grasp has none)
+  h.q_ep = r; r += (d->env && d->env->kind != BX_ENV_GRASP) ? 1 : 0;
   h.q_env = h.q_js + 2 * nj;
   h.n_quads = r;
 
@@ -486,14 +516,53 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     auto joints_part = [&](int which) {
       for (int i = 0; i < nj; i++) row3(h.q_js + 2 * i + which, 0, e.joint_free_dofs[i]);
     };
-    if (e.exclude_current_positions) row3(E + EQ_TORSO_POS, 2, 1); else row3(E + EQ_TORSO_POS);
-    row3(E + EQ_TORSO_ROT, 0, 4);
-    joints_part(0);
-    row3(bqn * 0 + vel_off);
-    row3(bqn * 0 + ang_off);
-    joints_part(1);
+    const bool ego = e.kind == BX_ENV_FETCH || e.kind == BX_ENV_GRASP;
     int nmetrics = 10;
-    if (e.kind == BX_ENV_ANT) {
+    if (ego) {
+      // egocentric envs (fetch.py:98-122, grasp.py:144-186).  Rows: contact flags 4 per quad,
+      // EV_* vectors, and per body {pos_local, vel_local}: in pbd these overwrite the body's
+      // previous-pose rows (dead after the last substep: pos1/rot1 when the result sits in
+      // pos0/rot0, which it does after the even number of half-steps of a full step), else JS rows
+      nmetrics = 5;
+      h.q_ecf = E + EQ_X;
+      h.q_ev = h.q_ecf + (nb + 3) / 4;
+      h.q_eloc = spring ? h.q_ev + EV_COUNT : -1;
+      auto loc = [&](int b, int which) { return spring ? h.q_eloc + 2 * b + which : bqn * b + 2 + which; };
+      auto flags = [&]() { for (int b = 0; b < nb; b++) m.push_back((h.q_ecf + (b >> 2)) * RF + (b & 3)); };
+      auto locals = [&]() {
+        for (int which = 0; which < 2; which++)
+          for (int b = 0; b < nb; b++) row3(loc(b, which));
+      };
+      if (e.kind == BX_ENV_FETCH) {
+        row3(h.q_ev + EV_0); row3(h.q_ev + EV_1);
+        row3(h.q_ev + EV_2, 3, 1); row3(h.q_ev + EV_2);
+        locals();
+        flags();
+      } else {
+        row3(h.q_ev + EV_0, 3, 1); row3(h.q_ev + EV_0);
+        row3(h.q_ev + EV_1, 3, 1); row3(h.q_ev + EV_1);
+        locals();
+        row3(h.q_ev + EV_2);                       // hand_to_obj
+        row3(bqn * e.hand_body + vel_off);         // hand_vel
+        row3(h.q_ev + EV_2, 3, 1);                 // heading_to_obj
+        row3(h.q_ev + EV_3, 3, 1); row3(h.q_ev + EV_3);
+        row3(h.q_ev + EV_4, 0, 1);
+        flags();
+      }
+      h.env_ref = e.ref_body; h.env_target = e.target_body;
+      h.env_object = e.object_body; h.env_hand = e.hand_body;
+      for (int i = 0; i < 4; i++) h.env_touch[i] = e.touch_bodies[i];
+      h.env_radius = e.target_radius;
+    } else {
+      if (e.exclude_current_positions) row3(E + EQ_TORSO_POS, 2, 1); else row3(E + EQ_TORSO_POS);
+      row3(E + EQ_TORSO_ROT, 0, 4);
+      joints_part(0);
+      row3(bqn * 0 + vel_off);
+      row3(bqn * 0 + ang_off);
+      joints_part(1);
+    }
+    if (ego) {
+    } else if (e.kind == BX_ENV_ANT) {
       if (e.use_contact_forces)
         for (int which = 0; which < 2; which++)
           for (int b = 0; b < nb; b++) row3(E + EQ_X + 2 * b + which);
@@ -512,7 +581,8 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     for (int i = 0; i < nmetrics; i++) mm.push_back((E + EQ_S0) * RF + ((2 + i) >> 2) * RF + ((2 + i) & 3));
     h.seg_out[BX_SEG_ENV + 3] = seg(nmetrics, 0.f, mm);
     h.env_kind = e.kind;
-    h.env_flags = (e.use_contact_forces ? 1 : 0) | (e.terminate_when_unhealthy ? 2 : 0);
+    h.env_flags = (e.use_contact_forces ? 1 : 0) | (e.terminate_when_unhealthy ? 2 : 0) |
+                  (ego ? 0 : 4);  // bit 2: the obs holds joint angles (phase_angle_vel runs)
     h.env_dt = e.dt;
     h.env_wf = e.forward_reward_weight;
     h.env_wc = e.ctrl_cost_weight;

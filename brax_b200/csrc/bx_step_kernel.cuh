@@ -1252,11 +1252,131 @@ BXS V3 env_com(const Ctx& c, const BxHeader& h, int po) {  // humanoid.py:332-33
 }
 // reference point before the step: torso position (ant.py:226) / centre of mass
 // (humanoid.py:250); one warp, at the start of every step
+BXS float* act_ptr(const Ctx& c, const BxHeader& h, int i) {
+  return reinterpret_cast<float*>(&QROW(c, h.q_act + (i >> 2))) + (i & 3);
+}
+// grasp.py:75: action = min_act + range_act * ((action + 1) / 2), in place
+BXS float env_map_act(const Ctx& c, const BxHeader& h, int i) {
+  const float* tab = reinterpret_cast<const float*>(c.tf + h.fo_envact);
+  float* a = act_ptr(c, h, i);
+  const float v = tab[i] + tab[4 * ((h.act_size + 3) >> 2) + i] * ((*a + 1.f) * 0.5f);
+  *a = v;
+  return v;
+}
+// Start of every step, ALL warps (ends before the barrier that precedes the first phase).
+// ant / humanoid / fetch: the last warp stores the reference point before the step.  grasp
+// (grasp.py:75-85): every warp maps its share of the action vector; the last warp maps the
+// three palm-target slots itself and moves the (frozen) palm towards the target.
 template <int MODE>
 static __device__ __noinline__ void phase_env_before(const Ctx c, const BxHeader& h) {
   typedef Lay<MODE> L;
   const int po = MODE == BX_MODE_PBD ? 2 * c.cur : 0;
-  stv(c, h.q_ep, h.env_kind == BX_ENV_ANT ? ldv(c, L::BQ * 0 + po) : env_com<MODE>(c, h, po));
+  const bool last = c.warp == c.nwarp - 1;
+  if (h.env_kind == BX_ENV_GRASP) {
+    const int na = h.act_size - 3;
+    for (int i = c.warp; i < na; i += c.nwarp) env_map_act(c, h, i);
+    if (last) {
+      const V3 target = v3(env_map_act(c, h, na), env_map_act(c, h, na + 1), env_map_act(c, h, na + 2));
+      const int row = L::BQ * h.env_ref + po;
+      const V3 palm = ldv(c, row);
+      const V3 d = target - palm;
+      const float nrm = bx_sqrt(d.x * d.x + d.y * d.y + d.z * d.z);
+      const float scale = nrm > 2.f ? bx_div(2.f, nrm) : 1.f;   // the hand does not move too fast
+      stv(c, row, palm + (scale * d) * 0.15f);
+    }
+    return;
+  }
+  if (!last) return;
+  V3 ref;
+  if (h.env_kind == BX_ENV_HUMANOID) ref = env_com<MODE>(c, h, po);
+  else ref = ldv(c, L::BQ * (h.env_kind == BX_ENV_FETCH ? h.env_ref : 0) + po);
+  stv(c, h.q_ep, ref);
+}
+// math.inv_rotate (math.py:43-53): rotate by quat_inv(q) = (w, -x, -y, -z) (math.py:190-199)
+BXS V3 inv_rotate(V3 v, Q4 q) { return rotate(v, q4(q.w, -q.x, -q.y, -q.z)); }
+BXS float norm3(V3 a) { return bx_sqrt(a.x * a.x + a.y * a.y + a.z * a.z); }
+// contacts = where(sum(square(info.contact.vel)) > 1e-5, 1, 0) (fetch.py:116-117, grasp.py:176-178)
+BXS float env_contact_flag(const Ctx& c, const BxHeader& h, int b) {
+  const int cs = c.ti[h.io_body + b * BI_STRIDE + BI_CSLOT];
+  if (cs < 0) return 0.f;
+  const V3 v = ldv(c, h.q_ic + 2 * cs);
+  return (v.x * v.x + v.y * v.y + v.z * v.z) > 0.00001f ? 1.f : 0.f;
+}
+// Fetch.step / Grasp.step after sys.step (fetch.py:55-122, grasp.py:88-186)
+template <int MODE>
+static __device__ __noinline__ void phase_env_ego(const Ctx c, const BxHeader& h) {
+  typedef Lay<MODE> L;
+  const int po = MODE == BX_MODE_PBD ? 2 * c.cur : 0;
+  const V3 pref = ldv(c, L::BQ * h.env_ref + po);
+  const Q4 qref = ldq(c, L::BQ * h.env_ref + po + 1);
+  for (int b = c.warp; b < h.nb; b += c.nwarp) {
+    // pbd: the body's previous-pose rows are dead after the last substep
+    const int r0 = MODE == BX_MODE_PBD ? L::BQ * b + 2 * (c.cur ^ 1) : h.q_eloc + 2 * b;
+    const V3 pl = inv_rotate(ldv(c, L::BQ * b + po) - pref, qref);
+    const V3 vl = inv_rotate(ldv(c, L::BQ * b + L::VEL), qref);
+    stv(c, r0, pl);
+    stv(c, r0 + 1, vl);
+    reinterpret_cast<float*>(&QROW(c, h.q_ecf + (b >> 2)))[b & 3] = env_contact_flag(c, h, b);
+  }
+  if (c.warp != c.nwarp - 1) return;
+  const int E = h.q_env, V = h.q_ev;
+  const V3 ptgt = ldv(c, L::BQ * h.env_target + po);
+  if (h.env_kind == BX_ENV_FETCH) {
+    const V3 ex = v3(1.f, 0.f, 0.f), ez = v3(0.f, 0.f, 1.f);
+    const V3 fwd = rotate(ex, qref), up = rotate(ez, qref);
+    const V3 tl = inv_rotate(ptgt - pref, qref);
+    const float tlm = norm3(tl);
+    stv(c, V + EV_0, fwd);
+    stv(c, V + EV_1, up);
+    stv4(c, V + EV_2, vdiv(tl, 1e-6f + tlm), tlm);
+    const V3 delta = pref - ldv(c, h.q_ep);                 // fetch.py:59
+    const V3 rel = ptgt - pref;
+    const float dist = norm3(rel);
+    const V3 dir = vdiv(rel, 1e-6f + dist);
+    const float moving = 0.1f * dot(delta, dir);
+    const float is_up = (0.1f * h.env_dt) * dot(up, ez);
+    const float height = (0.1f * h.env_dt) * ldv(c, L::BQ * 0 + po).z;   // qp.pos[0, 2] (fetch.py:70)
+    const float facing = dot(dir, fwd);
+    const float hit = dist < h.env_radius ? 1.f : 0.f;
+    const float weighted = hit * facing;
+    const float reward = height + moving + is_up + weighted;  // fetch.py:81
+    QROW(c, E + EQ_S0) = make_float4(reward, 0.f, hit, weighted);
+    QROW(c, E + EQ_S1) = make_float4(moving, is_up, height, 0.f);
+  } else {
+    const V3 pobj = ldv(c, L::BQ * h.env_object + po);
+    const V3 vobj = ldv(c, L::BQ * h.env_object + L::VEL);
+    const V3 hand_vel = ldv(c, L::BQ * h.env_hand + L::VEL);
+    const V3 ol = inv_rotate(pobj - pref, qref);
+    const float olm = norm3(ol);
+    const V3 tl = inv_rotate(ptgt - pref, qref);
+    const float tlm = norm3(tl);
+    const V3 h2o = pobj - pref;                               // hand_to_obj = object_rel
+    const float h2om = norm3(h2o);
+    const V3 h2od = vdiv(h2o, 1e-6f + h2om);
+    const V3 o2t = ptgt - pobj;                               // obj_to_target = target_rel
+    const float o2tm = norm3(o2t);
+    const V3 o2td = vdiv(o2t, 1e-6f + o2tm);
+    const float heading = dot(h2od, hand_vel);
+    const float obj_heading = dot(o2td, vobj);
+    stv4(c, V + EV_0, vdiv(ol, 1e-6f + olm), olm);
+    stv4(c, V + EV_1, vdiv(tl, 1e-6f + tlm), tlm);
+    stv4(c, V + EV_2, h2o, heading);
+    stv4(c, V + EV_3, o2td, o2tm);
+    QROW(c, V + EV_4) = make_float4(obj_heading, 0.f, 0.f, 0.f);
+    const float planar = bx_sqrt(h2o.x * h2o.x + h2o.y * h2o.y + 0.f);   // norm(object_rel * [1,1,0])
+    const float k = 0.1f * h.env_dt;
+    const float moving_to_object = k * heading;               // dot(hand_vel, object_dir), grasp.py:99
+    const float close = bx_div(k * 1.f, 1.f + planar);
+    const float moving_to_target = (1.5f * h.env_dt) * obj_heading;
+    float touch = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; i++) touch += env_contact_flag(c, h, h.env_touch[i]);
+    const float touching = (0.2f * h.env_dt) * touch;
+    const float hit = o2tm < h.env_radius ? 1.f : 0.f;
+    const float reward = moving_to_object + close + touching + 5.f * hit + moving_to_target;  // grasp.py:121
+    QROW(c, E + EQ_S0) = make_float4(reward, 0.f, hit, touching);
+    QROW(c, E + EQ_S1) = make_float4(moving_to_object, moving_to_target, close, 0.f);
+  }
 }
 template <int MODE>
 static __device__ __noinline__ void phase_env(const Ctx c, const BxHeader& h) {
@@ -1489,7 +1609,7 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
       if (h.iters == 0)  // contact_penetration = -1 (system.py:84)
         for (int i = threadIdx.x; i < (h.q_pre - h.q_ct) * QS; i += blockDim.x)
           sq[h.q_ct * QS + i] = i < h.nk * QS ? make_float4(0.f, 0.f, 0.f, -1.f) : z;
-      if (env_on && c.warp == c.nwarp - 1) phase_env_before<MODE>(c, h);
+      if (env_on) phase_env_before<MODE>(c, h);
     }
     __syncthreads();
     PT(1);
@@ -1550,8 +1670,12 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
       // Env.step's epilogue of THIS step (every step of a rollout): obs / reward / done /
       // metrics [T,B,...]
       __syncthreads();
-      phase_angle_vel<MODE>(c, h);  // writes rows only the stores read: no barrier before phase_env
-      phase_env<MODE>(c, h);
+      if (h.env_flags & 4) {
+        phase_angle_vel<MODE>(c, h);  // writes rows only the stores read: no barrier before phase_env
+        phase_env<MODE>(c, h);
+      } else {
+        phase_env_ego<MODE>(c, h);
+      }
       __syncthreads();
       auto env_ptr = [&](int s) -> float* {
         return p.out[s] == nullptr ? nullptr

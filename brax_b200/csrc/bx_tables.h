@@ -152,6 +152,14 @@ struct BxHeader {
   float env_wf, env_wc, env_wcc, env_hr;  // forward / ctrl / contact weights, healthy_reward
   float env_zmin, env_zmax;
   float env_msum;      // humanoid: sum of the masses of bodies [0, nb-1) (float32 sum on the host)
+  // fetch / grasp
+  int32_t env_ref, env_target, env_object, env_hand, env_touch[4];
+  int32_t q_eloc;      // egocentric rows of body b: q_eloc_base(b) + {0: pos_local, 1: vel_local}; pbd: the
+                       // dead previous-pose rows of the body block (-1), else first row of 2 per body in JS
+  int32_t q_ecf;       // contact flags, 4 bodies per quad
+  int32_t q_ev;        // env vectors (EV_*)
+  int32_t fo_envact;   // grasp action map in the float table: ceil(A/4) quads of min, then of range
+  float env_radius;
 };
 
 // env rows relative to q_env
@@ -165,10 +173,21 @@ enum {
                      // humanoid: per body b < nb-1 {com_inr rows 0..2}, {com_vel}, {com_ang} (5 rows),
                      // then one row per actuator {act[idx] * strength}
 };
+// env vectors relative to q_ev (fetch / grasp)
+enum {
+  EV_0 = 0,  // fetch: torso_fwd                     grasp: {object_local_dir, |object_local|}
+  EV_1 = 1,  // fetch: torso_up                      grasp: {target_local_dir, |target_local|}
+  EV_2 = 2,  // fetch: {target_local_dir, |..|}      grasp: {hand_to_obj, heading_to_obj}
+  EV_3 = 3,  //                                      grasp: {obj_to_target_dir, |obj_to_target|}
+  EV_4 = 4,  //                                      grasp: {obj_heading_to_target, 0, 0, 0}
+  EV_COUNT = 5,
+};
 #ifndef BX_ENV_NONE  // also in include/brax_b200.h
 #define BX_ENV_NONE 0
 #define BX_ENV_ANT 1
 #define BX_ENV_HUMANOID 2
+#define BX_ENV_FETCH 3
+#define BX_ENV_GRASP 4
 #endif
 
 #define BX_QSTRIDE 33  // quads per row: 32 env slots + 1 pad (conflict-free transposing I/O)

@@ -164,7 +164,12 @@ class State:
 class Env:
   """Common part of the mirrored envs: a `System` with the env epilogue switched on."""
 
-  def __init__(self, system_name: str, env: EnvDesc, device: int = 0):
+  def __init__(self, system_name: str, env, device: int = 0):
+    """env: an EnvDesc, or a function SystemDesc -> EnvDesc (fetch_desc, grasp_desc)."""
+    import os
+    if callable(env):
+      path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'systems', system_name + '.json')
+      env = env(SystemDesc.load(path))
     self.env = env
     self.sys = _system.load_system(system_name, device, env)
     self.observation_size = env.obs_size(self.sys.desc)
@@ -230,7 +235,72 @@ class Humanoid(Env):
         tuple(healthy_z_range), False, exclude_current_positions_from_observation), device)
 
 
-_ENVS = {'ant': Ant, 'humanoid': Humanoid}
+class _TargetEnv(Env):
+  """Common part of fetch / grasp: after the fused step, targets that were hit are teleported
+  to a new random place (fetch.py:88-93 + :124-134, grasp.py:131-136 + :188-198).  The
+  reference draws from the JAX PRNG carried in `state.info['rng']`; here a numpy / torch
+  generator (seeded at construction) is used -- same distribution, not the same stream."""
+  target_distance = 0.0
+  target_height = None   # None: z = 1 (fetch); else z = target_height * U (grasp)
+
+  def __init__(self, system_name, env, device=0, seed=0):
+    super().__init__(system_name, env, device)
+    self._np_rng = np.random.default_rng(seed)
+    self._seed = seed
+    self._torch_gen = None
+
+  def _uniform(self, like, n):
+    if _system._is_torch(like):
+      import torch
+      if self._torch_gen is None or self._torch_gen.device != like.device:
+        self._torch_gen = torch.Generator(device=like.device)
+        self._torch_gen.manual_seed(self._seed)
+      return torch.rand((3,) + tuple(n), generator=self._torch_gen, device=like.device, dtype=like.dtype)
+    return self._np_rng.uniform(size=(3,) + tuple(n)).astype(np.float32)
+
+  def step(self, state: State, action) -> State:
+    st = super().step(state, action)
+    hit = st.metrics['hits']
+    pos = st.qp.pos
+    u = self._uniform(pos, hit.shape)
+    xp = __import__('torch') if _system._is_torch(pos) else np
+    dist = self.env.target_radius + self.target_distance * u[0]
+    ang = (2.0 * np.pi) * u[1]
+    z = xp.ones_like(dist) if self.target_height is None else self.target_height * u[2]
+    target = xp.stack([dist * xp.cos(ang), dist * xp.sin(ang), z], -1)
+    ti = self.env.target_body
+    cur = pos[..., ti, :]
+    new = xp.where((hit > 0)[..., None], target, cur)
+    if _system._is_torch(pos):
+      pos = pos.clone()
+      pos[..., ti, :] = new
+    else:
+      pos = np.array(pos)
+      pos[..., ti, :] = new
+    qp = _system.QP(pos, st.qp.rot, st.qp.vel, st.qp.ang)
+    return st.replace(qp=qp)
+
+
+class Fetch(_TargetEnv):
+  """brax/envs/fetch.py:25-134."""
+  target_distance = 15.0
+
+  def __init__(self, legacy_spring=False, device: int = 0, seed: int = 0):
+    super().__init__('fetch_spring' if legacy_spring else 'fetch', fetch_desc, device, seed)
+
+
+class Grasp(_TargetEnv):
+  """brax/envs/grasp.py:25-198 (pbd; action_size = actuator dofs + 3 palm-target slots :140-142)."""
+  target_distance = 10.0
+  target_height = 8.0
+
+  def __init__(self, legacy_spring=False, device: int = 0, seed: int = 0):
+    if legacy_spring:
+      raise NotImplementedError('grasp env epilogue: pbd only (see grasp_desc)')
+    super().__init__('grasp', grasp_desc, device, seed)
+
+
+_ENVS = {'ant': Ant, 'humanoid': Humanoid, 'fetch': Fetch, 'grasp': Grasp}
 
 
 def create(env_name: str, **kwargs) -> Env:

@@ -146,6 +146,18 @@ typedef struct bx_pair {
 #define BX_ENV_NONE 0
 #define BX_ENV_ANT 1
 #define BX_ENV_HUMANOID 2
+/*   BX_ENV_FETCH     brax/envs/fetch.py:54-122  (Fetch.step, _get_obs)
+ *   BX_ENV_GRASP     brax/envs/grasp.py:73-186  (Grasp.step incl. the action map and palm move
+ *                    BEFORE sys.step :75-85, _get_obs); pbd only
+ * obs: fetch  torso_fwd torso_up |target_local| target_local_dir pos_local[N,3] vel_local[N,3]
+ *             contacts[N]                                                     (10 + 7N floats)
+ *      grasp  |object_local| dir |target_local| dir pos_local[N,3] vel_local[N,3] hand_to_obj
+ *             hand_vel heading |obj_to_target| dir obj_heading contacts[N]    (20 + 7N floats)
+ * metrics: fetch.py:83-88 (5), grasp.py:123-128 (5).  The random target teleport after a hit
+ * (fetch.py:88-93, grasp.py:131-136, JAX PRNG) stays with the caller: `hits` is metric 0. */
+#define BX_ENV_FETCH 3
+#define BX_ENV_GRASP 4
+#define BX_MAX_ACT 64 /* act_size of systems with an action map (grasp) */
 typedef struct bx_env_desc {
   uint32_t struct_size; /* = sizeof(bx_env_desc), checked */
   int32_t kind;
@@ -160,6 +172,14 @@ typedef struct bx_env_desc {
   int32_t exclude_current_positions; /* ..._from_observation */
   int32_t joint_free_dofs[BX_MAX_JOINTS];   /* dofs of joint i that Joint.angle_vel returns (joints.py:216-225) */
   int32_t actuator_width[BX_MAX_ACTUATORS]; /* act_index.shape[-1] of actuator i's group (humanoid.py:314-319) */
+  /* fetch / grasp (fetch.py:28-34, grasp.py:32-54) */
+  int32_t ref_body;    /* Torso / HandPalm: origin of the egocentric frame */
+  int32_t target_body; /* Target */
+  int32_t object_body; /* grasp: Object */
+  int32_t hand_body;   /* grasp: HandThumbProximal */
+  int32_t touch_bodies[4]; /* grasp.py:116 */
+  float target_radius;
+  float act_min[BX_MAX_ACT], act_range[BX_MAX_ACT]; /* grasp.py:43-54: act = min + range * (act + 1) / 2 */
 } bx_env_desc;
 
 /* The static description of one system; everything System.__init__ derives

@@ -24,7 +24,7 @@ def _env(variant, device=0):
   from brax_b200 import envs
   sysname, e = VARIANTS[variant]
   kw = dict(use_contact_forces=e.use_contact_forces) if e.kind == 'ant' else {}
-  cls = envs.Ant if e.kind == 'ant' else envs.Humanoid
+  cls = {'ant': envs.Ant, 'humanoid': envs.Humanoid, 'fetch': envs.Fetch, 'grasp': envs.Grasp}[e.kind]
   env = cls(legacy_spring=sysname.endswith('_spring'), device=device, **kw)
   assert env.env == e  # the mirrored constructor defaults ARE the reference's
   return sysname, env
@@ -35,9 +35,12 @@ def _oracle_chain(sysname, envdesc, ins, act, dtype):
   from oracle.oracle import Oracle
   desc = util.load_desc(sysname)
   o = Oracle(desc, dtype)
-  out = o.step(*ins, act)
+  pos_in, act_in = env_oracle.env_prologue(desc, envdesc, ins[0], act, dtype)   # grasp.py:75-85
+  out = o.step(pos_in, ins[1], ins[2], ins[3], act_in)
   fa, fv = env_oracle.flat_angle_vel(desc, *o.angle_vel(out['rot'], out['ang']))
-  return env_oracle.env_epilogue(desc, envdesc, ins[0], out, act, fa, fv, dtype)
+  r = env_oracle.env_epilogue(desc, envdesc, ins[0], out, act, fa, fv, dtype)
+  r['qp'] = {k: out[k] for k in util.QP_KEYS}
+  return r
 
 
 def check_env(sysname, envdesc, ins, act, got, outlier_frac=OUTLIER_FRAC):
@@ -55,11 +58,14 @@ def check_env(sysname, envdesc, ins, act, got, outlier_frac=OUTLIER_FRAC):
     over = np.abs(g - r) > tol
     assert not (np.abs(g - r) > 100 * tol).any(), (k, float(np.abs(g - r).max()))
     bad |= over.any(axis=1)
-  # done is a float compare of the torso height with the healthy range: exact unless
-  # the height sits within rounding of a bound
-  z = r64['obs'][:, 0]
-  near = np.minimum(np.abs(z - envdesc.healthy_z_range[0]), np.abs(z - envdesc.healthy_z_range[1])) < 1e-5
-  assert ((got['done'] == r32['done']) | near).all()
+  if envdesc.kind in ('ant', 'humanoid'):
+    # done is a float compare of the torso height with the healthy range: exact unless
+    # the height sits within rounding of a bound
+    z = r64['obs'][:, 0]
+    near = np.minimum(np.abs(z - envdesc.healthy_z_range[0]), np.abs(z - envdesc.healthy_z_range[1])) < 1e-5
+    assert ((got['done'] == r32['done']) | near).all()
+  else:
+    assert (got['done'] == 0).all()
   assert bad.sum() <= allowed, ('envs outside tolerance', int(bad.sum()), b)
   return r32
 
@@ -79,17 +85,30 @@ def test_env_step_on_golden_inputs(variant):
   got = {'obs': st.obs, 'reward': st.reward, 'done': st.done,
          'metrics': np.stack([st.metrics[k] for k in env.env.metric_names()], -1)}
   assert st.obs.shape == e['obs'].shape and st.obs.shape[1] == env.observation_size
-  check_env(sysname, env.env, ins, act, got)
+  r32 = check_env(sysname, env.env, ins, act, got)
   np.testing.assert_array_equal(st.done, e['done'])
   np.testing.assert_allclose(st.reward, e['reward'], rtol=1e-4, atol=5e-3)
   assert np.quantile(np.abs(st.obs - e['obs']), 0.99) < 1e-3
-  # the physics outputs of the env step are those of the plain step
-  qp2, _ = env.sys.step(QP(*ins), act)
-  np.testing.assert_array_equal(qp2.pos, st.qp.pos)
+  if env.env.kind == 'grasp':
+    # the action map and the palm move happen inside the launch: the step's QP is that of the
+    # oracle chain (prologue -> physics) and of the reference's Grasp.step
+    keep = np.arange(st.qp.pos.shape[1]) != env.env.target_body   # a hit target is teleported by the wrapper
+    np.testing.assert_allclose(st.qp.pos[:, keep], r32['qp']['pos'][:, keep], rtol=1e-5, atol=1e-4)
+    np.testing.assert_allclose(st.qp.pos[:, keep], e['qp_pos'][:, keep], rtol=1e-5, atol=2e-4)
+    palm = env.env.ref_body
+    assert np.abs(st.qp.pos[:, palm] - ins[0][:, palm]).max() > 1e-3   # the palm did move
+  else:
+    # the physics outputs of the env step are those of the plain step
+    qp2, _ = env.sys.step(QP(*ins), act)
+    keep = np.ones(qp2.pos.shape[1], bool)
+    if env.env.kind == 'fetch':
+      keep[env.env.target_body] = False   # a hit target is teleported by the wrapper
+    np.testing.assert_array_equal(qp2.pos[:, keep], st.qp.pos[:, keep])
 
 
 @pytest.mark.parametrize('variant,b,steps', [('ant', 2048, 30), ('humanoid', 2048, 30),
-                                             ('ant_spring', 1024, 20), ('humanoid_spring', 1024, 20)])
+                                             ('ant_spring', 1024, 20), ('humanoid_spring', 1024, 20),
+                                             ('fetch', 1024, 20), ('grasp', 1024, 20)])
 def test_env_step_on_harvested_states(variant, b, steps):
   """Device path (torch tensors) on states with active contacts."""
   torch = _torch()
@@ -97,6 +116,14 @@ def test_env_step_on_harvested_states(variant, b, steps):
   sysname, env = _env(variant)
   qp, rng = _harvest(env.sys, b, steps, 7)
   act = rng.uniform(-1, 1, (b, env.action_size)).astype(np.float32)
+  if env.env.kind in ('fetch', 'grasp'):
+    # put some targets inside the hit radius so `hits` and the 5 x hit / facing terms are live
+    pos = qp.pos.clone()
+    src = env.env.ref_body if env.env.kind == 'fetch' else env.env.object_body
+    far = torch.tensor([8.0, 3.0, 1.0], device=pos.device)
+    pos[:, env.env.target_body] = pos[:, src] + far      # as after the reference's reset: away
+    pos[: b // 4, env.env.target_body] = pos[: b // 4, src] + 0.3
+    qp = type(qp)(pos, qp.rot, qp.vel, qp.ang)
   st = env.step(State(qp, None, None, None), torch.from_numpy(act).cuda())
   torch.cuda.synchronize()
   got = {'obs': st.obs.cpu().numpy(), 'reward': st.reward.cpu().numpy(), 'done': st.done.cpu().numpy(),
@@ -105,6 +132,13 @@ def test_env_step_on_harvested_states(variant, b, steps):
   r32 = check_env(sysname, env.env, ins, act, got)
   if env.env.kind == 'ant':
     assert (np.abs(r32['obs'][:, 27:]) > 0).mean() > 0.02  # contact forces are live
+  if env.env.kind in ('fetch', 'grasp'):
+    hit = got['metrics'][:, 0] > 0
+    assert 0.1 < hit.mean() < 0.9
+    # hit targets were teleported by the wrapper (caller-side RNG), the others left alone
+    tgt = st.qp.pos[:, env.env.target_body].cpu().numpy()
+    assert (np.abs(tgt[~hit] - r32['qp']['pos'][~hit][:, env.env.target_body]) < 1e-4).all()
+    assert (np.linalg.norm(tgt[hit][:, :2], axis=-1) >= env.env.target_radius - 1e-4).all()
 
 
 def test_env_rollout_equals_repeated_steps():
