@@ -140,7 +140,7 @@ static int validate(const bx_system_desc* d) {
 }
 
 // The outputs of bx_step_io in segment order (pos_o is the first of BX_SEG_OUT pointers).
-static_assert(sizeof(bx_step_io) == (BX_SEG_IN + BX_SEG_OUT) * sizeof(void*), "bx_step_io vs segments");
+static_assert(sizeof(bx_step_io) == (BX_SEG_IN + BX_SEG_OUT + 1) * sizeof(void*), "bx_step_io vs segments");
 static float* const* io_outs(const bx_step_io* io) { return &io->pos_o; }
 static float** io_outs(bx_step_io* io) { return &io->pos_o; }
 
@@ -553,6 +553,8 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
       h.env_object = e.object_body; h.env_hand = e.hand_body;
       for (int i = 0; i < 4; i++) h.env_touch[i] = e.touch_bodies[i];
       h.env_radius = e.target_radius;
+      h.env_tdist = e.target_distance;
+      h.env_theight = e.target_height;
     } else {
       if (e.exclude_current_positions) row3(E + EQ_TORSO_POS, 2, 1); else row3(E + EQ_TORSO_POS);
       row3(E + EQ_TORSO_ROT, 0, 4);
@@ -806,6 +808,9 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   for (int i = 0; i < BX_SEG_OUT; i++) p.out[i] = io_outs(io)[i];
   if (!s->h.env_kind && (io->obs || io->reward || io->done || io->metrics))
     return fail("obs/reward/done/metrics need a system created with desc.env");
+  if (io->env_rand && s->h.env_kind != BX_ENV_FETCH && s->h.env_kind != BX_ENV_GRASP)
+    return fail("env_rand is the target teleport of the fetch / grasp epilogues");
+  p.env_rand = io->env_rand;
   p.num_envs = num_envs;
   p.num_steps = num_steps;
   p.stagger_ns = stagger_ns;
@@ -918,9 +923,12 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
       if (hout[i] && s->h.seg_out[i].nper > 0 && !constant)
         pinned = dev_ptr(hout[i], const_cast<const void**>(&dout[i]));
     }
+    const void* drand = nullptr;
+    if (pinned && hio->env_rand) pinned = dev_ptr(hio->env_rand, &drand);
     if (pinned) {
       bx_step_io d;
       memset(&d, 0, sizeof(d));
+      d.env_rand = static_cast<const float*>(drand);
       d.pos = (const float*)din[0]; d.rot = (const float*)din[1]; d.vel = (const float*)din[2];
       d.ang = (const float*)din[3]; d.act = (const float*)din[4];
       for (int i = 0; i < BX_SEG_OUT; i++) io_outs(&d)[i] = static_cast<float*>(dout[i]);
@@ -948,6 +956,7 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
   }
   size_t per_env = static_cast<size_t>(13 * n + a);
   for (int i = 0; i < BX_SEG_OUT; i++) per_env += s->h.seg_out[i].nper;
+  if (hio->env_rand) per_env += 3;
   const size_t need = per_env * B;
   if (need > s->scratch_floats) {
     cudaFree(s->d_scratch);
@@ -968,6 +977,7 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
   float* const* h_out = io_outs(hio);
   float* d_out[BX_SEG_OUT];
   for (int i = 0; i < BX_SEG_OUT; i++) d_out[i] = take(out_per[i]);
+  float* d_rand = hio->env_rand ? take(3) : nullptr;
   // Pipeline: the batch is cut into chunks (multiples of the 32-env tile); chunk
   // c's H2D, kernel and D2H run on stream c % 3, so the upload of one chunk, the
   // step of another and the download of a third overlap (PCIe is full duplex).
@@ -987,6 +997,10 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
     d.pos = d_in[0] + e0 * in_per[0]; d.rot = d_in[1] + e0 * in_per[1];
     d.vel = d_in[2] + e0 * in_per[2]; d.ang = d_in[3] + e0 * in_per[3];
     d.act = d_in[4] + e0 * in_per[4];
+    if (d_rand) {
+      CUDA_OK(cudaMemcpyAsync(d_rand + e0 * 3, hio->env_rand + e0 * 3, 3 * nb_ * 4, cudaMemcpyHostToDevice, st));
+      d.env_rand = d_rand + e0 * 3;
+    }
     float** dp = io_outs(&d);
     for (int i = 0; i < BX_SEG_OUT; i++) {
       const bool constant = s->h.seg_out[i].map < 0;

@@ -14,6 +14,7 @@ struct BxKernelParams {
   const float4* tab_f;
   const float* in[BX_SEG_IN];  // pos rot vel ang act
   float* out[BX_SEG_OUT];      // order of bx_step_io's outputs
+  const float* env_rand;       // fetch / grasp: [T,B,3] uniforms of the target teleport, or NULL
   int64_t num_envs;
   int32_t num_steps;  // >1: rollout, act is [T,B,A]
   // host path only (bx_step_host on mapped host memory): tile i starts i/grid of

@@ -1303,8 +1303,9 @@ BXS float env_contact_flag(const Ctx& c, const BxHeader& h, int b) {
   return (v.x * v.x + v.y * v.y + v.z * v.z) > 0.00001f ? 1.f : 0.f;
 }
 // Fetch.step / Grasp.step after sys.step (fetch.py:55-122, grasp.py:88-186)
+// rand: this tile's [32,3] uniforms of the target teleport for this step, or nullptr
 template <int MODE>
-static __device__ __noinline__ void phase_env_ego(const Ctx c, const BxHeader& h) {
+static __device__ __noinline__ void phase_env_ego(const Ctx c, const BxHeader& h, const float* rand, int nenv) {
   typedef Lay<MODE> L;
   const int po = MODE == BX_MODE_PBD ? 2 * c.cur : 0;
   const V3 pref = ldv(c, L::BQ * h.env_ref + po);
@@ -1321,6 +1322,7 @@ static __device__ __noinline__ void phase_env_ego(const Ctx c, const BxHeader& h
   if (c.warp != c.nwarp - 1) return;
   const int E = h.q_env, V = h.q_ev;
   const V3 ptgt = ldv(c, L::BQ * h.env_target + po);
+  float hit_any = 0.f;
   if (h.env_kind == BX_ENV_FETCH) {
     const V3 ex = v3(1.f, 0.f, 0.f), ez = v3(0.f, 0.f, 1.f);
     const V3 fwd = rotate(ex, qref), up = rotate(ez, qref);
@@ -1342,6 +1344,7 @@ static __device__ __noinline__ void phase_env_ego(const Ctx c, const BxHeader& h
     const float reward = height + moving + is_up + weighted;  // fetch.py:81
     QROW(c, E + EQ_S0) = make_float4(reward, 0.f, hit, weighted);
     QROW(c, E + EQ_S1) = make_float4(moving, is_up, height, 0.f);
+    hit_any = hit;
   } else {
     const V3 pobj = ldv(c, L::BQ * h.env_object + po);
     const V3 vobj = ldv(c, L::BQ * h.env_object + L::VEL);
@@ -1376,6 +1379,18 @@ static __device__ __noinline__ void phase_env_ego(const Ctx c, const BxHeader& h
     const float reward = moving_to_object + close + touching + 5.f * hit + moving_to_target;  // grasp.py:121
     QROW(c, E + EQ_S0) = make_float4(reward, 0.f, hit, touching);
     QROW(c, E + EQ_S1) = make_float4(moving_to_object, moving_to_target, close, 0.f);
+    hit_any = hit;
+  }
+  // teleport hit targets (fetch.py:88-93 + :124-134, grasp.py:131-136 + :188-198) with the
+  // caller's uniforms: dist = radius + distance * u0, ang = 2 pi u1, z = 1 | height * u2.
+  // The obs above is that of the state before the teleport, as in the reference.
+  const int lane = threadIdx.x & 31;
+  if (rand != nullptr && lane < nenv && hit_any > 0.f) {
+    const float u0 = rand[3 * lane], u1 = rand[3 * lane + 1], u2 = rand[3 * lane + 2];
+    const float dist = h.env_radius + h.env_tdist * u0;
+    float sn, cs;
+    sincosf(6.283185307179586f * u1, &sn, &cs);
+    stv(c, L::BQ * h.env_target + po, v3(dist * cs, dist * sn, h.env_theight > 0.f ? h.env_theight * u2 : 1.f));
   }
 }
 template <int MODE>
@@ -1674,7 +1689,8 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
         phase_angle_vel<MODE>(c, h);  // writes rows only the stores read: no barrier before phase_env
         phase_env<MODE>(c, h);
       } else {
-        phase_env_ego<MODE>(c, h);
+        phase_env_ego<MODE>(c, h, p.env_rand == nullptr ? nullptr
+                            : p.env_rand + 3 * (static_cast<int64_t>(step) * p.num_envs + env0), nenv);
       }
       __syncthreads();
       auto env_ptr = [&](int s) -> float* {

@@ -159,7 +159,7 @@ struct BxHeader {
   int32_t q_ecf;       // contact flags, 4 bodies per quad
   int32_t q_ev;        // env vectors (EV_*)
   int32_t fo_envact;   // grasp action map in the float table: ceil(A/4) quads of min, then of range
-  float env_radius;
+  float env_radius, env_tdist, env_theight;
 };
 
 // env rows relative to q_env

@@ -89,7 +89,7 @@ class CStepIO(C.Structure):
       'pos', 'rot', 'vel', 'ang', 'act', 'pos_o', 'rot_o', 'vel_o', 'ang_o',
       'contact_vel', 'contact_ang', 'joint_vel', 'joint_ang', 'actuator_vel',
       'actuator_ang', 'contact_pos', 'contact_normal', 'contact_penetration',
-      'joint_angle', 'joint_velocity', 'obs', 'reward', 'done', 'metrics')]
+      'joint_angle', 'joint_velocity', 'obs', 'reward', 'done', 'metrics', 'env_rand')]
 
 
 def _f(x):

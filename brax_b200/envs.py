@@ -49,6 +49,7 @@ class CEnvDesc(C.Structure):
               ('actuator_width', C.c_int32 * MAX_ACTUATORS),
               ('ref_body', C.c_int32), ('target_body', C.c_int32), ('object_body', C.c_int32),
               ('hand_body', C.c_int32), ('touch_bodies', C.c_int32 * 4), ('target_radius', C.c_float),
+              ('target_distance', C.c_float), ('target_height', C.c_float),
               ('act_min', C.c_float * MAX_ACT), ('act_range', C.c_float * MAX_ACT)]
 
 
@@ -72,6 +73,8 @@ class EnvDesc:
   hand_body: int = 0
   touch_bodies: Tuple[int, ...] = (0, 0, 0, 0)
   target_radius: float = 0.0
+  target_distance: float = 0.0   # _random_target: dist = radius + distance * u0
+  target_height: float = 0.0     # z = height * u2; <= 0: z = 1 (fetch)
   act_min: Tuple[float, ...] = ()
   act_range: Tuple[float, ...] = ()
 
@@ -111,6 +114,7 @@ class EnvDesc:
     c.object_body, c.hand_body = self.object_body, self.hand_body
     c.touch_bodies[:] = list(self.touch_bodies)
     c.target_radius = self.target_radius
+    c.target_distance, c.target_height = self.target_distance, self.target_height
     if self.kind == 'grasp':
       if len(self.act_min) != desc.act_size or len(self.act_range) != desc.act_size:
         raise ValueError('grasp: act_min / act_range must have act_size entries')
@@ -122,7 +126,8 @@ class EnvDesc:
 def fetch_desc(desc: SystemDesc) -> EnvDesc:
   """EnvDesc of `Fetch` (fetch.py:28-34): torso / target indices by body name, radius 2."""
   names = desc.body_names
-  return EnvDesc('fetch', ref_body=names.index('Torso'), target_body=names.index('Target'), target_radius=2.0)
+  return EnvDesc('fetch', ref_body=names.index('Torso'), target_body=names.index('Target'), target_radius=2.0,
+                 target_distance=15.0)
 
 
 def grasp_desc(desc: SystemDesc) -> EnvDesc:
@@ -144,7 +149,7 @@ def grasp_desc(desc: SystemDesc) -> EnvDesc:
   return EnvDesc('grasp', ref_body=names.index('HandPalm'), target_body=names.index('Target'),
                  object_body=names.index('Object'), hand_body=names.index('HandThumbProximal'),
                  touch_bodies=(3, 9, 12, 15),   # grasp.py:116, as written there
-                 target_radius=1.1, act_min=tuple(lo), act_range=tuple(rng))
+                 target_radius=1.1, target_distance=10.0, target_height=8.0, act_min=tuple(lo), act_range=tuple(rng))
 
 
 @dataclasses.dataclass
@@ -236,12 +241,12 @@ class Humanoid(Env):
 
 
 class _TargetEnv(Env):
-  """Common part of fetch / grasp: after the fused step, targets that were hit are teleported
-  to a new random place (fetch.py:88-93 + :124-134, grasp.py:131-136 + :188-198).  The
-  reference draws from the JAX PRNG carried in `state.info['rng']`; here a numpy / torch
-  generator (seeded at construction) is used -- same distribution, not the same stream."""
-  target_distance = 0.0
-  target_height = None   # None: z = 1 (fetch); else z = target_height * U (grasp)
+  """Common part of fetch / grasp: targets that were hit are teleported to a new random place
+  (fetch.py:88-93 + :124-134, grasp.py:131-136 + :188-198) INSIDE the launch, from three
+  uniform numbers per env handed to it (`bx_step_io.env_rand`).  The reference draws them from
+  the JAX PRNG carried in `state.info['rng']`; here a numpy / torch generator (seeded at
+  construction) does -- same distribution, not the same stream; pass `rand=` to `step` to
+  supply your own (e.g. the reference's draws)."""
 
   def __init__(self, system_name, env, device=0, seed=0):
     super().__init__(system_name, env, device)
@@ -249,41 +254,27 @@ class _TargetEnv(Env):
     self._seed = seed
     self._torch_gen = None
 
-  def _uniform(self, like, n):
+  def _uniform(self, like, lead):
     if _system._is_torch(like):
       import torch
       if self._torch_gen is None or self._torch_gen.device != like.device:
         self._torch_gen = torch.Generator(device=like.device)
         self._torch_gen.manual_seed(self._seed)
-      return torch.rand((3,) + tuple(n), generator=self._torch_gen, device=like.device, dtype=like.dtype)
-    return self._np_rng.uniform(size=(3,) + tuple(n)).astype(np.float32)
+      return torch.rand(tuple(lead) + (3,), generator=self._torch_gen, device=like.device, dtype=torch.float32)
+    return self._np_rng.uniform(size=tuple(lead) + (3,)).astype(np.float32)
 
-  def step(self, state: State, action) -> State:
-    st = super().step(state, action)
-    hit = st.metrics['hits']
-    pos = st.qp.pos
-    u = self._uniform(pos, hit.shape)
-    xp = __import__('torch') if _system._is_torch(pos) else np
-    dist = self.env.target_radius + self.target_distance * u[0]
-    ang = (2.0 * np.pi) * u[1]
-    z = xp.ones_like(dist) if self.target_height is None else self.target_height * u[2]
-    target = xp.stack([dist * xp.cos(ang), dist * xp.sin(ang), z], -1)
-    ti = self.env.target_body
-    cur = pos[..., ti, :]
-    new = xp.where((hit > 0)[..., None], target, cur)
-    if _system._is_torch(pos):
-      pos = pos.clone()
-      pos[..., ti, :] = new
-    else:
-      pos = np.array(pos)
-      pos[..., ti, :] = new
-    qp = _system.QP(pos, st.qp.rot, st.qp.vel, st.qp.ang)
-    return st.replace(qp=qp)
+  def step(self, state: State, action, rand=None) -> State:
+    if rand is None:
+      rand = self._uniform(state.qp.pos, state.qp.pos.shape[:-2])
+    qp, info, eo = self.sys.step(state.qp, action, env=True, env_rand=rand)
+    names = self.env.metric_names()
+    metrics = dict(state.metrics)
+    metrics.update({k: eo['metrics'][..., i] for i, k in enumerate(names)})
+    return State(qp, eo['obs'], eo['reward'], eo['done'], metrics, dict(state.info, physics=info))
 
 
 class Fetch(_TargetEnv):
   """brax/envs/fetch.py:25-134."""
-  target_distance = 15.0
 
   def __init__(self, legacy_spring=False, device: int = 0, seed: int = 0):
     super().__init__('fetch_spring' if legacy_spring else 'fetch', fetch_desc, device, seed)
@@ -291,8 +282,6 @@ class Fetch(_TargetEnv):
 
 class Grasp(_TargetEnv):
   """brax/envs/grasp.py:25-198 (pbd; action_size = actuator dofs + 3 palm-target slots :140-142)."""
-  target_distance = 10.0
-  target_height = 8.0
 
   def __init__(self, legacy_spring=False, device: int = 0, seed: int = 0):
     if legacy_spring:

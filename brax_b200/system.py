@@ -220,7 +220,8 @@ class System:
     return QP(*arrs)
 
   # ---- the step ---------------------------------------------------------------
-  def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False, env: bool = False):
+  def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False, env: bool = False,
+           env_rand=None):
     """`System.step(qp, act) -> (qp, info)` (system.py:244-247).
 
     out: optional `HostBuffers` (host path only): results are written into its
@@ -234,8 +235,8 @@ class System:
     if env and self.env is None:
       raise ValueError('this System was built without an EnvDesc')
     if _is_torch(qp.pos):
-      return self._step_torch(qp, act, 1, angle_vel, env)
-    return self._step_numpy(qp, act, out, angle_vel, env)
+      return self._step_torch(qp, act, 1, angle_vel, env, env_rand)
+    return self._step_numpy(qp, act, out, angle_vel, env, env_rand)
 
   def angle_vel_groups(self, js: JointState):
     """[(angle, vel) per joint group] exactly as `[j.angle_vel(qp) for j in
@@ -263,14 +264,14 @@ class System:
     self._lib.bx_host_transfer_bytes(self._h, batch, C.byref(h2d), C.byref(d2h))
     return int(h2d.value), int(d2h.value)
 
-  def rollout(self, qp: QP, acts, env: bool = False):
+  def rollout(self, qp: QP, acts, env: bool = False, env_rand=None):
     """T steps in ONE launch; acts is [T, B, A] (torch CUDA).  Returns the final
     QP and the Info of the last step (lax.scan of System.step over actions); with
     env=True also the env epilogue of EVERY step: obs [T,B,O], reward / done [T,B],
     metrics [T,B,M]."""
     if env and self.env is None:
       raise ValueError('this System was built without an EnvDesc')
-    return self._step_torch(qp, acts, int(acts.shape[0]), False, env)
+    return self._step_torch(qp, acts, int(acts.shape[0]), False, env, env_rand)
 
   def _shapes(self, pos_shape):
     n = self.num_bodies
@@ -333,8 +334,10 @@ class System:
   def _clear_optional(self, io):
     io.joint_angle = io.joint_velocity = None
     io.obs = io.reward = io.done = io.metrics = None
+    io.env_rand = None
 
-  def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False):
+  def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False, env_rand=None):
+    """env_rand: (fetch / grasp) uniforms of the target teleport, [B,3] or [T,B,3]."""
     import torch
     batched, b = self._shapes(qp.pos.shape)
     n, a = self.num_bodies, self.act_size
@@ -370,6 +373,9 @@ class System:
         cnt *= d
       out[name] = flat[off:off + cnt].view(shape)
       setattr(io, name, base + 4 * off if cnt else None)
+    if env_rand is not None:
+      env_rand = prep(env_rand, steps * b * 3)
+      io.env_rand = env_rand.data_ptr()
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     if self.autotune and steps == 1 and b >= 1024 and b not in self._tuned:
       # first call at this batch size: time the candidate CTA sizes once
@@ -384,7 +390,8 @@ class System:
       raise RuntimeError('bx_step: ' + _lib.last_error())
     return self._wrap(out, batched, steps)
 
-  def _step_numpy(self, qp: QP, act, bufs: 'HostBuffers' = None, av: bool = False, env: bool = False):
+  def _step_numpy(self, qp: QP, act, bufs: 'HostBuffers' = None, av: bool = False, env: bool = False,
+                  env_rand=None):
     batched, b = self._shapes(np.shape(qp.pos))
     n, a = self.num_bodies, self.act_size
 
@@ -413,6 +420,9 @@ class System:
       for name, shape in self._specs(b, av, env):
         out[name] = np.empty(shape, dtype=np.float32)
         setattr(io, name, out[name].__array_interface__['data'][0] if out[name].size else None)
+    if env_rand is not None:
+      env_rand = prep(env_rand, b * 3)
+      io.env_rand = env_rand.__array_interface__['data'][0]
     rc = self._lib.bx_step_host(self._h, b, C.byref(io))
     if rc != 0:
       raise RuntimeError('bx_step_host: ' + _lib.last_error())

@@ -179,6 +179,8 @@ typedef struct bx_env_desc {
   int32_t hand_body;   /* grasp: HandThumbProximal */
   int32_t touch_bodies[4]; /* grasp.py:116 */
   float target_radius;
+  float target_distance; /* _random_target: dist = radius + distance * u0 */
+  float target_height;   /* z = height * u2 (grasp); <= 0: z = 1 (fetch.py:131) */
   float act_min[BX_MAX_ACT], act_range[BX_MAX_ACT]; /* grasp.py:43-54: act = min + range * (act + 1) / 2 */
 } bx_env_desc;
 
@@ -231,6 +233,12 @@ typedef struct bx_step_io {
    * reference's Env.step outputs, State.obs [B,O], State.reward [B], State.done [B],
    * State.metrics as [B,M].  With bx_rollout they are [T,B,...]: written every step. */
   float *obs, *reward, *done, *metrics;
+  /* Optional INPUT of the fetch / grasp epilogues: three uniform [0,1) numbers per env (and per
+   * step of a rollout: [T,B,3]) -- the draws of `_random_target` (fetch.py:124-134: distance,
+   * angle; grasp.py:188-198: distance, angle, height).  With it the launch also teleports the
+   * target of every env that scored a hit (fetch.py:88-93, grasp.py:131-136) in the QP it
+   * returns; NULL leaves the targets where they are (the caller teleports). */
+  const float* env_rand;
 } bx_step_io;
 
 /* Creates a system on CUDA device `device` (tables uploaded once).  Returns 0

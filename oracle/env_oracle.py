@@ -82,6 +82,20 @@ def _egocentric(env, pos, rot, vel, cvel, dt):
   return pos_local, vel_local, contacts
 
 
+def env_teleport(env, pos, hit, rand, dtype=np.float32):
+  """fetch.py:88-93 + :124-134, grasp.py:131-136 + :188-198: targets of envs with a hit move to
+  (dist cos a, dist sin a, z), dist = radius + distance * u0, a = 2 pi u1, z = 1 | height * u2;
+  rand [B,3] are the uniforms the reference draws from its PRNG key."""
+  dt = np.dtype(dtype).type
+  pos, rand = np.array(pos, dtype), np.asarray(rand, dtype)
+  dist = dt(env.target_radius) + dt(env.target_distance) * rand[:, 0]
+  ang = dt(np.pi) * dt(2.) * rand[:, 1]
+  z = dt(env.target_height) * rand[:, 2] if env.target_height > 0 else np.ones_like(dist)
+  target = np.stack([dist * np.cos(ang), dist * np.sin(ang), z], axis=-1).astype(dtype)
+  pos[:, env.target_body] = np.where((np.asarray(hit) > 0)[:, None], target, pos[:, env.target_body])
+  return pos
+
+
 def _healthy(env, z, dt):
   # ant.py:229-231, humanoid.py:255-257
   h = np.where(z < dt(env.healthy_z_range[0]), dt(0.0), dt(1.0))

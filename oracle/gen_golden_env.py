@@ -71,6 +71,7 @@ def main(names):
     steps = g['pos'].shape[0]
     obs, rew, done, met, names_m = [], [], [], [], None
     qpo = {k: [] for k in ('pos', 'rot', 'vel', 'ang')}
+    rands = []
     for t in range(steps):
       qp = brax.QP(pos=g['pos'][t], rot=g['rot'][t], vel=g['vel'][t], ang=g['ang'][t])
       st = benv.State(qp=qp, obs=np.zeros(1), reward=np.zeros(()), done=np.zeros(()), metrics={},
@@ -80,6 +81,13 @@ def main(names):
         np.testing.assert_allclose(np.asarray(st2.qp.pos, np.float64)[:12], g['pos_o'][t][:12], rtol=0, atol=1e-12)
       for k in qpo:
         qpo[k].append(np.asarray(getattr(st2.qp, k), np.float64))
+      if modname in ('fetch', 'grasp'):
+        # the uniforms `_random_target` drew from state.info['rng'] (fetch.py:124-134,
+        # grasp.py:188-198): same jumpy calls on the same key
+        import brax.jumpy as jp
+        keys = jp.random_split(np.array([1, 2], dtype='uint32'), 3 if modname == 'fetch' else 4)
+        u = [float(jp.random_uniform(k)) for k in keys[1:]] + [0.0]
+        rands.append(u[:3])
       obs.append(np.asarray(st2.obs, np.float64))
       rew.append(float(st2.reward))
       done.append(float(st2.done))
@@ -91,6 +99,7 @@ def main(names):
                         metric_names=np.asarray(names_m), system=np.asarray(sysname),
                         dt=np.asarray(float(e.sys.config.dt)),
                         **{'qp_' + k: np.stack(v) for k, v in qpo.items()},
+                        **({'rand': np.asarray(rands)} if rands else {}),
                         **({'act_min': np.asarray(e._min_act, np.float64), 'act_range': np.asarray(e._range_act, np.float64)}
                            if modname == 'grasp' else {}))
     print('%-16s %3d steps, obs %d, metrics %s' % (name, steps, obs[0].shape[0], names_m))

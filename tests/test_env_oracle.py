@@ -69,10 +69,13 @@ def test_env_oracle_chain_matches_reference(variant):
     if tol is not None:
       for k in ('obs', 'reward', 'done', 'metrics'):
         np.testing.assert_allclose(r[k], e[k], rtol=0, atol=tol, err_msg=k)
-      if 'qp_pos' in e:   # the step's output QP (a hit teleports the target afterwards: caller's)
-        hit = e['metrics'][:, 0] > 0
+      if env.kind in ('fetch', 'grasp'):
+        # the step's output QP, hit targets teleported with the uniforms the reference drew
+        out = dict(out, pos=env_oracle.env_teleport(env, out['pos'], r['metrics'][:, 0], e['rand'], dtype))
         for k in util.QP_KEYS:
-          np.testing.assert_allclose(out[k][~hit], e['qp_' + k][~hit], rtol=0, atol=1e-9, err_msg=k)
+          np.testing.assert_allclose(out[k], e['qp_' + k], rtol=0, atol=1e-9, err_msg=k)
+        if variant == 'fetch':
+          assert (e['metrics'][:, 0] > 0).any()   # the golden does hold hits
     else:
       np.testing.assert_array_equal(r['done'], e['done'])
       # velocities are position differences over dt (ant.py:226): ulp(pos)/dt of float32

@@ -81,7 +81,9 @@ def test_env_step_on_golden_inputs(variant):
   g, e = util.load_golden(sysname), env_golden(variant)
   ins = [g[k].astype(np.float32) for k in util.QP_KEYS]
   act = g['act'].astype(np.float32)
-  st = env.step(State(QP(*ins), None, None, None), act)
+  ego = env.env.kind in ('fetch', 'grasp')
+  kw = dict(rand=e['rand'].astype(np.float32)) if ego else {}   # the reference's own draws
+  st = env.step(State(QP(*ins), None, None, None), act, **kw)
   got = {'obs': st.obs, 'reward': st.reward, 'done': st.done,
          'metrics': np.stack([st.metrics[k] for k in env.env.metric_names()], -1)}
   assert st.obs.shape == e['obs'].shape and st.obs.shape[1] == env.observation_size
@@ -89,21 +91,20 @@ def test_env_step_on_golden_inputs(variant):
   np.testing.assert_array_equal(st.done, e['done'])
   np.testing.assert_allclose(st.reward, e['reward'], rtol=1e-4, atol=5e-3)
   assert np.quantile(np.abs(st.obs - e['obs']), 0.99) < 1e-3
-  if env.env.kind == 'grasp':
-    # the action map and the palm move happen inside the launch: the step's QP is that of the
-    # oracle chain (prologue -> physics) and of the reference's Grasp.step
-    keep = np.arange(st.qp.pos.shape[1]) != env.env.target_body   # a hit target is teleported by the wrapper
-    np.testing.assert_allclose(st.qp.pos[:, keep], r32['qp']['pos'][:, keep], rtol=1e-5, atol=1e-4)
-    np.testing.assert_allclose(st.qp.pos[:, keep], e['qp_pos'][:, keep], rtol=1e-5, atol=2e-4)
-    palm = env.env.ref_body
-    assert np.abs(st.qp.pos[:, palm] - ins[0][:, palm]).max() > 1e-3   # the palm did move
+  if ego:
+    # the step's QP is that of the oracle chain (grasp: action map + palm move inside the launch)
+    # with hit targets teleported by the reference's draws, and that of the reference itself
+    from oracle import env_oracle
+    want = env_oracle.env_teleport(env.env, r32['qp']['pos'], r32['metrics'][:, 0], e['rand'], np.float32)
+    np.testing.assert_allclose(st.qp.pos, want, rtol=1e-5, atol=1e-4)
+    np.testing.assert_allclose(st.qp.pos, e['qp_pos'], rtol=1e-5, atol=2e-4)
+    if env.env.kind == 'grasp':
+      palm = env.env.ref_body
+      assert np.abs(st.qp.pos[:, palm] - ins[0][:, palm]).max() > 1e-3   # the palm did move
   else:
     # the physics outputs of the env step are those of the plain step
     qp2, _ = env.sys.step(QP(*ins), act)
-    keep = np.ones(qp2.pos.shape[1], bool)
-    if env.env.kind == 'fetch':
-      keep[env.env.target_body] = False   # a hit target is teleported by the wrapper
-    np.testing.assert_array_equal(qp2.pos[:, keep], st.qp.pos[:, keep])
+    np.testing.assert_array_equal(qp2.pos, st.qp.pos)
 
 
 @pytest.mark.parametrize('variant,b,steps', [('ant', 2048, 30), ('humanoid', 2048, 30),
@@ -124,7 +125,11 @@ def test_env_step_on_harvested_states(variant, b, steps):
     pos[:, env.env.target_body] = pos[:, src] + far      # as after the reference's reset: away
     pos[: b // 4, env.env.target_body] = pos[: b // 4, src] + 0.3
     qp = type(qp)(pos, qp.rot, qp.vel, qp.ang)
-  st = env.step(State(qp, None, None, None), torch.from_numpy(act).cuda())
+  kw = {}
+  if env.env.kind in ('fetch', 'grasp'):
+    rand = rng.uniform(0, 1, (b, 3)).astype(np.float32)
+    kw = dict(rand=torch.from_numpy(rand).cuda())
+  st = env.step(State(qp, None, None, None), torch.from_numpy(act).cuda(), **kw)
   torch.cuda.synchronize()
   got = {'obs': st.obs.cpu().numpy(), 'reward': st.reward.cpu().numpy(), 'done': st.done.cpu().numpy(),
          'metrics': torch.stack([st.metrics[k] for k in env.env.metric_names()], -1).cpu().numpy()}
@@ -135,10 +140,14 @@ def test_env_step_on_harvested_states(variant, b, steps):
   if env.env.kind in ('fetch', 'grasp'):
     hit = got['metrics'][:, 0] > 0
     assert 0.1 < hit.mean() < 0.9
-    # hit targets were teleported by the wrapper (caller-side RNG), the others left alone
-    tgt = st.qp.pos[:, env.env.target_body].cpu().numpy()
-    assert (np.abs(tgt[~hit] - r32['qp']['pos'][~hit][:, env.env.target_body]) < 1e-4).all()
-    assert (np.linalg.norm(tgt[hit][:, :2], axis=-1) >= env.env.target_radius - 1e-4).all()
+    # hit targets were teleported inside the launch with the given uniforms, the others left alone
+    from oracle import env_oracle
+    want = env_oracle.env_teleport(env.env, r32['qp']['pos'], got['metrics'][:, 0], rand, np.float32)
+    np.testing.assert_allclose(st.qp.pos.cpu().numpy()[:, env.env.target_body], want[:, env.env.target_body],
+                               rtol=1e-5, atol=1e-4)
+    # without env_rand the launch leaves every target where it is
+    _, _, eo = env.sys.step(qp, torch.from_numpy(act).cuda(), env=True)
+    assert torch.equal(eo['obs'], st.obs)
 
 
 def test_env_rollout_equals_repeated_steps():
