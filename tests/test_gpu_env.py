@@ -176,6 +176,45 @@ def test_env_rollout_equals_repeated_steps():
   assert torch.equal(one.obs, obs[0][5]) and torch.equal(one.reward, rew[0][5])
 
 
+def test_env_rollout_with_teleports_and_host_buffers():
+  """grasp: a rollout with per-step uniforms [T,B,3] == the same steps one by one (action map,
+  palm move and teleports inside the launch every step); ant: the page-locked host path
+  (zero-copy launch on HostBuffers) returns the env outputs of the device path."""
+  torch = _torch()
+  from brax_b200.envs import State
+  from brax_b200.system import QP
+  _, env = _env('grasp')
+  b, t_n = 200, 5
+  qp, rng = _harvest(env.sys, b, 3, 5)
+  pos = qp.pos.clone()
+  pos[:, env.env.target_body] = pos[:, env.env.object_body] + 0.2     # hits from the first step on
+  qp = QP(pos, qp.rot, qp.vel, qp.ang)
+  acts = torch.from_numpy(rng.uniform(-1, 1, (t_n, b, env.action_size)).astype(np.float32)).cuda()
+  rands = torch.from_numpy(rng.uniform(0, 1, (t_n, b, 3)).astype(np.float32)).cuda()
+  st, obs, rew = State(qp, None, None, None), [], []
+  for t in range(t_n):
+    st = env.step(st, acts[t], rand=rands[t])
+    obs.append(st.obs); rew.append(st.reward)
+  q2, _, eo = env.sys.rollout(qp, acts, env=True, env_rand=rands)
+  torch.cuda.synchronize()
+  assert torch.equal(q2.pos, st.qp.pos) and torch.equal(eo['obs'], torch.stack(obs))
+  assert torch.equal(eo['reward'], torch.stack(rew)) and float(eo['metrics'][..., 0].sum()) > 0
+  # host path on page-locked buffers
+  _, ant = _env('ant')
+  b = 96
+  qpa, rng = _harvest(ant.sys, b, 3, 9)
+  act = rng.uniform(-1, 1, (b, ant.action_size)).astype(np.float32)
+  dq, _, deo = ant.sys.step(qpa, torch.from_numpy(act).cuda(), env=True)
+  hb = ant.sys.host_buffers(b)
+  for k in util.QP_KEYS:
+    getattr(hb, k)[...] = getattr(qpa, k).cpu().numpy()
+  hb.act[...] = act
+  hq, _, heo = ant.sys.step(hb.qp(), hb.act, out=hb, env=True)
+  np.testing.assert_array_equal(hq.pos, dq.pos.cpu().numpy())
+  for k in ('obs', 'reward', 'done', 'metrics'):
+    np.testing.assert_array_equal(heo[k], deo[k].cpu().numpy(), err_msg=k)
+
+
 def test_env_outputs_need_an_env_system():
   _torch()
   from brax_b200.system import load_system
@@ -184,7 +223,7 @@ def test_env_outputs_need_an_env_system():
     s.step(s.default_qp(batch=4), np.zeros((4, 8), np.float32), env=True)
 
 
-@pytest.mark.parametrize('variant,b', [('ant', 1024), ('humanoid', 1024)])
+@pytest.mark.parametrize('variant,b', [('ant', 1024), ('humanoid', 1024), ('grasp', 512), ('fetch', 512)])
 def test_1000_step_statistics(variant, b):
   """North star: 'reward/energy statistics over 1000-step rollouts are compared
   within a stated tolerance'.  1000 env steps of B envs on the GPU (10 launches of
@@ -194,7 +233,10 @@ def test_1000_step_statistics(variant, b):
   reward per step, mean torso height, mean kinetic energy and the fraction of
   unhealthy env-steps over all B x 1000 samples agree within 2 % of the oracle's
   value (or 3 standard errors of the mean across envs, whichever is larger), and the
-  first 10 steps agree per env (rollout tolerance of test_rollout_10_steps)."""
+  first 10 steps agree per env (rollout tolerance of test_rollout_10_steps).
+  grasp / fetch (BASELINE config 4 and the box-collider env): the same with the in-launch
+  action map / palm move and target teleports (shared uniforms); 'height' is obs[0] (distance
+  to the object / torso_fwd.x) and 'unhealthy' the hit rate."""
   torch = _torch()
   from oracle import env_oracle
   from oracle.oracle import Oracle
@@ -214,15 +256,23 @@ def test_1000_step_statistics(variant, b):
   from brax_b200.system import QP
   qp = QP(*[torch.from_numpy(np.ascontiguousarray(getattr(st0.qp, k))).cuda() for k in util.QP_KEYS])
   g_rew, g_z, g_e, g_done, g_first = [], [], [], [], None
-  tz = 0 if env.env.exclude_current_positions else 2
+  ego = env.env.kind in ('fetch', 'grasp')
+  tz = 0 if (ego or env.env.exclude_current_positions) else 2
+  rands = rng.uniform(0, 1, (t_n, b, 3)).astype(np.float32) if ego else None
+  if ego:   # targets start away from the robot, as after the reference's reset
+    src = env.env.object_body if env.env.kind == 'grasp' else env.env.ref_body
+    st0.qp.pos[:, env.env.target_body] = st0.qp.pos[:, src] + np.asarray([3.0, 1.0, 1.0], np.float32)
+    qp = QP(*[torch.from_numpy(np.ascontiguousarray(getattr(st0.qp, k))).cuda() for k in util.QP_KEYS])
   for c0 in range(0, t_n, chunk):
     a = torch.from_numpy(acts[c0:c0 + chunk]).cuda()
     # energy needs the velocities of every step: step-by-step inside the chunk would be
     # 1000 launches; instead take z / reward / done from the per-step env outputs and
     # the energy at the chunk ends
-    qp, _, eo = env.sys.rollout(qp, a, env=True)
+    qp, _, eo = env.sys.rollout(qp, a, env=True,
+                                env_rand=torch.from_numpy(rands[c0:c0 + chunk]).cuda() if ego else None)
     g_rew.append(eo['reward'].cpu().numpy()); g_z.append(eo['obs'][..., tz].cpu().numpy())
-    g_done.append(eo['done'].cpu().numpy()); g_e.append(energy(qp.vel.cpu().numpy()))
+    g_done.append((eo['metrics'][..., 0] if ego else eo['done']).cpu().numpy())
+    g_e.append(energy(qp.vel.cpu().numpy()))
     if g_first is None:
       g_first = eo['obs'][9].cpu().numpy()
   g_rew, g_z, g_done = np.concatenate(g_rew), np.concatenate(g_z), np.concatenate(g_done)
@@ -234,10 +284,13 @@ def test_1000_step_statistics(variant, b):
   o_rew, o_z, o_done, o_e, o_first = np.empty((t_n, b), np.float32), np.empty((t_n, b), np.float32), \
       np.empty((t_n, b), np.float32), [], None
   for t in range(t_n):
-    out = o.step(cur['pos'], cur['rot'], cur['vel'], cur['ang'], acts[t], num_threads=os.cpu_count() or 1)
+    pos_in, act_in = env_oracle.env_prologue(desc, env.env, cur['pos'], acts[t], np.float32)
+    out = o.step(pos_in, cur['rot'], cur['vel'], cur['ang'], act_in, num_threads=os.cpu_count() or 1)
     fa, fv = env_oracle.flat_angle_vel(desc, *o.angle_vel(out['rot'], out['ang']))
     r = env_oracle.env_epilogue(desc, env.env, cur['pos'], out, acts[t], fa, fv, np.float32)
-    o_rew[t], o_z[t], o_done[t] = r['reward'], r['obs'][:, tz], r['done']
+    if ego:
+      out['pos'] = env_oracle.env_teleport(env.env, out['pos'], r['metrics'][:, 0], rands[t], np.float32)
+    o_rew[t], o_z[t], o_done[t] = r['reward'], r['obs'][:, tz], (r['metrics'][:, 0] if ego else r['done'])
     if t == 9:
       o_first = r['obs']
     if (t + 1) % chunk == 0:
