@@ -19,6 +19,11 @@ from tests.test_gpu_parity import GAP_MULT, OUTLIER_FRAC, VEL_ULPS, _harvest, _t
 
 pytestmark = pytest.mark.gpu
 
+# no reference golden (the env goldens cover the pbd config): checked against the oracle
+# chain only -- exercises the egocentric rows in JS (legacy_spring has no dead pose rows)
+from brax_b200 import envs as _envs  # noqa: E402
+VARIANTS = dict(VARIANTS, fetch_spring=('fetch_spring', _envs.fetch_desc(util.load_desc('fetch_spring'))))
+
 
 def _env(variant, device=0):
   from brax_b200 import envs
@@ -109,7 +114,8 @@ def test_env_step_on_golden_inputs(variant):
 
 @pytest.mark.parametrize('variant,b,steps', [('ant', 2048, 30), ('humanoid', 2048, 30),
                                              ('ant_spring', 1024, 20), ('humanoid_spring', 1024, 20),
-                                             ('fetch', 1024, 20), ('grasp', 1024, 20)])
+                                             ('fetch', 1024, 20), ('grasp', 1024, 20),
+                                             ('fetch_spring', 1024, 20)])
 def test_env_step_on_harvested_states(variant, b, steps):
   """Device path (torch tensors) on states with active contacts."""
   torch = _torch()
