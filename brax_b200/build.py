@@ -13,6 +13,8 @@ DEPS = ['bx_api.cu', 'bx_kernels.cu', 'bx_step_kernel.cuh', 'bx_params.h', 'bx_m
         os.path.join('..', '..', 'include', 'brax_b200.h')]
 # (launch bound threads, min blocks per SM): one kernel translation unit each
 BOUNDS = [(256, 2), (320, 2), (384, 2), (512, 1)]
+# extra units: (name, threads, min blocks per SM)
+EXTRA_UNITS = [('320x3', 320, 3)]
 
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3',
               '-std=c++17', '-Xcompiler', '-fPIC']
@@ -43,6 +45,11 @@ def build(force: bool = False, verbose: bool = False, extra=(), out: str = None)
     o = os.path.join(objdir, 'bx_kernels_%d.o' % maxt)
     objs.append(o)
     jobs.append(common + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-c',
+                          os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
+  for name, maxt, minb in EXTRA_UNITS:
+    o = os.path.join(objdir, 'bx_kernels_%s.o' % name)
+    objs.append(o)
+    jobs.append(common + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-DBX_TU_NAME=%s' % name, '-c',
                           os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
   procs = [subprocess.Popen(j) for j in jobs]
   rcs = [p.wait() for p in procs]

@@ -632,7 +632,11 @@ static void build_tables(const bx_system_desc* d, BxHeader* h, std::vector<int32
 // The kernels live in one translation unit per launch bound (bx_kernels.cu); the
 // launch picks the smallest bound that holds the configured CTA size.
 static cudaError_t launch_variant(int mode, int jc, int cc, unsigned grid, int threads, size_t smem,
-                                  cudaStream_t stream, const BxKernelParams& p) {
+                                  cudaStream_t stream, const BxKernelParams& p, bool three) {
+  // big batches of small systems: three tiles per SM (64 registers) when more than two waves
+  // of tiles exist and three tiles fit in shared memory
+  if (three && threads <= 320 && 3 * (smem + 1024) <= 233472)
+    return bx_launch_320x3(mode, jc, cc, grid, threads, smem, stream, p);
   if (threads <= 256) return bx_launch_256(mode, jc, cc, grid, threads, smem, stream, p);
   if (threads <= 320) return bx_launch_320(mode, jc, cc, grid, threads, smem, stream, p);
   // 12 warps with two tiles per SM (80 registers) only pays when two tiles fit in
@@ -644,6 +648,7 @@ static cudaError_t launch_variant(int mode, int jc, int cc, unsigned grid, int t
 static int set_smem_attr(int bytes) {
   CUDA_OK(bx_set_smem_256(bytes));
   CUDA_OK(bx_set_smem_320(bytes));
+  CUDA_OK(bx_set_smem_320x3(bytes));
   CUDA_OK(bx_set_smem_384(bytes));
   CUDA_OK(bx_set_smem_512(bytes));
   return 0;
@@ -818,11 +823,14 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   const int64_t tiles = (num_envs + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA;
   if (tiles > 0x7fffffffLL) return fail("too many environments for one launch");
   // systems with an env epilogue run the builds that contain it; all others the plain ones
+  // BX_THREE_TILES: 0 never, 1 always (where it fits), default: batches of more than 4 tiles per SM
+  static const int three_mode = getenv("BX_THREE_TILES") ? atoi(getenv("BX_THREE_TILES")) : 2;
+  const bool three = three_mode == 1 || (three_mode == 2 && tiles > 4 * static_cast<int64_t>(s->sm_count));
   // BX_PDL=0 switches programmatic dependent launch off (A/B, debugging)
   static const int pdl = (getenv("BX_PDL") && atoi(getenv("BX_PDL")) == 0) ? 0 : BX_CC_PDL;
   cudaError_t le = launch_variant(s->h.mode, s->jc, s->cc | (s->h.env_kind ? BX_CC_ENV : 0) | pdl,
                                   static_cast<unsigned>(tiles), 32 * s->warps,
-                                  s->smem_bytes, stream, p);
+                                  s->smem_bytes, stream, p, three);
   g_launches.fetch_add(1);
   CUDA_OK(le);
   return 0;

@@ -10,6 +10,9 @@
 
 #define BX_CAT_(a, b) a##b
 #define BX_CAT(a, b) BX_CAT_(a, b)
+#ifndef BX_TU_NAME  // suffix of the exported launcher (default: the thread bound)
+#define BX_TU_NAME BX_TU_MAXT
+#endif
 
 typedef void (*bx_kernel_fn)(const BxKernelParams);
 
@@ -41,7 +44,7 @@ static bx_kernel_fn pick_any(int mode, int jc, int cc) {
   return mode == BX_MODE_PBD ? pick<BX_MODE_PBD, 0>(jc, cc) : pick<BX_MODE_LEGACY_SPRING, 0>(jc, cc);
 }
 
-cudaError_t BX_CAT(bx_launch_, BX_TU_MAXT)(int mode, int jc, int cc, unsigned grid, int threads,
+cudaError_t BX_CAT(bx_launch_, BX_TU_NAME)(int mode, int jc, int cc, unsigned grid, int threads,
                                            size_t smem, cudaStream_t stream,
                                            const BxKernelParams& p) {
   if (!(cc & BX_CC_PDL)) {
@@ -61,7 +64,7 @@ cudaError_t BX_CAT(bx_launch_, BX_TU_MAXT)(int mode, int jc, int cc, unsigned gr
   return cudaLaunchKernelEx(&cfg, pick_any(mode, jc, cc), p);
 }
 
-cudaError_t BX_CAT(bx_set_smem_, BX_TU_MAXT)(int bytes) {
+cudaError_t BX_CAT(bx_set_smem_, BX_TU_NAME)(int bytes) {
   for (int mode = 0; mode < 2; mode++)
     for (int jc = 0; jc < BX_NUM_JC; jc++)
       for (int cc = 0; cc < BX_NUM_CC; cc++)

@@ -62,6 +62,7 @@ enum { BX_CC_PLANE_FUSED = 0, BX_CC_PLANE = 1, BX_CC_ALL = 2, BX_NUM_CC = 3 };
   cudaError_t bx_set_smem_##maxt(int bytes);
 BX_LAUNCHER_DECL(256)
 BX_LAUNCHER_DECL(320)
+BX_LAUNCHER_DECL(320x3)  // (320, 3): 64 registers, three tiles per SM for big batches of small systems
 BX_LAUNCHER_DECL(384)
 BX_LAUNCHER_DECL(512)
 

@@ -531,3 +531,26 @@ def test_cuda_graph_capture():
   a, c = _flat(q1, i1), _flat(q2, i2)
   for k in a:
     np.testing.assert_array_equal(a[k], c[k], err_msg=k)
+
+
+def test_three_tiles_per_sm_build_parity():
+  """Batches of more than four tiles per SM run the (320, 3) build of small systems (64
+  registers, three tiles per SM): same parity policy on a 1024-env slice of a 24576-env step,
+  and agreement to rounding with the two-tile build on the same envs."""
+  torch = _torch()
+  from brax_b200.system import QP
+  s = _system('ant')
+  b = 24576
+  qp, rng = _harvest(s, b, 10, 31)
+  act = rng.uniform(-1, 1, (b, s.act_size)).astype(np.float32)
+  qo, info = s.step(qp, torch.from_numpy(act).cuda())
+  torch.cuda.synchronize()
+  sl = slice(4096, 5120)
+  got = {k: v[sl] for k, v in _flat(qo, info).items()}
+  ins = [getattr(qp, k)[sl].cpu().numpy() for k in util.QP_KEYS]
+  check_step('ant', ins, act[sl], got)
+  small = QP(*[getattr(qp, k)[sl].contiguous() for k in util.QP_KEYS])   # 32 tiles: the two-tile build
+  q2, i2 = s.step(small, torch.from_numpy(act[sl]).cuda())
+  a2 = _flat(q2, i2)
+  for k in ('pos', 'rot'):
+    np.testing.assert_allclose(got[k], a2[k], rtol=1e-4, atol=1e-5, err_msg=k)
