@@ -37,6 +37,16 @@ SYSTEMS = {
     'inverted_pendulum': ('inverted_pendulum', '_SYSTEM_CONFIG', 4, 1),
     'reacherangle': ('reacherangle', '_SYSTEM_CONFIG', 4, 1),
     'humanoid_standup': ('humanoid_standup', '_SYSTEM_CONFIG', 4, 1),
+    # the remaining reference envs (every env of brax/envs with a v1 system is covered)
+    'walker2d': ('walker2d', '_SYSTEM_CONFIG', 4, 1),
+    'pusher': ('pusher', '_SYSTEM_CONFIG', 4, 1),
+    'ur5e': ('ur5e', '_SYSTEM_CONFIG', 4, 1),
+    'acrobot': ('acrobot', '_SYSTEM_CONFIG', 4, 1),
+    'reacher': ('reacher', '_SYSTEM_CONFIG', 4, 1),
+    'inverted_double_pendulum': ('inverted_double_pendulum', '_SYSTEM_CONFIG', 4, 1),
+    'fetch_spring': ('fetch', '_SYSTEM_CONFIG_SPRING', 4, 1),
+    'walker2d_spring': ('walker2d', '_SYSTEM_CONFIG_SPRING', 4, 1),
+    'ur5e_spring': ('ur5e', '_SYSTEM_CONFIG_SPRING', 4, 1),
 }
 EXTRA_ACT = {'grasp': 3}
 
