@@ -90,3 +90,24 @@ def test_obs_sizes():
   assert VARIANTS['humanoid_spring'][1].obs_size(util.load_desc('humanoid_spring')) == 227
   assert VARIANTS['fetch'][1].obs_size(util.load_desc('fetch')) == 101
   assert VARIANTS['grasp'][1].obs_size(util.load_desc('grasp')) == 132
+
+
+def test_wrapper_oracle_matches_reference():
+  """EpisodeWrapper + AutoResetWrapper (wrappers.py:85-148), the reference's own classes run
+  around its Ant (oracle/gen_golden_wrappers.py): the oracle's wrapped step reproduces every
+  stored step -- done by the healthy range, truncation at episode_length, the step counter
+  reset after a done, state and obs replaced by first_qp / first_obs."""
+  g = np.load(os.path.join(util.GOLDEN, 'ant_wrapped_env.npz'))
+  desc, env = util.load_desc('ant'), VARIANTS['ant'][1]
+  o = Oracle(desc, np.float64)
+  assert g['done'].sum() >= 3 and g['truncation'].sum() >= 2 and (g['done'] > g['truncation']).any()
+  nseq, t_n = g['done'].shape
+  for t in range(t_n):
+    qp = {k: g[k][:, t] for k in util.QP_KEYS}
+    first = {k: g['first_' + k] for k in util.QP_KEYS}
+    r = env_oracle.wrapped_step(desc, env, o, qp, g['done_in'][:, t], g['steps_in'][:, t], g['act'][:, t], first,
+                                g['first_obs'], int(g['episode_length']), np.float64)
+    for k in util.QP_KEYS:
+      np.testing.assert_allclose(r['qp'][k], g[k + '_o'][:, t], rtol=0, atol=1e-9, err_msg='%s step %d' % (k, t))
+    for k in ('obs', 'reward', 'done', 'steps', 'truncation', 'metrics'):
+      np.testing.assert_allclose(r[k], g[k][:, t], rtol=0, atol=1e-9, err_msg='%s step %d' % (k, t))
