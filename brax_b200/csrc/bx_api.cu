@@ -6,6 +6,7 @@
 // is one kernel launch on the caller's stream: no allocation, no host sync.
 // There is no CPU fallback: without a CUDA device every call fails loudly.
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -140,7 +141,7 @@ static int validate(const bx_system_desc* d) {
 }
 
 // The outputs of bx_step_io in segment order (pos_o is the first of BX_SEG_OUT pointers).
-static_assert(sizeof(bx_step_io) == (BX_SEG_IN + BX_SEG_OUT + 1) * sizeof(void*), "bx_step_io vs segments");
+static_assert(offsetof(bx_step_io, env_rand) == (BX_SEG_IN + BX_SEG_OUT) * sizeof(void*), "bx_step_io vs segments");
 static float* const* io_outs(const bx_step_io* io) { return &io->pos_o; }
 static float** io_outs(bx_step_io* io) { return &io->pos_o; }
 
@@ -816,6 +817,18 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   if (io->env_rand && s->h.env_kind != BX_ENV_FETCH && s->h.env_kind != BX_ENV_GRASP)
     return fail("env_rand is the target teleport of the fetch / grasp epilogues");
   p.env_rand = io->env_rand;
+  p.first[0] = io->first_pos; p.first[1] = io->first_rot; p.first[2] = io->first_vel; p.first[3] = io->first_ang;
+  p.first_obs = io->first_obs;
+  p.done_in = io->done_in; p.steps_in = io->steps_in;
+  p.steps_out = io->steps_out; p.truncation = io->truncation;
+  p.episode_length = io->episode_length;
+  if (io->first_pos) {
+    if (!s->h.env_kind) return fail("auto-reset needs a system created with desc.env");
+    if (!io->first_rot || !io->first_vel || !io->first_ang || !io->done_in)
+      return fail("auto-reset needs first_pos/rot/vel/ang and done_in");
+    if (!io->done) return fail("auto-reset needs the done output");
+    if (io->obs && !io->first_obs) return fail("auto-reset with an obs output needs first_obs");
+  }
   p.num_envs = num_envs;
   p.num_steps = num_steps;
   p.stagger_ns = stagger_ns;
@@ -904,6 +917,7 @@ extern "C" int bx_system_threads(const bx_system* s) { return s ? 32 * s->warps 
 extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
   if (!s || !hio) return fail("NULL argument");
   if (B <= 0) return fail("num_envs must be positive");
+  if (hio->first_pos) return fail("auto-reset inputs are supported on the device path only (bx_step / bx_rollout)");
   if (!hio->pos || !hio->rot || !hio->vel || !hio->ang || !hio->act || !hio->pos_o || !hio->rot_o ||
       !hio->vel_o || !hio->ang_o)
     return fail("QP / act pointers must not be NULL");

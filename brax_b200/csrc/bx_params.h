@@ -15,6 +15,14 @@ struct BxKernelParams {
   const float* in[BX_SEG_IN];  // pos rot vel ang act
   float* out[BX_SEG_OUT];      // order of bx_step_io's outputs
   const float* env_rand;       // fetch / grasp: [T,B,3] uniforms of the target teleport, or NULL
+  // auto-reset (EpisodeWrapper + AutoResetWrapper, wrappers.py:105-148); first[0] NULL = off
+  const float* first[4];       // first_qp: pos rot vel ang
+  const float* first_obs;
+  const float* done_in;
+  const float* steps_in;
+  float* steps_out;
+  float* truncation;
+  float episode_length;
   int64_t num_envs;
   int32_t num_steps;  // >1: rollout, act is [T,B,A]
   // host path only (bx_step_host on mapped host memory): tile i starts i/grid of

@@ -1598,6 +1598,14 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
 
   const bool env_on = (BX_FEAT & BXF_ENV) != 0 && h.env_kind != BX_ENV_NONE && (p.out[BX_SEG_ENV] != nullptr || p.out[BX_SEG_ENV + 1] != nullptr ||
                                                     p.out[BX_SEG_ENV + 2] != nullptr || p.out[BX_SEG_ENV + 3] != nullptr);
+  // auto-reset (EpisodeWrapper + AutoResetWrapper around the env epilogue, wrappers.py:105-148):
+  // the step counter and the previous done flag of env `lane` live in registers of the last warp
+  const bool auto_reset = env_on && p.first[0] != nullptr;
+  float ep_steps = 0.f, ep_prev_done = 0.f;
+  if (auto_reset && c.warp == c.nwarp - 1 && (threadIdx.x & 31) < nenv) {
+    ep_prev_done = p.done_in[env0 + (threadIdx.x & 31)];
+    if (p.steps_in != nullptr) ep_steps = p.steps_in[env0 + (threadIdx.x & 31)];
+  }
   for (int step = 0; step < p.num_steps; step++) {
     __syncthreads();
     if (step > 0) {  // rollout: the actions of step t (step 0 came with the state)
@@ -1692,6 +1700,42 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
         phase_env_ego<MODE>(c, h, p.env_rand == nullptr ? nullptr
                             : p.env_rand + 3 * (static_cast<int64_t>(step) * p.num_envs + env0), nenv);
       }
+      if (auto_reset) {
+        const int lane = threadIdx.x & 31;
+        if (c.warp == c.nwarp - 1) {
+          // EpisodeWrapper.step / AutoResetWrapper.step bookkeeping of env `lane` (the same warp
+          // wrote the scalars row in phase_env*)
+          float4 s0 = QROW(c, h.q_env + EQ_S0);
+          ep_steps = ep_prev_done > 0.f ? 0.f : ep_steps;             // wrappers.py:133-135
+          ep_steps += 1.f;                                            // wrappers.py:112
+          const bool over = p.episode_length > 0.f && ep_steps >= p.episode_length;
+          const float trunc = over ? 1.f - s0.y : 0.f;                // wrappers.py:117-118
+          s0.y = over ? 1.f : s0.y;                                   // wrappers.py:116
+          ep_prev_done = s0.y;
+          QROW(c, h.q_env + EQ_S0) = s0;
+          if (p.truncation != nullptr && lane < nenv)
+            p.truncation[static_cast<int64_t>(step) * p.num_envs + env0 + lane] = trunc;
+        }
+        __syncthreads();
+        // qp = where(done, first_qp, qp) (wrappers.py:146): done envs reload their first state
+        const bool done = lane < nenv && QROW(c, h.q_env + EQ_S0).y > 0.f;
+        if (__any_sync(0xffffffffu, done)) {
+          typedef Lay<MODE> L;
+          const int po = MODE == BX_MODE_PBD ? 2 * c.cur : 0;
+          const int64_t e = env0 + lane;
+          for (int b = c.warp; b < h.nb; b += c.nwarp) {
+            if (!done) continue;
+            const float* fp = p.first[0] + (e * h.nb + b) * 3;
+            const float* fr = p.first[1] + (e * h.nb + b) * 4;
+            const float* fv = p.first[2] + (e * h.nb + b) * 3;
+            const float* fa = p.first[3] + (e * h.nb + b) * 3;
+            QROW(c, L::BQ * b + po) = make_float4(fp[0], fp[1], fp[2], 0.f);
+            QROW(c, L::BQ * b + po + 1) = make_float4(fr[0], fr[1], fr[2], fr[3]);
+            QROW(c, L::BQ * b + L::VEL) = make_float4(fv[0], fv[1], fv[2], 0.f);
+            QROW(c, L::BQ * b + L::ANG) = make_float4(fa[0], fa[1], fa[2], 0.f);
+          }
+        }
+      }
       __syncthreads();
       auto env_ptr = [&](int s) -> float* {
         return p.out[s] == nullptr ? nullptr
@@ -1716,8 +1760,21 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
           if (p.out[s] != nullptr)
             io_segment_scalar<false>(smf, ti, h.seg_out[s], env_ptr(s), env0, nenv);
       }
+      if (auto_reset && p.out[BX_SEG_ENV] != nullptr) {
+        // obs = where(done, first_obs, obs) (wrappers.py:147): after this tile's obs store
+        __syncthreads();
+        const int no = h.seg_out[BX_SEG_ENV].nper;
+        float* obs = env_ptr(BX_SEG_ENV);
+        for (int e = 0; e < nenv; e++) {
+          if (!(sq[(h.q_env + EQ_S0) * QS + e].y > 0.f)) continue;
+          const int64_t off = (env0 + e) * no;
+          for (int i = threadIdx.x; i < no; i += blockDim.x) obs[off + i] = p.first_obs[off + i];
+        }
+      }
     }
   }
+  if (auto_reset && p.steps_out != nullptr && c.warp == c.nwarp - 1 && (threadIdx.x & 31) < nenv)
+    p.steps_out[env0 + (threadIdx.x & 31)] = ep_steps;
   __syncthreads();
   if (!env_on && (p.out[13] != nullptr || p.out[14] != nullptr)) {
     phase_angle_vel<MODE>(c, h);

@@ -20,7 +20,7 @@ from typing import Any, Dict, List
 
 import numpy as np
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 MODE = {'pbd': 0, 'legacy_spring': 1}
 JOINT_KIND = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
@@ -89,7 +89,9 @@ class CStepIO(C.Structure):
       'pos', 'rot', 'vel', 'ang', 'act', 'pos_o', 'rot_o', 'vel_o', 'ang_o',
       'contact_vel', 'contact_ang', 'joint_vel', 'joint_ang', 'actuator_vel',
       'actuator_ang', 'contact_pos', 'contact_normal', 'contact_penetration',
-      'joint_angle', 'joint_velocity', 'obs', 'reward', 'done', 'metrics', 'env_rand')]
+      'joint_angle', 'joint_velocity', 'obs', 'reward', 'done', 'metrics', 'env_rand',
+      'first_pos', 'first_rot', 'first_vel', 'first_ang', 'first_obs', 'done_in', 'steps_in',
+      'steps_out', 'truncation')] + [('episode_length', C.c_float)]
 
 
 def _f(x):

@@ -208,11 +208,15 @@ class Env:
 
   def step(self, state: State, action) -> State:
     """`Env.step(state, action)` (ant.py:222, humanoid.py:246): one kernel launch."""
-    qp, info, eo = self.sys.step(state.qp, action, env=True)
+    return self._launch(state, action)
+
+  def _launch(self, state: State, action, rand=None, auto_reset=None) -> State:
+    qp, info, eo = self.sys.step(state.qp, action, env=True, env_rand=rand, auto_reset=auto_reset)
     names = self.env.metric_names()
     metrics = dict(state.metrics)
     metrics.update({k: eo['metrics'][..., i] for i, k in enumerate(names)})
-    return State(qp, eo['obs'], eo['reward'], eo['done'], metrics, dict(state.info, physics=info))
+    extra = {k: eo[k] for k in ('steps', 'truncation') if k in eo}
+    return State(qp, eo['obs'], eo['reward'], eo['done'], metrics, dict(state.info, physics=info, **extra))
 
 
 class Ant(Env):
@@ -264,13 +268,12 @@ class _TargetEnv(Env):
     return self._np_rng.uniform(size=tuple(lead) + (3,)).astype(np.float32)
 
   def step(self, state: State, action, rand=None) -> State:
+    return self._launch(state, action, rand)
+
+  def _launch(self, state: State, action, rand=None, auto_reset=None) -> State:
     if rand is None:
       rand = self._uniform(state.qp.pos, state.qp.pos.shape[:-2])
-    qp, info, eo = self.sys.step(state.qp, action, env=True, env_rand=rand)
-    names = self.env.metric_names()
-    metrics = dict(state.metrics)
-    metrics.update({k: eo['metrics'][..., i] for i, k in enumerate(names)})
-    return State(qp, eo['obs'], eo['reward'], eo['done'], metrics, dict(state.info, physics=info))
+    return super()._launch(state, action, rand, auto_reset)
 
 
 class Fetch(_TargetEnv):
@@ -289,14 +292,69 @@ class Grasp(_TargetEnv):
     super().__init__('grasp', grasp_desc, device, seed)
 
 
+class EpisodeAutoReset:
+  """`AutoResetWrapper(EpisodeWrapper(env, episode_length, 1))` (brax/envs/wrappers.py:95-148,
+  stacked as in brax/envs/__init__.py:84-89) with both wrappers' `step` evaluated inside the env's
+  single kernel launch (`bx_step_io.first_* / done_in / steps_in / episode_length`): episode
+  counter, truncation, done at the episode limit, and the reload of (qp, obs) from the first
+  state where done.  torch CUDA states only.  episode_length None / 0: AutoResetWrapper alone."""
+
+  def __init__(self, env: Env, episode_length: int = 1000):
+    self.env = env
+    self.sys = env.sys
+    self.episode_length = int(episode_length or 0)
+    self.observation_size = env.observation_size
+    self.action_size = env.action_size
+
+  def reset(self, *args, first_obs=None, **kw) -> State:
+    """As `env.reset`, plus info['steps'], info['truncation'] (wrappers.py:98-103) and
+    info['first_qp'], info['first_obs'] (wrappers.py:126-129).  The obs of the first state is the
+    caller's (`first_obs=`; reset / `_get_obs(default_qp)` is row N3) -- zeros if not given."""
+    st = self.env.reset(*args, **kw)
+    if not _system._is_torch(st.qp.pos):
+      raise ValueError('EpisodeAutoReset needs torch CUDA states: reset(batch, device=...)')
+    import torch
+    if first_obs is not None:
+      st = st.replace(obs=torch.as_tensor(first_obs, dtype=torch.float32, device=st.obs.device).expand_as(st.obs).contiguous())
+    st.info.update(steps=torch.zeros_like(st.done), truncation=torch.zeros_like(st.done),
+                   first_qp=st.qp, first_obs=st.obs)
+    return st
+
+  def step(self, state: State, action, rand=None) -> State:
+    ar = _system.AutoReset(state.info['first_qp'], state.info['first_obs'], state.done,
+                           state.info.get('steps'), self.episode_length)
+    return self.env._launch(state, action, rand, ar)
+
+  def rollout(self, state: State, actions, rand=None):
+    """T wrapped steps in ONE launch (the scan over `step` of a training / eval unroll).  Returns
+    the final state and a dict of the per-step obs / reward / done / truncation / metrics."""
+    ar = _system.AutoReset(state.info['first_qp'], state.info['first_obs'], state.done,
+                           state.info.get('steps'), self.episode_length)
+    if rand is None and isinstance(self.env, _TargetEnv):
+      rand = self.env._uniform(state.qp.pos, (int(actions.shape[0]),) + tuple(state.qp.pos.shape[:-2]))
+    qp, info, eo = self.sys.rollout(state.qp, actions, env=True, env_rand=rand, auto_reset=ar)
+    names = self.env.env.metric_names()
+    metrics = {k: eo['metrics'][-1, ..., i] for i, k in enumerate(names)}
+    last = State(qp, eo['obs'][-1], eo['reward'][-1], eo['done'][-1], metrics,
+                 dict(state.info, physics=info, steps=eo['steps'], truncation=eo['truncation'][-1]))
+    return last, eo
+
+
 _ENVS = {'ant': Ant, 'humanoid': Humanoid, 'fetch': Fetch, 'grasp': Grasp}
 
 
-def create(env_name: str, **kwargs) -> Env:
-  """`envs.create(name)` for the mirrored envs.  'ant' is registered with
-  use_contact_forces=True as in this fork (brax/envs/__init__.py:45)."""
+def create(env_name: str, episode_length: int = None, auto_reset: bool = False, **kwargs):
+  """`envs.create(name, episode_length, auto_reset=...)` (brax/envs/__init__.py:74-90) for the
+  mirrored envs.  'ant' is registered with use_contact_forces=True as in this fork
+  (brax/envs/__init__.py:45).  Unlike the reference the wrappers are opt-in (defaults: the bare
+  env); with auto_reset=True the result is `EpisodeAutoReset(env, episode_length)`."""
   if env_name not in _ENVS:
     raise KeyError('env %r has no fused epilogue (available: %s)' % (env_name, sorted(_ENVS)))
   if env_name == 'ant':
     kwargs.setdefault('use_contact_forces', True)
-  return _ENVS[env_name](**kwargs)
+  env = _ENVS[env_name](**kwargs)
+  if auto_reset:
+    return EpisodeAutoReset(env, episode_length)
+  if episode_length:
+    raise ValueError('episode_length without auto_reset is not fused: wrap the env yourself')
+  return env

@@ -72,6 +72,17 @@ class JointState:
   vel: Any
 
 
+@dataclasses.dataclass
+class AutoReset:
+  """What EpisodeWrapper / AutoResetWrapper keep in `state` (envs/wrappers.py:95-148), handed to
+  `System.step(..., env=True, auto_reset=...)` so that both wrappers run inside the launch."""
+  first_qp: 'QP'            # state.info['first_qp'] [B,N,*]
+  first_obs: Any            # state.info['first_obs'] [B,O]
+  done: Any                 # state.done of the state passed in [B]
+  steps: Any = None         # state.info['steps'] [B] (None: zeros)
+  episode_length: int = 0   # EpisodeWrapper.episode_length; 0 = no EpisodeWrapper
+
+
 class HostBuffers:
   """Page-locked host arrays for the host path of `System.step` (bx_host_alloc).
 
@@ -221,7 +232,7 @@ class System:
 
   # ---- the step ---------------------------------------------------------------
   def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False, env: bool = False,
-           env_rand=None):
+           env_rand=None, auto_reset: 'AutoReset' = None):
     """`System.step(qp, act) -> (qp, info)` (system.py:244-247).
 
     out: optional `HostBuffers` (host path only): results are written into its
@@ -231,11 +242,18 @@ class System:
     asks for right after the step (envs/ant.py:259, envs/humanoid.py:285).
     env: (systems built with an EnvDesc) also return, last, a dict with what the
     reference's `Env.step` computes after `sys.step` -- obs [B,O], reward [B],
-    done [B], metrics [B,M] (envs/ant.py:222-281, envs/humanoid.py:246-340)."""
+    done [B], metrics [B,M] (envs/ant.py:222-281, envs/humanoid.py:246-340).
+    auto_reset: (with env=True, torch path) an `AutoReset`: EpisodeWrapper.step and
+    AutoResetWrapper.step (envs/wrappers.py:105-148) applied inside the launch; the env
+    dict gains 'steps' and 'truncation' and qp / obs / done are the wrapped ones."""
     if env and self.env is None:
       raise ValueError('this System was built without an EnvDesc')
+    if auto_reset is not None and not env:
+      raise ValueError('auto_reset needs env=True')
     if _is_torch(qp.pos):
-      return self._step_torch(qp, act, 1, angle_vel, env, env_rand)
+      return self._step_torch(qp, act, 1, angle_vel, env, env_rand, auto_reset)
+    if auto_reset is not None:
+      raise ValueError('auto_reset is supported with torch CUDA tensors only')
     return self._step_numpy(qp, act, out, angle_vel, env, env_rand)
 
   def angle_vel_groups(self, js: JointState):
@@ -264,14 +282,17 @@ class System:
     self._lib.bx_host_transfer_bytes(self._h, batch, C.byref(h2d), C.byref(d2h))
     return int(h2d.value), int(d2h.value)
 
-  def rollout(self, qp: QP, acts, env: bool = False, env_rand=None):
+  def rollout(self, qp: QP, acts, env: bool = False, env_rand=None, auto_reset: 'AutoReset' = None):
     """T steps in ONE launch; acts is [T, B, A] (torch CUDA).  Returns the final
     QP and the Info of the last step (lax.scan of System.step over actions); with
     env=True also the env epilogue of EVERY step: obs [T,B,O], reward / done [T,B],
-    metrics [T,B,M]."""
+    metrics [T,B,M]; with auto_reset (see `step`) episodes end and restart inside the
+    launch: 'truncation' is [T,B], 'steps' [B] the counters after the last step."""
     if env and self.env is None:
       raise ValueError('this System was built without an EnvDesc')
-    return self._step_torch(qp, acts, int(acts.shape[0]), False, env, env_rand)
+    if auto_reset is not None and not env:
+      raise ValueError('auto_reset needs env=True')
+    return self._step_torch(qp, acts, int(acts.shape[0]), False, env, env_rand, auto_reset)
 
   def _shapes(self, pos_shape):
     n = self.num_bodies
@@ -298,9 +319,9 @@ class System:
   def _wrap(self, out, batched, steps=1):
     env_out = None
     if 'obs' in out:
-      env_out = {k: out.pop(k) for k in ('obs', 'reward', 'done', 'metrics')}
+      env_out = {k: out.pop(k) for k in ('obs', 'reward', 'done', 'metrics', 'steps', 'truncation') if k in out}
       if not batched:
-        env_out = {k: (v[:, 0] if steps > 1 else v[0]) for k, v in env_out.items()}
+        env_out = {k: (v[:, 0] if steps > 1 and v.ndim > 1 and k != 'steps' else v[0]) for k, v in env_out.items()}
     if not batched:
       out = {k: v[0] for k, v in out.items()}
     qp = QP(out['pos_o'], out['rot_o'], out['vel_o'], out['ang_o'])
@@ -335,8 +356,12 @@ class System:
     io.joint_angle = io.joint_velocity = None
     io.obs = io.reward = io.done = io.metrics = None
     io.env_rand = None
+    io.first_pos = io.first_rot = io.first_vel = io.first_ang = io.first_obs = None
+    io.done_in = io.steps_in = io.steps_out = io.truncation = None
+    io.episode_length = 0.0
 
-  def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False, env_rand=None):
+  def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False, env_rand=None,
+                  auto_reset=None):
     """env_rand: (fetch / grasp) uniforms of the target teleport, [B,3] or [T,B,3]."""
     import torch
     batched, b = self._shapes(qp.pos.shape)
@@ -376,6 +401,19 @@ class System:
     if env_rand is not None:
       env_rand = prep(env_rand, steps * b * 3)
       io.env_rand = env_rand.data_ptr()
+    if auto_reset is not None:
+      ar = auto_reset
+      keep = (prep(ar.first_qp.pos, b * n * 3), prep(ar.first_qp.rot, b * n * 4), prep(ar.first_qp.vel, b * n * 3),
+              prep(ar.first_qp.ang, b * n * 3), prep(ar.first_obs, b * self.obs_size), prep(ar.done, b),
+              None if ar.steps is None else prep(ar.steps, b))
+      io.first_pos, io.first_rot, io.first_vel, io.first_ang, io.first_obs, io.done_in = [t.data_ptr() for t in keep[:6]]
+      io.steps_in = None if keep[6] is None else keep[6].data_ptr()
+      extra = torch.empty((steps + 1) * b, dtype=f32, device=dev)
+      out['steps'] = extra[:b].view((b,))
+      out['truncation'] = extra[b:].view((steps, b) if steps > 1 else (b,))
+      io.steps_out = extra.data_ptr()
+      io.truncation = extra.data_ptr() + 4 * b
+      io.episode_length = float(ar.episode_length or 0)
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     if self.autotune and steps == 1 and b >= 1024 and b not in self._tuned:
       # first call at this batch size: time the candidate CTA sizes once

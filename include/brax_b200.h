@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BX_ABI_VERSION 5
+#define BX_ABI_VERSION 6
 
 /* dynamics_mode (base.py:179-201) */
 #define BX_MODE_PBD 0
@@ -239,6 +239,23 @@ typedef struct bx_step_io {
    * target of every env that scored a hit (fetch.py:88-93, grasp.py:131-136) in the QP it
    * returns; NULL leaves the targets where they are (the caller teleports). */
   const float* env_rand;
+  /* Optional auto-reset of the env epilogue (device path; first_pos NULL = off): what
+   * `envs.create(name, episode_length, auto_reset=True)` wraps around Env.step
+   * (brax/envs/__init__.py:74-90): EpisodeWrapper.step (wrappers.py:105-120, action_repeat 1) and
+   * AutoResetWrapper.step (wrappers.py:131-148), evaluated per env inside the launch:
+   *   steps = done_in ? 0 : steps_in;  <Env.step>;  steps += 1;
+   *   over = episode_length > 0 && steps >= episode_length;
+   *   truncation = over ? 1 - done : 0;  done = over ? 1 : done;
+   *   done ? (qp, obs) = (first_qp, first_obs)
+   * The QP / obs / done the launch returns are the wrapped ones; in a rollout the chain
+   * (done, steps) -> next step stays inside the kernel and truncation is [T,B]. */
+  const float *first_pos, *first_rot, *first_vel, *first_ang; /* state.info['first_qp'] [B,N,3|4|3|3] */
+  const float* first_obs; /* state.info['first_obs'] [B,O] */
+  const float* done_in;   /* state.done of the state passed in [B] */
+  const float* steps_in;  /* state.info['steps'] [B] (NULL: zeros) */
+  float* steps_out;       /* [B] */
+  float* truncation;      /* state.info['truncation'] [B] ([T,B] in a rollout) */
+  float episode_length;   /* EpisodeWrapper.episode_length; 0 = no episode limit */
 } bx_step_io;
 
 /* Creates a system on CUDA device `device` (tables uploaded once).  Returns 0

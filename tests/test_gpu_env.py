@@ -318,3 +318,161 @@ def test_1000_step_statistics(variant, b):
   close('torso_z', g_z, o_z)
   close('unhealthy', g_done, o_done)
   close('kinetic_energy', np.stack(g_e), np.stack(o_e))
+
+
+def _auto_reset_case(variant, b, seed, episode_length):
+  """Harvested states, a share of them lifted out of the healthy range (ant / humanoid: done),
+  random step counters / done flags, per-env first states and first obs."""
+  torch = _torch()
+  from brax_b200.system import QP, AutoReset
+  sysname, env = _env(variant)
+  qp, rng = _harvest(env.sys, b, 12, seed)
+  pos = qp.pos.clone()
+  pos[: b // 5, :, 2] += 1.5                                   # unhealthy: above healthy_z_range
+  qp = QP(pos, qp.rot, qp.vel, qp.ang)
+  first, _ = _harvest(env.sys, b, 2, seed + 1)
+  first_obs = torch.from_numpy(rng.normal(size=(b, env.observation_size)).astype(np.float32)).cuda()
+  done_in = torch.from_numpy((rng.uniform(size=b) < 0.2).astype(np.float32)).cuda()
+  steps_in = torch.from_numpy(rng.integers(0, episode_length, b).astype(np.float32)).cuda()
+  return sysname, env, qp, rng, AutoReset(first, first_obs, done_in, steps_in, episode_length)
+
+
+@pytest.mark.parametrize('variant', ['ant', 'humanoid_spring', 'fetch'])
+def test_auto_reset_matches_oracle(variant):
+  """EpisodeWrapper + AutoResetWrapper inside the launch (wrappers.py:105-148) against the
+  oracle's wrapped step (pinned to the reference's wrapper classes, test_env_oracle) on the
+  same inputs: step counter, truncation and done exact; reset envs carry first_qp / first_obs
+  bit for bit; the others stay within the env tolerance."""
+  torch = _torch()
+  from oracle import env_oracle
+  from oracle.oracle import Oracle
+  b, length = 700, 3
+  sysname, env, qp, rng, ar = _auto_reset_case(variant, b, 11, length)
+  act = rng.uniform(-1, 1, (b, env.action_size)).astype(np.float32)
+  kw, rand = {}, None
+  if env.env.kind == 'fetch':
+    pos = qp.pos.clone()
+    pos[::3, env.env.target_body] = pos[::3, env.env.ref_body] + 0.3      # some hits -> teleports
+    qp = type(qp)(pos, qp.rot, qp.vel, qp.ang)
+    rand = rng.uniform(0, 1, (b, 3)).astype(np.float32)
+    kw = dict(env_rand=torch.from_numpy(rand).cuda())
+  q2, _, eo = env.sys.step(qp, torch.from_numpy(act).cuda(), env=True, auto_reset=ar, **kw)
+  torch.cuda.synchronize()
+  got = {k: v.cpu().numpy() for k, v in eo.items()}
+  desc = util.load_desc(sysname)
+  ins = {k: getattr(qp, k).cpu().numpy() for k in util.QP_KEYS}
+  first = {k: getattr(ar.first_qp, k).cpu().numpy() for k in util.QP_KEYS}
+  want = env_oracle.wrapped_step(desc, env.env, Oracle(desc, np.float32), ins, ar.done.cpu().numpy(),
+                                 ar.steps.cpu().numpy(), act, first, ar.first_obs.cpu().numpy(), length,
+                                 np.float32, rand)
+  np.testing.assert_array_equal(got['steps'], want['steps'])
+  over = want['steps'] >= length
+  assert over.any() and (~over).any()
+  # the env's own done, recovered from the wrapped outputs, goes through the env check below
+  inner_done = np.where(over, 1 - got['truncation'], got['done'])
+  np.testing.assert_array_equal(got['done'], np.where(over, 1, inner_done))
+  np.testing.assert_array_equal(got['truncation'], np.where(over, 1 - inner_done, 0))
+  d = got['done'] > 0
+  assert 0.2 < d.mean() < 0.9
+  if env.env.kind != 'fetch':
+    assert (d & ~over).any()                                  # done by the healthy range
+  for k in util.QP_KEYS:                                      # wrappers.py:146
+    np.testing.assert_array_equal(getattr(q2, k).cpu().numpy()[d], first[k][d], err_msg=k)
+  np.testing.assert_array_equal(got['obs'][d], ar.first_obs.cpu().numpy()[d])   # wrappers.py:147
+  inner = _oracle_chain(sysname, env.env, [ins[k] for k in util.QP_KEYS], act, np.float32)
+  obs = np.where(d[:, None], inner['obs'], got['obs'])
+  check_env(sysname, env.env, [ins[k] for k in util.QP_KEYS], act,
+            dict(obs=obs, reward=got['reward'], done=inner_done, metrics=got['metrics']))
+  keep = ~d
+  for k in util.QP_KEYS:
+    w = want['qp'][k][keep]
+    if env.env.kind == 'fetch' and k == 'pos':               # teleported targets: checked elsewhere
+      w, g = np.delete(w, env.env.target_body, 1), np.delete(getattr(q2, k).cpu().numpy()[keep], env.env.target_body, 1)
+    else:
+      g = getattr(q2, k).cpu().numpy()[keep]
+    frac = (np.abs(g - w) > 1e-4 + 1e-3 * np.abs(w)).reshape(len(w), -1).any(1).mean()
+    assert frac <= OUTLIER_FRAC, (k, frac)
+
+
+@pytest.mark.parametrize('variant', ['ant', 'humanoid', 'grasp', 'fetch_spring'])
+def test_auto_reset_rollout_equals_repeated_steps(variant):
+  """The (done, steps) chain of a rollout stays inside the kernel: T wrapped steps in one launch
+  are bit-identical to T single wrapped launches fed with each other's done / steps."""
+  torch = _torch()
+  import dataclasses
+  b, t_n, length = 300, 7, 3
+  _, env, qp, rng, ar = _auto_reset_case(variant, b, 5, length)
+  acts = torch.from_numpy(rng.uniform(-1, 1, (t_n, b, env.action_size)).astype(np.float32)).cuda()
+  kw = lambda t: {}  # noqa: E731
+  rand = None
+  if env.env.kind in ('fetch', 'grasp'):
+    rand = torch.from_numpy(rng.uniform(0, 1, (t_n, b, 3)).astype(np.float32)).cuda()
+    kw = lambda t: dict(env_rand=rand[t])  # noqa: E731
+  cur, a, seq = qp, ar, []
+  for t in range(t_n):
+    cur, _, eo = env.sys.step(cur, acts[t], env=True, auto_reset=a, **kw(t))
+    seq.append(eo)
+    a = dataclasses.replace(a, done=eo['done'], steps=eo['steps'])
+  q2, _, er = env.sys.rollout(qp, acts, env=True, auto_reset=ar, env_rand=rand)
+  torch.cuda.synchronize()
+  for k in util.QP_KEYS:
+    assert torch.equal(getattr(q2, k), getattr(cur, k)), k
+  for k in ('obs', 'reward', 'done', 'metrics', 'truncation'):
+    assert torch.equal(er[k], torch.stack([s[k] for s in seq])), k
+  assert torch.equal(er['steps'], seq[-1]['steps'])
+  done = er['done'].cpu().numpy()
+  assert done[1:].any() and er['truncation'].any() and float(er['steps'].max()) <= length
+
+
+def test_auto_reset_on_reference_sequences():
+  """tests/golden/ant_wrapped_env.npz (the reference's AutoResetWrapper(EpisodeWrapper(Ant)),
+  oracle/gen_golden_wrappers.py): each stored step through one wrapped launch, and each whole
+  sequence through the wrapper mirror `envs.create('ant', episode_length, auto_reset=True)`."""
+  torch = _torch()
+  from brax_b200 import envs
+  from brax_b200.system import QP, AutoReset
+  g = np.load(os.path.join(util.GOLDEN, 'ant_wrapped_env.npz'))
+  length = int(g['episode_length'])
+  env = envs.create('ant', episode_length=length, auto_reset=True)
+  assert isinstance(env, envs.EpisodeAutoReset)
+  cu = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).cuda()  # noqa: E731
+  first = QP(*[cu(g['first_' + k]) for k in util.QP_KEYS])
+  nseq, t_n = g['done'].shape
+  for t in range(t_n):
+    ar = AutoReset(first, cu(g['first_obs']), cu(g['done_in'][:, t]), cu(g['steps_in'][:, t]), length)
+    q2, _, eo = env.sys.step(QP(*[cu(g[k][:, t]) for k in util.QP_KEYS]), cu(g['act'][:, t]), env=True, auto_reset=ar)
+    for k in ('done', 'steps', 'truncation'):
+      np.testing.assert_array_equal(eo[k].cpu().numpy(), g[k][:, t], err_msg='%s step %d' % (k, t))
+    np.testing.assert_allclose(eo['obs'].cpu().numpy(), g['obs'][:, t], rtol=1e-3, atol=2e-3)
+    np.testing.assert_allclose(eo['reward'].cpu().numpy(), g['reward'][:, t], rtol=1e-3, atol=2e-3)
+    for k in util.QP_KEYS:
+      np.testing.assert_allclose(getattr(q2, k).cpu().numpy(), g[k + '_o'][:, t], rtol=1e-3, atol=2e-3, err_msg=k)
+  # the chained sequence through the wrapper mirror (reset -> state.info, then step / rollout)
+  st = envs.State(QP(*[cu(g[k][:, 0]) for k in util.QP_KEYS]), cu(g['first_obs']), cu(np.zeros(nseq)),
+                  cu(g['done_in'][:, 0]), {}, dict(first_qp=first, first_obs=cu(g['first_obs']), steps=cu(g['steps_in'][:, 0])))
+  last, eo = env.rollout(st, cu(np.swapaxes(g['act'], 0, 1)))
+  for k in ('done', 'truncation'):
+    np.testing.assert_array_equal(eo[k].cpu().numpy().T, g[k], err_msg=k)
+  np.testing.assert_array_equal(last.info['steps'].cpu().numpy(), g['steps'][:, -1])
+  np.testing.assert_allclose(np.swapaxes(eo['obs'].cpu().numpy(), 0, 1), g['obs'], rtol=5e-3, atol=1e-2)
+  for t in range(t_n):
+    st = env.step(st, cu(g['act'][:, t]))
+    np.testing.assert_array_equal(st.done.cpu().numpy(), g['done'][:, t])
+    assert torch.equal(st.obs, eo['obs'][t])
+
+
+def test_auto_reset_argument_errors():
+  torch = _torch()
+  from brax_b200.system import AutoReset
+  _, env = _env('ant')
+  st = env.reset(4, device='cuda')
+  act = torch.zeros(4, env.action_size, device='cuda')
+  ar = AutoReset(st.qp, st.obs, st.done, None, 5)
+  with pytest.raises(ValueError):
+    env.sys.step(st.qp, act, auto_reset=ar)                    # needs env=True
+  _, _, eo = env.sys.step(st.qp, act, env=True, auto_reset=ar)  # steps None: zeros
+  assert (eo['steps'] == 1).all() and (eo['truncation'] == 0).all()
+  from brax_b200 import system as bsys
+  plain = bsys.load_system('ant')
+  with pytest.raises(ValueError):
+    plain.step(st.qp, act, env=True, auto_reset=ar)
