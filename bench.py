@@ -381,7 +381,7 @@ def run_gpu(args, desc):
   ms_av = timed_chunks(av_step)
   # "next" row N1: the whole Env.step (sys.step + obs / reward / done / metrics of
   # envs/ant.py:222-281, envs/humanoid.py:246-340) as ONE launch; same timing method.
-  ms_env, env_obs = 0.0, 0
+  ms_env, ms_wenv, env_obs = 0.0, 0.0, 0
   env_name = args.env[:-len('_spring')] if args.env.endswith('_spring') else args.env
   if env_name in ('ant', 'humanoid', 'fetch', 'grasp') and args.env != 'grasp_spring':
     from brax_b200 import envs as bx_envs
@@ -404,6 +404,23 @@ def run_gpu(args, desc):
       j = i % nsets
       sts[j] = env.step(sts[j], acts[args.warmup + i])
     ms_env = timed_chunks(env_step)
+    # ... and with EpisodeWrapper(1000) + AutoResetWrapper applied inside the same launch
+    # (wrappers.py:105-148); step counters spread over the episode as in steady-state training,
+    # so ~0.1 % of the envs end their episode and reload their first state every step
+    wenv = bx_envs.EpisodeAutoReset(env, 1000)
+    first_obs = torch.zeros(b, env_obs, device=dev)
+    for j in range(nsets):
+      q = sts[j].qp
+      first = type(q)(*[getattr(q, k).clone() for k in ('pos', 'rot', 'vel', 'ang')])
+      sts[j] = State(q, first_obs, None, torch.zeros(b, device=dev), {},
+                     dict(first_qp=first, first_obs=first_obs,
+                          steps=torch.randint(0, 1000, (b,), device=dev).float()))
+      sts[j] = wenv.step(sts[j], acts[j % total])
+    barrier()
+    def wrapped_step(i):
+      j = i % nsets
+      sts[j] = wenv.step(sts[j], acts[args.warmup + i])
+    ms_wenv = timed_chunks(wrapped_step)
     qps = [st.qp for st in sts]
   ms_steps = [x.elapsed_time(y) for x, y in ev]
   ms_total = float(sum(ms_steps))
@@ -480,7 +497,10 @@ def run_gpu(args, desc):
         'env_step': ({'value': world * b * args.steps / (ms_env * 1e-3), 'unit': UNIT,
                       'ms_per_step': ms_env / args.steps, 'obs_size': env_obs,
                       'what': 'full Env.step (sys.step + obs/reward/done/metrics) in one launch',
-                      'extra_bytes_per_env_step': 4 * (env_obs + 12)} if ms_env > 0 else None),
+                      'extra_bytes_per_env_step': 4 * (env_obs + 12),
+                      'with_episode_and_auto_reset_wrappers': {
+                          'value': world * b * args.steps / (ms_wenv * 1e-3), 'unit': UNIT,
+                          'ms_per_step': ms_wenv / args.steps, 'episode_length': 1000}} if ms_env > 0 else None),
         'rollout': {'steps_per_launch': roll_t, 'launches': n_roll,
                     'value': world * b * roll_t * n_roll / (ms_roll * 1e-3), 'unit': UNIT,
                     'ms_per_step': ms_roll / (roll_t * n_roll)},
