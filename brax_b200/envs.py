@@ -176,6 +176,9 @@ class Env:
       path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'systems', system_name + '.json')
       env = env(SystemDesc.load(path))
     self.env = env
+    # True: state.info['physics'] carries the step's Info (an extra of this mirror; the reference's
+    # Env.step drops it, ant.py:224) -- costs the Info stores of the launch
+    self.keep_info = False
     self.sys = _system.load_system(system_name, device, env)
     self.observation_size = env.obs_size(self.sys.desc)
     self.action_size = self.sys.act_size
@@ -211,12 +214,16 @@ class Env:
     return self._launch(state, action)
 
   def _launch(self, state: State, action, rand=None, auto_reset=None) -> State:
-    qp, info, eo = self.sys.step(state.qp, action, env=True, env_rand=rand, auto_reset=auto_reset)
+    torch_path = _system._is_torch(state.qp.pos)
+    qp, info, eo = self.sys.step(state.qp, action, env=True, env_rand=rand, auto_reset=auto_reset,
+                                 info=self.keep_info or not torch_path)
     names = self.env.metric_names()
     metrics = dict(state.metrics)
     metrics.update({k: eo['metrics'][..., i] for i, k in enumerate(names)})
     extra = {k: eo[k] for k in ('steps', 'truncation') if k in eo}
-    return State(qp, eo['obs'], eo['reward'], eo['done'], metrics, dict(state.info, physics=info, **extra))
+    if info is not None:
+      extra['physics'] = info
+    return State(qp, eo['obs'], eo['reward'], eo['done'], metrics, dict(state.info, **extra))
 
 
 class Ant(Env):
@@ -332,11 +339,11 @@ class EpisodeAutoReset:
                            state.info.get('steps'), self.episode_length)
     if rand is None and isinstance(self.env, _TargetEnv):
       rand = self.env._uniform(state.qp.pos, (int(actions.shape[0]),) + tuple(state.qp.pos.shape[:-2]))
-    qp, info, eo = self.sys.rollout(state.qp, actions, env=True, env_rand=rand, auto_reset=ar)
+    qp, info, eo = self.sys.rollout(state.qp, actions, env=True, env_rand=rand, auto_reset=ar, info=False)
     names = self.env.env.metric_names()
     metrics = {k: eo['metrics'][-1, ..., i] for i, k in enumerate(names)}
     last = State(qp, eo['obs'][-1], eo['reward'][-1], eo['done'][-1], metrics,
-                 dict(state.info, physics=info, steps=eo['steps'], truncation=eo['truncation'][-1]))
+                 dict(state.info, steps=eo['steps'], truncation=eo['truncation'][-1]))
     return last, eo
 
 

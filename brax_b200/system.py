@@ -232,7 +232,7 @@ class System:
 
   # ---- the step ---------------------------------------------------------------
   def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False, env: bool = False,
-           env_rand=None, auto_reset: 'AutoReset' = None):
+           env_rand=None, auto_reset: 'AutoReset' = None, info: bool = True):
     """`System.step(qp, act) -> (qp, info)` (system.py:244-247).
 
     out: optional `HostBuffers` (host path only): results are written into its
@@ -245,13 +245,15 @@ class System:
     done [B], metrics [B,M] (envs/ant.py:222-281, envs/humanoid.py:246-340).
     auto_reset: (with env=True, torch path) an `AutoReset`: EpisodeWrapper.step and
     AutoResetWrapper.step (envs/wrappers.py:105-148) applied inside the launch; the env
-    dict gains 'steps' and 'truncation' and qp / obs / done are the wrapped ones."""
+    dict gains 'steps' and 'truncation' and qp / obs / done are the wrapped ones.
+    info: False (torch path) = do not write the Info outputs (the returned info is None): what
+    `Env.step` needs, which drops the Info after building the obs (envs/ant.py:224)."""
     if env and self.env is None:
       raise ValueError('this System was built without an EnvDesc')
     if auto_reset is not None and not env:
       raise ValueError('auto_reset needs env=True')
     if _is_torch(qp.pos):
-      return self._step_torch(qp, act, 1, angle_vel, env, env_rand, auto_reset)
+      return self._step_torch(qp, act, 1, angle_vel, env, env_rand, auto_reset, info)
     if auto_reset is not None:
       raise ValueError('auto_reset is supported with torch CUDA tensors only')
     return self._step_numpy(qp, act, out, angle_vel, env, env_rand)
@@ -282,7 +284,8 @@ class System:
     self._lib.bx_host_transfer_bytes(self._h, batch, C.byref(h2d), C.byref(d2h))
     return int(h2d.value), int(d2h.value)
 
-  def rollout(self, qp: QP, acts, env: bool = False, env_rand=None, auto_reset: 'AutoReset' = None):
+  def rollout(self, qp: QP, acts, env: bool = False, env_rand=None, auto_reset: 'AutoReset' = None,
+              info: bool = True):
     """T steps in ONE launch; acts is [T, B, A] (torch CUDA).  Returns the final
     QP and the Info of the last step (lax.scan of System.step over actions); with
     env=True also the env epilogue of EVERY step: obs [T,B,O], reward / done [T,B],
@@ -292,7 +295,7 @@ class System:
       raise ValueError('this System was built without an EnvDesc')
     if auto_reset is not None and not env:
       raise ValueError('auto_reset needs env=True')
-    return self._step_torch(qp, acts, int(acts.shape[0]), False, env, env_rand, auto_reset)
+    return self._step_torch(qp, acts, int(acts.shape[0]), False, env, env_rand, auto_reset, info)
 
   def _shapes(self, pos_shape):
     n = self.num_bodies
@@ -306,10 +309,11 @@ class System:
       raise ValueError('qp.pos has shape %s, system has %d bodies' % (tuple(pos_shape), n))
     return batched, b
 
-  def _specs(self, b, av, env, steps=1):
+  def _specs(self, b, av, env, steps=1, info=True):
     """[(name, shape)] of the outputs of one call."""
     dims = {'n': self.num_bodies, 'k': self.num_contacts, 'j': len(self.desc.joints)}
-    specs = [(name, (b, dims[dim], w) if w else (b, dims[dim])) for name, w, dim in (_OUT + _OUT_AV if av else _OUT)]
+    base = _OUT if info else _OUT[:4]
+    specs = [(name, (b, dims[dim], w) if w else (b, dims[dim])) for name, w, dim in (base + _OUT_AV if av else base)]
     if env:
       lead = (steps, b) if steps > 1 else (b,)
       specs += [('obs', lead + (self.obs_size,)), ('reward', lead), ('done', lead),
@@ -325,11 +329,13 @@ class System:
     if not batched:
       out = {k: v[0] for k, v in out.items()}
     qp = QP(out['pos_o'], out['rot_o'], out['vel_o'], out['ang_o'])
-    info = Info(P(out['contact_vel'], out['contact_ang']),
-                P(out['joint_vel'], out['joint_ang']),
-                P(out['actuator_vel'], out['actuator_ang']),
-                out['contact_pos'], out['contact_normal'],
-                out['contact_penetration'])
+    info = None
+    if 'contact_vel' in out:
+      info = Info(P(out['contact_vel'], out['contact_ang']),
+                  P(out['joint_vel'], out['joint_ang']),
+                  P(out['actuator_vel'], out['actuator_ang']),
+                  out['contact_pos'], out['contact_normal'],
+                  out['contact_penetration'])
     res = (qp, info)
     if 'joint_angle' in out:
       res += (JointState(out['joint_angle'], out['joint_velocity']),)
@@ -337,14 +343,14 @@ class System:
       res += (env_out,)
     return res
 
-  def _out_plan(self, b, av, env=False, steps=1):
+  def _out_plan(self, b, av, env=False, steps=1, info=True):
     """Per batch size: the outputs as slices of ONE allocation (each slice
     starts on a 16-byte boundary so the kernel's vector stores apply)."""
-    key = (b, av, env, steps)
+    key = (b, av, env, steps, info)
     plan = self._plans.get(key)
     if plan is None:
       names, shapes, offs, off = [], [], [], 0
-      for name, shape in self._specs(b, av, env, steps):
+      for name, shape in self._specs(b, av, env, steps, info):
         names.append(name)
         shapes.append(shape)
         offs.append(off)
@@ -353,6 +359,8 @@ class System:
     return plan
 
   def _clear_optional(self, io):
+    for name, _, _ in _OUT[4:]:
+      setattr(io, name, None)
     io.joint_angle = io.joint_velocity = None
     io.obs = io.reward = io.done = io.metrics = None
     io.env_rand = None
@@ -361,7 +369,7 @@ class System:
     io.episode_length = 0.0
 
   def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False, env_rand=None,
-                  auto_reset=None):
+                  auto_reset=None, info: bool = True):
     """env_rand: (fetch / grasp) uniforms of the target teleport, [B,3] or [T,B,3]."""
     import torch
     batched, b = self._shapes(qp.pos.shape)
@@ -385,7 +393,7 @@ class System:
 
     ins = (prep(qp.pos, b * n * 3), prep(qp.rot, b * n * 4), prep(qp.vel, b * n * 3),
            prep(qp.ang, b * n * 3), prep(act, steps * b * a))
-    names, shapes, offs, total = self._out_plan(b, av, env, steps)
+    names, shapes, offs, total = self._out_plan(b, av, env, steps, info)
     flat = torch.empty(total, dtype=f32, device=dev)
     base = flat.data_ptr()
     io = self._io

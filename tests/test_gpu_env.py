@@ -476,3 +476,26 @@ def test_auto_reset_argument_errors():
   plain = bsys.load_system('ant')
   with pytest.raises(ValueError):
     plain.step(st.qp, act, env=True, auto_reset=ar)
+
+
+def test_env_step_without_info_outputs():
+  """info=False leaves the Info stores out of the launch (the env mirror's default, as the
+  reference's Env.step drops the Info): same QP and env outputs, info is None."""
+  torch = _torch()
+  from brax_b200.envs import State
+  _, env = _env('ant')
+  qp, rng = _harvest(env.sys, 300, 5, 2)
+  act = torch.from_numpy(rng.uniform(-1, 1, (300, env.action_size)).astype(np.float32)).cuda()
+  q1, i1, e1 = env.sys.step(qp, act, env=True)
+  q2, i2, e2 = env.sys.step(qp, act, env=True, info=False)
+  q3, i3 = env.sys.step(qp, act, info=False)
+  assert i1 is not None and i2 is None and i3 is None
+  for k in util.QP_KEYS:
+    assert torch.equal(getattr(q1, k), getattr(q2, k)) and torch.equal(getattr(q1, k), getattr(q3, k))
+  for k in e1:
+    assert torch.equal(e1[k], e2[k]), k
+  st = env.step(State(qp, None, None, None), act)
+  assert 'physics' not in st.info and torch.equal(st.obs, e1['obs'])
+  env.keep_info = True
+  st = env.step(State(qp, None, None, None), act)
+  assert torch.equal(st.info['physics'].contact.vel, i1.contact.vel)
