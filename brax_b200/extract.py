@@ -127,6 +127,94 @@ def _pair_rows(collider, group: int) -> List[Dict[str, Any]]:
   return rows
 
 
+def _reset_desc(sys) -> Dict[str, Any]:
+  """The static part of `System.default_qp(joint_angle=..., joint_velocity=...)`
+  (system.py:112-242) and of `default_angle` (:86-110), default_index 0:
+
+    base     QP after the config's default qps only (:118-131)
+    joints   in the depth order of :142-152: bodies, offsets, euler_to_quat of `rotation` and
+             `reference_rotation` (:176-179), and `take`: the three slots of the flat joint-angle
+             vector the joint reads, num_dof = the appended zero (:156-168)
+    groups   trees without a default qp, lowered onto the xy plane (:211-240): per tree the
+             probes of `bodies.min_z` (bodies.py:62-98) -- z = pos.z + rotate(point, rot).z -
+             radius -- and `zero`: 0.0 is one of the candidates (bodies without colliders, planes)
+  """
+  from brax import math as bmath
+  from brax.physics.base import vec_to_arr
+  cfg = sys.config
+  n = sys.num_bodies
+  pos, rot = np.zeros((n, 3)), np.tile(np.array([1., 0., 0., 0.]), (n, 1))
+  vel, ang = np.zeros((n, 3)), np.zeros((n, 3))
+  default = cfg.defaults[0] if len(cfg.defaults) else None
+  if default is not None:
+    for dqp in default.qps:
+      i = sys.body.index[dqp.name]
+      pos[i], rot[i] = _a(vec_to_arr(dqp.pos)), _a(bmath.euler_to_quat(vec_to_arr(dqp.rot)))
+      vel[i], ang[i] = _a(vec_to_arr(dqp.vel)), _a(vec_to_arr(dqp.ang))
+  joint_idxs, beg = [], 0
+  for j in cfg.joints:
+    dof = sum([l.min != 0 or l.max != 0 for l in j.angle_limit])
+    joint_idxs.append((j, (beg, beg + dof)))
+    beg += dof
+  num_dof = beg
+  lineage = {j.child: j.parent for j in cfg.joints}
+  depth = {}
+  for child, parent in lineage.items():
+    depth[child] = 1
+    while parent in lineage:
+      parent = lineage[parent]
+      depth[child] += 1
+  joint_idxs = sorted(joint_idxs, key=lambda x: depth.get(x[0].parent, 0))
+  joints = []
+  for j, (b0, b1) in joint_idxs:
+    take = list(range(b0, b1))
+    take += [num_dof] * (3 - len(take))
+    joints.append({
+        'body_p': int(sys.body.index[j.parent]), 'body_c': int(sys.body.index[j.child]),
+        'off_p': _l(vec_to_arr(j.parent_offset)), 'off_c': _l(vec_to_arr(j.child_offset)),
+        'rot': _l(bmath.euler_to_quat(vec_to_arr(j.rotation))),
+        'ref': _l(bmath.euler_to_quat(vec_to_arr(j.reference_rotation))),
+        'take': [int(t) for t in take]})
+  fixed = {j.child for j, _ in joint_idxs}
+  if default is not None:
+    fixed |= {q.name for q in default.qps}
+  root_idx = {b.name: [i] for i, b in enumerate(cfg.bodies) if b.name not in fixed}
+  for j, _ in joint_idxs:
+    parent = j.parent
+    while parent in lineage:
+      parent = lineage[parent]
+    if parent in root_idx:
+      root_idx[parent].append(int(sys.body.index[j.child]))
+  groups = []
+  for children in root_idx.values():
+    probes, zero = [], False
+    for c in children:
+      body = cfg.bodies[c]
+      if not body.colliders:
+        zero = True
+      for col in body.colliders:
+        if col.HasField('sphere'):
+          probes.append({'body': c, 'point': _l(vec_to_arr(col.position)), 'radius': float(col.sphere.radius)})
+        elif col.HasField('capsule'):
+          axis = _a(bmath.rotate(np.array([0., 0., 1.]), bmath.euler_to_quat(vec_to_arr(col.rotation))))
+          length = col.capsule.length / 2 - col.capsule.radius
+          for end in (-1, 1):
+            probes.append({'body': c, 'point': _l(_a(vec_to_arr(col.position)) + end * axis * length),
+                           'radius': float(col.capsule.radius)})
+        elif col.HasField('box'):
+          q = bmath.euler_to_quat(vec_to_arr(col.rotation))
+          for i in range(8):
+            corner = np.array([i % 2 * 2 - 1, 2 * (i // 4) - 1, i // 2 % 2 * 2 - 1], dtype=float)
+            corner = _a(bmath.rotate(corner * _a(vec_to_arr(col.box.halfsize)), q)) + _a(vec_to_arr(col.position))
+            probes.append({'body': c, 'point': _l(corner), 'radius': 0.0})
+        else:
+          zero = True
+    groups.append({'bodies': [int(c) for c in children], 'probes': probes, 'zero': zero})
+  return {'num_dof': int(num_dof), 'default_angle': _l(sys.default_angle()),
+          'base': {'pos': pos.tolist(), 'rot': rot.tolist(), 'vel': vel.tolist(), 'ang': ang.tolist()},
+          'joints': joints, 'groups': groups}
+
+
 def describe(sys, name: str = 'system', act_size: int = None) -> SystemDesc:
   """Returns the `SystemDesc` of a constructed reference `brax.System`."""
   cfg = sys.config
@@ -201,4 +289,5 @@ def describe(sys, name: str = 'system', act_size: int = None) -> SystemDesc:
       bodies=bodies, joints=joints, actuators=actuators, forces=forces,
       pairs=pairs, body_names=[b.name for b in cfg.bodies],
       default_qp={'pos': _a(qp.pos).tolist(), 'rot': _a(qp.rot).tolist(),
-                  'vel': _a(qp.vel).tolist(), 'ang': _a(qp.ang).tolist()})
+                  'vel': _a(qp.vel).tolist(), 'ang': _a(qp.ang).tolist()},
+      reset=_reset_desc(sys))
