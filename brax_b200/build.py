@@ -9,7 +9,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libbrax_b200.so')
-DEPS = ['bx_api.cu', 'bx_kernels.cu', 'bx_step_kernel.cuh', 'bx_params.h', 'bx_math.cuh', 'bx_tables.h',
+DEPS = ['bx_api.cu', 'bx_reset.cu', 'bx_kernels.cu', 'bx_step_kernel.cuh', 'bx_params.h', 'bx_math.cuh', 'bx_tables.h',
         os.path.join('..', '..', 'include', 'brax_b200.h')]
 # (launch bound threads, min blocks per SM): one kernel translation unit each
 BOUNDS = [(256, 2), (320, 2), (384, 2), (512, 1)]
@@ -40,7 +40,8 @@ def build(force: bool = False, verbose: bool = False, extra=(), out: str = None)
   os.makedirs(objdir, exist_ok=True)
   common = [nvcc] + NVCC_FLAGS + list(extra) + (['-Xptxas', '-v'] if verbose else [])
   jobs = [(common + ['-c', os.path.join(CSRC, 'bx_api.cu'), '-o', os.path.join(objdir, 'bx_api.o')])]
-  objs = [os.path.join(objdir, 'bx_api.o')]
+  objs = [os.path.join(objdir, 'bx_api.o'), os.path.join(objdir, 'bx_reset.o')]
+  jobs.append(common + ['-c', os.path.join(CSRC, 'bx_reset.cu'), '-o', os.path.join(objdir, 'bx_reset.o')])
   for maxt, minb in BOUNDS:
     o = os.path.join(objdir, 'bx_kernels_%d.o' % maxt)
     objs.append(o)

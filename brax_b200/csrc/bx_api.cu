@@ -37,7 +37,13 @@ struct bx_system {
   float* d_scratch;
   size_t scratch_floats;
   cudaStream_t streams[BX_HOST_STREAMS];
+  bx_reset_desc* d_reset;  // device copy of desc.reset (bx_default_qp), or NULL
+  int reset_dof;
 };
+
+cudaError_t bx_reset_launch(const bx_reset_desc* d_tables, int nb, int64_t num_envs, const float* joint_angle,
+                            const float* joint_velocity, float* pos, float* rot, float* vel, float* ang,
+                            cudaStream_t stream);
 
 static thread_local std::string g_err;
 static std::atomic<int64_t> g_launches{0};
@@ -114,6 +120,24 @@ static int validate(const bx_system_desc* d) {
     k += p.n_contacts;
   }
   if (k > BX_MAX_CONTACTS) return fail("too many contact rows");
+  if (d->reset) {
+    const bx_reset_desc& r = *d->reset;
+    if (r.struct_size != sizeof(bx_reset_desc)) return fail("bx_reset_desc size mismatch (ABI skew)");
+    if (r.num_dof < 0 || r.num_joints < 0 || r.num_joints > BX_MAX_JOINTS || r.num_probes < 0 ||
+        r.num_probes > BX_MAX_PROBES || r.num_trees < 0 || r.num_trees > BX_MAX_TREES)
+      return fail("bx_reset_desc counts out of range");
+    for (int i = 0; i < r.num_joints; i++) {
+      const bx_reset_joint& j = r.joints[i];
+      if (j.body_p < 0 || j.body_p >= d->num_bodies || j.body_c < 0 || j.body_c >= d->num_bodies)
+        return fail("bx_reset_desc joint body index out of range");
+      for (int x = 0; x < 3; x++)
+        if (j.take[x] < 0 || j.take[x] > r.num_dof) return fail("bx_reset_desc joint take index out of range");
+    }
+    for (int i = 0; i < r.num_probes; i++)
+      if (r.probes[i].body < 0 || r.probes[i].body >= d->num_bodies || r.probes[i].tree < 0 ||
+          r.probes[i].tree >= r.num_trees)
+        return fail("bx_reset_desc probe index out of range");
+  }
   if (d->env) {
     const bx_env_desc& e = *d->env;
     if (e.struct_size != sizeof(bx_env_desc)) return fail("bx_env_desc size mismatch (ABI skew)");
@@ -763,7 +787,30 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   CUDA_OK(cudaMemcpy(s->d_tab_i, ti.data(), ti.size() * 4, cudaMemcpyHostToDevice));
   CUDA_OK(cudaMemcpy(s->d_tab_f, tf.data(), tf.size() * 4, cudaMemcpyHostToDevice));
   if (set_smem_attr(static_cast<int>(prop.sharedMemPerBlockOptin))) { delete s; return 1; }
+  s->d_reset = nullptr;
+  s->reset_dof = 0;
+  if (desc->reset) {
+    if (cudaMalloc(&s->d_reset, sizeof(bx_reset_desc)) != cudaSuccess) { delete s; return fail("cudaMalloc of reset tables failed"); }
+    CUDA_OK(cudaMemcpy(s->d_reset, desc->reset, sizeof(bx_reset_desc), cudaMemcpyHostToDevice));
+    s->reset_dof = desc->reset->num_dof;
+  }
   *out = s;
+  return 0;
+}
+
+extern "C" int bx_system_num_joint_dof(const bx_system* s) { return s && s->d_reset ? s->reset_dof : -1; }
+
+extern "C" int bx_default_qp(const bx_system* s, int64_t B, const float* joint_angle, const float* joint_velocity,
+                             float* pos, float* rot, float* vel, float* ang, void* stream) {
+  if (!s) return fail("system is NULL");
+  if (!s->d_reset) return fail("bx_default_qp needs a system created with desc.reset");
+  if (B <= 0) return fail("num_envs must be positive");
+  if (!pos || !rot || !vel || !ang) return fail("QP pointers must not be NULL");
+  if (s->reset_dof > 0 && (!joint_angle || !joint_velocity)) return fail("joint_angle / joint_velocity must not be NULL");
+  CUDA_OK(cudaSetDevice(s->device));
+  CUDA_OK(bx_reset_launch(s->d_reset, s->h.nb, B, joint_angle, joint_velocity, pos, rot, vel, ang,
+                          static_cast<cudaStream_t>(stream)));
+  g_launches.fetch_add(1);
   return 0;
 }
 
@@ -773,6 +820,7 @@ extern "C" void bx_system_destroy(bx_system* s) {
   cudaFree(s->d_tab_i);
   cudaFree(s->d_tab_f);
   cudaFree(s->d_scratch);
+  cudaFree(s->d_reset);
   for (int i = 0; i < BX_HOST_STREAMS; i++)
     if (s->streams[i]) cudaStreamDestroy(s->streams[i]);
   delete s;

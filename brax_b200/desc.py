@@ -20,7 +20,7 @@ from typing import Any, Dict, List
 
 import numpy as np
 
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 MODE = {'pbd': 0, 'legacy_spring': 1}
 JOINT_KIND = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
@@ -31,6 +31,7 @@ PAIR_KIND = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2}
 
 MAX_BODIES, MAX_JOINTS, MAX_ACTUATORS = 64, 64, 64
 MAX_FORCES, MAX_PAIRS, MAX_CONTACTS, MAX_GROUPS = 32, 64, 128, 8
+MAX_PROBES, MAX_TREES = 128, 8
 
 
 class CBody(C.Structure):
@@ -68,6 +69,24 @@ class CPair(C.Structure):
               ('pts', (C.c_float * 3) * 8)]
 
 
+class CResetJoint(C.Structure):
+  _fields_ = [('body_p', C.c_int32), ('body_c', C.c_int32), ('take', C.c_int32 * 3),
+              ('off_p', C.c_float * 3), ('off_c', C.c_float * 3), ('rot', C.c_float * 4), ('ref', C.c_float * 4)]
+
+
+class CResetProbe(C.Structure):
+  _fields_ = [('body', C.c_int32), ('tree', C.c_int32), ('point', C.c_float * 3), ('radius', C.c_float)]
+
+
+class CResetDesc(C.Structure):
+  _fields_ = [('struct_size', C.c_uint32), ('num_dof', C.c_int32), ('num_joints', C.c_int32),
+              ('num_probes', C.c_int32), ('num_trees', C.c_int32),
+              ('base_pos', (C.c_float * 3) * MAX_BODIES), ('base_rot', (C.c_float * 4) * MAX_BODIES),
+              ('base_vel', (C.c_float * 3) * MAX_BODIES), ('base_ang', (C.c_float * 3) * MAX_BODIES),
+              ('joints', CResetJoint * MAX_JOINTS), ('probes', CResetProbe * MAX_PROBES),
+              ('body_tree', C.c_int32 * MAX_BODIES), ('tree_zero', C.c_int32 * MAX_TREES)]
+
+
 class CSystemDesc(C.Structure):
   _fields_ = [('struct_size', C.c_uint32), ('abi_version', C.c_uint32),
               ('dynamics_mode', C.c_int32), ('substeps', C.c_int32),
@@ -81,7 +100,7 @@ class CSystemDesc(C.Structure):
               ('bodies', C.POINTER(CBody)), ('joints', C.POINTER(CJoint)),
               ('actuators', C.POINTER(CActuator)),
               ('forces', C.POINTER(CForce)), ('pairs', C.POINTER(CPair)),
-              ('env', C.c_void_p)]
+              ('env', C.c_void_p), ('reset', C.c_void_p)]
 
 
 class CStepIO(C.Structure):
@@ -265,4 +284,39 @@ class SystemDesc:
     d.pairs = C.cast(pairs, C.POINTER(CPair))
     cenv = env.to_c(self) if env is not None else None
     d.env = C.cast(C.pointer(cenv), C.c_void_p) if cenv is not None else None
-    return d, (bodies, joints, acts, forces, pairs, cenv)
+    creset = self.reset_to_c()
+    d.reset = C.cast(C.pointer(creset), C.c_void_p) if creset is not None else None
+    return d, (bodies, joints, acts, forces, pairs, cenv, creset)
+
+  def reset_to_c(self):
+    """bx_reset_desc of `self.reset` (extract._reset_desc), or None when the descriptor has none."""
+    r = self.reset
+    if not r:
+      return None
+    probes = [(p, t) for t, g in enumerate(r['groups']) for p in g['probes']]
+    if len(r['joints']) > MAX_JOINTS or len(probes) > MAX_PROBES or len(r['groups']) > MAX_TREES:
+      raise ValueError('reset tables exceed the compiled maxima')
+    c = CResetDesc()
+    c.struct_size = C.sizeof(CResetDesc)
+    c.num_dof, c.num_joints = int(r['num_dof']), len(r['joints'])
+    c.num_probes, c.num_trees = len(probes), len(r['groups'])
+    for k, w in (('pos', 3), ('rot', 4), ('vel', 3), ('ang', 3)):
+      arr = getattr(c, 'base_' + k)
+      for b in range(self.num_bodies):
+        arr[b][:] = _f(r['base'][k][b])
+    for i, j in enumerate(r['joints']):
+      cj = c.joints[i]
+      cj.body_p, cj.body_c = j['body_p'], j['body_c']
+      cj.take[:] = [int(t) for t in j['take']]
+      cj.off_p[:], cj.off_c[:] = _f(j['off_p']), _f(j['off_c'])
+      cj.rot[:], cj.ref[:] = _f(j['rot']), _f(j['ref'])
+    for i, (p, t) in enumerate(probes):
+      c.probes[i].body, c.probes[i].tree = p['body'], t
+      c.probes[i].point[:] = _f(p['point'])
+      c.probes[i].radius = p['radius']
+    c.body_tree[:] = [-1] * MAX_BODIES
+    for t, g in enumerate(r['groups']):
+      c.tree_zero[t] = int(bool(g['zero']))
+      for b in g['bodies']:
+        c.body_tree[b] = t
+    return c

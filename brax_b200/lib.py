@@ -17,7 +17,7 @@ SYMBOLS = ('bx_system_create', 'bx_system_destroy', 'bx_system_num_contacts',
            'bx_step_host', 'bx_rollout', 'bx_system_configure',
            'bx_system_autotune', 'bx_system_threads', 'bx_host_transfer_bytes',
            'bx_host_alloc', 'bx_host_free', 'bx_desc_tile_bytes',
-           'bx_launch_count', 'bx_last_error')
+           'bx_launch_count', 'bx_last_error', 'bx_system_num_joint_dof', 'bx_default_qp')
 
 _lib = None
 
@@ -39,9 +39,12 @@ def load():
   lib.bx_system_destroy.argtypes = [P]
   lib.bx_system_destroy.restype = None
   for f in ('bx_system_num_contacts', 'bx_system_num_bodies',
-            'bx_system_act_size', 'bx_system_obs_size', 'bx_system_num_metrics'):
+            'bx_system_act_size', 'bx_system_obs_size', 'bx_system_num_metrics',
+            'bx_system_num_joint_dof'):
     getattr(lib, f).argtypes = [P]
     getattr(lib, f).restype = C.c_int
+  lib.bx_default_qp.argtypes = [P, C.c_int64, P, P, P, P, P, P, P]
+  lib.bx_default_qp.restype = C.c_int
   lib.bx_step.argtypes = [P, C.c_int64, C.POINTER(_desc.CStepIO), P]
   lib.bx_step.restype = C.c_int
   lib.bx_step_host.argtypes = [P, C.c_int64, C.POINTER(_desc.CStepIO)]

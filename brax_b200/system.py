@@ -219,8 +219,25 @@ class System:
       self.autotune = False
 
   # ---- state helpers ---------------------------------------------------------
-  def default_qp(self, batch: int = None, device=None) -> QP:
-    """`System.default_qp()` (system.py:112) as recorded at extraction time."""
+  def default_angle(self):
+    """`System.default_angle()` (system.py:86-110), float32 [D]."""
+    return np.asarray(self.desc.reset['default_angle'], dtype=np.float32)
+
+  @property
+  def num_joint_dof(self) -> int:
+    """D: length of the joint_angle / joint_velocity vectors `default_qp` takes."""
+    return int(self.desc.reset['num_dof'])
+
+  def default_qp(self, batch: int = None, device=None, joint_angle=None, joint_velocity=None) -> QP:
+    """`System.default_qp(joint_angle=..., joint_velocity=...)` (system.py:112-242).
+
+    Without joint arguments: the default state as recorded at extraction time (numpy, or
+    torch on `device`).  With joint_angle / joint_velocity ([D] or [B,D] torch CUDA tensors;
+    a missing one is `default_angle()` / zeros): forward kinematics and the lowering of free
+    trees onto the xy plane in ONE kernel launch (bx_default_qp) -- what every env's reset
+    calls with its noisy joint state (envs/ant.py:198-204)."""
+    if joint_angle is not None or joint_velocity is not None:
+      return self._default_qp_torch(joint_angle, joint_velocity)
     d = self.desc.default_qp
     arrs = [np.asarray(d[k], dtype=np.float32) for k in ('pos', 'rot', 'vel', 'ang')]
     if batch is not None:
@@ -229,6 +246,36 @@ class System:
       import torch
       arrs = [torch.from_numpy(a).to(device) for a in arrs]
     return QP(*arrs)
+
+  def _default_qp_torch(self, joint_angle, joint_velocity) -> QP:
+    import torch
+    if not self.desc.reset:
+      raise ValueError('this descriptor carries no reset tables (SystemDesc.reset)')
+    given = joint_angle if joint_angle is not None else joint_velocity
+    if not _is_torch(given) or given.device.type != 'cuda':
+      raise RuntimeError('joint_angle / joint_velocity must be torch CUDA tensors (no CPU fallback)')
+    dev, nd = given.device, self.num_joint_dof
+    batched = given.dim() == 2
+    b = int(given.shape[0]) if batched else 1
+    f32 = torch.float32
+    if joint_angle is None:
+      joint_angle = torch.from_numpy(self.default_angle()).to(dev).expand(b, nd)
+    if joint_velocity is None:
+      joint_velocity = torch.zeros(b, nd, dtype=f32, device=dev)
+    ja = joint_angle.to(f32).reshape(b, nd).contiguous()
+    jv = joint_velocity.to(f32).reshape(b, nd).contiguous()
+    n = self.num_bodies
+    flat = torch.empty(b * n * 13, dtype=f32, device=dev)
+    outs = [flat[:b * n * 3].view(b, n, 3), flat[b * n * 3:b * n * 7].view(b, n, 4),
+            flat[b * n * 7:b * n * 10].view(b, n, 3), flat[b * n * 10:].view(b, n, 3)]
+    stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    rc = self._lib.bx_default_qp(self._h, b, ja.data_ptr() if nd else None, jv.data_ptr() if nd else None,
+                                 *[o.data_ptr() for o in outs], stream)
+    if rc != 0:
+      raise RuntimeError('bx_default_qp: ' + _lib.last_error())
+    if not batched:
+      outs = [o[0] for o in outs]
+    return QP(*outs)
 
   # ---- the step ---------------------------------------------------------------
   def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False, env: bool = False,

@@ -4,8 +4,8 @@
  *   c_driver <system.blob> <io.blob> <out.blob>
  *
  * system.blob: the bytes of a bx_system_desc followed by its bodies / joints / actuators /
- *              forces / pairs arrays and, if desc.env was set, one bx_env_desc (pointer fields
- *              are patched here) -- tests/test_cdriver.py writes it from a SystemDesc.
+ *              forces / pairs arrays and, if desc.env / desc.reset were set, one bx_env_desc / one
+ *              bx_reset_desc (pointer fields are patched here) -- tests/test_cdriver.py writes it from a SystemDesc.
  * io.blob:     int64 B, int64 T, then pos[B,N,3] rot[B,N,4] vel[B,N,3] ang[B,N,3] act[T,B,A].
  * out.blob:    after T chained bx_step_host calls (System.step, system.py:244, fed with its own
  *              QP): pos rot vel ang of the last state, then the Info of the last step
@@ -43,13 +43,14 @@ int main(int argc, char** argv) {
   FILE* f = fopen(argv[1], "rb");
   if (!f) { perror(argv[1]); return 1; }
   bx_system_desc* d = (bx_system_desc*)slurp(f, sizeof(bx_system_desc));
-  const int has_env = d->env != NULL;
+  const int has_env = d->env != NULL, has_reset = d->reset != NULL;
   d->bodies = (const bx_body*)slurp(f, sizeof(bx_body) * (size_t)d->num_bodies);
   d->joints = (const bx_joint*)slurp(f, sizeof(bx_joint) * (size_t)d->num_joints);
   d->actuators = (const bx_actuator*)slurp(f, sizeof(bx_actuator) * (size_t)d->num_actuators);
   d->forces = (const bx_force*)slurp(f, sizeof(bx_force) * (size_t)d->num_forces);
   d->pairs = (const bx_pair*)slurp(f, sizeof(bx_pair) * (size_t)d->num_pairs);
   d->env = has_env ? (const bx_env_desc*)slurp(f, sizeof(bx_env_desc)) : NULL;
+  d->reset = has_reset ? (const bx_reset_desc*)slurp(f, sizeof(bx_reset_desc)) : NULL;
   fclose(f);
 
   bx_system* sys = NULL;

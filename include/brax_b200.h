@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BX_ABI_VERSION 6
+#define BX_ABI_VERSION 7
 
 /* dynamics_mode (base.py:179-201) */
 #define BX_MODE_PBD 0
@@ -184,6 +184,41 @@ typedef struct bx_env_desc {
   float act_min[BX_MAX_ACT], act_range[BX_MAX_ACT]; /* grasp.py:43-54: act = min + range * (act + 1) / 2 */
 } bx_env_desc;
 
+/* Optional reset tables ("next" row N3): the static part of
+ * System.default_qp(joint_angle=..., joint_velocity=...) (system.py:112-242), default_index 0.
+ *   base_*  the QP after the config's default qps only (system.py:118-131)
+ *   joints  in the depth order of system.py:142-152.  take[d] = slot of the flat joint-angle /
+ *           joint-velocity vector that dof d reads, num_dof = none (0) (system.py:156-168);
+ *           rot / ref = euler_to_quat of the joint's rotation / reference_rotation (:176-179)
+ *   probes  of bodies.min_z (bodies.py:62-98): z = pos.z + rotate(point, rot).z - radius of
+ *           sphere centres, capsule ends and box corners; every tree of bodies without a
+ *           default qp is lowered by the minimum over its probes (and 0.0 if tree_zero: bodies
+ *           without colliders, planes) (system.py:211-240).  body_tree[b] = tree of body b, -1 none. */
+#define BX_MAX_PROBES 128
+#define BX_MAX_TREES 8
+typedef struct bx_reset_joint {
+  int32_t body_p, body_c;
+  int32_t take[3];
+  float off_p[3], off_c[3];
+  float rot[4], ref[4];
+} bx_reset_joint;
+typedef struct bx_reset_probe {
+  int32_t body, tree;
+  float point[3];
+  float radius;
+} bx_reset_probe;
+typedef struct bx_reset_desc {
+  uint32_t struct_size; /* = sizeof(bx_reset_desc), checked */
+  int32_t num_dof;      /* D: length of the joint_angle / joint_velocity vectors */
+  int32_t num_joints, num_probes, num_trees;
+  float base_pos[BX_MAX_BODIES][3], base_rot[BX_MAX_BODIES][4];
+  float base_vel[BX_MAX_BODIES][3], base_ang[BX_MAX_BODIES][3];
+  bx_reset_joint joints[BX_MAX_JOINTS];
+  bx_reset_probe probes[BX_MAX_PROBES];
+  int32_t body_tree[BX_MAX_BODIES];
+  int32_t tree_zero[BX_MAX_TREES];
+} bx_reset_desc;
+
 /* The static description of one system; everything System.__init__ derives
  * from the config (system.py:53-84).  Built on the host by
  * brax_b200.extract.describe(sys) from a constructed reference System. */
@@ -208,6 +243,7 @@ typedef struct bx_system_desc {
   const bx_force* forces;
   const bx_pair* pairs;
   const bx_env_desc* env; /* optional env epilogue, NULL = none */
+  const bx_reset_desc* reset; /* optional reset tables (bx_default_qp), NULL = none */
 } bx_system_desc;
 
 typedef struct bx_system bx_system; /* opaque; owns device copies of tables */
@@ -271,6 +307,16 @@ int bx_system_act_size(const bx_system* sys);
 /* Env epilogue sizes: O floats of obs per env, M metrics (0 without desc.env). */
 int bx_system_obs_size(const bx_system* sys);
 int bx_system_num_metrics(const bx_system* sys);
+
+/* System.default_qp(joint_angle=..., joint_velocity=...) (system.py:112-242) for B independent
+ * environments: forward kinematics down the joint tree from per-env joint angles / velocities
+ * [B,D] (what every env's reset draws, envs/ant.py:198-204), then each free tree lowered onto the
+ * xy plane.  ONE launch on `stream`, device pointers, outputs [B,N,3|4|3|3].  Systems created
+ * with desc.reset only.  D = bx_system_num_joint_dof. */
+int bx_system_num_joint_dof(const bx_system* sys);
+int bx_default_qp(const bx_system* sys, int64_t num_envs, const float* joint_angle,
+                  const float* joint_velocity, float* pos, float* rot, float* vel, float* ang,
+                  void* stream);
 
 /* One System.step for B independent environments: ONE kernel launch on
  * `stream` (a cudaStream_t passed as void*; NULL = default stream).  No host

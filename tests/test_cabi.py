@@ -53,9 +53,10 @@ def test_struct_sizes_match_header():
 #include <stdio.h>
 #include "brax_b200.h"
 int main(void) {
-  printf("%zu %zu %zu %zu %zu %zu %zu %zu %d\n", sizeof(bx_body), sizeof(bx_joint),
+  printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %d\n", sizeof(bx_body), sizeof(bx_joint),
          sizeof(bx_actuator), sizeof(bx_force), sizeof(bx_pair),
-         sizeof(bx_system_desc), sizeof(bx_step_io), sizeof(bx_env_desc), BX_ABI_VERSION);
+         sizeof(bx_system_desc), sizeof(bx_step_io), sizeof(bx_env_desc), sizeof(bx_reset_joint),
+         sizeof(bx_reset_probe), sizeof(bx_reset_desc), BX_ABI_VERSION);
   return 0;
 }'''
   import tempfile
@@ -67,7 +68,8 @@ int main(void) {
     got = [int(x) for x in subprocess.check_output([exe]).split()]
   want = [C.sizeof(c) for c in (bx_desc.CBody, bx_desc.CJoint, bx_desc.CActuator,
                                 bx_desc.CForce, bx_desc.CPair,
-                                bx_desc.CSystemDesc, bx_desc.CStepIO, bx_envs.CEnvDesc)]
+                                bx_desc.CSystemDesc, bx_desc.CStepIO, bx_envs.CEnvDesc,
+                                bx_desc.CResetJoint, bx_desc.CResetProbe, bx_desc.CResetDesc)]
   assert got[:-1] == want
   assert got[-1] == bx_desc.ABI_VERSION
 
@@ -111,17 +113,37 @@ def test_create_rejects_bad_env_desc(lib):
   """The optional env epilogue (bx_env_desc) is validated before any device is touched."""
   env = bx_envs.EnvDesc('ant', use_contact_forces=True)
   cdesc, keep = util.load_desc('ant').to_c(env)
-  keep[-1].struct_size = 12
+  keep[5].struct_size = 12
   rc, msg = _create(lib, cdesc)
   assert rc != 0 and 'bx_env_desc size mismatch' in msg
   cdesc, keep = util.load_desc('ant').to_c(env)
-  keep[-1].kind = 9
+  keep[5].kind = 9
   rc, msg = _create(lib, cdesc)
   assert rc != 0 and 'unsupported env kind' in msg
   cdesc, keep = util.load_desc('ant').to_c(env)
-  keep[-1].joint_free_dofs[0] = 5
+  keep[5].joint_free_dofs[0] = 5
   rc, msg = _create(lib, cdesc)
   assert rc != 0 and 'joint_free_dofs' in msg
+
+
+def test_create_rejects_bad_reset_desc(lib):
+  """The optional reset tables (bx_reset_desc) are validated before any device is touched."""
+  cdesc, keep = util.load_desc('ant').to_c()
+  keep[6].struct_size = 12
+  rc, msg = _create(lib, cdesc)
+  assert rc != 0 and 'bx_reset_desc size mismatch' in msg
+  cdesc, keep = util.load_desc('ant').to_c()
+  keep[6].joints[3].body_c = 99
+  rc, msg = _create(lib, cdesc)
+  assert rc != 0 and 'joint body index' in msg
+  cdesc, keep = util.load_desc('ant').to_c()
+  keep[6].joints[0].take[1] = 40
+  rc, msg = _create(lib, cdesc)
+  assert rc != 0 and 'take index' in msg
+  cdesc, keep = util.load_desc('ant').to_c()
+  keep[6].probes[2].tree = 7
+  rc, msg = _create(lib, cdesc)
+  assert rc != 0 and 'probe index' in msg
 
 
 def test_tile_bytes_with_env_epilogue(lib):
