@@ -870,6 +870,13 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   p.done_in = io->done_in; p.steps_in = io->steps_in;
   p.steps_out = io->steps_out; p.truncation = io->truncation;
   p.episode_length = io->episode_length;
+  p.observe = io->observe;
+  if (io->observe) {
+    if (!s->h.env_kind) return fail("observe needs a system created with desc.env");
+    if (num_steps != 1) return fail("observe is a single launch (bx_step)");
+    if (!io->obs) return fail("observe needs the obs output");
+    if (io->first_pos) return fail("observe and auto-reset exclude each other");
+  }
   if (io->first_pos) {
     if (!s->h.env_kind) return fail("auto-reset needs a system created with desc.env");
     if (!io->first_rot || !io->first_vel || !io->first_ang || !io->done_in)

@@ -23,6 +23,7 @@ struct BxKernelParams {
   float* steps_out;
   float* truncation;
   float episode_length;
+  int observe;                 // env builds: skip the substeps (obs of the state passed in)
   int64_t num_envs;
   int32_t num_steps;  // >1: rollout, act is [T,B,A]
   // host path only (bx_step_host on mapped host memory): tile i starts i/grid of

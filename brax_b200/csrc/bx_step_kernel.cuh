@@ -1606,6 +1606,8 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
     ep_prev_done = p.done_in[env0 + (threadIdx.x & 31)];
     if (p.steps_in != nullptr) ep_steps = p.steps_in[env0 + (threadIdx.x & 31)];
   }
+  // observe (env builds): zero substeps -- the epilogue then sees the state passed in and a zero Info
+  const int iters = ((BX_FEAT & BXF_ENV) != 0 && p.observe != 0) ? 0 : h.iters;
   for (int step = 0; step < p.num_steps; step++) {
     __syncthreads();
     if (step > 0) {  // rollout: the actions of step t (step 0 came with the state)
@@ -1629,15 +1631,16 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
     {
       const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int i = threadIdx.x; i < h.n_zero * QS; i += blockDim.x) sq[h.q_ic * QS + i] = z;
-      if (h.iters == 0)  // contact_penetration = -1 (system.py:84)
+      if (iters == 0)  // contact_penetration = -1 (system.py:84)
         for (int i = threadIdx.x; i < (h.q_pre - h.q_ct) * QS; i += blockDim.x)
           sq[h.q_ct * QS + i] = i < h.nk * QS ? make_float4(0.f, 0.f, 0.f, -1.f) : z;
-      if (env_on) phase_env_before<MODE>(c, h);
+      // (observe: grasp's prologue -- action map and palm move, grasp.py:75-85 -- belongs to step)
+      if (env_on && !(p.observe != 0 && h.env_kind == BX_ENV_GRASP)) phase_env_before<MODE>(c, h);
     }
     __syncthreads();
     PT(1);
     if constexpr (MODE == BX_MODE_PBD) {
-      for (int it = 0; it < h.iters; it++) {
+      for (int it = 0; it < iters; it++) {
 #pragma unroll 1
         for (int half = 0; half < 2; half++) {
           phase_torques<MODE>(c, h, true);
@@ -1675,7 +1678,7 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
         }
       }
     } else {
-      for (int it = 0; it < h.iters; it++) {
+      for (int it = 0; it < iters; it++) {
         phase_body_kinetic(c, h);
         __syncthreads();
         phase_torques<MODE>(c, h, false);

@@ -183,12 +183,22 @@ class Env:
     self.observation_size = env.obs_size(self.sys.desc)
     self.action_size = self.sys.act_size
 
-  def reset(self, batch: int = None, device=None, rng=None, velocity_noise: float = 0.0) -> State:
-    """Initial state from the recorded `default_qp()`.  The reference draws joint
-    angles and runs forward kinematics (ant.py:198-204, system.py:112-242: row N3,
-    not built); here only body velocities can be perturbed.  obs is that of a zero
-    step (filled by the first `step`), reward = done = 0 and zero metrics as in the
-    reference's reset (ant.py:206-220)."""
+  def reset(self, batch: int = None, device=None, rng=None, velocity_noise: float = 0.0, seed: int = None,
+            joint_angle=None, joint_velocity=None) -> State:
+    """`Env.reset` (ant.py:198-220, humanoid.py:223-245, fetch.py:36-53, grasp.py:55-72).
+
+    On a CUDA `device` this is the reference's recipe in two launches: joint angles
+    `default_angle() + U(-s, s)` and joint velocities `U(-s, s)` per env (s = reset_noise_scale;
+    torch generator seeded with `seed` -- same distribution as the reference's JAX draws, not the
+    same stream; pass `joint_angle=` / `joint_velocity=` [B,D] to supply your own) ->
+    `sys.default_qp(joint_angle, joint_velocity)` (bx_default_qp: forward kinematics) ->
+    fetch: a random target (fetch.py:38-40) -> obs = `_get_obs(qp, info)` with a zero Info
+    (`System.observe`).  reward = done = 0 and zero metrics as in the reference.
+
+    Without a device (numpy): the recorded `default_qp()` with optional noise on the body
+    velocities only, obs zeros (the host path has no reset kernel)."""
+    if device is not None and str(device).startswith('cuda') and self.sys.desc.reset:
+      return self._reset_cuda(batch, device, seed, joint_angle, joint_velocity)
     qp = self.sys.default_qp(batch=batch)
     if velocity_noise:
       rng = rng or np.random.default_rng(0)
@@ -208,6 +218,31 @@ class Env:
       obs, rew, done = to(obs), to(rew), to(done)
       met = {k: to(v) for k, v in met.items()}
     return State(qp, obs, rew, done, met)
+
+  def _reset_cuda(self, batch, device, seed, joint_angle, joint_velocity) -> State:
+    import torch
+    b = int(batch) if batch is not None else 1
+    dev = torch.device(device)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(int(seed or 0))
+    nd, scale = self.sys.num_joint_dof, float(getattr(self, '_reset_noise_scale', 0.0))
+    noise = lambda: (torch.rand(b, nd, generator=gen, device=dev, dtype=torch.float32) * 2 - 1) * scale  # noqa: E731
+    if joint_angle is None:
+      joint_angle = torch.from_numpy(self.sys.default_angle()).to(dev) + noise()    # ant.py:202
+    if joint_velocity is None:
+      joint_velocity = noise()                                                      # ant.py:203
+    qp = self.sys.default_qp(joint_angle=joint_angle.reshape(b, nd), joint_velocity=joint_velocity.reshape(b, nd))
+    qp = self._place_targets(qp, gen)
+    obs = self.sys.observe(qp)
+    zero = torch.zeros(b, dtype=torch.float32, device=dev)
+    met = {k: zero for k in self.env.metric_names()}
+    if batch is None:
+      qp = _system.QP(*[getattr(qp, k)[0] for k in ('pos', 'rot', 'vel', 'ang')])
+      obs, zero, met = obs[0], zero[0], {k: v[0] for k, v in met.items()}
+    return State(qp, obs, zero, zero, met)
+
+  def _place_targets(self, qp, gen):
+    return qp
 
   def step(self, state: State, action) -> State:
     """`Env.step(state, action)` (ant.py:222, humanoid.py:246): one kernel launch."""
@@ -289,6 +324,17 @@ class Fetch(_TargetEnv):
   def __init__(self, legacy_spring=False, device: int = 0, seed: int = 0):
     super().__init__('fetch_spring' if legacy_spring else 'fetch', fetch_desc, device, seed)
 
+  def _place_targets(self, qp, gen):
+    # reset's `_random_target` (fetch.py:38-40, :124-134)
+    import math
+    import torch
+    b = qp.pos.shape[0]
+    u = torch.rand(b, 2, generator=gen, device=qp.pos.device, dtype=torch.float32)
+    dist = self.env.target_radius + self.env.target_distance * u[:, 0]
+    ang = (math.pi * 2.) * u[:, 1]
+    qp.pos[:, self.env.target_body] = torch.stack([dist * torch.cos(ang), dist * torch.sin(ang), torch.ones_like(dist)], -1)
+    return qp
+
 
 class Grasp(_TargetEnv):
   """brax/envs/grasp.py:25-198 (pbd; action_size = actuator dofs + 3 palm-target slots :140-142)."""
@@ -306,17 +352,23 @@ class EpisodeAutoReset:
   counter, truncation, done at the episode limit, and the reload of (qp, obs) from the first
   state where done.  torch CUDA states only.  episode_length None / 0: AutoResetWrapper alone."""
 
-  def __init__(self, env: Env, episode_length: int = 1000):
+  def __init__(self, env: Env, episode_length: int = 1000, resample: bool = False):
+    """resample: draw a NEW noisy first state (and its obs) before every step / rollout instead
+    of reusing the one `reset` stored -- per-episode reset noise (the reference
+    restarts every episode of an env from the same first state, wrappers.py:146-147).  Costs the
+    two reset launches (bx_default_qp + observe) per call."""
     self.env = env
     self.sys = env.sys
+    self.resample = bool(resample)
+    self._draws = 0
     self.episode_length = int(episode_length or 0)
     self.observation_size = env.observation_size
     self.action_size = env.action_size
 
   def reset(self, *args, first_obs=None, **kw) -> State:
     """As `env.reset`, plus info['steps'], info['truncation'] (wrappers.py:98-103) and
-    info['first_qp'], info['first_obs'] (wrappers.py:126-129).  The obs of the first state is the
-    caller's (`first_obs=`; reset / `_get_obs(default_qp)` is row N3) -- zeros if not given."""
+    info['first_qp'], info['first_obs'] (wrappers.py:126-129): the reset state and its obs
+    (`first_obs=` overrides the latter)."""
     st = self.env.reset(*args, **kw)
     if not _system._is_torch(st.qp.pos):
       raise ValueError('EpisodeAutoReset needs torch CUDA states: reset(batch, device=...)')
@@ -327,16 +379,21 @@ class EpisodeAutoReset:
                    first_qp=st.qp, first_obs=st.obs)
     return st
 
+  def _auto_reset(self, state: State):
+    first_qp, first_obs = state.info['first_qp'], state.info['first_obs']
+    if self.resample:
+      self._draws += 1
+      fresh = self.env.reset(int(state.qp.pos.shape[0]), device=state.qp.pos.device, seed=1_000_003 * self._draws)
+      first_qp, first_obs = fresh.qp, fresh.obs
+    return _system.AutoReset(first_qp, first_obs, state.done, state.info.get('steps'), self.episode_length)
+
   def step(self, state: State, action, rand=None) -> State:
-    ar = _system.AutoReset(state.info['first_qp'], state.info['first_obs'], state.done,
-                           state.info.get('steps'), self.episode_length)
-    return self.env._launch(state, action, rand, ar)
+    return self.env._launch(state, action, rand, self._auto_reset(state))
 
   def rollout(self, state: State, actions, rand=None):
     """T wrapped steps in ONE launch (the scan over `step` of a training / eval unroll).  Returns
     the final state and a dict of the per-step obs / reward / done / truncation / metrics."""
-    ar = _system.AutoReset(state.info['first_qp'], state.info['first_obs'], state.done,
-                           state.info.get('steps'), self.episode_length)
+    ar = self._auto_reset(state)
     if rand is None and isinstance(self.env, _TargetEnv):
       rand = self.env._uniform(state.qp.pos, (int(actions.shape[0]),) + tuple(state.qp.pos.shape[:-2]))
     qp, info, eo = self.sys.rollout(state.qp, actions, env=True, env_rand=rand, auto_reset=ar, info=False)

@@ -247,6 +247,21 @@ class System:
       arrs = [torch.from_numpy(a).to(device) for a in arrs]
     return QP(*arrs)
 
+  def observe(self, qp: QP):
+    """obs [B,O] of a state as `Env.reset` builds it: `_get_obs(qp, info)` with a zero Info and a
+    zero action (envs/ant.py:203-204, humanoid.py:230-231, fetch.py:41-42, grasp.py:60-61) -- the
+    env epilogue of the step kernel without its substeps, one launch.  torch CUDA tensors;
+    systems built with an EnvDesc."""
+    import torch
+    if self.env is None:
+      raise ValueError('this System was built without an EnvDesc')
+    if not _is_torch(qp.pos):
+      raise RuntimeError('observe takes torch CUDA tensors (no CPU fallback)')
+    b = int(qp.pos.shape[0]) if qp.pos.dim() == 3 else 1
+    shape = (b, self.act_size) if qp.pos.dim() == 3 else (self.act_size,)
+    act = torch.zeros(shape, dtype=torch.float32, device=qp.pos.device)
+    return self._step_torch(qp, act, 1, False, True, None, None, False, observe=True)[2]['obs']
+
   def _default_qp_torch(self, joint_angle, joint_velocity) -> QP:
     import torch
     if not self.desc.reset:
@@ -414,9 +429,10 @@ class System:
     io.first_pos = io.first_rot = io.first_vel = io.first_ang = io.first_obs = None
     io.done_in = io.steps_in = io.steps_out = io.truncation = None
     io.episode_length = 0.0
+    io.observe = 0
 
   def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False, env_rand=None,
-                  auto_reset=None, info: bool = True):
+                  auto_reset=None, info: bool = True, observe: bool = False):
     """env_rand: (fetch / grasp) uniforms of the target teleport, [B,3] or [T,B,3]."""
     import torch
     batched, b = self._shapes(qp.pos.shape)
@@ -469,8 +485,9 @@ class System:
       io.steps_out = extra.data_ptr()
       io.truncation = extra.data_ptr() + 4 * b
       io.episode_length = float(ar.episode_length or 0)
+    io.observe = int(observe)
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-    if self.autotune and steps == 1 and b >= 1024 and b not in self._tuned:
+    if self.autotune and not observe and steps == 1 and b >= 1024 and b not in self._tuned:
       # first call at this batch size: time the candidate CTA sizes once
       self._tuned.add(b)
       if self._lib.bx_system_autotune(self._h, b, C.byref(io), stream) != 0:

@@ -111,3 +111,25 @@ def test_wrapper_oracle_matches_reference():
       np.testing.assert_allclose(r['qp'][k], g[k + '_o'][:, t], rtol=0, atol=1e-9, err_msg='%s step %d' % (k, t))
     for k in ('obs', 'reward', 'done', 'steps', 'truncation', 'metrics'):
       np.testing.assert_allclose(r[k], g[k][:, t], rtol=0, atol=1e-9, err_msg='%s step %d' % (k, t))
+
+
+def test_reset_obs_oracle_matches_reference():
+  """The obs `Env.reset` returns (`_get_obs(qp, sys.info(qp))`, tests/golden/reset_obs.npz from
+  the reference's own env classes): the oracle reproduces it given the reference's info.contact,
+  and with a ZERO Info -- what the fused observe launch uses -- wherever the reference's
+  `sys.info(qp).contact` is zero (always for the envs' own reset recipe; with joint-velocity noise
+  a collider resting exactly on the plane can flip `penetration > 0` by rounding)."""
+  g = np.load(os.path.join(util.GOLDEN, 'reset.npz'))
+  go = np.load(os.path.join(util.GOLDEN, 'reset_obs.npz'))
+  for name in ('ant', 'ant_nocfrc', 'ant_spring', 'humanoid', 'humanoid_spring', 'fetch', 'grasp'):
+    sysname, env = VARIANTS[name]
+    desc = util.load_desc(sysname)
+    qp = {k: g[sysname + '/' + k] for k in util.QP_KEYS}
+    o = Oracle(desc, np.float64)
+    ref = go[name + '/obs']
+    full = env_oracle.reset_obs(desc, env, o, qp, np.float64, go[name + '/contact_vel'], go[name + '/contact_ang'])
+    np.testing.assert_allclose(full, ref, rtol=0, atol=1e-12, err_msg=name)
+    quiet = (np.abs(go[name + '/contact_vel']).max(axis=(1, 2)) == 0) | (env.kind == 'humanoid')
+    assert quiet[0] and quiet.sum() >= 4, name          # draw 0 is the noise-free default state
+    zero = env_oracle.reset_obs(desc, env, o, qp, np.float64)
+    np.testing.assert_allclose(zero[quiet], ref[quiet], rtol=0, atol=1e-12, err_msg=name)

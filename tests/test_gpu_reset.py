@@ -73,3 +73,115 @@ def test_default_qp_argument_errors():
     s.default_qp(joint_angle=torch.zeros(4, s.num_joint_dof))          # CPU tensor: no fallback
   with pytest.raises(RuntimeError):
     s.default_qp(joint_angle=torch.zeros(4, s.num_joint_dof + 1).cuda())
+
+
+@pytest.mark.parametrize('variant', ['ant', 'ant_spring', 'humanoid', 'humanoid_spring', 'fetch', 'grasp'])
+def test_observe_matches_reference_reset_obs(variant):
+  """System.observe (the env epilogue without substeps, zero Info) on the golden reset states
+  against the obs of the reference's own `_get_obs(qp, sys.info(qp))` (reset_obs.npz), wherever
+  the reference's info.contact is zero, and against the float32 oracle everywhere."""
+  torch = _torch()
+  from oracle import env_oracle
+  from oracle.oracle import Oracle
+  from tests.test_gpu_env import _env
+  from brax_b200.system import QP
+  go = np.load(os.path.join(util.GOLDEN, 'reset_obs.npz'))
+  sysname, env = _env(variant)
+  ins = {k: G[sysname + '/' + k].astype(np.float32) for k in util.QP_KEYS}
+  qp = QP(*[torch.from_numpy(ins[k]).cuda() for k in util.QP_KEYS])
+  obs = env.sys.observe(qp).cpu().numpy()
+  assert obs.shape == (ins['pos'].shape[0], env.observation_size)
+  want = env_oracle.reset_obs(env.sys.desc, env.env, Oracle(env.sys.desc, np.float32), ins, np.float32)
+  # 1e-5 relative + the float32 conditioning of the obs terms that cancel (humanoid's com_ang)
+  w64 = env_oracle.reset_obs(env.sys.desc, env.env, Oracle(env.sys.desc, np.float64), ins, np.float64)
+  tol = 5e-6 + 1e-5 * np.abs(want) + 4 * np.abs(want - w64)
+  assert (np.abs(obs - want) <= tol).all(), float((np.abs(obs - want) - tol).max())
+  quiet = (np.abs(go[variant + '/contact_vel']).max(axis=(1, 2)) == 0) | (env.env.kind == 'humanoid')
+  np.testing.assert_allclose(obs[quiet], go[variant + '/obs'][quiet], rtol=1e-5, atol=2e-5)
+  # the state passes through untouched; unbatched call == row 2
+  q2, _, eo = env.sys._step_torch(qp, torch.zeros(obs.shape[0], env.action_size).cuda(), 1, False, True, None, None,
+                                  False, observe=True)
+  for k in util.QP_KEYS:
+    assert torch.equal(getattr(q2, k), getattr(qp, k)), k
+  one = env.sys.observe(QP(*[getattr(qp, k)[2] for k in util.QP_KEYS]))
+  assert torch.equal(one, torch.from_numpy(obs[2]).cuda())
+
+
+@pytest.mark.parametrize('variant', ['ant', 'humanoid', 'fetch', 'grasp'])
+def test_env_reset_on_the_gpu(variant):
+  """Env.reset(batch, device='cuda'): the reference's recipe -- noisy joint state -> default_qp
+  (forward kinematics) -> obs -- against the oracles on the joint state that was drawn."""
+  torch = _torch()
+  from oracle import env_oracle, reset_oracle
+  from oracle.oracle import Oracle
+  from tests.test_gpu_env import _env
+  sysname, env = _env(variant)
+  b = 333
+  st = env.reset(b, device='cuda', seed=3)
+  st2 = env.reset(b, device='cuda', seed=3)
+  assert torch.equal(st.qp.pos, st2.qp.pos) and torch.equal(st.obs, st2.obs)
+  assert st.obs.shape == (b, env.observation_size) and float(st.reward.abs().max()) == 0 and float(st.done.max()) == 0
+  assert set(st.metrics) == set(env.env.metric_names())
+  desc = env.sys.desc
+  scale = getattr(env, '_reset_noise_scale', 0.0)
+  # redraw the joint state with the same generator to check the kernel chain on it
+  gen = torch.Generator(device='cuda'); gen.manual_seed(3)
+  nd = env.sys.num_joint_dof
+  ja = torch.from_numpy(env.sys.default_angle()).cuda() + (torch.rand(b, nd, generator=gen, device='cuda') * 2 - 1) * scale
+  jv = (torch.rand(b, nd, generator=gen, device='cuda') * 2 - 1) * scale
+  want = reset_oracle.default_qp(desc, ja.cpu().numpy(), jv.cpu().numpy(), np.float32)
+  pos = st.qp.pos.cpu().numpy()
+  if env.env.kind == 'fetch':     # the random target: on the circle of fetch.py:124-134, z = 1
+    t = pos[:, env.env.target_body]
+    r = np.hypot(t[:, 0], t[:, 1])
+    assert (r >= env.env.target_radius - 1e-4).all() and (r <= env.env.target_radius + env.env.target_distance + 1e-4).all()
+    assert np.allclose(t[:, 2], 1.0) and np.std(np.arctan2(t[:, 1], t[:, 0])) > 1.0
+    want['pos'][:, env.env.target_body] = t
+  for k in util.QP_KEYS:
+    np.testing.assert_allclose(getattr(st.qp, k).cpu().numpy(), want[k], rtol=1e-5, atol=3e-6, err_msg=k)
+  if scale:
+    assert np.std(pos[:, 1, 2]) > 1e-4                      # per-env noise reached the poses
+  ins = {k: getattr(st.qp, k).cpu().numpy() for k in util.QP_KEYS}
+  wobs = env_oracle.reset_obs(desc, env.env, Oracle(desc, np.float32), ins, np.float32)
+  w64 = env_oracle.reset_obs(desc, env.env, Oracle(desc, np.float64), ins, np.float64)
+  tol = 5e-6 + 1e-5 * np.abs(wobs) + 4 * np.abs(wobs - w64)
+  assert (np.abs(st.obs.cpu().numpy() - wobs) <= tol).all()
+  # caller-supplied joint state; unbatched reset
+  st3 = env.reset(b, device='cuda', joint_angle=ja, joint_velocity=jv)
+  np.testing.assert_allclose(st3.qp.rot.cpu().numpy(), want['rot'], rtol=1e-5, atol=3e-6)
+  one = env.reset(device='cuda', seed=1)
+  assert one.qp.pos.shape == (desc.num_bodies, 3) and one.obs.shape == (env.observation_size,)
+  # and the state steps: a wrapped rollout from it stays finite
+  from brax_b200 import envs
+  w = envs.EpisodeAutoReset(env, 5)
+  s0 = w.reset(b, device='cuda', seed=2)
+  assert torch.equal(s0.info['first_obs'], s0.obs)
+  acts = torch.rand(12, b, env.action_size, device='cuda') * 2 - 1
+  last, eo = w.rollout(s0, acts)
+  assert bool(torch.isfinite(eo['obs']).all()) and float(eo['truncation'].sum()) > 0
+  done = eo['done'][4] > 0                 # episode_length 5: envs without an earlier done end at step 5
+  early = eo['done'][:4].sum(0) > 0
+  assert bool((done | early).all()) and float(done.float().mean()) > 0.5
+  assert torch.equal(eo['obs'][4][done], s0.obs[done])
+
+
+def test_resampled_auto_reset_draws_new_first_states():
+  """EpisodeAutoReset(resample=True): every reset inside the launch starts from a freshly drawn
+  noisy state (two reset launches per call), not from the state `reset` stored."""
+  torch = _torch()
+  from brax_b200 import envs
+  from tests.test_gpu_env import _env
+  _, env = _env('ant')
+  b = 256
+  w = envs.EpisodeAutoReset(env, 2, resample=True)
+  st = w.reset(b, device='cuda', seed=0)
+  act = torch.zeros(b, env.action_size, device='cuda')
+  st = w.step(st, act)
+  st = w.step(st, act)                      # steps == 2: every env is reset ...
+  assert bool((st.done > 0).all())
+  assert not torch.equal(st.qp.pos, st.info['first_qp'].pos)   # ... to a state that is not the stored one
+  z0 = st.qp.pos[:, 0, 2]
+  assert float((z0 - st.info['first_qp'].pos[:, 0, 2]).abs().max()) < 0.2   # but a reset pose all the same
+  st = w.step(st, act)
+  st2 = w.step(st, act)
+  assert bool((st2.done > 0).all()) and not torch.equal(st2.qp.pos, st.qp.pos)
