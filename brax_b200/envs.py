@@ -3,7 +3,7 @@
 
     env = envs.Ant(use_contact_forces=True)        # brax/envs/ant.py:173-196
     env = envs.Humanoid()                          # brax/envs/humanoid.py:200-221
-    state = env.reset(batch=8192, device='cuda')   # default_qp (+ noise on the velocities)
+    state = env.reset(batch=8192, device='cuda')   # noisy joint state -> default_qp (FK) -> obs: two launches
     state = env.step(state, action)                # ONE launch: physics + obs/reward/done/metrics
 
 `State` carries the reference's fields (brax/envs/env.py:28-37): qp, obs, reward,
@@ -11,11 +11,11 @@ done, metrics (dict, the reference's keys in the reference's order), info.
 `env.sys` is the `brax_b200.System` (so `env.sys.step` stays available).
 
 What runs on the GPU: `sys.step` and, in the same launch, everything the
-reference computes after it in `Ant.step` / `Humanoid.step` (ant.py:222-281,
-humanoid.py:246-340).  What does not: `reset`'s forward kinematics
-(`default_qp(joint_angle=...)`, system.py:112-242, row N3) -- `reset` here starts
-from the recorded `default_qp()` and perturbs velocities only; wrappers and
-agents are callers and stay reference code.  No CPU fallback.
+reference computes after it in `Ant.step` / `Humanoid.step` / `Fetch.step` / `Grasp.step`
+(ant.py:222-281, humanoid.py:246-340, fetch.py:54-122, grasp.py:73-186), optionally with
+EpisodeWrapper + AutoResetWrapper folded in (`EpisodeAutoReset`); `reset` (row N3): the forward
+kinematics of `default_qp(joint_angle, joint_velocity)` (system.py:112-242, bx_default_qp) and
+the reset obs (`System.observe`).  Agents are callers and stay reference code.  No CPU fallback.
 """
 import ctypes as C
 import dataclasses
