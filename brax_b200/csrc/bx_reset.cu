@@ -2,7 +2,8 @@
 // for a batch of environments: forward kinematics down the joint tree and the lowering of free
 // trees onto the xy plane.  One warp per 32 envs, lane = env; the tile's poses live in shared
 // memory as rows [10 per body: pos 3, rot 4, ang 3][32 lanes] and leave through coalesced
-// stores of the tile's contiguous [32, N, w] output spans.
+// stores of the tile's contiguous [32, N, w] output spans.  The static tables (11 KB) are copied
+// into shared memory first: the joint / probe loops are one warp's serial chain of table reads.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -12,12 +13,21 @@
 #define ROW(r) sm[(r) * 32 + lane]
 
 __global__ void __launch_bounds__(32)
-bx_reset_kernel(const bx_reset_desc* __restrict__ t, int nb, int64_t num_envs,
+bx_reset_kernel(const bx_reset_desc* __restrict__ gt, int nb, int64_t num_envs,
                 const float* __restrict__ joint_angle, const float* __restrict__ joint_velocity,
                 float* __restrict__ pos_o, float* __restrict__ rot_o, float* __restrict__ vel_o,
                 float* __restrict__ ang_o) {
-  extern __shared__ float sm[];
+  extern __shared__ float smem_all[];
   const int lane = threadIdx.x;
+  constexpr int TAB_WORDS = (sizeof(bx_reset_desc) + 15) / 16 * 4;
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(gt);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(smem_all);
+    for (int i = lane; i < static_cast<int>(sizeof(bx_reset_desc) / 4); i += 32) dst[i] = src[i];
+  }
+  __syncwarp();
+  const bx_reset_desc* t = reinterpret_cast<const bx_reset_desc*>(smem_all);
+  float* sm = smem_all + TAB_WORDS;
   const int64_t env0 = static_cast<int64_t>(blockIdx.x) * 32;
   const int nenv = static_cast<int>(num_envs - env0 < 32 ? num_envs - env0 : 32);
   const int64_t e = env0 + (lane < nenv ? lane : 0);
@@ -85,7 +95,7 @@ bx_reset_kernel(const bx_reset_desc* __restrict__ t, int nb, int64_t num_envs,
 cudaError_t bx_reset_launch(const bx_reset_desc* d_tables, int nb, int64_t num_envs, const float* joint_angle,
                             const float* joint_velocity, float* pos, float* rot, float* vel, float* ang,
                             cudaStream_t stream) {
-  const size_t smem = static_cast<size_t>(nb) * 10 * 32 * sizeof(float);
+  const size_t smem = (sizeof(bx_reset_desc) + 15) / 16 * 16 + static_cast<size_t>(nb) * 10 * 32 * sizeof(float);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(bx_reset_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));

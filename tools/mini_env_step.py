@@ -1,5 +1,5 @@
-"""Tiny driver for compute-sanitizer: env steps (fused epilogue) + a short rollout on 70 envs
-(two full tiles + a ragged one).  usage: mini_env_step.py ant|humanoid|fetch|grasp [legacy_spring]"""
+"""Tiny driver (ncu launch lists): Env.reset (bx_default_qp + observe), env steps (fused epilogue),
+a short rollout and a wrapped (episode + auto-reset) rollout on 70 envs (two full tiles + a ragged one).  usage: mini_env_step.py ant|humanoid|fetch|grasp [legacy_spring]"""
 import os
 import sys
 
@@ -25,5 +25,8 @@ kw = {}
 if name in ('fetch', 'grasp'):
   kw['env_rand'] = torch.rand((3, b, 3), device='cuda')
 qp, info, eo = env.sys.rollout(st.qp, acts, env=True, **kw)
+w = envs.EpisodeAutoReset(env, 2)
+last, ew = w.rollout(w.reset(b, device='cuda', seed=1), acts)
 torch.cuda.synchronize()
+assert float(ew['truncation'].sum()) > 0
 print(name, 'ok', float(eo['obs'].abs().max()), float(eo['reward'].mean()))
