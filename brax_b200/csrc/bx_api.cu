@@ -973,6 +973,7 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
   if (!s || !hio) return fail("NULL argument");
   if (B <= 0) return fail("num_envs must be positive");
   if (hio->first_pos) return fail("auto-reset inputs are supported on the device path only (bx_step / bx_rollout)");
+  if (hio->observe) return fail("observe is supported on the device path only (bx_step)");
   if (!hio->pos || !hio->rot || !hio->vel || !hio->ang || !hio->act || !hio->pos_o || !hio->rot_o ||
       !hio->vel_o || !hio->ang_o)
     return fail("QP / act pointers must not be NULL");
