@@ -368,7 +368,10 @@ def run_gpu(args, desc):
     qps[j], _ = s.rollout(qps[j], acts[a0:a0 + roll_t])
     er[i][1].record()
   barrier()
-  ms_roll = float(sum(x.elapsed_time(y) for x, y in er))
+  # median launch x launches: one multi-millisecond hiccup of the box inside these few launches
+  # (seen about once per ten runs) would otherwise dominate the figure
+  ms_roll_each = sorted(x.elapsed_time(y) for x, y in er)
+  ms_roll = float(ms_roll_each[len(ms_roll_each) // 2]) * n_roll
   # "next" row N1, first piece: Joint.angle_vel of the new state as a kernel epilogue
   # (what every env's _get_obs asks for after the step); same timing method as `value`.
   for j in range(nsets):   # untimed: the allocator sees the larger output block of every set once
@@ -503,7 +506,7 @@ def run_gpu(args, desc):
                           'ms_per_step': ms_wenv / args.steps, 'episode_length': 1000}} if ms_env > 0 else None),
         'rollout': {'steps_per_launch': roll_t, 'launches': n_roll,
                     'value': world * b * roll_t * n_roll / (ms_roll * 1e-3), 'unit': UNIT,
-                    'ms_per_step': ms_roll / (roll_t * n_roll)},
+                    'ms_per_step': ms_roll / (roll_t * n_roll), 'timing': 'median launch'},
         'wall_s_timed_loop_incl_spin': t_wall,
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d,
                 'd2h_bytes_per_step': d2h, 'steps': e2e_steps, 'finite': e2e_finite,
