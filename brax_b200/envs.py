@@ -404,10 +404,72 @@ class EpisodeAutoReset:
     return last, eo
 
 
+@dataclasses.dataclass
+class EvalMetrics:
+  """brax/envs/wrappers.py:150-165."""
+  episode_metrics: Dict[str, Any]
+  active_episodes: Any
+  episode_steps: Any
+
+
+class EvalWrapper:
+  """`EvalWrapper` (brax/envs/wrappers.py:168-200) around an `EpisodeAutoReset`: per-env sums of
+  the metrics (and the reward) over the first episode, its length and the still-active flag, kept
+  in `state.info['eval_metrics']`.  `step` is the wrapped env's single launch plus three small
+  elementwise updates; `rollout` folds the recurrence over the T steps of ONE launch."""
+
+  def __init__(self, env: 'EpisodeAutoReset'):
+    self.env = env
+    self.sys = env.sys
+    self.observation_size, self.action_size = env.observation_size, env.action_size
+
+  def reset(self, *args, **kw) -> State:
+    import torch
+    st = self.env.reset(*args, **kw)
+    st.metrics['reward'] = st.reward                                   # wrappers.py:173
+    st.info['eval_metrics'] = EvalMetrics({k: torch.zeros_like(v) for k, v in st.metrics.items()},
+                                          torch.ones_like(st.reward), torch.zeros_like(st.reward))
+    return st
+
+  def step(self, state: State, action, rand=None) -> State:
+    import torch
+    em = state.info['eval_metrics']
+    if not isinstance(em, EvalMetrics):
+      raise ValueError('Incorrect type for state_metrics: %s' % type(em))
+    n = self.env.step(state, action, rand)
+    n.metrics['reward'] = n.reward                                     # wrappers.py:185
+    act = em.active_episodes
+    n.info['eval_metrics'] = EvalMetrics(
+        {k: em.episode_metrics[k] + n.metrics[k] * act for k in n.metrics},          # :189-191
+        act * (1 - n.done),                                                           # :192
+        torch.where(act > 0, n.info['steps'], em.episode_steps))                      # :187-188
+    return n
+
+  def rollout(self, state: State, actions, rand=None):
+    """T wrapped steps in one launch; the eval bookkeeping of all T steps from the [T,B] outputs."""
+    import torch
+    em = state.info['eval_metrics']
+    s0 = torch.where(state.done > 0, torch.zeros_like(state.done), state.info['steps'])
+    last, eo = self.env.rollout(state, actions, rand)
+    alive = torch.cumprod(1 - eo['done'], 0)                           # active after step t, given active before
+    before = torch.cat([torch.ones_like(alive[:1]), alive[:-1]], 0) * em.active_episodes   # active before step t
+    names = self.env.env.env.metric_names()
+    sums = {k: (eo['metrics'][..., i] * before).sum(0) for i, k in enumerate(names)}
+    sums['reward'] = (eo['reward'] * before).sum(0)
+    last.metrics['reward'] = last.reward
+    # while an env is active nothing has reset its counter: steps after step t = s0 + t + 1
+    last.info['eval_metrics'] = EvalMetrics(
+        {k: em.episode_metrics[k] + sums[k] for k in sums},
+        em.active_episodes * alive[-1],
+        torch.where(em.active_episodes > 0, s0 + before.sum(0), em.episode_steps))
+    return last, eo
+
+
 _ENVS = {'ant': Ant, 'humanoid': Humanoid, 'fetch': Fetch, 'grasp': Grasp}
 
 
-def create(env_name: str, episode_length: int = None, auto_reset: bool = False, **kwargs):
+def create(env_name: str, episode_length: int = None, auto_reset: bool = False, eval_metrics: bool = False,
+           **kwargs):
   """`envs.create(name, episode_length, auto_reset=...)` (brax/envs/__init__.py:74-90) for the
   mirrored envs.  'ant' is registered with use_contact_forces=True as in this fork
   (brax/envs/__init__.py:45).  Unlike the reference the wrappers are opt-in (defaults: the bare
@@ -418,7 +480,10 @@ def create(env_name: str, episode_length: int = None, auto_reset: bool = False, 
     kwargs.setdefault('use_contact_forces', True)
   env = _ENVS[env_name](**kwargs)
   if auto_reset:
-    return EpisodeAutoReset(env, episode_length)
+    env = EpisodeAutoReset(env, episode_length)
+    return EvalWrapper(env) if eval_metrics else env      # brax/envs/__init__.py:88-89
+  if eval_metrics:
+    raise ValueError('eval_metrics needs auto_reset=True (EvalWrapper reads info[\'steps\'])')
   if episode_length:
     raise ValueError('episode_length without auto_reset is not fused: wrap the env yourself')
   return env

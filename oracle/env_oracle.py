@@ -276,3 +276,14 @@ def reset_obs(desc, env, oracle, qp, dtype=np.float32, contact_vel=None, contact
   if env.kind == 'grasp':     # the epilogue is given the raw action; zeros map to mid-range, unused by the obs
     act = np.zeros((b, desc.act_size), dtype)
   return env_epilogue(desc, env, out['pos'], out, act, fa, fv, dtype)['obs']
+
+
+def eval_step(episode_metrics, active, episode_steps, metrics, reward, done, steps):
+  """EvalWrapper.step's bookkeeping (brax/envs/wrappers.py:186-200) on arrays [B] / [B,M]:
+  `metrics` are the step's env metrics with the reward appended last (`nstate.metrics['reward']`,
+  :185).  Returns the new (episode_metrics [B,M+1], active_episodes, episode_steps)."""
+  m = np.concatenate([np.asarray(metrics), np.asarray(reward)[:, None]], axis=-1)
+  new_steps = np.where(active > 0, steps, episode_steps)            # :187-188
+  new_metrics = episode_metrics + m * active[:, None]               # :189-191
+  new_active = active * (1 - done)                                  # :192
+  return new_metrics, new_active, new_steps

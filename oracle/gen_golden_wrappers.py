@@ -39,25 +39,32 @@ def wrapper_classes():
   path = os.path.join(refsys.REFERENCE, 'brax', 'envs', 'wrappers.py')
   src = open(path).read()
   tree = ast.parse(src)
-  keep = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name in ('EpisodeWrapper', 'AutoResetWrapper')]
+  keep = [n for n in tree.body if isinstance(n, ast.ClassDef)
+          and n.name in ('EpisodeWrapper', 'AutoResetWrapper', 'EvalMetrics', 'EvalWrapper')]
   mod = ast.Module(body=keep, type_ignores=[])
-  ns = {'brax_env': brax_env, 'jp': jp, 'copy': copy}
+  import typing
+  import flax
+  import jax
+  ns = {'brax_env': brax_env, 'jp': jp, 'copy': copy, 'flax': flax, 'jax': jax, 'Dict': typing.Dict}
   exec(compile(mod, path, 'exec'), ns)
-  return ns['EpisodeWrapper'], ns['AutoResetWrapper']
+  return ns['EpisodeWrapper'], ns['AutoResetWrapper'], ns['EvalWrapper']
 
 
 def main():
   out_dir = os.path.join(ROOT, 'tests', 'golden')
-  Episode, AutoReset = wrapper_classes()
+  Episode, AutoReset, Eval = wrapper_classes()
   import brax
   import brax.jumpy as jp
   ant = env_module('ant').Ant(use_contact_forces=True)
-  env = AutoReset(Episode(ant, EPISODE_LENGTH, 1))
+  # eval_metrics=True wraps EvalWrapper outermost (brax/envs/__init__.py:88-89); it only adds
+  # state.info['eval_metrics'] and metrics['reward'], so the sequences are those of the inner stack
+  env = Eval(AutoReset(Episode(ant, EPISODE_LENGTH, 1)))
   g = np.load(os.path.join(out_dir, 'ant_steps.npz'))
   rng = np.random.default_rng(5)
   names = None
   rec = {k: [] for k in ('pos', 'rot', 'vel', 'ang', 'done_in', 'steps_in', 'act', 'pos_o', 'rot_o', 'vel_o',
-                         'ang_o', 'obs', 'reward', 'done', 'steps', 'truncation', 'metrics')}
+                         'ang_o', 'obs', 'reward', 'done', 'steps', 'truncation', 'metrics',
+                         'eval_episode_metrics', 'eval_active_episodes', 'eval_episode_steps')}
   firsts = {k: [] for k in ('first_pos', 'first_rot', 'first_vel', 'first_ang', 'first_obs')}
   for seq in range(3):
     st = env.reset(jp.random_prngkey(seq))
@@ -84,8 +91,12 @@ def main():
       rec['done'].append(float(st.done))
       rec['steps'].append(float(st.info['steps']))
       rec['truncation'].append(float(st.info['truncation']))
-      names = names or list(st.metrics.keys())
+      names = names or [k for k in st.metrics.keys() if k != 'reward']
       rec['metrics'].append([float(st.metrics[k]) for k in names])
+      em = st.info['eval_metrics']                                   # wrappers.py:186-200
+      rec['eval_episode_metrics'].append([float(em.episode_metrics[k]) for k in names + ['reward']])
+      rec['eval_active_episodes'].append(float(em.active_episodes))
+      rec['eval_episode_steps'].append(float(em.episode_steps))
   shape = lambda v: np.asarray(v).reshape((3, T) + np.asarray(v[0]).shape)  # noqa: E731
   np.savez_compressed(os.path.join(out_dir, 'ant_wrapped_env.npz'),
                       episode_length=np.asarray(EPISODE_LENGTH), metric_names=np.asarray(names),

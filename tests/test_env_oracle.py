@@ -133,3 +133,18 @@ def test_reset_obs_oracle_matches_reference():
     assert quiet[0] and quiet.sum() >= 4, name          # draw 0 is the noise-free default state
     zero = env_oracle.reset_obs(desc, env, o, qp, np.float64)
     np.testing.assert_allclose(zero[quiet], ref[quiet], rtol=0, atol=1e-12, err_msg=name)
+
+
+def test_eval_wrapper_oracle_matches_reference():
+  """EvalWrapper (wrappers.py:168-200, the reference's class around the wrapped Ant of
+  gen_golden_wrappers.py): accumulated episode metrics, active flags and episode steps."""
+  g = np.load(os.path.join(util.GOLDEN, 'ant_wrapped_env.npz'))
+  nseq, t_n = g['done'].shape
+  m = g['metrics'].shape[-1]
+  em, act, es = np.zeros((nseq, m + 1)), np.ones(nseq), np.zeros(nseq)   # reset: wrappers.py:173-180
+  for t in range(t_n):
+    em, act, es = env_oracle.eval_step(em, act, es, g['metrics'][:, t], g['reward'][:, t], g['done'][:, t], g['steps'][:, t])
+    np.testing.assert_allclose(em, g['eval_episode_metrics'][:, t], rtol=0, atol=1e-12)
+    np.testing.assert_array_equal(act, g['eval_active_episodes'][:, t])
+    np.testing.assert_array_equal(es, g['eval_episode_steps'][:, t])
+  assert g['eval_active_episodes'][:, -1].sum() == 0 and g['eval_active_episodes'][:, 0].sum() == 2

@@ -499,3 +499,55 @@ def test_env_step_without_info_outputs():
   env.keep_info = True
   st = env.step(State(qp, None, None, None), act)
   assert torch.equal(st.info['physics'].contact.vel, i1.contact.vel)
+
+
+def test_eval_wrapper_on_reference_sequences():
+  """envs.create('ant', episode_length, auto_reset=True, eval_metrics=True) against the reference's
+  EvalWrapper(AutoResetWrapper(EpisodeWrapper(Ant))) sequences (ant_wrapped_env.npz): stepwise and
+  as one rollout launch."""
+  torch = _torch()
+  from brax_b200 import envs
+  from brax_b200.system import QP
+  g = np.load(os.path.join(util.GOLDEN, 'ant_wrapped_env.npz'))
+  length = int(g['episode_length'])
+  env = envs.create('ant', episode_length=length, auto_reset=True, eval_metrics=True)
+  assert isinstance(env, envs.EvalWrapper)
+  cu = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).cuda()  # noqa: E731
+  names = [str(k) for k in g['metric_names']]
+  nseq, t_n = g['done'].shape
+
+  def start():
+    first = QP(*[cu(g['first_' + k]) for k in util.QP_KEYS])
+    zero = cu(np.zeros(nseq))
+    st = envs.State(QP(*[cu(g[k][:, 0]) for k in util.QP_KEYS]), cu(g['first_obs']), zero, cu(g['done_in'][:, 0]),
+                    {k: zero for k in names + ['reward']},
+                    dict(first_qp=first, first_obs=cu(g['first_obs']), steps=cu(g['steps_in'][:, 0])))
+    st.info['eval_metrics'] = envs.EvalMetrics({k: torch.zeros_like(zero) for k in names + ['reward']},
+                                               torch.ones_like(zero), torch.zeros_like(zero))
+    return st
+
+  st = start()
+  for t in range(t_n):
+    st = env.step(st, cu(g['act'][:, t]))
+    em = st.info['eval_metrics']
+    np.testing.assert_array_equal(em.active_episodes.cpu().numpy(), g['eval_active_episodes'][:, t])
+    np.testing.assert_array_equal(em.episode_steps.cpu().numpy(), g['eval_episode_steps'][:, t])
+    got = torch.stack([em.episode_metrics[k] for k in names + ['reward']], -1).cpu().numpy()
+    np.testing.assert_allclose(got, g['eval_episode_metrics'][:, t], rtol=2e-3, atol=5e-3)
+  last, _ = env.rollout(start(), cu(np.swapaxes(g['act'], 0, 1)))
+  e1, e2 = st.info['eval_metrics'], last.info['eval_metrics']
+  assert torch.equal(e1.active_episodes, e2.active_episodes) and torch.equal(e1.episode_steps, e2.episode_steps)
+  for k in names + ['reward']:
+    assert torch.allclose(e1.episode_metrics[k], e2.episode_metrics[k], rtol=1e-5, atol=1e-5), k
+  # from the mirror's own reset: a 1000-step-limit eval of random actions stays consistent
+  ev = envs.create('ant', episode_length=6, auto_reset=True, eval_metrics=True)
+  s0 = ev.reset(128, device='cuda', seed=4)
+  acts = torch.rand(9, 128, ev.action_size, device='cuda') * 2 - 1
+  a, _ = ev.rollout(s0, acts)
+  b = s0
+  for t in range(9):
+    b = ev.step(b, acts[t])
+  ea, eb = a.info['eval_metrics'], b.info['eval_metrics']
+  assert float(ea.active_episodes.sum()) == 0 and float(ea.episode_steps.max()) == 6
+  assert torch.equal(ea.episode_steps, eb.episode_steps)
+  assert torch.allclose(ea.episode_metrics['reward'], eb.episode_metrics['reward'], rtol=1e-5, atol=1e-5)
