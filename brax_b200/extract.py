@@ -13,6 +13,8 @@ set raises `NotImplementedError` -- fail loudly, never fall back.
 """
 from typing import Any, Dict, List
 
+import itertools
+
 import numpy as np
 
 from brax_b200.desc import SystemDesc
@@ -151,40 +153,40 @@ def _reset_desc(sys) -> Dict[str, Any]:
       i = sys.body.index[dqp.name]
       pos[i], rot[i] = _a(vec_to_arr(dqp.pos)), _a(bmath.euler_to_quat(vec_to_arr(dqp.rot)))
       vel[i], ang[i] = _a(vec_to_arr(dqp.vel)), _a(vec_to_arr(dqp.ang))
-  joint_idxs, beg = [], 0
+  # dof slots of each joint in the flat joint-angle vector, in config order
+  slots, nxt = {}, 0
   for j in cfg.joints:
-    dof = sum([l.min != 0 or l.max != 0 for l in j.angle_limit])
-    joint_idxs.append((j, (beg, beg + dof)))
-    beg += dof
-  num_dof = beg
-  lineage = {j.child: j.parent for j in cfg.joints}
-  depth = {}
-  for child, parent in lineage.items():
-    depth[child] = 1
-    while parent in lineage:
-      parent = lineage[parent]
-      depth[child] += 1
-  joint_idxs = sorted(joint_idxs, key=lambda x: depth.get(x[0].parent, 0))
+    width = sum(1 for l in j.angle_limit if l.min != 0 or l.max != 0)
+    slots[j.name] = (nxt, nxt + width)
+    nxt += width
+  num_dof = nxt
+  parent_of = {j.child: j.parent for j in cfg.joints}
+
+  def root_and_depth(body):
+    hops = 0
+    while body in parent_of:
+      body, hops = parent_of[body], hops + 1
+    return body, hops
+
+  # parents before children: stable order by the depth of the joint's parent body
+  ordered = sorted(cfg.joints, key=lambda j: root_and_depth(j.parent)[1])
   joints = []
-  for j, (b0, b1) in joint_idxs:
-    take = list(range(b0, b1))
-    take += [num_dof] * (3 - len(take))
+  for j in ordered:
+    b0, b1 = slots[j.name]
+    take = list(range(b0, b1)) + [num_dof] * (3 - (b1 - b0))
     joints.append({
         'body_p': int(sys.body.index[j.parent]), 'body_c': int(sys.body.index[j.child]),
         'off_p': _l(vec_to_arr(j.parent_offset)), 'off_c': _l(vec_to_arr(j.child_offset)),
         'rot': _l(bmath.euler_to_quat(vec_to_arr(j.rotation))),
         'ref': _l(bmath.euler_to_quat(vec_to_arr(j.reference_rotation))),
         'take': [int(t) for t in take]})
-  fixed = {j.child for j, _ in joint_idxs}
-  if default is not None:
-    fixed |= {q.name for q in default.qps}
-  root_idx = {b.name: [i] for i, b in enumerate(cfg.bodies) if b.name not in fixed}
-  for j, _ in joint_idxs:
-    parent = j.parent
-    while parent in lineage:
-      parent = lineage[parent]
-    if parent in root_idx:
-      root_idx[parent].append(int(sys.body.index[j.child]))
+  # free trees: bodies that are neither a joint's child nor given a default qp, with their descendants
+  pinned = set(parent_of) | ({q.name for q in default.qps} if default is not None else set())
+  root_idx = {b.name: [i] for i, b in enumerate(cfg.bodies) if b.name not in pinned}
+  for j in ordered:
+    root = root_and_depth(j.parent)[0]
+    if root in root_idx:
+      root_idx[root].append(int(sys.body.index[j.child]))
   groups = []
   for children in root_idx.values():
     probes, zero = [], False
@@ -203,9 +205,9 @@ def _reset_desc(sys) -> Dict[str, Any]:
                            'radius': float(col.capsule.radius)})
         elif col.HasField('box'):
           q = bmath.euler_to_quat(vec_to_arr(col.rotation))
-          for i in range(8):
-            corner = np.array([i % 2 * 2 - 1, 2 * (i // 4) - 1, i // 2 % 2 * 2 - 1], dtype=float)
-            corner = _a(bmath.rotate(corner * _a(vec_to_arr(col.box.halfsize)), q)) + _a(vec_to_arr(col.position))
+          half = _a(vec_to_arr(col.box.halfsize))
+          for signs in itertools.product((-1.0, 1.0), repeat=3):   # the 8 corners; the min is order-free
+            corner = _a(bmath.rotate(np.array(signs) * half, q)) + _a(vec_to_arr(col.position))
             probes.append({'body': c, 'point': _l(corner), 'radius': 0.0})
         else:
           zero = True
