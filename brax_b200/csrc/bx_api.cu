@@ -884,8 +884,15 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
     if (!io->done) return fail("auto-reset needs the done output");
     if (io->obs && !io->first_obs) return fail("auto-reset with an obs output needs first_obs");
   }
+  const int repeat = io->action_repeat > 1 ? io->action_repeat : 1;
+  if (repeat > 1) {
+    if (!io->first_pos) return fail("action_repeat belongs to EpisodeWrapper: it needs the auto-reset inputs");
+    if (s->h.env_kind == BX_ENV_GRASP) return fail("action_repeat is not available for grasp (its action map runs per launch step)");
+    if (static_cast<int64_t>(num_steps) * repeat > 0x7fffffffLL) return fail("num_steps * action_repeat overflows");
+  }
+  p.action_repeat = repeat;
   p.num_envs = num_envs;
-  p.num_steps = num_steps;
+  p.num_steps = num_steps * repeat;
   p.stagger_ns = stagger_ns;
   p.dbg = g_dbg;
   const int64_t tiles = (num_envs + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA;

@@ -24,6 +24,7 @@ struct BxKernelParams {
   float* truncation;
   float episode_length;
   int observe;                 // env builds: skip the substeps (obs of the state passed in)
+  int action_repeat;           // EpisodeWrapper.action_repeat (auto-reset launches), >= 1
   int64_t num_envs;
   int32_t num_steps;  // >1: rollout, act is [T,B,A]
   // host path only (bx_step_host on mapped host memory): tile i starts i/grid of

@@ -1608,10 +1608,15 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
   }
   // observe (env builds): zero substeps -- the epilogue then sees the state passed in and a zero Info
   const int iters = ((BX_FEAT & BXF_ENV) != 0 && p.observe != 0) ? 0 : h.iters;
+  // EpisodeWrapper's action_repeat (wrappers.py:106-110): `repeat` env steps share one action, their
+  // rewards are summed, and the wrappers' bookkeeping / outputs happen after the last of them
+  const int repeat = (auto_reset && p.action_repeat > 1) ? p.action_repeat : 1;
+  float ep_reward = 0.f;
   for (int step = 0; step < p.num_steps; step++) {
+    const int ot = step / repeat, rep = step - ot * repeat;
     __syncthreads();
-    if (step > 0) {  // rollout: the actions of step t (step 0 came with the state)
-      const float* act = p.in[4] + static_cast<int64_t>(step) * p.num_envs * h.act_size;
+    if (step > 0 && rep == 0) {  // rollout: the actions of step t (step 0 came with the state)
+      const float* act = p.in[4] + static_cast<int64_t>(ot) * p.num_envs * h.act_size;
       const BxSeg sg = h.seg_in[4];
       if (full && span_bulk_ok(sg, act, env0)) {
         if (threadIdx.x == 0) {
@@ -1709,16 +1714,21 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
           // EpisodeWrapper.step / AutoResetWrapper.step bookkeeping of env `lane` (the same warp
           // wrote the scalars row in phase_env*)
           float4 s0 = QROW(c, h.q_env + EQ_S0);
-          ep_steps = ep_prev_done > 0.f ? 0.f : ep_steps;             // wrappers.py:133-135
-          ep_steps += 1.f;                                            // wrappers.py:112
-          const bool over = p.episode_length > 0.f && ep_steps >= p.episode_length;
-          const float trunc = over ? 1.f - s0.y : 0.f;                // wrappers.py:117-118
-          s0.y = over ? 1.f : s0.y;                                   // wrappers.py:116
-          ep_prev_done = s0.y;
-          QROW(c, h.q_env + EQ_S0) = s0;
-          if (p.truncation != nullptr && lane < nenv)
-            p.truncation[static_cast<int64_t>(step) * p.num_envs + env0 + lane] = trunc;
+          ep_reward = (rep == 0 ? 0.f : ep_reward) + s0.x;            // jp.sum(rewards) wrappers.py:110-111
+          if (rep == repeat - 1) {
+            s0.x = ep_reward;
+            ep_steps = ep_prev_done > 0.f ? 0.f : ep_steps;           // wrappers.py:133-135
+            ep_steps += static_cast<float>(repeat);                   // wrappers.py:112
+            const bool over = p.episode_length > 0.f && ep_steps >= p.episode_length;
+            const float trunc = over ? 1.f - s0.y : 0.f;              // wrappers.py:117-118
+            s0.y = over ? 1.f : s0.y;                                 // wrappers.py:116
+            ep_prev_done = s0.y;
+            QROW(c, h.q_env + EQ_S0) = s0;
+            if (p.truncation != nullptr && lane < nenv)
+              p.truncation[static_cast<int64_t>(ot) * p.num_envs + env0 + lane] = trunc;
+          }
         }
+        if (rep < repeat - 1) continue;  // (whole CTA) the env's next step with the same action
         __syncthreads();
         // qp = where(done, first_qp, qp) (wrappers.py:146): done envs reload their first state
         const bool done = lane < nenv && QROW(c, h.q_env + EQ_S0).y > 0.f;
@@ -1742,7 +1752,7 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
       __syncthreads();
       auto env_ptr = [&](int s) -> float* {
         return p.out[s] == nullptr ? nullptr
-            : p.out[s] + static_cast<int64_t>(step) * p.num_envs * h.seg_out[s].nper;
+            : p.out[s] + static_cast<int64_t>(ot) * p.num_envs * h.seg_out[s].nper;
       };
       bool vec = full;
 #pragma unroll

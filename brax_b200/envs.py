@@ -352,14 +352,17 @@ class EpisodeAutoReset:
   counter, truncation, done at the episode limit, and the reload of (qp, obs) from the first
   state where done.  torch CUDA states only.  episode_length None / 0: AutoResetWrapper alone."""
 
-  def __init__(self, env: Env, episode_length: int = 1000, resample: bool = False):
-    """resample: draw a NEW noisy first state (and its obs) before every step / rollout instead
+  def __init__(self, env: Env, episode_length: int = 1000, action_repeat: int = 1, resample: bool = False):
+    """action_repeat: EpisodeWrapper's (wrappers.py:106-111): every step runs that many env steps on
+    the same action inside the launch and returns the sum of their rewards.
+    resample: draw a NEW noisy first state (and its obs) before every step / rollout instead
     of reusing the one `reset` stored -- per-episode reset noise (the reference
     restarts every episode of an env from the same first state, wrappers.py:146-147).  Costs the
     two reset launches (bx_default_qp + observe) per call."""
     self.env = env
     self.sys = env.sys
     self.resample = bool(resample)
+    self.action_repeat = max(1, int(action_repeat or 1))
     self._draws = 0
     self.episode_length = int(episode_length or 0)
     self.observation_size = env.observation_size
@@ -385,9 +388,12 @@ class EpisodeAutoReset:
       self._draws += 1
       fresh = self.env.reset(int(state.qp.pos.shape[0]), device=state.qp.pos.device, seed=1_000_003 * self._draws)
       first_qp, first_obs = fresh.qp, fresh.obs
-    return _system.AutoReset(first_qp, first_obs, state.done, state.info.get('steps'), self.episode_length)
+    return _system.AutoReset(first_qp, first_obs, state.done, state.info.get('steps'), self.episode_length,
+                             self.action_repeat)
 
   def step(self, state: State, action, rand=None) -> State:
+    if rand is None and self.action_repeat > 1 and isinstance(self.env, _TargetEnv):
+      rand = self.env._uniform(state.qp.pos, (self.action_repeat,) + tuple(state.qp.pos.shape[:-2]))
     return self.env._launch(state, action, rand, self._auto_reset(state))
 
   def rollout(self, state: State, actions, rand=None):
@@ -395,7 +401,7 @@ class EpisodeAutoReset:
     the final state and a dict of the per-step obs / reward / done / truncation / metrics."""
     ar = self._auto_reset(state)
     if rand is None and isinstance(self.env, _TargetEnv):
-      rand = self.env._uniform(state.qp.pos, (int(actions.shape[0]),) + tuple(state.qp.pos.shape[:-2]))
+      rand = self.env._uniform(state.qp.pos, (int(actions.shape[0]) * self.action_repeat,) + tuple(state.qp.pos.shape[:-2]))
     qp, info, eo = self.sys.rollout(state.qp, actions, env=True, env_rand=rand, auto_reset=ar, info=False)
     names = self.env.env.metric_names()
     metrics = {k: eo['metrics'][-1, ..., i] for i, k in enumerate(names)}
@@ -468,8 +474,8 @@ class EvalWrapper:
 _ENVS = {'ant': Ant, 'humanoid': Humanoid, 'fetch': Fetch, 'grasp': Grasp}
 
 
-def create(env_name: str, episode_length: int = None, auto_reset: bool = False, eval_metrics: bool = False,
-           **kwargs):
+def create(env_name: str, episode_length: int = None, action_repeat: int = 1, auto_reset: bool = False,
+           eval_metrics: bool = False, **kwargs):
   """`envs.create(name, episode_length, auto_reset=...)` (brax/envs/__init__.py:74-90) for the
   mirrored envs.  'ant' is registered with use_contact_forces=True as in this fork
   (brax/envs/__init__.py:45).  Unlike the reference the wrappers are opt-in (defaults: the bare
@@ -480,10 +486,10 @@ def create(env_name: str, episode_length: int = None, auto_reset: bool = False, 
     kwargs.setdefault('use_contact_forces', True)
   env = _ENVS[env_name](**kwargs)
   if auto_reset:
-    env = EpisodeAutoReset(env, episode_length)
+    env = EpisodeAutoReset(env, episode_length, action_repeat)
     return EvalWrapper(env) if eval_metrics else env      # brax/envs/__init__.py:88-89
   if eval_metrics:
     raise ValueError('eval_metrics needs auto_reset=True (EvalWrapper reads info[\'steps\'])')
-  if episode_length:
-    raise ValueError('episode_length without auto_reset is not fused: wrap the env yourself')
+  if episode_length or (action_repeat or 1) > 1:
+    raise ValueError('episode_length / action_repeat without auto_reset are not fused: wrap the env yourself')
   return env

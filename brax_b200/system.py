@@ -81,6 +81,7 @@ class AutoReset:
   done: Any                 # state.done of the state passed in [B]
   steps: Any = None         # state.info['steps'] [B] (None: zeros)
   episode_length: int = 0   # EpisodeWrapper.episode_length; 0 = no EpisodeWrapper
+  action_repeat: int = 1    # EpisodeWrapper.action_repeat (wrappers.py:106-111)
 
 
 class HostBuffers:
@@ -430,6 +431,7 @@ class System:
     io.done_in = io.steps_in = io.steps_out = io.truncation = None
     io.episode_length = 0.0
     io.observe = 0
+    io.action_repeat = 0
 
   def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False, env_rand=None,
                   auto_reset=None, info: bool = True, observe: bool = False):
@@ -470,7 +472,8 @@ class System:
       out[name] = flat[off:off + cnt].view(shape)
       setattr(io, name, base + 4 * off if cnt else None)
     if env_rand is not None:
-      env_rand = prep(env_rand, steps * b * 3)
+      rep = int(auto_reset.action_repeat or 1) if auto_reset is not None else 1
+      env_rand = prep(env_rand, steps * rep * b * 3)
       io.env_rand = env_rand.data_ptr()
     if auto_reset is not None:
       ar = auto_reset
@@ -485,6 +488,7 @@ class System:
       io.steps_out = extra.data_ptr()
       io.truncation = extra.data_ptr() + 4 * b
       io.episode_length = float(ar.episode_length or 0)
+      io.action_repeat = int(ar.action_repeat or 1)
     io.observe = int(observe)
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     if self.autotune and not observe and steps == 1 and b >= 1024 and b not in self._tuned:

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BX_ABI_VERSION 7
+#define BX_ABI_VERSION 8
 
 /* dynamics_mode (base.py:179-201) */
 #define BX_MODE_PBD 0
@@ -298,6 +298,11 @@ typedef struct bx_step_io {
    * sys.info(qp).contact is zero at a resting pose up to rounding-level flips of `penetration > 0`).
    * The QP outputs are the inputs; reward / done / metrics are those of a zero-length step. */
   int32_t observe;
+  /* EpisodeWrapper.action_repeat (wrappers.py:106-111; auto-reset launches only, 0 / 1 = none): every
+   * wrapped step runs `action_repeat` env steps on the same action, sums their rewards and applies
+   * the episode / reset logic once after the last; steps advance by action_repeat.  act and the
+   * outputs stay [T,...]; env_rand, if given, is [T * action_repeat, B, 3] (one draw per env step). */
+  int32_t action_repeat;
 } bx_step_io;
 
 /* Creates a system on CUDA device `device` (tables uploaded once).  Returns 0

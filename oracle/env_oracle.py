@@ -232,22 +232,29 @@ def env_epilogue(desc, env, pos_before, out, act, flat_angle, flat_vel, dtype=np
 
 
 def wrapped_step(desc, env, oracle, qp, done_in, steps_in, act, first_qp, first_obs, episode_length,
-                 dtype=np.float32, rand=None):
-  """One step of AutoResetWrapper(EpisodeWrapper(env, episode_length, action_repeat=1))
+                 dtype=np.float32, rand=None, action_repeat=1):
+  """One step of AutoResetWrapper(EpisodeWrapper(env, episode_length, action_repeat))
   (brax/envs/wrappers.py:131-148 around :105-120), as `envs.create` composes them
   (brax/envs/__init__.py:74-90).  qp / first_qp: dicts pos rot vel ang [B,N,*];
-  oracle: the C physics oracle of the same dtype.  Returns qp (dict), obs, reward, done,
-  metrics, steps, truncation."""
+  oracle: the C physics oracle of the same dtype; rand: [B,3] or, with action_repeat > 1,
+  [action_repeat,B,3] (one draw per env step).  Returns qp (dict), obs, reward, done, metrics,
+  steps, truncation."""
   dt = np.dtype(dtype).type
   done_in, steps = np.asarray(done_in, dtype), np.asarray(steps_in, dtype)
   steps = np.where(done_in > 0, dt(0), steps)                       # wrappers.py:133-135
-  pos_in, act_in = env_prologue(desc, env, qp['pos'], act, dtype)
-  out = oracle.step(pos_in, qp['rot'], qp['vel'], qp['ang'], act_in)
-  fa, fv = flat_angle_vel(desc, *oracle.angle_vel(out['rot'], out['ang']))
-  r = env_epilogue(desc, env, qp['pos'], out, act, fa, fv, dtype)
-  if rand is not None:
-    out['pos'] = env_teleport(env, out['pos'], r['metrics'][:, 0], rand, dtype)
-  steps = steps + dt(1)                                             # wrappers.py:112
+  cur = {k: np.asarray(qp[k], dtype) for k in ('pos', 'rot', 'vel', 'ang')}
+  reward = None
+  for rep in range(action_repeat):                                  # wrappers.py:106-110
+    pos_in, act_in = env_prologue(desc, env, cur['pos'], act, dtype)
+    out = oracle.step(pos_in, cur['rot'], cur['vel'], cur['ang'], act_in)
+    fa, fv = flat_angle_vel(desc, *oracle.angle_vel(out['rot'], out['ang']))
+    r = env_epilogue(desc, env, cur['pos'], out, act, fa, fv, dtype)
+    if rand is not None:
+      rr = np.asarray(rand)
+      out['pos'] = env_teleport(env, out['pos'], r['metrics'][:, 0], rr[rep] if rr.ndim == 3 else rr, dtype)
+    reward = r['reward'] if reward is None else (reward + r['reward']).astype(dtype)   # :111
+    cur = {k: out[k] for k in ('pos', 'rot', 'vel', 'ang')}
+  steps = steps + dt(action_repeat)                                 # wrappers.py:112
   over = steps >= dt(episode_length)
   done = np.where(over, dt(1), r['done']).astype(dtype)             # wrappers.py:116
   trunc = np.where(over, dt(1) - r['done'], dt(0)).astype(dtype)    # wrappers.py:117-118
@@ -255,7 +262,7 @@ def wrapped_step(desc, env, oracle, qp, done_in, steps_in, act, first_qp, first_
   new_qp = {k: np.where(d.reshape((-1,) + (1,) * (out[k].ndim - 1)), np.asarray(first_qp[k], dtype), out[k])
             for k in ('pos', 'rot', 'vel', 'ang')}                  # wrappers.py:146
   obs = np.where(d[:, None], np.asarray(first_obs, dtype), r['obs'])  # wrappers.py:147
-  return {'qp': new_qp, 'obs': obs.astype(dtype), 'reward': r['reward'], 'done': done, 'metrics': r['metrics'],
+  return {'qp': new_qp, 'obs': obs.astype(dtype), 'reward': reward, 'done': done, 'metrics': r['metrics'],
           'steps': steps.astype(dtype), 'truncation': trunc}
 
 

@@ -51,6 +51,12 @@ def wrapper_classes():
 
 
 def main():
+  generate('ant_wrapped_env.npz', 1)
+  # EpisodeWrapper's action_repeat (wrappers.py:106-111): two env steps per wrapped step
+  generate('ant_wrapped_repeat_env.npz', 2)
+
+
+def generate(fname, action_repeat):
   out_dir = os.path.join(ROOT, 'tests', 'golden')
   Episode, AutoReset, Eval = wrapper_classes()
   import brax
@@ -58,7 +64,7 @@ def main():
   ant = env_module('ant').Ant(use_contact_forces=True)
   # eval_metrics=True wraps EvalWrapper outermost (brax/envs/__init__.py:88-89); it only adds
   # state.info['eval_metrics'] and metrics['reward'], so the sequences are those of the inner stack
-  env = Eval(AutoReset(Episode(ant, EPISODE_LENGTH, 1)))
+  env = Eval(AutoReset(Episode(ant, EPISODE_LENGTH, action_repeat)))
   g = np.load(os.path.join(out_dir, 'ant_steps.npz'))
   rng = np.random.default_rng(5)
   names = None
@@ -98,8 +104,9 @@ def main():
       rec['eval_active_episodes'].append(float(em.active_episodes))
       rec['eval_episode_steps'].append(float(em.episode_steps))
   shape = lambda v: np.asarray(v).reshape((3, T) + np.asarray(v[0]).shape)  # noqa: E731
-  np.savez_compressed(os.path.join(out_dir, 'ant_wrapped_env.npz'),
-                      episode_length=np.asarray(EPISODE_LENGTH), metric_names=np.asarray(names),
+  np.savez_compressed(os.path.join(out_dir, fname),
+                      episode_length=np.asarray(EPISODE_LENGTH), action_repeat=np.asarray(action_repeat),
+                      metric_names=np.asarray(names),
                       **{k: shape(v) for k, v in rec.items()}, **{k: np.stack(v) for k, v in firsts.items()})
   d = np.asarray(rec['done']).reshape(3, T)
   print('done\n', d, '\ntruncation\n', np.asarray(rec['truncation']).reshape(3, T), '\nsteps\n',

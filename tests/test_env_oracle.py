@@ -92,12 +92,13 @@ def test_obs_sizes():
   assert VARIANTS['grasp'][1].obs_size(util.load_desc('grasp')) == 132
 
 
-def test_wrapper_oracle_matches_reference():
+@pytest.mark.parametrize('fname', ['ant_wrapped_env.npz', 'ant_wrapped_repeat_env.npz'])
+def test_wrapper_oracle_matches_reference(fname):
   """EpisodeWrapper + AutoResetWrapper (wrappers.py:85-148), the reference's own classes run
   around its Ant (oracle/gen_golden_wrappers.py): the oracle's wrapped step reproduces every
   stored step -- done by the healthy range, truncation at episode_length, the step counter
   reset after a done, state and obs replaced by first_qp / first_obs."""
-  g = np.load(os.path.join(util.GOLDEN, 'ant_wrapped_env.npz'))
+  g = np.load(os.path.join(util.GOLDEN, fname))
   desc, env = util.load_desc('ant'), VARIANTS['ant'][1]
   o = Oracle(desc, np.float64)
   assert g['done'].sum() >= 3 and g['truncation'].sum() >= 2 and (g['done'] > g['truncation']).any()
@@ -106,7 +107,7 @@ def test_wrapper_oracle_matches_reference():
     qp = {k: g[k][:, t] for k in util.QP_KEYS}
     first = {k: g['first_' + k] for k in util.QP_KEYS}
     r = env_oracle.wrapped_step(desc, env, o, qp, g['done_in'][:, t], g['steps_in'][:, t], g['act'][:, t], first,
-                                g['first_obs'], int(g['episode_length']), np.float64)
+                                g['first_obs'], int(g['episode_length']), np.float64, action_repeat=int(g['action_repeat']))
     for k in util.QP_KEYS:
       np.testing.assert_allclose(r['qp'][k], g[k + '_o'][:, t], rtol=0, atol=1e-9, err_msg='%s step %d' % (k, t))
     for k in ('obs', 'reward', 'done', 'steps', 'truncation', 'metrics'):

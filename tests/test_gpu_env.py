@@ -551,3 +551,87 @@ def test_eval_wrapper_on_reference_sequences():
   assert float(ea.active_episodes.sum()) == 0 and float(ea.episode_steps.max()) == 6
   assert torch.equal(ea.episode_steps, eb.episode_steps)
   assert torch.allclose(ea.episode_metrics['reward'], eb.episode_metrics['reward'], rtol=1e-5, atol=1e-5)
+
+
+def test_action_repeat_on_reference_sequences():
+  """EpisodeWrapper(action_repeat=2) inside the launch against the reference's wrapper stack
+  (ant_wrapped_repeat_env.npz): two env steps per wrapped step on one action, summed rewards,
+  steps += 2; stepwise, as one rollout launch, and through the create() mirror."""
+  torch = _torch()
+  from brax_b200 import envs
+  from brax_b200.system import QP, AutoReset
+  g = np.load(os.path.join(util.GOLDEN, 'ant_wrapped_repeat_env.npz'))
+  length, rep = int(g['episode_length']), int(g['action_repeat'])
+  assert rep == 2
+  env = envs.create('ant', episode_length=length, action_repeat=rep, auto_reset=True)
+  cu = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).cuda()  # noqa: E731
+  first = QP(*[cu(g['first_' + k]) for k in util.QP_KEYS])
+  nseq, t_n = g['done'].shape
+  for t in range(t_n):
+    ar = AutoReset(first, cu(g['first_obs']), cu(g['done_in'][:, t]), cu(g['steps_in'][:, t]), length, rep)
+    q2, _, eo = env.sys.step(QP(*[cu(g[k][:, t]) for k in util.QP_KEYS]), cu(g['act'][:, t]), env=True, auto_reset=ar)
+    for k in ('done', 'steps', 'truncation'):
+      np.testing.assert_array_equal(eo[k].cpu().numpy(), g[k][:, t], err_msg='%s step %d' % (k, t))
+    np.testing.assert_allclose(eo['reward'].cpu().numpy(), g['reward'][:, t], rtol=2e-3, atol=4e-3)
+    np.testing.assert_allclose(eo['obs'].cpu().numpy(), g['obs'][:, t], rtol=2e-3, atol=4e-3)
+    for k in util.QP_KEYS:
+      np.testing.assert_allclose(getattr(q2, k).cpu().numpy(), g[k + '_o'][:, t], rtol=2e-3, atol=4e-3, err_msg=k)
+  st = envs.State(QP(*[cu(g[k][:, 0]) for k in util.QP_KEYS]), cu(g['first_obs']), cu(np.zeros(nseq)),
+                  cu(g['done_in'][:, 0]), {}, dict(first_qp=first, first_obs=cu(g['first_obs']), steps=cu(g['steps_in'][:, 0])))
+  last, eo = env.rollout(st, cu(np.swapaxes(g['act'], 0, 1)))
+  for k in ('done', 'truncation'):
+    np.testing.assert_array_equal(eo[k].cpu().numpy().T, g[k], err_msg=k)
+  np.testing.assert_array_equal(last.info['steps'].cpu().numpy(), g['steps'][:, -1])
+  np.testing.assert_allclose(eo['reward'].cpu().numpy().T, g['reward'], rtol=5e-3, atol=1e-2)
+
+
+@pytest.mark.parametrize('variant', ['ant', 'fetch_spring'])
+def test_action_repeat_matches_oracle_and_chained_launches(variant):
+  torch = _torch()
+  import dataclasses
+  from oracle import env_oracle
+  from oracle.oracle import Oracle
+  b, length, rep, t_n = 300, 7, 3, 4
+  sysname, env, qp, rng, ar = _auto_reset_case(variant, b, 9, length)
+  ar = dataclasses.replace(ar, action_repeat=rep)
+  acts = torch.from_numpy(rng.uniform(-1, 1, (t_n, b, env.action_size)).astype(np.float32)).cuda()
+  rand = None
+  if env.env.kind == 'fetch':
+    rand = torch.from_numpy(rng.uniform(0, 1, (t_n * rep, b, 3)).astype(np.float32)).cuda()
+  kw = lambda t: {} if rand is None else dict(env_rand=rand[t * rep:(t + 1) * rep])  # noqa: E731
+  # one wrapped step against the float32 oracle
+  q1, _, e1 = env.sys.step(qp, acts[0], env=True, auto_reset=ar, **kw(0))
+  desc = util.load_desc(sysname)
+  ins = {k: getattr(qp, k).cpu().numpy() for k in util.QP_KEYS}
+  first = {k: getattr(ar.first_qp, k).cpu().numpy() for k in util.QP_KEYS}
+  want = env_oracle.wrapped_step(desc, env.env, Oracle(desc, np.float32), ins, ar.done.cpu().numpy(),
+                                 ar.steps.cpu().numpy(), acts[0].cpu().numpy(), first, ar.first_obs.cpu().numpy(),
+                                 length, np.float32, None if rand is None else rand[:rep].cpu().numpy(), rep)
+  np.testing.assert_array_equal(e1['steps'].cpu().numpy(), want['steps'])
+  got_done = e1['done'].cpu().numpy()
+  assert (got_done == want['done']).mean() > 0.99
+  same = got_done == want['done']
+  frac = (np.abs(e1['reward'].cpu().numpy() - want['reward'])[same] > 1e-3 + 1e-3 * np.abs(want['reward'][same])).mean()
+  assert frac <= 0.02, frac
+  d = got_done > 0
+  np.testing.assert_array_equal(q1.pos.cpu().numpy()[d], first['pos'][d])
+  # T wrapped steps in one launch == T chained wrapped launches, bit for bit
+  cur, a, seq = qp, ar, []
+  for t in range(t_n):
+    cur, _, eo = env.sys.step(cur, acts[t], env=True, auto_reset=a, **kw(t))
+    seq.append(eo)
+    a = dataclasses.replace(a, done=eo['done'], steps=eo['steps'])
+  q2, _, er = env.sys.rollout(qp, acts, env=True, auto_reset=ar, env_rand=rand)
+  torch.cuda.synchronize()
+  for k in util.QP_KEYS:
+    assert torch.equal(getattr(q2, k), getattr(cur, k)), k
+  for k in ('obs', 'reward', 'done', 'metrics', 'truncation'):
+    assert torch.equal(er[k], torch.stack([s[k] for s in seq])), k
+  assert er['truncation'].any() and float(er['steps'].max()) <= length + rep - 1
+  # action_repeat without the wrappers' inputs, and for grasp, is refused
+  with pytest.raises(RuntimeError):
+    _, genv = _env('grasp')
+    gq, _ = _harvest(genv.sys, 64, 2, 1)
+    z = torch.zeros(64, device='cuda')
+    genv.sys.step(gq, torch.zeros(64, genv.action_size, device='cuda'), env=True,
+                  auto_reset=type(ar)(gq, torch.zeros(64, genv.observation_size, device='cuda'), z, z, 5, 2))
