@@ -384,7 +384,7 @@ def run_gpu(args, desc):
   ms_av = timed_chunks(av_step)
   # "next" row N1: the whole Env.step (sys.step + obs / reward / done / metrics of
   # envs/ant.py:222-281, envs/humanoid.py:246-340) as ONE launch; same timing method.
-  ms_env, ms_wenv, env_obs = 0.0, 0.0, 0
+  ms_env, ms_wenv, ms_reset, env_obs = 0.0, 0.0, 0.0, 0
   env_name = args.env[:-len('_spring')] if args.env.endswith('_spring') else args.env
   if env_name in ('ant', 'humanoid', 'fetch', 'grasp') and args.env != 'grasp_spring':
     from brax_b200 import envs as bx_envs
@@ -425,6 +425,17 @@ def run_gpu(args, desc):
       sts[j] = wenv.step(sts[j], acts[args.warmup + i])
     ms_wenv = timed_chunks(wrapped_step)
     qps = [st.qp for st in sts]
+    # "next" row N3: Env.reset on the GPU (noisy joint state -> bx_default_qp -> observe launch)
+    for i in range(3):
+      env.reset(b, device=dev, seed=i)
+    r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    r0.record()
+    for i in range(10):
+      env.reset(b, device=dev, seed=i)
+    r1.record()
+    torch.cuda.synchronize()
+    ms_reset = r0.elapsed_time(r1) / 10
   ms_steps = [x.elapsed_time(y) for x, y in ev]
   ms_total = float(sum(ms_steps))
   ms_sorted = sorted(ms_steps)
@@ -503,7 +514,10 @@ def run_gpu(args, desc):
                       'extra_bytes_per_env_step': 4 * (env_obs + 12),
                       'with_episode_and_auto_reset_wrappers': {
                           'value': world * b * args.steps / (ms_wenv * 1e-3), 'unit': UNIT,
-                          'ms_per_step': ms_wenv / args.steps, 'episode_length': 1000}} if ms_env > 0 else None),
+                          'ms_per_step': ms_wenv / args.steps, 'episode_length': 1000},
+                      'reset_ms': ms_reset,
+                      'reset_what': 'Env.reset of the whole batch through the Python mirror (host-bound at this size): '
+                                    'joint noise, bx_default_qp forward kinematics, observe launch'} if ms_env > 0 else None),
         'rollout': {'steps_per_launch': roll_t, 'launches': n_roll,
                     'value': world * b * roll_t * n_roll / (ms_roll * 1e-3), 'unit': UNIT,
                     'ms_per_step': ms_roll / (roll_t * n_roll), 'timing': 'median launch'},
