@@ -1776,12 +1776,16 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
       if (auto_reset && p.out[BX_SEG_ENV] != nullptr) {
         // obs = where(done, first_obs, obs) (wrappers.py:147): after this tile's obs store
         __syncthreads();
+        // (one flat pass over the tile's [nenv, O] span: the copies of different envs are independent
+        // loads in flight together, not one load -> store round trip per done env)
         const int no = h.seg_out[BX_SEG_ENV].nper;
-        float* obs = env_ptr(BX_SEG_ENV);
-        for (int e = 0; e < nenv; e++) {
-          if (!(sq[(h.q_env + EQ_S0) * QS + e].y > 0.f)) continue;
-          const int64_t off = (env0 + e) * no;
-          for (int i = threadIdx.x; i < no; i += blockDim.x) obs[off + i] = p.first_obs[off + i];
+        float* __restrict__ obs = env_ptr(BX_SEG_ENV) + env0 * no;
+        const float* __restrict__ fobs = p.first_obs + env0 * no;
+        const int total = nenv * no;
+#pragma unroll 4
+        for (int i = threadIdx.x; i < total; i += blockDim.x) {
+          const int e = i / no;
+          if (sq[(h.q_env + EQ_S0) * QS + e].y > 0.f) obs[i] = __ldg(fobs + i);
         }
       }
     }
