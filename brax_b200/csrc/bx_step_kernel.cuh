@@ -1774,18 +1774,22 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
             io_segment_scalar<false>(smf, ti, h.seg_out[s], env_ptr(s), env0, nenv);
       }
       if (auto_reset && p.out[BX_SEG_ENV] != nullptr) {
-        // obs = where(done, first_obs, obs) (wrappers.py:147): after this tile's obs store
-        __syncthreads();
-        // (one flat pass over the tile's [nenv, O] span: the copies of different envs are independent
-        // loads in flight together, not one load -> store round trip per done env)
-        const int no = h.seg_out[BX_SEG_ENV].nper;
-        float* __restrict__ obs = env_ptr(BX_SEG_ENV) + env0 * no;
-        const float* __restrict__ fobs = p.first_obs + env0 * no;
-        const int total = nenv * no;
+        // obs = where(done, first_obs, obs) (wrappers.py:147): after this tile's obs store; the
+        // barrier also tells whether any env of the tile is done at all
+        const int ln = threadIdx.x & 31;
+        const int any_done = __syncthreads_or(ln < nenv && sq[(h.q_env + EQ_S0) * QS + ln].y > 0.f);
+        if (any_done) {
+          // (one flat pass over the tile's [nenv, O] span: the copies of different envs are
+          // independent loads in flight together, not one load -> store round trip per done env)
+          const int no = h.seg_out[BX_SEG_ENV].nper;
+          float* __restrict__ obs = env_ptr(BX_SEG_ENV) + env0 * no;
+          const float* __restrict__ fobs = p.first_obs + env0 * no;
+          const int total = nenv * no;
 #pragma unroll 4
-        for (int i = threadIdx.x; i < total; i += blockDim.x) {
-          const int e = i / no;
-          if (sq[(h.q_env + EQ_S0) * QS + e].y > 0.f) obs[i] = __ldg(fobs + i);
+          for (int i = threadIdx.x; i < total; i += blockDim.x) {
+            const int e = i / no;
+            if (sq[(h.q_env + EQ_S0) * QS + e].y > 0.f) obs[i] = __ldg(fobs + i);
+          }
         }
       }
     }
