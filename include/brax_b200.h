@@ -357,9 +357,10 @@ void bx_host_free(void* p);
  * 2 * (bytes + 1024) <= 233472. */
 int bx_desc_tile_bytes(const bx_system_desc* desc, int64_t* bytes, int32_t* rows);
 
-/* T consecutive steps in one call: act is [T,B,A]; state ping-pongs inside
- * device scratch; Info of the LAST step is written.  Mirrors
- * lax.scan(env.step) over actions (training/acting.py:53-74) at System level. */
+/* T consecutive steps in ONE launch: act is [T,B,A]; the state stays in shared memory between
+ * the steps; the QP after the last step and the Info of the LAST step are written, the env
+ * outputs (obs / reward / done / metrics / truncation) of EVERY step as [T,B,...].  Mirrors
+ * lax.scan(env.step) over actions (training/acting.py:53-74). */
 int bx_rollout(bx_system* sys, int64_t num_envs, int32_t num_steps,
                const bx_step_io* io, void* stream);
 
