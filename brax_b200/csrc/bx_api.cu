@@ -1137,3 +1137,114 @@ extern "C" void* bx_host_alloc(size_t bytes) {
   return p;
 }
 extern "C" void bx_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+// ---- bx_step_host_static: the host-buffer step for callers that may not allocate ----
+// (no counterpart in the reference, see
+// include/brax_b200.h).  Same contract as bx_step_host's staged route -- copy in, ONE
+// launch, copy out, synchronise -- but the device staging area is this file-scope array
+// instead of a cudaMalloc'ed buffer, the work runs on the CALLER's stream (no stream is
+// created) and nothing is allocated or freed.  Every GPU that loads the library holds the
+// array (BX_STATIC_SCRATCH_BYTES) until exit.
+//
+// Contents: the array keeps whatever the previous call left.  Nothing in it has to start
+// at zero: the input part is overwritten by this call's H2D copies before the launch and
+// the kernel writes every requested output in full (zero_info is done in shared memory,
+// system.py:76-84), so stale contents are never read.  Calls that overlap on the GPU
+// (two host threads, two streams) share the array and RACE: one call at a time per device.
+static __device__ __align__(256) float bx_static_scratch[BX_STATIC_SCRATCH_BYTES / 4];
+
+#define BX_STATIC_MAX_DEVICES 64
+static float* g_static_ptr[BX_STATIC_MAX_DEVICES];  // device address of the array, per device
+static std::atomic<int> g_static_state[BX_STATIC_MAX_DEVICES];  // 0 = not looked up, 2 = ready
+
+// The array's NAME is a host-side stand-in in host code, not a device address: look the
+// address up once per device, with that device current.
+static int static_scratch_ptr(int device, float** out) {
+  if (device < 0 || device >= BX_STATIC_MAX_DEVICES) return fail("bx_step_host_static: device index out of range");
+  if (g_static_state[device].load(std::memory_order_acquire) != 2) {
+    void* p = nullptr;
+    CUDA_OK(cudaGetSymbolAddress(&p, bx_static_scratch));  // s->device is current (caller)
+    if (!p) return fail("cudaGetSymbolAddress returned NULL");
+    g_static_ptr[device] = static_cast<float*>(p);  // every thread that gets here stores the same value
+    g_static_state[device].store(2, std::memory_order_release);
+  }
+  *out = g_static_ptr[device];
+  return 0;
+}
+
+extern "C" int64_t bx_static_scratch_bytes(void) { return BX_STATIC_SCRATCH_BYTES; }
+
+extern "C" int bx_step_host_static(const bx_system* s, int64_t B, const bx_step_io* hio, void* stream) {
+  if (!s || !hio) return fail("NULL argument");
+  if (B <= 0) return fail("num_envs must be positive");
+  if (hio->first_pos) return fail("auto-reset inputs are supported on the device path only (bx_step / bx_rollout)");
+  if (hio->observe) return fail("observe is supported on the device path only (bx_step)");
+  if (!hio->pos || !hio->rot || !hio->vel || !hio->ang || !hio->act || !hio->pos_o || !hio->rot_o ||
+      !hio->vel_o || !hio->ang_o)
+    return fail("QP / act pointers must not be NULL");
+  const int64_t n = s->h.nb, a = s->h.act_size;
+  float* const* h_out = io_outs(hio);
+  // layout of the staging area: inputs, then the requested non-constant outputs, each
+  // sub-array on a 256-byte boundary (the kernel's 128-bit / bulk paths need 16)
+  const size_t in_per[BX_SEG_IN] = {(size_t)3 * n, (size_t)4 * n, (size_t)3 * n, (size_t)3 * n, (size_t)a};
+  size_t out_per[BX_SEG_OUT];
+  bool staged[BX_SEG_OUT];
+  auto round64 = [](size_t floats) { return (floats + 63) / 64 * 64; };
+  size_t need = 0;
+  for (int i = 0; i < BX_SEG_IN; i++) need += round64(in_per[i] * B);
+  for (int i = 0; i < BX_SEG_OUT; i++) {
+    out_per[i] = static_cast<size_t>(s->h.seg_out[i].nper);
+    staged[i] = i < 4 || (h_out[i] && out_per[i] && s->h.seg_out[i].map >= 0);
+    if (staged[i]) need += round64(out_per[i] * B);
+  }
+  if (hio->env_rand) need += round64((size_t)3 * B);
+  if (need * 4 > static_cast<size_t>(BX_STATIC_SCRATCH_BYTES)) {
+    char msg[256];
+    snprintf(msg, sizeof(msg),
+             "bx_step_host_static: %lld environments need %zu bytes of staging, the static scratch array holds "
+             "%lld (maximum %lld environments of this system with these outputs); use bx_step_host",
+             static_cast<long long>(B), need * 4, static_cast<long long>(BX_STATIC_SCRATCH_BYTES),
+             static_cast<long long>(static_cast<size_t>(BX_STATIC_SCRATCH_BYTES) / 4 / (need / B + 1)));
+    return fail(msg);
+  }
+  int prev_device = -1;
+  CUDA_OK(cudaGetDevice(&prev_device));
+  if (prev_device != s->device) CUDA_OK(cudaSetDevice(s->device));
+  struct Restore {
+    int prev, cur;
+    ~Restore() { if (prev != cur) cudaSetDevice(prev); }
+  } restore{prev_device, s->device};
+  float* cur = nullptr;
+  if (static_scratch_ptr(s->device, &cur)) return 1;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  auto take = [&](size_t floats) { float* r = cur; cur += round64(floats); return r; };
+  const float* h_in[BX_SEG_IN] = {hio->pos, hio->rot, hio->vel, hio->ang, hio->act};
+  float* d_in[BX_SEG_IN];
+  for (int i = 0; i < BX_SEG_IN; i++) {
+    d_in[i] = take(in_per[i] * B);
+    CUDA_OK(cudaMemcpyAsync(d_in[i], h_in[i], in_per[i] * B * 4, cudaMemcpyHostToDevice, st));
+  }
+  bx_step_io d;
+  memset(&d, 0, sizeof(d));
+  d.pos = d_in[0]; d.rot = d_in[1]; d.vel = d_in[2]; d.ang = d_in[3]; d.act = d_in[4];
+  float** dp = io_outs(&d);
+  for (int i = 0; i < BX_SEG_OUT; i++) dp[i] = staged[i] ? take(out_per[i] * B) : nullptr;
+  if (hio->env_rand) {
+    float* d_rand = take((size_t)3 * B);
+    CUDA_OK(cudaMemcpyAsync(d_rand, hio->env_rand, (size_t)3 * B * 4, cudaMemcpyHostToDevice, st));
+    d.env_rand = d_rand;
+  }
+  if (launch(s, B, 1, &d, st)) return 1;
+  for (int i = 0; i < BX_SEG_OUT; i++)
+    if (dp[i] && h_out[i])
+      CUDA_OK(cudaMemcpyAsync(h_out[i], dp[i], out_per[i] * B * 4, cudaMemcpyDeviceToHost, st));
+  // outputs that are constants of the dynamics mode: filled here, not transferred
+  for (int i = 4; i < BX_SEG_OUT; i++)
+    if (h_out[i] && out_per[i] && s->h.seg_out[i].map < 0) {
+      const float f = s->h.seg_out[i].fill;
+      if (f == 0.f) memset(h_out[i], 0, out_per[i] * B * 4);
+      else std::fill(h_out[i], h_out[i] + out_per[i] * B, f);
+    }
+  CUDA_OK(cudaStreamSynchronize(st));
+  return 0;
+}

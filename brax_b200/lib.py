@@ -17,7 +17,8 @@ SYMBOLS = ('bx_system_create', 'bx_system_destroy', 'bx_system_num_contacts',
            'bx_step_host', 'bx_rollout', 'bx_system_configure',
            'bx_system_autotune', 'bx_system_threads', 'bx_host_transfer_bytes',
            'bx_host_alloc', 'bx_host_free', 'bx_desc_tile_bytes',
-           'bx_launch_count', 'bx_last_error', 'bx_system_num_joint_dof', 'bx_default_qp')
+           'bx_launch_count', 'bx_last_error', 'bx_system_num_joint_dof', 'bx_default_qp',
+           'bx_step_host_static', 'bx_static_scratch_bytes')
 
 _lib = None
 
@@ -49,6 +50,10 @@ def load():
   lib.bx_step.restype = C.c_int
   lib.bx_step_host.argtypes = [P, C.c_int64, C.POINTER(_desc.CStepIO)]
   lib.bx_step_host.restype = C.c_int
+  lib.bx_step_host_static.argtypes = [P, C.c_int64, C.POINTER(_desc.CStepIO), P]
+  lib.bx_step_host_static.restype = C.c_int
+  lib.bx_static_scratch_bytes.argtypes = []
+  lib.bx_static_scratch_bytes.restype = C.c_int64
   lib.bx_rollout.argtypes = [P, C.c_int64, C.c_int32,
                              C.POINTER(_desc.CStepIO), P]
   lib.bx_rollout.restype = C.c_int

@@ -342,6 +342,26 @@ int bx_step(const bx_system* sys, int64_t num_envs, const bx_step_io* io,
  * System.step makes and what bench.py's e2e number times. */
 int bx_step_host(bx_system* sys, int64_t num_envs, const bx_step_io* host_io);
 
+/* The host-buffer step for callers that may NOT allocate (code under CUDA graph capture
+ * elsewhere in the process, tight serving loops, harnesses that forbid cudaMalloc).
+ * NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and results as bx_step_host (host pointers, pageable or pinned;
+ * H2D, ONE launch, D2H, synchronise `stream`), but
+ *   - the device staging area is a file-scope `static __device__` array of
+ *     BX_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the library holds it
+ *     until exit) instead of a cudaMalloc'ed buffer;
+ *   - everything runs on the caller's `stream` (NULL = default stream); no stream, event or
+ *     memory is created: the call makes no cudaMalloc / cudaFree / allocating library call;
+ *   - a batch whose staging exceeds the array is REJECTED with an error that names the limit
+ *     (ant with the full Info: about 21 300 environments; use bx_step_host beyond it).
+ * All calls on one device share the array; it keeps the previous call's contents (nothing in
+ * it needs to start at zero: inputs are overwritten before the launch, every requested output
+ * is written in full).  Calls that overlap on the GPU race: one call at a time per device. */
+#define BX_STATIC_SCRATCH_BYTES (32ll << 20)
+int bx_step_host_static(const bx_system* sys, int64_t num_envs, const bx_step_io* host_io,
+                        void* stream);
+int64_t bx_static_scratch_bytes(void); /* = BX_STATIC_SCRATCH_BYTES of the loaded library */
+
 /* PCIe bytes one bx_step_host call moves (outputs that are constants of the
  * dynamics mode are filled on the host, not transferred). */
 int bx_host_transfer_bytes(const bx_system* sys, int64_t num_envs, int64_t* h2d,
