@@ -6,6 +6,7 @@
 // is one kernel launch on the caller's stream: no allocation, no host sync.
 // There is no CPU fallback: without a CUDA device every call fails loudly.
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stddef.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -247,6 +248,16 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     for (int r = 0; r < 3; r++) quad(s.axis_c[3 * r], s.axis_c[3 * r + 1], s.axis_c[3 * r + 2], wc[r]);
     quad(s.limit[0], s.limit[1], s.limit[2], s.limit[3]);
     quad(s.limit[4], s.limit[5], 0.f, 0.f);
+    for (int dd = 0; dd < 3; dd++) {  // direction vectors of the limits (clip_dir, bx_step_kernel.cuh)
+      float cs[4];
+      for (int e = 0; e < 2; e++) {
+        const double a = s.limit[2 * dd + e];
+        const bool open_end = !(fabs(a) < 3.14159265358979323846 - 1e-6);  // a signed angle never passes +-pi
+        cs[2 * e] = open_end ? -1.f : static_cast<float>(cos(a));
+        cs[2 * e + 1] = open_end ? 0.f : static_cast<float>(sin(a));
+      }
+      quad(cs[0], cs[1], cs[2], cs[3]);
+    }
   }
   h.fo_act = nquads();
   for (int i = 0; i < na; i++) quad(d->actuators[i].strength, 0.f, 0.f, 0.f);

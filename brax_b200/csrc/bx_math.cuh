@@ -20,17 +20,31 @@ struct Q4 { float w, x, y, z; };
 // the correctly rounded one in all but a vanishing fraction of cases (<= 1 ulp
 // otherwise), i.e. the same float32 result IEEE division gives, without the
 // FCHK + slow-path call the compiler's a / b expands to.
+// BX_FAST_DIV (default 1): a / b = a * rcp(b) with rcp = MUFU.RCP + one Newton step (<= 1 ulp):
+// quotients within 1.5 ulp of the IEEE one.  0 = the correctly rounded quotient (residual
+// correction, 2 more FFMA per quotient); 2 = the raw MUFU.RCP seed (A/B only).
+#ifndef BX_FAST_DIV
+#define BX_FAST_DIV 1
+#endif
 BXD float bx_rcp(float b) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+#if BX_FAST_DIV == 2
+  return r;
+#else
   float e = fmaf(-b, r, 1.f);
   return fmaf(r, e, r);
+#endif
 }
 // a / b given r ~= 1/b (from bx_rcp)
 BXD float bx_mul_rcp(float a, float b, float r) {
+#if BX_FAST_DIV
+  return a * r;
+#else
   float q = a * r;
   float e = fmaf(-q, b, a);
   return fmaf(e, r, q);
+#endif
 }
 BXD float bx_div(float a, float b) { return bx_mul_rcp(a, b, bx_rcp(b)); }
 BXD float bx_sqrt(float a) {
@@ -84,16 +98,138 @@ BXD Q4 vec_quat_mul(V3 u, Q4 v) {
             -u.x * v.z + u.y * v.w + u.z * v.x,
             u.x * v.y - u.y * v.x + u.z * v.w);
 }
+// ---- inline, branch-free arctan2 / sin+cos / arccos for the substep loop ---------------
+// The libm versions expand to ~70 instructions each with several reconvergence regions and
+// slow-path calls (they split the basic block of a joint item, which is what the scheduler
+// interleaves); these are straight-line polynomial evaluations (tools/fit_trig.py: max
+// absolute error 9.5e-8 / 1.3e-7 / 2.2e-7, i.e. 1-2 ulp of the result, float32 evaluation).
+#ifndef BX_LIBM_TRIG  // -DBX_LIBM_TRIG=1: the CUDA libm functions (A/B)
+#define BX_LIBM_TRIG 0
+#endif
+// jnp.arctan2 semantics incl. (0, 0) -> 0
+BXD float bx_atan2(float y, float x) {
+#if BX_LIBM_TRIG
+  return atan2f(y, x);
+#else
+  const float ax = fabsf(x), ay = fabsf(y);
+  const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+  float a = mn * bx_rcp(mx);
+  a = mx > 0.f ? a : 0.f;
+  const float t = a * a;
+  float p = 0.002903143409639597f;
+  p = fmaf(p, t, -0.0162810105830431f);
+  p = fmaf(p, t, 0.04303545877337456f);
+  p = fmaf(p, t, -0.07533279806375504f);
+  p = fmaf(p, t, 0.10654453933238983f);
+  p = fmaf(p, t, -0.14207063615322113f);
+  p = fmaf(p, t, 0.19993042945861816f);
+  p = fmaf(p, t, -0.3333309292793274f);
+  p = fmaf(p, t, 1.0f);
+  float r = a * p;
+  r = ay > ax ? 1.57079637050628662f - r : r;
+  r = x < 0.f ? 3.14159274101257324f - r : r;
+  return copysignf(r, y);
+#endif
+}
+// sin and cos of x, |x| <= pi/2 (+2 %): half of an angle in [-pi, pi]
+BXD void bx_sincos_half(float x, float* sn, float* cs) {
+#if BX_LIBM_TRIG
+  sincosf(x, sn, cs);
+#else
+  const float t = x * x;
+  float ps = 2.637510533531895e-06f;
+  ps = fmaf(ps, t, -0.00019824535411316901f);
+  ps = fmaf(ps, t, 0.008333271369338036f);
+  ps = fmaf(ps, t, -0.1666666716337204f);
+  *sn = fmaf(x * t, ps, x);
+  float pc = 9.446637250221102e-08f;
+  pc = fmaf(pc, t, -8.698758051650657e-07f);
+  pc = fmaf(pc, t, 2.61406439676648e-05f);
+  pc = fmaf(pc, t, -0.0013901225756853819f);
+  pc = fmaf(pc, t, 0.041667066514492035f);
+  pc = fmaf(pc, t, -0.5f);
+  *cs = fmaf(t, pc, 1.f);
+#endif
+}
+// arccos(x), x in [-1, 1]
+BXD float bx_acos(float x) {
+#if BX_LIBM_TRIG
+  return acosf(x);
+#else
+  const float t = fabsf(x);
+  float p = -0.0012626672396436334f;
+  p = fmaf(p, t, 0.006670547649264336f);
+  p = fmaf(p, t, -0.01708851009607315f);
+  p = fmaf(p, t, 0.030891938135027885f);
+  p = fmaf(p, t, -0.05017422139644623f);
+  p = fmaf(p, t, 0.08897893875837326f);
+  p = fmaf(p, t, -0.21459878981113434f);
+  p = fmaf(p, t, 1.570796251296997f);
+  const float r = bx_sqrt(fmaxf(1.f - t, 0.f)) * p;
+  return x < 0.f ? 3.14159274101257324f - r : r;
+#endif
+}
+
+// ---- clip(signed_angle, lo, hi) as a DIRECTION, without arctan2 / sincos -----------------
+// (x, y) = (dot(ref_p, ref_c), dot(cross(ref_p, ref_c), axis)) is r (cos psi, sin psi) of the signed
+// angle psi = arctan2(y, x) (math.py:116-127).  What the joint code needs of clip(psi, lo, hi) is the
+// rotation by it (joints.py:291-293, :349-352): its cosine and sine.  Inside the limits that is (x, y) / r
+// -- no arctan2 -> sincos round trip, whose rounding shows up as a spurious constraint violation --
+// and outside it is the limit's own (cos, sin) from the table (lcs = {cos lo, sin lo, cos hi, sin hi}).
+// psi < lo / psi > hi are decided by the sign of sin(psi - limit) = (cos lim * y - sin lim * x) / r on
+// the half plane (sign of y) where psi - limit cannot wrap; limits at or beyond +-pi never clip.
+BXD void clip_dir(float x, float y, float4 lcs, float lo, float hi, float* c, float* s, float* outside) {
+  const float r2 = x * x + y * y;
+  float ri;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(ri) : "f"(r2));
+  ri = ri * fmaf(-0.5f * r2 * ri, ri, 1.5f);  // one Newton step
+  const float d_lo = lcs.x * y - lcs.y * x, d_hi = lcs.z * y - lcs.w * x;
+  const bool below = lo >= 0.f ? (y < 0.f || d_lo < 0.f) : (y < 0.f && d_lo < 0.f);
+  const bool above = hi <= 0.f ? (y > 0.f || d_hi > 0.f) : (y > 0.f && d_hi > 0.f);
+  float cc = r2 > 0.f ? x * ri : 1.f, ss = r2 > 0.f ? y * ri : 0.f;  // arctan2(0, 0) = 0
+  cc = below ? lcs.x : cc; ss = below ? lcs.y : ss;
+  cc = above ? lcs.z : cc; ss = above ? lcs.w : ss;                  // clip = min(max(psi, lo), hi)
+  *c = cc; *s = ss;
+  *outside = (below || above) ? 1.f : 0.f;
+}
+// rotate(v, quat_rot_axis(axis, phi)) for a unit axis, given cos / sin of phi (Rodrigues)
+BXD V3 rot_axis_cs(V3 v, V3 axis, float c, float s) {
+  return v * c + cross(axis, v) * s + axis * (dot(axis, v) * (1.f - c));
+}
+
 // math.py:116-127
 BXD float signed_angle(V3 axis, V3 ref_p, V3 ref_c) {
-  return atan2f(dot(cross(ref_p, ref_c), axis), dot(ref_p, ref_c));
+  return bx_atan2(dot(cross(ref_p, ref_c), axis), dot(ref_p, ref_c));
 }
-// math.py:173-187
+// math.py:173-187.  The step kernel only ever passes clipped signed angles (|angle| <= pi).
 BXD Q4 quat_rot_axis(V3 axis, float angle) {
+  float s, c;
+  bx_sincos_half(angle * 0.5f, &s, &c);
+  return q4(c, axis.x * s, axis.y * s, axis.z * s);
+}
+// any angle (bx_reset.cu: joint angles of a reset are not range-limited)
+BXD Q4 quat_rot_axis_any(V3 axis, float angle) {
   float s, c;
   sincosf(angle * 0.5f, &s, &c);
   return q4(c, axis.x * s, axis.y * s, axis.z * s);
 }
+// The rotation of `rotate` as a matrix (rows): 25 operations to build, 9 per vector instead of
+// ~30 -- for items that rotate several constants by the same quaternion.  Same linear map as
+// math.py:25-40 also for a non-unit q (it scales by |q|^2 exactly like the formula does).
+struct M3 { V3 r0, r1, r2; };
+BXD M3 rotmat(Q4 q) {
+  const float d = q.w * q.w - (q.x * q.x + q.y * q.y + q.z * q.z);
+  const float x2 = q.x + q.x, y2 = q.y + q.y, z2 = q.z + q.z;
+  const float xx = q.x * x2, yy = q.y * y2, zz = q.z * z2;
+  const float xy = q.x * y2, xz = q.x * z2, yz = q.y * z2;
+  const float sx = q.w * x2, sy = q.w * y2, sz = q.w * z2;
+  M3 m;
+  m.r0 = v3(d + xx, xy - sz, xz + sy);
+  m.r1 = v3(xy + sz, d + yy, yz - sx);
+  m.r2 = v3(xz - sy, yz + sx, d + zz);
+  return m;
+}
+BXD V3 mrot(const M3& m, V3 v) { return v3(dot(m.r0, v), dot(m.r1, v), dot(m.r2, v)); }
 // jumpy.py:170-192: jnp path -- 0 when every |x_i| <= 1e-8 (allclose(x, 0)).
 BXD float safe_norm(V3 a) {
   bool zero = fabsf(a.x) <= 1e-8f && fabsf(a.y) <= 1e-8f && fabsf(a.z) <= 1e-8f;

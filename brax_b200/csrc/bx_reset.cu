@@ -55,7 +55,7 @@ bx_reset_kernel(const bx_reset_desc* __restrict__ gt, int nb, int64_t num_envs,
                      axes[0].z * w[0] + axes[1].z * w[1] + axes[2].z * w[2]);
     Q4 lr = q4(jt.ref[0], jt.ref[1], jt.ref[2], jt.ref[3]);
     for (int d = 0; d < 3; d++)  // intrinsic euler rotations (system.py:185-189)
-      lr = quat_mul(quat_rot_axis(rotate(axes[d], lr), a[d]), lr);
+      lr = quat_mul(quat_rot_axis_any(rotate(axes[d], lr), a[d]), lr);
     const Q4 rp = body_rot(jt.body_p);
     const V3 pp = body_pos(jt.body_p);
     const Q4 wr = quat_mul(rp, lr);                                                     // :204

@@ -251,28 +251,28 @@ BXS void store_warp(const float* smf, const int32_t* ti, const BxSeg& sg, float*
 }
 
 // ---- joints: axis / angle -------------------------------------------------
-// Revolute.axis_angle joints.py:311-319 (spring_joints.py:150-157)
-BXS void axis_angle_revolute(const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
-  V3 ax = rotate(f3(jq[JQ_AXIS_P]), rp);
-  V3 ref_p = rotate(f3(jq[JQ_AXIS_P + 2]), rp);
-  V3 ref_c = rotate(f3(jq[JQ_AXIS_C + 2]), rc);
+// Revolute.axis_angle joints.py:311-319 (spring_joints.py:150-157); mp / mc = rotmat(rot_p / rot_c)
+BXS void axis_angle_revolute(const float4* jq, const M3& mp, const M3& mc, V3* axis, float* angle) {
+  V3 ax = mrot(mp, f3(jq[JQ_AXIS_P]));
+  V3 ref_p = mrot(mp, f3(jq[JQ_AXIS_P + 2]));
+  V3 ref_c = mrot(mc, f3(jq[JQ_AXIS_C + 2]));
   axis[0] = ax;
   angle[0] = signed_angle(ax, ref_p, ref_c);
 }
 
 // Spherical.axis_angle joints.py:388-415 (spring_joints.py:212-224, 276-303)
-BXS void axis_angle_spherical(const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
-  V3 a1p = rotate(f3(jq[JQ_AXIS_P]), rp);
-  V3 a2p = rotate(f3(jq[JQ_AXIS_P + 1]), rp);
-  V3 a1c = rotate(f3(jq[JQ_AXIS_C]), rc);
-  V3 a2c = rotate(f3(jq[JQ_AXIS_C + 1]), rc);
-  V3 a3c = rotate(f3(jq[JQ_AXIS_C + 2]), rc);
+BXS void axis_angle_spherical(const float4* jq, const M3& mp, const M3& mc, V3* axis, float* angle) {
+  V3 a1p = mrot(mp, f3(jq[JQ_AXIS_P]));
+  V3 a2p = mrot(mp, f3(jq[JQ_AXIS_P + 1]));
+  V3 a1c = mrot(mc, f3(jq[JQ_AXIS_C]));
+  V3 a2c = mrot(mc, f3(jq[JQ_AXIS_C + 1]));
+  V3 a3c = mrot(mc, f3(jq[JQ_AXIS_C + 2]));
   V3 lon = cross(a3c, a1p);
   lon = vdiv(lon, 1e-10f + safe_norm(lon));
   float psi = signed_angle(a1p, a2p, lon);
   V3 xz = dot(a1p, a1c) * a1c + dot(a1p, a2c) * a2c;
   xz = vdiv(xz, 1e-10f + safe_norm(xz));
-  float theta = acosf(clipf(dot(xz, a1p), -1.f, 1.f)) * signf(dot(a1p, a3c));
+  float theta = bx_acos(clipf(dot(xz, a1p), -1.f, 1.f)) * signf(dot(a1p, a3c));
   float phi = signed_angle(-a3c, a2c, lon);
   axis[0] = a1p; axis[1] = a2c; axis[2] = a3c;
   angle[0] = psi; angle[1] = theta; angle[2] = phi;
@@ -285,12 +285,15 @@ BXS int joint_dof(int kind) {
              : (BXF_IS(kind == BX_JOINT_SPRING_UNIVERSAL, BXF_UNIVERSAL, BXF_SPHERICAL) ? 2 : 3);
 }
 
-BXS void joint_axis_angle(int kind, const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
+BXS void joint_axis_angle(int kind, const float4* jq, const M3& mp, const M3& mc, V3* axis, float* angle) {
   if (BXF_IS(kind == BX_JOINT_REVOLUTE || kind == BX_JOINT_SPRING_REVOLUTE, BXF_REVOLUTE,
              BXF_SPHERICAL | BXF_UNIVERSAL))
-    axis_angle_revolute(jq, rp, rc, axis, angle);
+    axis_angle_revolute(jq, mp, mc, axis, angle);
   else
-    axis_angle_spherical(jq, rp, rc, axis, angle);
+    axis_angle_spherical(jq, mp, mc, axis, angle);
+}
+BXS void joint_axis_angle(int kind, const float4* jq, Q4 rp, Q4 rc, V3* axis, float* angle) {
+  joint_axis_angle(kind, jq, rotmat(rp), rotmat(rc), axis, angle);
 }
 
 // ---- phase T: actuator torques and joint damping torques -------------------
@@ -334,7 +337,7 @@ BXS void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
           t = angle[d] < lo[d] ? 0.f : t;
           t = angle[d] > hi[d] ? 0.f : t;
         } else {
-          float tgt = clipf(av * 3.14159265358979323846f / 180.f, lo[d], hi[d]);
+          float tgt = clipf(av * 0.017453292519943295f, lo[d], hi[d]);  // act * pi / 180 (actuators.py:83)
           t = (tgt - angle[d]) * strength;
         }
         tq = tq + axis[d] * t;
@@ -496,13 +499,12 @@ BXS void position_update(V3 wp, V3 wc, V3 pos_p, V3 pos_c, Q4 rp, Q4 rc,
 }
 
 // limit_angle closure of Spherical.apply_reduced joints.py:343-354
-BXS void limit_angle(V3 n, V3 n_1, V3 n_2, float lo, float hi, V3 ii_p, V3 ii_c,
+BXS void limit_angle(V3 n, V3 n_1, V3 n_2, float lo, float hi, float4 lcs, V3 ii_p, V3 ii_c,
                      Q4 rp, Q4 rc, float scale_ang, Q4* out_p, Q4* out_c) {
-  float ph = signed_angle(n, n_1, n_2);
-  float mask = ph < lo ? 1.f : 0.f;
-  mask = ph > hi ? 1.f : mask;
-  ph = clipf(ph, lo, hi);
-  V3 n1 = rotate(n_1, quat_rot_axis(n, ph));
+  // ph = signed_angle(n, n_1, n_2); mask = ph outside [lo, hi]; n1 = n_1 rotated about n by clip(ph)
+  float cs, sn, mask;
+  clip_dir(dot(n_1, n_2), dot(cross(n_1, n_2), n), lcs, lo, hi, &cs, &sn, &mask);
+  V3 n1 = rot_axis_cs(n_1, n, cs, sn);
   V3 dq = cross(n1, n_2) * mask;
   angle_update(dq, ii_p, ii_c, rp, rc, scale_ang, out_p, out_c);
 }
@@ -525,8 +527,9 @@ BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
     const float4 mp = bqp[BQ_MASS], mc = bqc[BQ_MASS];
     const float4 j0 = jq[JQ_OFF_P], j1 = jq[JQ_OFF_C];
     const float4 ap0 = jq[JQ_AXIS_P];
-    V3 wp = pos_p + rotate(f3(j0), rp);
-    V3 wc = pos_c + rotate(f3(j1), rc);
+    const M3 Rp = rotmat(rp), Rc = rotmat(rc);
+    V3 wp = pos_p + mrot(Rp, f3(j0));
+    V3 wc = pos_c + mrot(Rc, f3(j1));
     PTM(c, 4);
     DQ dp, dc;
     position_update(wp, wc, pos_p, pos_c, rp, rc, mp.x, mc.x, mp.y, mc.y, ii_p, ii_c, j1.w, &dp, &dc);
@@ -534,15 +537,16 @@ BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
     const float sa = ap0.w;
     const float4 l01 = jq[JQ_LIMIT];
     if (BXF_IS(ji.x == BX_JOINT_REVOLUTE, BXF_REVOLUTE, BXF_SPHERICAL)) {
-      V3 axis = rotate(f3(ap0), rp);
-      V3 ref_p = rotate(f3(jq[JQ_AXIS_P + 2]), rp);
-      V3 ref_c = rotate(f3(jq[JQ_AXIS_C + 2]), rc);
-      float psi = signed_angle(axis, ref_p, ref_c);
+      V3 axis = mrot(Rp, f3(ap0));
+      V3 ref_p = mrot(Rp, f3(jq[JQ_AXIS_P + 2]));
+      V3 ref_c = mrot(Rc, f3(jq[JQ_AXIS_C + 2]));
+      // psi = signed_angle(axis, ref_p, ref_c); n1 = ref_p rotated about axis by clip(psi, lo, hi)
+      float cs, sn, outside;
+      clip_dir(dot(ref_p, ref_c), dot(cross(ref_p, ref_c), axis), jq[JQ_LIMCS], l01.x, l01.y, &cs, &sn, &outside);
       PTM(c, 6);
-      V3 axis_c = rotate(f3(jq[JQ_AXIS_C]), rc);
+      V3 axis_c = mrot(Rc, f3(jq[JQ_AXIS_C]));
       V3 dq_1 = cross(axis, axis_c);
-      float ph = clipf(psi, l01.x, l01.y);
-      V3 n1 = rotate(ref_p, quat_rot_axis(axis, ph));
+      V3 n1 = rot_axis_cs(ref_p, axis, cs, sn);
       V3 dq_2 = cross(n1, ref_c);
       PTM(c, 7);
       Q4 p1, c1, p2, c2;
@@ -553,11 +557,11 @@ BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
       PTM(c, 8);
     } else {
       const float4 l2 = jq[JQ_LIMIT + 1];
-      V3 a1p = rotate(f3(ap0), rp);
-      V3 a2p = rotate(f3(jq[JQ_AXIS_P + 1]), rp);
-      V3 a1c = rotate(f3(jq[JQ_AXIS_C]), rc);
-      V3 a2c = rotate(f3(jq[JQ_AXIS_C + 1]), rc);
-      V3 a3c = rotate(f3(jq[JQ_AXIS_C + 2]), rc);
+      V3 a1p = mrot(Rp, f3(ap0));
+      V3 a2p = mrot(Rp, f3(jq[JQ_AXIS_P + 1]));
+      V3 a1c = mrot(Rc, f3(jq[JQ_AXIS_C]));
+      V3 a2c = mrot(Rc, f3(jq[JQ_AXIS_C + 1]));
+      V3 a3c = mrot(Rc, f3(jq[JQ_AXIS_C + 2]));
       V3 lon = cross(a3c, a1p);
       lon = vdiv(lon, 1e-6f + safe_norm(lon));
       V3 xz = dot(a1p, a1c) * a1c + dot(a1p, a2c) * a2c;
@@ -566,9 +570,9 @@ BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
       a2n = vdiv(a2n, 1e-6f + safe_norm(a2n));
       float sg = signf(dot(a1p, a3c));
       Q4 p1, c1, p2, c2, p3, c3;
-      limit_angle(a1p, a2p, lon, l01.x, l01.y, ii_p, ii_c, rp, rc, sa, &p1, &c1);
-      limit_angle((-a2n) * sg, a1p, xz, l01.z, l01.w, ii_p, ii_c, rp, rc, sa, &p2, &c2);
-      limit_angle(a3c, lon, a2c, l2.x, l2.y, ii_p, ii_c, rp, rc, sa, &p3, &c3);
+      limit_angle(a1p, a2p, lon, l01.x, l01.y, jq[JQ_LIMCS], ii_p, ii_c, rp, rc, sa, &p1, &c1);
+      limit_angle((-a2n) * sg, a1p, xz, l01.z, l01.w, jq[JQ_LIMCS + 1], ii_p, ii_c, rp, rc, sa, &p2, &c2);
+      limit_angle(a3c, lon, a2c, l2.x, l2.y, jq[JQ_LIMCS + 2], ii_p, ii_c, rp, rc, sa, &p3, &c3);
       dp.rot = dp.rot + ((p1 + p2) + p3);
       dc.rot = dc.rot + ((c1 + c2) + c3);
     }
@@ -689,8 +693,9 @@ BXS Contact contact_fn(int kind, const float4* cq, V3 pa, Q4 ra, V3 va, V3 wa, V
   const float4 mat = cq[CQ_MAT];
   if (BXF_IS(kind == BX_PAIR_CAPSULE_CAPSULE, BXF_CAPSULE_CAPSULE,
              BXF_CAPSULE_PLANE | BXF_BOX_PLANE)) {
-    V3 ca = pa + rotate(f3(cq[CQ_PTS + 1]), ra), ea = rotate(f3(cq[CQ_PTS]), ra);
-    V3 cb = pb + rotate(f3(cq[CQ_PTS + 3]), rb), eb = rotate(f3(cq[CQ_PTS + 2]), rb);
+    const M3 ma = rotmat(ra), mb = rotmat(rb);
+    V3 ca = pa + mrot(ma, f3(cq[CQ_PTS + 1])), ea = mrot(ma, f3(cq[CQ_PTS]));
+    V3 cb = pb + mrot(mb, f3(cq[CQ_PTS + 3])), eb = mrot(mb, f3(cq[CQ_PTS + 2]));
     V3 best_a, best_b;
     closest_seg_seg(ca + ea, ca - ea, cb + eb, cb - eb, &best_a, &best_b);
     V3 pv = best_a - best_b;
@@ -1068,7 +1073,8 @@ BXS void phase_joints_spring(const Ctx& c, const BxHeader& h) {
     const float stiffness = jq[JQ_AXIS_P + 1].w, spring_damp = jq[JQ_AXIS_P + 2].w;
     const float ang_damp = j0.w, ls = jq[JQ_AXIS_C].w;
     // QP.to_world base.py:112-125
-    V3 op = rotate(f3(j0), rp), oc = rotate(f3(j1), rc);
+    const M3 mp = rotmat(rp), mc = rotmat(rc);
+    V3 op = mrot(mp, f3(j0)), oc = mrot(mc, f3(j1));
     V3 wp = pos_p + op, wc = pos_c + oc;
     V3 vp = ldv(c, rp0 + L::VEL) + cross(ang_p, op);
     V3 vc = ldv(c, rc0 + L::VEL) + cross(ang_c, oc);
@@ -1078,7 +1084,7 @@ BXS void phase_joints_spring(const Ctx& c, const BxHeader& h) {
     body_impulse(bqc[BQ_MASS].y, ii_c, pos_c, imp, wc, &dvc, &dac);
     V3 axis[3];
     float angle[3], dang[3];
-    joint_axis_angle(kind, jq, rp, rc, axis, angle);
+    joint_axis_angle(kind, jq, mp, mc, axis, angle);
     const int dof = joint_dof(kind);
     const float4 l01 = jq[JQ_LIMIT], l2 = jq[JQ_LIMIT + 1];
     const float lo[3] = {l01.x, l01.z, l2.x}, hi[3] = {l01.y, l01.w, l2.y};
@@ -1093,7 +1099,7 @@ BXS void phase_joints_spring(const Ctx& c, const BxHeader& h) {
     }
     V3 tq;
     if (BXF_IS(kind == BX_JOINT_SPRING_REVOLUTE, BXF_REVOLUTE, BXF_SPHERICAL | BXF_UNIVERSAL)) {  // spring_joints.py:127-148
-      V3 axis_c = rotate(f3(jq[JQ_AXIS_C]), rc);
+      V3 axis_c = mrot(mc, f3(jq[JQ_AXIS_C]));
       tq = stiffness * cross(axis[0], axis_c);
       tq = tq - (ls * axis[0]) * dang[0];
     } else if (BXF_IS(kind == BX_JOINT_SPRING_UNIVERSAL, BXF_UNIVERSAL, BXF_SPHERICAL)) {  // :178-210
@@ -1310,7 +1316,11 @@ static __device__ __noinline__ void phase_env_ego(const Ctx c, const BxHeader& h
   const int po = MODE == BX_MODE_PBD ? 2 * c.cur : 0;
   const V3 pref = ldv(c, L::BQ * h.env_ref + po);
   const Q4 qref = ldq(c, L::BQ * h.env_ref + po + 1);
-  for (int b = c.warp; b < h.nb; b += c.nwarp) {
+  // The target body's rows belong to the LAST warp: it is the one that teleports a hit target
+  // below (writes that body's pose row), and the obs must see the pose before the teleport
+  // (fetch.py:56 vs :88-93, grasp.py:88 vs :131-136) -- no other warp may read that row here.
+  const bool last = c.warp == c.nwarp - 1;
+  auto local_rows = [&](int b) {
     // pbd: the body's previous-pose rows are dead after the last substep
     const int r0 = MODE == BX_MODE_PBD ? L::BQ * b + 2 * (c.cur ^ 1) : h.q_eloc + 2 * b;
     const V3 pl = inv_rotate(ldv(c, L::BQ * b + po) - pref, qref);
@@ -1318,8 +1328,11 @@ static __device__ __noinline__ void phase_env_ego(const Ctx c, const BxHeader& h
     stv(c, r0, pl);
     stv(c, r0 + 1, vl);
     reinterpret_cast<float*>(&QROW(c, h.q_ecf + (b >> 2)))[b & 3] = env_contact_flag(c, h, b);
-  }
-  if (c.warp != c.nwarp - 1) return;
+  };
+  for (int b = c.warp; b < h.nb; b += c.nwarp)
+    if (b != h.env_target) local_rows(b);
+  if (!last) return;
+  local_rows(h.env_target);
   const int E = h.q_env, V = h.q_ev;
   const V3 ptgt = ldv(c, L::BQ * h.env_target + po);
   float hit_any = 0.f;

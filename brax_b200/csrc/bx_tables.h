@@ -30,7 +30,8 @@ enum {
   JQ_AXIS_P = 2,  // rows 0..2: {axis_p[r], w}; w = scale_ang, stiffness, spring_damping
   JQ_AXIS_C = 5,  // rows 0..2: {axis_c[r], w}; w = limit_strength, 0, 0
   JQ_LIMIT = 8,   // {lo0, hi0, lo1, hi1}, {lo2, hi2, 0, 0}
-  JQ_STRIDE = 10,
+  JQ_LIMCS = 10,  // per dof d: {cos lo_d, sin lo_d, cos hi_d, sin hi_d} (a limit at or beyond +-pi: (-1, 0))
+  JQ_STRIDE = 13,
 
   // actuator / force: 1 quad {strength, 0, 0, 0}
   // contact row (one per contact, pairs expanded): 5 quads

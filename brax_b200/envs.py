@@ -463,11 +463,13 @@ class EvalWrapper:
     sums = {k: (eo['metrics'][..., i] * before).sum(0) for i, k in enumerate(names)}
     sums['reward'] = (eo['reward'] * before).sum(0)
     last.metrics['reward'] = last.reward
-    # while an env is active nothing has reset its counter: steps after step t = s0 + t + 1
+    # while an env is active nothing has reset its counter: steps after wrapped step t =
+    # s0 + action_repeat * (t + 1) (EpisodeWrapper advances `steps` by action_repeat, wrappers.py:112)
     last.info['eval_metrics'] = EvalMetrics(
         {k: em.episode_metrics[k] + sums[k] for k in sums},
         em.active_episodes * alive[-1],
-        torch.where(em.active_episodes > 0, s0 + before.sum(0), em.episode_steps))
+        torch.where(em.active_episodes > 0, s0 + float(self.env.action_repeat or 1) * before.sum(0),
+                    em.episode_steps))
     return last, eo
 
 

@@ -1,0 +1,131 @@
+"""Generates tests/golden/bounce/: reference trajectories that exercise RESTITUTION
+(elasticity > 0) -- the branch no env config of the reference reaches (build container only).
+
+Source: `ElasticityTest` (/root/reference/brax/tests/physics_test.py:835-914).  Its config is
+used as is except that the far-away `boxwall` body (a box vs capsule pair = capsule_mesh,
+out of scope; 10 m from everything in the vertical tests) is dropped:
+
+  ball_ball_<mode>_e<E>_<free|frozen>   test_ball_bounce_vertical(_frozen) (:880-914):
+        default_qp(1), dt = (2*5/9.8)/100, elasticity E in {0, .5, 1}; a capsule-capsule
+        pair (TwoWayCollider; OneWayCollider when the lower ball is frozen) + two
+        capsule-plane pairs; 400 (free) / 110 (frozen) steps
+  ball_plane_<mode>_e50                 a ball thrown onto the ground plane, elasticity .5
+        (the one-way capsule_plane restitution branch, colliders.py:411-430)
+
+in dynamics modes pbd and legacy_spring.  The UNMODIFIED reference (numpy float64,
+oracle/refsys.py) is rolled forward and EVERY step's input state and outputs (QP + Info)
+are stored, so the tests check single steps from the reference's own states (tight) as
+well as the reference test's assertion on the chained result.
+
+usage: python oracle/gen_golden_bounce.py [name-prefix ...]
+"""
+import os
+import sys
+import time
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+sys.path.insert(0, HERE)
+
+import refsys  # noqa: E402
+
+OUT = os.path.join(ROOT, 'tests', 'golden', 'bounce')
+INFO = ('contact_vel', 'contact_ang', 'joint_vel', 'joint_ang', 'actuator_vel', 'actuator_ang',
+        'contact_pos', 'contact_normal', 'contact_penetration')
+
+
+def _info_arrays(info):
+  f = lambda x: np.asarray(x, np.float64)  # noqa: E731
+  return {'contact_vel': f(info.contact.vel), 'contact_ang': f(info.contact.ang),
+          'joint_vel': f(info.joint.vel), 'joint_ang': f(info.joint.ang),
+          'actuator_vel': f(info.actuator.vel), 'actuator_ang': f(info.actuator.ang),
+          'contact_pos': f(info.contact_pos), 'contact_normal': f(info.contact_normal),
+          'contact_penetration': f(info.contact_penetration)}
+
+
+def roll(name, config, qp_index, steps, note=''):
+  import brax
+  from brax_b200.extract import describe
+  t0 = time.time()
+  s = brax.System(config)
+  desc = describe(s, name, act_size=1)
+  qp = s.default_qp(qp_index)
+  rec = {k: [] for k in ('pos', 'rot', 'vel', 'ang')}
+  rec.update({'out_' + k: [] for k in ('pos', 'rot', 'vel', 'ang') + INFO})
+  act = np.zeros(0)
+  for _ in range(steps):
+    for k in ('pos', 'rot', 'vel', 'ang'):
+      rec[k].append(np.asarray(getattr(qp, k), np.float64))
+    qp, info = s.step(qp, act)
+    for k in ('pos', 'rot', 'vel', 'ang'):
+      rec['out_' + k].append(np.asarray(getattr(qp, k), np.float64))
+    for k, v in _info_arrays(info).items():
+      rec['out_' + k].append(v)
+  rec = {k: np.stack(v) for k, v in rec.items()}
+  rec['act'] = np.zeros((steps, 1))
+  rec['elasticity'] = np.asarray(float(config.elasticity))
+  os.makedirs(OUT, exist_ok=True)
+  with open(os.path.join(OUT, name + '.json'), 'w') as f:
+    f.write(desc.to_json())
+  np.savez_compressed(os.path.join(OUT, name + '.npz'), **rec)
+  vz = rec['out_vel'][:, 0, 2]
+  print('%-34s %4d steps  %.1fs  final vel.z %+.4f  max vel.z %+.4f %s' % (
+      name, steps, time.time() - t0, vz[-1], vz[5:].max(), note))
+
+
+def main(only):
+  brax = refsys.setup()
+  from google.protobuf import text_format
+  import importlib
+  pt = importlib.import_module('brax.tests.physics_test')
+
+  def want(n):
+    return not only or any(n.startswith(p) for p in only)
+
+  def elasticity_config(mode):
+    c = text_format.Parse(pt.ElasticityTest._CONFIG, brax.Config())
+    assert c.bodies[2].name == 'boxwall'
+    del c.bodies[2]
+    for d in c.defaults:
+      keep = [q for q in d.qps if q.name != 'boxwall']
+      del d.qps[:]
+      d.qps.extend(keep)
+    if mode == 'spring':
+      c.dynamics_mode = 'legacy_spring'
+    return c
+
+  for mode in ('pbd', 'spring'):
+    for e in (0.0, 0.5, 1.0):
+      for frozen in (False, True):
+        n = 'ball_ball_%s_e%d_%s' % (mode, int(100 * e), 'frozen' if frozen else 'free')
+        if not want(n):
+          continue
+        c = elasticity_config(mode)
+        c.elasticity = e
+        if frozen:
+          c.bodies[1].frozen.all = True      # physics_test.py:901
+        c.dt = (2 * 5 / 9.8) / 100.          # :886-887
+        roll(n, c, 1, 110 if frozen else 400)
+    n = 'ball_plane_%s_e50' % mode
+    if want(n):
+      c = text_format.Parse('''
+        dt: 0.01 substeps: 10 friction: 0.5 elasticity: 0.5
+        gravity { z: -9.8 }
+        bodies {
+          name: "ball" mass: 1
+          colliders { capsule { radius: .5 length: 1.0 } }
+          inertia { x: 1 y: 1 z: 1 }
+        }
+        bodies { name: "Ground" frozen: { all: true } colliders { plane {}}}
+        defaults { qps { name: "ball" pos { z: 1.0 } vel { x: 1.0 z: -3.0 } ang { y: 1.0 } } }
+      ''', brax.Config())
+      if mode == 'spring':
+        c.dynamics_mode = 'legacy_spring'
+      roll(n, c, 0, 120)
+
+
+if __name__ == '__main__':
+  main(sys.argv[1:])

@@ -68,25 +68,32 @@ def step_case(name, config, qp, act, steps=1, note=''):
   print('%-28s substeps %5d x %d steps  %.1fs %s' % (name, config.substeps, steps, time.time() - t0, note))
 
 
-def physics_cases(only):
+def physics_cases(only, module='physics_test', prefix=''):
+  """module 'physics_test' (pbd) or 'physics_legacy_test' (the same classes with
+  `dynamics_mode: "legacy_spring"` configs; prefix 'legacy_')."""
   brax = refsys.setup()
   from google.protobuf import text_format
   import importlib
-  pt = importlib.import_module('brax.tests.physics_test')
+  pt = importlib.import_module('brax.tests.' + module)
+  legacy = module == 'physics_legacy_test'
+  _step_case = globals()['step_case']
+
+  def step_case(name, *args, **kw):   # noqa: F811 (prefixing wrapper)
+    return _step_case(prefix + name, *args, **kw)
 
   def parse(text):
     return text_format.Parse(text, brax.Config())
 
   def want(n):
-    return not only or any(n.startswith(p) for p in only)
+    return not only or any((prefix + n).startswith(p) for p in only)
 
-  if want('projectile'):   # physics_test.py:32-48
+  if want('projectile'):   # physics_test.py:32-48 / physics_legacy_test.py:32-48
     step_case('projectile', parse('''
     dt: 1 substeps: 1000
     gravity { z: -9.8 }
     bodies { name: "Ball" mass: 1 }
     defaults { qps { name: "Ball" vel {x: 1}}}
-    '''), lambda s: s.default_qp(), [])
+    ''' + ('dynamics_mode: "legacy_spring"' if legacy else '')), lambda s: s.default_qp(), [])
   for i, n in enumerate(('box_hits_ground', 'box_slide')):   # :67-82
     if want(n):
       step_case(n, parse(pt.BoxTest._CONFIG), lambda s, i=i: s.default_qp(i), [])
@@ -97,7 +104,7 @@ def physics_cases(only):
     step_case('capsule_hits_ground', parse(pt.CapsuleTest._CONFIG), lambda s: s.default_qp(0), [])
   if want('capsule_hits_capsule'):   # :340-349
     c = parse(pt.CapsuleTest._CONFIG)
-    c.dt, c.substeps = 2.0, 400
+    c.dt, c.substeps = 2.0, (1000 if legacy else 400)   # physics_legacy_test.py:298-299
     step_case('capsule_hits_capsule', c, lambda s: s.default_qp(1), [])
   for k, (mass, radius, vel) in enumerate(((2.0, 0.125, 0.0625), (5.0, 0.125, 0.03125), (1.0, 0.0625, 0.1))):
     n = 'pendulum_%d' % k    # :497-523
@@ -125,7 +132,7 @@ def physics_cases(only):
       for al, lim in zip(c.joints[0].angle_limit, limits):
         al.min, al.max = -lim, lim
       step_case(n, c, lambda s: s.default_qp(), list(tq))
-  for f in (1, 5, 10):   # :813-831
+  for f in (() if legacy else (1, 5, 10)):   # :813-831 (physics_legacy_test.py has no ForceTest)
     if want('thruster_%d' % f):
       step_case('thruster_%d' % f, parse(pt.ForceTest._CONFIG), lambda s: s.default_qp(),
                 f * np.array([1., 0., 0., 0., 0., 0.]))
@@ -204,4 +211,10 @@ if __name__ == '__main__':
   only = sys.argv[1:]
   if not only or 'unit' in only:
     unit_cases()
-  physics_cases([o for o in only if o != 'unit'] if only != ['unit'] else ['__none__'])
+  sel = [o for o in only if o != 'unit'] if only != ['unit'] else ['__none__']
+  if not sel or any(not o.startswith('legacy_') for o in sel):
+    physics_cases([o for o in sel if not o.startswith('legacy_')] or (['__none__'] if sel else []))
+  if not sel or any(o.startswith('legacy_') for o in sel):
+    # physics_legacy_test.py: the same known-answer tests in dynamics_mode legacy_spring
+    physics_cases([o for o in sel if o.startswith('legacy_')] or (['__none__'] if sel else []),
+                  'physics_legacy_test', 'legacy_')

@@ -1,0 +1,187 @@
+"""Restitution (elasticity > 0): the reference's `ElasticityTest` restated.
+
+tests/golden/bounce/ (oracle/gen_golden_bounce.py) holds trajectories of the UNMODIFIED
+reference (numpy float64) for `ElasticityTest.test_ball_bounce_vertical(_frozen)`
+(/root/reference/brax/tests/physics_test.py:880-914; config :835-861 without the far-away
+`boxwall` body) with elasticity in {0, .5, 1}, free and frozen lower ball, plus a ball thrown
+onto the plane with elasticity .5 -- in pbd and legacy_spring.  No env config of the reference
+has a non-zero elasticity, so these are the only vectors that reach `dv_rest` / `sinking`
+(colliders.py:411-430, :626-650) and the spring `-(1 + e) v_n` (colliders.py:281, :463).
+
+Every stored step is checked on its own (the T states of a trajectory = one batch of T
+environments, each stepped once from the reference's state), and the reference test's assertion
+is checked on the chained result.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from brax_b200.desc import SystemDesc
+from tests import util
+
+BOUNCE = os.path.join(util.GOLDEN, 'bounce')
+CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(BOUNCE, '*.npz')))
+
+
+def load_case(case):
+  desc = SystemDesc.from_json(open(os.path.join(BOUNCE, case + '.json')).read())
+  return desc, dict(np.load(os.path.join(BOUNCE, case + '.npz')))
+
+
+def reference_assertion(case, vel_z_after_step, v0_z, e):
+  """The literal lines physics_test.py:893-894 (free: after 400 steps, delta .02) / :913-914
+  (frozen: after 100 steps, delta .04): the upper ball has elasticity**2 of the velocity it left
+  with.  The step count is tuned to the float32 jit run: dt = (time of flight) / 100, so the
+  sampled step sits within one step of an impact and which side it falls on is rounding-level
+  (the reference's OWN float64 numpy run samples e = 1 / free just BEFORE the 4th impact, -4.85
+  instead of +5).  It is therefore asserted only where the reference's stored float64 run meets it;
+  the physics it stands for is `restitution_holds` below, asserted on every path."""
+  if not case.startswith('ball_ball') or e not in (0.0, 1.0):   # the reference's parameters: (0, 1.)
+    return True
+  if case.endswith('frozen'):
+    return abs(v0_z * e ** 2 - vel_z_after_step[99]) <= .04
+  return abs(v0_z * e ** 2 - vel_z_after_step[399]) <= .02
+
+
+def impact_steps(vz_in, vz_out):
+  """Steps in which the upper ball arrives at >= 0.5 m/s and is stopped or thrown back."""
+  return np.nonzero((vz_in < -0.5) & (vz_out > vz_in + 0.5))[0]
+
+
+def restitution_holds(case, vz_in, vz_out, e):
+  """What ElasticityTest asserts, free of the sampling phase.  Ball on the plane / on the FROZEN
+  ball: it leaves its first impact with elasticity_a * elasticity_b = e**2 of its arrival speed
+  (gravity changes the speed by g * dt = 0.1 per step around the contact: tolerance 0.15 + 2 %).
+  FREE lower ball (a three-body exchange ball -> ball -> ground, no single-impact law): e = 0 ends
+  at rest, e = 1 keeps bouncing back with the speed it started with (the two outcomes the
+  reference asserts after 400 steps)."""
+  hits = impact_steps(vz_in, vz_out)
+  if len(hits) == 0:
+    return False
+  if case.endswith('free'):
+    if e == 0.0:
+      return np.abs(vz_out[-20:]).max() <= 0.05
+    if e == 1.0:
+      return abs(vz_out[-110:].max() - vz_in[0]) <= 0.15 + 0.02 * vz_in[0]
+    return True
+  i = hits[0]
+  arrive = -vz_in[i]
+  leave = vz_out[i:i + 3].max()
+  return abs(leave - e ** 2 * arrive) <= 0.15 + 0.02 * arrive
+
+
+def chain(step_fn, g, steps):
+  """Rolls `steps` steps from the first stored state; vel.z of body 0 before / after each."""
+  cur = {k: g[k][0] for k in util.QP_KEYS}
+  vz_in, vz = [], []
+  for _ in range(steps):
+    vz_in.append(float(cur['vel'][0, 2]))
+    out = step_fn(cur)
+    cur = {k: out[k][0] for k in util.QP_KEYS}
+    vz.append(float(cur['vel'][0, 2]))
+  return np.asarray(vz_in), np.asarray(vz)
+
+
+def test_cases_present():
+  assert len(CASES) == 14, CASES
+  descs = [load_case(c)[0] for c in CASES]
+  assert any(p['elasticity_a'] * p['elasticity_b'] > 0 and p['two_way'] for d in descs for p in d.pairs)
+  assert any(p['elasticity_a'] * p['elasticity_b'] > 0 and not p['two_way'] and p['kind'] == 'capsule_capsule' for d in descs for p in d.pairs)
+  assert any(p['elasticity_a'] * p['elasticity_b'] > 0 and p['kind'] == 'capsule_plane' for d in descs for p in d.pairs)
+
+
+@pytest.mark.parametrize('case', CASES)
+def test_oracle_reproduces_reference_bounce(case):
+  from oracle.oracle import Oracle
+  desc, g = load_case(case)
+  e = float(g['elasticity'])
+  t_n = g['pos'].shape[0]
+  vz_in_ref, vz_ref = g['vel'][:, 0, 2], g['out_vel'][:, 0, 2]
+  v0 = float(g['vel'][0, 0, 2])
+  # the data is sane: the reference's run shows the restitution its test asserts
+  assert restitution_holds(case, vz_in_ref, vz_ref, e)
+  literal = reference_assertion(case, vz_ref, v0, e)
+  # every stored step from the reference's own state: float64 oracle == reference (the pin)
+  o64 = Oracle(desc, np.float64)
+  out = o64.step(g['pos'], g['rot'], g['vel'], g['ang'], g['act'])
+  for k in util.QP_KEYS + util.INFO_KEYS:
+    ref = g['out_' + k]
+    if ref.size == 0:
+      continue
+    np.testing.assert_allclose(out[k], ref, rtol=0, atol=1e-9 * max(1.0, np.abs(ref).max()), err_msg='%s %s' % (case, k))
+  # chained: the float64 oracle follows the reference's whole trajectory, the float32 oracle shows
+  # the same restitution
+  for dtype in (np.float64, np.float32):
+    o = Oracle(desc, dtype)
+    vz_in, vz = chain(lambda cur: o.step(cur['pos'], cur['rot'], cur['vel'], cur['ang'], g['act'][0]), g, t_n)
+    assert restitution_holds(case, vz_in, vz, e), (case, dtype)
+    if dtype == np.float64:
+      np.testing.assert_allclose(vz, vz_ref, rtol=0, atol=1e-7)
+      assert reference_assertion(case, vz, v0, e) == literal
+  # the float32 oracle step by step from the reference's states: equal to float32 rounding on the
+  # impact steps (where the restitution acts) and in flight.  Only the upper ball (body 0) is compared, on those steps: steps with a body RESTING on another
+  # (penetration within rounding of 0: `penetration > 0` is a coin flip per substep, and these
+  # scenes stack two spheres exactly on top of each other) are compared under the parity policy
+  # of tests/test_gpu_parity.py on the GPU side, not here.
+  o32 = Oracle(desc, np.float32).step(g['pos'], g['rot'], g['vel'], g['ang'], g['act'])
+  hits = impact_steps(vz_in_ref, vz_ref)
+  rows0 = _rows_of_body0(desc)
+  sel = np.abs(g['out_contact_penetration'][:, rows0]).min(axis=1) > 2e-2   # upper ball in flight
+  sel[hits] = True
+  assert len(hits) >= 1 and sel.sum() >= t_n // 4
+  for k in ('pos', 'rot'):
+    np.testing.assert_allclose(o32[k][sel, 0], g['out_' + k][sel, 0], rtol=1e-5, atol=1e-5, err_msg=k)
+  np.testing.assert_allclose(o32['vel'][sel, 0], g['out_vel'][sel, 0], rtol=1e-4, atol=2e-3)
+
+
+def _rows_of_body0(desc):
+  """Contact rows (group-major, pair-major) of the pairs that involve body 0, the upper ball."""
+  rows, k = [], 0
+  for p in desc.pairs:
+    if p['body_a'] == 0 or p['body_b'] == 0:
+      rows += list(range(k, k + p['n_contacts']))
+    k += p['n_contacts']
+  return rows
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('case', CASES)
+def test_cuda_path_on_reference_bounce(case):
+  """The sm_100a kernel (through bx_step / bx_step_host) on every stored step -- under the parity
+  policy of tests/test_gpu_parity.py -- and chained, against the reference test's assertion."""
+  import torch
+  if not torch.cuda.is_available():
+    pytest.skip('no CUDA device')
+  from brax_b200.system import QP, System
+  from tests.test_gpu_parity import _flat, check_step
+  desc, g = load_case(case)
+  e = float(g['elasticity'])
+  t_n = g['pos'].shape[0]
+  s = System(desc)
+  ins = [g[k].astype(np.float32) for k in util.QP_KEYS]
+  act = g['act'].astype(np.float32)
+  dev = [torch.from_numpy(x).cuda() for x in ins]
+  qp, info = s.step(QP(*dev), torch.from_numpy(act).cuda())
+  torch.cuda.synchronize()
+  # the steps in which a contact opens / closes are discrete decisions on float compares (the
+  # ball touches down inside ONE substep): such a step may differ between two correct float32
+  # evaluations; T = 110..400 "environments", so the policy's outlier budget applies
+  _, stats = check_step(desc, ins, act, _flat(qp, info), strict_frac=0.97, outlier_frac=0.02)
+  print(case, stats)
+  # chained through the host path (B = 1): the reference test's own assertion
+  def step_fn(cur):
+    q, _ = s.step(QP(cur['pos'], cur['rot'], cur['vel'], cur['ang']), act[0])
+    return {k: np.asarray(getattr(q, k))[None] for k in util.QP_KEYS}
+  vz_in, vz = chain(step_fn, {k: g[k].astype(np.float32) for k in util.QP_KEYS}, t_n)
+  assert np.isfinite(vz).all()
+  assert restitution_holds(case, vz_in, vz, e), (case, vz[95:105])
+  print(case, 'literal reference assertion on the CUDA chain:', reference_assertion(case, vz, float(g['vel'][0, 0, 2]), e),
+        '(reference float64 run: %s)' % reference_assertion(case, g['out_vel'][:, 0, 2], float(g['vel'][0, 0, 2]), e))
+  # the impact steps themselves, tightly: float32 kernel vs the reference's float64 result
+  hits = impact_steps(g['vel'][:, 0, 2], g['out_vel'][:, 0, 2])
+  got = _flat(qp, info)
+  assert len(hits) >= 1
+  np.testing.assert_allclose(got['pos'][hits, 0], g['out_pos'][hits, 0], rtol=1e-5, atol=1e-5)
+  np.testing.assert_allclose(got['vel'][hits, 0], g['out_vel'][hits, 0], rtol=1e-4, atol=2e-3)

@@ -156,6 +156,40 @@ def test_env_step_on_harvested_states(variant, b, steps):
     assert torch.equal(eo['obs'], st.obs)
 
 
+@pytest.mark.parametrize('variant', ['fetch', 'grasp'])
+def test_obs_is_built_before_the_target_teleport(variant):
+  """Every env scores a hit, so every target is teleported inside the launch; the obs (target
+  body's pos_local included) must still be that of the state BEFORE the teleport (fetch.py:56
+  vs :88-93, grasp.py:88 vs :131-136) for every CTA size, i.e. whichever warp owns the target
+  body's rows (the teleporting warp itself: no other warp reads the row it rewrites)."""
+  torch = _torch()
+  from brax_b200.envs import State
+  from oracle import env_oracle
+  sysname, env = _env(variant)
+  b = 512
+  qp, rng = _harvest(env.sys, b, 10, 3)
+  act = rng.uniform(-1, 1, (b, env.action_size)).astype(np.float32)
+  pos = qp.pos.clone()
+  src = env.env.ref_body if env.env.kind == 'fetch' else env.env.object_body
+  pos[:, env.env.target_body] = pos[:, src] + 0.05
+  qp = type(qp)(pos, qp.rot, qp.vel, qp.ang)
+  rand = rng.uniform(0, 1, (b, 3)).astype(np.float32)
+  ins = [getattr(qp, k).cpu().numpy() for k in util.QP_KEYS]
+  for w in (8, 10, 12, 16):
+    env.sys.configure(threads_per_block=32 * w)
+    for _ in range(3):   # the race this guards against was timing dependent
+      st = env.step(State(qp, None, None, None), torch.from_numpy(act).cuda(), rand=torch.from_numpy(rand).cuda())
+      torch.cuda.synchronize()
+      got = {'obs': st.obs.cpu().numpy(), 'reward': st.reward.cpu().numpy(), 'done': st.done.cpu().numpy(),
+             'metrics': torch.stack([st.metrics[k] for k in env.env.metric_names()], -1).cpu().numpy()}
+      r32 = check_env(sysname, env.env, ins, act, got)
+      assert (got['metrics'][:, 0] > 0).mean() > 0.9, w
+      want = env_oracle.env_teleport(env.env, r32['qp']['pos'], got['metrics'][:, 0], rand, np.float32)
+      tb = env.env.target_body
+      np.testing.assert_allclose(st.qp.pos.cpu().numpy()[:, tb], want[:, tb], rtol=1e-5, atol=1e-4)
+      assert np.abs(want[:, tb] - r32['qp']['pos'][:, tb]).max() > 0.5   # the targets did move
+
+
 def test_env_rollout_equals_repeated_steps():
   """bx_rollout writes the env outputs of EVERY step: [T,B,...] bit-identical to T
   env steps; ragged and unbatched shapes equal the same envs inside a big batch."""
@@ -550,6 +584,25 @@ def test_eval_wrapper_on_reference_sequences():
   ea, eb = a.info['eval_metrics'], b.info['eval_metrics']
   assert float(ea.active_episodes.sum()) == 0 and float(ea.episode_steps.max()) == 6
   assert torch.equal(ea.episode_steps, eb.episode_steps)
+  assert torch.allclose(ea.episode_metrics['reward'], eb.episode_metrics['reward'], rtol=1e-5, atol=1e-5)
+
+
+def test_eval_wrapper_rollout_with_action_repeat():
+  """EvalWrapper.rollout == chained EvalWrapper.step with action_repeat = 2: `steps` advances by
+  action_repeat per wrapped step (wrappers.py:112), so does eval_metrics.episode_steps."""
+  torch = _torch()
+  from brax_b200 import envs
+  ev = envs.create('ant', episode_length=8, action_repeat=2, auto_reset=True, eval_metrics=True)
+  s0 = ev.reset(96, device='cuda', seed=9)
+  acts = torch.rand(6, 96, ev.action_size, device='cuda') * 2 - 1
+  a, _ = ev.rollout(s0, acts)
+  b = s0
+  for t in range(6):
+    b = ev.step(b, acts[t])
+  ea, eb = a.info['eval_metrics'], b.info['eval_metrics']
+  assert float(eb.episode_steps.max()) == 8 and float(ea.active_episodes.sum()) == 0
+  assert torch.equal(ea.episode_steps, eb.episode_steps)
+  assert torch.equal(ea.active_episodes, eb.active_episodes)
   assert torch.allclose(ea.episode_metrics['reward'], eb.episode_metrics['reward'], rtol=1e-5, atol=1e-5)
 
 

@@ -17,8 +17,9 @@ every field is asserted as
 
 i.e. the stated tolerance plus a small multiple of the MEASURED float32
 conditioning of that very step (o32/o64 = float32/float64 oracle on the same
-inputs), and additionally the stated tolerance alone must hold for >= 90 % of
-all pos/rot elements (measured: 92 % grasp .. 100 % ant).  Velocity-like fields (vel, ang, Info impulses) get a
+inputs), and additionally the stated tolerance alone (against o32, or -- where o32 itself is further
+from o64 than that -- the kernel being at least as close to o64 as o32 is) must hold for >= 90 %
+of all pos/rot elements (measured: 93 % grasp .. 100 % ant, profiles/r02_parity_report.txt).  Velocity-like fields (vel, ang, Info impulses) get a
 further floor of VEL_ULPS * 6e-8 / dt_sub: velocity_projection computes
 (pos - pos_prev) / dt_sub, so half an ulp of a position near 1 (6e-8) IS
 1.2e-5 (ant) .. 3.2e-5 (humanoid) of velocity whatever the arithmetic order.
@@ -51,9 +52,14 @@ def _system(name):
   return load_system(name)
 
 
+def _desc(name):
+  """A system name (brax_b200/systems/<name>.json) or a SystemDesc itself."""
+  return util.load_desc(name) if isinstance(name, str) else name
+
+
 def _oracle(name, dtype=np.float32):
   from oracle.oracle import Oracle
-  return Oracle(util.load_desc(name), dtype)
+  return Oracle(_desc(name), dtype)
 
 
 def _flat(qp, info):
@@ -86,16 +92,19 @@ def check_step(name, ins, act, got, strict_frac=0.90, outlier_frac=OUTLIER_FRAC)
   colliders.py:366, `sinking` :430, limit masks joints.py:346) that two correct
   float32 evaluations can take differently when the compared values are within
   an ulp; such an env then differs by far more than any smooth bound.  With
-  B >= 200 up to OUTLIER_FRAC of the envs may miss the tolerance (never by more
-  than OUTLIER_BOUND x); on the small golden batches none may."""
+  B >= 200 up to OUTLIER_FRAC of the envs may miss the tolerance (by no more than
+  OUTLIER_BOUND x, unless the env's Info accumulators show the decision that was taken
+  differently: then 1e-2 absolute on pos / rot); on the small golden batches none may."""
   ref = _oracle(name, np.float32).step(*ins, act)
   r64 = _oracle(name, np.float64).step(*ins, act)
   b = ref['pos'].shape[0]
   allowed = int(outlier_frac * b) if b >= 200 else 0
   stats = {}
-  vel_floor = VEL_ULPS * 6e-8 / util.load_desc(name).dt_sub
+  vel_floor = VEL_ULPS * 6e-8 / _desc(name).dt_sub
+  name = name if isinstance(name, str) else name.name
   bad_env = np.zeros(b, bool)
-  for k in util.QP_KEYS + util.INFO_KEYS:
+  flip_env = np.zeros(b, bool)   # envs whose Info accumulators show a decision taken differently
+  for k in ACCUMULATORS + tuple(x for x in util.QP_KEYS + util.INFO_KEYS if x not in ACCUMULATORS):
     if ref[k].size == 0:
       continue
     err = np.abs(got[k] - ref[k])
@@ -110,9 +119,27 @@ def check_step(name, ins, act, got, strict_frac=0.90, outlier_frac=OUTLIER_FRAC)
       tol = tol + vel_floor
     assert np.isfinite(got[k]).all(), (name, k)
     over = (err > tol).reshape(b, -1).any(axis=1)
-    assert not (err > OUTLIER_BOUND * tol).any(), (name, k, float(err.max()))
+    if k in ACCUMULATORS:
+      # An Info accumulator (the summed impulses of all substeps) far off = a discrete decision taken
+      # differently in some substep: a torque zeroed at its angle limit (actuators.py:103-104: the whole
+      # strength * act of that substep), a contact opened.  Such an env spends the outlier budget; its
+      # state then differs by that impulse integrated over the rest of the step (measured: humanoid,
+      # one torque flip in substep 3 of 8 -> 0.4 rad/s, 7e-4 in rot; tools/flip_probe.py) and is held
+      # to an absolute bound instead of a multiple of the rounding tolerance.
+      flip_env |= (err > OUTLIER_BOUND * tol).reshape(b, -1).any(axis=1)
+    else:
+      far = (err > OUTLIER_BOUND * tol).reshape(b, -1).any(axis=1)
+      assert not (far & ~flip_env).any(), (name, k, float(err.max()))
+      if k in ('pos', 'rot'):
+        assert not (err > 1e-2 * np.maximum(1.0, np.abs(ref[k]))).any(), (name, k, float(err.max()))
     bad_env |= over
-    stats[k] = float((err <= base).mean())
+    # "literal": within the stated tolerance of the float32 oracle, or -- where the float32 oracle
+    # itself is further than that from the float64 reference -- at least as close to the float64
+    # reference as the float32 oracle is.  (The kernel does not reproduce the oracle's rounding:
+    # e.g. it clips a joint angle without the arctan2 -> sincos round trip, bx_math.cuh clip_dir,
+    # and lands CLOSER to float64 than o32 on stiff chains such as pusher: profiles/r02_parity_report.txt.)
+    acc = np.abs(got[k] - r64[k]) <= base + np.abs(ref[k].astype(np.float64) - r64[k])
+    stats[k] = float(((err <= base) | acc).mean())
   pen, pen64 = ref['contact_penetration'], r64['contact_penetration']
   if pen.size:
     mism = (got['contact_penetration'] > 0) != (pen > 0)
@@ -194,7 +221,7 @@ def _harvest(s, b, steps, seed):
 
 
 @pytest.mark.parametrize('name,b,steps', [
-    ('ant', 2048, 30), ('humanoid', 2048, 30), ('grasp', 1024, 20),
+    ('ant', 2048, 30), ('humanoid', 2048, 30), ('grasp', 2048, 20),
     ('fetch', 1024, 20), ('ant_spring', 1024, 30), ('humanoid_spring', 1024, 30),
     # two rows per contact item (pbd and legacy_spring), many rows per body, two-way pairs
     ('fetch_spring', 1024, 20), ('humanoid_standup', 1024, 20), ('half_cheetah', 1024, 6)])
@@ -407,7 +434,7 @@ def test_full_size_properties(name, b):
   if d.dynamics_mode == 'pbd':
     assert np.abs(a['joint_vel']).max() == 0 and np.abs(a['joint_ang']).max() == 0
   # random subset against the oracle
-  idx = np.sort(np.random.default_rng(1).choice(b, 512, replace=False))
+  idx = np.sort(np.random.default_rng(1).choice(b, 2048, replace=False))
   ins = [getattr(qp, k).cpu().numpy()[idx] for k in util.QP_KEYS]
   check_step(name, ins, act.cpu().numpy()[idx], {k: v[idx] for k, v in a.items()})
 

@@ -35,19 +35,29 @@ CASES = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(KAT, '*.
 # of 2.5e-6 next to 1 -> 2-4 % off in ANY float32 evaluation).  For those the float32
 # paths are compared with each other (CUDA vs float32 oracle) instead.
 JIT_PREFIXES = ('capsule_hits', 'pendulum', 'actuator2d', 'actuator3d')
+JIT_PREFIXES += tuple('legacy_' + p for p in JIT_PREFIXES)
 # the pendulum config (solver_scale_pos .2) rings at the substep rate: last-bit differences
 # grow ~1e4 x per 30 substeps in vel/ang (measured oracle vs reference: 0 at 20 substeps,
 # 3e-12 at 50, O(1) at 100) while pos/rot -- what the reference asserts -- stay put
-CHAOTIC_PREFIXES = ('pendulum',)
+CHAOTIC_PREFIXES = ('pendulum', 'legacy_pendulum')
 
 
 def almost(a, b, places):
   return abs(float(a) - float(b)) < 0.5 * 10.0 ** (-places)
 
 
+def base_case(case):
+  """legacy_<case>: the same test of brax/tests/physics_legacy_test.py (dynamics_mode legacy_spring;
+  the assertions are line for line those of physics_test.py)."""
+  return case[len('legacy_'):] if case.startswith('legacy_') else case
+
+
 def known_answer(case, q, g):
   """The assertions of the reference test this case restates (file:line in the
-  comments); q = dict of final pos/rot/vel/ang [N,..], angles = joint-0 angles."""
+  comments, physics_test.py; physics_legacy_test.py:45-48, :73, :80-83, :233, :240, :289-292,
+  :302-303, :478, :594, :638-639, :709-713 for the legacy_ cases); q = dict of final
+  pos/rot/vel/ang [N,..], angles = joint-0 angles."""
+  case = base_case(case)
   pos, vel, ang = q['pos'], q['vel'], q['ang']
   if case == 'projectile':            # physics_test.py:45-48
     return almost(vel[0, 2], -9.8, 2) and almost(pos[0, 0], 1, 2) and almost(pos[0, 2], -9.8 / 2, 2)
@@ -111,7 +121,10 @@ def run_oracle(desc, g, dtype):
 def test_cases_present():
   assert len(CASES) >= 20, CASES
   for prefix in ('projectile', 'box_', 'sphere_', 'capsule_hits_', 'pendulum', 'actuator1d', 'actuator2d',
-                 'actuator3d', 'thruster', 'twister'):
+                 'actuator3d', 'thruster', 'twister',
+                 # brax/tests/physics_legacy_test.py (legacy_spring): every in-scope test
+                 'legacy_projectile', 'legacy_box_', 'legacy_sphere_', 'legacy_capsule_hits_', 'legacy_pendulum',
+                 'legacy_actuator1d', 'legacy_actuator2d', 'legacy_actuator3d'):
     assert any(c.startswith(prefix) for c in CASES), prefix
 
 
@@ -219,6 +232,13 @@ def test_cuda_path_passes_reference_test(case):
     pytest.skip('no CUDA device')
   from brax_b200.system import QP, System
   desc, g = load_case(case)
+  o32 = run_oracle(desc, g, np.float32)
+  if not all(np.isfinite(o32[k]).all() for k in util.QP_KEYS):
+    # physics_legacy_test.py's Actuator1DTest (dt_sub = 0.05 against a joint stiffness of 5000) is
+    # unstable in POSITION: the reference's own float64 run ends with the bob at |pos| ~ 1e84 and only
+    # asserts the joint angle (it never runs under jit); float32 overflows on any implementation
+    assert np.abs(g['out_pos']).max() > 1e30, case
+    pytest.skip('reference scene overflows float32 (reference float64 |pos| = %.1e)' % np.abs(g['out_pos']).max())
   s = System(desc)
   qp = QP(*[g['in_' + k].astype(np.float32) for k in util.QP_KEYS])
   act = g['act'].astype(np.float32)
@@ -231,7 +251,6 @@ def test_cuda_path_passes_reference_test(case):
     assert known_answer(case, got, g), case
   # the two float32 evaluations (CUDA with FMA contraction, oracle without) after 80..10000
   # substeps in one call
-  o32 = run_oracle(desc, g, np.float32)
   report = {k: float(np.abs(got[k] - o32[k]).max()) for k in util.QP_KEYS}
   print(case, 'max |cuda - o32|', report)
   # measured: <= 4.4e-4 (pos) / 5.2e-5 (rot) on every non-chaotic case; the pendulum's bob rings
