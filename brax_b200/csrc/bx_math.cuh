@@ -47,6 +47,12 @@ BXD float bx_mul_rcp(float a, float b, float r) {
 #endif
 }
 BXD float bx_div(float a, float b) { return bx_mul_rcp(a, b, bx_rcp(b)); }
+// 1 / sqrt(a), a > 0: MUFU.RSQ + one Newton step
+BXD float bx_rsqrt(float a) {
+  float y;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(a));
+  return y * fmaf(-0.5f * a * y, y, 1.5f);
+}
 BXD float bx_sqrt(float a) {
   float y;
   asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(a));
@@ -66,6 +72,28 @@ BXD V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
 BXD V3 vdiv(V3 a, float s) {
   float r = bx_rcp(s);
   return v3(bx_mul_rcp(a.x, s, r), bx_mul_rcp(a.y, s, r), bx_mul_rcp(a.z, s, r));
+}
+// a / mass, given inv_mass = the float32 quotient 1 / mass from the table
+#ifndef BX_INVMASS
+#define BX_INVMASS 1
+#endif
+// Quaternion normalisation as rot * rsqrt(|rot|^2) instead of rot / sqrt(|rot|^2): OFF.  Measured: it
+// breaks parity on resting bodies -- sqrt of an already unit |rot|^2 rounds to exactly 1 and the exact
+// quotient returns rot unchanged, so velocity_projection (integrators.py:139-146) yields ang = 0 exactly
+// for a body at rest, in the reference and here; a 1-ulp scale factor perturbs every component, leaves
+// ~1e-5 rad/s of noise per substep and flips static-friction / penetration decisions.
+#ifndef BX_NORM_RSQRT
+#define BX_NORM_RSQRT 0
+#endif
+#ifndef BX_TORQUE_ARC
+#define BX_TORQUE_ARC 1
+#endif
+BXD V3 vdivm(V3 a, float mass, float inv_mass) {
+#if BX_FAST_DIV && BX_INVMASS
+  return v3(a.x * inv_mass, a.y * inv_mass, a.z * inv_mass);
+#else
+  return v3(bx_mul_rcp(a.x, mass, inv_mass), bx_mul_rcp(a.y, mass, inv_mass), bx_mul_rcp(a.z, mass, inv_mass));
+#endif
 }
 BXD float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 BXD V3 cross(V3 a, V3 b) {
@@ -178,14 +206,16 @@ BXD float bx_acos(float x) {
 // and outside it is the limit's own (cos, sin) from the table (lcs = {cos lo, sin lo, cos hi, sin hi}).
 // psi < lo / psi > hi are decided by the sign of sin(psi - limit) = (cos lim * y - sin lim * x) / r on
 // the half plane (sign of y) where psi - limit cannot wrap; limits at or beyond +-pi never clip.
+BXD void angle_outside(float x, float y, float4 lcs, float lo, float hi, bool* below, bool* above) {
+  const float d_lo = lcs.x * y - lcs.y * x, d_hi = lcs.z * y - lcs.w * x;
+  *below = lo >= 0.f ? (y < 0.f || d_lo < 0.f) : (y < 0.f && d_lo < 0.f);
+  *above = hi <= 0.f ? (y > 0.f || d_hi > 0.f) : (y > 0.f && d_hi > 0.f);
+}
 BXD void clip_dir(float x, float y, float4 lcs, float lo, float hi, float* c, float* s, float* outside) {
   const float r2 = x * x + y * y;
-  float ri;
-  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(ri) : "f"(r2));
-  ri = ri * fmaf(-0.5f * r2 * ri, ri, 1.5f);  // one Newton step
-  const float d_lo = lcs.x * y - lcs.y * x, d_hi = lcs.z * y - lcs.w * x;
-  const bool below = lo >= 0.f ? (y < 0.f || d_lo < 0.f) : (y < 0.f && d_lo < 0.f);
-  const bool above = hi <= 0.f ? (y > 0.f || d_hi > 0.f) : (y > 0.f && d_hi > 0.f);
+  const float ri = bx_rsqrt(r2);
+  bool below, above;
+  angle_outside(x, y, lcs, lo, hi, &below, &above);
   float cc = r2 > 0.f ? x * ri : 1.f, ss = r2 > 0.f ? y * ri : 0.f;  // arctan2(0, 0) = 0
   cc = below ? lcs.x : cc; ss = below ? lcs.y : ss;
   cc = above ? lcs.z : cc; ss = above ? lcs.w : ss;                  // clip = min(max(psi, lo), hi)

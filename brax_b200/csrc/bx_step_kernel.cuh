@@ -278,6 +278,47 @@ BXS void axis_angle_spherical(const float4* jq, const M3& mp, const M3& mc, V3* 
   angle[0] = psi; angle[1] = theta; angle[2] = phi;
 }
 
+// The same axes, and per dof only WHETHER the angle lies outside [lo, hi]: all a Torque actuator asks
+// of the angle (actuators.py:103-104).  psi / phi are signed angles: decided from their (cos, sin)
+// without arctan2 (bx_math.cuh angle_outside); theta is compared as a value.
+BXS void axis_outside_revolute(const float4* jq, const M3& mp, const M3& mc, V3* axis, bool* outside) {
+  V3 ax = mrot(mp, f3(jq[JQ_AXIS_P]));
+  V3 ref_p = mrot(mp, f3(jq[JQ_AXIS_P + 2]));
+  V3 ref_c = mrot(mc, f3(jq[JQ_AXIS_C + 2]));
+  const float4 l01 = jq[JQ_LIMIT];
+  bool below, above;
+  angle_outside(dot(ref_p, ref_c), dot(cross(ref_p, ref_c), ax), jq[JQ_LIMCS], l01.x, l01.y, &below, &above);
+  axis[0] = ax;
+  outside[0] = below || above;
+}
+BXS void axis_outside_spherical(const float4* jq, const M3& mp, const M3& mc, V3* axis, bool* outside) {
+  V3 a1p = mrot(mp, f3(jq[JQ_AXIS_P]));
+  V3 a2p = mrot(mp, f3(jq[JQ_AXIS_P + 1]));
+  V3 a1c = mrot(mc, f3(jq[JQ_AXIS_C]));
+  V3 a2c = mrot(mc, f3(jq[JQ_AXIS_C + 1]));
+  V3 a3c = mrot(mc, f3(jq[JQ_AXIS_C + 2]));
+  const float4 l01 = jq[JQ_LIMIT], l2 = jq[JQ_LIMIT + 1];
+  V3 lon = cross(a3c, a1p);
+  lon = vdiv(lon, 1e-10f + safe_norm(lon));
+  bool below, above;
+  angle_outside(dot(a2p, lon), dot(cross(a2p, lon), a1p), jq[JQ_LIMCS], l01.x, l01.y, &below, &above);
+  outside[0] = below || above;
+  V3 xz = dot(a1p, a1c) * a1c + dot(a1p, a2c) * a2c;
+  xz = vdiv(xz, 1e-10f + safe_norm(xz));
+  float theta = bx_acos(clipf(dot(xz, a1p), -1.f, 1.f)) * signf(dot(a1p, a3c));
+  outside[1] = theta < l01.z || theta > l01.w;
+  angle_outside(dot(a2c, lon), dot(cross(a2c, lon), -a3c), jq[JQ_LIMCS + 2], l2.x, l2.y, &below, &above);
+  outside[2] = below || above;
+  axis[0] = a1p; axis[1] = a2c; axis[2] = a3c;
+}
+BXS void joint_axis_outside(int kind, const float4* jq, const M3& mp, const M3& mc, V3* axis, bool* outside) {
+  if (BXF_IS(kind == BX_JOINT_REVOLUTE || kind == BX_JOINT_SPRING_REVOLUTE, BXF_REVOLUTE,
+             BXF_SPHERICAL | BXF_UNIVERSAL))
+    axis_outside_revolute(jq, mp, mc, axis, outside);
+  else
+    axis_outside_spherical(jq, mp, mc, axis, outside);
+}
+
 BXS int joint_dof(int kind) {
   return BXF_IS(kind == BX_JOINT_REVOLUTE || kind == BX_JOINT_SPRING_REVOLUTE, BXF_REVOLUTE,
                 BXF_SPHERICAL | BXF_UNIVERSAL)
@@ -315,8 +356,14 @@ BXS void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
     Q4 rp = ldq(c, L::BQ * ji.y + ro);
     Q4 rc = ldq(c, L::BQ * ji.z + ro);
     V3 axis[3];
-    float angle[3];
-    joint_axis_angle(kind, jq, rp, rc, axis, angle);
+    float angle[3] = {0.f, 0.f, 0.f};
+    bool outside[3] = {false, false, false};
+    const bool torque_act = BXF_IS(ai.x == BX_ACT_TORQUE, BXF_TORQUE, BXF_ANGLE);
+    {
+      const M3 Rp = rotmat(rp), Rc = rotmat(rc);
+      if (BX_TORQUE_ARC && torque_act) joint_axis_outside(kind, jq, Rp, Rc, axis, outside);
+      else joint_axis_angle(kind, jq, Rp, Rc, axis, angle);
+    }
     const float strength = c.tf[h.fo_act + a].x;
     const int dof = joint_dof(kind);
     const float4 l01 = jq[JQ_LIMIT], l2 = jq[JQ_LIMIT + 1];
@@ -332,10 +379,9 @@ BXS void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
         idx = min(max(idx, 0), h.act_size - 1);
         float av = act_at(c, h, idx) * m;
         float t;
-        if (BXF_IS(ai.x == BX_ACT_TORQUE, BXF_TORQUE, BXF_ANGLE)) {
+        if (torque_act) {
           t = av * strength * -1.f;
-          t = angle[d] < lo[d] ? 0.f : t;
-          t = angle[d] > hi[d] ? 0.f : t;
+          t = (BX_TORQUE_ARC ? outside[d] : (angle[d] < lo[d] || angle[d] > hi[d])) ? 0.f : t;   // actuators.py:103-104
         } else {
           float tgt = clipf(av * 0.017453292519943295f, lo[d], hi[d]);  // act * pi / 180 (actuators.py:83)
           t = (tgt - angle[d]) * strength;
@@ -406,18 +452,28 @@ BXS void kinetic(const BxHeader& h, V3 pm, V3 rm, V3 vel, V3 ang, V3* pos, Q4* r
   *pos = *pos + (vel * h.dt) * pm;
   V3 w = (ang * rm) * h.half_dt;
   Q4 r = *rot + quat_mul(q4(0.f, w.x, w.y, w.z), *rot);
+#if BX_FAST_DIV && BX_NORM_RSQRT
+  float rn = bx_rsqrt(r.w * r.w + r.x * r.x + r.y * r.y + r.z * r.z);  // rot / norm(rot)
+  *rot = q4(r.w * rn, r.x * rn, r.y * rn, r.z * rn);
+#else
   float n = bx_sqrt(r.w * r.w + r.x * r.x + r.y * r.y + r.z * r.z);
   float rn = bx_rcp(n);
   *rot = q4(bx_mul_rcp(r.w, n, rn), bx_mul_rcp(r.x, n, rn), bx_mul_rcp(r.y, n, rn), bx_mul_rcp(r.z, n, rn));
+#endif
 }
 
 // Euler.velocity_projection integrators.py:122-146
 BXS void velocity_projection(const BxHeader& h, V3 pm, V3 rm, V3 pos, V3 ppos, Q4 prot, Q4* rot,
                              V3* vel, V3* ang) {
   Q4 r = *rot;
+#if BX_FAST_DIV && BX_NORM_RSQRT
+  float rn = bx_rsqrt(r.w * r.w + r.x * r.x + r.y * r.y + r.z * r.z);
+  Q4 nr = q4(r.w * rn, r.x * rn, r.y * rn, r.z * rn);
+#else
   float n = bx_sqrt(r.w * r.w + r.x * r.x + r.y * r.y + r.z * r.z);
   float rn = bx_rcp(n);
   Q4 nr = q4(bx_mul_rcp(r.w, n, rn), bx_mul_rcp(r.x, n, rn), bx_mul_rcp(r.y, n, rn), bx_mul_rcp(r.z, n, rn));
+#endif
   *vel = ((pos - ppos) * h.inv_dt) * pm;
   Q4 dq = quat_mul(nr, qconj(prot));
   float sg = dq.w >= 0.f ? 1.f : -1.f;
@@ -492,9 +548,9 @@ BXS void position_update(V3 wp, V3 wc, V3 pos_p, V3 pos_c, Q4 rp, Q4 rc,
   float w2 = im_c + dot(cr2, ii_c * cr2);
   float dl = bx_div(-cn, w1 + w2 + 1e-6f);
   V3 p = dl * n;
-  dp->pos = scale_pos * vdiv(p, m_p);
+  dp->pos = scale_pos * vdivm(p, m_p, im_p);
   dp->rot = scale_pos * (.5f * vec_quat_mul(ii_p * cross(r_p, p), rp));
-  dc->pos = scale_pos * vdiv(-p, m_c);
+  dc->pos = scale_pos * vdivm(-p, m_c, im_c);
   dc->rot = scale_pos * (-.5f * vec_quat_mul(ii_c * cross(r_c, p), rc));
 }
 
@@ -754,7 +810,7 @@ BXS void c1_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
       float dl = bx_div(-cc, w1 + 1e-6f);
       float cm = cc < 0.f ? 1.f : 0.f;
       V3 p = (dl * n) * cm;
-      V3 dpos = cs * vdiv(p, ma);
+      V3 dpos = cs * vdivm(p, ma, ima);
       Q4 drot = cs * (.5f * vec_quat_mul(iia * cross(rp, p), ra));
       // static friction
       V3 r1 = rotate(rp, qconj(ra));
@@ -767,7 +823,7 @@ BXS void c1_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
       float dlt = bx_div(-c2, w1t + 0.f);
       float sm = fabsf(dlt) < fabsf(friction * dl) ? 1.f : 0.f;
       V3 pt = ((dlt * n2) * sm) * cm;
-      dpos = dpos + cs * vdiv(pt, ma);
+      dpos = dpos + cs * vdivm(pt, ma, ima);
       drot = drot + cs * (.5f * vec_quat_mul(iia * cross(rp, pt), ra));
       cacc_add(acc.la, acc.sa, dpos, wxyz(drot));
       dl_out = dl * cm;
@@ -783,7 +839,7 @@ BXS void c1_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
       float dl = bx_div(-cc, w1 + w2 + 1e-6f);
       float cm = cc < 0.f ? 1.f : 0.f;
       V3 p = (dl * n) * cm;
-      V3 dpa = cs * vdiv(p, ma), dpb = cs * vdiv(-p, mb);
+      V3 dpa = cs * vdivm(p, ma, ima), dpb = cs * vdivm(-p, mb, imb);
       Q4 dra = cs * (.5f * vec_quat_mul(iia * cross(rp, p), ra));
       Q4 drb = cs * (-.5f * vec_quat_mul(iib * cross(rc, p), rb));
       // static friction
@@ -799,8 +855,8 @@ BXS void c1_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
       float dlt = bx_div(-c2, w1t + w2t);
       float sm = fabsf(dlt) < fabsf(dl) ? 1.f : 0.f;
       V3 pt = ((dlt * n2) * sm) * cm;
-      dpa = dpa + cs * vdiv(pt, ma);
-      dpb = dpb + cs * vdiv(-pt, mb);
+      dpa = dpa + cs * vdivm(pt, ma, ima);
+      dpb = dpb + cs * vdivm(-pt, mb, imb);
       dra = dra + cs * (.5f * vec_quat_mul(iia * cross(xa, pt), ra));
       drb = drb + cs * (.5f * vec_quat_mul(iib * cross(xb, -pt), rb));
       cacc_add(acc.la, acc.sa, dpa, wxyz(dra));
@@ -938,7 +994,7 @@ BXS void c2_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
       float dlr = bx_div(cc, w1 + 1e-6f);
       float sink = v_n_old <= -h.vth ? 1.f : 0.f;
       V3 p = (((dlr * n2) * sink) + p_dyn) * stat;
-      cacc_add(acc.la, acc.sa, vdiv(p, ma), xyz0(cross(iia * ra, p)));
+      cacc_add(acc.la, acc.sa, vdivm(p, ma, ima), xyz0(cross(iia * ra, p)));
     } else {
       const float4* bqb = c.tf + h.fo_body + b * BQ_STRIDE;
       const int rb0 = L::BQ * b;
@@ -969,8 +1025,8 @@ BXS void c2_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
       float dlr = bx_div(cc, w1r + w2r + 1e-6f);
       float sink = v_n_old <= 0.f ? 1.f : 0.f;
       V3 p = (((dlr * n2) * sink) + p_dyn) * stat;
-      cacc_add(acc.la, acc.sa, vdiv(p, ma), xyz0(cross(iia * ra, p)));
-      cacc_add(acc.lb, acc.sb, vdiv(-p, mb), xyz0(cross(iib * rb, -p)));
+      cacc_add(acc.la, acc.sa, vdivm(p, ma, ima), xyz0(cross(iia * ra, p)));
+      cacc_add(acc.lb, acc.sb, vdivm(-p, mb, imb), xyz0(cross(iib * rb, -p)));
     }
 }
 BXS void c2_item(const Ctx& c, const BxHeader& h, int item) {
@@ -1034,8 +1090,8 @@ BXS void phase_contacts_fused(const Ctx& c, const BxHeader& h) {
 
 // ======================= legacy_spring (system.py:342-377) =====================
 // Body.impulse bodies.py:46-59
-BXS void body_impulse(float mass, V3 inv_i, V3 bpos, V3 imp, V3 at, V3* dvel, V3* dang) {
-  *dvel = vdiv(imp, mass);
+BXS void body_impulse(float4 bm /* {1/mass, mass} */, V3 inv_i, V3 bpos, V3 imp, V3 at, V3* dvel, V3* dang) {
+  *dvel = vdivm(imp, bm.y, bm.x);
   *dang = inv_i * cross(at - bpos, imp);
 }
 
@@ -1080,8 +1136,8 @@ BXS void phase_joints_spring(const Ctx& c, const BxHeader& h) {
     V3 vc = ldv(c, rc0 + L::VEL) + cross(ang_c, oc);
     V3 imp = (wp - wc) * stiffness + spring_damp * (vp - vc);
     V3 dvp, dap, dvc, dac;
-    body_impulse(bqp[BQ_MASS].y, ii_p, pos_p, -imp, wp, &dvp, &dap);
-    body_impulse(bqc[BQ_MASS].y, ii_c, pos_c, imp, wc, &dvc, &dac);
+    body_impulse(bqp[BQ_MASS], ii_p, pos_p, -imp, wp, &dvp, &dap);
+    body_impulse(bqc[BQ_MASS], ii_c, pos_c, imp, wc, &dvc, &dac);
     V3 axis[3];
     float angle[3], dang[3];
     joint_axis_angle(kind, jq, mp, mc, axis, angle);
@@ -1170,7 +1226,7 @@ BXS void spring_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
                             pb, ldq(c, rb0 + 1), ldv(c, rb0 + L::VEL), ldv(c, rb0 + L::ANG));
     const float4 mat = cq[CQ_MAT];
     V3 iia = f3(bqa[BQ_INV_INERTIA]), iib = f3(bqb[BQ_INV_INERTIA]);
-    const float mass_a = bqa[BQ_MASS].y, mass_b = bqb[BQ_MASS].y;
+    const float4 bma = bqa[BQ_MASS], bmb = bqb[BQ_MASS];  // {1/mass (float32 quotient), mass}
     V3 n = ct.normal;
     V3 ra = ct.pos - pa, rb = ct.pos - pb;
     float baum = h.erp * ct.pen;
@@ -1180,10 +1236,10 @@ BXS void spring_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
     if (two_way) {
       V3 c2 = cross(iib * cross(rb, n), rb);
       ang = dot(n, c1 + c2);
-      denom = bx_div(1.f, mass_a) + bx_div(1.f, mass_b) + ang;
+      denom = bma.x + bmb.x + ang;
     } else {
       ang = dot(n, c1);
-      denom = bx_div(1.f, mass_a) + ang;
+      denom = bma.x + ang;
     }
     float imp = bx_div(-1.f * (1.f + mat.y) * nv + baum, denom);
     V3 vd = ct.vel - nv * n;
@@ -1193,12 +1249,12 @@ BXS void spring_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
     float apn = (ct.pen > 0.f && nv < 0.f && imp > 0.f) ? 1.f : 0.f;
     float apd = apn * (nvd > 0.01f ? 1.f : 0.f);
     V3 dvn, dan, dvd, dad;
-    body_impulse(mass_a, iia, pa, imp * n, ct.pos, &dvn, &dan);
-    body_impulse(mass_a, iia, pa, (-impd) * dir, ct.pos, &dvd, &dad);
+    body_impulse(bma, iia, pa, imp * n, ct.pos, &dvn, &dan);
+    body_impulse(bma, iia, pa, (-impd) * dir, ct.pos, &dvd, &dad);
     cacc_add(acc.la, acc.sa, dvn * apn + dvd * apd, xyz0(dan * apn + dad * apd));
     if (two_way) {
-      body_impulse(mass_b, iib, pb, (-imp) * n, ct.pos, &dvn, &dan);
-      body_impulse(mass_b, iib, pb, impd * dir, ct.pos, &dvd, &dad);
+      body_impulse(bmb, iib, pb, (-imp) * n, ct.pos, &dvn, &dan);
+      body_impulse(bmb, iib, pb, impd * dir, ct.pos, &dvd, &dad);
       cacc_add(acc.lb, acc.sb, dvn * apn + dvd * apd, xyz0(dan * apn + dad * apd));
     }
     stv4(c, h.q_ct + k, ct.pos, ct.pen);
