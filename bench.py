@@ -44,7 +44,12 @@ L2_BYTES = 126 * 1000 * 1000  # B200 L2 (B200_PROFILING.md)
 # dram__bytes_read.sum + dram__bytes_write.sum of one bx_step_kernel launch at the
 # bench workload, from the committed `ncu --set full` capture (profiles/); bytes.
 # (reads only: the 11.3 MB of outputs were still in L2 when the kernel ended)
-NCU_TRAFFIC = {'ant': 4592128}
+NCU_TRAFFIC = {
+    # env: (bytes per launch, capture under profiles/).  Reads + writes seen at DRAM by one launch of the
+    # bench workload under ncu (--set full, cache control on: the outputs of a launch stay in the 126 MB L2
+    # until a later launch evicts them, so the figure is dominated by the cold input reads).
+    'ant': (4592128, 'profiles/r01_ncu_full_ant8192_step_kernel.csv'),
+}
 FP32_LANES = 128
 
 
@@ -184,7 +189,7 @@ def workload_name(args, desc):
 def cpu_baseline(desc, env, b, budget_s=12.0, threads=0):
   """Times the oracle port (float32, OpenMP over envs) on the host cores."""
   from oracle.oracle import Oracle
-  o = Oracle(desc, np.float32)
+  o = Oracle(desc, np.float32, baseline=True)   # -O3 -march=native build of the port (timing only)
   cores = threads or (os.cpu_count() or 1)
   rng = np.random.default_rng(7)
   pos, rot, vel, ang = make_state(desc, b, 7)
@@ -195,10 +200,125 @@ def cpu_baseline(desc, env, b, budget_s=12.0, threads=0):
     out = o.step(out['pos'], out['rot'], out['vel'], out['ang'], act, num_threads=cores)
     n += 1
     el = time.perf_counter() - t0
-    if el > budget_s or n >= 200:
+    if el > budget_s or n >= 5000:
       break
   return {'value': b * n / el, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-          'sample': '%s %d envs x %d steps (%.1f s), C oracle float32 + OpenMP' % (env, b, n, el)}
+          'build_flags': ' '.join(o.build_flags) + ' -fopenmp',
+          'sample': '%s %d envs x %d steps (%.1f s), C port of the reference float32 + OpenMP over envs '
+                    '(scalar per env; the reference\'s own jit+vmap needs jax: unavailable on this box)' % (env, b, n, el)}
+
+
+# The other BASELINE.json configs, measured by the default run beside the headline (configs[1]):
+# (env, envs per GPU, steps) -- configs[2] humanoid 8192, configs[3] grasp 4096, configs[0] ant 128 x 1000.
+SECONDARY = [('humanoid', 8192, None), ('grasp', 4096, None), ('ant', 128, 1000)]
+CHUNK = 128
+
+
+def timed_chunks(torch, n_steps, step_i, sync):
+  """n_steps calls of step_i(i), one CUDA event pair per chunk of <= CHUNK launches queued behind a spin
+  kernel that outlasts the host's enqueue time (device time only, launches chained as in a stepping
+  loop); returns the summed device time in ms."""
+  spin = int((20e-3 + 0.25e-3 * min(n_steps, CHUNK)) * 1.9e9)
+  pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+           for _ in range(0, n_steps, CHUNK)]
+  for ci, c0 in enumerate(range(0, n_steps, CHUNK)):
+    torch.cuda._sleep(spin)
+    pairs[ci][0].record()
+    for i in range(c0, min(n_steps, c0 + CHUNK)):
+      step_i(i)
+    pairs[ci][1].record()
+  sync()
+  return float(sum(x.elapsed_time(y) for x, y in pairs))
+
+
+def measure_config(torch, name, b, steps, warmup, local, rank, sync):
+  """One more config with the headline's method: `System.step` (value), the full `Env.step` in one
+  launch (env_step) and 10 steps per launch (rollout).  Returns per-rank milliseconds; the caller
+  reduces them (max over ranks) and turns them into whole-job env-steps/s."""
+  from brax_b200 import envs as bx_envs
+  from brax_b200.desc import SystemDesc
+  from brax_b200.envs import State
+  from brax_b200.system import QP, System
+  desc = SystemDesc.load(os.path.join(ROOT, 'brax_b200', 'systems', name + '.json'))
+  dev = torch.device('cuda', local)
+  s = System(desc, device=local)
+  bytes_set = b * desc.bytes_per_env_step()
+  nsets = min(64, max(2, -(-2 * L2_BYTES // bytes_set)))
+  base = QP(*[torch.from_numpy(x).to(dev) for x in make_state(desc, b, 300 + rank)])
+  qps = [QP(base.pos.clone(), base.rot.clone(), base.vel.clone(), base.ang.clone()) for _ in range(nsets)]
+  gen = torch.Generator(device=dev)
+  gen.manual_seed(20_000 + rank)
+  n_act = min(steps + warmup, 256)
+  acts = torch.rand((n_act, b, desc.act_size), generator=gen, device=dev) * 2 - 1
+  for i in range(max(warmup, nsets)):
+    qps[i % nsets], _ = s.step(qps[i % nsets], acts[i % n_act])
+  sync()
+
+  def step_i(i):
+    j = i % nsets
+    qps[j], _ = s.step(qps[j], acts[(warmup + i) % n_act])
+  ms = timed_chunks(torch, steps, step_i, sync)
+  # T = 10 steps per launch
+  roll_t = 10
+  n_roll = max(1, min(steps, 100) // roll_t)
+  qps[0], _ = s.rollout(qps[0], acts[:roll_t])
+  er = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_roll)]
+  torch.cuda._sleep(int(25e-3 * 1.9e9))
+  for i in range(n_roll):
+    j = i % nsets
+    er[i][0].record()
+    qps[j], _ = s.rollout(qps[j], acts[:roll_t])
+    er[i][1].record()
+  sync()
+  each = sorted(x.elapsed_time(y) for x, y in er)
+  ms_roll = float(each[len(each) // 2]) * n_roll
+  # full Env.step in one launch
+  env = bx_envs.create(name, device=local, **(dict(use_contact_forces=True) if name == 'ant' else {}))
+  if name in ('fetch', 'grasp'):
+    far = torch.tensor([8.0, 3.0, 1.0], device=dev)
+    for q in qps:
+      q.pos[:, env.env.target_body] = q.pos[:, env.env.object_body if name == 'grasp' else env.env.ref_body] + far
+  sts = [State(q, None, None, None) for q in qps]
+  for j in range(nsets):
+    sts[j] = env.step(sts[j], acts[j % n_act])
+  sync()
+
+  def env_i(i):
+    j = i % nsets
+    sts[j] = env.step(sts[j], acts[(warmup + i) % n_act])
+  ms_env = timed_chunks(torch, steps, env_i, sync)
+  finite = bool(torch.isfinite(sts[0].qp.pos).all().item())
+  info = {'env': name, 'envs_per_gpu': b, 'steps': steps, 'substeps': desc.substeps, 'dynamics': desc.dynamics_mode,
+          'threads_per_tile': s_threads(s), 'env_batches': nsets, 'obs_size': env.observation_size,
+          'working_set_mb': nsets * bytes_set / 1e6, 'rollout_launches': n_roll, 'finite': finite,
+          'l2': ('inputs larger than L2 (%d env batches in rotation)' % nsets) if nsets * bytes_set > L2_BYTES
+                else 'working set %.1f MB < L2 (a batch this small cannot exceed L2 within 64 batches)' % (nsets * bytes_set / 1e6)}
+  return [ms, ms_roll, ms_env], info, desc
+
+
+def config_entry(info, desc, world, ms, ms_roll, ms_env, hbm_gbs, sm_max_mhz):
+  b, steps = info['envs_per_gpu'], info['steps']
+  value = world * b * steps / (ms * 1e-3)
+  per_gpu = value / world
+  flops = load_flops(info['env'])
+  peak = SM_COUNT * FP32_LANES * 2 * sm_max_mhz * 1e6 / 1e12
+  out = dict(info)
+  out.update({
+      'workload': '%s %d envs/GPU, default substeps (%d), dynamics %s' % (info['env'], b, desc.substeps, desc.dynamics_mode),
+      'value': value, 'unit': UNIT, 'ms_per_step': ms / steps,
+      'roofline': {'bound': 'hbm', 'achieved': per_gpu * desc.bytes_per_env_step() / 1e9, 'peak': hbm_gbs, 'unit': 'GB/s',
+                   'frac': per_gpu * desc.bytes_per_env_step() / 1e9 / hbm_gbs,
+                   'bytes_per_env_step': desc.bytes_per_env_step(),
+                   'traffic': NCU_TRAFFIC.get(info['env'], (None, None))[0] if b == 8192 or info['env'] == 'grasp' else None,
+                   'traffic_source': NCU_TRAFFIC.get(info['env'], (None, 'no ncu --set full capture committed'))[1]},
+      'roofline_fp32': ({'bound': 'fp32', 'achieved': per_gpu * flops['flops'] / 1e12, 'peak': peak, 'unit': 'TFLOP/s',
+                         'frac': per_gpu * flops['flops'] / 1e12 / peak, 'flops_per_env_step': flops['flops']} if flops else None),
+      'env_step': {'value': world * b * steps / (ms_env * 1e-3), 'unit': UNIT, 'ms_per_step': ms_env / steps},
+      'rollout': {'steps_per_launch': 10, 'value': world * b * 10 * info['rollout_launches'] / (ms_roll * 1e-3), 'unit': UNIT,
+                  'ms_per_step': ms_roll / (10 * info['rollout_launches']), 'timing': 'median launch'},
+  })
+  return out
+
 
 
 def run_reference(args, desc):
@@ -209,7 +329,7 @@ def run_reference(args, desc):
   if rank != 0:
     return
   from oracle.oracle import Oracle
-  o = Oracle(desc, np.float32)
+  o = Oracle(desc, np.float32, baseline=True)   # -O3 -march=native build of the port (timing only)
   cores = os.cpu_count() or 1
   b = args.envs  # per-step bounded sample: one GPU's shard of the workload
   rng = np.random.default_rng(7)
@@ -230,7 +350,8 @@ def run_reference(args, desc):
       'ms_per_step': 1e3 * el / args.steps, 'higher_is_better': True,
       'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
       'config': {'workload': workload_name(args, desc)},
-      'cpu_baseline': {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+      'cpu_baseline': {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample,
+                       'build_flags': ' '.join(o.build_flags) + ' -fopenmp'},
       'e2e': {'value': v, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
   }))
 
@@ -385,6 +506,7 @@ def run_gpu(args, desc):
   # "next" row N1: the whole Env.step (sys.step + obs / reward / done / metrics of
   # envs/ant.py:222-281, envs/humanoid.py:246-340) as ONE launch; same timing method.
   ms_env, ms_wenv, ms_reset, env_obs = 0.0, 0.0, 0.0, 0
+  last_reward = None
   env_name = args.env[:-len('_spring')] if args.env.endswith('_spring') else args.env
   if env_name in ('ant', 'humanoid', 'fetch', 'grasp') and args.env != 'grasp_spring':
     from brax_b200 import envs as bx_envs
@@ -407,6 +529,7 @@ def run_gpu(args, desc):
       j = i % nsets
       sts[j] = env.step(sts[j], acts[args.warmup + i])
     ms_env = timed_chunks(env_step)
+    last_reward = sts[0].reward
     # ... and with EpisodeWrapper(1000) + AutoResetWrapper applied inside the same launch
     # (wrappers.py:105-148); step counters spread over the episode as in steady-state training,
     # so ~0.1 % of the envs end their episode and reload their first state every step
@@ -467,10 +590,25 @@ def run_gpu(args, desc):
   e2e_finite = bool(np.isfinite(hqp.pos).all())
   h2d, d2h = s.host_transfer_bytes(b)
 
-  # ---- max over ranks -----------------------------------------------------------
+  # ---- the other BASELINE configs (humanoid 8192, grasp 4096, ant 128 x 1000), each rank its shard ----
+  sec = []
+  if not args.no_configs and args.env == 'ant' and args.envs == 8192:
+    for name, sb, ssteps in SECONDARY:
+      sec.append(measure_config(torch, name, sb, ssteps or args.steps, args.warmup, local, rank, barrier))
+  # ---- per-rank statistics of the final state: summed over ranks below ----
+  mass = torch.tensor([x['mass'] for x in desc.bodies], dtype=torch.float32, device=dev)
+  q_fin = qps[0]
+  energy = float((0.5 * mass[None, :, None] * q_fin.vel.double() ** 2).sum().item())
+  nonfinite = int(sum((~torch.isfinite(getattr(q_fin, k))).sum().item() for k in ('pos', 'rot', 'vel', 'ang')))
+  reward_sum = float(last_reward.double().sum().item()) if last_reward is not None else 0.0
+
+  # ---- max over ranks (timings), sum over ranks (statistics) --------------------------
   from brax_b200 import shard
   ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll, ms_av, ms_env, ms_chunk = shard.reduce_stats(
       [ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll, ms_av, ms_env, ms_chunk], ['max'] * 9, device=dev)
+  sec_ms = shard.reduce_stats([x for m, _, _ in sec for x in m], ['max'] * (3 * len(sec)), device=dev)
+  reward_sum, energy, nonfinite, sec_bad = shard.reduce_stats(
+      [reward_sum, energy, nonfinite, sum(0 if i['finite'] else 1 for _, i, _ in sec)], ['sum'] * 4, device=dev)
   value = world * b * args.steps / (ms_chunk * 1e-3)
   value_per_step_events = world * b * args.steps / (ms_total * 1e-3)
   value_b2b = world * b * args.steps / (ms_b2b * 1e-3)
@@ -500,8 +638,11 @@ def run_gpu(args, desc):
                   'event records between the launches)' % (nsets, nsets * bytes_set / 1e6, nsets),
             'env_batches': nsets,
             'threads_per_tile': s_threads(s), 'bodies': n, 'contacts': k, 'act': a},
-        'value_l2_flushed': value_flushed,
-        'value_l2_flushed_median_step': value_flushed_median,
+        # one env batch, whole L2 (kernel code and tables included) evicted before every step: the MEDIAN
+        # step is the figure; the mean beside it carries the run's rare multi-100-us hiccups of single
+        # launches right after a 256 MiB fill (max in ms_l2_flushed_min_median_max)
+        'value_l2_flushed': value_flushed_median,
+        'value_l2_flushed_mean_step': value_flushed,
         'ms_per_step_l2_flushed': ms_flushed / args.steps,
         'ms_l2_flushed_min_median_max': [ms_fl_steps[0], ms_fl_steps[len(ms_fl_steps) // 2], ms_fl_steps[-1]],
         'value_back_to_back': value_b2b,
@@ -528,14 +669,18 @@ def run_gpu(args, desc):
                         'one launch working on the mapped host memory (tiles pull inputs / push outputs '
                         'over PCIe); pageable callers get the chunked 3-stream copy pipeline'},
         'gpu_launches': int(launches),
-        'clocks': clocks, 'finite': finite,
+        'clocks': clocks, 'finite': finite and nonfinite == 0 and sec_bad == 0,
+        'stats_all_ranks': {'sum_reward_last_env_step': reward_sum, 'sum_kinetic_energy_final_state': energy,
+                            'n_nonfinite': int(nonfinite),
+                            'what': 'summed over the %d ranks in the final reduce (nccl); finite covers every rank and config' % world},
     }
     # dominant (only) kernel: bx_step_kernel, one launch per step; its average
     # duration IS ms_per_step (CUDA events bracket each launch on its stream).
     hbm_ach = per_gpu * bytes_env / 1e9
     out['roofline'] = {
         'bound': 'hbm', 'achieved': hbm_ach, 'peak': hbm_gbs, 'unit': 'GB/s',
-        'frac': hbm_ach / hbm_gbs, 'traffic': NCU_TRAFFIC.get(args.env),
+        'frac': hbm_ach / hbm_gbs, 'traffic': NCU_TRAFFIC.get(args.env, (None, None))[0],
+        'traffic_source': NCU_TRAFFIC.get(args.env, (None, 'no ncu --set full capture of this env committed'))[1],
         'peak_source': src, 'bytes_per_env_step': bytes_env,
         'bytes_per_launch': bytes_env * b,
         'note': 'schema roofline (HBM). The kernel is NOT HBM-bound: it is FP32-pipe / '
@@ -550,6 +695,16 @@ def run_gpu(args, desc):
           'peak_at_observed_clock': SM_COUNT * FP32_LANES * 2 * mhz * 1e6 / 1e12,
           'note': 'flops = exact add+mul+div+sqrt+trig count of the oracle (oracle/flops.json); '
                   'peak = 148 SM x 128 lanes x 2 (FMA) x sm_max_mhz; tensor cores do not apply'}
+    # every BASELINE.json config under one key: the headline first, then the secondary ones
+    head = {'env': args.env, 'envs_per_gpu': b, 'steps': args.steps, 'workload': workload_name(args, desc),
+            'value': value, 'unit': UNIT, 'ms_per_step': ms_chunk / args.steps,
+            'roofline': {k: out['roofline'][k] for k in ('bound', 'achieved', 'peak', 'unit', 'frac', 'traffic', 'traffic_source')},
+            'roofline_fp32': ({k: out['roofline_fp32'][k] for k in ('bound', 'achieved', 'peak', 'unit', 'frac')} if flops else None),
+            'env_step': ({'value': out['env_step']['value'], 'unit': UNIT, 'ms_per_step': out['env_step']['ms_per_step']}
+                         if out['env_step'] else None),
+            'rollout': {k: out['rollout'][k] for k in ('steps_per_launch', 'value', 'unit', 'ms_per_step', 'timing')}}
+    out['configs'] = [head] + [config_entry(info, d2, world, sec_ms[3 * i], sec_ms[3 * i + 1], sec_ms[3 * i + 2],
+                                            hbm_gbs, sm_max_mhz) for i, (_, info, d2) in enumerate(sec)]
     if world == 1 and not args.no_cpu:
       out['cpu_baseline'] = cpu_baseline(desc, args.env, min(b, 8192), budget_s=args.cpu_seconds)
     print(json.dumps(out))
@@ -576,6 +731,7 @@ def main():
   ap.add_argument('--cpu-seconds', type=float, default=12.0)
   ap.add_argument('--no-cpu', action='store_true')
   ap.add_argument('--no-e2e', action='store_true')
+  ap.add_argument('--no-configs', action='store_true', help='skip the secondary BASELINE configs')
   args = ap.parse_args()
   from brax_b200.desc import SystemDesc
   desc = SystemDesc.load(os.path.join(ROOT, 'brax_b200', 'systems', args.env + '.json'))

@@ -43,6 +43,29 @@ def build(force: bool = False):
   return out
 
 
+BASELINE_FLAGS = ['-O3', '-march=native', '-ffp-contract=fast', '-fno-math-errno', '-fno-trapping-math']
+
+
+def build_baseline():
+  """The TIMED CPU baseline build of the same port (bench.py only): `-O3 -march=native`, multiply-add
+  contraction allowed -- what a performance build of this C code is.  (The checker build above stays
+  `-O2 -ffp-contract=off`: plain IEEE single arithmetic in the reference's operation order.)
+  -march=native binds it to the CPU it was compiled on, so it is compiled on the machine that runs
+  it, keyed by the CPU's flag set.  Returns (path, flags)."""
+  import hashlib
+  try:
+    flags_line = next(l for l in open('/proc/cpuinfo') if l.startswith('flags'))
+  except Exception:
+    flags_line = 'unknown'
+  key = hashlib.sha1(flags_line.encode()).hexdigest()[:10]
+  lib = os.path.join(HERE, 'liboracle_f32_native_%s.so' % key)
+  if not os.path.exists(lib) or os.path.getmtime(lib) < os.path.getmtime(SRC):
+    cmd = ['gcc'] + BASELINE_FLAGS + ['-fPIC', '-shared', '-fopenmp', '-Wall', '-Wno-unused-function',
+                                      SRC, '-o', lib, '-lm']
+    subprocess.check_call(cmd)
+  return lib, BASELINE_FLAGS
+
+
 def _structs(R):
   class Body(C.Structure):
     _fields_ = [('mass', R), ('inv_inertia', R * 3), ('pos_mask', R * 3),
@@ -96,11 +119,17 @@ def _structs(R):
 class Oracle:
   """CPU restatement of `System.step` for one `SystemDesc`."""
 
-  def __init__(self, desc, dtype=np.float32, safe_norm_jax=None):
+  def __init__(self, desc, dtype=np.float32, safe_norm_jax=None, baseline=False):
+    """baseline=True (float32 only): the -O3 -march=native build, for TIMING the port (bench.py)."""
     f32lib, f64lib = build()
     self.dtype = np.dtype(dtype)
     is32 = self.dtype == np.float32
     R = C.c_float if is32 else C.c_double
+    self.build_flags = ['-O2', '-ffp-contract=off']
+    if baseline:
+      if not is32:
+        raise ValueError('the baseline build is float32')
+      f32lib, self.build_flags = build_baseline()
     self._lib = C.CDLL(f32lib if is32 else f64lib)
     sfx = '_f32' if is32 else '_f64'
     self._step = getattr(self._lib, 'bxo_step' + sfx)
