@@ -475,6 +475,21 @@ def run_gpu(args, desc):
     q2, _ = s.step(q2, acts[args.warmup + i])
   e1.record()
   torch.cuda.synchronize()
+  # the same loop without per-step host work: System.make_stepper (8 in-place steps per CUDA graph replay)
+  st8 = s.make_stepper(b, steps_per_replay=8, graph=True)
+  for name in ('pos', 'rot', 'vel', 'ang'):
+    getattr(st8.qp, name).copy_(getattr(qp, name))
+  st8.acts.copy_(acts[:8])
+  st8.replay()
+  n_rep = max(1, args.steps // 8)
+  g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  torch.cuda.synchronize()
+  g0.record()
+  for i in range(n_rep):
+    st8.replay()
+  g1.record()
+  torch.cuda.synchronize()
+  ms_graph = g0.elapsed_time(g1) / (8 * n_rep)
   # "next" row N2: T steps per launch (bx_rollout, actions [T,B,A]); the
   # state stays in shared memory between the steps of a launch.  Reported beside value.
   roll_t = min(10, args.steps)
@@ -645,7 +660,12 @@ def run_gpu(args, desc):
         'value_l2_flushed_mean_step': value_flushed,
         'ms_per_step_l2_flushed': ms_flushed / args.steps,
         'ms_l2_flushed_min_median_max': [ms_fl_steps[0], ms_fl_steps[len(ms_fl_steps) // 2], ms_fl_steps[-1]],
+        # a plain Python loop `qp, info = sys.step(qp, act)` with NO spin kernel in front: host enqueue
+        # rate included (event pair around the whole loop) ...
         'value_back_to_back': value_b2b,
+        # ... and System.make_stepper: 8 in-place steps per CUDA-graph replay, same event method, ONE env batch
+        # stepped in place (its state stays in L2, unlike `value`'s rotation over cold batches)
+        'value_stepper_graph': world * b / (ms_graph * 1e-3),
         'with_angle_vel_epilogue': {'value': world * b * args.steps / (ms_av * 1e-3), 'unit': UNIT,
                                     'ms_per_step': ms_av / args.steps,
                                     'extra_bytes_per_env_step': 24 * len(desc.joints)},

@@ -52,6 +52,61 @@ class Info:
   contact_penetration: Any
 
 
+class _LazyInfo(Info):
+  """`Info` of a torch-path step whose tensors (views of the step's one output block) are built
+  on first access: a stepping loop that never looks at the Info pays nothing for it."""
+
+  def __init__(self, views):
+    object.__setattr__(self, '_views', views)   # name -> zero-argument callable returning the view
+
+  def __getattr__(self, name):                  # only reached for fields not built yet
+    v = object.__getattribute__(self, '_views')
+    if name in ('contact', 'joint', 'actuator'):
+      val = P(v[name + '_vel'](), v[name + '_ang']())
+    elif name in ('contact_pos', 'contact_normal', 'contact_penetration'):
+      val = v[name]()
+    else:
+      raise AttributeError(name)
+    object.__setattr__(self, name, val)
+    return val
+
+  def __repr__(self):
+    return 'Info(<views of the step output block>)'
+
+
+_PTR_FIELDS = [n for n, t in CStepIO._fields_ if t is C.c_void_p]
+_PTR_INDEX = {n: i for i, n in enumerate(_PTR_FIELDS)}
+
+
+class _Plan:
+  """Per (batch, outputs) call plan of the torch path: its own CStepIO, viewed as an array of
+  pointer words so that a call writes all output pointers with one vectorised store."""
+
+  def __init__(self, specs):
+    self.names, self.shapes, self.offs, self.counts = [], [], [], []
+    off = 0
+    for name, shape in specs:
+      cnt = 1
+      for d in shape:
+        cnt *= int(d)
+      self.names.append(name)
+      self.shapes.append(tuple(shape))
+      self.offs.append(off)
+      self.counts.append(cnt)
+      off += -(-cnt // 4) * 4          # every slice starts on a 16-byte boundary (vector stores)
+    self.total = max(off, 4)
+    self.io = CStepIO()                 # zero-initialised: every optional pointer NULL
+    self.words = np.ctypeslib.as_array((C.c_uint64 * len(_PTR_FIELDS)).from_address(C.addressof(self.io)))
+    live = [i for i, c in enumerate(self.counts) if c]
+    self.out_idx = np.asarray([_PTR_INDEX[self.names[i]] for i in live], dtype=np.int64)
+    self.out_off = np.asarray([4 * self.offs[i] for i in live], dtype=np.uint64)
+    self.index = {n: i for i, n in enumerate(self.names)}
+
+  def view(self, flat, name):
+    i = self.index[name]
+    return flat[self.offs[i]:self.offs[i] + self.counts[i]].view(self.shapes[i])
+
+
 _OUT = (('pos_o', 3, 'n'), ('rot_o', 4, 'n'), ('vel_o', 3, 'n'),
         ('ang_o', 3, 'n'), ('contact_vel', 3, 'n'), ('contact_ang', 3, 'n'),
         ('joint_vel', 3, 'n'), ('joint_ang', 3, 'n'), ('actuator_vel', 3, 'n'),
@@ -293,6 +348,12 @@ class System:
       outs = [o[0] for o in outs]
     return QP(*outs)
 
+  def make_stepper(self, batch: int, steps_per_replay: int = 8, graph: bool = True, info: bool = False) -> 'Stepper':
+    """A stepping loop without per-step host work: `steps_per_replay` chained `System.step`s on
+    static device buffers, captured once into a CUDA graph and replayed (one graph launch per k
+    steps).  The reference shape: `jax.jit(step)` is one dispatch per call (envs/wrappers.py:243)."""
+    return Stepper(self, batch, steps_per_replay, graph, info)
+
   # ---- the step ---------------------------------------------------------------
   def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False, env: bool = False,
            env_rand=None, auto_reset: 'AutoReset' = None, info: bool = True):
@@ -406,21 +467,6 @@ class System:
       res += (env_out,)
     return res
 
-  def _out_plan(self, b, av, env=False, steps=1, info=True):
-    """Per batch size: the outputs as slices of ONE allocation (each slice
-    starts on a 16-byte boundary so the kernel's vector stores apply)."""
-    key = (b, av, env, steps, info)
-    plan = self._plans.get(key)
-    if plan is None:
-      names, shapes, offs, off = [], [], [], 0
-      for name, shape in self._specs(b, av, env, steps, info):
-        names.append(name)
-        shapes.append(shape)
-        offs.append(off)
-        off += -(-int(np.prod(shape)) // 4) * 4
-      plan = self._plans[key] = (names, shapes, offs, max(off, 4))
-    return plan
-
   def _clear_optional(self, io):
     for name, _, _ in _OUT[4:]:
       setattr(io, name, None)
@@ -435,7 +481,12 @@ class System:
 
   def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False, env_rand=None,
                   auto_reset=None, info: bool = True, observe: bool = False):
-    """env_rand: (fetch / grasp) uniforms of the target teleport, [B,3] or [T,B,3]."""
+    """env_rand: (fetch / grasp) uniforms of the target teleport, [B,3] or [T,B,3].
+
+    Host cost per call is what bounds a plain Python stepping loop (the kernel takes ~57 us for
+    8192 ants), so the call keeps to: five input checks, ONE output allocation, one vectorised store
+    of the output pointers into the plan's CStepIO, the C call, four views for the QP; the Info views
+    are built lazily (`_LazyInfo`)."""
     import torch
     batched, b = self._shapes(qp.pos.shape)
     n, a = self.num_bodies, self.act_size
@@ -458,23 +509,23 @@ class System:
 
     ins = (prep(qp.pos, b * n * 3), prep(qp.rot, b * n * 4), prep(qp.vel, b * n * 3),
            prep(qp.ang, b * n * 3), prep(act, steps * b * a))
-    names, shapes, offs, total = self._out_plan(b, av, env, steps, info)
-    flat = torch.empty(total, dtype=f32, device=dev)
-    base = flat.data_ptr()
-    io = self._io
-    io.pos, io.rot, io.vel, io.ang, io.act = [t.data_ptr() for t in ins]
-    self._clear_optional(io)
-    out = {}
-    for name, shape, off in zip(names, shapes, offs):
-      cnt = 1
-      for d in shape:
-        cnt *= d
-      out[name] = flat[off:off + cnt].view(shape)
-      setattr(io, name, base + 4 * off if cnt else None)
+    key = (b, av, env, steps, info)
+    plan = self._plans.get(key)
+    if plan is None:
+      plan = self._plans[key] = _Plan(self._specs(b, av, env, steps, info))
+    flat = torch.empty(plan.total, dtype=f32, device=dev)
+    w = plan.words
+    w[:5] = [t.data_ptr() for t in ins]
+    w[plan.out_idx] = plan.out_off + np.uint64(flat.data_ptr())
+    io = plan.io
+    keep = None
     if env_rand is not None:
       rep = int(auto_reset.action_repeat or 1) if auto_reset is not None else 1
       env_rand = prep(env_rand, steps * rep * b * 3)
       io.env_rand = env_rand.data_ptr()
+    else:
+      io.env_rand = None
+    extra = None
     if auto_reset is not None:
       ar = auto_reset
       keep = (prep(ar.first_qp.pos, b * n * 3), prep(ar.first_qp.rot, b * n * 4), prep(ar.first_qp.vel, b * n * 3),
@@ -483,12 +534,15 @@ class System:
       io.first_pos, io.first_rot, io.first_vel, io.first_ang, io.first_obs, io.done_in = [t.data_ptr() for t in keep[:6]]
       io.steps_in = None if keep[6] is None else keep[6].data_ptr()
       extra = torch.empty((steps + 1) * b, dtype=f32, device=dev)
-      out['steps'] = extra[:b].view((b,))
-      out['truncation'] = extra[b:].view((steps, b) if steps > 1 else (b,))
       io.steps_out = extra.data_ptr()
       io.truncation = extra.data_ptr() + 4 * b
       io.episode_length = float(ar.episode_length or 0)
       io.action_repeat = int(ar.action_repeat or 1)
+    elif io.first_pos:
+      io.first_pos = io.first_rot = io.first_vel = io.first_ang = io.first_obs = None
+      io.done_in = io.steps_in = io.steps_out = io.truncation = None
+      io.episode_length = 0.0
+      io.action_repeat = 0
     io.observe = int(observe)
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     if self.autotune and not observe and steps == 1 and b >= 1024 and b not in self._tuned:
@@ -502,7 +556,25 @@ class System:
       rc = self._lib.bx_step(self._h, b, C.byref(io), stream)
     if rc != 0:
       raise RuntimeError('bx_step: ' + _lib.last_error())
-    return self._wrap(out, batched, steps)
+    if not batched:
+      # unbatched call ([N,..] in, [N,..] out): the general wrapper
+      out = {name: plan.view(flat, name) for name in plan.names}
+      if extra is not None:
+        out['steps'] = extra[:b].view((b,))
+        out['truncation'] = extra[b:].view((steps, b) if steps > 1 else (b,))
+      return self._wrap(out, batched, steps)
+    view = plan.view
+    res = (QP(view(flat, 'pos_o'), view(flat, 'rot_o'), view(flat, 'vel_o'), view(flat, 'ang_o')),
+           _LazyInfo({nm: (lambda nm=nm: view(flat, nm)) for nm in plan.names[4:13]}) if info else None)
+    if av:
+      res += (JointState(view(flat, 'joint_angle'), view(flat, 'joint_velocity')),)
+    if env:
+      eo = {k: view(flat, k) for k in ('obs', 'reward', 'done', 'metrics')}
+      if extra is not None:
+        eo['steps'] = extra[:b].view((b,))
+        eo['truncation'] = extra[b:].view((steps, b) if steps > 1 else (b,))
+      res += (eo,)
+    return res
 
   def _step_numpy(self, qp: QP, act, bufs: 'HostBuffers' = None, av: bool = False, env: bool = False,
                   env_rand=None):
@@ -541,6 +613,83 @@ class System:
     if rc != 0:
       raise RuntimeError('bx_step_host: ' + _lib.last_error())
     return self._wrap(out, batched)
+
+
+class Stepper:
+  """k chained steps on static buffers, replayed as one CUDA graph (`System.make_stepper`).
+
+      st = sys.make_stepper(batch, steps_per_replay=8)
+      st.qp.pos.copy_(pos) ...                 # the state lives in st.qp (static tensors)
+      st.acts.copy_(actions)                   # [k, B, A]: step i of a replay reads acts[i]
+      st.replay()                              # k steps, in place: st.qp now holds the state k steps on
+      st.info                                  # (info=True) the Info of the last step, static tensors
+
+  The launches step IN PLACE (outputs = inputs): a tile reads the whole state of its 32 environments
+  into shared memory before it writes anything, and tiles own disjoint environments, so `bx_step`
+  allows pos_o == pos; consecutive launches chain through programmatic dependent launch.
+  graph=False issues the same k launches directly (for A/B and debugging)."""
+
+  def __init__(self, system: 'System', batch: int, k: int, graph: bool, info: bool):
+    import torch
+    if k < 1:
+      raise ValueError('steps_per_replay must be >= 1')
+    self.sys, self.batch, self.k = system, int(batch), int(k)
+    dev = torch.device('cuda', system.device)
+    n, a, kk = system.num_bodies, system.act_size, system.num_contacts
+    f32 = torch.float32
+    q0 = system.default_qp(batch=batch)
+    self.qp = QP(*[torch.from_numpy(np.ascontiguousarray(x)).to(dev) for x in (q0.pos, q0.rot, q0.vel, q0.ang)])
+    self.acts = torch.zeros((k, batch, a), dtype=f32, device=dev)
+    self.info = None
+    self._ios = []
+    out = {}
+    if info:
+      dims = {'n': n, 'k': kk}
+      for name, w, dim in _OUT[4:]:
+        out[name] = torch.zeros((batch, dims[dim], w) if w else (batch, dims[dim]), dtype=f32, device=dev)
+      self.info = Info(P(out['contact_vel'], out['contact_ang']), P(out['joint_vel'], out['joint_ang']),
+                       P(out['actuator_vel'], out['actuator_ang']), out['contact_pos'], out['contact_normal'],
+                       out['contact_penetration'])
+    for i in range(k):
+      io = CStepIO()
+      io.pos, io.rot, io.vel, io.ang = [t.data_ptr() for t in (self.qp.pos, self.qp.rot, self.qp.vel, self.qp.ang)]
+      io.pos_o, io.rot_o, io.vel_o, io.ang_o = io.pos, io.rot, io.vel, io.ang      # in place
+      io.act = self.acts[i].data_ptr()
+      if info and i == k - 1:
+        for name, t in out.items():
+          setattr(io, name, t.data_ptr() if t.numel() else None)
+      self._ios.append(io)
+    self._graph = None
+    if graph:
+      side = torch.cuda.Stream(device=dev)
+      side.wait_stream(torch.cuda.current_stream(dev))
+      with torch.cuda.stream(side):          # warm-up on the capture stream (module load, attributes)
+        keep = [t.clone() for t in (self.qp.pos, self.qp.rot, self.qp.vel, self.qp.ang)]
+        self._launch_all()
+        for t, kp in zip((self.qp.pos, self.qp.rot, self.qp.vel, self.qp.ang), keep):
+          t.copy_(kp)
+      torch.cuda.current_stream(dev).wait_stream(side)
+      g = torch.cuda.CUDAGraph()
+      with torch.cuda.graph(g):
+        self._launch_all()
+      self._graph = g
+      # the capture does not execute: the state is still the default pose
+
+  def _launch_all(self):
+    import torch
+    lib, h, b = self.sys._lib, self.sys._h, self.batch
+    stream = C.c_void_p(torch.cuda.current_stream(torch.device('cuda', self.sys.device)).cuda_stream)
+    for io in self._ios:
+      if lib.bx_step(h, b, C.byref(io), stream) != 0:
+        raise RuntimeError('bx_step: ' + _lib.last_error())
+
+  def replay(self):
+    """Advances st.qp by k steps with st.acts (on torch's current stream)."""
+    if self._graph is not None:
+      self._graph.replay()
+    else:
+      self._launch_all()
+    return self.qp
 
 
 def load_system(name: str, device: int = 0, env=None) -> System:

@@ -333,6 +333,9 @@ int bx_default_qp(const bx_system* sys, int64_t num_envs, const float* joint_ang
  * `stream` (a cudaStream_t passed as void*; NULL = default stream).  No host
  * sync, no allocation: CUDA-graph capturable.  Replaces
  * jit(vmap(System.step)) (system.py:244, envs/wrappers.py:70,80). */
+/* In-place stepping is allowed: pos_o / rot_o / vel_o / ang_o may alias pos / rot / vel / ang (a tile reads
+ * the whole state of its 32 environments into shared memory before it writes anything; tiles own
+ * disjoint environments). */
 int bx_step(const bx_system* sys, int64_t num_envs, const bx_step_io* io,
             void* stream);
 

@@ -560,6 +560,33 @@ def test_cuda_graph_capture():
     np.testing.assert_array_equal(a[k], c[k], err_msg=k)
 
 
+def test_stepper_graph_replay_equals_eager_steps():
+  """System.make_stepper: k chained IN-PLACE steps replayed as one CUDA graph == the same steps
+  issued one by one through System.step (bitwise), over several replays; graph=False likewise."""
+  torch = _torch()
+  s = _system('ant')
+  b, k, reps = 777, 4, 3     # ragged last tile
+  qp, rng = _harvest(s, b, 3, 29)
+  acts = torch.from_numpy(rng.uniform(-1, 1, (reps, k, b, s.act_size)).astype(np.float32)).cuda()
+  q1 = qp
+  for r in range(reps):
+    for t in range(k):
+      q1, i1 = s.step(q1, acts[r, t])
+  torch.cuda.synchronize()
+  want = _flat(q1, i1)
+  for graph in (True, False):
+    st = s.make_stepper(b, steps_per_replay=k, graph=graph, info=True)
+    for name in util.QP_KEYS:
+      getattr(st.qp, name).copy_(getattr(qp, name))
+    for r in range(reps):
+      st.acts.copy_(acts[r])
+      st.replay()
+    torch.cuda.synchronize()
+    got = _flat(st.qp, st.info)
+    for key in want:
+      np.testing.assert_array_equal(got[key], want[key], err_msg='%s graph=%s' % (key, graph))
+
+
 def test_three_tiles_per_sm_build_parity():
   """Batches of more than four tiles per SM run the (320, 3) build of small systems (64
   registers, three tiles per SM): same parity policy on a 1024-env slice of a 24576-env step,
