@@ -582,28 +582,93 @@ def run_gpu(args, desc):
   ms_b2b = e0.elapsed_time(e1)
   finite = bool(torch.isfinite(qp.pos).all().item())
 
-  # ---- e2e: host buffers through System.step (bx_step_host) ----------------
-  # Inputs start in page-locked host memory, every step uploads QP + act, steps,
-  # and downloads QP + Info into page-locked host memory (two HostBuffers sets
-  # ping-pong so a step's outputs are the next step's inputs, like a host-side
-  # rollout loop of the reference's numpy path).
-  hb = [s.host_buffers(b), s.host_buffers(b)]
-  for dst, src in zip((hb[0].out['pos_o'], hb[0].out['rot_o'], hb[0].out['vel_o'], hb[0].out['ang_o']),
-                      (pos, rot, vel, ang)):
-    dst[...] = src
-  hact = acts[args.warmup:].cpu().pin_memory().numpy()
-  hqp = QP(hb[0].out['pos_o'], hb[0].out['rot_o'], hb[0].out['vel_o'], hb[0].out['ang_o'])
+  # ---- e2e: host buffers through System.step (bx_step_host / bx_step_host_async) ---------------
+  # Inputs start in page-locked host memory; every step uploads QP + act, steps, and downloads QP + Info
+  # into page-locked host memory (HostBuffers ping-pong so a step's outputs are the next step's inputs,
+  # like a host-side rollout loop of the reference's numpy path).
+  #   single chain: the whole batch as ONE dependent chain of synchronous calls (round 1's figure): each
+  #     step waits for the previous step's last byte, so the link idles while tiles start and drain;
+  #   two groups (the e2e figure): the batch as two independent halves, each its own chain, stepped
+  #     through System.step_async on two slots -- one half's results travel down while the other half's
+  #     inputs travel up and compute.  Same envs, same bytes per step, same public API.
   e2e_steps = 1 if args.no_e2e else max(3, min(args.steps, 50))
+  hact = acts[args.warmup:].cpu().pin_memory().numpy()
+  h2d, d2h = s.host_transfer_bytes(b)
+
+  def host_chain(lo, hi):
+    n_e = hi - lo
+    hb = [s.host_buffers(n_e), s.host_buffers(n_e)]
+    for dst, src in zip((hb[0].out['pos_o'], hb[0].out['rot_o'], hb[0].out['vel_o'], hb[0].out['ang_o']),
+                        (pos, rot, vel, ang)):
+      dst[...] = src[lo:hi]
+    ha = [np.ascontiguousarray(hact[i % hact.shape[0], lo:hi]) for i in range(min(e2e_steps + 3, hact.shape[0]))]
+    return {'hb': hb, 'qp': QP(hb[0].out['pos_o'], hb[0].out['rot_o'], hb[0].out['vel_o'], hb[0].out['ang_o']),
+            'acts': ha, 'act_buf': [hb[0].act, hb[1].act]}   # page-locked action buffers (one per in-flight step)
+
+  one = host_chain(0, b)
   for i in range(3):
-    hqp, hinfo = s.step(hqp, hact[i % hact.shape[0]], out=hb[(i + 1) % 2])
+    one['act_buf'][i % 2][...] = one['acts'][i % len(one['acts'])]
+    one['qp'], _ = s.step(one['qp'], one['act_buf'][i % 2], out=one['hb'][(i + 1) % 2])
   barrier()
   t0 = time.perf_counter()
   for i in range(e2e_steps):
-    hqp, hinfo = s.step(hqp, hact[i % hact.shape[0]], out=hb[i % 2])
+    one['act_buf'][i % 2][...] = one['acts'][i % len(one['acts'])]
+    one['qp'], _ = s.step(one['qp'], one['act_buf'][i % 2], out=one['hb'][i % 2])
+  barrier()
+  t_e2e_single = time.perf_counter() - t0
+  e2e_finite = bool(np.isfinite(one['qp'].pos).all())
+  del one
+  halves = [host_chain(0, b // 2), host_chain(b // 2, b)]
+
+  def issue(g, i):
+    c = halves[g]
+    c['act_buf'][i % 2][...] = c['acts'][i % len(c['acts'])]
+    c['pending'] = s.step_async(c['qp'], c['act_buf'][i % 2], out=c['hb'][(i + 1) % 2], slot=g)
+
+  def finish(g):
+    s.wait(g)
+    halves[g]['qp'] = halves[g]['pending'][0]
+
+  for i in range(3):
+    for g in range(2):
+      issue(g, i)
+    for g in range(2):
+      finish(g)
+  barrier()
+  t0 = time.perf_counter()
+  issue(0, 0)
+  issue(1, 0)
+  for i in range(1, e2e_steps):     # while one half is in flight the host turns the other around
+    finish(0)
+    issue(0, i)
+    finish(1)
+    issue(1, i)
+  finish(0)
+  finish(1)
   barrier()
   t_e2e = time.perf_counter() - t0
-  e2e_finite = bool(np.isfinite(hqp.pos).all())
-  h2d, d2h = s.host_transfer_bytes(b)
+  e2e_finite = e2e_finite and all(bool(np.isfinite(c['qp'].pos).all()) for c in halves)
+  del halves
+
+  # ---- e2e of the gym-style loop (what envs/to_torch.py moves per step): the state stays on the device,
+  # page-locked host ACTIONS in, obs / reward / done / metrics out, one launch working on the mapped host
+  # memory; the host waits for every step's results before it issues the next (a policy would need them).
+  t_gym, gym_bytes = 0.0, (0, 0)
+  if ms_env > 0 and not args.no_e2e:
+    hio = env.host_io(b)
+    st_g = State(qps[0], None, None, None)
+    hact_t = [torch.from_numpy(hact[i % hact.shape[0]]).pin_memory() for i in range(4)]
+    for i in range(3):
+      st_g = env.step(st_g, hact_t[i % 4], host_out=hio)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+      st_g = env.step(st_g, hact_t[i % 4], host_out=hio)
+      torch.cuda.current_stream().synchronize()
+    barrier()
+    t_gym = time.perf_counter() - t0
+    e2e_finite = e2e_finite and bool(torch.isfinite(hio['obs']).all())
+    gym_bytes = (4 * b * a, 4 * b * (env_obs + 2 + env.sys.num_metrics))
 
   # ---- the other BASELINE configs (humanoid 8192, grasp 4096, ant 128 x 1000), each rank its shard ----
   sec = []
@@ -621,6 +686,7 @@ def run_gpu(args, desc):
   from brax_b200 import shard
   ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll, ms_av, ms_env, ms_chunk = shard.reduce_stats(
       [ms_total, ms_b2b, t_e2e, t_wall, ms_flushed, ms_roll, ms_av, ms_env, ms_chunk], ['max'] * 9, device=dev)
+  t_e2e_single, t_gym = shard.reduce_stats([t_e2e_single, t_gym], ['max'] * 2, device=dev)
   sec_ms = shard.reduce_stats([x for m, _, _ in sec for x in m], ['max'] * (3 * len(sec)), device=dev)
   reward_sum, energy, nonfinite, sec_bad = shard.reduce_stats(
       [reward_sum, energy, nonfinite, sum(0 if i['finite'] else 1 for _, i, _ in sec)], ['sum'] * 4, device=dev)
@@ -685,9 +751,20 @@ def run_gpu(args, desc):
         'wall_s_timed_loop_incl_spin': t_wall,
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d,
                 'd2h_bytes_per_step': d2h, 'steps': e2e_steps, 'finite': e2e_finite,
-                'path': 'System.step(numpy QP on page-locked HostBuffers, out=HostBuffers) -> bx_step_host: '
-                        'one launch working on the mapped host memory (tiles pull inputs / push outputs '
-                        'over PCIe); pageable callers get the chunked 3-stream copy pipeline'},
+                'gbs_per_rank': {'h2d': h2d * e2e_steps / t_e2e / 1e9, 'd2h': d2h * e2e_steps / t_e2e / 1e9},
+                'path': 'System.step_async / wait (numpy QP + act on page-locked HostBuffers, QP + full Info out) -> '
+                        'bx_step_host_async: the batch as two independent halves on two slots, each half a dependent '
+                        'chain step -> step; every launch works on the mapped host memory (tiles pull inputs / push '
+                        'outputs over PCIe)',
+                'single_chain': {'value': world * b * e2e_steps / t_e2e_single, 'unit': UNIT,
+                                 'what': 'the whole batch as ONE dependent chain of synchronous System.step calls '
+                                         '(bx_step_host; round 1\'s e2e figure)'}},
+        'e2e_env_step': ({'value': world * b * e2e_steps / t_gym, 'unit': UNIT, 'h2d_bytes_per_step': gym_bytes[0],
+                          'd2h_bytes_per_step': gym_bytes[1], 'steps': e2e_steps,
+                          'gbs_per_rank': {'h2d': gym_bytes[0] * e2e_steps / t_gym / 1e9, 'd2h': gym_bytes[1] * e2e_steps / t_gym / 1e9},
+                          'path': 'Env.step(state on the device, page-locked host actions, host_out=page-locked obs / reward / '
+                                  'done / metrics): the gym-style loop of brax/envs/wrappers.py:228-260 + to_torch.py:56-64; the '
+                                  'host synchronises after every step'} if t_gym > 0 else None),
         'gpu_launches': int(launches),
         'clocks': clocks, 'finite': finite and nonfinite == 0 and sec_bad == 0,
         'stats_all_ranks': {'sum_reward_last_env_step': reward_sum, 'sum_kinetic_energy_final_state': energy,

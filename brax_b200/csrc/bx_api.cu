@@ -986,8 +986,7 @@ extern "C" int bx_system_autotune(bx_system* s, int64_t num_envs, const bx_step_
 
 extern "C" int bx_system_threads(const bx_system* s) { return s ? 32 * s->warps : -1; }
 
-// Host-buffer step: H2D copies, one launch, D2H copies, synchronise.
-extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
+static int host_args_ok(const bx_system* s, int64_t B, const bx_step_io* hio) {
   if (!s || !hio) return fail("NULL argument");
   if (B <= 0) return fail("num_envs must be positive");
   if (hio->first_pos) return fail("auto-reset inputs are supported on the device path only (bx_step / bx_rollout)");
@@ -995,64 +994,108 @@ extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
   if (!hio->pos || !hio->rot || !hio->vel || !hio->ang || !hio->act || !hio->pos_o || !hio->rot_o ||
       !hio->vel_o || !hio->ang_o)
     return fail("QP / act pointers must not be NULL");
+  return 0;
+}
+
+// Zero-copy route of the host path: when every buffer is page-locked (bx_host_alloc, cudaHostRegister,
+// torch pin_memory) the kernel works on the host memory directly -- each tile pulls its input spans
+// over PCIe with bulk async copies and pushes its outputs with coalesced 128-bit stores, so upload,
+// compute and download of different tiles overlap inside ONE launch on streams[slot].  *pinned = 0
+// (nothing launched) when some buffer is pageable.  Does not synchronise.
+// (Measured and rejected: outputs staged in device memory and moved by the copy engine, one DMA per
+// contiguous host run -- 30-33 M env-steps/s for 8192 ants in 2-3 groups against 38 M for the tiles'
+// own stores: the kernel -> copy serialisation costs more than the engine's higher link rate gains.)
+static int host_launch_pinned(bx_system* s, int64_t B, const bx_step_io* hio, int slot, int* pinned_out) {
+  const float* hin[BX_SEG_IN] = {hio->pos, hio->rot, hio->vel, hio->ang, hio->act};
+  float* const* hout = io_outs(hio);
+  const void* din[BX_SEG_IN];
+  void* dout[BX_SEG_OUT];
+  bool pinned = true;
+  auto dev_ptr = [&](const void* hp, const void** dp) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, hp) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (at.type != cudaMemoryTypeHost || at.devicePointer == nullptr) return false;
+    *dp = at.devicePointer;
+    return true;
+  };
+  for (int i = 0; i < BX_SEG_IN && pinned; i++) pinned = dev_ptr(hin[i], &din[i]);
+  for (int i = 0; i < BX_SEG_OUT && pinned; i++) {
+    dout[i] = nullptr;
+    const bool constant = i >= 4 && s->h.seg_out[i].map < 0;
+    if (hout[i] && s->h.seg_out[i].nper > 0 && !constant)
+      pinned = dev_ptr(hout[i], const_cast<const void**>(&dout[i]));
+  }
+  const void* drand = nullptr;
+  if (pinned && hio->env_rand) pinned = dev_ptr(hio->env_rand, &drand);
+  *pinned_out = pinned ? 1 : 0;
+  if (!pinned) return 0;
+  bx_step_io d;
+  memset(&d, 0, sizeof(d));
+  d.env_rand = static_cast<const float*>(drand);
+  d.pos = (const float*)din[0]; d.rot = (const float*)din[1]; d.vel = (const float*)din[2];
+  d.ang = (const float*)din[3]; d.act = (const float*)din[4];
+  for (int i = 0; i < BX_SEG_OUT; i++) io_outs(&d)[i] = static_cast<float*>(dout[i]);
+  cudaStream_t st = s->streams[slot];
+  // One wave of tiles (all resident together): stagger their starts over the time
+  // the larger transfer direction needs at 60 GB/s (measured flat optimum 45-100,
+  // profiles/r01_sweeps.txt), see bx_step_kernel.cuh.
+  uint32_t stagger_ns = 0;
+  if ((B + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA <= 2 * static_cast<int64_t>(s->sm_count)) {
+    int64_t h2d = 0, d2h = 0;
+    bx_host_transfer_bytes(s, B, &h2d, &d2h);
+    static const double gbps = getenv("BX_HOST_STAGGER_GBPS") ? atof(getenv("BX_HOST_STAGGER_GBPS")) : 60.0;
+    if (gbps > 0) stagger_ns = static_cast<uint32_t>(static_cast<double>(std::max(h2d, d2h)) / gbps);
+  }
+  if (launch(s, B, 1, &d, st, stagger_ns)) return 1;
+  for (int i = 4; i < BX_SEG_OUT; i++)
+    if (hout[i] && s->h.seg_out[i].nper > 0 && s->h.seg_out[i].map < 0) {
+      const float f = s->h.seg_out[i].fill;
+      const size_t cnt = static_cast<size_t>(s->h.seg_out[i].nper) * B;
+      if (f == 0.f) memset(hout[i], 0, cnt * 4); else std::fill(hout[i], hout[i] + cnt, f);
+    }
+  return 0;
+}
+
+static int host_streams(bx_system* s) {
+  for (int i = 0; i < BX_HOST_STREAMS; i++)
+    if (!s->streams[i]) CUDA_OK(cudaStreamCreateWithFlags(&s->streams[i], cudaStreamNonBlocking));
+  return 0;
+}
+
+// The asynchronous form of the zero-copy host step: launches on internal stream `slot` and returns;
+// bx_host_wait(sys, slot) waits for it.  Independent environment groups stepped through different
+// slots overlap: one group's results travel to the host while another group's inputs arrive and a
+// third computes (PCIe is full duplex; a single host-side stepping chain is latency bound).
+extern "C" int bx_step_host_async(bx_system* s, int64_t B, const bx_step_io* hio, int32_t slot) {
+  if (host_args_ok(s, B, hio)) return 1;
+  if (slot < 0 || slot >= BX_HOST_STREAMS) return fail("slot must be 0, 1 or 2");
+  CUDA_OK(cudaSetDevice(s->device));
+  if (host_streams(s)) return 1;
+  int pinned = 0;
+  if (host_launch_pinned(s, B, hio, slot, &pinned)) return 1;
+  if (!pinned) return fail("bx_step_host_async needs page-locked buffers (bx_host_alloc / cudaHostRegister / pin_memory); "
+                           "pageable buffers go through bx_step_host");
+  return 0;
+}
+extern "C" int bx_host_wait(bx_system* s, int32_t slot) {
+  if (!s) return fail("system is NULL");
+  if (slot < 0 || slot >= BX_HOST_STREAMS) return fail("slot must be 0, 1 or 2");
+  if (s->streams[slot]) CUDA_OK(cudaStreamSynchronize(s->streams[slot]));
+  return 0;
+}
+
+// Host-buffer step: H2D copies, one launch, D2H copies, synchronise.
+extern "C" int bx_step_host(bx_system* s, int64_t B, const bx_step_io* hio) {
+  if (host_args_ok(s, B, hio)) return 1;
   CUDA_OK(cudaSetDevice(s->device));
   const int64_t n = s->h.nb, a = s->h.act_size;
   // in: 13n + a ; out: the segments' nper (floats per env)
-  for (int i = 0; i < BX_HOST_STREAMS; i++)
-    if (!s->streams[i]) CUDA_OK(cudaStreamCreateWithFlags(&s->streams[i], cudaStreamNonBlocking));
+  if (host_streams(s)) return 1;
   {
-    // Zero-copy path: when every buffer is page-locked (bx_host_alloc,
-    // cudaHostRegister, torch pin_memory) the kernel works on the host memory
-    // directly -- each tile pulls its input spans over PCIe with bulk async copies
-    // and pushes its outputs with coalesced 128-bit stores, so upload, compute and
-    // download of different tiles overlap inside ONE launch.
-    const float* hin[BX_SEG_IN] = {hio->pos, hio->rot, hio->vel, hio->ang, hio->act};
-    float* const* hout = io_outs(hio);
-    const void* din[BX_SEG_IN];
-    void* dout[BX_SEG_OUT];
-    bool pinned = true;
-    auto dev_ptr = [&](const void* hp, const void** dp) {
-      cudaPointerAttributes at;
-      if (cudaPointerGetAttributes(&at, hp) != cudaSuccess) { cudaGetLastError(); return false; }
-      if (at.type != cudaMemoryTypeHost || at.devicePointer == nullptr) return false;
-      *dp = at.devicePointer;
-      return true;
-    };
-    for (int i = 0; i < BX_SEG_IN && pinned; i++) pinned = dev_ptr(hin[i], &din[i]);
-    for (int i = 0; i < BX_SEG_OUT && pinned; i++) {
-      dout[i] = nullptr;
-      const bool constant = i >= 4 && s->h.seg_out[i].map < 0;
-      if (hout[i] && s->h.seg_out[i].nper > 0 && !constant)
-        pinned = dev_ptr(hout[i], const_cast<const void**>(&dout[i]));
-    }
-    const void* drand = nullptr;
-    if (pinned && hio->env_rand) pinned = dev_ptr(hio->env_rand, &drand);
+    int pinned = 0;
+    if (host_launch_pinned(s, B, hio, 0, &pinned)) return 1;
     if (pinned) {
-      bx_step_io d;
-      memset(&d, 0, sizeof(d));
-      d.env_rand = static_cast<const float*>(drand);
-      d.pos = (const float*)din[0]; d.rot = (const float*)din[1]; d.vel = (const float*)din[2];
-      d.ang = (const float*)din[3]; d.act = (const float*)din[4];
-      for (int i = 0; i < BX_SEG_OUT; i++) io_outs(&d)[i] = static_cast<float*>(dout[i]);
-      cudaStream_t st = s->streams[0];
-      // One wave of tiles (all resident together): stagger their starts over the time
-      // the larger transfer direction needs at 60 GB/s (measured flat optimum 45-100,
-      // profiles/r01_sweeps.txt), see bx_step_kernel.cuh.
-      uint32_t stagger_ns = 0;
-      if ((B + BX_ENVS_PER_CTA - 1) / BX_ENVS_PER_CTA <= 2 * static_cast<int64_t>(s->sm_count)) {
-        int64_t h2d = 0, d2h = 0;
-        bx_host_transfer_bytes(s, B, &h2d, &d2h);
-        static const double gbps = getenv("BX_HOST_STAGGER_GBPS") ? atof(getenv("BX_HOST_STAGGER_GBPS")) : 60.0;
-        if (gbps > 0) stagger_ns = static_cast<uint32_t>(static_cast<double>(std::max(h2d, d2h)) / gbps);
-      }
-      if (launch(s, B, 1, &d, st, stagger_ns)) return 1;
-      for (int i = 4; i < BX_SEG_OUT; i++)
-        if (hout[i] && s->h.seg_out[i].nper > 0 && s->h.seg_out[i].map < 0) {
-          const float f = s->h.seg_out[i].fill;
-          const size_t cnt = static_cast<size_t>(s->h.seg_out[i].nper) * B;
-          if (f == 0.f) memset(hout[i], 0, cnt * 4); else std::fill(hout[i], hout[i] + cnt, f);
-        }
-      CUDA_OK(cudaStreamSynchronize(st));
+      CUDA_OK(cudaStreamSynchronize(s->streams[0]));
       return 0;
     }
   }

@@ -244,14 +244,28 @@ class Env:
   def _place_targets(self, qp, gen):
     return qp
 
-  def step(self, state: State, action) -> State:
-    """`Env.step(state, action)` (ant.py:222, humanoid.py:246): one kernel launch."""
-    return self._launch(state, action)
+  def step(self, state: State, action, host_out=None) -> State:
+    """`Env.step(state, action)` (ant.py:222, humanoid.py:246): one kernel launch.
 
-  def _launch(self, state: State, action, rand=None, auto_reset=None) -> State:
+    host_out: (state on the GPU) the dict of `host_io(batch)`: obs / reward / done / metrics are
+    written straight into those page-locked host tensors by the launch, and `action` may be its
+    page-locked 'action' tensor -- the gym-style loop (wrappers.py:228-260, to_torch.py:56-64) with
+    the state resident on the device.  Synchronise before reading them."""
+    return self._launch(state, action, host_out=host_out)
+
+  def host_io(self, batch: int):
+    """Page-locked host tensors for `step(..., host_out=)`: 'action' [B,A] in, 'obs' [B,O],
+    'reward' [B], 'done' [B], 'metrics' [B,M] out."""
+    import torch
+    mk = lambda *s: torch.zeros(s, dtype=torch.float32).pin_memory()  # noqa: E731
+    return {'action': mk(batch, self.action_size), 'obs': mk(batch, self.observation_size), 'reward': mk(batch),
+            'done': mk(batch), 'metrics': mk(batch, self.sys.num_metrics)}
+
+  def _launch(self, state: State, action, rand=None, auto_reset=None, host_out=None) -> State:
     torch_path = _system._is_torch(state.qp.pos)
     qp, info, eo = self.sys.step(state.qp, action, env=True, env_rand=rand, auto_reset=auto_reset,
-                                 info=self.keep_info or not torch_path)
+                                 info=self.keep_info or not torch_path,
+                                 env_out=None if host_out is None else {k: host_out[k] for k in ('obs', 'reward', 'done', 'metrics')})
     names = self.env.metric_names()
     metrics = dict(state.metrics)
     metrics.update({k: eo['metrics'][..., i] for i, k in enumerate(names)})

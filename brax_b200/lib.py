@@ -18,7 +18,7 @@ SYMBOLS = ('bx_system_create', 'bx_system_destroy', 'bx_system_num_contacts',
            'bx_system_autotune', 'bx_system_threads', 'bx_host_transfer_bytes',
            'bx_host_alloc', 'bx_host_free', 'bx_desc_tile_bytes',
            'bx_launch_count', 'bx_last_error', 'bx_system_num_joint_dof', 'bx_default_qp',
-           'bx_step_host_static', 'bx_static_scratch_bytes')
+           'bx_step_host_static', 'bx_static_scratch_bytes', 'bx_step_host_async', 'bx_host_wait')
 
 _lib = None
 
@@ -54,6 +54,10 @@ def load():
   lib.bx_step_host_static.restype = C.c_int
   lib.bx_static_scratch_bytes.argtypes = []
   lib.bx_static_scratch_bytes.restype = C.c_int64
+  lib.bx_step_host_async.argtypes = [P, C.c_int64, C.POINTER(_desc.CStepIO), C.c_int32]
+  lib.bx_step_host_async.restype = C.c_int
+  lib.bx_host_wait.argtypes = [P, C.c_int32]
+  lib.bx_host_wait.restype = C.c_int
   lib.bx_rollout.argtypes = [P, C.c_int64, C.c_int32,
                              C.POINTER(_desc.CStepIO), P]
   lib.bx_rollout.restype = C.c_int

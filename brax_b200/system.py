@@ -152,29 +152,36 @@ class HostBuffers:
     self._ptrs = []
     n, k, a = system.num_bodies, system.num_contacts, system.act_size
 
-    def arr(shape):
-      count = int(np.prod(shape))
-      p = self._lib.bx_host_alloc(max(count, 1) * 4)
+    def block(shapes):
+      """One page-locked allocation holding arrays of the given shapes back to back (each on a 16-byte
+      boundary): the outputs of a step are then one contiguous run of host memory, which
+      bx_step_host_async moves with a single DMA."""
+      counts = [int(np.prod(sh)) for sh in shapes]
+      offs, off = [], 0
+      for c in counts:
+        offs.append(off)
+        off += -(-max(c, 1) // 4) * 4
+      p = self._lib.bx_host_alloc(off * 4)
       if not p:
         raise MemoryError('bx_host_alloc: ' + _lib.last_error())
       self._ptrs.append(p)
-      return np.ctypeslib.as_array((C.c_float * max(count, 1)).from_address(p))[:count].reshape(shape)
+      whole = np.ctypeslib.as_array((C.c_float * off).from_address(p))
+      return [(whole[o:o + c].reshape(sh), p + 4 * o) for o, c, sh in zip(offs, counts, shapes)]
+
+    def arr(shape):
+      return block([shape])[0][0]
 
     self.out = {}
     self.out_ptr = {}   # name -> address (None for empty outputs), read by System.step
-    for name, w, dim in _OUT:
-      m = n if dim == 'n' else k
-      self.out[name] = arr((batch, m, w) if w else (batch, m))
-      self.out_ptr[name] = self._ptrs[-1] if self.out[name].size else None
+    specs = [(name, ((batch, n if dim == 'n' else k, w) if w else (batch, n if dim == 'n' else k))) for name, w, dim in _OUT]
     nj = len(system.desc.joints)
-    for name, w, _ in _OUT_AV:
-      self.out[name] = arr((batch, nj, w))
-      self.out_ptr[name] = self._ptrs[-1] if self.out[name].size else None
+    specs += [(name, (batch, nj, w)) for name, w, _ in _OUT_AV]
     if system.env is not None:
-      for name, shape in (('obs', (batch, system.obs_size)), ('reward', (batch,)), ('done', (batch,)),
-                          ('metrics', (batch, system.num_metrics))):
-        self.out[name] = arr(shape)
-        self.out_ptr[name] = self._ptrs[-1]
+      specs += [('obs', (batch, system.obs_size)), ('reward', (batch,)), ('done', (batch,)),
+                ('metrics', (batch, system.num_metrics))]
+    for (name, _), (a_, ptr) in zip(specs, block([sh for _, sh in specs])):
+      self.out[name] = a_
+      self.out_ptr[name] = ptr if a_.size else None
     self.pos, self.rot = arr((batch, n, 3)), arr((batch, n, 4))
     self.vel, self.ang = arr((batch, n, 3)), arr((batch, n, 3))
     self.act = arr((batch, a))
@@ -356,7 +363,7 @@ class System:
 
   # ---- the step ---------------------------------------------------------------
   def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False, env: bool = False,
-           env_rand=None, auto_reset: 'AutoReset' = None, info: bool = True):
+           env_rand=None, auto_reset: 'AutoReset' = None, info: bool = True, env_out=None):
     """`System.step(qp, act) -> (qp, info)` (system.py:244-247).
 
     out: optional `HostBuffers` (host path only): results are written into its
@@ -371,13 +378,21 @@ class System:
     AutoResetWrapper.step (envs/wrappers.py:105-148) applied inside the launch; the env
     dict gains 'steps' and 'truncation' and qp / obs / done are the wrapped ones.
     info: False (torch path) = do not write the Info outputs (the returned info is None): what
-    `Env.step` needs, which drops the Info after building the obs (envs/ant.py:224)."""
+    `Env.step` needs, which drops the Info after building the obs (envs/ant.py:224).
+    env_out: (torch path, env=True) dict of preallocated float32 tensors 'obs' [B,O], 'reward' [B],
+    'done' [B], 'metrics' [B,M] that receive the env outputs -- CUDA tensors, or PAGE-LOCKED host
+    tensors (`pin_memory=True`): the launch then writes them over PCIe itself.  `act` may likewise be a
+    page-locked host tensor.  That is the gym-style loop with the state resident on the device
+    (brax/envs/wrappers.py:228-260 + to_torch.py:56-64): actions in, obs / reward / done out, one
+    launch, no separate copies; synchronise the stream before reading the host tensors."""
     if env and self.env is None:
       raise ValueError('this System was built without an EnvDesc')
     if auto_reset is not None and not env:
       raise ValueError('auto_reset needs env=True')
     if _is_torch(qp.pos):
-      return self._step_torch(qp, act, 1, angle_vel, env, env_rand, auto_reset, info)
+      return self._step_torch(qp, act, 1, angle_vel, env, env_rand, auto_reset, info, env_out=env_out)
+    if env_out is not None:
+      raise ValueError('env_out belongs to the torch path')
     if auto_reset is not None:
       raise ValueError('auto_reset is supported with torch CUDA tensors only')
     return self._step_numpy(qp, act, out, angle_vel, env, env_rand)
@@ -480,7 +495,7 @@ class System:
     io.action_repeat = 0
 
   def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False, env_rand=None,
-                  auto_reset=None, info: bool = True, observe: bool = False):
+                  auto_reset=None, info: bool = True, observe: bool = False, env_out=None):
     """env_rand: (fetch / grasp) uniforms of the target teleport, [B,3] or [T,B,3].
 
     Host cost per call is what bounds a plain Python stepping loop (the kernel takes ~57 us for
@@ -509,10 +524,15 @@ class System:
 
     ins = (prep(qp.pos, b * n * 3), prep(qp.rot, b * n * 4), prep(qp.vel, b * n * 3),
            prep(qp.ang, b * n * 3), prep(act, steps * b * a))
-    key = (b, av, env, steps, info)
+    if ins[4].device.type != 'cuda' and not ins[4].is_pinned():
+      raise RuntimeError('host actions must be page-locked (pin_memory): the launch reads them over PCIe')
+    ext = env_out is not None
+    if ext and not (env and batched and steps == 1):
+      raise ValueError('env_out needs env=True on a batched single step')
+    key = (b, av, env, steps, info, ext)
     plan = self._plans.get(key)
     if plan is None:
-      plan = self._plans[key] = _Plan(self._specs(b, av, env, steps, info))
+      plan = self._plans[key] = _Plan(self._specs(b, av, env and not ext, steps, info))
     flat = torch.empty(plan.total, dtype=f32, device=dev)
     w = plan.words
     w[:5] = [t.data_ptr() for t in ins]
@@ -544,6 +564,12 @@ class System:
       io.episode_length = 0.0
       io.action_repeat = 0
     io.observe = int(observe)
+    if ext:
+      for nm, cnt in (('obs', b * self.obs_size), ('reward', b), ('done', b), ('metrics', b * self.num_metrics)):
+        t = env_out[nm]
+        if t.dtype is not f32 or not t.is_contiguous() or t.numel() != cnt or not (t.is_cuda or t.is_pinned()):
+          raise ValueError('env_out[%r] must be a contiguous float32 CUDA or page-locked tensor of %d elements' % (nm, cnt))
+        setattr(io, nm, t.data_ptr())
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     if self.autotune and not observe and steps == 1 and b >= 1024 and b not in self._tuned:
       # first call at this batch size: time the candidate CTA sizes once
@@ -569,15 +595,26 @@ class System:
     if av:
       res += (JointState(view(flat, 'joint_angle'), view(flat, 'joint_velocity')),)
     if env:
-      eo = {k: view(flat, k) for k in ('obs', 'reward', 'done', 'metrics')}
+      eo = dict(env_out) if ext else {k: view(flat, k) for k in ('obs', 'reward', 'done', 'metrics')}
       if extra is not None:
         eo['steps'] = extra[:b].view((b,))
         eo['truncation'] = extra[b:].view((steps, b) if steps > 1 else (b,))
       res += (eo,)
     return res
 
+  def step_async(self, qp: QP, act, out: 'HostBuffers', slot: int = 0, angle_vel: bool = False, env: bool = False,
+                 env_rand=None):
+    """Host path without the wait: page-locked inputs and outputs (`HostBuffers`), the zero-copy launch
+    goes to the library's internal stream `slot` (0..2) and the call returns; `wait(slot)` blocks until
+    the results are in `out`.  Independent env groups on different slots overlap transfers and compute."""
+    return self._step_numpy(qp, act, out, angle_vel, env, env_rand, slot=int(slot))
+
+  def wait(self, slot: int = 0):
+    if self._lib.bx_host_wait(self._h, int(slot)) != 0:
+      raise RuntimeError('bx_host_wait: ' + _lib.last_error())
+
   def _step_numpy(self, qp: QP, act, bufs: 'HostBuffers' = None, av: bool = False, env: bool = False,
-                  env_rand=None):
+                  env_rand=None, slot: int = None):
     batched, b = self._shapes(np.shape(qp.pos))
     n, a = self.num_bodies, self.act_size
 
@@ -591,7 +628,7 @@ class System:
 
     ins = (prep(qp.pos, b * n * 3), prep(qp.rot, b * n * 4), prep(qp.vel, b * n * 3),
            prep(qp.ang, b * n * 3), prep(act, b * a))
-    io = self._io
+    io = self._io if slot is None else CStepIO()   # (an in-flight call keeps its own struct)
     io.pos, io.rot, io.vel, io.ang, io.act = [t.__array_interface__['data'][0] for t in ins]
     self._clear_optional(io)
     if bufs is not None:
@@ -609,7 +646,12 @@ class System:
     if env_rand is not None:
       env_rand = prep(env_rand, b * 3)
       io.env_rand = env_rand.__array_interface__['data'][0]
-    rc = self._lib.bx_step_host(self._h, b, C.byref(io))
+    if slot is None:
+      rc = self._lib.bx_step_host(self._h, b, C.byref(io))
+    else:
+      if bufs is None:
+        raise ValueError('step_async needs out=HostBuffers (page-locked outputs)')
+      rc = self._lib.bx_step_host_async(self._h, b, C.byref(io), slot)
     if rc != 0:
       raise RuntimeError('bx_step_host: ' + _lib.last_error())
     return self._wrap(out, batched)

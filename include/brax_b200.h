@@ -345,6 +345,15 @@ int bx_step(const bx_system* sys, int64_t num_envs, const bx_step_io* io,
  * System.step makes and what bench.py's e2e number times. */
 int bx_step_host(bx_system* sys, int64_t num_envs, const bx_step_io* host_io);
 
+/* Asynchronous form of bx_step_host for page-locked buffers: launches the zero-copy step on internal
+ * stream `slot` (0..2) and returns; bx_host_wait(sys, slot) blocks until that slot's work is done and
+ * its outputs are in host memory.  Independent groups of environments stepped through different slots
+ * overlap their PCIe traffic and compute (a single host-side chain step -> step is latency bound).
+ * The reference analogue is JAX's asynchronous dispatch of jit(vmap(System.step)) followed by
+ * block_until_ready / device_get (brax/envs/to_torch.py:56-64).  Pageable buffers are refused. */
+int bx_step_host_async(bx_system* sys, int64_t num_envs, const bx_step_io* host_io, int32_t slot);
+int bx_host_wait(bx_system* sys, int32_t slot);
+
 /* The host-buffer step for callers that may NOT allocate (code under CUDA graph capture
  * elsewhere in the process, tight serving loops, harnesses that forbid cudaMalloc).
  * NO COUNTERPART IN THE REFERENCE.

@@ -190,6 +190,33 @@ def test_obs_is_built_before_the_target_teleport(variant):
       assert np.abs(want[:, tb] - r32['qp']['pos'][:, tb]).max() > 0.5   # the targets did move
 
 
+@pytest.mark.parametrize('variant', ['ant', 'humanoid'])
+def test_env_step_with_host_io(variant):
+  """Gym-style loop with the state resident on the GPU: page-locked host actions in, obs / reward /
+  done / metrics written by the launch into page-locked host tensors == the device-tensor path."""
+  torch = _torch()
+  from brax_b200.envs import State
+  sysname, env = _env(variant)
+  b = 777
+  qp, rng = _harvest(env.sys, b, 5, 13)
+  hio = env.host_io(b)
+  st_d = st_h = State(qp, None, None, None)
+  for t in range(3):
+    act = torch.from_numpy(rng.uniform(-1, 1, (b, env.action_size)).astype(np.float32))
+    hio['action'].copy_(act)
+    st_d = env.step(st_d, act.cuda())
+    st_h = env.step(st_h, hio['action'], host_out=hio)
+    torch.cuda.synchronize()
+    assert not st_h.obs.is_cuda and st_h.obs.data_ptr() == hio['obs'].data_ptr()
+    assert torch.equal(st_h.obs, st_d.obs.cpu()) and torch.equal(st_h.reward, st_d.reward.cpu())
+    assert torch.equal(st_h.done, st_d.done.cpu())
+    for k in env.env.metric_names():
+      assert torch.equal(st_h.metrics[k], st_d.metrics[k].cpu()), k
+    assert torch.equal(st_h.qp.pos, st_d.qp.pos)
+  with pytest.raises(RuntimeError, match='page-locked'):
+    env.step(st_h, torch.zeros(b, env.action_size), host_out=hio)
+
+
 def test_env_rollout_equals_repeated_steps():
   """bx_rollout writes the env outputs of EVERY step: [T,B,...] bit-identical to T
   env steps; ragged and unbatched shapes equal the same envs inside a big batch."""

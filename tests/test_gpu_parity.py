@@ -509,6 +509,50 @@ def test_host_path_pinned_buffers_and_chunking():
       assert d2h == 4 * b * (31 * n + 7 * kk - 9 * n)
 
 
+def test_host_path_async_groups_equal_sync_calls():
+  """bx_step_host_async / bx_host_wait: two independent env groups stepped through two slots,
+  three chained steps each, interleaved -- bitwise the synchronous bx_step_host results; pageable
+  buffers are refused."""
+  _torch()
+  from brax_b200.system import QP
+  s = _system('ant')
+  b = 1000
+  rng = np.random.default_rng(3)
+  groups = []
+  for g in range(2):
+    q0 = s.default_qp(batch=b)
+    pos = q0.pos + rng.uniform(-.02, .02, q0.pos.shape).astype(np.float32)
+    vel = rng.uniform(-.3, .3, q0.vel.shape).astype(np.float32)
+    acts = rng.uniform(-1, 1, (3, b, s.act_size)).astype(np.float32)
+    groups.append((QP(pos, q0.rot.copy(), vel, vel.copy()), acts))
+  want = []
+  for qp, acts in groups:
+    for t in range(3):
+      qp, info = s.step(qp, acts[t])
+    want.append(_flat(qp, info))
+  bufs = [[s.host_buffers(b), s.host_buffers(b)] for _ in range(2)]
+  cur = []
+  for g, (qp, acts) in enumerate(groups):
+    hb = bufs[g][1]
+    hb.pos[...], hb.rot[...], hb.vel[...], hb.ang[...] = qp.pos, qp.rot, qp.vel, qp.ang
+    cur.append(hb.qp())
+  hact = [s.host_buffers(b) for _ in range(2)]
+  res = [None, None]
+  for t in range(3):
+    for g in range(2):
+      hact[g].act[...] = groups[g][1][t]
+      res[g] = s.step_async(cur[g], hact[g].act, out=bufs[g][t % 2], slot=g)
+    for g in range(2):
+      s.wait(g)
+      cur[g] = res[g][0]
+  for g in range(2):
+    got = _flat(*res[g])
+    for k in want[g]:
+      np.testing.assert_array_equal(got[k], want[g][k], err_msg='group %d %s' % (g, k))
+  with pytest.raises(RuntimeError, match='page-locked'):
+    s.step_async(groups[0][0], groups[0][1][0], out=bufs[0][0], slot=0)   # pageable inputs
+
+
 def test_dependent_launch_chain_is_ordered():
   """Launches use programmatic stream serialization (the next launch's CTAs may become
   resident and load tables while this one drains); the chain step N -> N+1 must still see
