@@ -60,5 +60,22 @@ def build(force: bool = False, verbose: bool = False, extra=(), out: str = None)
   return out
 
 
+def build_ffi(verbose: bool = True):
+  """Compiles csrc/bx_ffi.cc (the XLA FFI handler) next to the library -- only where jaxlib's headers
+  resolve.  Returns the .so path, or None after printing why it was skipped."""
+  try:
+    import jax.ffi  # noqa: F401
+    inc = jax.ffi.include_dir()
+  except Exception as e:  # jax is not installed on this box (and cannot be: no network)
+    if verbose:
+      print('brax_b200: bx_ffi.cc not built -- jaxlib headers unavailable on this box (%s: %s)' % (type(e).__name__, e))
+    return None
+  out = os.path.join(HERE, 'libbrax_b200_ffi.so')
+  subprocess.check_call(['g++', '-std=c++17', '-O2', '-fPIC', '-shared', '-I' + inc, '-I/usr/local/cuda/include',
+                         os.path.join(CSRC, 'bx_ffi.cc'), '-o', out, '-L' + HERE, '-lbrax_b200', '-Wl,-rpath,$ORIGIN'])
+  return out
+
+
 if __name__ == '__main__':
   print(build(force=True, verbose=True))
+  build_ffi()

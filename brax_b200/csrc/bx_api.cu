@@ -84,6 +84,11 @@ static int validate(const bx_system_desc* d) {
   if (d->act_size < 1) return fail("act_size must be >= 1");
   if (d->substeps < 1) return fail("substeps must be >= 1");
   if (!(d->dt_sub > 0.f)) return fail("dt_sub must be positive");
+  if (!d->bodies) return fail("bodies is NULL");
+  if (d->num_joints > 0 && !d->joints) return fail("joints is NULL");
+  if (d->num_actuators > 0 && !d->actuators) return fail("actuators is NULL");
+  if (d->num_forces > 0 && !d->forces) return fail("forces is NULL");
+  if (d->num_pairs > 0 && !d->pairs) return fail("pairs is NULL");
   for (int i = 0; i < d->num_joints; i++) {
     const bx_joint& j = d->joints[i];
     if (j.kind < BX_JOINT_REVOLUTE || j.kind > BX_JOINT_SPRING_SPHERICAL)
@@ -99,12 +104,14 @@ static int validate(const bx_system_desc* d) {
     if (a.kind != BX_ACT_TORQUE && a.kind != BX_ACT_ANGLE) return fail("unsupported actuator kind");
     if (a.joint < 0 || a.joint >= d->num_joints) return fail("actuator joint out of range");
     for (int k = 0; k < 3; k++)
-      if (a.act_index[k] >= d->act_size) return fail("actuator act_index out of range");
+      if (a.act_index[k] < -1 || a.act_index[k] >= d->act_size) return fail("actuator act_index out of range (-1 = masked)");
   }
   for (int i = 0; i < d->num_forces; i++) {
     const bx_force& f = d->forces[i];
     if (f.kind != BX_FORCE_THRUSTER && f.kind != BX_FORCE_TWISTER) return fail("unsupported force kind");
     if (f.body < 0 || f.body >= d->num_bodies) return fail("force body out of range");
+    // (act_index is NOT range-checked: the reference reads it with jp.take(..., mode='clip'), forces.py:44,87,
+    // and its own swimmer config indexes past the action vector; the kernel clamps the same way)
   }
   int k = 0;
   for (int i = 0; i < d->num_pairs; i++) {
@@ -719,6 +726,12 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   if (e != cudaSuccess || ndev == 0)
     return fail("no CUDA device: brax_b200 has no CPU fallback");
   if (device < 0 || device >= ndev) return fail("device index out of range");
+  // the caller's current device is restored on every way out
+  struct DeviceGuard {
+    int prev = -1;
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+  } guard;
+  if (cudaGetDevice(&guard.prev) != cudaSuccess) guard.prev = -1;
   CUDA_OK(cudaSetDevice(device));
   cudaDeviceProp prop;
   CUDA_OK(cudaGetDeviceProperties(&prop, device));
@@ -792,17 +805,30 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
       if (cost < best - 1e-9) { best = cost; s->warps = w; }
     }
   }
-  cudaError_t e1 = cudaMalloc(&s->d_tab_i, std::max<size_t>(ti.size(), 1) * 4);
-  cudaError_t e2 = cudaMalloc(&s->d_tab_f, std::max<size_t>(tf.size(), 1) * 4);
-  if (e1 != cudaSuccess || e2 != cudaSuccess) { delete s; return fail("cudaMalloc of tables failed"); }
-  CUDA_OK(cudaMemcpy(s->d_tab_i, ti.data(), ti.size() * 4, cudaMemcpyHostToDevice));
-  CUDA_OK(cudaMemcpy(s->d_tab_f, tf.data(), tf.size() * 4, cudaMemcpyHostToDevice));
-  if (set_smem_attr(static_cast<int>(prop.sharedMemPerBlockOptin))) { delete s; return 1; }
+  s->d_tab_i = nullptr;
+  s->d_tab_f = nullptr;
   s->d_reset = nullptr;
   s->reset_dof = 0;
+  auto drop = [&](const char* what, cudaError_t err) {   // frees whatever exists of a half-built system
+    const std::string m = std::string(what) + (err != cudaSuccess ? std::string(": ") + cudaGetErrorString(err) : "");
+    cudaFree(s->d_tab_i); cudaFree(s->d_tab_f); cudaFree(s->d_reset);
+    delete s;
+    return fail(m);
+  };
+  cudaError_t e1 = cudaMalloc(&s->d_tab_i, std::max<size_t>(ti.size(), 1) * 4);
+  cudaError_t e2 = cudaMalloc(&s->d_tab_f, std::max<size_t>(tf.size(), 1) * 4);
+  if (e1 != cudaSuccess || e2 != cudaSuccess) return drop("cudaMalloc of tables failed", e1 != cudaSuccess ? e1 : e2);
+  if ((e1 = cudaMemcpy(s->d_tab_i, ti.data(), ti.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e1 = cudaMemcpy(s->d_tab_f, tf.data(), tf.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess)
+    return drop("upload of tables failed", e1);
+  if (set_smem_attr(static_cast<int>(prop.sharedMemPerBlockOptin))) {
+    const std::string keep = g_err;
+    return drop(keep.c_str(), cudaSuccess);
+  }
   if (desc->reset) {
-    if (cudaMalloc(&s->d_reset, sizeof(bx_reset_desc)) != cudaSuccess) { delete s; return fail("cudaMalloc of reset tables failed"); }
-    CUDA_OK(cudaMemcpy(s->d_reset, desc->reset, sizeof(bx_reset_desc), cudaMemcpyHostToDevice));
+    if ((e1 = cudaMalloc(&s->d_reset, sizeof(bx_reset_desc))) != cudaSuccess) return drop("cudaMalloc of reset tables failed", e1);
+    if ((e1 = cudaMemcpy(s->d_reset, desc->reset, sizeof(bx_reset_desc), cudaMemcpyHostToDevice)) != cudaSuccess)
+      return drop("upload of reset tables failed", e1);
     s->reset_dof = desc->reset->num_dof;
   }
   *out = s;
@@ -827,6 +853,9 @@ extern "C" int bx_default_qp(const bx_system* s, int64_t B, const float* joint_a
 
 extern "C" void bx_system_destroy(bx_system* s) {
   if (!s) return;
+  int prev = -1;
+  if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+  struct Restore { int d; ~Restore() { if (d >= 0) cudaSetDevice(d); } } restore{prev};
   cudaSetDevice(s->device);
   cudaFree(s->d_tab_i);
   cudaFree(s->d_tab_f);
@@ -920,9 +949,15 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   static const int pdl_mode = getenv("BX_PDL") ? atoi(getenv("BX_PDL")) : 2;
   const bool one_wave = tiles <= s->sm_count && 4 * tiles > s->sm_count;
   const int pdl = (pdl_mode == 1 || (pdl_mode == 2 && !one_wave)) ? BX_CC_PDL : 0;
+  // the launch goes to the system's device whatever the caller's current device is (and leaves the
+  // caller's current device as it was); `stream` must belong to the system's device
+  int cur_dev = s->device;
+  if (cudaGetDevice(&cur_dev) != cudaSuccess) cur_dev = s->device;
+  if (cur_dev != s->device) CUDA_OK(cudaSetDevice(s->device));
   cudaError_t le = launch_variant(s->h.mode, s->jc, s->cc | (s->h.env_kind ? BX_CC_ENV : 0) | pdl,
                                   static_cast<unsigned>(tiles), 32 * s->warps,
                                   s->smem_bytes, stream, p, three);
+  if (cur_dev != s->device) cudaSetDevice(cur_dev);
   g_launches.fetch_add(1);
   CUDA_OK(le);
   return 0;
@@ -943,9 +978,13 @@ extern "C" int bx_system_autotune(bx_system* s, int64_t num_envs, const bx_step_
   if (!s || !io) return fail("NULL argument");
   CUDA_OK(cudaSetDevice(s->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  cudaEvent_t e0, e1;
-  CUDA_OK(cudaEventCreate(&e0));
-  CUDA_OK(cudaEventCreate(&e1));
+  struct Events {
+    cudaEvent_t a = nullptr, b = nullptr;
+    ~Events() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+  } ev;
+  CUDA_OK(cudaEventCreate(&ev.a));
+  CUDA_OK(cudaEventCreate(&ev.b));
+  const cudaEvent_t e0 = ev.a, e1 = ev.b;
   const int cand[4] = {8, 10, 12, 16};
   const int keep = s->warps, keep_cc = s->cc;
   float best = 1e30f;
@@ -979,8 +1018,6 @@ extern "C" int bx_system_autotune(bx_system* s, int64_t num_envs, const bx_step_
       }
   s->cc = best_cc;
   s->warps = best_w;
-  cudaEventDestroy(e0);
-  cudaEventDestroy(e1);
   return 0;
 }
 

@@ -1210,8 +1210,12 @@ BXS void phase_body_acc_spring(const Ctx& c, const BxHeader& h) {
 
 // phase S4: contact_fn + velocity-level _contact (colliders.py:116-153,
 // OneWay :267-304, TwoWay :449-493).
+// MODE: where the pose rows live (pbd: the current ping-pong buffer) -- the spring-style impulse is
+// also what System.info(qp) evaluates in pbd systems (system.py:327-340), see phase_info_contacts.
+template <int MODE>
 BXS void spring_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
-  typedef Lay<BX_MODE_LEGACY_SPRING> L;
+  typedef Lay<MODE> L;
+  const int po = MODE == BX_MODE_PBD ? 2 * c.cur : 0;
   {
     const int4 ci = ldi4(c.ti + h.io_contact + k * CI_STRIDE);
     const int pair_row = c.ti[h.io_contact + k * CI_STRIDE + CI_PAIR];
@@ -1221,9 +1225,9 @@ BXS void spring_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
     const float4* bqa = c.tf + h.fo_body + a * BQ_STRIDE;
     const float4* bqb = c.tf + h.fo_body + b * BQ_STRIDE;
     const int ra0 = L::BQ * a, rb0 = L::BQ * b;
-    V3 pa = ldv(c, ra0), pb = ldv(c, rb0);
-    Contact ct = contact_fn(ci.x, cq, pa, ldq(c, ra0 + 1), ldv(c, ra0 + L::VEL), ldv(c, ra0 + L::ANG),
-                            pb, ldq(c, rb0 + 1), ldv(c, rb0 + L::VEL), ldv(c, rb0 + L::ANG));
+    V3 pa = ldv(c, ra0 + po), pb = ldv(c, rb0 + po);
+    Contact ct = contact_fn(ci.x, cq, pa, ldq(c, ra0 + po + 1), ldv(c, ra0 + L::VEL), ldv(c, ra0 + L::ANG),
+                            pb, ldq(c, rb0 + po + 1), ldv(c, rb0 + L::VEL), ldv(c, rb0 + L::ANG));
     const float4 mat = cq[CQ_MAT];
     V3 iia = f3(bqa[BQ_INV_INERTIA]), iib = f3(bqb[BQ_INV_INERTIA]);
     const float4 bma = bqa[BQ_MASS], bmb = bqb[BQ_MASS];  // {1/mass (float32 quotient), mass}
@@ -1261,13 +1265,31 @@ BXS void spring_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
     stv(c, h.q_cn + pair_row, ct.normal);
   }
 }
+template <int MODE>
 BXS void phase_contacts_spring(const Ctx& c, const BxHeader& h) {
   for (int i = c.warp; i < h.nci; i += c.nwarp) {
     const int2 it = *reinterpret_cast<const int2*>(c.ti + h.io_citem + 2 * i);
     CAcc acc = cacc_zero();
 #pragma unroll 1
-    for (int r = 0; r < it.y; r++) spring_row(c, h, it.x + r, acc);
+    for (int r = 0; r < it.y; r++) spring_row<MODE>(c, h, it.x + r, acc);
     cacc_store(c, h, it.x, acc);
+  }
+}
+// System.info(qp).contact (system.py:327-340 `_pbd_info`, :378-390 `_spring_info`): the summed
+// Collider.apply(qp) of all colliders -- per body and collider group the spring-style impulses of its
+// rows, averaged over the rows with a non-zero impulse (1e-8 + count, colliders.py:149-152) -- into the
+// info.contact accumulators only (the state is left alone).  Follows phase_contacts_spring + a barrier.
+template <int MODE>
+BXS void phase_info_bodies(const Ctx& c, const BxHeader& h) {
+  for (int b = c.warp; b < h.nb; b += c.nwarp) {
+    const int32_t* bi = c.ti + h.io_body + b * BI_STRIDE;
+    const int cadj_n = bi[BI_CG_N];
+    if (cadj_n == 0) continue;
+    float4 dl, ds;
+    gather_contact_deltas(c, h, bi[BI_CG_OFF], cadj_n, 1e-8f, &dl, &ds);
+    const int r = h.q_ic + 2 * bi[BI_CSLOT];
+    stv(c, r, f3(dl));
+    stv(c, r + 1, f3(ds));
   }
 }
 
@@ -1760,11 +1782,19 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
         __syncthreads();
         phase_body_acc_spring(c, h);
         __syncthreads();
-        phase_contacts_spring(c, h);
+        phase_contacts_spring<MODE>(c, h);
         __syncthreads();
         phase_body_velocity_update<MODE>(c, h, 1e-8f);
         // same warp<->body mapping as phase_body_kinetic: no barrier needed
       }
+    }
+    if ((BX_FEAT & BXF_ENV) != 0 && p.observe != 0 && h.nk > 0) {
+      // observe (Env.reset): info = sys.info(qp) of the state passed in (envs/ant.py:204) -- the
+      // contact rows and the spring-style contact impulse; actuator / joint parts are not read by any obs
+      __syncthreads();
+      phase_contacts_spring<MODE>(c, h);
+      __syncthreads();
+      phase_info_bodies<MODE>(c, h);
     }
     if (env_on) {
       // Env.step's epilogue of THIS step (every step of a rollout): obs / reward / done /

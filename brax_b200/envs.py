@@ -224,7 +224,12 @@ class Env:
     b = int(batch) if batch is not None else 1
     dev = torch.device(device)
     gen = torch.Generator(device=dev)
-    gen.manual_seed(int(seed or 0))
+    if seed is None:
+      # no seed given: every call draws fresh noise (a per-env counter on top of a fixed base), the way
+      # the reference's callers split a new key per reset; pass `seed` for a reproducible state
+      self._reset_count = getattr(self, '_reset_count', 0) + 1
+      seed = 0x5EED0000 + self._reset_count
+    gen.manual_seed(int(seed))
     nd, scale = self.sys.num_joint_dof, float(getattr(self, '_reset_noise_scale', 0.0))
     noise = lambda: (torch.rand(b, nd, generator=gen, device=dev, dtype=torch.float32) * 2 - 1) * scale  # noqa: E731
     if joint_angle is None:
@@ -234,12 +239,14 @@ class Env:
     qp = self.sys.default_qp(joint_angle=joint_angle.reshape(b, nd), joint_velocity=joint_velocity.reshape(b, nd))
     qp = self._place_targets(qp, gen)
     obs = self.sys.observe(qp)
-    zero = torch.zeros(b, dtype=torch.float32, device=dev)
-    met = {k: zero for k in self.env.metric_names()}
+    names = self.env.metric_names()
+    zeros = torch.zeros((len(names) + 2, b), dtype=torch.float32, device=dev)   # distinct rows: no aliasing
+    reward, done = zeros[0], zeros[1]
+    met = {k: zeros[2 + i] for i, k in enumerate(names)}
     if batch is None:
       qp = _system.QP(*[getattr(qp, k)[0] for k in ('pos', 'rot', 'vel', 'ang')])
-      obs, zero, met = obs[0], zero[0], {k: v[0] for k, v in met.items()}
-    return State(qp, obs, zero, zero, met)
+      obs, reward, done, met = obs[0], reward[0], done[0], {k: v[0] for k, v in met.items()}
+    return State(qp, obs, reward, done, met)
 
   def _place_targets(self, qp, gen):
     return qp

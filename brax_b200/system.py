@@ -203,6 +203,22 @@ def _is_torch(x) -> bool:
   return type(x).__module__.startswith('torch')
 
 
+def _ingest(x):
+  """Arrays that are neither torch tensors nor numpy: anything that speaks DLPack (`__dlpack__`: JAX
+  arrays, CuPy, ...) or the CUDA array interface (`__cuda_array_interface__`: Numba, CuPy) is viewed --
+  zero copy -- as a torch CUDA tensor (the DLPack hop brax/io/torch.py:48-53,79-88 makes between JAX and
+  torch).  torch tensors and numpy arrays pass through."""
+  if _is_torch(x) or isinstance(x, np.ndarray) or isinstance(x, (list, tuple, float, int)):
+    return x
+  if hasattr(x, '__dlpack__'):
+    import torch
+    return torch.from_dlpack(x)
+  if hasattr(x, '__cuda_array_interface__'):
+    import torch
+    return torch.as_tensor(x, device=torch.device('cuda', int(getattr(x, 'device_index', 0) or 0)))
+  return x
+
+
 def tile_bytes(desc: SystemDesc, env=None):
   """(shared-memory bytes of one 32-env tile, quad rows per region) of a system
   (with the env epilogue of `env`, an EnvDesc, if given); needs no device
@@ -389,6 +405,14 @@ class System:
       raise ValueError('this System was built without an EnvDesc')
     if auto_reset is not None and not env:
       raise ValueError('auto_reset needs env=True')
+    if not (_is_torch(qp.pos) or isinstance(qp.pos, np.ndarray)):
+      # DLPack / CUDA-array-interface producers (JAX, CuPy, Numba): zero-copy torch views
+      qp = QP(_ingest(qp.pos), _ingest(qp.rot), _ingest(qp.vel), _ingest(qp.ang))
+      act = _ingest(act)
+    elif _is_torch(qp.pos) and not _is_torch(act):
+      act = _ingest(act)
+      if isinstance(act, np.ndarray):
+        raise TypeError('qp is on the GPU, act is a numpy array: pass a CUDA (or page-locked) tensor')
     if _is_torch(qp.pos):
       return self._step_torch(qp, act, 1, angle_vel, env, env_rand, auto_reset, info, env_out=env_out)
     if env_out is not None:

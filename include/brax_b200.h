@@ -292,10 +292,11 @@ typedef struct bx_step_io {
   float* steps_out;       /* [B] */
   float* truncation;      /* state.info['truncation'] [B] ([T,B] in a rollout) */
   float episode_length;   /* EpisodeWrapper.episode_length; 0 = no episode limit */
-  /* Non-zero (systems with desc.env, bx_step only): no physics -- the launch evaluates the env
-   * epilogue on the state passed in with a zero Info: obs = _get_obs(qp, info) as Env.reset builds
-   * it (envs/ant.py:203-204, humanoid.py:230-231, fetch.py:41-42, grasp.py:60-61; the reference's
-   * sys.info(qp).contact is zero at a resting pose up to rounding-level flips of `penetration > 0`).
+  /* Non-zero (systems with desc.env, bx_step only): no physics -- the launch evaluates
+   * info = System.info(qp) of the state passed in (system.py:327-340 / :378-390: the contact rows and
+   * info.contact = the summed Collider.apply(qp), the spring-style impulse of the pose; the joint /
+   * actuator parts, which no obs reads, stay zero) and the env epilogue on it: obs = _get_obs(qp, info)
+   * as Env.reset builds it (envs/ant.py:203-204, humanoid.py:230-231, fetch.py:41-42, grasp.py:60-61).
    * The QP outputs are the inputs; reward / done / metrics are those of a zero-length step. */
   int32_t observe;
   /* EpisodeWrapper.action_repeat (wrappers.py:106-111; auto-reset launches only, 0 / 1 = none): every

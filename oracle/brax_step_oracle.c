@@ -1543,6 +1543,43 @@ int FN(bxo_angle_vel)(const osys* s, int64_t num_envs, const R* rot, const R* an
   return 0;
 }
 
+/* System.info(qp).contact and the contact data (system.py:327-340 `_pbd_info`, :378-390 `_spring_info`):
+ * in BOTH dynamics modes the summed `Collider.apply(qp)` of all colliders -- the spring-style
+ * contact impulse (colliders.py:116-153) evaluated on the state, with the baumgarte_erp of the
+ * config -- plus contact_pos / normal / penetration of every contact row.  This is the Info the
+ * reference's Env.reset hands to _get_obs (envs/ant.py:204).  Arrays are batched [B, ...]. */
+int FN(bxo_info_contact)(const osys* s, int64_t num_envs, const R* pos, const R* rot, const R* vel,
+                         const R* ang, R* cvel, R* cang, R* cpos, R* cnormal, R* cpen) {
+  const int nk = num_contacts(s);
+  for (int64_t e = 0; e < num_envs; e++) {
+    static _Thread_local oqp qp;
+    static _Thread_local op dp;
+    static _Thread_local ocontact ct[MAXK];
+    for (int b = 0; b < s->nb; b++) {
+      for (int k = 0; k < 3; k++) {
+        qp.pos[b][k] = pos[(e * s->nb + b) * 3 + k];
+        qp.vel[b][k] = vel[(e * s->nb + b) * 3 + k];
+        qp.ang[b][k] = ang[(e * s->nb + b) * 3 + k];
+      }
+      for (int k = 0; k < 4; k++) qp.rot[b][k] = rot[(e * s->nb + b) * 4 + k];
+    }
+    colliders_apply_spring(s, &qp, &dp, ct);
+    for (int b = 0; b < s->nb; b++)
+      for (int k = 0; k < 3; k++) {
+        cvel[(e * s->nb + b) * 3 + k] = dp.vel[b][k];
+        cang[(e * s->nb + b) * 3 + k] = dp.ang[b][k];
+      }
+    for (int c = 0; c < nk; c++) {
+      for (int k = 0; k < 3; k++) {
+        cpos[(e * nk + c) * 3 + k] = ct[c].pos[k];
+        cnormal[(e * nk + c) * 3 + k] = ct[c].normal[k];
+      }
+      cpen[e * nk + c] = ct[c].pen;
+    }
+  }
+  return 0;
+}
+
 #ifdef BXO_COUNT
 /* C-linkage entry of the counting build (oracle/count_flops.py) */
 extern "C" int bxo_step_count(const osys* s, int64_t num_envs, const oio* io) {

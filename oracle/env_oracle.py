@@ -269,15 +269,18 @@ def wrapped_step(desc, env, oracle, qp, done_in, steps_in, act, first_qp, first_
 def reset_obs(desc, env, oracle, qp, dtype=np.float32, contact_vel=None, contact_ang=None):
   """The obs of `Env.reset`: `_get_obs(qp, info)` of a state (envs/ant.py:203-204,
   envs/humanoid.py:230-231 with a zero action, envs/fetch.py:41-42, envs/grasp.py:60-61) with the
-  given `info.contact` (default: zeros -- what the fused "observe" launch uses; the reference's
-  `sys.info(qp)`, system.py:327-340, evaluates the spring-style contact impulse of the resting
-  pose, which is zero unless a collider sits in the plane moving downwards).  oracle: the C
-  physics oracle of the same dtype (for Joint.angle_vel)."""
+  given `info.contact` (default: that of the reference's `sys.info(qp)`, system.py:327-340 -- the
+  spring-style contact impulse of the pose, `Oracle.info_contact`; zero unless a collider sits in
+  the plane moving downwards).  oracle: the C physics oracle of the same dtype (Joint.angle_vel,
+  info_contact)."""
   b, n = qp['pos'].shape[0], qp['pos'].shape[1]
-  z = np.zeros((b, n, 3), dtype)
   out = {k: np.asarray(qp[k], dtype) for k in ('pos', 'rot', 'vel', 'ang')}
-  out['contact_vel'] = z if contact_vel is None else np.asarray(contact_vel, dtype)
-  out['contact_ang'] = z if contact_ang is None else np.asarray(contact_ang, dtype)
+  if contact_vel is None or contact_ang is None:
+    ic = oracle.info_contact(out['pos'], out['rot'], out['vel'], out['ang'])   # sys.info(qp).contact
+    contact_vel = ic['contact_vel'] if contact_vel is None else contact_vel
+    contact_ang = ic['contact_ang'] if contact_ang is None else contact_ang
+  out['contact_vel'] = np.asarray(contact_vel, dtype)
+  out['contact_ang'] = np.asarray(contact_ang, dtype)
   fa, fv = flat_angle_vel(desc, *oracle.angle_vel(out['rot'], out['ang']))
   act = np.zeros((b, desc.act_size), dtype)
   if env.kind == 'grasp':     # the epilogue is given the raw action; zeros map to mid-range, unused by the obs

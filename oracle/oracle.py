@@ -229,6 +229,29 @@ class Oracle:
       raise RuntimeError('bxo_angle_vel failed')
     return angle, vel
 
+  def info_contact(self, pos, rot, vel, ang):
+    """`System.info(qp)` (system.py:327-340 / :378-390): info.contact (vel, ang) [B,N,3] -- the summed
+    `Collider.apply(qp)` of all colliders, in both dynamics modes -- and contact_pos / contact_normal
+    [B,K,3], contact_penetration [B,K]."""
+    d, dt = self.desc, self.dtype
+    n, k = d.num_bodies, d.num_contacts
+    pos = np.ascontiguousarray(np.asarray(pos, dtype=dt).reshape(-1, n, 3))
+    b = pos.shape[0]
+    rot = np.ascontiguousarray(np.asarray(rot, dtype=dt).reshape(b, n, 4))
+    vel = np.ascontiguousarray(np.asarray(vel, dtype=dt).reshape(b, n, 3))
+    ang = np.ascontiguousarray(np.asarray(ang, dtype=dt).reshape(b, n, 3))
+    out = {'contact_vel': np.zeros((b, n, 3), dt), 'contact_ang': np.zeros((b, n, 3), dt),
+           'contact_pos': np.zeros((b, k, 3), dt), 'contact_normal': np.zeros((b, k, 3), dt),
+           'contact_penetration': np.zeros((b, k), dt)}
+    fn = getattr(self._lib, 'bxo_info_contact' + ('_f32' if dt == np.float32 else '_f64'))
+    fn.restype = C.c_int
+    rc = fn(C.byref(self._sys), C.c_int64(b), *[C.c_void_p(x.ctypes.data) for x in (pos, rot, vel, ang)],
+            *[C.c_void_p(out[key].ctypes.data) for key in ('contact_vel', 'contact_ang', 'contact_pos',
+                                                           'contact_normal', 'contact_penetration')])
+    if rc != 0:
+      raise RuntimeError('bxo_info_contact failed')
+    return out
+
   def step(self, pos, rot, vel, ang, act, num_threads: int = 0):
     """One batched step.  Inputs [B,N,3|4|3|3], [B,A] (or unbatched)."""
     d, dt = self.desc, self.dtype

@@ -177,3 +177,21 @@ def test_product_does_not_import_oracle():
         text = open(os.path.join(dp, f)).read()
         assert not re.search(r'^\s*(from|import)\s+oracle', text, re.M), f
         assert 'liboracle' not in text, f
+
+
+def test_xla_ffi_handler_is_a_real_source_and_its_build_is_gated():
+  """The JAX side of the boundary exists as source (csrc/bx_ffi.cc + jax_ffi.py) and its build step is
+  skipped with a printed reason where jaxlib's headers are missing (this box: no jax, no network)."""
+  src = open(os.path.join(os.path.dirname(bx_build.CSRC), 'csrc', 'bx_ffi.cc')).read()
+  assert 'XLA_FFI_DEFINE_HANDLER_SYMBOL(bx_step_ffi' in src and src.count('.Ret<F32>()') == 13 and src.count('.Arg<F32>()') == 5
+  import brax_b200.jax_ffi as jf   # imports without jax
+  try:
+    import jax  # noqa: F401
+    have = True
+  except Exception:
+    have = False
+  out = bx_build.build_ffi(verbose=False)
+  assert (out is not None) == have
+  if not have:
+    with pytest.raises(Exception):
+      jf.register()

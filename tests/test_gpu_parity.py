@@ -509,6 +509,41 @@ def test_host_path_pinned_buffers_and_chunking():
       assert d2h == 4 * b * (31 * n + 7 * kk - 9 * n)
 
 
+def test_dlpack_and_cuda_array_interface_inputs():
+  """System.step takes any DLPack producer (`__dlpack__`: a JAX or CuPy array) or CUDA-array-interface
+  object zero-copy -- the DLPack hop of brax/io/torch.py:48-53 -- with the same result as torch tensors;
+  the outputs are torch tensors and export through DLPack themselves."""
+  torch = _torch()
+  from brax_b200.system import QP
+  s = _system('ant')
+
+  class OnlyDLPack:           # what a jax.Array offers: __dlpack__ / __dlpack_device__, nothing of torch
+    def __init__(self, t):
+      self._t = t
+
+    def __dlpack__(self, stream=None, **kw):
+      return self._t.__dlpack__(stream=stream) if stream is not None else self._t.__dlpack__()
+
+    def __dlpack_device__(self):
+      return self._t.__dlpack_device__()
+
+  class OnlyCAI:              # what a Numba device array offers
+    def __init__(self, t):
+      self._t = t
+      self.__cuda_array_interface__ = t.__cuda_array_interface__
+
+  qp, rng = _harvest(s, 300, 3, 31)
+  act = torch.from_numpy(rng.uniform(-1, 1, (300, s.act_size)).astype(np.float32)).cuda()
+  want = _flat(*s.step(qp, act))
+  for wrap in (OnlyDLPack, OnlyCAI):
+    got = _flat(*s.step(QP(*[wrap(getattr(qp, k)) for k in util.QP_KEYS]), wrap(act)))
+    for k in want:
+      np.testing.assert_array_equal(got[k], want[k], err_msg='%s %s' % (wrap.__name__, k))
+  out, _ = s.step(qp, act)
+  back = torch.from_dlpack(out.pos.__dlpack__())
+  assert back.data_ptr() == out.pos.data_ptr()
+
+
 def test_host_path_async_groups_equal_sync_calls():
   """bx_step_host_async / bx_host_wait: two independent env groups stepped through two slots,
   three chained steps each, interleaved -- bitwise the synchronous bx_step_host results; pageable

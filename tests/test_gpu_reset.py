@@ -75,11 +75,82 @@ def test_default_qp_argument_errors():
     s.default_qp(joint_angle=torch.zeros(4, s.num_joint_dof + 1).cuda())
 
 
+def _touching(desc, ins):
+  """Envs with a contact row whose penetration is within rounding of zero (a collider resting exactly ON
+  the plane, as after default_qp's lowering): `penetration > 0` -- and with it the whole contact impulse
+  of System.info(qp), colliders.py:131-133 -- is a coin flip per float32 evaluation, in the reference too."""
+  from oracle.oracle import Oracle
+  pen = Oracle(desc, np.float64).info_contact(ins['pos'], ins['rot'], ins['vel'], ins['ang'])['contact_penetration']
+  return (np.abs(pen) < 1e-5).any(axis=1) if pen.size else np.zeros(ins['pos'].shape[0], bool)
+
+
+def _contact_block(env, desc):
+  """Indices of the obs entries that read info.contact: ant's clipped contact forces (ant.py:271-279),
+  fetch / grasp's contact flags (fetch.py:116-117, grasp.py:176-178); humanoid's obs reads none."""
+  n, o = desc.num_bodies, env.obs_size(desc)
+  if env.kind == 'ant':
+    return np.arange(o - 6 * n, o) if env.use_contact_forces else np.arange(0)
+  if env.kind in ('fetch', 'grasp'):
+    return np.arange(o - n, o)
+  return np.arange(0)
+
+
+def _obs_close(obs, want, tol, touching, block):
+  """Equal to the obs built on sys.info(qp), except that a `touching` env's contact entries are exempt
+  (each of its resting contacts may be decided either way by either evaluation)."""
+  ok = np.abs(obs - want) <= tol
+  exempt = np.zeros_like(ok)
+  exempt[np.ix_(np.nonzero(touching)[0], block)] = True
+  return ok | exempt
+
+
+@pytest.mark.parametrize('variant,b,steps', [('ant', 1024, 25), ('ant_spring', 1024, 25), ('humanoid', 1024, 25),
+                                             ('fetch', 1024, 15), ('grasp', 1024, 15)])
+def test_observe_info_matches_oracle_on_moving_states(variant, b, steps):
+  """System.info(qp) (system.py:327-340 / :378-390) as the observe launch evaluates it: info.contact and
+  the contact rows on states taken mid-simulation (bodies pressing into the ground with velocity, so the
+  contacts are decided well away from rounding) against the oracle's `info_contact`, pinned to the
+  reference's sys.info(qp) by tests/test_env_oracle.py."""
+  torch = _torch()
+  from oracle.oracle import Oracle
+  from tests.test_gpu_env import _env
+  from tests.test_gpu_parity import _harvest
+  sysname, env = _env(variant)
+  qp, _ = _harvest(env.sys, b, steps, 17)
+  # a step leaves its contacts resolved (normal velocity >= 0: no impulse): push the free bodies down
+  free = torch.tensor([float(min(x['pos_mask'])) for x in env.sys.desc.bodies], device='cuda')
+  vel = qp.vel.clone()
+  vel[..., 2] -= 0.3 * free
+  qp = type(qp)(qp.pos, qp.rot, vel, qp.ang)
+  _, info, eo = env.sys._step_torch(qp, torch.zeros(b, env.action_size).cuda(), 1, False, True, None, None, True,
+                                    observe=True)
+  ins = {k: getattr(qp, k).cpu().numpy() for k in util.QP_KEYS}
+  o32 = Oracle(env.sys.desc, np.float32).info_contact(ins['pos'], ins['rot'], ins['vel'], ins['ang'])
+  o64 = Oracle(env.sys.desc, np.float64).info_contact(ins['pos'], ins['rot'], ins['vel'], ins['ang'])
+  got = {'contact_vel': info.contact.vel, 'contact_ang': info.contact.ang, 'contact_pos': info.contact_pos,
+         'contact_normal': info.contact_normal, 'contact_penetration': info.contact_penetration}
+  live = np.abs(o32['contact_vel']).reshape(b, -1).max(axis=1) > 0
+  assert live.mean() > 0.05, live.mean()                 # the impulse is exercised
+  edge = (np.abs(o64['contact_penetration']) < 1e-5).any(axis=1)   # envs with a contact at rounding of 0
+  bad = np.zeros(b, bool)
+  for k, v in got.items():
+    g = v.cpu().numpy()
+    assert np.isfinite(g).all(), k
+    tol = 2e-6 + 1e-5 * np.abs(o32[k]) + 4 * np.abs(o32[k] - o64[k])
+    if k in ('contact_vel', 'contact_ang'):
+      tol = tol + 1e-5 * np.abs(o32[k]).reshape(b, -1).max(axis=1).reshape((b,) + (1,) * (g.ndim - 1))
+    bad |= (np.abs(g - o32[k]) > tol).reshape(b, -1).any(axis=1)
+  assert (bad & ~edge).sum() <= int(0.005 * b), int((bad & ~edge).sum())
+  flags = (got['contact_penetration'].cpu().numpy() > 0) == (o32['contact_penetration'] > 0)
+  assert (flags | (np.abs(o32['contact_penetration']) < 1e-6)).all()
+
+
 @pytest.mark.parametrize('variant', ['ant', 'ant_spring', 'humanoid', 'humanoid_spring', 'fetch', 'grasp'])
 def test_observe_matches_reference_reset_obs(variant):
-  """System.observe (the env epilogue without substeps, zero Info) on the golden reset states
-  against the obs of the reference's own `_get_obs(qp, sys.info(qp))` (reset_obs.npz), wherever
-  the reference's info.contact is zero, and against the float32 oracle everywhere."""
+  """System.observe (the env epilogue without substeps, on `sys.info(qp)` of the state) on the golden
+  reset states against the obs of the reference's own `_get_obs(qp, sys.info(qp))` (reset_obs.npz)
+  on EVERY draw -- including the humanoid / fetch draws whose info.contact is non-zero -- and against
+  the float32 oracle."""
   torch = _torch()
   from oracle import env_oracle
   from oracle.oracle import Oracle
@@ -95,9 +166,15 @@ def test_observe_matches_reference_reset_obs(variant):
   # 1e-5 relative + the float32 conditioning of the obs terms that cancel (humanoid's com_ang)
   w64 = env_oracle.reset_obs(env.sys.desc, env.env, Oracle(env.sys.desc, np.float64), ins, np.float64)
   tol = 5e-6 + 1e-5 * np.abs(want) + 4 * np.abs(want - w64)
-  assert (np.abs(obs - want) <= tol).all(), float((np.abs(obs - want) - tol).max())
-  quiet = (np.abs(go[variant + '/contact_vel']).max(axis=(1, 2)) == 0) | (env.env.kind == 'humanoid')
-  np.testing.assert_allclose(obs[quiet], go[variant + '/obs'][quiet], rtol=1e-5, atol=2e-5)
+  touching = _touching(env.sys.desc, ins)
+  block = _contact_block(env.env, env.sys.desc)
+  assert _obs_close(obs, want, tol, touching, block).all()
+  # ... and the reference's own obs (float64), on every draw.  After default_qp the lowest collider of
+  # every reset state rests exactly ON the plane, so whether that contact counts is rounding-level in
+  # the reference itself; the contact entries of such states are compared on moving states instead
+  # (test_observe_info_matches_oracle_on_moving_states).
+  ref = go[variant + '/obs']
+  assert _obs_close(obs, ref, 2e-5 + 1e-5 * np.abs(ref), touching, block).all()
   # the state passes through untouched; unbatched call == row 2
   q2, _, eo = env.sys._step_torch(qp, torch.zeros(obs.shape[0], env.action_size).cuda(), 1, False, True, None, None,
                                   False, observe=True)
@@ -145,7 +222,7 @@ def test_env_reset_on_the_gpu(variant):
   wobs = env_oracle.reset_obs(desc, env.env, Oracle(desc, np.float32), ins, np.float32)
   w64 = env_oracle.reset_obs(desc, env.env, Oracle(desc, np.float64), ins, np.float64)
   tol = 5e-6 + 1e-5 * np.abs(wobs) + 4 * np.abs(wobs - w64)
-  assert (np.abs(st.obs.cpu().numpy() - wobs) <= tol).all()
+  assert _obs_close(st.obs.cpu().numpy(), wobs, tol, _touching(desc, ins), _contact_block(env.env, desc)).all()
   # caller-supplied joint state; unbatched reset
   st3 = env.reset(b, device='cuda', joint_angle=ja, joint_velocity=jv)
   np.testing.assert_allclose(st3.qp.rot.cpu().numpy(), want['rot'], rtol=1e-5, atol=3e-6)
