@@ -48,7 +48,9 @@ NCU_TRAFFIC = {
     # env: (bytes per launch, capture under profiles/).  Reads + writes seen at DRAM by one launch of the
     # bench workload under ncu (--set full, cache control on: the outputs of a launch stay in the 126 MB L2
     # until a later launch evicts them, so the figure is dominated by the cold input reads).
-    'ant': (4592128, 'profiles/r01_ncu_full_ant8192_step_kernel.csv'),
+    'ant': (4591616, 'profiles/r02_ncu_full_ant_step_kernel.csv (ant 8192 envs)'),
+    'humanoid': (5748992, 'profiles/r02_ncu_full_humanoid_step_kernel.csv (humanoid 8192 envs)'),
+    'grasp': (4142848, 'profiles/r02_ncu_full_grasp_step_kernel.csv (grasp 4096 envs)'),
 }
 FP32_LANES = 128
 
@@ -309,7 +311,7 @@ def config_entry(info, desc, world, ms, ms_roll, ms_env, hbm_gbs, sm_max_mhz):
       'roofline': {'bound': 'hbm', 'achieved': per_gpu * desc.bytes_per_env_step() / 1e9, 'peak': hbm_gbs, 'unit': 'GB/s',
                    'frac': per_gpu * desc.bytes_per_env_step() / 1e9 / hbm_gbs,
                    'bytes_per_env_step': desc.bytes_per_env_step(),
-                   'traffic': NCU_TRAFFIC.get(info['env'], (None, None))[0] if b == 8192 or info['env'] == 'grasp' else None,
+                   'traffic': NCU_TRAFFIC.get(info['env'], (None, None))[0] if b == (4096 if info['env'] == 'grasp' else 8192) else None,
                    'traffic_source': NCU_TRAFFIC.get(info['env'], (None, 'no ncu --set full capture committed'))[1]},
       'roofline_fp32': ({'bound': 'fp32', 'achieved': per_gpu * flops['flops'] / 1e12, 'peak': peak, 'unit': 'TFLOP/s',
                          'frac': per_gpu * flops['flops'] / 1e12 / peak, 'flops_per_env_step': flops['flops']} if flops else None),
@@ -319,6 +321,69 @@ def config_entry(info, desc, world, ms, ms_roll, ms_env, hbm_gbs, sm_max_mhz):
   })
   return out
 
+
+
+def run_sweep(args, desc):
+  """BASELINE config 5: `--sweep B1,B2,...` = TOTAL batch sizes split over the ranks (contiguous env
+  blocks, brax_b200.shard): per point the chunked-event device time of `--steps` steps, max over ranks;
+  rank 0 prints ONE JSON line whose `sweep` holds every point (env-steps/s and roofline fractions)."""
+  import torch
+  import torch.distributed as dist
+  from brax_b200 import shard
+  from brax_b200.system import QP, System
+  world = int(os.environ.get('WORLD_SIZE', '1'))
+  rank = int(os.environ.get('RANK', '0'))
+  local = int(os.environ.get('LOCAL_RANK', '0'))
+  if world > 1:
+    dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+  torch.cuda.set_device(local)
+  dev = torch.device('cuda', local)
+  s = System(desc, device=local)
+
+  def sync():
+    if world > 1:
+      dist.barrier()
+    torch.cuda.synchronize()
+
+  hbm_gbs, sm_max_mhz, _ = load_peaks()
+  flops = load_flops(args.env)
+  peak = SM_COUNT * FP32_LANES * 2 * sm_max_mhz * 1e6 / 1e12
+  points = []
+  with ClockSampler(local) as clk:
+    for total in [int(x) for x in args.sweep.split(',')]:
+      lo, hi = shard.shard_range(total, world, rank)
+      b = hi - lo
+      ms = 0.0
+      if b > 0:
+        bytes_set = b * desc.bytes_per_env_step()
+        nsets = min(32, max(2, -(-2 * L2_BYTES // bytes_set)))
+        base = QP(*[torch.from_numpy(x).to(dev) for x in make_state(desc, b, 500 + rank)])
+        qps = [QP(base.pos.clone(), base.rot.clone(), base.vel.clone(), base.ang.clone()) for _ in range(nsets)]
+        acts = torch.rand((16, b, desc.act_size), device=dev) * 2 - 1
+        for i in range(max(args.warmup, nsets)):
+          qps[i % nsets], _ = s.step(qps[i % nsets], acts[i % 16])
+        sync()
+
+        def step_i(i):
+          j = i % nsets
+          qps[j], _ = s.step(qps[j], acts[i % 16])
+        ms = timed_chunks(torch, args.steps, step_i, sync)
+        del qps, base, acts
+      else:
+        sync()
+        sync()
+      (ms,) = shard.reduce_stats([ms], ['max'], device=dev)
+      v = total * args.steps / (ms * 1e-3)
+      points.append({'total_envs': total, 'envs_per_gpu': -(-total // world), 'value': v, 'ms_per_step': ms / args.steps,
+                     'fp32_frac': (v / world * flops['flops'] / 1e12 / peak) if flops else None,
+                     'hbm_frac': v / world * desc.bytes_per_env_step() / 1e9 / hbm_gbs})
+  if rank == 0:
+    print(json.dumps({'metric': METRIC, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
+                      'scaling': 'strong per point (total batch split over the ranks)', 'dtype': 'f32', 'data': 'synthetic',
+                      'config': {'workload': '%s batch sweep, total envs over %d GPU(s), default substeps' % (args.env, world)},
+                      'sweep': points, 'clocks': clk.summary()}))
+  if world > 1:
+    dist.destroy_process_group()
 
 
 def run_reference(args, desc):
@@ -828,11 +893,14 @@ def main():
   ap.add_argument('--cpu-seconds', type=float, default=12.0)
   ap.add_argument('--no-cpu', action='store_true')
   ap.add_argument('--no-e2e', action='store_true')
+  ap.add_argument('--sweep', default='', help='comma-separated TOTAL batch sizes (BASELINE config 5), split over the ranks')
   ap.add_argument('--no-configs', action='store_true', help='skip the secondary BASELINE configs')
   args = ap.parse_args()
   from brax_b200.desc import SystemDesc
   desc = SystemDesc.load(os.path.join(ROOT, 'brax_b200', 'systems', args.env + '.json'))
-  if args.impl == 'reference':
+  if args.sweep and args.impl != 'reference':
+    run_sweep(args, desc)
+  elif args.impl == 'reference':
     run_reference(args, desc)
   else:
     run_gpu(args, desc)
