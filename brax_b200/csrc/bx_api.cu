@@ -116,15 +116,18 @@ static int validate(const bx_system_desc* d) {
   int k = 0;
   for (int i = 0; i < d->num_pairs; i++) {
     const bx_pair& p = d->pairs[i];
-    if (p.kind < BX_PAIR_CAPSULE_PLANE || p.kind > BX_PAIR_BOX_PLANE)
-      return fail("unsupported collider pair kind (mesh/heightmap/clipped-plane/box-box are out of scope)");
+    if (p.kind < BX_PAIR_CAPSULE_PLANE || p.kind > BX_PAIR_CAPSULE_BOX)
+      return fail("unsupported collider pair kind (general mesh/heightmap/clipped-plane/box-box are out of scope)");
     if (p.body_a < 0 || p.body_a >= d->num_bodies || p.body_b < 0 || p.body_b >= d->num_bodies)
       return fail("pair body index out of range");
     if (p.group < 0 || p.group >= BX_MAX_GROUPS) return fail("pair group out of range");
     if (i > 0 && p.group < d->pairs[i - 1].group) return fail("pairs must be sorted by group");
-    if (p.n_contacts < 1 || p.n_contacts > 8) return fail("pair n_contacts out of range");
+    if (p.n_contacts < 1 || p.n_contacts > 12) return fail("pair n_contacts out of range");
+    if (p.kind != BX_PAIR_CAPSULE_BOX && p.n_contacts > 8) return fail("pair n_contacts out of range");
     if (p.kind == BX_PAIR_CAPSULE_CAPSULE && p.n_contacts != 1) return fail("capsule_capsule has 1 contact");
-    if (p.kind != BX_PAIR_CAPSULE_CAPSULE && p.two_way) return fail("two-way plane colliders do not exist");
+    if (p.kind == BX_PAIR_CAPSULE_BOX && p.n_contacts != 12) return fail("capsule_box has 12 contacts (one per triangle)");
+    if (p.kind != BX_PAIR_CAPSULE_CAPSULE && p.kind != BX_PAIR_CAPSULE_BOX && p.two_way)
+      return fail("two-way plane colliders do not exist");
     k += p.n_contacts;
   }
   if (k > BX_MAX_CONTACTS) return fail("too many contact rows");
@@ -206,6 +209,16 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     for (int c = 0; c < d->pairs[i].n_contacts; c++) rows.push_back({i, c});
   const int nk = static_cast<int>(rows.size());
   h.nk = nk;
+  // row of the contact NORMAL of contact row k: one per collider pair (all rows of a plane pair share
+  // the plane's normal; capsule_capsule has one row), one per ROW for capsule_box (a normal per triangle)
+  std::vector<int> normal_row(nk, 0), tri_index(nk, -1);
+  int n_normals = 0, n_tris = 0;
+  for (int k = 0; k < nk; k++) {
+    const bool per_row = d->pairs[rows[k].pair].kind == BX_PAIR_CAPSULE_BOX;
+    if (per_row || k == 0 || rows[k].pair != rows[k - 1].pair) n_normals++;
+    normal_row[k] = n_normals - 1;
+    if (per_row) tri_index[k] = n_tris++;
+  }
   // contact items: up to rows_per_item consecutive rows of one pair share one
   // slot-list entry per side
   std::vector<int> item_k0, item_n, item_of(nk, 0);
@@ -274,7 +287,7 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
   for (int k = 0; k < nk; k++) {
     const bx_pair& p = d->pairs[rows[k].pair];
     quad(p.friction, p.elasticity, p.radius_a, p.radius_b);
-    if (p.kind == BX_PAIR_CAPSULE_CAPSULE) {
+    if (p.kind == BX_PAIR_CAPSULE_CAPSULE || p.kind == BX_PAIR_CAPSULE_BOX) {
       for (int q = 0; q < 4; q++) quad(p.pts[q][0], p.pts[q][1], p.pts[q][2], 0.f);
     } else {
       const float* pt = p.pts[rows[k].c];
@@ -282,6 +295,15 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
       for (int q = 0; q < 3; q++) quad(0.f, 0.f, 0.f, 0.f);
     }
   }
+  // capsule_box rows: {p0, p1, p2, normal} of the row's triangle (body-b frame), 4 quads each
+  h.fo_tri = nquads();
+  for (int k = 0; k < nk; k++)
+    if (tri_index[k] >= 0) {
+      const bx_pair& p = d->pairs[rows[k].pair];
+      const int f = rows[k].c;
+      for (int v = 0; v < 3; v++) quad(p.tri[f][v][0], p.tri[f][v][1], p.tri[f][v][2], 0.f);
+      quad(p.tri_normal[f][0], p.tri_normal[f][1], p.tri_normal[f][2], 0.f);
+    }
   if (d->env && d->env->kind == BX_ENV_GRASP) {  // action map: min quads, then range quads
     h.fo_envact = nquads();
     const int nq = (d->act_size + 3) / 4;
@@ -365,7 +387,7 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
   }
   int js = std::max(std::max(t_quads, j_quads), c_quads);
   const int cd_rows = spring ? 0 : (nk + 3) / 4;
-  const int ct_rows = nk + d->num_pairs + cd_rows;
+  const int ct_rows = nk + n_normals + cd_rows;
   {
     // region JS doubles as the staging buffer of the bulk-copy I/O: it must hold
     // the largest output span of a tile, and JS..end must hold all input spans.
@@ -390,7 +412,7 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
   h.q_act = r; r += (d->act_size + 3) / 4;
   h.q_js = r; r += js;
   h.q_ct = r; r += nk;
-  h.q_cn = r; r += d->num_pairs;
+  h.q_cn = r; r += n_normals;
   h.q_cd = r; r += cd_rows;
   h.q_pre = r; r += spring ? 0 : 2 * ncb;
   h.q_ic = r; r += 2 * ncb;   // q_ic, q_ia, q_ij contiguous: zeroed together
@@ -461,7 +483,7 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     const bx_pair& p = d->pairs[rows[k].pair];
     ti.push_back(p.kind); ti.push_back(p.two_way); ti.push_back(p.body_a);
     ti.push_back(p.body_b); ti.push_back(cslot_a[item_of[k]]); ti.push_back(cslot_b[item_of[k]]);
-    ti.push_back(rows[k].pair); ti.push_back(0);
+    ti.push_back(normal_row[k]); ti.push_back(tri_index[k] < 0 ? 0 : 4 * tri_index[k]);
   }
   h.io_citem = static_cast<int>(ti.size());
   for (int i = 0; i < nci; i++) { ti.push_back(item_k0[i]); ti.push_back(item_n[i]); }
@@ -530,7 +552,7 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     for (int k = 0; k < nk; k++) {
       for (int x = 0; x < 3; x++) {
         mp.push_back((h.q_ct + k) * RF + x);
-        mn.push_back((h.q_cn + rows[k].pair) * RF + x);
+        mn.push_back((h.q_cn + normal_row[k]) * RF + x);
       }
       me.push_back((h.q_ct + k) * RF + 3);
     }
@@ -759,14 +781,16 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
     for (int b = 0; b < desc->num_bodies; b++) contact_bodies += rows_of[b] > 0;
     s->fusable = desc->dynamics_mode == BX_MODE_PBD && max_rows <= 2;
     for (int i = 0; i < desc->num_pairs; i++)
-      if (desc->pairs[i].two_way || desc->pairs[i].kind == BX_PAIR_CAPSULE_CAPSULE) {
-        s->cc = BX_CC_ALL;
+      if (desc->pairs[i].two_way || desc->pairs[i].kind == BX_PAIR_CAPSULE_CAPSULE ||
+          desc->pairs[i].kind == BX_PAIR_CAPSULE_BOX) {
+        if (s->cc != BX_CC_MESH) s->cc = BX_CC_ALL;
+        if (desc->pairs[i].kind == BX_PAIR_CAPSULE_BOX) s->cc = BX_CC_MESH;
         s->fusable = false;
       }
     // Measured (profiles/r01_sweeps.txt): the fused section wins when the chains
     // leave warps free (ant: 4 of 10 bodies collide, +2.5%) and loses when nearly
     // every body carries one (humanoid, -1%); bx_system_autotune times both.
-    if (s->cc != BX_CC_ALL)
+    if (s->cc != BX_CC_ALL && s->cc != BX_CC_MESH)
       s->cc = (s->fusable && 2 * contact_bodies <= desc->num_bodies) ? BX_CC_PLANE_FUSED : BX_CC_PLANE;
   }
   s->device = device;
@@ -881,7 +905,7 @@ extern "C" int bx_system_configure(bx_system* s, int32_t threads_per_block, int3
   if (contact_section == 2 && !s->fusable)
     return fail("fused contact section needs pbd, one-way plane colliders, <= 2 rows per body");
   if (threads_per_block) s->warps = threads_per_block / 32;
-  if (contact_section && s->cc != BX_CC_ALL)
+  if (contact_section && s->cc != BX_CC_ALL && s->cc != BX_CC_MESH)
     s->cc = contact_section == 2 ? BX_CC_PLANE_FUSED : BX_CC_PLANE;
   return 0;
 }

@@ -24,10 +24,15 @@ static bx_kernel_fn pick(int jc, int cc) {
     if (jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC0 | BXF_FUSED_CONTACTS);
     return BX_K(BXF_JC2, BXF_CC0 | BXF_FUSED_CONTACTS);
   }
-  if (cc != BX_CC_ALL) {
+  if (cc != BX_CC_ALL && cc != BX_CC_MESH) {
     if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC0);
     if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC0);
     return BX_K(BXF_JC2, BXF_CC0);
+  }
+  if (cc == BX_CC_MESH) {
+    if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC2);
+    if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC2);
+    return BX_K(BXF_JC2, BXF_CC2);
   }
   if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC1);
   if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC1);

@@ -43,6 +43,7 @@ enum {
   BXF_TORQUE = 256, BXF_ANGLE = 512, BXF_FORCES = 1024,
   BXF_FUSED_CONTACTS = 2048,  // pbd, one-way colliders, <= 2 rows per body
   BXF_ENV = 4096,             // env epilogue compiled in (systems created with desc.env)
+  BXF_CAPSULE_BOX = 8192,     // capsule against a triangulated box (capsule_mesh, colliders.py:822-849)
   BXF_ALL = 2047
 };
 #define BX_CC_ENV 8  // or-ed into the contact class passed to bx_launch_*: env-epilogue build
@@ -51,18 +52,20 @@ enum {
 // griddepcontrol.wait while the previous kernel of the stream drains
 #define BX_CC_PDL 16
 // Kernel variants are instantiated per (dynamics mode, joint class, contact
-// class, launch bound).  Classes are the feature sets of the reference's envs:
+// class, launch bound).  Classes are the feature sets of the reference's envs (BX_CC_MESH: the
+// round-2 capsule-box collider on top of everything):
 // all-revolute (ant, fetch), all-spherical (humanoid, grasp: joints.py:418-474
 // "sphericalize"), anything; plane contacts only (one-way capsule/box vs plane)
 // or everything.
 enum { BX_JC_REVOLUTE = 0, BX_JC_SPHERICAL = 1, BX_JC_ALL = 2, BX_NUM_JC = 3 };
-enum { BX_CC_PLANE_FUSED = 0, BX_CC_PLANE = 1, BX_CC_ALL = 2, BX_NUM_CC = 3 };
+enum { BX_CC_PLANE_FUSED = 0, BX_CC_PLANE = 1, BX_CC_ALL = 2, BX_CC_MESH = 3, BX_NUM_CC = 4 };
 #define BXF_COMMON (BXF_TORQUE | BXF_ANGLE | BXF_FORCES)
 #define BXF_JC0 BXF_REVOLUTE
 #define BXF_JC1 BXF_SPHERICAL
 #define BXF_JC2 (BXF_REVOLUTE | BXF_SPHERICAL | BXF_UNIVERSAL)
 #define BXF_CC0 (BXF_ONE_WAY | BXF_CAPSULE_PLANE | BXF_BOX_PLANE)
 #define BXF_CC1 (BXF_ONE_WAY | BXF_TWO_WAY | BXF_CAPSULE_PLANE | BXF_CAPSULE_CAPSULE | BXF_BOX_PLANE)
+#define BXF_CC2 (BXF_CC1 | BXF_CAPSULE_BOX)  // ... and capsule against a triangulated box
 
 // One translation unit per launch bound (bx_kernels.cu compiled with
 // -DBX_TU_MAXT=.. -DBX_TU_MINB=..) exports these two functions.

@@ -736,6 +736,60 @@ BXS void closest_seg_seg(V3 a0, V3 a1, V3 b0, V3 b1, V3* best_a, V3* best_b) {
   *best_b = first ? bb : nb;
 }
 
+// geometry.py:377-391
+BXS V3 closest_segment_point_plane(V3 a, V3 b, V3 p0, V3 n) {
+  const V3 ab = b - a;
+  const float t = bx_div(dot(p0, n) - dot(n, a), dot(n, ab) + 1e-6f);
+  return a + clipf(t, 0.f, 1.f) * ab;
+}
+// geometry.py:462-500
+BXS V3 closest_triangle_point(V3 p0, V3 p1, V3 p2, V3 pt) {
+  const V3 e0 = p1 - p0, e1 = p2 - p0, d = pt - p0;
+  const float a = dot(e0, e0), b = dot(e0, e1), cc = dot(e1, e1);
+  const float rdet = bx_rcp(a * cc - b * b);
+  const float u = (cc * dot(e0, d) - b * dot(e1, d)) * rdet;
+  const float v = (-b * dot(e0, d) + a * dot(e1, d)) * rdet;
+  const bool inside = 0.f <= u && u <= 1.f && 0.f <= v && v <= 1.f && u + v <= 1.f;
+  V3 cp = p0 + u * e0 + v * e1;
+  const V3 df = cp - pt;
+  const float d0 = dot(df, df);
+  float d1, d2, d3;
+  const V3 c1 = closest_segment_point_and_dist(p0, p1, pt, &d1);
+  const bool take0 = d0 < d1 && inside;
+  cp = take0 ? cp : c1;
+  float min_d = take0 ? d0 : d1;
+  const V3 c2 = closest_segment_point_and_dist(p1, p2, pt, &d2);
+  cp = d2 < min_d ? c2 : cp;
+  min_d = fminf(min_d, d2);
+  const V3 c3 = closest_segment_point_and_dist(p2, p0, pt, &d3);
+  return d3 < min_d ? c3 : cp;
+}
+// geometry.py:503-540: the closest of the three edge candidates and the in-triangle candidate;
+// candidates that tie are averaged (mask = distance == min; sum * mask / sum(mask))
+BXS void closest_segment_triangle_points(V3 a, V3 b, V3 p0, V3 p1, V3 p2, V3 tn, V3* seg_pt, V3* tri_pt) {
+  V3 sp[4], tp[4];
+  float dd[4];
+  closest_seg_seg(a, b, p0, p1, &sp[0], &tp[0]);
+  closest_seg_seg(a, b, p1, p2, &sp[1], &tp[1]);
+  closest_seg_seg(a, b, p0, p2, &sp[2], &tp[2]);
+  sp[3] = closest_segment_point_plane(a, b, p0, tn);
+  tp[3] = closest_triangle_point(p0, p1, p2, sp[3]);
+#pragma unroll
+  for (int i = 0; i < 4; i++) { const V3 v = sp[i] - tp[i]; dd[i] = dot(v, v); }
+  const float mn = fminf(fminf(dd[0], dd[1]), fminf(dd[2], dd[3]));
+  V3 ss = v3(0.f, 0.f, 0.f), ts = ss;
+  float cnt = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const float m = dd[i] == mn ? 1.f : 0.f;
+    cnt += m;
+    ss = ss + sp[i] * m;
+    ts = ts + tp[i] * m;
+  }
+  *seg_pt = vdiv(ss, cnt);
+  *tri_pt = vdiv(ts, cnt);
+}
+
 BXS float w_of(float inv_mass, V3 inv_i, V3 r, V3 n) {
   V3 cr = cross(r, n);
   return inv_mass + dot(cr, inv_i * cr);
@@ -743,10 +797,26 @@ BXS float w_of(float inv_mass, V3 inv_i, V3 r, V3 n) {
 
 // contact function of one contact row (colliders.py:667-680 box_plane,
 // :744-759 capsule_plane, :805-819 capsule_capsule).
-BXS Contact contact_fn(int kind, const float4* cq, V3 pa, Q4 ra, V3 va, V3 wa, V3 pb, Q4 rb,
+BXS Contact contact_fn(int kind, const float4* cq, const float4* tq, V3 pa, Q4 ra, V3 va, V3 wa, V3 pb, Q4 rb,
                        V3 vb, V3 wb) {
   Contact ct;
   const float4 mat = cq[CQ_MAT];
+  if ((BX_FEAT & BXF_CAPSULE_BOX) && kind == BX_PAIR_CAPSULE_BOX) {
+    // capsule_mesh (colliders.py:822-849) against one triangle of the box: tq = {p0, p1, p2, normal}
+    const M3 ma = rotmat(ra), mb = rotmat(rb);
+    const V3 ca = pa + mrot(ma, f3(cq[CQ_PTS + 1])), ea = mrot(ma, f3(cq[CQ_PTS]));
+    const V3 p0 = pb + mrot(mb, f3(tq[0])), p1 = pb + mrot(mb, f3(tq[1])), p2 = pb + mrot(mb, f3(tq[2]));
+    const V3 tn = mrot(mb, f3(tq[3]));
+    V3 seg_p, tri_p;
+    closest_segment_triangle_points(ca + ea, ca - ea, p0, p1, p2, tn, &seg_p, &tri_p);
+    const V3 pv = seg_p - tri_p;
+    const float dist = safe_norm(pv);
+    ct.normal = vdiv(pv, 1e-6f + dist);
+    ct.pen = mat.z - dist;
+    ct.pos = tri_p;
+    ct.vel = (va + cross(wa, ct.pos - pa)) - (vb + cross(wb, ct.pos - pb));
+    return ct;
+  }
   if (BXF_IS(kind == BX_PAIR_CAPSULE_CAPSULE, BXF_CAPSULE_CAPSULE,
              BXF_CAPSULE_PLANE | BXF_BOX_PLANE)) {
     const M3 ma = rotmat(ra), mb = rotmat(rb);
@@ -792,7 +862,8 @@ BXS void c1_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
     const int ra0 = L::BQ * a, rb0 = L::BQ * b;
     V3 pa = ldv(c, ra0 + co), pb = ldv(c, rb0 + co);
     Q4 ra = ldq(c, ra0 + co + 1), rb = ldq(c, rb0 + co + 1);
-    Contact ct = contact_fn(ci.x, cq, pa, ra, ldv(c, ra0 + L::VEL), ldv(c, ra0 + L::ANG), pb, rb,
+    Contact ct = contact_fn(ci.x, cq, c.tf + h.fo_tri + c.ti[h.io_contact + k * CI_STRIDE + CI_TRI], pa, ra,
+                            ldv(c, ra0 + L::VEL), ldv(c, ra0 + L::ANG), pb, rb,
                             ldv(c, rb0 + L::VEL), ldv(c, rb0 + L::ANG));
     V3 iia = f3(bqa[BQ_INV_INERTIA]);
     const float4 ma4 = bqa[BQ_MASS];
@@ -1226,7 +1297,8 @@ BXS void spring_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
     const float4* bqb = c.tf + h.fo_body + b * BQ_STRIDE;
     const int ra0 = L::BQ * a, rb0 = L::BQ * b;
     V3 pa = ldv(c, ra0 + po), pb = ldv(c, rb0 + po);
-    Contact ct = contact_fn(ci.x, cq, pa, ldq(c, ra0 + po + 1), ldv(c, ra0 + L::VEL), ldv(c, ra0 + L::ANG),
+    Contact ct = contact_fn(ci.x, cq, c.tf + h.fo_tri + c.ti[h.io_contact + k * CI_STRIDE + CI_TRI], pa,
+                            ldq(c, ra0 + po + 1), ldv(c, ra0 + L::VEL), ldv(c, ra0 + L::ANG),
                             pb, ldq(c, rb0 + po + 1), ldv(c, rb0 + L::VEL), ldv(c, rb0 + L::ANG));
     const float4 mat = cq[CQ_MAT];
     V3 iia = f3(bqa[BQ_INV_INERTIA]), iib = f3(bqb[BQ_INV_INERTIA]);

@@ -88,7 +88,7 @@ enum {
   FI_IDX = 2,  // [3]
   FI_STRIDE = 8,
 
-  // contact row: 2 x int4 {kind, two_way, body_a, body_b} {slot_a, slot_b, pair, 0}.
+  // contact row: 2 x int4 {kind, two_way, body_a, body_b} {slot_a, slot_b, normal row, triangle quad offset}.
   // slot_a / slot_b are those of the row's ITEM (1 or 2 consecutive rows of one pair
   // that share one slot-list entry per side); `pair` is the row of the pair's normal.
   CI_KIND = 0,
@@ -97,7 +97,8 @@ enum {
   CI_BODY_B = 3,
   CI_SLOT_A = 4,
   CI_SLOT_B = 5,
-  CI_PAIR = 6,
+  CI_PAIR = 6,   // row of the contact normal (per pair; per row for capsule_box)
+  CI_TRI = 7,    // capsule_box: quad offset of the row's triangle in the fo_tri table
   CI_STRIDE = 8,
 };
 
@@ -129,6 +130,7 @@ struct BxHeader {
   int32_t io_forder;  // body order of the fused contact section (contact bodies first)
   int32_t io_citem;
   int32_t fo_body, fo_joint, fo_act, fo_force, fo_contact;          // quad offs
+  int32_t fo_tri;     // capsule_box rows: {p0, p1, p2, normal} of the row's triangle, 4 quads per row
   // state quad rows (each row = 32 env slots x float4, + 1 pad quad)
   // q_ct: one quad {pos, penetration} per contact row; q_cn: one quad {normal} per
   // collider pair; q_cd: dlambda of the rows, 4 per quad (pbd)

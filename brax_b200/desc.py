@@ -20,14 +20,14 @@ from typing import Any, Dict, List
 
 import numpy as np
 
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 MODE = {'pbd': 0, 'legacy_spring': 1}
 JOINT_KIND = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
               'spring_universal': 3, 'spring_spherical': 4}
 ACT_KIND = {'torque': 0, 'angle': 1}
 FORCE_KIND = {'thruster': 0, 'twister': 1}
-PAIR_KIND = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2}
+PAIR_KIND = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2, 'capsule_box': 3}
 
 MAX_BODIES, MAX_JOINTS, MAX_ACTUATORS = 64, 64, 64
 MAX_FORCES, MAX_PAIRS, MAX_CONTACTS, MAX_GROUPS = 32, 64, 128, 8
@@ -66,7 +66,8 @@ class CPair(C.Structure):
               ('body_b', C.c_int32), ('n_contacts', C.c_int32),
               ('friction', C.c_float), ('elasticity', C.c_float),
               ('radius_a', C.c_float), ('radius_b', C.c_float),
-              ('pts', (C.c_float * 3) * 8)]
+              ('pts', (C.c_float * 3) * 8), ('tri', ((C.c_float * 3) * 3) * 12),
+              ('tri_normal', (C.c_float * 3) * 12)]
 
 
 class CResetJoint(C.Structure):
@@ -261,6 +262,13 @@ class SystemDesc:
       pts[:len(src)] = src
       for r in range(8):
         c.pts[r][:] = _f(pts[r])
+      if p['kind'] == 'capsule_box':
+        tri = np.asarray(p['tri'], dtype=np.float64).reshape(12, 3, 3)
+        trn = np.asarray(p['tri_normal'], dtype=np.float64).reshape(12, 3)
+        for f in range(12):
+          c.tri_normal[f][:] = _f(trn[f])
+          for v in range(3):
+            c.tri[f][v][:] = _f(tri[f, v])
     d = CSystemDesc()
     d.struct_size = C.sizeof(CSystemDesc)
     d.abi_version = ABI_VERSION

@@ -26,7 +26,7 @@ _JOINT_KINDS = {
     ('brax.physics.spring_joints', 'Universal'): 'spring_universal',
     ('brax.physics.spring_joints', 'Spherical'): 'spring_spherical',
 }
-_PAIR_KINDS = {'capsule_plane', 'capsule_capsule', 'box_plane'}
+_PAIR_KINDS = {'capsule_plane', 'capsule_capsule', 'box_plane', 'capsule_box'}
 
 
 def _a(x) -> np.ndarray:
@@ -92,6 +92,8 @@ def _pair_rows(collider, group: int) -> List[Dict[str, Any]]:
     raise NotImplementedError(
         'collider cull %s (NearNeighbors is out of scope)' % type(cull).__name__)
   fn = collider.contact_fn.__name__
+  if fn == 'capsule_mesh' and type(collider.cull.get()[1]).__name__ == 'TriangulatedBox':
+    fn = 'capsule_box'          # ('capsule', 'box') of colliders.get (colliders.py:898-899)
   if fn not in _PAIR_KINDS:
     raise NotImplementedError('contact function %s is out of scope' % fn)
   two_way = type(collider).__name__ == 'TwoWayCollider'
@@ -117,14 +119,26 @@ def _pair_rows(collider, group: int) -> List[Dict[str, Any]]:
       corners = _a(ca.corner)[i].reshape(-1, 3)  # geometry.py:123-136
       r['n_contacts'] = int(corners.shape[0])
       r['pts'] = corners.tolist()
+    elif fn == 'capsule_box':
+      # capsule_mesh against geometry.TriangulatedBox (colliders.py:822-849, geometry.py:193-199):
+      # one contact row per triangle; faces / normals as the built object holds them (BaseMesh's
+      # winding fix applied, collider rotation / position folded in), body-b frame
+      faces = _a(cb.faces)[i].reshape(-1, 3, 3)
+      r['n_contacts'] = int(faces.shape[0])
+      r['pts'] = [_l(_a(ca.end)[i]), _l(_a(ca.pos)[i])]
+      r['tri'] = faces.tolist()
+      r['tri_normal'] = _a(cb.face_normals)[i].reshape(-1, 3).tolist()
+      r['radius_a'] = float(_a(ca.radius)[i])
+      if r['n_contacts'] != 12:
+        raise NotImplementedError('capsule_mesh against a general mesh (only TriangulatedBox: 12 faces)')
     else:  # capsule_capsule, geometry.py:243-258
       r['n_contacts'] = 1
       r['pts'] = [_l(_a(ca.end)[i]), _l(_a(ca.pos)[i]),
                   _l(_a(cb.end)[i]), _l(_a(cb.pos)[i])]
       r['radius_a'] = float(_a(ca.radius)[i])
       r['radius_b'] = float(_a(cb.radius)[i])
-    if r['n_contacts'] > 8:
-      raise NotImplementedError('more than 8 contacts per pair')
+    if r['n_contacts'] > 12:
+      raise NotImplementedError('more than 12 contacts per pair')
     rows.append(r)
   return rows
 

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BX_ABI_VERSION 8
+#define BX_ABI_VERSION 9
 
 /* dynamics_mode (base.py:179-201) */
 #define BX_MODE_PBD 0
@@ -59,6 +59,9 @@ extern "C" {
 #define BX_PAIR_CAPSULE_PLANE 0
 #define BX_PAIR_CAPSULE_CAPSULE 1
 #define BX_PAIR_BOX_PLANE 2
+/* colliders.py:822-849 capsule_mesh against geometry.TriangulatedBox (the ('capsule', 'box') entry of
+ * colliders.get, :898-899; geometry.py:193-199, 462-540): one contact row per triangle of the box. */
+#define BX_PAIR_CAPSULE_BOX 3
 
 #define BX_MAX_BODIES 64
 #define BX_MAX_JOINTS 64
@@ -117,7 +120,10 @@ typedef struct bx_force {
  *   box_plane     : pts[0..7] = corners in the body-a frame.
  *   capsule_capsule: pts[0] = end_a, pts[1] = pos_a, pts[2] = end_b,
  *                   pts[3] = pos_b (segment half-vector and centre offset in
- *                   each body frame), radius_a, radius_b. n_contacts = 1. */
+ *                   each body frame), radius_a, radius_b. n_contacts = 1.
+ *   capsule_box   : pts[0] = end_a, pts[1] = pos_a, radius_a; tri[f][v] = vertex v of triangle f
+ *                   of the box in the body-b frame (BaseMesh.faces, geometry.py:146-156),
+ *                   tri_normal[f] its normal. n_contacts = 12 (one row per triangle). */
 typedef struct bx_pair {
   int32_t kind;
   int32_t group;   /* collider group: averaging is per group (colliders.py:231) */
@@ -128,6 +134,8 @@ typedef struct bx_pair {
   float elasticity; /* elasticity_a * elasticity_b */
   float radius_a, radius_b;
   float pts[8][3];
+  float tri[12][3][3];    /* capsule_box only */
+  float tri_normal[12][3];
 } bx_pair;
 
 /* Optional env epilogue ("next" row N1): everything the reference's Env.step computes

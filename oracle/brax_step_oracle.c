@@ -66,7 +66,7 @@ enum { MODE_PBD = 0, MODE_SPRING = 1 };
 enum { J_REV = 0, J_SPH = 1, J_SREV = 2, J_SUNI = 3, J_SSPH = 4 };
 enum { A_TORQUE = 0, A_ANGLE = 1 };
 enum { F_THRUSTER = 0, F_TWISTER = 1 };
-enum { P_CAPSULE_PLANE = 0, P_CAPSULE_CAPSULE = 1, P_BOX_PLANE = 2 };
+enum { P_CAPSULE_PLANE = 0, P_CAPSULE_CAPSULE = 1, P_BOX_PLANE = 2, P_CAPSULE_BOX = 3 };
 
 #define MAXB 64
 #define MAXK 128
@@ -97,6 +97,10 @@ typedef struct {
   int32_t kind, group, two_way, body_a, body_b, n_contacts;
   R friction, elasticity, radius_a, radius_b;
   R pts[8][3];
+  /* capsule_box (capsule_mesh against geometry.TriangulatedBox): the 12 triangles of the box
+   * in the body-b frame (BaseMesh.faces after its winding fix, geometry.py:146-156) and their
+   * normals (BoxMesh, geometry.py:162-189) */
+  R tri[12][3][3], tri_normal[12][3];
 } opair;
 
 typedef struct {
@@ -711,6 +715,67 @@ static void closest_seg_seg(const osys* s, const R* a0, const R* a1, const R* b0
   }
 }
 
+/* geometry.py:377-391 */
+static void closest_segment_point_plane(const R* a, const R* b, const R* p0, const R* n, R* out) {
+  R ab[3];
+  for (int k = 0; k < 3; k++) ab[k] = b[k] - a[k];
+  R d = dot3(p0, n);
+  R denom = dot3(n, ab);
+  R t = (d - dot3(n, a)) / (denom + C(1e-6));
+  t = clipr(t, C(0), C(1));
+  for (int k = 0; k < 3; k++) out[k] = a[k] + t * ab[k];
+}
+
+/* geometry.py:462-500 closest_triangle_point */
+static void closest_triangle_point(const R* p0, const R* p1, const R* p2, const R* pt, R* out) {
+  R e0[3], e1[3], d[3], cp[3], df[3];
+  for (int k = 0; k < 3; k++) { e0[k] = p1[k] - p0[k]; e1[k] = p2[k] - p0[k]; d[k] = pt[k] - p0[k]; }
+  R a = dot3(e0, e0), b = dot3(e0, e1), c = dot3(e1, e1);
+  R det = a * c - b * b;
+  R u = (c * dot3(e0, d) - b * dot3(e1, d)) / det;
+  R v = (-b * dot3(e0, d) + a * dot3(e1, d)) / det;
+  int inside = (C(0) <= u) && (u <= C(1)) && (C(0) <= v) && (v <= C(1)) && (u + v <= C(1));
+  for (int k = 0; k < 3; k++) { cp[k] = p0[k] + u * e0[k] + v * e1[k]; df[k] = cp[k] - pt[k]; }
+  R d0 = dot3(df, df);
+  R c1[3], c2[3], c3[3];
+  R d1 = closest_segment_point_and_dist(p0, p1, pt, c1);
+  int take0 = (d0 < d1) && inside;
+  R min_d = take0 ? d0 : d1;
+  for (int k = 0; k < 3; k++) out[k] = take0 ? cp[k] : c1[k];
+  R d2 = closest_segment_point_and_dist(p1, p2, pt, c2);
+  if (d2 < min_d) for (int k = 0; k < 3; k++) out[k] = c2[k];
+  min_d = d2 < min_d ? d2 : min_d; /* jp.minimum */
+  R d3 = closest_segment_point_and_dist(p2, p0, pt, c3);
+  if (d3 < min_d) for (int k = 0; k < 3; k++) out[k] = c3[k];
+}
+
+/* geometry.py:503-540 closest_segment_triangle_points */
+static void closest_segment_triangle_points(const osys* s, const R* a, const R* b, const R* p0, const R* p1,
+                                            const R* p2, const R* tn, R* seg_pt, R* tri_pt) {
+  R sp[4][3], tp[4][3], dd[4];
+  closest_seg_seg(s, a, b, p0, p1, sp[0], tp[0]);
+  closest_seg_seg(s, a, b, p1, p2, sp[1], tp[1]);
+  closest_seg_seg(s, a, b, p0, p2, sp[2], tp[2]);
+  closest_segment_point_plane(a, b, p0, tn, sp[3]);
+  closest_triangle_point(p0, p1, p2, sp[3], tp[3]);
+  for (int i = 0; i < 4; i++) {
+    R v[3];
+    for (int k = 0; k < 3; k++) v[k] = sp[i][k] - tp[i][k];
+    dd[i] = dot3(v, v);
+  }
+  R mn = dd[0];
+  for (int i = 1; i < 4; i++) mn = dd[i] < mn ? dd[i] : mn;
+  /* mask = (distance == min); the candidates that tie are AVERAGED (sum * mask / sum(mask)) */
+  R cnt = C(0);
+  for (int k = 0; k < 3; k++) { seg_pt[k] = C(0); tri_pt[k] = C(0); }
+  for (int i = 0; i < 4; i++) {
+    R m = dd[i] == mn ? C(1) : C(0);
+    cnt += m;
+    for (int k = 0; k < 3; k++) { seg_pt[k] += sp[i][k] * m; tri_pt[k] += tp[i][k] * m; }
+  }
+  for (int k = 0; k < 3; k++) { seg_pt[k] = seg_pt[k] / cnt; tri_pt[k] = tri_pt[k] / cnt; }
+}
+
 static void world_velocity(const oqp* qp, int b, const R* pos, R* out) {
   R r[3], cr[3];
   for (int k = 0; k < 3; k++) r[k] = pos[k] - qp->pos[b][k];
@@ -753,6 +818,33 @@ static void pair_contacts(const osys* s, const opair* p, const oqp* qp, ocontact
         d[k] = qp->pos[b][k] - out[c].pos[k];
       }
       out[c].pen = dot3(d, n);
+    }
+  } else if (p->kind == P_CAPSULE_BOX) { /* capsule_mesh colliders.py:822-849, one row per triangle */
+    R pa[3], ea[3], a0[3], a1[3];
+    rotate(p->pts[1], qp->rot[a], pa);
+    rotate(p->pts[0], qp->rot[a], ea);
+    for (int k = 0; k < 3; k++) {
+      pa[k] = qp->pos[a][k] + pa[k];
+      a0[k] = pa[k] + ea[k]; a1[k] = pa[k] - ea[k];
+    }
+    for (int c = 0; c < p->n_contacts; c++) {
+      R tn[3], v[3][3], sp[3], tp[3], pv[3], va[3], vb[3];
+      rotate(p->tri_normal[c], qp->rot[b], tn);
+      for (int i = 0; i < 3; i++) {
+        rotate(p->tri[c][i], qp->rot[b], v[i]);
+        for (int k = 0; k < 3; k++) v[i][k] = qp->pos[b][k] + v[i][k];
+      }
+      closest_segment_triangle_points(s, a0, a1, v[0], v[1], v[2], tn, sp, tp);
+      for (int k = 0; k < 3; k++) pv[k] = sp[k] - tp[k];
+      R dist = safe_norm3(s, pv);
+      for (int k = 0; k < 3; k++) {
+        out[c].normal[k] = pv[k] / (C(1e-6) + dist);
+        out[c].pos[k] = tp[k];
+      }
+      out[c].pen = p->radius_a - dist;
+      world_velocity(qp, a, out[c].pos, va);
+      world_velocity(qp, b, out[c].pos, vb);
+      for (int k = 0; k < 3; k++) out[c].vel[k] = va[k] - vb[k];
     }
   } else { /* capsule_capsule colliders.py:805-819, _endpoints :661-664 */
     R pa[3], ea[3], pb[3], eb[3], a0[3], a1[3], b0[3], b1[3], ba[3], bb[3];
@@ -1494,7 +1586,7 @@ void FN(bxo_rotate)(const R* v, const R* q, R* out) { rotate(v, q, out); }
 int FN(bxo_pair_contacts)(const osys* s, int pair_index, const R* pos, const R* rot,
                           const R* vel, const R* ang, R* out10) {
   static _Thread_local oqp qp;
-  ocontact ct[8];
+  ocontact ct[12];
   if (pair_index < 0 || pair_index >= s->np) return 1;
   for (int b = 0; b < s->nb; b++) {
     for (int k = 0; k < 3; k++) {

@@ -109,6 +109,61 @@ def main(only):
           c.bodies[1].frozen.all = True      # physics_test.py:901
         c.dt = (2 * 5 / 9.8) / 100.          # :886-887
         roll(n, c, 1, 110 if frozen else 400)
+    # ElasticityTest.test_ball_bounce (physics_test.py:863-878): the ball flies into the frozen box wall
+    # -- capsule_mesh against geometry.TriangulatedBox (colliders.py:822-849), one-way -- with the
+    # config AS IS (boxwall included), default_qp(0), 100 steps
+    for e in (0.0, 0.5, 1.0):
+      n = 'ball_wall_%s_e%d' % (mode, int(100 * e))
+      if want(n):
+        c = text_format.Parse(pt.ElasticityTest._CONFIG, brax.Config())
+        c.elasticity = e
+        if mode == 'spring':
+          c.dynamics_mode = 'legacy_spring'
+        roll(n, c, 0, 100)
+    # a tilted capsule dropped onto a frozen box (edge / face contacts of the triangulated box, one-way)
+    # and a ball dropped onto a FREE box resting on the plane (two-way capsule_mesh + box_plane)
+    n = 'capsule_on_box_%s' % mode
+    if want(n):
+      c = text_format.Parse('''
+        dt: 0.02 substeps: 8 friction: 0.6 elasticity: 0.3
+        gravity { z: -9.8 }
+        bodies {
+          name: "cap" mass: 1
+          colliders { rotation { y: 60 } capsule { radius: .15 length: 1.0 } }
+          inertia { x: 0.05 y: 0.05 z: 0.02 }
+        }
+        bodies {
+          name: "ball" mass: 0.5
+          colliders { capsule { radius: .25 length: 0.5 } }
+          inertia { x: 0.02 y: 0.02 z: 0.02 }
+        }
+        bodies {
+          name: "block" mass: 1
+          colliders { rotation { z: 20 } box { halfsize { x: 0.6 y: 0.4 z: 0.3 } } }
+          inertia { x: 1 y: 1 z: 1 }
+          frozen { all: true }
+        }
+        bodies {
+          name: "crate" mass: 2
+          colliders { box { halfsize { x: 0.4 y: 0.4 z: 0.4 } } }
+          inertia { x: 0.3 y: 0.3 z: 0.3 }
+        }
+        bodies { name: "Ground" frozen: { all: true } colliders { plane {}}}
+        collide_include { first: "cap" second: "block" }
+        collide_include { first: "cap" second: "Ground" }
+        collide_include { first: "ball" second: "crate" }
+        collide_include { first: "ball" second: "Ground" }
+        collide_include { first: "crate" second: "Ground" }
+        defaults {
+          qps { name: "cap" pos { x: 0.3 y: 0.1 z: 1.2 } vel { z: -1.0 } ang { x: 0.5 } }
+          qps { name: "ball" pos { x: 3.1 y: 0.05 z: 1.6 } vel { z: -2.0 } }
+          qps { name: "block" pos { z: 0.3 } }
+          qps { name: "crate" pos { x: 3.0 z: 0.4 } }
+        }
+      ''', brax.Config())
+      if mode == 'spring':
+        c.dynamics_mode = 'legacy_spring'
+      roll(n, c, 0, 80)
     n = 'ball_plane_%s_e50' % mode
     if want(n):
       c = text_format.Parse('''

@@ -23,7 +23,7 @@ _JK = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
        'spring_universal': 3, 'spring_spherical': 4}
 _AK = {'torque': 0, 'angle': 1}
 _FK = {'thruster': 0, 'twister': 1}
-_PK = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2}
+_PK = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2, 'capsule_box': 3}
 
 
 def build(force: bool = False):
@@ -93,7 +93,8 @@ def _structs(R):
                 ('two_way', C.c_int32), ('body_a', C.c_int32),
                 ('body_b', C.c_int32), ('n_contacts', C.c_int32),
                 ('friction', R), ('elasticity', R), ('radius_a', R),
-                ('radius_b', R), ('pts', (R * 3) * 8)]
+                ('radius_b', R), ('pts', (R * 3) * 8), ('tri', ((R * 3) * 3) * 12),
+                ('tri_normal', (R * 3) * 12)]
 
   class Sys(C.Structure):
     _fields_ = [('mode', C.c_int32), ('substeps', C.c_int32),
@@ -193,6 +194,13 @@ class Oracle:
       src = np.asarray(p['pts'], dtype=np.float64).reshape(-1, 3)
       for r in range(len(src)):
         c.pts[r][:] = arr(src[r])
+      if p['kind'] == 'capsule_box':
+        tri = np.asarray(p['tri'], dtype=np.float64).reshape(12, 3, 3)
+        trn = np.asarray(p['tri_normal'], dtype=np.float64).reshape(12, 3)
+        for f in range(12):
+          c.tri_normal[f][:] = arr(trn[f])
+          for v in range(3):
+            c.tri[f][v][:] = arr(tri[f, v])
     s = Sys()
     s.mode = _MODE[desc.dynamics_mode]
     s.substeps, s.nb, s.nj = desc.substeps, nb, nj
