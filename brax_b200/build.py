@@ -52,10 +52,30 @@ def build(force: bool = False, verbose: bool = False, extra=(), out: str = None)
     objs.append(o)
     jobs.append(common + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-DBX_TU_NAME=%s' % name, '-c',
                           os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
+  # incremental: an object is recompiled only if one of ITS sources is newer (same flags: the object
+  # directory is keyed by the output name; `extra` flags force everything)
+  kernel_deps = ['bx_kernels.cu', 'bx_step_kernel.cuh', 'bx_params.h', 'bx_math.cuh', 'bx_tables.h',
+                 os.path.join('..', '..', 'include', 'brax_b200.h')]
+  deps_of = {'bx_api.o': ['bx_api.cu', 'bx_params.h', 'bx_tables.h', os.path.join('..', '..', 'include', 'brax_b200.h')],
+             'bx_reset.o': ['bx_reset.cu', 'bx_math.cuh', os.path.join('..', '..', 'include', 'brax_b200.h')]}
+  stamp = os.path.join(objdir, 'flags.txt')
+  flags_now = ' '.join(common)
+  same_flags = os.path.exists(stamp) and open(stamp).read() == flags_now
+
+  def fresh(job):
+    o = job[job.index('-o') + 1]
+    if not same_flags or not os.path.exists(o):
+      return False
+    deps = deps_of.get(os.path.basename(o), kernel_deps)
+    return all(os.path.getmtime(os.path.join(CSRC, d)) <= os.path.getmtime(o) for d in deps)
+
+  jobs = [j for j in jobs if not fresh(j)]
   procs = [subprocess.Popen(j) for j in jobs]
   rcs = [p.wait() for p in procs]
   if any(rcs):
     raise subprocess.CalledProcessError(max(rcs), 'nvcc')
+  with open(stamp, 'w') as f:
+    f.write(flags_now)
   subprocess.check_call([nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', out] + objs)
   return out
 

@@ -31,6 +31,7 @@ struct bx_system {
   float4* d_tab_f;
   size_t smem_bytes;
   int warps;  // warps per CTA (W)
+  bool warps_chosen;  // set by bx_system_configure / bx_system_autotune: the launch keeps it as is
   int jc, cc; // joint / contact class of the kernel variant (bx_params.h)
   bool fusable;  // the fused contact section is legal for this system
   int sm_count;
@@ -794,6 +795,7 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
       s->cc = (s->fusable && 2 * contact_bodies <= desc->num_bodies) ? BX_CC_PLANE_FUSED : BX_CC_PLANE;
   }
   s->device = device;
+  s->warps_chosen = false;
   s->sm_count = prop.multiProcessorCount;
   s->d_scratch = nullptr;
   s->scratch_floats = 0;
@@ -904,7 +906,7 @@ extern "C" int bx_system_configure(bx_system* s, int32_t threads_per_block, int3
   if (contact_section < 0 || contact_section > 2) return fail("contact_section must be 0, 1 or 2");
   if (contact_section == 2 && !s->fusable)
     return fail("fused contact section needs pbd, one-way plane colliders, <= 2 rows per body");
-  if (threads_per_block) s->warps = threads_per_block / 32;
+  if (threads_per_block) { s->warps = threads_per_block / 32; s->warps_chosen = true; }
   if (contact_section && s->cc != BX_CC_ALL && s->cc != BX_CC_MESH)
     s->cc = contact_section == 2 ? BX_CC_PLANE_FUSED : BX_CC_PLANE;
   return 0;
@@ -978,8 +980,13 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   int cur_dev = s->device;
   if (cudaGetDevice(&cur_dev) != cudaSuccess) cur_dev = s->device;
   if (cur_dev != s->device) CUDA_OK(cudaSetDevice(s->device));
+  // At most one tile per SM (batches up to 32 x SM count: 4736 envs): nothing shares the SM, so the tile
+  // takes 16 warps with the one-tile register budget -- every phase's items in one round (measured at
+  // 4096 envs: grasp 38.9 -> 34.9 us, humanoid 55.3 -> 49.8, fetch 34.2 -> 30.8, ant 44.0 -> 43.0).
+  // An explicit bx_system_configure / autotune choice is kept.
+  const int warps = (!s->warps_chosen && tiles <= s->sm_count && s->warps < 16) ? 16 : s->warps;
   cudaError_t le = launch_variant(s->h.mode, s->jc, s->cc | (s->h.env_kind ? BX_CC_ENV : 0) | pdl,
-                                  static_cast<unsigned>(tiles), 32 * s->warps,
+                                  static_cast<unsigned>(tiles), 32 * warps,
                                   s->smem_bytes, stream, p, three);
   if (cur_dev != s->device) cudaSetDevice(cur_dev);
   g_launches.fetch_add(1);
@@ -1011,6 +1018,7 @@ extern "C" int bx_system_autotune(bx_system* s, int64_t num_envs, const bx_step_
   const cudaEvent_t e0 = ev.a, e1 = ev.b;
   const int cand[4] = {8, 10, 12, 16};
   const int keep = s->warps, keep_cc = s->cc;
+  s->warps_chosen = true;  // the trial launches run the candidate W as is
   float best = 1e30f;
   int best_w = keep, best_cc = keep_cc;
   // two interleaved passes over all candidates, 8 timed launches each, best pass
@@ -1042,6 +1050,7 @@ extern "C" int bx_system_autotune(bx_system* s, int64_t num_envs, const bx_step_
       }
   s->cc = best_cc;
   s->warps = best_w;
+  s->warps_chosen = true;
   return 0;
 }
 
