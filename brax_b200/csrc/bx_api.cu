@@ -259,6 +259,9 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     quad(s.rot_mask[0], s.rot_mask[1], s.rot_mask[2], 0.f);
   }
   h.fo_joint = nquads();
+  bool rev_only = true;   // the revolute-only kernel variants read the 10-quad record (bx_step_kernel.cuh JQS)
+  for (int i = 0; i < nj; i++)
+    rev_only = rev_only && (d->joints[i].kind == BX_JOINT_REVOLUTE || d->joints[i].kind == BX_JOINT_SPRING_REVOLUTE);
   for (int i = 0; i < nj; i++) {
     const bx_joint& s = d->joints[i];
     quad(s.off_p[0], s.off_p[1], s.off_p[2], s.angular_damping);
@@ -268,8 +271,8 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     for (int r = 0; r < 3; r++) quad(s.axis_p[3 * r], s.axis_p[3 * r + 1], s.axis_p[3 * r + 2], wp[r]);
     for (int r = 0; r < 3; r++) quad(s.axis_c[3 * r], s.axis_c[3 * r + 1], s.axis_c[3 * r + 2], wc[r]);
     quad(s.limit[0], s.limit[1], s.limit[2], s.limit[3]);
-    quad(s.limit[4], s.limit[5], 0.f, 0.f);
-    for (int dd = 0; dd < 3; dd++) {  // direction vectors of the limits (clip_dir, bx_step_kernel.cuh)
+    if (!rev_only) quad(s.limit[4], s.limit[5], 0.f, 0.f);
+    for (int dd = 0; dd < (rev_only ? 1 : 3); dd++) {  // direction vectors of the limits (clip_dir, bx_step_kernel.cuh)
       float cs[4];
       for (int e = 0; e < 2; e++) {
         const double a = s.limit[2 * dd + e];

@@ -250,6 +250,15 @@ BXS void store_warp(const float* smf, const int32_t* ti, const BxSeg& sg, float*
   }
 }
 
+// Joint float record stride and the limit directions {cos lo, sin lo, cos hi, sin hi} of dof d
+// (bx_tables.h): systems with revolute joints only (the BXF_JC0 variants) keep the 10-quad record --
+// their dof-0 directions take the place of the unused {lo2, hi2} quad -- so their tiles do not grow
+// (ant stays under the three-tiles-per-SM limit); all others carry three more quads.
+static constexpr int JQS = (BX_FEAT & (BXF_SPHERICAL | BXF_UNIVERSAL)) ? JQ_STRIDE : JQ_STRIDE_REVOLUTE;
+BXS float4 limcs(const float4* jq, int d) {
+  return (BX_FEAT & (BXF_SPHERICAL | BXF_UNIVERSAL)) ? jq[JQ_LIMCS + d] : jq[JQ_LIMIT + 1];
+}
+
 // ---- joints: axis / angle -------------------------------------------------
 // Revolute.axis_angle joints.py:311-319 (spring_joints.py:150-157); mp / mc = rotmat(rot_p / rot_c)
 BXS void axis_angle_revolute(const float4* jq, const M3& mp, const M3& mc, V3* axis, float* angle) {
@@ -287,7 +296,7 @@ BXS void axis_outside_revolute(const float4* jq, const M3& mp, const M3& mc, V3*
   V3 ref_c = mrot(mc, f3(jq[JQ_AXIS_C + 2]));
   const float4 l01 = jq[JQ_LIMIT];
   bool below, above;
-  angle_outside(dot(ref_p, ref_c), dot(cross(ref_p, ref_c), ax), jq[JQ_LIMCS], l01.x, l01.y, &below, &above);
+  angle_outside(dot(ref_p, ref_c), dot(cross(ref_p, ref_c), ax), limcs(jq, 0), l01.x, l01.y, &below, &above);
   axis[0] = ax;
   outside[0] = below || above;
 }
@@ -301,13 +310,13 @@ BXS void axis_outside_spherical(const float4* jq, const M3& mp, const M3& mc, V3
   V3 lon = cross(a3c, a1p);
   lon = vdiv(lon, 1e-10f + safe_norm(lon));
   bool below, above;
-  angle_outside(dot(a2p, lon), dot(cross(a2p, lon), a1p), jq[JQ_LIMCS], l01.x, l01.y, &below, &above);
+  angle_outside(dot(a2p, lon), dot(cross(a2p, lon), a1p), limcs(jq, 0), l01.x, l01.y, &below, &above);
   outside[0] = below || above;
   V3 xz = dot(a1p, a1c) * a1c + dot(a1p, a2c) * a2c;
   xz = vdiv(xz, 1e-10f + safe_norm(xz));
   float theta = bx_acos(clipf(dot(xz, a1p), -1.f, 1.f)) * signf(dot(a1p, a3c));
   outside[1] = theta < l01.z || theta > l01.w;
-  angle_outside(dot(a2c, lon), dot(cross(a2c, lon), -a3c), jq[JQ_LIMCS + 2], l2.x, l2.y, &below, &above);
+  angle_outside(dot(a2c, lon), dot(cross(a2c, lon), -a3c), limcs(jq, 2), l2.x, l2.y, &below, &above);
   outside[2] = below || above;
   axis[0] = a1p; axis[1] = a2c; axis[2] = a3c;
 }
@@ -351,7 +360,7 @@ BXS void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
     const int idx2 = ai2.x;
     const int j = ai.y;
     const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
-    const float4* jq = c.tf + h.fo_joint + j * JQ_STRIDE;
+    const float4* jq = c.tf + h.fo_joint + j * JQS;
     const int kind = ji.x;
     Q4 rp = ldq(c, L::BQ * ji.y + ro);
     Q4 rc = ldq(c, L::BQ * ji.z + ro);
@@ -401,7 +410,7 @@ BXS void phase_torques(const Ctx& c, const BxHeader& h, bool damp) {
     for (int j = c.damp_j0; j < h.nj; j += c.damp_step) {
       const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
       const int4 js = ldi4(c.ti + h.io_joint + j * JI_STRIDE + 4);  // dslot_p dslot_c jslot_p jslot_c
-      const float damping = c.tf[h.fo_joint + j * JQ_STRIDE + JQ_OFF_P].w;
+      const float damping = c.tf[h.fo_joint + j * JQS + JQ_OFF_P].w;
       V3 ap = ldv(c, L::BQ * ji.y + L::ANG);
       V3 ac = ldv(c, L::BQ * ji.z + L::ANG);
       V3 tq = (-1.f * damping) * (ap - ac);
@@ -573,7 +582,7 @@ BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
   for (int j = c.warp; j < h.nj; j += c.nwarp) {
     PTM0(c);
     const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
-    const float4* jq = c.tf + h.fo_joint + j * JQ_STRIDE;
+    const float4* jq = c.tf + h.fo_joint + j * JQS;
     const int bp = ji.y, bc = ji.z;
     const float4* bqp = c.tf + h.fo_body + bp * BQ_STRIDE;
     const float4* bqc = c.tf + h.fo_body + bc * BQ_STRIDE;
@@ -598,7 +607,7 @@ BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
       V3 ref_c = mrot(Rc, f3(jq[JQ_AXIS_C + 2]));
       // psi = signed_angle(axis, ref_p, ref_c); n1 = ref_p rotated about axis by clip(psi, lo, hi)
       float cs, sn, outside;
-      clip_dir(dot(ref_p, ref_c), dot(cross(ref_p, ref_c), axis), jq[JQ_LIMCS], l01.x, l01.y, &cs, &sn, &outside);
+      clip_dir(dot(ref_p, ref_c), dot(cross(ref_p, ref_c), axis), limcs(jq, 0), l01.x, l01.y, &cs, &sn, &outside);
       PTM(c, 6);
       V3 axis_c = mrot(Rc, f3(jq[JQ_AXIS_C]));
       V3 dq_1 = cross(axis, axis_c);
@@ -626,9 +635,9 @@ BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
       a2n = vdiv(a2n, 1e-6f + safe_norm(a2n));
       float sg = signf(dot(a1p, a3c));
       Q4 p1, c1, p2, c2, p3, c3;
-      limit_angle(a1p, a2p, lon, l01.x, l01.y, jq[JQ_LIMCS], ii_p, ii_c, rp, rc, sa, &p1, &c1);
-      limit_angle((-a2n) * sg, a1p, xz, l01.z, l01.w, jq[JQ_LIMCS + 1], ii_p, ii_c, rp, rc, sa, &p2, &c2);
-      limit_angle(a3c, lon, a2c, l2.x, l2.y, jq[JQ_LIMCS + 2], ii_p, ii_c, rp, rc, sa, &p3, &c3);
+      limit_angle(a1p, a2p, lon, l01.x, l01.y, limcs(jq, 0), ii_p, ii_c, rp, rc, sa, &p1, &c1);
+      limit_angle((-a2n) * sg, a1p, xz, l01.z, l01.w, limcs(jq, 1), ii_p, ii_c, rp, rc, sa, &p2, &c2);
+      limit_angle(a3c, lon, a2c, l2.x, l2.y, limcs(jq, 2), ii_p, ii_c, rp, rc, sa, &p3, &c3);
       dp.rot = dp.rot + ((p1 + p2) + p3);
       dc.rot = dc.rot + ((c1 + c2) + c3);
     }
@@ -1187,7 +1196,7 @@ BXS void phase_joints_spring(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_LEGACY_SPRING> L;
   for (int j = c.warp; j < h.nj; j += c.nwarp) {
     const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
-    const float4* jq = c.tf + h.fo_joint + j * JQ_STRIDE;
+    const float4* jq = c.tf + h.fo_joint + j * JQS;
     const int kind = ji.x, bp = ji.y, bc = ji.z;
     const float4* bqp = c.tf + h.fo_body + bp * BQ_STRIDE;
     const float4* bqc = c.tf + h.fo_body + bc * BQ_STRIDE;
@@ -1375,7 +1384,7 @@ BXS void phase_angle_vel(const Ctx& c, const BxHeader& h) {
   const int ro = MODE == BX_MODE_PBD ? 2 * c.cur + 1 : 1;
   for (int j = c.warp; j < h.nj; j += c.nwarp) {
     const int4 ji = ldi4(c.ti + h.io_joint + j * JI_STRIDE);
-    const float4* jq = c.tf + h.fo_joint + j * JQ_STRIDE;
+    const float4* jq = c.tf + h.fo_joint + j * JQS;
     Q4 rp = ldq(c, L::BQ * ji.y + ro), rc = ldq(c, L::BQ * ji.z + ro);
     V3 axis[3];
     float angle[3];

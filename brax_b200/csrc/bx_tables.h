@@ -32,6 +32,7 @@ enum {
   JQ_LIMIT = 8,   // {lo0, hi0, lo1, hi1}, {lo2, hi2, 0, 0}
   JQ_LIMCS = 10,  // per dof d: {cos lo_d, sin lo_d, cos hi_d, sin hi_d} (a limit at or beyond +-pi: (-1, 0))
   JQ_STRIDE = 13,
+  JQ_STRIDE_REVOLUTE = 10,  // systems with revolute joints only: quad 9 = the dof-0 limit directions
 
   // actuator / force: 1 quad {strength, 0, 0, 0}
   // contact row (one per contact, pairs expanded): 5 quads

@@ -1,6 +1,6 @@
 """Kernel-only timing for A/B work on the step kernel (GPU box).
 
-usage: [BRAX_B200_LIB=path.so] python tools/kbench.py [env:B[:threads] ...] [--steps K] [--check]
+usage: [BRAX_B200_LIB=path.so] python tools/kbench.py [env:B[:threads[:contact_section]] ...] [--steps K] [--check]
 
 Per case: K chained `System.step` launches behind a spin kernel, ONE event pair around them
 (bench.py's method), rotating over enough env batches to exceed L2; prints us/step and M env-steps/s.
@@ -29,10 +29,10 @@ def state(s, b, seed):
   return QP(*[torch.from_numpy(np.ascontiguousarray(x)).cuda() for x in (q.pos, q.rot, vel, ang)])
 
 
-def run(name, b, threads, steps, check):
+def run(name, b, threads, steps, check, cs=0):
   s = load_system(name)
-  if threads:
-    s.configure(threads)
+  if threads or cs:
+    s.configure(threads, cs)
   nsets = max(2, -(-2 * 126_000_000 // (b * s.desc.bytes_per_env_step())))
   nsets = min(nsets, 64)
   qps = [state(s, b, 1 + i) for i in range(nsets)]
@@ -53,8 +53,8 @@ def run(name, b, threads, steps, check):
     torch.cuda.synchronize()
     best = min(best, e0.elapsed_time(e1) / steps)
   fin = bool(torch.isfinite(qps[0].pos).all())
-  line = '%-16s B=%-7d T=%-3d %8.2f us/step %8.2f M env-steps/s finite=%s' % (
-      name, b, int(s._lib.bx_system_threads(s._h)), best * 1e3, b / best / 1e3, fin)
+  line = '%-16s B=%-7d T=%-3d cs=%d %8.2f us/step %8.2f M env-steps/s finite=%s' % (
+      name, b, int(s._lib.bx_system_threads(s._h)), cs, best * 1e3, b / best / 1e3, fin)
   if check:
     from oracle.oracle import Oracle
     q = qps[0]
@@ -86,7 +86,7 @@ def main():
   print('lib:', os.environ.get('BRAX_B200_LIB', 'default'))
   for c in args.cases:
     p = c.split(':')
-    run(p[0], int(p[1]), int(p[2]) if len(p) > 2 else 0, args.steps, args.check)
+    run(p[0], int(p[1]), int(p[2]) if len(p) > 2 else 0, args.steps, args.check, int(p[3]) if len(p) > 3 else 0)
 
 
 if __name__ == '__main__':
