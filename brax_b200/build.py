@@ -13,6 +13,8 @@ DEPS = ['bx_api.cu', 'bx_reset.cu', 'bx_kernels.cu', 'bx_step_kernel.cuh', 'bx_p
         os.path.join('..', '..', 'include', 'brax_b200.h')]
 # (launch bound threads, min blocks per SM): one kernel translation unit each
 BOUNDS = [(256, 2), (320, 2), (384, 2), (512, 1)]
+# units that also instantiate the capsule-box contact class (the others would only add build time)
+MESH_BOUNDS = [(320, 2), (512, 1)]
 # extra units: (name, threads, min blocks per SM)
 EXTRA_UNITS = [('320x3', 320, 3)]
 
@@ -45,8 +47,9 @@ def build(force: bool = False, verbose: bool = False, extra=(), out: str = None)
   for maxt, minb in BOUNDS:
     o = os.path.join(objdir, 'bx_kernels_%d.o' % maxt)
     objs.append(o)
-    jobs.append(common + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-c',
-                          os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
+    mesh = ['-DBX_TU_MESH=1'] if (maxt, minb) in MESH_BOUNDS else []
+    jobs.append(common + mesh + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-c',
+                                 os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
   for name, maxt, minb in EXTRA_UNITS:
     o = os.path.join(objdir, 'bx_kernels_%s.o' % name)
     objs.append(o)

@@ -704,6 +704,9 @@ static cudaError_t launch_variant(int mode, int jc, int cc, unsigned grid, int t
                                   cudaStream_t stream, const BxKernelParams& p, bool three) {
   // big batches of small systems: three tiles per SM (64 registers) when more than two waves
   // of tiles exist and three tiles fit in shared memory
+  if ((cc & 7) == BX_CC_MESH)  // capsule-box systems: two builds exist (bx_kernels.cu BX_TU_MESH)
+    return threads <= 320 ? bx_launch_320(mode, jc, cc, grid, threads, smem, stream, p)
+                          : bx_launch_512(mode, jc, cc, grid, threads, smem, stream, p);
   if (three && threads <= 320 && 3 * (smem + 1024) <= 233472)
     return bx_launch_320x3(mode, jc, cc, grid, threads, smem, stream, p);
   if (threads <= 256) return bx_launch_256(mode, jc, cc, grid, threads, smem, stream, p);

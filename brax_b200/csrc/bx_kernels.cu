@@ -30,9 +30,15 @@ static bx_kernel_fn pick(int jc, int cc) {
     return BX_K(BXF_JC2, BXF_CC0);
   }
   if (cc == BX_CC_MESH) {
+    // the capsule-box class is instantiated in two translation units only (320 threads x 2 tiles,
+    // 512 x 1: -DBX_TU_MESH, brax_b200/build.py); bx_api.cu's launch_variant routes it there
+#ifdef BX_TU_MESH
     if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC2);
     if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC2);
     return BX_K(BXF_JC2, BXF_CC2);
+#else
+    return nullptr;
+#endif
   }
   if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC1);
   if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC1);
@@ -52,6 +58,7 @@ static bx_kernel_fn pick_any(int mode, int jc, int cc) {
 cudaError_t BX_CAT(bx_launch_, BX_TU_NAME)(int mode, int jc, int cc, unsigned grid, int threads,
                                            size_t smem, cudaStream_t stream,
                                            const BxKernelParams& p) {
+  if (pick_any(mode, jc, cc) == nullptr) return cudaErrorInvalidDeviceFunction;
   if (!(cc & BX_CC_PDL)) {
     pick_any(mode, jc, cc)<<<grid, threads, smem, stream>>>(p);
     return cudaGetLastError();
@@ -74,6 +81,7 @@ cudaError_t BX_CAT(bx_set_smem_, BX_TU_NAME)(int bytes) {
     for (int jc = 0; jc < BX_NUM_JC; jc++)
       for (int cc = 0; cc < BX_NUM_CC; cc++)
         for (int env = 0; env < 2; env++) {
+          if (pick_any(mode, jc, cc | (env ? BX_CC_ENV : 0)) == nullptr) continue;
           cudaError_t e = cudaFuncSetAttribute(pick_any(mode, jc, cc | (env ? BX_CC_ENV : 0)),
                                                cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
           if (e != cudaSuccess) return e;
