@@ -1009,6 +1009,78 @@ extern "C" int bx_rollout(bx_system* s, int64_t num_envs, int32_t num_steps, con
   return launch(s, num_envs, num_steps, io, static_cast<cudaStream_t>(stream));
 }
 
+// ---- opaque device-resident state (include/brax_b200.h "bx_state") ------------------------------
+struct bx_state {
+  const bx_system* sys;
+  int64_t num_envs;
+  float* buf;  // one allocation: pos[B,N,3] rot[B,N,4] vel[B,N,3] ang[B,N,3], each on a 256-byte boundary
+  float *pos, *rot, *vel, *ang;
+};
+
+extern "C" int bx_state_create(const bx_system* s, int64_t B, bx_state** out) {
+  if (!out) return fail("out is NULL");
+  *out = nullptr;
+  if (!s) return fail("system is NULL");
+  if (B <= 0) return fail("num_envs must be positive");
+  int prev = -1;
+  if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+  struct Restore { int d; ~Restore() { if (d >= 0) cudaSetDevice(d); } } restore{prev};
+  CUDA_OK(cudaSetDevice(s->device));
+  const size_t n = static_cast<size_t>(s->h.nb);
+  auto pad = [](size_t floats) { return (floats + 63) / 64 * 64; };
+  const size_t f3 = pad(3 * n * B), f4 = pad(4 * n * B);
+  bx_state* st = new bx_state();
+  st->sys = s;
+  st->num_envs = B;
+  st->buf = nullptr;
+  cudaError_t e = cudaMalloc(&st->buf, (3 * f3 + f4) * sizeof(float));
+  if (e != cudaSuccess) { delete st; return fail(std::string("cudaMalloc of the state failed: ") + cudaGetErrorString(e)); }
+  st->pos = st->buf; st->rot = st->pos + f3; st->vel = st->rot + f4; st->ang = st->vel + f3;
+  *out = st;
+  return 0;
+}
+extern "C" void bx_state_destroy(bx_state* st) {
+  if (!st) return;
+  int prev = -1;
+  if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+  cudaSetDevice(st->sys->device);
+  cudaFree(st->buf);
+  if (prev >= 0) cudaSetDevice(prev);
+  delete st;
+}
+extern "C" int64_t bx_state_num_envs(const bx_state* st) { return st ? st->num_envs : -1; }
+static int state_copy(const bx_state* st, float* const dst[4], const float* const src[4], cudaStream_t stream) {
+  const size_t n = static_cast<size_t>(st->sys->h.nb) * st->num_envs;
+  const size_t w[4] = {3, 4, 3, 3};
+  for (int i = 0; i < 4; i++) {
+    if (!dst[i] || !src[i]) return fail("QP pointers must not be NULL");
+    CUDA_OK(cudaMemcpyAsync(dst[i], src[i], w[i] * n * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  }
+  return 0;
+}
+extern "C" int bx_state_set(bx_state* st, const float* pos, const float* rot, const float* vel, const float* ang,
+                            void* stream) {
+  if (!st) return fail("state is NULL");
+  float* const dst[4] = {st->pos, st->rot, st->vel, st->ang};
+  const float* const src[4] = {pos, rot, vel, ang};
+  return state_copy(st, dst, src, static_cast<cudaStream_t>(stream));
+}
+extern "C" int bx_state_get(const bx_state* st, float* pos, float* rot, float* vel, float* ang, void* stream) {
+  if (!st) return fail("state is NULL");
+  float* const dst[4] = {pos, rot, vel, ang};
+  const float* const src[4] = {st->pos, st->rot, st->vel, st->ang};
+  return state_copy(st, dst, src, static_cast<cudaStream_t>(stream));
+}
+extern "C" int bx_state_rollout(bx_state* st, int32_t num_steps, const bx_step_io* io, void* stream) {
+  if (!st || !io) return fail("NULL argument");
+  if (io->pos || io->rot || io->vel || io->ang || io->pos_o || io->rot_o || io->vel_o || io->ang_o)
+    return fail("bx_state_rollout: the QP pointers of bx_step_io must be NULL (the state handle owns the QP)");
+  bx_step_io d = *io;
+  d.pos = st->pos; d.rot = st->rot; d.vel = st->vel; d.ang = st->ang;
+  d.pos_o = st->pos; d.rot_o = st->rot; d.vel_o = st->vel; d.ang_o = st->ang;   // in place
+  return launch(st->sys, st->num_envs, num_steps, &d, static_cast<cudaStream_t>(stream));
+}
+
 // Times the candidate CTA sizes on the caller's own buffers and keeps the fastest
 // (outputs are overwritten by every trial: call it before a real step).
 extern "C" int bx_system_autotune(bx_system* s, int64_t num_envs, const bx_step_io* io, void* stream) {

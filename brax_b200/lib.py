@@ -18,7 +18,8 @@ SYMBOLS = ('bx_system_create', 'bx_system_destroy', 'bx_system_num_contacts',
            'bx_system_autotune', 'bx_system_threads', 'bx_host_transfer_bytes',
            'bx_host_alloc', 'bx_host_free', 'bx_desc_tile_bytes',
            'bx_launch_count', 'bx_last_error', 'bx_system_num_joint_dof', 'bx_default_qp',
-           'bx_step_host_static', 'bx_static_scratch_bytes', 'bx_step_host_async', 'bx_host_wait')
+           'bx_step_host_static', 'bx_static_scratch_bytes', 'bx_step_host_async', 'bx_host_wait', 'bx_state_create', 'bx_state_destroy',
+           'bx_state_num_envs', 'bx_state_set', 'bx_state_get', 'bx_state_rollout')
 
 _lib = None
 
@@ -58,6 +59,18 @@ def load():
   lib.bx_step_host_async.restype = C.c_int
   lib.bx_host_wait.argtypes = [P, C.c_int32]
   lib.bx_host_wait.restype = C.c_int
+  lib.bx_state_create.argtypes = [P, C.c_int64, C.POINTER(P)]
+  lib.bx_state_create.restype = C.c_int
+  lib.bx_state_destroy.argtypes = [P]
+  lib.bx_state_destroy.restype = None
+  lib.bx_state_num_envs.argtypes = [P]
+  lib.bx_state_num_envs.restype = C.c_int64
+  lib.bx_state_set.argtypes = [P, P, P, P, P, P]
+  lib.bx_state_set.restype = C.c_int
+  lib.bx_state_get.argtypes = [P, P, P, P, P, P]
+  lib.bx_state_get.restype = C.c_int
+  lib.bx_state_rollout.argtypes = [P, C.c_int32, C.POINTER(_desc.CStepIO), P]
+  lib.bx_state_rollout.restype = C.c_int
   lib.bx_rollout.argtypes = [P, C.c_int64, C.c_int32,
                              C.POINTER(_desc.CStepIO), P]
   lib.bx_rollout.restype = C.c_int

@@ -377,6 +377,10 @@ class System:
     steps).  The reference shape: `jax.jit(step)` is one dispatch per call (envs/wrappers.py:243)."""
     return Stepper(self, batch, steps_per_replay, graph, info)
 
+  def make_state(self, batch: int) -> 'DeviceState':
+    """An opaque device-resident state of `batch` environments, stepped in place (C ABI `bx_state`)."""
+    return DeviceState(self, batch)
+
   # ---- the step ---------------------------------------------------------------
   def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False, env: bool = False,
            env_rand=None, auto_reset: 'AutoReset' = None, info: bool = True, env_out=None):
@@ -679,6 +683,91 @@ class System:
     if rc != 0:
       raise RuntimeError('bx_step_host: ' + _lib.last_error())
     return self._wrap(out, batched)
+
+
+class DeviceState:
+  """Opaque device-resident state of a batch (`System.make_state`, C ABI `bx_state`): the QP lives
+  inside the library and is stepped in place; only actions go in and env outputs / Info come out.
+
+      st = sys.make_state(batch); st.set(qp)           # qp: torch CUDA tensors [B,N,...]
+      eo = st.rollout(acts, env=True)                   # T steps, ONE launch: obs [T,B,O], reward [T,B] ...
+      qp = st.get()                                     # a copy of the current QP
+
+  The carry of `lax.scan(env.step)` (training/acting.py:53-74) that never crosses the boundary."""
+
+  def __init__(self, system: 'System', batch: int):
+    self.sys, self.batch = system, int(batch)
+    h = C.c_void_p()
+    if system._lib.bx_state_create(system._h, self.batch, C.byref(h)) != 0:
+      raise RuntimeError('bx_state_create: ' + _lib.last_error())
+    self._h = h
+    self._plans = {}
+
+  def __del__(self):
+    h, self._h = getattr(self, '_h', None), None
+    if h:
+      try:
+        self.sys._lib.bx_state_destroy(h)
+      except Exception:
+        pass
+
+  def _stream(self):
+    import torch
+    return C.c_void_p(torch.cuda.current_stream(torch.device('cuda', self.sys.device)).cuda_stream)
+
+  def set(self, qp: QP):
+    import torch
+    n, b = self.sys.num_bodies, self.batch
+    ts = []
+    for t, w in ((qp.pos, 3), (qp.rot, 4), (qp.vel, 3), (qp.ang, 3)):
+      t = t.to(torch.float32).contiguous()
+      if not t.is_cuda or t.numel() != b * n * w:
+        raise ValueError('set() takes CUDA tensors [B,N,%d] of this state\'s batch' % w)
+      ts.append(t)
+    if self.sys._lib.bx_state_set(self._h, *[C.c_void_p(t.data_ptr()) for t in ts], self._stream()) != 0:
+      raise RuntimeError('bx_state_set: ' + _lib.last_error())
+    return self
+
+  def get(self) -> QP:
+    import torch
+    n, b = self.sys.num_bodies, self.batch
+    dev = torch.device('cuda', self.sys.device)
+    out = [torch.empty((b, n, w), dtype=torch.float32, device=dev) for w in (3, 4, 3, 3)]
+    if self.sys._lib.bx_state_get(self._h, *[C.c_void_p(t.data_ptr()) for t in out], self._stream()) != 0:
+      raise RuntimeError('bx_state_get: ' + _lib.last_error())
+    return QP(*out)
+
+  def rollout(self, acts, env: bool = False, info: bool = False, env_rand=None):
+    """acts [T,B,A] (or [B,A] for one step), torch CUDA.  Returns (info of the last step or None,
+    env outputs of every step or None)."""
+    import torch
+    sysm, b = self.sys, self.batch
+    if env and sysm.env is None:
+      raise ValueError('this System was built without an EnvDesc')
+    steps = int(acts.shape[0]) if acts.dim() == 3 else 1
+    acts = acts.to(torch.float32).contiguous()
+    if not acts.is_cuda or acts.numel() != steps * b * sysm.act_size:
+      raise ValueError('acts must be a CUDA tensor [T,%d,%d]' % (b, sysm.act_size))
+    key = (env, steps, info)
+    plan = self._plans.get(key)
+    if plan is None:
+      plan = self._plans[key] = _Plan(sysm._specs(b, False, env, steps, True)[4:] if info
+                                      else sysm._specs(b, False, env, steps, False)[4:])
+    flat = torch.empty(plan.total, dtype=torch.float32, device=acts.device)
+    plan.words[4] = acts.data_ptr()
+    plan.words[plan.out_idx] = plan.out_off + np.uint64(flat.data_ptr())
+    io = plan.io
+    if env_rand is not None:
+      env_rand = env_rand.to(torch.float32).contiguous()
+      io.env_rand = env_rand.data_ptr()
+    else:
+      io.env_rand = None
+    if sysm._lib.bx_state_rollout(self._h, steps, C.byref(io), self._stream()) != 0:
+      raise RuntimeError('bx_state_rollout: ' + _lib.last_error())
+    view = plan.view
+    inf = _LazyInfo({nm: (lambda nm=nm: view(flat, nm)) for nm in plan.names[:9]}) if info else None
+    eo = {k: view(flat, k) for k in ('obs', 'reward', 'done', 'metrics')} if env else None
+    return inf, eo
 
 
 class Stepper:

@@ -405,6 +405,26 @@ int bx_desc_tile_bytes(const bx_system_desc* desc, int64_t* bytes, int32_t* rows
 int bx_rollout(bx_system* sys, int64_t num_envs, int32_t num_steps,
                const bx_step_io* io, void* stream);
 
+/* Opaque device-resident state of B environments ("next" row N2: persistent rollout state).  The handle
+ * owns the QP of the batch on the system's device in a layout of the library's choosing; it is stepped
+ * IN PLACE, so a training / acting loop (training/acting.py:53-74: lax.scan over env.step, the carry
+ * living on the device) never moves the state through the boundary: actions in, env outputs out.
+ *   bx_state_create   allocates the state for num_envs environments (contents undefined until set)
+ *   bx_state_set/get  copy the QP in / out in the boundary layout [B,N,3|4|3|3] (device pointers, async
+ *                     on `stream`)
+ *   bx_state_rollout  num_steps >= 1 steps in ONE launch on the state: io->act is [T,B,A]; io's QP
+ *                     input / output pointers are ignored (must be NULL); every other field of
+ *                     bx_step_io means what it means for bx_rollout (Info of the last step, env outputs
+ *                     of every step, auto-reset inputs, env_rand ...). */
+typedef struct bx_state bx_state;
+int bx_state_create(const bx_system* sys, int64_t num_envs, bx_state** out);
+void bx_state_destroy(bx_state* state);
+int64_t bx_state_num_envs(const bx_state* state);
+int bx_state_set(bx_state* state, const float* pos, const float* rot, const float* vel, const float* ang,
+                 void* stream);
+int bx_state_get(const bx_state* state, float* pos, float* rot, float* vel, float* ang, void* stream);
+int bx_state_rollout(bx_state* state, int32_t num_steps, const bx_step_io* io, void* stream);
+
 /* Kernel launch configuration (tuning knobs; defaults are chosen per system).
  * threads_per_block: multiple of 32 in [32, 512], 0 = keep.
  * contact_section: 0 = keep, 1 = four barrier-separated contact phases,

@@ -217,6 +217,34 @@ def test_env_step_with_host_io(variant):
     env.step(st_h, torch.zeros(b, env.action_size), host_out=hio)
 
 
+def test_device_state_handle_rollouts_equal_plain_rollouts():
+  """bx_state (System.make_state): the QP lives in the library and is stepped in place -- two chained
+  rollouts on the handle == the same rollouts through bx_rollout with the QP passed around (bitwise:
+  obs / reward / done / metrics of every step, Info of the last, the final QP)."""
+  torch = _torch()
+  sysname, env = _env('ant')
+  b, t_n = 700, 5
+  qp, rng = _harvest(env.sys, b, 5, 41)
+  acts = torch.from_numpy(rng.uniform(-1, 1, (2, t_n, b, env.action_size)).astype(np.float32)).cuda()
+  st = env.sys.make_state(b).set(qp)
+  q = qp
+  for r in range(2):
+    q, info_w, eo_w = env.sys.rollout(q, acts[r], env=True)
+    info_g, eo_g = st.rollout(acts[r], env=True, info=True)
+    for k in ('obs', 'reward', 'done', 'metrics'):
+      assert torch.equal(eo_g[k], eo_w[k]), (r, k)
+    assert torch.equal(info_g.contact.vel, info_w.contact.vel) and torch.equal(info_g.contact_pos, info_w.contact_pos)
+  got = st.get()
+  for k in util.QP_KEYS:
+    assert torch.equal(getattr(got, k), getattr(q, k)), k
+  # one step without env outputs, and argument errors
+  st.rollout(acts[0, 0])
+  with pytest.raises(ValueError):
+    st.rollout(acts[0, :, :10])
+  with pytest.raises(ValueError):
+    st.set(type(qp)(qp.pos[:10], qp.rot[:10], qp.vel[:10], qp.ang[:10]))
+
+
 def test_env_rollout_equals_repeated_steps():
   """bx_rollout writes the env outputs of EVERY step: [T,B,...] bit-identical to T
   env steps; ragged and unbatched shapes equal the same envs inside a big batch."""
