@@ -35,6 +35,7 @@ struct bx_system {
   int jc, cc; // joint / contact class of the kernel variant (bx_params.h)
   bool fusable;  // the fused contact section is legal for this system
   int sm_count;
+  int smem_optin;  // sharedMemPerBlockOptin of the device
   // scratch for bx_step_host / bx_rollout
   float* d_scratch;
   size_t scratch_floats;
@@ -803,6 +804,7 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   s->device = device;
   s->warps_chosen = false;
   s->sm_count = prop.multiProcessorCount;
+  s->smem_optin = static_cast<int>(prop.sharedMemPerBlockOptin);
   s->d_scratch = nullptr;
   s->scratch_floats = 0;
   for (int i = 0; i < BX_HOST_STREAMS; i++) s->streams[i] = nullptr;
@@ -923,10 +925,45 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   if (!s || !io) return fail("NULL argument");
   if (num_envs <= 0) return fail("num_envs must be positive");
   if (num_steps < 1) return fail("num_steps must be >= 1");
-  if (!io->pos || !io->rot || !io->vel || !io->ang || !io->act || !io->pos_o || !io->rot_o ||
-      !io->vel_o || !io->ang_o)
+  if (!io->pos || !io->rot || !io->vel || !io->ang || !io->pos_o || !io->rot_o || !io->vel_o || !io->ang_o)
     return fail("QP / act pointers must not be NULL");
+  if (!io->act && !io->policy) return fail("QP / act pointers must not be NULL");
   BxKernelParams p;
+  memset(&p.pol, 0, sizeof(p.pol));
+  p.obs0 = nullptr;
+  p.act_out = nullptr;
+  size_t policy_smem = 0;
+  if (io->policy) {
+    // in-kernel policy (include/brax_b200.h bx_policy): validated here, passed by value
+    const bx_policy& q = *io->policy;
+    if (q.struct_size != sizeof(bx_policy)) return fail("bx_policy size mismatch (ABI skew)");
+    if (!s->h.env_kind) return fail("the in-kernel policy needs a system created with desc.env (it reads the obs)");
+    if (io->observe) return fail("policy and observe exclude each other");
+    if (io->action_repeat > 1) return fail("policy with action_repeat > 1 is not supported");
+    if (q.num_layers < 1 || q.num_layers > BX_POLICY_MAX_LAYERS) return fail("bx_policy.num_layers out of range");
+    if (q.sizes[0] != s->h.seg_out[BX_SEG_ENV].nper) return fail("bx_policy.sizes[0] must be the obs size");
+    int hmax = 0;
+    for (int l = 1; l <= q.num_layers; l++) {
+      if (q.sizes[l] < 1 || q.sizes[l] > 256) return fail("bx_policy layer width out of range (1..256)");
+      hmax = std::max(hmax, q.sizes[l]);
+    }
+    const int outn = q.sizes[q.num_layers];
+    if (outn != s->h.act_size && outn != 2 * s->h.act_size) return fail("bx_policy output width must be A or 2A");
+    if (q.noise && outn != 2 * s->h.act_size) return fail("bx_policy.noise needs a 2A-wide output (loc, scale)");
+    if (q.activation < BX_POLICY_RELU || q.activation > BX_POLICY_TANH) return fail("bx_policy.activation unknown");
+    if (!q.params || !io->obs0) return fail("bx_policy.params and obs0 must not be NULL");
+    p.pol.num_layers = q.num_layers;
+    for (int l = 0; l <= q.num_layers; l++) p.pol.sizes[l] = q.sizes[l];
+    p.pol.activation = q.activation;
+    p.pol.hmax = hmax;
+    p.pol.min_std = q.min_std;
+    p.pol.params = q.params; p.pol.obs_mean = q.obs_mean; p.pol.obs_std = q.obs_std; p.pol.noise = q.noise;
+    p.obs0 = io->obs0;
+    p.act_out = io->act_out;
+    policy_smem = static_cast<size_t>(2) * hmax * BX_ENVS_PER_CTA * sizeof(float);
+    if (s->smem_bytes + policy_smem > static_cast<size_t>(s->smem_optin))
+      return fail("the policy's activation buffers do not fit in shared memory beside the tile");
+  }
   p.h = s->h;
   p.tab_i = s->d_tab_i;
   p.tab_f = s->d_tab_f;
@@ -993,7 +1030,7 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   const int warps = (!s->warps_chosen && tiles <= s->sm_count && s->warps < 16) ? 16 : s->warps;
   cudaError_t le = launch_variant(s->h.mode, s->jc, s->cc | (s->h.env_kind ? BX_CC_ENV : 0) | pdl,
                                   static_cast<unsigned>(tiles), 32 * warps,
-                                  s->smem_bytes, stream, p, three);
+                                  s->smem_bytes + policy_smem, stream, p, three);
   if (cur_dev != s->device) cudaSetDevice(cur_dev);
   g_launches.fetch_add(1);
   CUDA_OK(le);

@@ -8,6 +8,19 @@
 
 #include "bx_tables.h"
 
+// bx_policy by value (include/brax_b200.h): the in-kernel MLP policy of a rollout
+struct BxPolicy {
+  int32_t num_layers;  // 0 = no policy
+  int32_t sizes[9];
+  int32_t activation;
+  int32_t hmax;        // widest layer output: the two activation buffers hold hmax x 32 floats each
+  float min_std;
+  const float* params;
+  const float* obs_mean;
+  const float* obs_std;
+  const float* noise;
+};
+
 struct BxKernelParams {
   BxHeader h;
   const int32_t* tab_i;
@@ -25,6 +38,9 @@ struct BxKernelParams {
   float episode_length;
   int observe;                 // env builds: skip the substeps (obs of the state passed in)
   int action_repeat;           // EpisodeWrapper.action_repeat (auto-reset launches), >= 1
+  BxPolicy pol;                // in-kernel policy (env builds), pol.num_layers == 0: none
+  const float* obs0;           // [B,O] obs of the state passed in (policy launches)
+  float* act_out;              // [T,B,A] actions the policy chose, or NULL
   int64_t num_envs;
   int32_t num_steps;  // >1: rollout, act is [T,B,A]
   // host path only (bx_step_host on mapped host memory): tile i starts i/grid of

@@ -1657,6 +1657,87 @@ static __device__ __noinline__ void phase_env(const Ctx c, const BxHeader& h) {
   }
 }
 
+// ---- optional in-kernel policy (include/brax_b200.h bx_policy): actions = policy(obs) -----------------
+// The reference's acting loop (training/acting.py:53-74) evaluates the policy MLP (training/networks.py:83-102)
+// on the normalised obs and feeds NormalTanhDistribution's mode / sample (training/distribution.py:131-158) to
+// env.step.  Here: lane = env as everywhere; the warps split the units of a layer in chunks of four (four
+// independent accumulators per lane; the weights are warp-uniform read-only loads), the activations of a
+// layer sit in one of two shared-memory buffers [unit][lane], a CTA barrier separates the layers.  The obs of
+// the first step comes from obs0, later steps read the rows the previous step's env epilogue left in shared
+// memory through the obs map (envs the auto-reset restarted read first_obs).  Writes the actions into the act
+// quads (and act_out).  Called by ALL warps; ends with a barrier.
+BXS float policy_act(int kind, float x) {
+  if (kind == BX_POLICY_RELU) return fmaxf(x, 0.f);
+  if (kind == BX_POLICY_TANH) return tanhf(x);
+  return bx_div(x, 1.f + __expf(-x));   // swish: x * sigmoid(x)
+}
+template <int MODE>
+static __device__ __noinline__ void policy_forward(const Ctx c, const BxHeader& h, const BxKernelParams& p, float* pbuf,
+                                                   const float* smf, int t, int64_t env0, int nenv, bool restarted) {
+  const BxPolicy& q = p.pol;
+  const int lane = threadIdx.x & 31;
+  const bool live = lane < nenv;
+  const int64_t e = env0 + lane;
+  const int no = q.sizes[0];
+  const BxSeg sg = h.seg_out[BX_SEG_ENV];
+  const int32_t* omap = c.ti + sg.map;
+  const float* obs_g = t == 0 ? p.obs0 : (restarted ? p.first_obs : nullptr);   // global source of this lane's obs
+  const float* w = q.params;
+  float* bufs[2] = {pbuf, pbuf + q.hmax * 32};
+  for (int l = 0; l < q.num_layers; l++) {
+    const int nin = q.sizes[l], nout = q.sizes[l + 1];
+    const float* bias = w + static_cast<size_t>(nin) * nout;
+    const float* xin = bufs[(l + 1) & 1];
+    float* xout = bufs[l & 1];
+    for (int u0 = 4 * c.warp; u0 < nout; u0 += 4 * c.nwarp) {
+      float acc[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) acc[j] = u0 + j < nout ? __ldg(bias + u0 + j) : 0.f;
+#pragma unroll 2
+      for (int k = 0; k < nin; k++) {
+        float x;
+        if (l == 0) {
+          if (obs_g != nullptr) {
+            x = live ? obs_g[e * no + k] : 0.f;
+          } else {
+            const int m = omap[k];
+            x = m >= 0 ? smf[m + 4 * lane] : sg.fill;
+          }
+          if (q.obs_mean != nullptr) x -= __ldg(q.obs_mean + k);
+          if (q.obs_std != nullptr) x = bx_div(x, __ldg(q.obs_std + k));
+        } else {
+          x = xin[k * 32 + lane];
+        }
+        const float* wk = w + static_cast<size_t>(k) * nout + u0;
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+          if (u0 + j < nout) acc[j] = fmaf(__ldg(wk + j), x, acc[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (u0 + j < nout) xout[(u0 + j) * 32 + lane] = l + 1 < q.num_layers ? policy_act(q.activation, acc[j]) : acc[j];
+    }
+    w = bias + nout;
+    __syncthreads();
+  }
+  // NormalTanhDistribution: loc = out[:A], scale = softplus(out[A:]) + min_std; mode / sample, then tanh
+  const float* out = bufs[(q.num_layers - 1) & 1];
+  const int na = h.act_size;
+  for (int a = c.warp; a < na; a += c.nwarp) {
+    float loc = out[a * 32 + lane];
+    if (q.noise != nullptr) {
+      const float raw = out[(na + a) * 32 + lane];
+      const float scale = (raw > 20.f ? raw : log1pf(__expf(raw))) + q.min_std;   // softplus
+      const float eps = live ? q.noise[(static_cast<int64_t>(t) * p.num_envs + e) * na + a] : 0.f;
+      loc = fmaf(scale, eps, loc);
+    }
+    const float act = tanhf(loc);
+    *act_ptr(c, h, a) = act;
+    if (p.act_out != nullptr && live) p.act_out[(static_cast<int64_t>(t) * p.num_envs + e) * na + a] = act;
+  }
+  __syncthreads();
+}
+
 // ============================== the kernel ====================================
 // The whole step of one tile of 32 environments (called by bx_step_kernel below).
 template <int MODE>
@@ -1694,23 +1775,26 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
   uint64_t* mbar = reinterpret_cast<uint64_t*>(ti + h.n_ints);
   float* stage = smf + h.q_js * QS * 4;  // JS.. regions are dead outside the substep loop
   const bool full = nenv == BX_ENVS_PER_CTA;
+  // env builds with an in-kernel policy: the actions are computed in the launch, `act` is not read
+  const bool policy_on = (BX_FEAT & BXF_ENV) != 0 && p.pol.num_layers > 0;
+  const int n_in = policy_on ? BX_SEG_IN - 1 : BX_SEG_IN;   // (act is the last input segment)
   bool in_bulk = full;
 #pragma unroll
-  for (int s = 0; s < BX_SEG_IN; s++) in_bulk = in_bulk && span_bulk_ok(h.seg_in[s], p.in[s], env0);
+  for (int s = 0; s < BX_SEG_IN; s++) in_bulk = in_bulk && (s >= n_in || span_bulk_ok(h.seg_in[s], p.in[s], env0));
   uint32_t phase = 0;
   if (threadIdx.x == 0) mbar_init(mbar, 1);
   __syncthreads();
   if (threadIdx.x == 0) {
     uint32_t bytes = h.n_fquads * 16 + h.n_ints * 4;
     if (in_bulk)
-      for (int s = 0; s < BX_SEG_IN; s++) bytes += 4 * BX_ENVS_PER_CTA * h.seg_in[s].nper;
+      for (int s = 0; s < n_in; s++) bytes += 4 * BX_ENVS_PER_CTA * h.seg_in[s].nper;
     mbar_expect_tx(mbar, bytes);
     bulk_g2s(tf, p.tab_f, h.n_fquads * 16, mbar);  // static tables: not produced by a kernel
     bulk_g2s(ti, p.tab_i, h.n_ints * 4, mbar);
     pdl_wait();  // the inputs may be the previous launch's outputs
     if (in_bulk) {
       int off = 0;
-      for (int s = 0; s < BX_SEG_IN; s++) {
+      for (int s = 0; s < n_in; s++) {
         const int n = BX_ENVS_PER_CTA * h.seg_in[s].nper;
         if (n) bulk_g2s(stage + off, p.in[s] + env0 * h.seg_in[s].nper, 4 * n, mbar);
         off += n;
@@ -1735,14 +1819,14 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
   phase ^= 1;
   PT(0);
   if (in_bulk) {
-    for (int s = threadIdx.x >> 5; s < BX_SEG_IN; s += blockDim.x >> 5) {
+    for (int s = threadIdx.x >> 5; s < n_in; s += blockDim.x >> 5) {
       int off = 0;
       for (int t = 0; t < s; t++) off += BX_ENVS_PER_CTA * h.seg_in[t].nper;
       unstage_warp(smf, ti, h.seg_in[s], stage + off, threadIdx.x & 31);
     }
   } else {
 #pragma unroll 1
-    for (int s = 0; s < BX_SEG_IN; s++)
+    for (int s = 0; s < n_in; s++)
       if (h.seg_in[s].nper)
         io_segment_scalar<true>(smf, ti, h.seg_in[s], const_cast<float*>(p.in[s]), env0, nenv);
   }
@@ -1787,7 +1871,14 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
   for (int step = 0; step < p.num_steps; step++) {
     const int ot = step / repeat, rep = step - ot * repeat;
     __syncthreads();
-    if (step > 0 && rep == 0) {  // rollout: the actions of step t (step 0 came with the state)
+    if (policy_on) {
+      // actions of this step from the policy: obs of the previous step (obs0 for the first; first_obs for
+      // envs the auto-reset restarted at the end of the previous step)
+      float* pbuf = reinterpret_cast<float*>(mbar + 2);
+      const bool restarted = step > 0 && p.first[0] != nullptr && (threadIdx.x & 31) < nenv &&
+                             sq[(h.q_env + EQ_S0) * QS + (threadIdx.x & 31)].y > 0.f;
+      policy_forward<MODE>(c, h, p, pbuf, smf, step, env0, nenv, restarted);
+    } else if (step > 0 && rep == 0) {  // rollout: the actions of step t (step 0 came with the state)
       const float* act = p.in[4] + static_cast<int64_t>(ot) * p.num_envs * h.act_size;
       const BxSeg sg = h.seg_in[4];
       if (full && span_bulk_ok(sg, act, env0)) {

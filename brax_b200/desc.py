@@ -20,7 +20,7 @@ from typing import Any, Dict, List
 
 import numpy as np
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 MODE = {'pbd': 0, 'legacy_spring': 1}
 JOINT_KIND = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
@@ -111,7 +111,17 @@ class CStepIO(C.Structure):
       'actuator_ang', 'contact_pos', 'contact_normal', 'contact_penetration',
       'joint_angle', 'joint_velocity', 'obs', 'reward', 'done', 'metrics', 'env_rand',
       'first_pos', 'first_rot', 'first_vel', 'first_ang', 'first_obs', 'done_in', 'steps_in',
-      'steps_out', 'truncation')] + [('episode_length', C.c_float), ('observe', C.c_int32), ('action_repeat', C.c_int32)]
+      'steps_out', 'truncation', 'policy', 'obs0', 'act_out')] + [('episode_length', C.c_float), ('observe', C.c_int32), ('action_repeat', C.c_int32)]
+
+
+POLICY_MAX_LAYERS = 8
+POLICY_ACT = {'relu': 0, 'swish': 1, 'tanh': 2}
+
+
+class CPolicy(C.Structure):
+  _fields_ = [('struct_size', C.c_uint32), ('num_layers', C.c_int32), ('sizes', C.c_int32 * (POLICY_MAX_LAYERS + 1)),
+              ('activation', C.c_int32), ('min_std', C.c_float), ('params', C.c_void_p), ('obs_mean', C.c_void_p),
+              ('obs_std', C.c_void_p), ('noise', C.c_void_p)]
 
 
 def _f(x):

@@ -22,7 +22,7 @@ from typing import Any, Tuple
 import numpy as np
 
 from brax_b200 import lib as _lib
-from brax_b200.desc import CStepIO, SystemDesc
+from brax_b200.desc import POLICY_ACT, POLICY_MAX_LAYERS, CPolicy, CStepIO, SystemDesc
 
 
 @dataclasses.dataclass
@@ -137,6 +137,57 @@ class AutoReset:
   steps: Any = None         # state.info['steps'] [B] (None: zeros)
   episode_length: int = 0   # EpisodeWrapper.episode_length; 0 = no EpisodeWrapper
   action_repeat: int = 1    # EpisodeWrapper.action_repeat (wrappers.py:106-111)
+
+
+@dataclasses.dataclass
+class Policy:
+  """An MLP policy evaluated INSIDE a rollout launch (C ABI `bx_policy`): the reference's policy network
+  (training/networks.py:83-102) on the normalised obs, NormalTanhDistribution's mode or sample
+  (training/distribution.py:131-158) as the action.
+
+  params: list of (W [in, out], b [out]) torch CUDA tensors per dense layer (flax `kernel`, `bias`), or one
+  flat float32 CUDA tensor already in the ABI's order; the last layer is 2A wide (loc, scale) or A (loc).
+  obs_mean / obs_std: [O] CUDA tensors or None.  activation: 'relu' | 'swish' | 'tanh' (hidden layers)."""
+  params: Any
+  sizes: Any = None          # [O, h0, ..., out]; inferred from a list of (W, b)
+  activation: str = 'swish'
+  obs_mean: Any = None
+  obs_std: Any = None
+  min_std: float = 0.001
+
+  def pack(self):
+    """-> (CPolicy without noise, tensors to keep alive)."""
+    import torch
+    if isinstance(self.params, (list, tuple)):
+      sizes = [int(self.params[0][0].shape[0])] + [int(w.shape[1]) for w, _ in self.params]
+      flat = torch.cat([torch.cat([w.to(torch.float32).contiguous().reshape(-1), b.to(torch.float32).reshape(-1)])
+                        for w, b in self.params])
+    else:
+      sizes, flat = [int(x) for x in self.sizes], self.params.to(torch.float32).contiguous()
+    if not 2 <= len(sizes) <= POLICY_MAX_LAYERS + 1:
+      raise ValueError('a policy has 1..%d dense layers' % POLICY_MAX_LAYERS)
+    if flat.numel() != sum(sizes[i] * sizes[i + 1] + sizes[i + 1] for i in range(len(sizes) - 1)):
+      raise ValueError('params do not match sizes %s' % sizes)
+    if not flat.is_cuda:
+      raise RuntimeError('policy parameters must live on the GPU (no CPU fallback)')
+    cp = CPolicy()
+    cp.struct_size = C.sizeof(CPolicy)
+    cp.num_layers = len(sizes) - 1
+    for i, v in enumerate(sizes):
+      cp.sizes[i] = v
+    cp.activation = POLICY_ACT[self.activation]
+    cp.min_std = float(self.min_std)
+    keep = [flat]
+    cp.params = flat.data_ptr()
+    for name in ('obs_mean', 'obs_std'):
+      t = getattr(self, name)
+      if t is not None:
+        t = t.to(torch.float32).contiguous()
+        if t.numel() != sizes[0] or not t.is_cuda:
+          raise ValueError('%s must be a CUDA tensor of %d elements' % (name, sizes[0]))
+        keep.append(t)
+        setattr(cp, name, t.data_ptr())
+    return cp, keep
 
 
 class HostBuffers:
@@ -452,7 +503,7 @@ class System:
     return int(h2d.value), int(d2h.value)
 
   def rollout(self, qp: QP, acts, env: bool = False, env_rand=None, auto_reset: 'AutoReset' = None,
-              info: bool = True):
+              info: bool = True, policy: 'Policy' = None, obs0=None, noise=None, steps: int = None):
     """T steps in ONE launch; acts is [T, B, A] (torch CUDA).  Returns the final
     QP and the Info of the last step (lax.scan of System.step over actions); with
     env=True also the env epilogue of EVERY step: obs [T,B,O], reward / done [T,B],
@@ -462,6 +513,14 @@ class System:
       raise ValueError('this System was built without an EnvDesc')
     if auto_reset is not None and not env:
       raise ValueError('auto_reset needs env=True')
+    if policy is not None:
+      # acts=None: the actions of every step come from `policy` evaluated inside the launch on the obs of
+      # the previous step (obs0 [B,O] = state.obs for the first); the env dict gains 'action' [T,B,A].
+      # noise: optional standard normal draws [T,B,A] (stochastic actions); steps: T.
+      if not env or obs0 is None or steps is None:
+        raise ValueError('a policy rollout needs env=True, obs0 and steps')
+      return self._step_torch(qp, None, int(steps), False, True, env_rand, auto_reset, info,
+                              policy=(policy, obs0, noise))
     return self._step_torch(qp, acts, int(acts.shape[0]), False, env, env_rand, auto_reset, info)
 
   def _shapes(self, pos_shape):
@@ -523,7 +582,7 @@ class System:
     io.action_repeat = 0
 
   def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False, env_rand=None,
-                  auto_reset=None, info: bool = True, observe: bool = False, env_out=None):
+                  auto_reset=None, info: bool = True, observe: bool = False, env_out=None, policy=None):
     """env_rand: (fetch / grasp) uniforms of the target teleport, [B,3] or [T,B,3].
 
     Host cost per call is what bounds a plain Python stepping loop (the kernel takes ~57 us for
@@ -551,7 +610,7 @@ class System:
       return t
 
     ins = (prep(qp.pos, b * n * 3), prep(qp.rot, b * n * 4), prep(qp.vel, b * n * 3),
-           prep(qp.ang, b * n * 3), prep(act, steps * b * a))
+           prep(qp.ang, b * n * 3), prep(act, steps * b * a) if policy is None else qp.pos)
     if ins[4].device.type != 'cuda' and not ins[4].is_pinned():
       raise RuntimeError('host actions must be page-locked (pin_memory): the launch reads them over PCIe')
     ext = env_out is not None
@@ -592,6 +651,22 @@ class System:
       io.episode_length = 0.0
       io.action_repeat = 0
     io.observe = int(observe)
+    pol_keep = None
+    if policy is not None:
+      pol, obs0, noise = policy
+      cp, pol_keep = pol.pack()
+      obs0 = prep(obs0, b * self.obs_size)
+      act_out = torch.empty((steps, b, a) if steps > 1 else (b, a), dtype=f32, device=dev)
+      if noise is not None:
+        noise = prep(noise, steps * b * a)
+        cp.noise = noise.data_ptr()
+      pol_keep += [obs0, noise, act_out, cp]
+      w[4] = 0                      # act: not read
+      io.policy = C.addressof(cp)
+      io.obs0 = obs0.data_ptr()
+      io.act_out = act_out.data_ptr()
+    elif io.policy:
+      io.policy = io.obs0 = io.act_out = None
     if ext:
       for nm, cnt in (('obs', b * self.obs_size), ('reward', b), ('done', b), ('metrics', b * self.num_metrics)):
         t = env_out[nm]
@@ -624,6 +699,8 @@ class System:
       res += (JointState(view(flat, 'joint_angle'), view(flat, 'joint_velocity')),)
     if env:
       eo = dict(env_out) if ext else {k: view(flat, k) for k in ('obs', 'reward', 'done', 'metrics')}
+      if policy is not None:
+        eo['action'] = pol_keep[-2]
       if extra is not None:
         eo['steps'] = extra[:b].view((b,))
         eo['truncation'] = extra[b:].view((steps, b) if steps > 1 else (b,))

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BX_ABI_VERSION 9
+#define BX_ABI_VERSION 10
 
 /* dynamics_mode (base.py:179-201) */
 #define BX_MODE_PBD 0
@@ -256,6 +256,35 @@ typedef struct bx_system_desc {
 
 typedef struct bx_system bx_system; /* opaque; owns device copies of tables */
 
+/* Optional in-kernel policy of a rollout ("next" row N2: "T steps per launch with actions [T,B,A] or an
+ * in-kernel MLP policy"): the acting loop of training/acting.py:53-74 -- actions = policy(obs),
+ * state = env.step(state, actions) -- with the policy evaluated INSIDE the launch between the env steps, so a
+ * whole unroll is one launch and neither obs nor actions cross the boundary between steps.
+ * The network is the reference's policy MLP (training/networks.py:83-102: dense layers, the activation after
+ * every layer but the last) on the normalised observation (obs - mean) / std
+ * (training/acme/running_statistics.py `normalize`), its output the parameters of NormalTanhDistribution
+ * (training/distribution.py:131-158): loc = out[:A], scale = softplus(out[A:2A]) + min_std;
+ *   action = tanh(loc)                      (deterministic, `noise` NULL -- the distribution's mode)
+ *   action = tanh(loc + scale * noise)      (`noise` = the caller's standard normal draws [T,B,A])
+ * params: per layer l the weight matrix W_l[sizes[l]][sizes[l+1]] row-major followed by the bias
+ * b_l[sizes[l+1]] (flax Dense `kernel`, `bias`), all layers concatenated, float32, device memory. */
+#define BX_POLICY_MAX_LAYERS 8
+#define BX_POLICY_RELU 0
+#define BX_POLICY_SWISH 1
+#define BX_POLICY_TANH 2
+typedef struct bx_policy {
+  uint32_t struct_size;  /* = sizeof(bx_policy), checked */
+  int32_t num_layers;    /* dense layers including the output layer, 1..BX_POLICY_MAX_LAYERS */
+  int32_t sizes[BX_POLICY_MAX_LAYERS + 1]; /* sizes[0] = obs size O; sizes[l+1] = width of layer l (<= 256);
+                                              the last is 2A (loc, scale) or A (loc only) */
+  int32_t activation;    /* BX_POLICY_* of the hidden layers */
+  float min_std;         /* NormalTanhDistribution min_std (0.001) */
+  const float* params;   /* device */
+  const float* obs_mean; /* device [O] or NULL */
+  const float* obs_std;  /* device [O] or NULL */
+  const float* noise;    /* device [T,B,A] or NULL */
+} bx_policy;
+
 /* Device-side I/O of one batched step.  All pointers are DEVICE pointers,
  * float32, C-contiguous.  Shapes: N bodies, A act_size, K contact rows. */
 typedef struct bx_step_io {
@@ -299,6 +328,13 @@ typedef struct bx_step_io {
   const float* steps_in;  /* state.info['steps'] [B] (NULL: zeros) */
   float* steps_out;       /* [B] */
   float* truncation;      /* state.info['truncation'] [B] ([T,B] in a rollout) */
+  /* Optional in-kernel policy (systems with desc.env; bx_step / bx_rollout / bx_state_rollout; NULL = the
+   * actions come from `act`).  With it `act` is ignored (may be NULL): step t's action is computed in the
+   * launch from the obs of step t-1 (first_obs for envs the auto-reset restarted) -- obs0 [B,O] = state.obs
+   * for the first step -- and written to act_out [T,B,A] if given. */
+  const bx_policy* policy; /* HOST pointer to the descriptor (its array pointers are device pointers) */
+  const float* obs0;
+  float* act_out;
   float episode_length;   /* EpisodeWrapper.episode_length; 0 = no episode limit */
   /* Non-zero (systems with desc.env, bx_step only): no physics -- the launch evaluates
    * info = System.info(qp) of the state passed in (system.py:327-340 / :378-390: the contact rows and

@@ -217,6 +217,94 @@ def test_env_step_with_host_io(variant):
     env.step(st_h, torch.zeros(b, env.action_size), host_out=hio)
 
 
+def _mlp(torch, sizes, seed, scale=1.0):
+  g = torch.Generator(device='cuda'); g.manual_seed(seed)
+  return [((torch.rand(sizes[i], sizes[i + 1], generator=g, device='cuda') * 2 - 1) * scale * (3.0 / sizes[i]) ** 0.5,
+           (torch.rand(sizes[i + 1], generator=g, device='cuda') * 2 - 1) * 0.1) for i in range(len(sizes) - 1)]
+
+
+def _policy_torch(torch, params, act_fn, obs, mean, std, na, noise=None, min_std=0.001):
+  """training/networks.py:83-102 + distribution.py:131-158 in torch float32 (the checker of the in-kernel policy)."""
+  x = (obs - mean) / std
+  for i, (w, b) in enumerate(params):
+    x = x @ w + b
+    if i < len(params) - 1:
+      x = {'relu': torch.relu, 'tanh': torch.tanh, 'swish': lambda v: v * torch.sigmoid(v)}[act_fn](x)
+  loc = x[:, :na]
+  if noise is not None:
+    loc = loc + (torch.nn.functional.softplus(x[:, na:]) + min_std) * noise
+  return torch.tanh(loc)
+
+
+@pytest.mark.parametrize('variant,act_fn,hidden', [('ant', 'swish', (32, 32, 32, 32)), ('humanoid', 'relu', (64, 48)),
+                                                   ('grasp', 'tanh', (40,))])
+def test_in_kernel_policy_rollout_equals_acting_loop(variant, act_fn, hidden):
+  """bx_policy: T steps of actions = policy(obs); state = env.step(state, actions) in ONE launch == the
+  acting loop (training/acting.py:53-74) with the policy evaluated in torch between single-step launches:
+  the first step's actions to float32 rounding, the following steps within the growth of that rounding."""
+  torch = _torch()
+  from brax_b200.envs import State
+  from brax_b200.system import Policy
+  sysname, env = _env(variant)
+  b, t_n = 333, 5
+  na, no = env.action_size, env.observation_size
+  qp, rng = _harvest(env.sys, b, 5, 51)
+  if env.env.kind == 'grasp':
+    pos = qp.pos.clone()
+    pos[:, env.env.target_body] = pos[:, env.env.object_body] + torch.tensor([8.0, 3.0, 1.0], device='cuda')
+    qp = type(qp)(pos, qp.rot, qp.vel, qp.ang)
+  params = _mlp(torch, (no,) + hidden + (2 * na,), 7)
+  mean = torch.from_numpy(rng.uniform(-.2, .2, no).astype(np.float32)).cuda()
+  std = torch.from_numpy(rng.uniform(.5, 2., no).astype(np.float32)).cuda()
+  obs0 = env.sys.observe(qp)
+  for noise in (None, torch.from_numpy(rng.standard_normal((t_n, b, na)).astype(np.float32)).cuda()):
+    pol = Policy(params, activation=act_fn, obs_mean=mean, obs_std=std)
+    q2, _, eo = env.sys.rollout(qp, None, env=True, policy=pol, obs0=obs0, noise=noise, steps=t_n, info=False)
+    torch.cuda.synchronize()
+    assert eo['action'].shape == (t_n, b, na) and eo['obs'].shape == (t_n, b, no)
+    st, obs = State(qp, obs0, None, None), obs0
+    for t in range(t_n):
+      a = _policy_torch(torch, params, act_fn, obs, mean, std, na, None if noise is None else noise[t])
+      tol = 2e-5 * (4 ** t)
+      assert float((eo['action'][t] - a).abs().max()) <= tol + 1e-3 * (t > 0), (variant, t, float((eo['action'][t] - a).abs().max()))
+      st = env.step(st, eo['action'][t].contiguous())     # the kernel's own action: the env step itself is bitwise
+      assert torch.equal(st.obs, eo['obs'][t]), (variant, t)
+      assert torch.equal(st.reward, eo['reward'][t])
+      obs = st.obs
+    assert torch.equal(st.qp.pos, q2.pos)
+  with pytest.raises(RuntimeError, match='obs size'):
+    env.sys.rollout(qp, None, env=True, policy=Policy(_mlp(torch, (no + 1, 8, 2 * na), 1)), obs0=obs0, steps=2)
+
+
+def test_in_kernel_policy_with_auto_reset():
+  """Policy rollout under EpisodeWrapper + AutoResetWrapper in the launch: an env that was restarted acts on
+  first_obs at the next step (wrappers.py:147), exactly like the acting loop around the wrapped env."""
+  torch = _torch()
+  from brax_b200.system import AutoReset, Policy
+  sysname, env = _env('ant')
+  b, t_n, length = 256, 6, 3
+  na, no = env.action_size, env.observation_size
+  qp, rng = _harvest(env.sys, b, 5, 53)
+  params = _mlp(torch, (no, 32, 2 * na), 9)
+  one = torch.ones(no, device='cuda')
+  pol = Policy(params, activation='relu')
+  first_qp = type(qp)(*[getattr(qp, k).clone() for k in util.QP_KEYS])
+  first_obs = env.sys.observe(first_qp)
+  steps0 = torch.from_numpy(rng.integers(0, length, b).astype(np.float32)).cuda()
+  ar = AutoReset(first_qp, first_obs, torch.zeros(b, device='cuda'), steps0, length)
+  q2, _, eo = env.sys.rollout(qp, None, env=True, policy=pol, obs0=first_obs, steps=t_n, auto_reset=ar, info=False)
+  q, obs, done, steps = qp, first_obs, torch.zeros(b, device='cuda'), steps0
+  for t in range(t_n):
+    a = _policy_torch(torch, params, 'relu', obs, 0 * one, one, na)
+    assert float((eo['action'][t] - a).abs().max()) <= 1e-4, t
+    q, _, e1 = env.sys.step(q, eo['action'][t].contiguous(), env=True, info=False,
+                            auto_reset=AutoReset(first_qp, first_obs, done, steps, length))
+    assert torch.equal(e1['obs'], eo['obs'][t]) and torch.equal(e1['done'], eo['done'][t]), t
+    obs, done, steps = e1['obs'], e1['done'], e1['steps']
+  assert float(eo['done'].sum()) > 0     # episodes did end and restart inside the launch
+  assert torch.equal(q.pos, q2.pos)
+
+
 def test_device_state_handle_rollouts_equal_plain_rollouts():
   """bx_state (System.make_state): the QP lives in the library and is stepped in place -- two chained
   rollouts on the handle == the same rollouts through bx_rollout with the QP passed around (bitwise:
