@@ -585,7 +585,7 @@ def run_gpu(args, desc):
   ms_av = timed_chunks(av_step)
   # "next" row N1: the whole Env.step (sys.step + obs / reward / done / metrics of
   # envs/ant.py:222-281, envs/humanoid.py:246-340) as ONE launch; same timing method.
-  ms_env, ms_wenv, ms_reset, env_obs = 0.0, 0.0, 0.0, 0
+  ms_env, ms_wenv, ms_reset, env_obs, ms_pol = 0.0, 0.0, 0.0, 0, 1.0
   last_reward = None
   env_name = args.env[:-len('_spring')] if args.env.endswith('_spring') else args.env
   if env_name in ('ant', 'humanoid', 'fetch', 'grasp') and args.env != 'grasp_spring':
@@ -628,6 +628,33 @@ def run_gpu(args, desc):
       sts[j] = wenv.step(sts[j], acts[args.warmup + i])
     ms_wenv = timed_chunks(wrapped_step)
     qps = [st.qp for st in sts]
+    # "next" row N2 with the policy inside the launch (bx_policy): the acting loop of training/acting.py:53-74 with
+    # PPO's default policy network (ppo/networks.py:67-69: 4 x 32 swish, 2A outputs), sampled actions
+    # (caller-supplied N(0,1) noise), observation normalisation on; T = 10 steps per launch, env outputs every step
+    from brax_b200.system import Policy
+    sizes = (env_obs, 32, 32, 32, 32, 2 * desc.act_size)
+    pol = Policy([((torch.rand(sizes[i], sizes[i + 1], device=dev) * 2 - 1) * (3.0 / sizes[i]) ** 0.5,
+                   torch.zeros(sizes[i + 1], device=dev)) for i in range(len(sizes) - 1)], activation='swish',
+                 obs_mean=torch.zeros(env_obs, device=dev), obs_std=torch.ones(env_obs, device=dev))
+    pol_noise = torch.randn(10, b, desc.act_size, device=dev)
+    pol_sets = min(nsets, max(2, -(-2 * 126_000_000 // (b * 10 * 4 * (env_obs + 2 * desc.act_size + 8)))))
+    pol_obs = [env.sys.observe(q) for q in qps[:pol_sets]]
+    n_pol = max(5, args.steps // 10)
+    def policy_rollout(i):
+      j = i % pol_sets
+      qps[j], _, eo = env.sys.rollout(qps[j], None, env=True, policy=pol, obs0=pol_obs[j], noise=pol_noise, steps=10,
+                                      info=False)
+      pol_obs[j].copy_(eo['obs'][-1])    # (a view would pin the whole [T,B,obs] block: a fresh cudaMalloc per launch)
+    for i in range(2 * pol_sets):        # also warms torch's caching allocator: no cudaMalloc in the timed launches
+      policy_rollout(i)
+    barrier()
+    pe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_pol)]
+    for i, (x, y) in enumerate(pe):
+      x.record()
+      policy_rollout(i)
+      y.record()
+    torch.cuda.synchronize()
+    ms_pol = sorted(x.elapsed_time(y) for x, y in pe)[n_pol // 2]
     # "next" row N3: Env.reset on the GPU (noisy joint state -> bx_default_qp -> observe launch)
     for i in range(3):
       env.reset(b, device=dev, seed=i)
@@ -807,6 +834,11 @@ def run_gpu(args, desc):
                       'with_episode_and_auto_reset_wrappers': {
                           'value': world * b * args.steps / (ms_wenv * 1e-3), 'unit': UNIT,
                           'ms_per_step': ms_wenv / args.steps, 'episode_length': 1000},
+                      'policy_rollout': {
+                          'value': world * b * 10 / (ms_pol * 1e-3), 'unit': UNIT, 'ms_per_step': ms_pol / 10,
+                          'steps_per_launch': 10, 'timing': 'median launch',
+                          'what': 'actions = policy(obs); state = env.step(state, actions) x 10 in one launch (bx_policy: '
+                                  'normalize -> MLP 4 x 32 swish -> tanh-normal sample), no actions read from memory'},
                       'reset_ms': ms_reset,
                       'reset_what': 'Env.reset of the whole batch through the Python mirror (host-bound at this size): '
                                     'joint noise, bx_default_qp forward kinematics, observe launch'} if ms_env > 0 else None),

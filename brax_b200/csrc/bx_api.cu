@@ -933,6 +933,7 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   p.obs0 = nullptr;
   p.act_out = nullptr;
   size_t policy_smem = 0;
+  bool policy_one_tile = false;   // the policy's buffers leave room for one tile per SM only
   if (io->policy) {
     // in-kernel policy (include/brax_b200.h bx_policy): validated here, passed by value
     const bx_policy& q = *io->policy;
@@ -960,9 +961,21 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
     p.pol.params = q.params; p.pol.obs_mean = q.obs_mean; p.pol.obs_std = q.obs_std; p.pol.noise = q.noise;
     p.obs0 = io->obs0;
     p.act_out = io->act_out;
-    policy_smem = static_cast<size_t>(2) * hmax * BX_ENVS_PER_CTA * sizeof(float);
-    if (s->smem_bytes + policy_smem > static_cast<size_t>(s->smem_optin))
-      return fail("the policy's activation buffers do not fit in shared memory beside the tile");
+    // the normalised obs is staged whole when that keeps the tile's occupancy, else in chunks of 128 / 64 /
+    // 32 rows (two more barriers per chunk): the largest that still lets two tiles share an SM, or fits at all
+    const bool two_now = 2 * (s->smem_bytes + 1024) <= 233472;
+    const int cand[4] = {q.sizes[0], 128, 64, 32};
+    int rows = 0;
+    for (int pass = two_now ? 0 : 1; pass < 2 && !rows; pass++)
+      for (int i = 0; i < 4 && !rows; i++) {
+        if (cand[i] > q.sizes[0]) continue;
+        const size_t total = s->smem_bytes + BX_POLICY_SMEM(cand[i], hmax);
+        if (pass == 0 ? 2 * (total + 1024) <= 233472 : total <= static_cast<size_t>(s->smem_optin)) rows = cand[i];
+      }
+    if (!rows) return fail("the policy's activation buffers do not fit in shared memory beside the tile");
+    p.pol.obs_rows = rows;
+    policy_smem = BX_POLICY_SMEM(rows, hmax);
+    policy_one_tile = 2 * (s->smem_bytes + policy_smem + 1024) > 233472;
   }
   p.h = s->h;
   p.tab_i = s->d_tab_i;
@@ -1027,7 +1040,8 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   // takes 16 warps with the one-tile register budget -- every phase's items in one round (measured at
   // 4096 envs: grasp 38.9 -> 34.9 us, humanoid 55.3 -> 49.8, fetch 34.2 -> 30.8, ant 44.0 -> 43.0).
   // An explicit bx_system_configure / autotune choice is kept.
-  const int warps = (!s->warps_chosen && tiles <= s->sm_count && s->warps < 16) ? 16 : s->warps;
+  // The same holds when the in-kernel policy's buffers leave room for one tile per SM only (humanoid).
+  const int warps = (!s->warps_chosen && (tiles <= s->sm_count || policy_one_tile) && s->warps < 16) ? 16 : s->warps;
   cudaError_t le = launch_variant(s->h.mode, s->jc, s->cc | (s->h.env_kind ? BX_CC_ENV : 0) | pdl,
                                   static_cast<unsigned>(tiles), 32 * warps,
                                   s->smem_bytes + policy_smem, stream, p, three);

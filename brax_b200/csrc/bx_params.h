@@ -9,11 +9,17 @@
 #include "bx_tables.h"
 
 // bx_policy by value (include/brax_b200.h): the in-kernel MLP policy of a rollout
+#define BX_POLICY_KBLOCK 32     // weight rows a warp stages per block (4 units wide)
+#define BX_POLICY_MAX_WARPS 16  // slices are laid out for the widest launch
+// shared memory of the in-kernel policy beside the tile: weight slices, normalised obs, two activation buffers
+#define BX_POLICY_SMEM(obs_rows, hmax) \
+  (16 + sizeof(float) * (BX_POLICY_MAX_WARPS * 4 * BX_POLICY_KBLOCK + 32 * ((obs_rows) + 2 * (hmax))))
 struct BxPolicy {
   int32_t num_layers;  // 0 = no policy
   int32_t sizes[9];
   int32_t activation;
   int32_t hmax;        // widest layer output: the two activation buffers hold hmax x 32 floats each
+  int32_t obs_rows;    // rows of the normalised obs staged at a time (= sizes[0] when all of it fits)
   float min_std;
   const float* params;
   const float* obs_mean;

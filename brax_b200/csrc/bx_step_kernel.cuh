@@ -1661,74 +1661,169 @@ static __device__ __noinline__ void phase_env(const Ctx c, const BxHeader& h) {
 // The reference's acting loop (training/acting.py:53-74) evaluates the policy MLP (training/networks.py:83-102)
 // on the normalised obs and feeds NormalTanhDistribution's mode / sample (training/distribution.py:131-158) to
 // env.step.  Here: lane = env as everywhere; the warps split the units of a layer in chunks of four (four
-// independent accumulators per lane; the weights are warp-uniform read-only loads), the activations of a
-// layer sit in one of two shared-memory buffers [unit][lane], a CTA barrier separates the layers.  The obs of
+// independent accumulators per lane).  A warp stages its 32 rows x 4 units of the weight matrix in its own
+// shared-memory slice (the next 32 rows are already in flight in registers), so the inner loop is one broadcast
+// LDS.128 of weights + one LDS of the activation per four FMAs and no global-memory latency sits on it.  The
+// normalised obs and the activations of a layer sit in shared-memory buffers [unit][lane], a CTA barrier
+// separates the layers.  The obs of
 // the first step comes from obs0, later steps read the rows the previous step's env epilogue left in shared
 // memory through the obs map (envs the auto-reset restarted read first_obs).  Writes the actions into the act
 // quads (and act_out).  Called by ALL warps; ends with a barrier.
 BXS float policy_act(int kind, float x) {
   if (kind == BX_POLICY_RELU) return fmaxf(x, 0.f);
   if (kind == BX_POLICY_TANH) return tanhf(x);
-  return bx_div(x, 1.f + __expf(-x));   // swish: x * sigmoid(x)
+  // swish: x * sigmoid(x), sigmoid without overflow (exp of a non-positive argument only)
+  const float t = __expf(-fabsf(x));
+  const float r = bx_rcp(1.f + t);
+  return x * (x >= 0.f ? r : t * r);
 }
 template <int MODE>
-static __device__ __noinline__ void policy_forward(const Ctx c, const BxHeader& h, const BxKernelParams& p, float* pbuf,
+static __device__ __forceinline__ void policy_forward(const Ctx c, const BxHeader& h, const BxKernelParams& p, float* pbuf,
                                                    const float* smf, int t, int64_t env0, int nenv, bool restarted) {
   const BxPolicy& q = p.pol;
   const int lane = threadIdx.x & 31;
   const bool live = lane < nenv;
   const int64_t e = env0 + lane;
   const int no = q.sizes[0];
-  const BxSeg sg = h.seg_out[BX_SEG_ENV];
-  const int32_t* omap = c.ti + sg.map;
-  const float* obs_g = t == 0 ? p.obs0 : (restarted ? p.first_obs : nullptr);   // global source of this lane's obs
-  const float* w = q.params;
-  float* bufs[2] = {pbuf, pbuf + q.hmax * 32};
-  for (int l = 0; l < q.num_layers; l++) {
-    const int nin = q.sizes[l], nout = q.sizes[l + 1];
+  float* slice = pbuf + c.warp * (4 * BX_POLICY_KBLOCK);                  // this warp's weight rows
+  float* obsn = pbuf + BX_POLICY_MAX_WARPS * (4 * BX_POLICY_KBLOCK);      // [obs_rows][32]
+  float* hid_a = obsn + q.obs_rows * 32;                                  // [hmax][32] x 2
+  float* hid_b = hid_a + q.hmax * 32;
+  // Weights do not depend on activations: the first 32-row block (and the bias) of a warp's NEXT chunk --
+  // also across the layer barrier -- is fetched into registers while the current chunk computes.
+  // element i * 32 + lane of a 32-row block = (row i * 8 + lane / 4, unit lane % 4): a warp load covers
+  // 8 rows x 16 bytes.
+  float wreg[BX_POLICY_KBLOCK / 8], breg[4];
+  auto fetch = [&](const float* wl, int k_hi, int nout, int u0, int k0) {
+    const int su = u0 + (lane & 3);
+#pragma unroll
+    for (int i = 0; i < BX_POLICY_KBLOCK / 8; i++) {
+      const int row = k0 + i * 8 + (lane >> 2);
+      wreg[i] = (row < k_hi && su < nout) ? __ldg(wl + static_cast<size_t>(row) * nout + su) : 0.f;
+    }
+  };
+  auto fetch_bias = [&](const float* bias, int nout, int u0) {
+#pragma unroll
+    for (int j = 0; j < 4; j++) breg[j] = u0 + j < nout ? __ldg(bias + u0 + j) : 0.f;
+  };
+  PTM0(c);
+  const int orows = q.obs_rows;
+  bool have = 4 * c.warp < q.sizes[1];
+  if (have) {
+    fetch(q.params, no < orows ? no : orows, q.sizes[1], 4 * c.warp, 0);
+    fetch_bias(q.params + static_cast<size_t>(no) * q.sizes[1], q.sizes[1], 4 * c.warp);
+  }
+  const int na = h.act_size;
+  float eps0 = 0.f;   // the noise of this warp's first action, in flight during the whole forward pass
+  if (q.noise != nullptr && c.warp < na && live) eps0 = q.noise[(static_cast<int64_t>(t) * p.num_envs + e) * na + c.warp];
+
+  // Rows [k_lo, k_hi) of layer l's input for all of this warp's unit chunks: acc = (first range ? bias :
+  // the partial sums left in xout) + sum_k W[k][u] x[k]; the last range applies the activation.
+  // xin is indexed by the absolute row.
+  auto run_range = [&](int l, const float* w, int nin, int nout, int k_lo, int k_hi, const float* xin, float* xout) {
     const float* bias = w + static_cast<size_t>(nin) * nout;
-    const float* xin = bufs[(l + 1) & 1];
-    float* xout = bufs[l & 1];
+    const bool first = k_lo == 0, last = k_hi == nin;
     for (int u0 = 4 * c.warp; u0 < nout; u0 += 4 * c.nwarp) {
-      float acc[4];
-#pragma unroll
-      for (int j = 0; j < 4; j++) acc[j] = u0 + j < nout ? __ldg(bias + u0 + j) : 0.f;
-#pragma unroll 2
-      for (int k = 0; k < nin; k++) {
-        float x;
-        if (l == 0) {
-          if (obs_g != nullptr) {
-            x = live ? obs_g[e * no + k] : 0.f;
-          } else {
-            const int m = omap[k];
-            x = m >= 0 ? smf[m + 4 * lane] : sg.fill;
-          }
-          if (q.obs_mean != nullptr) x -= __ldg(q.obs_mean + k);
-          if (q.obs_std != nullptr) x = bx_div(x, __ldg(q.obs_std + k));
-        } else {
-          x = xin[k * 32 + lane];
-        }
-        const float* wk = w + static_cast<size_t>(k) * nout + u0;
-#pragma unroll
-        for (int j = 0; j < 4; j++)
-          if (u0 + j < nout) acc[j] = fmaf(__ldg(wk + j), x, acc[j]);
+      if (!have) {
+        fetch(w, k_hi, nout, u0, k_lo);
+        if (first) fetch_bias(bias, nout, u0);
       }
+      have = false;
+      // two packed accumulators: FFMA2 (fma.rn.f32x2, sm_100) does two units per issue slot, each
+      // component rounded like a scalar fmaf
+      float2 acc01, acc23;
+      if (first) {
+        acc01 = make_float2(breg[0], breg[1]);
+        acc23 = make_float2(breg[2], breg[3]);
+      } else {
+        acc01 = make_float2(xout[u0 * 32 + lane], u0 + 1 < nout ? xout[(u0 + 1) * 32 + lane] : 0.f);
+        acc23 = make_float2(u0 + 2 < nout ? xout[(u0 + 2) * 32 + lane] : 0.f, u0 + 3 < nout ? xout[(u0 + 3) * 32 + lane] : 0.f);
+      }
+      for (int k0 = k_lo; k0 < k_hi; k0 += BX_POLICY_KBLOCK) {
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < BX_POLICY_KBLOCK / 8; i++) slice[i * 32 + lane] = wreg[i];
+        __syncwarp();
+        if (k0 + BX_POLICY_KBLOCK < k_hi) {
+          fetch(w, k_hi, nout, u0, k0 + BX_POLICY_KBLOCK);
+        } else if (u0 + 4 * c.nwarp < nout) {
+          fetch(w, k_hi, nout, u0 + 4 * c.nwarp, k_lo);
+          if (first) fetch_bias(bias, nout, u0 + 4 * c.nwarp);
+          have = true;
+        } else if (last && l + 1 < q.num_layers && 4 * c.warp < q.sizes[l + 2]) {
+          fetch(bias + nout, nout, q.sizes[l + 2], 4 * c.warp, 0);
+          fetch_bias(bias + nout + static_cast<size_t>(nout) * q.sizes[l + 2], q.sizes[l + 2], 4 * c.warp);
+          have = true;
+        }
+        const int nk = k_hi - k0 < BX_POLICY_KBLOCK ? k_hi - k0 : BX_POLICY_KBLOCK;
+        const float* xk = xin + k0 * 32 + lane;
+#pragma unroll 4
+        for (int kk = 0; kk < nk; kk++) {
+          const float4 wv = *reinterpret_cast<const float4*>(slice + 4 * kk);
+          const float x = xk[kk * 32];
+          const float2 xx = make_float2(x, x);
+          acc01 = __ffma2_rn(make_float2(wv.x, wv.y), xx, acc01);
+          acc23 = __ffma2_rn(make_float2(wv.z, wv.w), xx, acc23);
+        }
+      }
+      const float acc[4] = {acc01.x, acc01.y, acc23.x, acc23.y};
+      const bool act = last && l + 1 < q.num_layers;
 #pragma unroll
       for (int j = 0; j < 4; j++)
-        if (u0 + j < nout) xout[(u0 + j) * 32 + lane] = l + 1 < q.num_layers ? policy_act(q.activation, acc[j]) : acc[j];
+        if (u0 + j < nout) xout[(u0 + j) * 32 + lane] = act ? policy_act(q.activation, acc[j]) : acc[j];
     }
-    w = bias + nout;
+  };
+
+  // layer 0 over the normalised obs, `obs_rows` rows at a time (all of it when it fits beside the tile; the
+  // host shrinks the chunk when that is what lets two tiles share an SM)
+  {
+    const BxSeg sg = h.seg_out[BX_SEG_ENV];
+    const int32_t* omap = c.ti + sg.map;
+    const float* obs_g = t == 0 ? p.obs0 : (restarted ? p.first_obs : nullptr);   // global source of this lane's obs
+    for (int r0 = 0; r0 < no; r0 += orows) {
+      const int r1 = r0 + orows < no ? r0 + orows : no;
+      if (r0 > 0) __syncthreads();   // the previous chunk has been consumed
+#pragma unroll 4
+      for (int k = r0 + c.warp; k < r1; k += c.nwarp) {
+        float x;
+        if (obs_g != nullptr) {
+          x = live ? obs_g[e * no + k] : 0.f;
+        } else {
+          const int m = omap[k];
+          x = m >= 0 ? smf[m + 4 * lane] : sg.fill;
+        }
+        if (q.obs_mean != nullptr) x -= __ldg(q.obs_mean + k);
+        if (q.obs_std != nullptr) x = bx_div(x, __ldg(q.obs_std + k));
+        obsn[(k - r0) * 32 + lane] = x;
+      }
+      __syncthreads();
+      if (r0 == 0) PTM(c, 16);
+      run_range(0, q.params, no, q.sizes[1], r0, r1, obsn - r0 * 32, hid_a);
+    }
+  }
+  PTM(c, 32);
+  __syncthreads();
+  PTM(c, 17);
+  const float* w = q.params + (static_cast<size_t>(no) + 1) * q.sizes[1];
+  const float* xin = hid_a;
+  for (int l = 1; l < q.num_layers; l++) {
+    const int nin = q.sizes[l], nout = q.sizes[l + 1];
+    float* xout = (l & 1) ? hid_b : hid_a;
+    run_range(l, w, nin, nout, 0, nin, xin, xout);
+    w += (static_cast<size_t>(nin) + 1) * nout;
+    xin = xout;
+    PTM(c, 32 + l);
     __syncthreads();
+    PTM(c, 17 + l);
   }
   // NormalTanhDistribution: loc = out[:A], scale = softplus(out[A:]) + min_std; mode / sample, then tanh
-  const float* out = bufs[(q.num_layers - 1) & 1];
-  const int na = h.act_size;
+  const float* out = xin;
   for (int a = c.warp; a < na; a += c.nwarp) {
     float loc = out[a * 32 + lane];
     if (q.noise != nullptr) {
       const float raw = out[(na + a) * 32 + lane];
       const float scale = (raw > 20.f ? raw : log1pf(__expf(raw))) + q.min_std;   // softplus
-      const float eps = live ? q.noise[(static_cast<int64_t>(t) * p.num_envs + e) * na + a] : 0.f;
+      const float eps = a == c.warp ? eps0 : (live ? q.noise[(static_cast<int64_t>(t) * p.num_envs + e) * na + a] : 0.f);
       loc = fmaf(scale, eps, loc);
     }
     const float act = tanhf(loc);
@@ -1736,6 +1831,7 @@ static __device__ __noinline__ void policy_forward(const Ctx c, const BxHeader& 
     if (p.act_out != nullptr && live) p.act_out[(static_cast<int64_t>(t) * p.num_envs + e) * na + a] = act;
   }
   __syncthreads();
+  PTM(c, 23);
 }
 
 // ============================== the kernel ====================================
@@ -1874,7 +1970,8 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
     if (policy_on) {
       // actions of this step from the policy: obs of the previous step (obs0 for the first; first_obs for
       // envs the auto-reset restarted at the end of the previous step)
-      float* pbuf = reinterpret_cast<float*>(mbar + 2);
+      // (the policy's buffers start at the 16-byte boundary behind the mbarriers)
+      float* pbuf = reinterpret_cast<float*>(bx_smem + h.n_quads * QS + h.n_fquads + ((h.n_ints * 4 + 16 + 15) >> 4));
       const bool restarted = step > 0 && p.first[0] != nullptr && (threadIdx.x & 31) < nenv &&
                              sq[(h.q_env + EQ_S0) * QS + (threadIdx.x & 31)].y > 0.f;
       policy_forward<MODE>(c, h, p, pbuf, smf, step, env0, nenv, restarted);

@@ -237,7 +237,9 @@ def _policy_torch(torch, params, act_fn, obs, mean, std, na, noise=None, min_std
 
 
 @pytest.mark.parametrize('variant,act_fn,hidden', [('ant', 'swish', (32, 32, 32, 32)), ('humanoid', 'relu', (64, 48)),
-                                                   ('grasp', 'tanh', (40,))])
+                                                   ('humanoid', 'swish', (32, 32)),   # pre-activations below -88 (swish without overflow)
+                                                   ('ant', 'tanh', (64, 64)),         # obs staged in chunks of 64 rows (two tiles per SM kept)
+                                                   ('grasp', 'tanh', (40,)), ('ant', 'relu', (256, 100))])
 def test_in_kernel_policy_rollout_equals_acting_loop(variant, act_fn, hidden):
   """bx_policy: T steps of actions = policy(obs); state = env.step(state, actions) in ONE launch == the
   acting loop (training/acting.py:53-74) with the policy evaluated in torch between single-step launches:
