@@ -729,7 +729,7 @@ static int set_smem_attr(int bytes) {
 
 static size_t tile_bytes(const BxHeader& h) {
   return (static_cast<size_t>(h.n_quads) * BX_QSTRIDE + h.n_fquads) * 16 +
-         static_cast<size_t>(h.n_ints) * 4 + 16 /* mbarrier */;
+         static_cast<size_t>(h.n_ints) * 4 + 16 /* mbarrier */ + BX_FRICTION_SMEM /* per-env friction */;
 }
 
 extern "C" int bx_desc_tile_bytes(const bx_system_desc* desc, int64_t* bytes, int32_t* rows) {
@@ -932,6 +932,7 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   memset(&p.pol, 0, sizeof(p.pol));
   p.obs0 = nullptr;
   p.act_out = nullptr;
+  p.friction = io->friction;
   size_t policy_smem = 0;
   bool policy_one_tile = false;   // the policy's buffers leave room for one tile per SM only
   if (io->policy) {
@@ -978,6 +979,8 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
     policy_one_tile = 2 * (s->smem_bytes + policy_smem + 1024) > 233472;
   }
   p.h = s->h;
+  // (float index behind the two mbarriers; 0 = off)
+  p.h.fr_off = io->friction ? (s->h.n_quads * BX_QSTRIDE + s->h.n_fquads) * 4 + s->h.n_ints + 4 : 0;
   p.tab_i = s->d_tab_i;
   p.tab_f = s->d_tab_f;
   p.in[0] = io->pos; p.in[1] = io->rot; p.in[2] = io->vel; p.in[3] = io->ang; p.in[4] = io->act;

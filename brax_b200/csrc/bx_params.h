@@ -9,6 +9,7 @@
 #include "bx_tables.h"
 
 // bx_policy by value (include/brax_b200.h): the in-kernel MLP policy of a rollout
+#define BX_FRICTION_SMEM 128   // bytes behind the mbarriers: friction[e]^2 of the tile's 32 envs
 #define BX_POLICY_KBLOCK 32     // weight rows a warp stages per block (4 units wide)
 #define BX_POLICY_MAX_WARPS 16  // slices are laid out for the widest launch
 // shared memory of the in-kernel policy beside the tile: weight slices, normalised obs, two activation buffers
@@ -47,6 +48,7 @@ struct BxKernelParams {
   BxPolicy pol;                // in-kernel policy (env builds), pol.num_layers == 0: none
   const float* obs0;           // [B,O] obs of the state passed in (policy launches)
   float* act_out;              // [T,B,A] actions the policy chose, or NULL
+  const float* friction;       // [B] per-env collider friction (h.fr_off != 0), or NULL
   int64_t num_envs;
   int32_t num_steps;  // >1: rollout, act is [T,B,A]
   // host path only (bx_step_host on mapped host memory): tile i starts i/grid of

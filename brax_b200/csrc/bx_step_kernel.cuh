@@ -804,6 +804,12 @@ BXS float w_of(float inv_mass, V3 inv_i, V3 r, V3 n) {
   return inv_mass + dot(cr, inv_i * cr);
 }
 
+// Friction of a collider pair: the pair table's, or with per-env collider friction (bx_step_io.friction:
+// domain randomisation, experimental/tracing/randomizers.py:26-51) this env's friction^2 from shared memory.
+BXS float pair_friction(const BxHeader& h, float table) {
+  return h.fr_off ? reinterpret_cast<const float*>(bx_smem)[h.fr_off + (threadIdx.x & 31)] : table;
+}
+
 // contact function of one contact row (colliders.py:667-680 box_plane,
 // :744-759 capsule_plane, :805-819 capsule_capsule).
 BXS Contact contact_fn(int kind, const float4* cq, const float4* tq, V3 pa, Q4 ra, V3 va, V3 wa, V3 pb, Q4 rb,
@@ -877,7 +883,7 @@ BXS void c1_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
     V3 iia = f3(bqa[BQ_INV_INERTIA]);
     const float4 ma4 = bqa[BQ_MASS];
     const float ima = ma4.x, ma = ma4.y;
-    const float friction = cq[CQ_MAT].x;
+    const float friction = pair_friction(h, cq[CQ_MAT].x);
     const float cs = h.collide_scale;
     V3 n = ct.normal;
     float dl_out;
@@ -1059,7 +1065,7 @@ BXS void c2_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
       V3 v_t = rel - n * v_n;
       float vtn = safe_norm(v_t);
       V3 vdir = vdiv(v_t, 1e-6f + vtn);
-      float lim = (mat.x * fabsf(dlambda)) * h.inv_2h;
+      float lim = (pair_friction(h, mat.x) * fabsf(dlambda)) * h.inv_2h;
       V3 dvel = (-vdir) * fminf(lim, vtn);
       V3 angw = cross(ra, vdir);
       float w = ima + dot(angw, angw);  // no inertia here (colliders.py:405-406)
@@ -1090,7 +1096,7 @@ BXS void c2_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
       V3 v_t = rel - n * v_n;
       float vtn = safe_norm(v_t);
       V3 vdir = vdiv(v_t, 1e-6f + vtn);
-      float lim = (mat.x * fabsf(dlambda)) * h.inv_2h;
+      float lim = (pair_friction(h, mat.x) * fabsf(dlambda)) * h.inv_2h;
       V3 dvel = (-vdir) * fminf(lim, vtn);
       float w1 = w_of(ima, iia, ra, vdir), w2 = w_of(imb, iib, rb, vdir);
       V3 p_dyn = vdiv(dvel, w1 + w2 + 1e-6f);
@@ -1329,7 +1335,7 @@ BXS void spring_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
     float imp = bx_div(-1.f * (1.f + mat.y) * nv + baum, denom);
     V3 vd = ct.vel - nv * n;
     float nvd = safe_norm(vd);
-    float impd = fminf(bx_div(nvd, denom), mat.x * imp);
+    float impd = fminf(bx_div(nvd, denom), pair_friction(h, mat.x) * imp);
     V3 dir = vdiv(vd, 1e-6f + nvd);
     float apn = (ct.pen > 0.f && nv < 0.f && imp > 0.f) ? 1.f : 0.f;
     float apd = apn * (nvd > 0.01f ? 1.f : 0.f);
@@ -1898,6 +1904,13 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
     }
   }
   if (threadIdx.x != 0) pdl_wait();  // every thread that will read or write global memory
+  if (h.fr_off && threadIdx.x >= blockDim.x - 32) {
+    // per-env collider friction: a pair's friction is friction_a * friction_b = friction[e]^2 (float32
+    // product, like the descriptor's); read by the contact rows after the barriers that follow
+    const int l = threadIdx.x & 31;
+    const float f = l < nenv ? p.friction[env0 + l] : 1.f;
+    smf[h.fr_off + l] = f * f;
+  }
   if (!full) {
     // partial tile: give the idle env slots a benign state (identity rotations)
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1971,7 +1984,7 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
       // actions of this step from the policy: obs of the previous step (obs0 for the first; first_obs for
       // envs the auto-reset restarted at the end of the previous step)
       // (the policy's buffers start at the 16-byte boundary behind the mbarriers)
-      float* pbuf = reinterpret_cast<float*>(bx_smem + h.n_quads * QS + h.n_fquads + ((h.n_ints * 4 + 16 + 15) >> 4));
+      float* pbuf = reinterpret_cast<float*>(bx_smem + h.n_quads * QS + h.n_fquads + ((h.n_ints * 4 + 16 + BX_FRICTION_SMEM + 15) >> 4));
       const bool restarted = step > 0 && p.first[0] != nullptr && (threadIdx.x & 31) < nenv &&
                              sq[(h.q_env + EQ_S0) * QS + (threadIdx.x & 31)].y > 0.f;
       policy_forward<MODE>(c, h, p, pbuf, smf, step, env0, nenv, restarted);

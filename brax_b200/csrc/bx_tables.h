@@ -138,6 +138,9 @@ struct BxHeader {
   int32_t q_act, q_js, q_ct, q_cn, q_cd, q_pre, q_ic, q_ia, q_ij;
   int32_t n_quads;
   int32_t n_zero;  // quads from q_ic to zero at the start of every step
+  // per-env collider friction (bx_step_io.friction): float index in shared memory of the tile's 32
+  // friction[e]^2 values (behind the mbarriers), set per launch; 0 = the pair tables' friction
+  int32_t fr_off;
   BxSeg seg_in[BX_SEG_IN];
   BxSeg seg_out[BX_SEG_OUT];
   // scalars

@@ -179,6 +179,8 @@ class Env:
     # True: state.info['physics'] carries the step's Info (an extra of this mirror; the reference's
     # Env.step drops it, ant.py:224) -- costs the Info stores of the launch
     self.keep_info = False
+    # per-env collider friction [B] (CUDA tensor) or None: see `randomize_friction`
+    self.friction = None
     self.sys = _system.load_system(system_name, device, env)
     self.observation_size = env.obs_size(self.sys.desc)
     self.action_size = self.sys.act_size
@@ -238,7 +240,7 @@ class Env:
       joint_velocity = noise()                                                      # ant.py:203
     qp = self.sys.default_qp(joint_angle=joint_angle.reshape(b, nd), joint_velocity=joint_velocity.reshape(b, nd))
     qp = self._place_targets(qp, gen)
-    obs = self.sys.observe(qp)
+    obs = self.sys.observe(qp, self.friction)
     names = self.env.metric_names()
     zeros = torch.zeros((len(names) + 2, b), dtype=torch.float32, device=dev)   # distinct rows: no aliasing
     reward, done = zeros[0], zeros[1]
@@ -260,6 +262,16 @@ class Env:
     the state resident on the device.  Synchronise before reading them."""
     return self._launch(state, action, host_out=host_out)
 
+  def randomize_friction(self, friction):
+    """Domain randomisation over collider friction, as `DomainRandomizationWrapper(env_fn,
+    *friction_randomizer(env, friction))` (experimental/tracing/wrappers.py:27-88,
+    randomizers.py:26-51): env e is simulated with material.friction = friction[e] on EVERY collider
+    (a pair's friction is friction[e]^2, colliders.py:277,315,392).  friction: float32 CUDA tensor [B] matching
+    the batch of the states stepped afterwards, or None to return to the config's friction.  Applies to
+    `step`, `reset` (the reset obs reads System.info's contact impulse) and the wrappers around this env."""
+    self.friction = friction
+    return self
+
   def host_io(self, batch: int):
     """Page-locked host tensors for `step(..., host_out=)`: 'action' [B,A] in, 'obs' [B,O],
     'reward' [B], 'done' [B], 'metrics' [B,M] out."""
@@ -271,7 +283,7 @@ class Env:
   def _launch(self, state: State, action, rand=None, auto_reset=None, host_out=None) -> State:
     torch_path = _system._is_torch(state.qp.pos)
     qp, info, eo = self.sys.step(state.qp, action, env=True, env_rand=rand, auto_reset=auto_reset,
-                                 info=self.keep_info or not torch_path,
+                                 info=self.keep_info or not torch_path, friction=self.friction,
                                  env_out=None if host_out is None else {k: host_out[k] for k in ('obs', 'reward', 'done', 'metrics')})
     names = self.env.metric_names()
     metrics = dict(state.metrics)
@@ -423,7 +435,8 @@ class EpisodeAutoReset:
     ar = self._auto_reset(state)
     if rand is None and isinstance(self.env, _TargetEnv):
       rand = self.env._uniform(state.qp.pos, (int(actions.shape[0]) * self.action_repeat,) + tuple(state.qp.pos.shape[:-2]))
-    qp, info, eo = self.sys.rollout(state.qp, actions, env=True, env_rand=rand, auto_reset=ar, info=False)
+    qp, info, eo = self.sys.rollout(state.qp, actions, env=True, env_rand=rand, auto_reset=ar, info=False,
+                                    friction=self.env.friction)
     names = self.env.env.metric_names()
     metrics = {k: eo['metrics'][-1, ..., i] for i, k in enumerate(names)}
     last = State(qp, eo['obs'][-1], eo['reward'][-1], eo['done'][-1], metrics,

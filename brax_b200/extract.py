@@ -234,9 +234,10 @@ def _reset_desc(sys) -> Dict[str, Any]:
 def describe(sys, name: str = 'system', act_size: int = None) -> SystemDesc:
   """Returns the `SystemDesc` of a constructed reference `brax.System`."""
   cfg = sys.config
-  if type(cfg).__name__ == 'TracedConfig':
-    raise NotImplementedError(
-        'TracedConfig / per-env randomised constants are out of scope')
+  # A `TracedConfig` (experimental/tracing/customize.py) is read through like the config it wraps: with a
+  # scalar custom tree (one lane of the reference's vmap over the config) the built System carries the
+  # substituted values and this descriptor records them; a vmapped tree (arrays) has no single descriptor
+  # -- float() below fails -- and is served per env at step time instead (`System.step(friction=)`).
   mode = cfg.dynamics_mode
   integ = sys.integrator
 

@@ -377,7 +377,7 @@ class System:
       arrs = [torch.from_numpy(a).to(device) for a in arrs]
     return QP(*arrs)
 
-  def observe(self, qp: QP):
+  def observe(self, qp: QP, friction=None):
     """obs [B,O] of a state as `Env.reset` builds it: `_get_obs(qp, info)` with a zero Info and a
     zero action (envs/ant.py:203-204, humanoid.py:230-231, fetch.py:41-42, grasp.py:60-61) -- the
     env epilogue of the step kernel without its substeps, one launch.  torch CUDA tensors;
@@ -390,7 +390,7 @@ class System:
     b = int(qp.pos.shape[0]) if qp.pos.dim() == 3 else 1
     shape = (b, self.act_size) if qp.pos.dim() == 3 else (self.act_size,)
     act = torch.zeros(shape, dtype=torch.float32, device=qp.pos.device)
-    return self._step_torch(qp, act, 1, False, True, None, None, False, observe=True)[2]['obs']
+    return self._step_torch(qp, act, 1, False, True, None, None, False, observe=True, friction=friction)[2]['obs']
 
   def _default_qp_torch(self, joint_angle, joint_velocity) -> QP:
     import torch
@@ -434,7 +434,7 @@ class System:
 
   # ---- the step ---------------------------------------------------------------
   def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False, env: bool = False,
-           env_rand=None, auto_reset: 'AutoReset' = None, info: bool = True, env_out=None):
+           env_rand=None, auto_reset: 'AutoReset' = None, info: bool = True, env_out=None, friction=None):
     """`System.step(qp, act) -> (qp, info)` (system.py:244-247).
 
     out: optional `HostBuffers` (host path only): results are written into its
@@ -455,7 +455,10 @@ class System:
     tensors (`pin_memory=True`): the launch then writes them over PCIe itself.  `act` may likewise be a
     page-locked host tensor.  That is the gym-style loop with the state resident on the device
     (brax/envs/wrappers.py:228-260 + to_torch.py:56-64): actions in, obs / reward / done out, one
-    launch, no separate copies; synchronise the stream before reading the host tensors."""
+    launch, no separate copies; synchronise the stream before reading the host tensors.
+    friction: (torch path) float32 CUDA tensor [B]: per-env collider material friction -- the domain
+    randomisation of experimental/tracing/randomizers.py:26-51 (every collider of env e has
+    material.friction = friction[e]; pair friction = friction[e]^2)."""
     if env and self.env is None:
       raise ValueError('this System was built without an EnvDesc')
     if auto_reset is not None and not env:
@@ -469,9 +472,9 @@ class System:
       if isinstance(act, np.ndarray):
         raise TypeError('qp is on the GPU, act is a numpy array: pass a CUDA (or page-locked) tensor')
     if _is_torch(qp.pos):
-      return self._step_torch(qp, act, 1, angle_vel, env, env_rand, auto_reset, info, env_out=env_out)
-    if env_out is not None:
-      raise ValueError('env_out belongs to the torch path')
+      return self._step_torch(qp, act, 1, angle_vel, env, env_rand, auto_reset, info, env_out=env_out, friction=friction)
+    if env_out is not None or friction is not None:
+      raise ValueError('env_out / friction belong to the torch path')
     if auto_reset is not None:
       raise ValueError('auto_reset is supported with torch CUDA tensors only')
     return self._step_numpy(qp, act, out, angle_vel, env, env_rand)
@@ -503,7 +506,7 @@ class System:
     return int(h2d.value), int(d2h.value)
 
   def rollout(self, qp: QP, acts, env: bool = False, env_rand=None, auto_reset: 'AutoReset' = None,
-              info: bool = True, policy: 'Policy' = None, obs0=None, noise=None, steps: int = None):
+              info: bool = True, policy: 'Policy' = None, obs0=None, noise=None, steps: int = None, friction=None):
     """T steps in ONE launch; acts is [T, B, A] (torch CUDA).  Returns the final
     QP and the Info of the last step (lax.scan of System.step over actions); with
     env=True also the env epilogue of EVERY step: obs [T,B,O], reward / done [T,B],
@@ -520,8 +523,8 @@ class System:
       if not env or obs0 is None or steps is None:
         raise ValueError('a policy rollout needs env=True, obs0 and steps')
       return self._step_torch(qp, None, int(steps), False, True, env_rand, auto_reset, info,
-                              policy=(policy, obs0, noise))
-    return self._step_torch(qp, acts, int(acts.shape[0]), False, env, env_rand, auto_reset, info)
+                              policy=(policy, obs0, noise), friction=friction)
+    return self._step_torch(qp, acts, int(acts.shape[0]), False, env, env_rand, auto_reset, info, friction=friction)
 
   def _shapes(self, pos_shape):
     n = self.num_bodies
@@ -582,7 +585,7 @@ class System:
     io.action_repeat = 0
 
   def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False, env_rand=None,
-                  auto_reset=None, info: bool = True, observe: bool = False, env_out=None, policy=None):
+                  auto_reset=None, info: bool = True, observe: bool = False, env_out=None, policy=None, friction=None):
     """env_rand: (fetch / grasp) uniforms of the target teleport, [B,3] or [T,B,3].
 
     Host cost per call is what bounds a plain Python stepping loop (the kernel takes ~57 us for
@@ -667,6 +670,13 @@ class System:
       io.act_out = act_out.data_ptr()
     elif io.policy:
       io.policy = io.obs0 = io.act_out = None
+    if friction is not None:
+      if not (_is_torch(friction) and friction.is_cuda):
+        raise ValueError('friction must be a CUDA tensor [B]')
+      friction = prep(friction, b)
+      io.friction = friction.data_ptr()
+    elif io.friction:
+      io.friction = None
     if ext:
       for nm, cnt in (('obs', b * self.obs_size), ('reward', b), ('done', b), ('metrics', b * self.num_metrics)):
         t = env_out[nm]

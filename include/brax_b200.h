@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BX_ABI_VERSION 10
+#define BX_ABI_VERSION 11
 
 /* dynamics_mode (base.py:179-201) */
 #define BX_MODE_PBD 0
@@ -335,6 +335,12 @@ typedef struct bx_step_io {
   const bx_policy* policy; /* HOST pointer to the descriptor (its array pointers are device pointers) */
   const float* obs0;
   float* act_out;
+  /* Optional per-env collider friction [B] (device; NULL = the descriptor's): domain randomisation as
+   * experimental/tracing/randomizers.py:26-51 (friction_randomizer) + tracing/wrappers.py:27-88 do it --
+   * EVERY collider of env e has material.friction = friction[e], so a pair's friction is
+   * friction[e] * friction[e] (colliders.py:277,315,392,459,596).  bx_step / bx_rollout / bx_state_rollout;
+   * the host-buffer entry points (bx_step_host*) refuse it. */
+  const float* friction;
   float episode_length;   /* EpisodeWrapper.episode_length; 0 = no episode limit */
   /* Non-zero (systems with desc.env, bx_step only): no physics -- the launch evaluates
    * info = System.info(qp) of the state passed in (system.py:327-340 / :378-390: the contact rows and

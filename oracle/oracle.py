@@ -117,6 +117,44 @@ def _structs(R):
   return Body, Joint, Actuator, Force, Pair, Sys, IO
 
 
+def with_collider_friction(desc, friction: float):
+  """A copy of `desc` in which EVERY collider has material.friction = `friction` -- what
+  experimental/tracing/randomizers.py:26-51 (friction_randomizer) substitutes per env through
+  TracedConfig: both sides of every pair (a pair's friction is friction_a * friction_b,
+  colliders.py:277,315,392,459,596)."""
+  import copy
+  d = copy.copy(desc)
+  d.pairs = [dict(p, friction_a=float(friction), friction_b=float(friction)) for p in desc.pairs]
+  return d
+
+
+class FrictionOracle:
+  """`Oracle.step` with per-env collider friction [B] (domain randomisation): env e is stepped by the
+  oracle of `with_collider_friction(desc, friction[e])`, one Oracle per distinct value."""
+
+  def __init__(self, desc, friction, dtype=np.float32):
+    self.desc, self.dtype = desc, np.dtype(dtype)
+    self.friction = np.asarray(friction).reshape(-1)   # (the caller's precision: float64 values stay exact)
+    self._oracles = {}
+
+  def step(self, pos, rot, vel, ang, act):
+    ins = [np.asarray(x) for x in (pos, rot, vel, ang, act)]
+    b = ins[0].shape[0]
+    assert self.friction.shape[0] == b
+    out = None
+    for f in np.unique(self.friction):
+      idx = np.nonzero(self.friction == f)[0]
+      o = self._oracles.get(float(f))
+      if o is None:
+        o = self._oracles[float(f)] = Oracle(with_collider_friction(self.desc, float(f)), self.dtype)
+      part = o.step(*[x[idx] for x in ins])
+      if out is None:
+        out = {k: np.empty((b,) + v.shape[1:], v.dtype) for k, v in part.items()}
+      for k, v in part.items():
+        out[k][idx] = v
+    return out
+
+
 class Oracle:
   """CPU restatement of `System.step` for one `SystemDesc`."""
 

@@ -1,0 +1,165 @@
+"""Per-env collider friction (domain randomisation; `bx_step_io.friction`, `System.step(friction=)`).
+
+Reference: `DomainRandomizationWrapper` + `friction_randomizer` (/root/reference/brax/experimental/tracing/
+wrappers.py:27-88, randomizers.py:26-51): env e steps a System whose colliders all have material.friction =
+friction[e].  tests/golden/friction/*.npz holds such steps produced by the unmodified reference through its own
+TracedConfig hook, one System per value (oracle/gen_golden_friction.py).
+
+CPU: the float64 oracle with the substituted pair frictions reproduces them.  GPU: ONE launch over a batch whose
+envs carry different friction values matches the float32 oracle run per value."""
+import os
+
+import numpy as np
+import pytest
+
+from tests import util
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'friction')
+SYSTEMS = ('ant', 'ant_spring', 'grasp')
+
+
+def _golden(name):
+  g = np.load(os.path.join(GOLD, name + '.npz'))
+  f, t = g['pos'].shape[:2]
+  flat = {k: g[k].reshape((f * t,) + g[k].shape[2:]) for k in g.files if k not in ('friction', 'pair_friction')}
+  friction = np.repeat(g['friction'], t).astype(np.float32)
+  a = util.load_desc(name).act_size      # (grasp: the descriptor's act vector carries the env's 3 palm-target slots too)
+  if flat['act'].shape[1] < a:
+    flat['act'] = np.concatenate([flat['act'], np.zeros((f * t, a - flat['act'].shape[1]))], axis=1)
+  return g, flat, friction
+
+
+@pytest.mark.parametrize('name', SYSTEMS)
+def test_oracle_f64_reproduces_reference_steps_under_substituted_friction(name):
+  from oracle.oracle import FrictionOracle
+  g, flat, friction = _golden(name)
+  # the extractor read friction_a = friction_b = the substituted value off every built System
+  assert g['pair_friction'].shape[1] == len(util.load_desc(name).pairs)
+  for i, f in enumerate(g['friction']):
+    assert np.all(g['pair_friction'][i] == f)
+  t = g['pos'].shape[1]
+  o = FrictionOracle(util.load_desc(name), np.repeat(g['friction'], t), np.float64)
+  out = o.step(*[flat[k] for k in util.QP_KEYS], flat['act'])
+  for k in util.QP_KEYS + util.INFO_KEYS:
+    if out[k].size:
+      np.testing.assert_allclose(out[k], flat['out_' + k], rtol=0, atol=1e-9 * max(1.0, np.abs(flat['out_' + k]).max()), err_msg=k)
+  # and friction matters in these states: the slipperiest and the stickiest lane end up apart
+  assert np.abs(g['out_pos'][0, -1] - g['out_pos'][-1, -1]).max() > 1e-2
+
+
+def test_friction_oracle_equals_plain_oracle_at_the_config_value():
+  from oracle.oracle import FrictionOracle, Oracle
+  d = util.load_desc('ant')
+  f0 = d.pairs[0]['friction_a']
+  assert all(p['friction_a'] == f0 and p['friction_b'] == f0 for p in d.pairs)
+  g = util.load_golden('ant')
+  ins = [g[k].astype(np.float32) for k in util.QP_KEYS]
+  act = g['act'].astype(np.float32)
+  a = Oracle(d, np.float32).step(*ins, act)
+  b = FrictionOracle(d, np.full(ins[0].shape[0], f0, np.float32), np.float32).step(*ins, act)
+  for k in a:
+    assert np.array_equal(a[k], b[k]), k
+
+
+# ------------------------------------------------------------------ GPU
+def _torch():
+  import torch
+  if not torch.cuda.is_available():
+    pytest.skip('no CUDA device')
+  return torch
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', SYSTEMS)
+def test_gpu_step_with_per_env_friction_on_reference_states(name):
+  torch = _torch()
+  from oracle.oracle import FrictionOracle
+  from brax_b200.system import QP
+  from tests.test_gpu_parity import _flat, _system, check_step
+  g, flat, friction = _golden(name)
+  s = _system(name)
+  ins = [flat[k].astype(np.float32) for k in util.QP_KEYS]
+  act = flat['act'].astype(np.float32)
+  qp = QP(*[torch.from_numpy(x).cuda() for x in ins])
+  got = _flat(*s.step(qp, torch.from_numpy(act).cuda(), friction=torch.from_numpy(friction).cuda()))
+  d = util.load_desc(name)
+  check_step(name, ins, act, got, oracles=(FrictionOracle(d, friction, np.float32), FrictionOracle(d, friction, np.float64)))
+  # and it is the friction that moved them: the same launch without it differs on the non-config lanes
+  plain = _flat(*s.step(qp, torch.from_numpy(act).cuda()))
+  lanes = friction != np.float32(d.pairs[0]['friction_a'])
+  assert np.abs(plain['vel'][lanes] - got['vel'][lanes]).max() > 1e-3
+  assert np.array_equal(plain['pos'][~lanes], got['pos'][~lanes])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('name,b', [('ant', 1000), ('grasp', 333), ('humanoid', 512), ('fetch', 300), ('ant_spring', 512)])
+def test_gpu_per_env_friction_on_harvested_states(name, b):
+  """A contact-rich batch, 8 friction values spread over the envs (ragged last tile), one launch."""
+  torch = _torch()
+  from oracle.oracle import FrictionOracle
+  from tests.test_gpu_parity import _flat, _harvest, _system, check_step
+  s = _system(name)
+  qp, rng = _harvest(s, b, 6 if name == 'half_cheetah' else 20, 17)
+  friction = rng.choice(np.float32([0.1, 0.3, 0.5, 0.75, 1.0, 1.25, 1.5, 2.0]), b).astype(np.float32)
+  act = rng.uniform(-1, 1, (b, s.act_size)).astype(np.float32)
+  got = _flat(*s.step(qp, torch.from_numpy(act).cuda(), friction=torch.from_numpy(friction).cuda()))
+  ins = [getattr(qp, k).cpu().numpy() for k in util.QP_KEYS]
+  d = util.load_desc(name)
+  check_step(name, ins, act, got, oracles=(FrictionOracle(d, friction, np.float32), FrictionOracle(d, friction, np.float64)))
+
+
+@pytest.mark.gpu
+def test_gpu_friction_at_the_config_value_is_bitwise_the_plain_step_and_rollouts_chain():
+  torch = _torch()
+  from tests.test_gpu_parity import _harvest, _system
+  s = _system('ant')
+  d = util.load_desc('ant')
+  b, t_n = 700, 5
+  qp, rng = _harvest(s, b, 20, 19)
+  acts = torch.from_numpy(rng.uniform(-1, 1, (t_n, b, s.act_size)).astype(np.float32)).cuda()
+  same = torch.full((b,), float(d.pairs[0]['friction_a']), device='cuda')
+  q0, i0 = s.step(qp, acts[0])
+  q1, i1 = s.step(qp, acts[0], friction=same)
+  for k in util.QP_KEYS:
+    assert torch.equal(getattr(q0, k), getattr(q1, k)), k
+  assert torch.equal(i0.contact.vel, i1.contact.vel)
+  # T steps in one launch == T single launches, with friction
+  fr = torch.from_numpy(rng.uniform(0.2, 1.8, b).astype(np.float32)).cuda()
+  qr, _ = s.rollout(qp, acts, friction=fr)
+  qc = qp
+  for t in range(t_n):
+    qc, _ = s.step(qc, acts[t], friction=fr)
+  for k in util.QP_KEYS:
+    assert torch.equal(getattr(qr, k), getattr(qc, k)), k
+  # the next launch without friction is back on the tables
+  q2, _ = s.step(qp, acts[0])
+  assert torch.equal(q2.pos, q0.pos)
+  with pytest.raises((ValueError, RuntimeError)):
+    s.step(qp, acts[0], friction=fr[:10])
+
+
+@pytest.mark.gpu
+def test_gpu_env_randomize_friction():
+  """`Env.randomize_friction` = DomainRandomizationWrapper over friction: step, reset obs and the wrapped env."""
+  torch = _torch()
+  from brax_b200 import envs
+  env = envs.create('ant')
+  b = 256
+  st = env.reset(b, device='cuda', seed=3)
+  act = torch.rand(b, env.action_size, device='cuda') * 2 - 1
+  for _ in range(15):
+    st = env.step(st, act)
+  plain = env.step(st, act)
+  fr = torch.linspace(0.1, 2.0, b, device='cuda')
+  env.randomize_friction(fr)
+  rnd = env.step(st, act)
+  q, _, eo = env.sys.step(st.qp, act, env=True, friction=fr, info=False)
+  assert torch.equal(rnd.obs, eo['obs']) and torch.equal(rnd.qp.pos, q.pos)
+  assert float((rnd.obs - plain.obs).abs().max()) > 1e-3
+  wrapped = envs.EpisodeAutoReset(env, 1000)
+  ws = wrapped.reset(b, device='cuda', seed=3)
+  ws = ws.replace(qp=st.qp)
+  w1 = wrapped.step(ws, act)
+  assert torch.equal(w1.qp.pos, rnd.qp.pos)
+  env.randomize_friction(None)
+  assert torch.equal(env.step(st, act).obs, plain.obs)

@@ -84,7 +84,7 @@ ACCUMULATORS = ('contact_vel', 'contact_ang', 'joint_vel', 'joint_ang',
                 'actuator_vel', 'actuator_ang')
 
 
-def check_step(name, ins, act, got, strict_frac=0.90, outlier_frac=OUTLIER_FRAC, contact_point_atol=0.0):
+def check_step(name, ins, act, got, strict_frac=0.90, outlier_frac=OUTLIER_FRAC, contact_point_atol=0.0, oracles=None):
   """Kernel output `got` vs the float32 oracle, with the float64 oracle run on
   the same inputs measuring how ill-conditioned each env's step is in float32.
 
@@ -95,8 +95,9 @@ def check_step(name, ins, act, got, strict_frac=0.90, outlier_frac=OUTLIER_FRAC,
   B >= 200 up to OUTLIER_FRAC of the envs may miss the tolerance (by no more than
   OUTLIER_BOUND x, unless the env's Info accumulators show the decision that was taken
   differently: then 1e-2 absolute on pos / rot); on the small golden batches none may."""
-  ref = _oracle(name, np.float32).step(*ins, act)
-  r64 = _oracle(name, np.float64).step(*ins, act)
+  o32, o64 = oracles if oracles is not None else (_oracle(name, np.float32), _oracle(name, np.float64))
+  ref = o32.step(*ins, act)      # (oracles=: a (float32, float64) pair with the same `step`, e.g. FrictionOracle)
+  r64 = o64.step(*ins, act)
   b = ref['pos'].shape[0]
   allowed = int(outlier_frac * b) if b >= 200 else 0
   stats = {}
