@@ -118,7 +118,7 @@ static int validate(const bx_system_desc* d) {
   int k = 0;
   for (int i = 0; i < d->num_pairs; i++) {
     const bx_pair& p = d->pairs[i];
-    if (p.kind < BX_PAIR_CAPSULE_PLANE || p.kind > BX_PAIR_CAPSULE_BOX)
+    if (p.kind < BX_PAIR_CAPSULE_PLANE || p.kind > BX_PAIR_CAPSULE_CLIPPED_PLANE)
       return fail("unsupported collider pair kind (general mesh/heightmap/clipped-plane/box-box are out of scope)");
     if (p.body_a < 0 || p.body_a >= d->num_bodies || p.body_b < 0 || p.body_b >= d->num_bodies)
       return fail("pair body index out of range");
@@ -217,9 +217,14 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
   int n_normals = 0, n_tris = 0;
   for (int k = 0; k < nk; k++) {
     const bool per_row = d->pairs[rows[k].pair].kind == BX_PAIR_CAPSULE_BOX;
-    if (per_row || k == 0 || rows[k].pair != rows[k - 1].pair) n_normals++;
+    const bool new_pair = k == 0 || rows[k].pair != rows[k - 1].pair;
+    if (per_row || new_pair) n_normals++;
     normal_row[k] = n_normals - 1;
     if (per_row) tri_index[k] = n_tris++;
+    // capsule_clipped_plane: the rows of a pair share one 8-quad block {normal, pos, x, y, halfsize, -, -, -}
+    if (d->pairs[rows[k].pair].kind == BX_PAIR_CAPSULE_CLIPPED_PLANE) {
+      if (new_pair) { tri_index[k] = n_tris; n_tris += 2; } else tri_index[k] = tri_index[k - 1];
+    }
   }
   // contact items: up to rows_per_item consecutive rows of one pair share one
   // slot-list entry per side
@@ -303,7 +308,14 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
   // capsule_box rows: {p0, p1, p2, normal} of the row's triangle (body-b frame), 4 quads each
   h.fo_tri = nquads();
   for (int k = 0; k < nk; k++)
-    if (tri_index[k] >= 0) {
+    if (tri_index[k] >= 0 && d->pairs[rows[k].pair].kind == BX_PAIR_CAPSULE_CLIPPED_PLANE) {
+      if (k > 0 && rows[k].pair == rows[k - 1].pair) continue;   // one block per pair
+      const bx_pair& p = d->pairs[rows[k].pair];
+      for (int v = 0; v < 3; v++) quad(p.tri[0][v][0], p.tri[0][v][1], p.tri[0][v][2], 0.f);   // normal, pos, x
+      quad(p.tri[1][0][0], p.tri[1][0][1], p.tri[1][0][2], 0.f);                              // y
+      quad(p.tri[1][1][0], p.tri[1][1][1], 0.f, 0.f);                                          // halfsize_x, halfsize_y
+      for (int v = 0; v < 3; v++) quad(0.f, 0.f, 0.f, 0.f);
+    } else if (tri_index[k] >= 0) {
       const bx_pair& p = d->pairs[rows[k].pair];
       const int f = rows[k].c;
       for (int v = 0; v < 3; v++) quad(p.tri[f][v][0], p.tri[f][v][1], p.tri[f][v][2], 0.f);
@@ -790,9 +802,9 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
     s->fusable = desc->dynamics_mode == BX_MODE_PBD && max_rows <= 2;
     for (int i = 0; i < desc->num_pairs; i++)
       if (desc->pairs[i].two_way || desc->pairs[i].kind == BX_PAIR_CAPSULE_CAPSULE ||
-          desc->pairs[i].kind == BX_PAIR_CAPSULE_BOX) {
+          desc->pairs[i].kind == BX_PAIR_CAPSULE_BOX || desc->pairs[i].kind == BX_PAIR_CAPSULE_CLIPPED_PLANE) {
         if (s->cc != BX_CC_MESH) s->cc = BX_CC_ALL;
-        if (desc->pairs[i].kind == BX_PAIR_CAPSULE_BOX) s->cc = BX_CC_MESH;
+        if (desc->pairs[i].kind == BX_PAIR_CAPSULE_BOX || desc->pairs[i].kind == BX_PAIR_CAPSULE_CLIPPED_PLANE) s->cc = BX_CC_MESH;
         s->fusable = false;
       }
     // Measured (profiles/r01_sweeps.txt): the fused section wins when the chains

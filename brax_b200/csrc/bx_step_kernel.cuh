@@ -832,6 +832,31 @@ BXS Contact contact_fn(int kind, const float4* cq, const float4* tq, V3 pa, Q4 r
     ct.vel = (va + cross(wa, ct.pos - pa)) - (vb + cross(wb, ct.pos - pb));
     return ct;
   }
+  if ((BX_FEAT & BXF_CAPSULE_BOX) && kind == BX_PAIR_CAPSULE_CLIPPED_PLANE) {
+    // capsule_clippedplane (colliders.py:762-802): tq = {normal, pos, x, y, {halfsize_x, halfsize_y}} of the
+    // plane in the body-b frame; this row's capsule end in cq[CQ_PTS]
+    const M3 mb = rotmat(rb);
+    const V3 n0 = mrot(mb, f3(tq[0]));
+    // the normal is oriented so that it points at the capsule body's position (:771-773: qp_a.pos . normal)
+    const float dir = dot(pa, n0) > 0.f ? 1.f : -1.f;
+    const V3 n = n0 * dir;
+    ct.pos = (pa + rotate(f3(cq[CQ_PTS]), ra)) - n * mat.z;
+    ct.vel = va + cross(wa, ct.pos - pa);
+    const V3 plane_pt = mrot(mb, f3(tq[1])) + pb;
+    ct.pen = dot(plane_pt - ct.pos, n);
+    ct.normal = n;
+    // clip against the four side planes (:779-798): normal * normal_dir is the flipped normal times dir again
+    const V3 nx = mrot(mb, f3(tq[2])), ny = mrot(mb, f3(tq[3]));
+    const float4 hs = tq[4];
+    const V3 nn = n * dir;
+    const V3 yn = cross(nn, nx), xn = -cross(nn, ny);
+    const V3 rel = ct.pos - plane_pt;
+    // point_in_front_of_plane (geometry.py:563-565): (pt - plane_pt) . plane_normal > 1e-6
+    const bool open = dot(rel - nx * hs.x, xn) > 1e-6f || dot(rel + nx * hs.x, -xn) > 1e-6f ||
+                      dot(rel - ny * hs.y, yn) > 1e-6f || dot(rel + ny * hs.y, -yn) > 1e-6f;
+    if (open) ct.pen = -1.f;
+    return ct;
+  }
   if (BXF_IS(kind == BX_PAIR_CAPSULE_CAPSULE, BXF_CAPSULE_CAPSULE,
              BXF_CAPSULE_PLANE | BXF_BOX_PLANE)) {
     const M3 ma = rotmat(ra), mb = rotmat(rb);

@@ -27,7 +27,7 @@ JOINT_KIND = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
               'spring_universal': 3, 'spring_spherical': 4}
 ACT_KIND = {'torque': 0, 'angle': 1}
 FORCE_KIND = {'thruster': 0, 'twister': 1}
-PAIR_KIND = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2, 'capsule_box': 3}
+PAIR_KIND = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2, 'capsule_box': 3, 'capsule_clippedplane': 4}
 
 MAX_BODIES, MAX_JOINTS, MAX_ACTUATORS = 64, 64, 64
 MAX_FORCES, MAX_PAIRS, MAX_CONTACTS, MAX_GROUPS = 32, 64, 128, 8
@@ -279,6 +279,11 @@ class SystemDesc:
           c.tri_normal[f][:] = _f(trn[f])
           for v in range(3):
             c.tri[f][v][:] = _f(tri[f, v])
+      if p['kind'] == 'capsule_clippedplane':
+        cl = p['clip']      # geometry.ClippedPlane: normal, pos, x, y, halfsize (body-b frame)
+        c.tri[0][0][:], c.tri[0][1][:], c.tri[0][2][:] = _f(cl['normal']), _f(cl['pos']), _f(cl['x'])
+        c.tri[1][0][:] = _f(cl['y'])
+        c.tri[1][1][:] = _f(list(cl['halfsize']) + [0.0])
     d = CSystemDesc()
     d.struct_size = C.sizeof(CSystemDesc)
     d.abi_version = ABI_VERSION

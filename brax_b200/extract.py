@@ -26,7 +26,7 @@ _JOINT_KINDS = {
     ('brax.physics.spring_joints', 'Universal'): 'spring_universal',
     ('brax.physics.spring_joints', 'Spherical'): 'spring_spherical',
 }
-_PAIR_KINDS = {'capsule_plane', 'capsule_capsule', 'box_plane', 'capsule_box'}
+_PAIR_KINDS = {'capsule_plane', 'capsule_capsule', 'box_plane', 'capsule_box', 'capsule_clippedplane'}
 
 
 def _a(x) -> np.ndarray:
@@ -115,6 +115,14 @@ def _pair_rows(collider, group: int) -> List[Dict[str, Any]]:
       r['n_contacts'] = int(ends.shape[0])
       r['pts'] = ends.tolist()
       r['radius_a'] = float(_a(ca.radius)[i])
+    elif fn == 'capsule_clippedplane':
+      # colliders.py:762-802; geometry.CapsuleEnd (:262-288) against geometry.ClippedPlane (:215-239)
+      ends = _a(ca.end)[i].reshape(-1, 3)
+      r['n_contacts'] = int(ends.shape[0])
+      r['pts'] = ends.tolist()
+      r['radius_a'] = float(_a(ca.radius)[i])
+      r['clip'] = {'normal': _l(_a(cb.normal)[i]), 'pos': _l(_a(cb.pos)[i]), 'x': _l(_a(cb.x)[i]), 'y': _l(_a(cb.y)[i]),
+                   'halfsize': [float(_a(cb.halfsize_x)[i]), float(_a(cb.halfsize_y)[i])]}
     elif fn == 'box_plane':
       corners = _a(ca.corner)[i].reshape(-1, 3)  # geometry.py:123-136
       r['n_contacts'] = int(corners.shape[0])

@@ -62,6 +62,10 @@ extern "C" {
 /* colliders.py:822-849 capsule_mesh against geometry.TriangulatedBox (the ('capsule', 'box') entry of
  * colliders.get, :898-899; geometry.py:193-199, 462-540): one contact row per triangle of the box. */
 #define BX_PAIR_CAPSULE_BOX 3
+/* colliders.py:762-802 capsule_clippedplane (the ('capsule', 'clipped_plane') entry of colliders.get, :907-908;
+ * geometry.ClippedPlane geometry.py:215-239): capsule ends against a finite rectangle of a plane whose normal is
+ * oriented towards the capsule's body; a contact point in front of one of the four side planes is open. */
+#define BX_PAIR_CAPSULE_CLIPPED_PLANE 4
 
 #define BX_MAX_BODIES 64
 #define BX_MAX_JOINTS 64
@@ -123,7 +127,10 @@ typedef struct bx_force {
  *                   each body frame), radius_a, radius_b. n_contacts = 1.
  *   capsule_box   : pts[0] = end_a, pts[1] = pos_a, radius_a; tri[f][v] = vertex v of triangle f
  *                   of the box in the body-b frame (BaseMesh.faces, geometry.py:146-156),
- *                   tri_normal[f] its normal. n_contacts = 12 (one row per triangle). */
+ *                   tri_normal[f] its normal. n_contacts = 12 (one row per triangle).
+ *   capsule_clipped_plane: pts[0..n_contacts-1] = capsule ends, radius_a (as capsule_plane); the plane in the
+ *                   body-b frame (geometry.py:222-239): tri[0][0] = normal, tri[0][1] = pos, tri[0][2] = x,
+ *                   tri[1][0] = y, tri[1][1] = {halfsize_x, halfsize_y, 0}. One-way only. */
 typedef struct bx_pair {
   int32_t kind;
   int32_t group;   /* collider group: averaging is per group (colliders.py:231) */
@@ -134,7 +141,7 @@ typedef struct bx_pair {
   float elasticity; /* elasticity_a * elasticity_b */
   float radius_a, radius_b;
   float pts[8][3];
-  float tri[12][3][3];    /* capsule_box only */
+  float tri[12][3][3];    /* capsule_box; capsule_clipped_plane: the plane (see above) */
   float tri_normal[12][3];
 } bx_pair;
 

@@ -66,7 +66,7 @@ enum { MODE_PBD = 0, MODE_SPRING = 1 };
 enum { J_REV = 0, J_SPH = 1, J_SREV = 2, J_SUNI = 3, J_SSPH = 4 };
 enum { A_TORQUE = 0, A_ANGLE = 1 };
 enum { F_THRUSTER = 0, F_TWISTER = 1 };
-enum { P_CAPSULE_PLANE = 0, P_CAPSULE_CAPSULE = 1, P_BOX_PLANE = 2, P_CAPSULE_BOX = 3 };
+enum { P_CAPSULE_PLANE = 0, P_CAPSULE_CAPSULE = 1, P_BOX_PLANE = 2, P_CAPSULE_BOX = 3, P_CAPSULE_CLIPPED_PLANE = 4 };
 
 #define MAXB 64
 #define MAXK 128
@@ -818,6 +818,55 @@ static void pair_contacts(const osys* s, const opair* p, const oqp* qp, ocontact
         d[k] = qp->pos[b][k] - out[c].pos[k];
       }
       out[c].pen = dot3(d, n);
+    }
+  } else if (p->kind == P_CAPSULE_CLIPPED_PLANE) { /* colliders.py:762-802; plane data in tri[0], tri[1] */
+    const R* pl_normal = p->tri[0][0];
+    const R* pl_pos = p->tri[0][1];
+    const R* pl_x = p->tri[0][2];
+    const R* pl_y = p->tri[1][0];
+    const R hx = p->tri[1][1][0], hy = p->tri[1][1][1];
+    for (int c = 0; c < p->n_contacts; c++) {
+      R e[3], n[3], r[3], cr[3], d[3], ppt[3], nx[3], ny[3], nn[3], yn[3], xn[3];
+      rotate(p->pts[c], qp->rot[a], e);
+      for (int k = 0; k < 3; k++) e[k] = qp->pos[a][k] + e[k];
+      rotate(pl_normal, qp->rot[b], n);
+      /* orient the normal s.t. it points at the CoM of the capsule (:771-773) */
+      R dir = dot3(qp->pos[a], n) > C(0.) ? C(1.) : C(-1.);
+      for (int k = 0; k < 3; k++) n[k] = n[k] * dir;
+      for (int k = 0; k < 3; k++) {
+        out[c].pos[k] = e[k] - n[k] * p->radius_a;
+        r[k] = out[c].pos[k] - qp->pos[a][k];
+      }
+      cross3(qp->ang[a], r, cr);
+      rotate(pl_pos, qp->rot[b], ppt);
+      for (int k = 0; k < 3; k++) {
+        out[c].vel[k] = qp->vel[a][k] + cr[k];
+        out[c].normal[k] = n[k];
+        ppt[k] = ppt[k] + qp->pos[b][k];
+        d[k] = ppt[k] - out[c].pos[k];
+      }
+      R pen = dot3(d, n);
+      /* clip against side planes (:779-798) */
+      rotate(pl_x, qp->rot[b], nx);
+      rotate(pl_y, qp->rot[b], ny);
+      for (int k = 0; k < 3; k++) nn[k] = n[k] * dir;
+      cross3(nn, nx, yn);
+      cross3(nn, ny, xn);
+      for (int k = 0; k < 3; k++) xn[k] = -xn[k];
+      int open = 0;
+      for (int sd = 0; sd < 4; sd++) {
+        const R* dv = sd < 2 ? nx : ny;
+        const R* sn = sd < 2 ? xn : yn;
+        R hs = sd < 2 ? hx : hy, sg = (sd & 1) ? C(-1.) : C(1.);
+        R spt[3], rel[3], snn[3];
+        for (int k = 0; k < 3; k++) {
+          spt[k] = (sd & 1) ? ppt[k] - dv[k] * hs : ppt[k] + dv[k] * hs;
+          rel[k] = out[c].pos[k] - spt[k];
+          snn[k] = sg * sn[k];
+        }
+        if (dot3(rel, snn) > C(1e-6)) open = 1; /* geometry.py:563-565 */
+      }
+      out[c].pen = open ? C(-1.) : pen;
     }
   } else if (p->kind == P_CAPSULE_BOX) { /* capsule_mesh colliders.py:822-849, one row per triangle */
     R pa[3], ea[3], a0[3], a1[3];

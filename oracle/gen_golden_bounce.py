@@ -164,6 +164,51 @@ def main(only):
       if mode == 'spring':
         c.dynamics_mode = 'legacy_spring'
       roll(n, c, 0, 80)
+    # CapsuleClippedPlaneTest (physics_test.py:426-476): three spheres, one lands on the clipped plane, two
+    # miss it and land on the ground -- the config AS IS except dt: the reference takes ONE step of
+    # dt 2 / 800 substeps; here the same 800 substeps of 0.0025 s run as 40 steps of 20 (same arithmetic)
+    n = 'clipped_plane_%s' % mode
+    if want(n):
+      c = text_format.Parse(pt.CapsuleClippedPlaneTest._CONFIG, brax.Config())
+      assert abs(c.dt / c.substeps - 0.0025) < 1e-9
+      c.dt, c.substeps = 0.05, 20
+      if mode == 'spring':
+        c.dynamics_mode = 'legacy_spring'
+      roll(n, c, 0, 40)
+    # a tilted clipped plane: a capsule (two ends) lands on it, rolls down and leaves over the lower edge, a ball
+    # rolls down it and leaves over the side; both end on the ground (the side-plane clipping opens the contacts
+    # while the bodies are still above the plane: an end that re-enters the rectangle from below would be
+    # ejected by the reference's one-sided penetration -- :776 -- a launch this scene avoids)
+    n = 'clipped_ramp_%s' % mode
+    if want(n):
+      c = text_format.Parse('''
+        dt: 0.02 substeps: 8 friction: 0.5 elasticity: 0.2
+        gravity { z: -9.8 }
+        bodies {
+          name: "cap" mass: 1
+          colliders { rotation { x: 90 } capsule { radius: .15 length: 1.0 } }
+          inertia { x: 0.1 y: 0.1 z: 0.1 }
+        }
+        bodies {
+          name: "ball" mass: 0.5
+          colliders { sphere { radius: .2 } }
+          inertia { x: 0.01 y: 0.01 z: 0.01 }
+        }
+        bodies {
+          name: "ramp" mass: 1
+          colliders { rotation { y: 15 } position { z: 1.0 } clipped_plane { halfsize_x: 1.5 halfsize_y: 0.8 } }
+          frozen { all: true }
+        }
+        bodies { name: "Ground" frozen: { all: true } colliders { plane {}}}
+        defaults {
+          qps { name: "cap" pos { x: 0.7 y: 0.1 z: 1.2 } vel { z: -0.5 } ang { z: 0.2 } }
+          qps { name: "ball" pos { x: -0.8 y: -0.3 z: 1.9 } vel { y: -0.6 } }
+          qps { name: "ramp" pos { x: 0 } }
+        }
+      ''', brax.Config())
+      if mode == 'spring':
+        c.dynamics_mode = 'legacy_spring'
+      roll(n, c, 0, 90)
     n = 'ball_plane_%s_e50' % mode
     if want(n):
       c = text_format.Parse('''

@@ -23,7 +23,7 @@ _JK = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
        'spring_universal': 3, 'spring_spherical': 4}
 _AK = {'torque': 0, 'angle': 1}
 _FK = {'thruster': 0, 'twister': 1}
-_PK = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2, 'capsule_box': 3}
+_PK = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2, 'capsule_box': 3, 'capsule_clippedplane': 4}
 
 
 def build(force: bool = False):
@@ -239,6 +239,11 @@ class Oracle:
           c.tri_normal[f][:] = arr(trn[f])
           for v in range(3):
             c.tri[f][v][:] = arr(tri[f, v])
+      if p['kind'] == 'capsule_clippedplane':
+        cl = p['clip']
+        c.tri[0][0][:], c.tri[0][1][:], c.tri[0][2][:] = arr(cl['normal']), arr(cl['pos']), arr(cl['x'])
+        c.tri[1][0][:] = arr(cl['y'])
+        c.tri[1][1][:] = arr(list(cl['halfsize']) + [0.0])
     s = Sys()
     s.mode = _MODE[desc.dynamics_mode]
     s.substeps, s.nb, s.nj = desc.substeps, nb, nj

@@ -88,15 +88,23 @@ def chain(step_fn, g, steps):
 
 
 def test_cases_present():
-  assert len(CASES) == 22, CASES
+  assert len(CASES) == 26, CASES
+  assert sum(c.startswith('clipped_') for c in CASES) == 4
   assert sum(c.startswith('ball_wall') for c in CASES) == 6 and sum(c.startswith('capsule_on_box') for c in CASES) == 2
   descs = [load_case(c)[0] for c in CASES]
   assert any(p['kind'] == 'capsule_box' and p['two_way'] for d in descs for p in d.pairs)
   assert any(p['kind'] == 'capsule_box' and not p['two_way'] and p['elasticity_a'] * p['elasticity_b'] > 0
              for d in descs for p in d.pairs)
   assert any(p['elasticity_a'] * p['elasticity_b'] > 0 and p['two_way'] for d in descs for p in d.pairs)
+  assert any(p['kind'] == 'capsule_clippedplane' and p['n_contacts'] == 2 and p['clip']['normal'][0] != 0 for d in descs for p in d.pairs)
   assert any(p['elasticity_a'] * p['elasticity_b'] > 0 and not p['two_way'] and p['kind'] == 'capsule_capsule' for d in descs for p in d.pairs)
   assert any(p['elasticity_a'] * p['elasticity_b'] > 0 and p['kind'] == 'capsule_plane' for d in descs for p in d.pairs)
+
+
+def clipped_plane_holds(pos):
+  """CapsuleClippedPlaneTest.test_collision (physics_test.py:463-476), after the 800 substeps: sphere1 rests on
+  the clipped plane, sphere2 / sphere3 missed it and rest on the ground (assertAlmostEqual places=4)."""
+  return abs(pos[0, 2] - 2.5) < 0.5e-4 and abs(pos[1, 2] - 0.5) < 0.5e-4 and abs(pos[2, 2] - 0.5) < 0.5e-4
 
 
 def wall_bounce_holds(vx, v0_x, e):
@@ -119,6 +127,8 @@ def test_oracle_reproduces_reference_bounce(case):
     assert restitution_holds(case, vz_in_ref, vz_ref, e)
   if case.startswith('ball_wall'):
     assert wall_bounce_holds(g['out_vel'][:, 0, 0], float(g['vel'][0, 0, 0]), e)
+  if case == 'clipped_plane_pbd':     # (the reference test runs the config's mode, pbd; legacy_spring rests 6 mm deep)
+    assert clipped_plane_holds(g['out_pos'][-1])
   literal = reference_assertion(case, vz_ref, v0, e)
   # every stored step from the reference's own state: float64 oracle == reference (the pin)
   o64 = Oracle(desc, np.float64)
@@ -148,10 +158,12 @@ def test_oracle_reproduces_reference_bounce(case):
       assert restitution_holds(case, vz_in, traj[:, 2], e), (case, dtype)
     if case.startswith('ball_wall'):
       assert wall_bounce_holds(traj[:, 0], float(g['vel'][0, 0, 0]), e), (case, dtype, traj[99])
+    if case == 'clipped_plane_pbd':
+      assert clipped_plane_holds(cur['pos']), (case, dtype, cur['pos'][:3, 2])
     if dtype == np.float64:
       # (the tumbling capsule of capsule_on_box amplifies last-bit differences -- a tie decided the other
       # way in one contact row -- to 3e-5 over its 80 steps; every single step of it is pinned above)
-      np.testing.assert_allclose(traj, g['out_vel'][:, 0], rtol=0, atol=1e-3 if case.startswith('capsule_on_box') else 1e-6)
+      np.testing.assert_allclose(traj, g['out_vel'][:, 0], rtol=0, atol=1e-3 if case.startswith(('capsule_on_box', 'clipped_ramp')) else 1e-6)
       assert reference_assertion(case, traj[:, 2], v0, e) == literal
   if not vertical:
     return
@@ -228,7 +240,11 @@ def test_cuda_path_on_reference_bounce(case):
   if case.startswith('ball_wall'):
     assert wall_bounce_holds(traj[:, 0], float(g['vel'][0, 0, 0]), e), (case, traj[99])
     hits = np.nonzero(np.abs(g['out_vel'][:, 0, 0] - g['vel'][:, 0, 0]) > 0.5)[0]   # the step at the wall
-  elif case.startswith('capsule_on_box'):
+  elif case.startswith('capsule_on_box') or case.startswith('clipped_ramp'):
+    return
+  elif case.startswith('clipped_plane'):
+    if case == 'clipped_plane_pbd':
+      assert clipped_plane_holds(cur['pos']), (case, cur['pos'][:3, 2])   # the reference test's assertion on the CUDA chain
     return
   else:
     vz_in = np.concatenate([[float(g['vel'][0, 0, 2])], traj[:-1, 2]])
