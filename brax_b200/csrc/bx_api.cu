@@ -42,6 +42,7 @@ struct bx_system {
   cudaStream_t streams[BX_HOST_STREAMS];
   bx_reset_desc* d_reset;  // device copy of desc.reset (bx_default_qp), or NULL
   int reset_dof;
+  float* d_hm;  // height grids of the box_heightmap pairs, concatenated in pair order, or NULL
 };
 
 cudaError_t bx_reset_launch(const bx_reset_desc* d_tables, int nb, int64_t num_envs, const float* joint_angle,
@@ -118,8 +119,8 @@ static int validate(const bx_system_desc* d) {
   int k = 0;
   for (int i = 0; i < d->num_pairs; i++) {
     const bx_pair& p = d->pairs[i];
-    if (p.kind < BX_PAIR_CAPSULE_PLANE || p.kind > BX_PAIR_CAPSULE_CLIPPED_PLANE)
-      return fail("unsupported collider pair kind (general mesh/heightmap/clipped-plane/box-box are out of scope)");
+    if (p.kind < BX_PAIR_CAPSULE_PLANE || p.kind > BX_PAIR_BOX_HEIGHTMAP)
+      return fail("unsupported collider pair kind (general meshes and box-box are out of scope)");
     if (p.body_a < 0 || p.body_a >= d->num_bodies || p.body_b < 0 || p.body_b >= d->num_bodies)
       return fail("pair body index out of range");
     if (p.group < 0 || p.group >= BX_MAX_GROUPS) return fail("pair group out of range");
@@ -130,6 +131,8 @@ static int validate(const bx_system_desc* d) {
     if (p.kind == BX_PAIR_CAPSULE_BOX && p.n_contacts != 12) return fail("capsule_box has 12 contacts (one per triangle)");
     if (p.kind != BX_PAIR_CAPSULE_CAPSULE && p.kind != BX_PAIR_CAPSULE_BOX && p.two_way)
       return fail("two-way plane colliders do not exist");
+    if (p.kind == BX_PAIR_BOX_HEIGHTMAP && (!p.hm_height || p.hm_size < 2 || p.hm_size > 1024 || !(p.hm_cell_size > 0.f)))
+      return fail("box_heightmap needs hm_height, 2 <= hm_size <= 1024 and hm_cell_size > 0");
     k += p.n_contacts;
   }
   if (k > BX_MAX_CONTACTS) return fail("too many contact rows");
@@ -216,11 +219,16 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
   std::vector<int> normal_row(nk, 0), tri_index(nk, -1);
   int n_normals = 0, n_tris = 0;
   for (int k = 0; k < nk; k++) {
-    const bool per_row = d->pairs[rows[k].pair].kind == BX_PAIR_CAPSULE_BOX;
+    const int kind_k = d->pairs[rows[k].pair].kind;
+    const bool per_row = kind_k == BX_PAIR_CAPSULE_BOX || kind_k == BX_PAIR_BOX_HEIGHTMAP;   // a normal per row
     const bool new_pair = k == 0 || rows[k].pair != rows[k - 1].pair;
     if (per_row || new_pair) n_normals++;
     normal_row[k] = n_normals - 1;
-    if (per_row) tri_index[k] = n_tris++;
+    if (kind_k == BX_PAIR_CAPSULE_BOX) tri_index[k] = n_tris++;
+    // box_heightmap: the rows of a pair share one 4-quad block {cell_size, size, offset of the grid in h.hm}
+    if (kind_k == BX_PAIR_BOX_HEIGHTMAP) {
+      if (new_pair) tri_index[k] = n_tris++; else tri_index[k] = tri_index[k - 1];
+    }
     // capsule_clipped_plane: the rows of a pair share one 8-quad block {normal, pos, x, y, halfsize, -, -, -}
     if (d->pairs[rows[k].pair].kind == BX_PAIR_CAPSULE_CLIPPED_PLANE) {
       if (new_pair) { tri_index[k] = n_tris; n_tris += 2; } else tri_index[k] = tri_index[k - 1];
@@ -308,7 +316,15 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
   // capsule_box rows: {p0, p1, p2, normal} of the row's triangle (body-b frame), 4 quads each
   h.fo_tri = nquads();
   for (int k = 0; k < nk; k++)
-    if (tri_index[k] >= 0 && d->pairs[rows[k].pair].kind == BX_PAIR_CAPSULE_CLIPPED_PLANE) {
+    if (tri_index[k] >= 0 && d->pairs[rows[k].pair].kind == BX_PAIR_BOX_HEIGHTMAP) {
+      if (k > 0 && rows[k].pair == rows[k - 1].pair) continue;   // one block per pair
+      const bx_pair& p = d->pairs[rows[k].pair];
+      int off = 0;   // grids are concatenated in pair order (bx_system_create uploads them the same way)
+      for (int q = 0; q < rows[k].pair; q++)
+        if (d->pairs[q].kind == BX_PAIR_BOX_HEIGHTMAP) off += d->pairs[q].hm_size * d->pairs[q].hm_size;
+      quad(p.hm_cell_size, static_cast<float>(p.hm_size), static_cast<float>(off), 0.f);
+      for (int v = 0; v < 3; v++) quad(0.f, 0.f, 0.f, 0.f);
+    } else if (tri_index[k] >= 0 && d->pairs[rows[k].pair].kind == BX_PAIR_CAPSULE_CLIPPED_PLANE) {
       if (k > 0 && rows[k].pair == rows[k - 1].pair) continue;   // one block per pair
       const bx_pair& p = d->pairs[rows[k].pair];
       for (int v = 0; v < 3; v++) quad(p.tri[0][v][0], p.tri[0][v][1], p.tri[0][v][2], 0.f);   // normal, pos, x
@@ -802,9 +818,9 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
     s->fusable = desc->dynamics_mode == BX_MODE_PBD && max_rows <= 2;
     for (int i = 0; i < desc->num_pairs; i++)
       if (desc->pairs[i].two_way || desc->pairs[i].kind == BX_PAIR_CAPSULE_CAPSULE ||
-          desc->pairs[i].kind == BX_PAIR_CAPSULE_BOX || desc->pairs[i].kind == BX_PAIR_CAPSULE_CLIPPED_PLANE) {
+          desc->pairs[i].kind >= BX_PAIR_CAPSULE_BOX) {
         if (s->cc != BX_CC_MESH) s->cc = BX_CC_ALL;
-        if (desc->pairs[i].kind == BX_PAIR_CAPSULE_BOX || desc->pairs[i].kind == BX_PAIR_CAPSULE_CLIPPED_PLANE) s->cc = BX_CC_MESH;
+        if (desc->pairs[i].kind >= BX_PAIR_CAPSULE_BOX) s->cc = BX_CC_MESH;   // capsule_box, capsule_clipped_plane, box_heightmap
         s->fusable = false;
       }
     // Measured (profiles/r01_sweeps.txt): the fused section wins when the chains
@@ -854,10 +870,11 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   s->d_tab_i = nullptr;
   s->d_tab_f = nullptr;
   s->d_reset = nullptr;
+  s->d_hm = nullptr;
   s->reset_dof = 0;
   auto drop = [&](const char* what, cudaError_t err) {   // frees whatever exists of a half-built system
     const std::string m = std::string(what) + (err != cudaSuccess ? std::string(": ") + cudaGetErrorString(err) : "");
-    cudaFree(s->d_tab_i); cudaFree(s->d_tab_f); cudaFree(s->d_reset);
+    cudaFree(s->d_tab_i); cudaFree(s->d_tab_f); cudaFree(s->d_reset); cudaFree(s->d_hm);
     delete s;
     return fail(m);
   };
@@ -870,6 +887,18 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   if (set_smem_attr(static_cast<int>(prop.sharedMemPerBlockOptin))) {
     const std::string keep = g_err;
     return drop(keep.c_str(), cudaSuccess);
+  }
+  {
+    std::vector<float> hm;   // height grids of the box_heightmap pairs, in pair order
+    for (int i = 0; i < desc->num_pairs; i++)
+      if (desc->pairs[i].kind == BX_PAIR_BOX_HEIGHTMAP)
+        hm.insert(hm.end(), desc->pairs[i].hm_height, desc->pairs[i].hm_height + desc->pairs[i].hm_size * desc->pairs[i].hm_size);
+    if (!hm.empty()) {
+      if ((e1 = cudaMalloc(&s->d_hm, hm.size() * 4)) != cudaSuccess) return drop("cudaMalloc of the height grids failed", e1);
+      if ((e1 = cudaMemcpy(s->d_hm, hm.data(), hm.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess)
+        return drop("upload of the height grids failed", e1);
+      s->h.hm = s->d_hm;
+    }
   }
   if (desc->reset) {
     if ((e1 = cudaMalloc(&s->d_reset, sizeof(bx_reset_desc))) != cudaSuccess) return drop("cudaMalloc of reset tables failed", e1);
@@ -907,6 +936,7 @@ extern "C" void bx_system_destroy(bx_system* s) {
   cudaFree(s->d_tab_f);
   cudaFree(s->d_scratch);
   cudaFree(s->d_reset);
+  cudaFree(s->d_hm);
   for (int i = 0; i < BX_HOST_STREAMS; i++)
     if (s->streams[i]) cudaStreamDestroy(s->streams[i]);
   delete s;

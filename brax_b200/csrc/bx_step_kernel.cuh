@@ -812,10 +812,43 @@ BXS float pair_friction(const BxHeader& h, float table) {
 
 // contact function of one contact row (colliders.py:667-680 box_plane,
 // :744-759 capsule_plane, :805-819 capsule_capsule).
-BXS Contact contact_fn(int kind, const float4* cq, const float4* tq, V3 pa, Q4 ra, V3 va, V3 wa, V3 pb, Q4 rb,
-                       V3 vb, V3 wb) {
+BXS Contact contact_fn(const BxHeader& h, int kind, const float4* cq, const float4* tq, V3 pa, Q4 ra, V3 va, V3 wa, V3 pb,
+                       Q4 rb, V3 vb, V3 wb) {
   Contact ct;
   const float4 mat = cq[CQ_MAT];
+  if ((BX_FEAT & BXF_CAPSULE_BOX) && kind == BX_PAIR_BOX_HEIGHTMAP) {
+    // box_heightmap (colliders.py:699-742): this row's box corner against the triangle of the height grid
+    // under it; tq[0] = {cell_size, grid size n, offset of the grid in h.hm}
+    const V3 off = rotate(f3(cq[CQ_PTS]), ra);
+    ct.pos = pa + off;                  // QP.to_world base.py:112-125
+    ct.vel = va + cross(wa, off);
+    const Q4 rbi = q4(rb.w, -rb.x, -rb.y, -rb.z);
+    const V3 lp = rotate(ct.pos - pb, rbi);   // math.inv_rotate
+    const float cell = tq[0].x;
+    const int n = static_cast<int>(tq[0].y);
+    const float* grid = h.hm + static_cast<int>(tq[0].z);
+    const float u = __fdiv_rn(lp.x, cell), v = __fdiv_rn(lp.y, cell);
+    const float fu = floorf(u), fv = floorf(v);
+    const int iu = static_cast<int>(fu), iv = static_cast<int>(fv);
+    const bool lower = (u - fu) + (v - fv) < 1.f;   // the square's two triangles (:716-717)
+    const float mu = lower ? -1.f : 1.f;
+    const int tu0 = iu + (lower ? 0 : 1), tu1 = iu + (lower ? 1 : 0), tu2 = tu0;
+    const int tv0 = iv + (lower ? 0 : 1), tv1 = tv0, tv2 = iv + (lower ? 1 : 0);
+    // height[u, -v] (:726): a negative index wraps once, anything still outside is clamped (jax gather)
+    auto at = [&](int a, int b) {
+      b = -b;
+      a = a < 0 ? a + n : a; b = b < 0 ? b + n : b;
+      a = min(max(a, 0), n - 1); b = min(max(b, 0), n - 1);
+      return __ldg(grid + a * n + b);
+    };
+    const float h0 = at(tu0, tv0), h1 = at(tu1, tv1), h2 = at(tu2, tv2);
+    const V3 raw = v3(mu * (h1 - h0), mu * (h2 - h0), cell);
+    const V3 nl = vdiv(raw, safe_norm(raw));
+    const V3 p0 = v3(static_cast<float>(tu0) * cell, static_cast<float>(tv0) * cell, h0);
+    ct.pen = dot(p0 - lp, nl);
+    ct.normal = rotate(nl, rb);
+    return ct;
+  }
   if ((BX_FEAT & BXF_CAPSULE_BOX) && kind == BX_PAIR_CAPSULE_BOX) {
     // capsule_mesh (colliders.py:822-849) against one triangle of the box: tq = {p0, p1, p2, normal}
     const M3 ma = rotmat(ra), mb = rotmat(rb);
@@ -902,7 +935,7 @@ BXS void c1_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
     const int ra0 = L::BQ * a, rb0 = L::BQ * b;
     V3 pa = ldv(c, ra0 + co), pb = ldv(c, rb0 + co);
     Q4 ra = ldq(c, ra0 + co + 1), rb = ldq(c, rb0 + co + 1);
-    Contact ct = contact_fn(ci.x, cq, c.tf + h.fo_tri + c.ti[h.io_contact + k * CI_STRIDE + CI_TRI], pa, ra,
+    Contact ct = contact_fn(h, ci.x, cq, c.tf + h.fo_tri + c.ti[h.io_contact + k * CI_STRIDE + CI_TRI], pa, ra,
                             ldv(c, ra0 + L::VEL), ldv(c, ra0 + L::ANG), pb, rb,
                             ldv(c, rb0 + L::VEL), ldv(c, rb0 + L::ANG));
     V3 iia = f3(bqa[BQ_INV_INERTIA]);
@@ -1337,7 +1370,7 @@ BXS void spring_row(const Ctx& c, const BxHeader& h, int k, CAcc& acc) {
     const float4* bqb = c.tf + h.fo_body + b * BQ_STRIDE;
     const int ra0 = L::BQ * a, rb0 = L::BQ * b;
     V3 pa = ldv(c, ra0 + po), pb = ldv(c, rb0 + po);
-    Contact ct = contact_fn(ci.x, cq, c.tf + h.fo_tri + c.ti[h.io_contact + k * CI_STRIDE + CI_TRI], pa,
+    Contact ct = contact_fn(h, ci.x, cq, c.tf + h.fo_tri + c.ti[h.io_contact + k * CI_STRIDE + CI_TRI], pa,
                             ldq(c, ra0 + po + 1), ldv(c, ra0 + L::VEL), ldv(c, ra0 + L::ANG),
                             pb, ldq(c, rb0 + po + 1), ldv(c, rb0 + L::VEL), ldv(c, rb0 + L::ANG));
     const float4 mat = cq[CQ_MAT];

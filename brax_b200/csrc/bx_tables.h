@@ -141,6 +141,8 @@ struct BxHeader {
   // per-env collider friction (bx_step_io.friction): float index in shared memory of the tile's 32
   // friction[e]^2 values (behind the mbarriers), set per launch; 0 = the pair tables' friction
   int32_t fr_off;
+  // box_heightmap pairs: the height grids of the system, concatenated (device memory; NULL without one)
+  const float* hm;
   BxSeg seg_in[BX_SEG_IN];
   BxSeg seg_out[BX_SEG_OUT];
   // scalars

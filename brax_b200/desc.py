@@ -20,14 +20,15 @@ from typing import Any, Dict, List
 
 import numpy as np
 
-ABI_VERSION = 11
+ABI_VERSION = 12
 
 MODE = {'pbd': 0, 'legacy_spring': 1}
 JOINT_KIND = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
               'spring_universal': 3, 'spring_spherical': 4}
 ACT_KIND = {'torque': 0, 'angle': 1}
 FORCE_KIND = {'thruster': 0, 'twister': 1}
-PAIR_KIND = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2, 'capsule_box': 3, 'capsule_clippedplane': 4}
+PAIR_KIND = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2, 'capsule_box': 3, 'capsule_clippedplane': 4,
+             'box_heightmap': 5}
 
 MAX_BODIES, MAX_JOINTS, MAX_ACTUATORS = 64, 64, 64
 MAX_FORCES, MAX_PAIRS, MAX_CONTACTS, MAX_GROUPS = 32, 64, 128, 8
@@ -67,7 +68,8 @@ class CPair(C.Structure):
               ('friction', C.c_float), ('elasticity', C.c_float),
               ('radius_a', C.c_float), ('radius_b', C.c_float),
               ('pts', (C.c_float * 3) * 8), ('tri', ((C.c_float * 3) * 3) * 12),
-              ('tri_normal', (C.c_float * 3) * 12)]
+              ('tri_normal', (C.c_float * 3) * 12),
+              ('hm_height', C.POINTER(C.c_float)), ('hm_size', C.c_int32), ('hm_cell_size', C.c_float)]
 
 
 class CResetJoint(C.Structure):
@@ -256,6 +258,7 @@ class SystemDesc:
       forces[i].act_index[:] = list(f['act_index'])
       forces[i].strength = f['strength']
     pairs = (CPair * max(1, len(self.pairs)))()
+    hm_keep = []
     for i, p in enumerate(self.pairs):
       c = pairs[i]
       c.kind = PAIR_KIND[p['kind']]
@@ -279,6 +282,12 @@ class SystemDesc:
           c.tri_normal[f][:] = _f(trn[f])
           for v in range(3):
             c.tri[f][v][:] = _f(tri[f, v])
+      if p['kind'] == 'box_heightmap':
+        hm = np.ascontiguousarray(np.asarray(p['heightmap']['height'], dtype=np.float32))
+        assert hm.ndim == 2 and hm.shape[0] == hm.shape[1]
+        hm_keep.append(hm)
+        c.hm_height = hm.ctypes.data_as(C.POINTER(C.c_float))
+        c.hm_size, c.hm_cell_size = int(hm.shape[0]), float(p['heightmap']['cell_size'])
       if p['kind'] == 'capsule_clippedplane':
         cl = p['clip']      # geometry.ClippedPlane: normal, pos, x, y, halfsize (body-b frame)
         c.tri[0][0][:], c.tri[0][1][:], c.tri[0][2][:] = _f(cl['normal']), _f(cl['pos']), _f(cl['x'])
@@ -309,7 +318,7 @@ class SystemDesc:
     d.env = C.cast(C.pointer(cenv), C.c_void_p) if cenv is not None else None
     creset = self.reset_to_c()
     d.reset = C.cast(C.pointer(creset), C.c_void_p) if creset is not None else None
-    return d, (bodies, joints, acts, forces, pairs, cenv, creset)
+    return d, (bodies, joints, acts, forces, pairs, cenv, creset, hm_keep)
 
   def reset_to_c(self):
     """bx_reset_desc of `self.reset` (extract._reset_desc), or None when the descriptor has none."""

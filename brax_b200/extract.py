@@ -26,7 +26,7 @@ _JOINT_KINDS = {
     ('brax.physics.spring_joints', 'Universal'): 'spring_universal',
     ('brax.physics.spring_joints', 'Spherical'): 'spring_spherical',
 }
-_PAIR_KINDS = {'capsule_plane', 'capsule_capsule', 'box_plane', 'capsule_box', 'capsule_clippedplane'}
+_PAIR_KINDS = {'capsule_plane', 'capsule_capsule', 'box_plane', 'capsule_box', 'capsule_clippedplane', 'box_heightmap'}
 
 
 def _a(x) -> np.ndarray:
@@ -123,6 +123,12 @@ def _pair_rows(collider, group: int) -> List[Dict[str, Any]]:
       r['radius_a'] = float(_a(ca.radius)[i])
       r['clip'] = {'normal': _l(_a(cb.normal)[i]), 'pos': _l(_a(cb.pos)[i]), 'x': _l(_a(cb.x)[i]), 'y': _l(_a(cb.y)[i]),
                    'halfsize': [float(_a(cb.halfsize_x)[i]), float(_a(cb.halfsize_y)[i])]}
+    elif fn == 'box_heightmap':
+      # colliders.py:699-742; geometry.Box corners (:123-136) against geometry.HeightMap (:292-308)
+      corners = _a(ca.corner)[i].reshape(-1, 3)
+      r['n_contacts'] = int(corners.shape[0])
+      r['pts'] = corners.tolist()
+      r['heightmap'] = {'height': _a(cb.height)[i].tolist(), 'cell_size': float(_a(cb.cell_size)[i])}
     elif fn == 'box_plane':
       corners = _a(ca.corner)[i].reshape(-1, 3)  # geometry.py:123-136
       r['n_contacts'] = int(corners.shape[0])

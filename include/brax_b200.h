@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BX_ABI_VERSION 11
+#define BX_ABI_VERSION 12
 
 /* dynamics_mode (base.py:179-201) */
 #define BX_MODE_PBD 0
@@ -66,6 +66,9 @@ extern "C" {
  * geometry.ClippedPlane geometry.py:215-239): capsule ends against a finite rectangle of a plane whose normal is
  * oriented towards the capsule's body; a contact point in front of one of the four side planes is open. */
 #define BX_PAIR_CAPSULE_CLIPPED_PLANE 4
+/* colliders.py:699-742 box_heightmap (the ('box', 'heightMap') entry of colliders.get, :895; geometry.HeightMap
+ * geometry.py:292-308): the 8 box corners against the triangle of the height grid under each corner. */
+#define BX_PAIR_BOX_HEIGHTMAP 5
 
 #define BX_MAX_BODIES 64
 #define BX_MAX_JOINTS 64
@@ -130,7 +133,12 @@ typedef struct bx_force {
  *                   tri_normal[f] its normal. n_contacts = 12 (one row per triangle).
  *   capsule_clipped_plane: pts[0..n_contacts-1] = capsule ends, radius_a (as capsule_plane); the plane in the
  *                   body-b frame (geometry.py:222-239): tri[0][0] = normal, tri[0][1] = pos, tri[0][2] = x,
- *                   tri[1][0] = y, tri[1][1] = {halfsize_x, halfsize_y, 0}. One-way only. */
+ *                   tri[1][0] = y, tri[1][1] = {halfsize_x, halfsize_y, 0}. One-way only.
+ *   box_heightmap : pts[0..7] = box corners in the body-a frame (as box_plane); hm_height = the hm_size x hm_size
+ *                   grid `HeightMap.height` row-major (HOST pointer, copied at bx_system_create), hm_cell_size =
+ *                   size / (hm_size - 1).  The grid is indexed height[u, -v] as the reference does (:726);
+ *                   negative indices wrap once, anything still outside is clamped (jax gather semantics; the
+ *                   reference calls collisions outside the map 'not well defined', :705-706). One-way only. */
 typedef struct bx_pair {
   int32_t kind;
   int32_t group;   /* collider group: averaging is per group (colliders.py:231) */
@@ -143,6 +151,9 @@ typedef struct bx_pair {
   float pts[8][3];
   float tri[12][3][3];    /* capsule_box; capsule_clipped_plane: the plane (see above) */
   float tri_normal[12][3];
+  const float* hm_height; /* box_heightmap only (else NULL) */
+  int32_t hm_size;
+  float hm_cell_size;
 } bx_pair;
 
 /* Optional env epilogue ("next" row N1): everything the reference's Env.step computes

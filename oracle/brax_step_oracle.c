@@ -49,6 +49,7 @@ typedef double R;
 #define ATAN2 atan2
 #define ACOS acos
 #define FABS fabs
+#define FLOOR floor
 #else
 typedef float R;
 #define FN(n) n##_f32
@@ -58,6 +59,7 @@ typedef float R;
 #define ATAN2 atan2f
 #define ACOS acosf
 #define FABS fabsf
+#define FLOOR floorf
 #endif
 
 #define C(x) ((R)(x))
@@ -66,7 +68,8 @@ enum { MODE_PBD = 0, MODE_SPRING = 1 };
 enum { J_REV = 0, J_SPH = 1, J_SREV = 2, J_SUNI = 3, J_SSPH = 4 };
 enum { A_TORQUE = 0, A_ANGLE = 1 };
 enum { F_THRUSTER = 0, F_TWISTER = 1 };
-enum { P_CAPSULE_PLANE = 0, P_CAPSULE_CAPSULE = 1, P_BOX_PLANE = 2, P_CAPSULE_BOX = 3, P_CAPSULE_CLIPPED_PLANE = 4 };
+enum { P_CAPSULE_PLANE = 0, P_CAPSULE_CAPSULE = 1, P_BOX_PLANE = 2, P_CAPSULE_BOX = 3, P_CAPSULE_CLIPPED_PLANE = 4,
+       P_BOX_HEIGHTMAP = 5 };
 
 #define MAXB 64
 #define MAXK 128
@@ -101,6 +104,10 @@ typedef struct {
    * in the body-b frame (BaseMesh.faces after its winding fix, geometry.py:146-156) and their
    * normals (BoxMesh, geometry.py:162-189) */
   R tri[12][3][3], tri_normal[12][3];
+  /* box_heightmap: geometry.HeightMap (geometry.py:292-308) -- hm_size x hm_size heights, row-major */
+  const R* hm_height;
+  int32_t hm_size;
+  R hm_cell_size;
 } opair;
 
 typedef struct {
@@ -819,6 +826,47 @@ static void pair_contacts(const osys* s, const opair* p, const oqp* qp, ocontact
       }
       out[c].pen = dot3(d, n);
     }
+#ifndef BXO_COUNT   /* (no env config has a height map: the operation-counting build leaves it out) */
+  } else if (p->kind == P_BOX_HEIGHTMAP) { /* colliders.py:699-742 */
+    const int n = p->hm_size;
+    const R cell = p->hm_cell_size;
+    R qinv[4] = {qp->rot[b][0], -qp->rot[b][1], -qp->rot[b][2], -qp->rot[b][3]}; /* math.inv_rotate */
+    for (int c = 0; c < p->n_contacts; c++) {
+      R ro[3], cr[3], d[3], lp[3];
+      rotate(p->pts[c], qp->rot[a], ro);
+      cross3(qp->ang[a], ro, cr);
+      for (int k = 0; k < 3; k++) {
+        out[c].pos[k] = qp->pos[a][k] + ro[k];
+        out[c].vel[k] = qp->vel[a][k] + cr[k];
+        d[k] = out[c].pos[k] - qp->pos[b][k];
+      }
+      rotate(d, qinv, lp);
+      R u = lp[0] / cell, v = lp[1] / cell;
+      R fu = FLOOR(u), fv = FLOOR(v);
+      int iu = (int)fu, iv = (int)fv;
+      int lower = (u - fu) + (v - fv) < C(1.);
+      R mu = lower ? C(-1.) : C(1.);
+      int tu[3], tv[3];
+      tu[0] = iu + (lower ? 0 : 1); tu[1] = iu + (lower ? 1 : 0); tu[2] = iu + (lower ? 0 : 1);
+      tv[0] = iv + (lower ? 0 : 1); tv[1] = iv + (lower ? 0 : 1); tv[2] = iv + (lower ? 1 : 0);
+      R hh[3];
+      for (int i = 0; i < 3; i++) { /* height[u, -v]: a negative index wraps once, the rest is clamped (jax gather) */
+        int ia = tu[i], ib = -tv[i];
+        if (ia < 0) ia += n;
+        if (ib < 0) ib += n;
+        ia = ia < 0 ? 0 : (ia > n - 1 ? n - 1 : ia);
+        ib = ib < 0 ? 0 : (ib > n - 1 ? n - 1 : ib);
+        hh[i] = p->hm_height[ia * n + ib];
+      }
+      R raw[3] = {mu * (hh[1] - hh[0]), mu * (hh[2] - hh[0]), cell}, nl[3], p0[3], dd[3];
+      R nrm = safe_norm3(s, raw);
+      for (int k = 0; k < 3; k++) nl[k] = raw[k] / nrm;
+      p0[0] = (R)tu[0] * cell; p0[1] = (R)tv[0] * cell; p0[2] = hh[0];
+      for (int k = 0; k < 3; k++) dd[k] = p0[k] - lp[k];
+      out[c].pen = dot3(dd, nl);
+      rotate(nl, qp->rot[b], out[c].normal);
+    }
+#endif
   } else if (p->kind == P_CAPSULE_CLIPPED_PLANE) { /* colliders.py:762-802; plane data in tri[0], tri[1] */
     const R* pl_normal = p->tri[0][0];
     const R* pl_pos = p->tri[0][1];

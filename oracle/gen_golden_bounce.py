@@ -209,6 +209,59 @@ def main(only):
       if mode == 'spring':
         c.dynamics_mode = 'legacy_spring'
       roll(n, c, 0, 90)
+    # HeightMapTest.test_box_stays_on_heightmap (physics_test.py:229-258): a box falls onto the bottom left of a
+    # 3 x 3 height map -- the config AS IS except dt: the reference takes ONE step of dt 2 / 1000 substeps; here
+    # the same 1000 substeps of 0.002 s run as 50 steps of 20
+    n = 'heightmap_%s' % mode
+    if want(n):
+      c = text_format.Parse(pt.HeightMapTest._CONFIG, brax.Config())
+      assert abs(c.dt / c.substeps - 0.002) < 1e-9
+      c.dt, c.substeps = 0.04, 20
+      if mode == 'spring':
+        c.dynamics_mode = 'legacy_spring'
+      roll(n, c, 0, 50)
+    # a 5 x 5 terrain on a tilted frozen body: a spinning box lands on a slope, slides / tumbles across cells
+    # (both triangles of a square, several squares), a second box rests in a hollow
+    n = 'terrain_%s' % mode
+    if want(n):
+      c = text_format.Parse('''
+        dt: 0.02 substeps: 8 friction: 0.7 elasticity: 0.1
+        gravity { z: -9.8 }
+        bodies {
+          name: "crate" mass: 1
+          colliders { box { halfsize { x: 0.3 y: 0.2 z: 0.25 } } }
+          inertia { x: 0.1 y: 0.1 z: 0.1 }
+        }
+        bodies {
+          name: "brick" mass: 2
+          colliders { rotation { z: 30 } box { halfsize { x: 0.25 y: 0.25 z: 0.15 } } }
+          inertia { x: 0.2 y: 0.2 z: 0.2 }
+        }
+        bodies {
+          name: "terrain"
+          frozen: { all: true }
+          colliders {
+            heightMap {
+              size: 8
+              data: [0.0, 0.3, 0.8, 0.4, 0.1,
+                     0.2, 0.1, 0.5, 0.9, 0.3,
+                     0.6, 0.0, 0.2, 0.5, 0.7,
+                     0.9, 0.4, 0.0, 0.1, 0.5,
+                     1.2, 0.8, 0.3, 0.0, 0.2]
+            }
+          }
+        }
+        collide_include { first: "crate" second: "terrain" }
+        collide_include { first: "brick" second: "terrain" }
+        defaults {
+          qps { name: "crate" pos { x: 2.6 y: -2.2 z: 1.8 } vel { x: 0.8 y: -0.5 z: -0.5 } ang { x: 0.6 y: -0.4 z: 0.3 } }
+          qps { name: "brick" pos { x: 5.0 y: -5.2 z: 1.0 } }
+          qps { name: "terrain" pos { x: 0.0 y: 0.0 z: 0.0 } rot { x: 4 y: -3 } }
+        }
+      ''', brax.Config())
+      if mode == 'spring':
+        c.dynamics_mode = 'legacy_spring'
+      roll(n, c, 0, 90)
     n = 'ball_plane_%s_e50' % mode
     if want(n):
       c = text_format.Parse('''

@@ -23,7 +23,7 @@ _JK = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
        'spring_universal': 3, 'spring_spherical': 4}
 _AK = {'torque': 0, 'angle': 1}
 _FK = {'thruster': 0, 'twister': 1}
-_PK = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2, 'capsule_box': 3, 'capsule_clippedplane': 4}
+_PK = {'capsule_plane': 0, 'capsule_capsule': 1, 'box_plane': 2, 'capsule_box': 3, 'capsule_clippedplane': 4, 'box_heightmap': 5}
 
 
 def build(force: bool = False):
@@ -94,7 +94,8 @@ def _structs(R):
                 ('body_b', C.c_int32), ('n_contacts', C.c_int32),
                 ('friction', R), ('elasticity', R), ('radius_a', R),
                 ('radius_b', R), ('pts', (R * 3) * 8), ('tri', ((R * 3) * 3) * 12),
-                ('tri_normal', (R * 3) * 12)]
+                ('tri_normal', (R * 3) * 12),
+                ('hm_height', C.POINTER(R)), ('hm_size', C.c_int32), ('hm_cell_size', R)]
 
   class Sys(C.Structure):
     _fields_ = [('mode', C.c_int32), ('substeps', C.c_int32),
@@ -239,6 +240,11 @@ class Oracle:
           c.tri_normal[f][:] = arr(trn[f])
           for v in range(3):
             c.tri[f][v][:] = arr(tri[f, v])
+      if p['kind'] == 'box_heightmap':
+        hm = np.ascontiguousarray(np.asarray(p['heightmap']['height'], dtype=np.float64).astype(self.dtype))
+        self._hm_keep = getattr(self, '_hm_keep', []) + [hm]
+        c.hm_height = hm.ctypes.data_as(C.POINTER(R))
+        c.hm_size, c.hm_cell_size = int(hm.shape[0]), cast(p['heightmap']['cell_size'])
       if p['kind'] == 'capsule_clippedplane':
         cl = p['clip']
         c.tri[0][0][:], c.tri[0][1][:], c.tri[0][2][:] = arr(cl['normal']), arr(cl['pos']), arr(cl['x'])

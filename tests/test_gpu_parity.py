@@ -84,7 +84,8 @@ ACCUMULATORS = ('contact_vel', 'contact_ang', 'joint_vel', 'joint_ang',
                 'actuator_vel', 'actuator_ang')
 
 
-def check_step(name, ins, act, got, strict_frac=0.90, outlier_frac=OUTLIER_FRAC, contact_point_atol=0.0, oracles=None):
+def check_step(name, ins, act, got, strict_frac=0.90, outlier_frac=OUTLIER_FRAC, contact_point_atol=0.0, oracles=None,
+               min_outliers=0, vel_floor_scale=1.0):
   """Kernel output `got` vs the float32 oracle, with the float64 oracle run on
   the same inputs measuring how ill-conditioned each env's step is in float32.
 
@@ -99,9 +100,10 @@ def check_step(name, ins, act, got, strict_frac=0.90, outlier_frac=OUTLIER_FRAC,
   ref = o32.step(*ins, act)      # (oracles=: a (float32, float64) pair with the same `step`, e.g. FrictionOracle)
   r64 = o64.step(*ins, act)
   b = ref['pos'].shape[0]
-  allowed = int(outlier_frac * b) if b >= 200 else 0
+  allowed = max(int(outlier_frac * b) if b >= 200 else 0, min_outliers)   # (min_outliers: see tests/test_bounce.py)
   stats = {}
-  vel_floor = VEL_ULPS * 6e-8 / _desc(name).dt_sub
+  # (vel_floor_scale: ulp(|pos|) / ulp(1) for scenes that play far from the origin, tests/test_bounce.py)
+  vel_floor = vel_floor_scale * VEL_ULPS * 6e-8 / _desc(name).dt_sub
   name = name if isinstance(name, str) else name.name
   bad_env = np.zeros(b, bool)
   flip_env = np.zeros(b, bool)   # envs whose Info accumulators show a decision taken differently
