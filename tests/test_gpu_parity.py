@@ -692,3 +692,72 @@ def test_three_tiles_per_sm_build_parity():
   a2 = _flat(q2, i2)
   for k in ('pos', 'rot'):
     np.testing.assert_allclose(got[k], a2[k], rtol=1e-4, atol=1e-5, err_msg=k)
+
+
+@pytest.mark.gpu
+def test_shim_returns_reference_types_from_the_cuda_path():
+  """brax_b200.shim (the `step` override installed into a reference `brax.System`) with the CUDA backend: the
+  reference's `QP` / `Info` constructors (stand-ins with the reference's field names here: the reference tree is
+  not on the GPU box; the real ones are exercised on CPU by tests/test_extract_reference.py) receive exactly what
+  `System.step` returns, for numpy (host path) and CUDA inputs."""
+  torch = _torch()
+  import dataclasses
+  import sys
+  import types
+
+  @dataclasses.dataclass
+  class RQP:
+    pos: object
+    rot: object
+    vel: object
+    ang: object
+
+  @dataclasses.dataclass
+  class RP:
+    vel: object
+    ang: object
+
+  @dataclasses.dataclass
+  class RInfo:
+    contact: object
+    joint: object
+    actuator: object
+    contact_pos: object
+    contact_normal: object
+    contact_penetration: object
+
+  saved = {k: sys.modules.get(k) for k in ('brax', 'brax.physics', 'brax.physics.base')}
+  try:
+    base = types.ModuleType('brax.physics.base')
+    base.QP, base.P, base.Info = RQP, RP, RInfo
+    sys.modules.setdefault('brax', types.ModuleType('brax'))
+    sys.modules.setdefault('brax.physics', types.ModuleType('brax.physics'))
+    sys.modules['brax.physics.base'] = base
+    import brax_b200.shim as shim
+    from brax_b200.system import QP
+    s = _system('ant')
+    g = util.load_golden('ant')
+    class FakeSystem:   # what install() needs of a brax.System: an attribute to override
+      pass
+    fs = shim.install(FakeSystem(), backend=s)
+    for b in range(2):
+      qp = RQP(*[g[k][b] for k in util.QP_KEYS])            # unbatched float64 numpy, as the numpy reference hands them
+      q1, i1 = fs.step(qp, g['act'][b])
+      q0, i0 = s.step(QP(*[g[k][b].astype(np.float32) for k in util.QP_KEYS]), g['act'][b].astype(np.float32))
+      assert type(q1) is RQP and type(i1) is RInfo and type(i1.contact) is RP
+      for k in util.QP_KEYS:
+        assert np.array_equal(np.asarray(getattr(q1, k)), np.asarray(getattr(q0, k))), k
+      assert np.array_equal(np.asarray(i1.contact.vel), np.asarray(i0.contact.vel))
+      assert np.array_equal(np.asarray(i1.contact_penetration), np.asarray(i0.contact_penetration))
+    # CUDA arrays in -> CUDA arrays out (what a jax.Array / dlpack producer gets)
+    dq = RQP(*[torch.from_numpy(g[k].astype(np.float32)).cuda() for k in util.QP_KEYS])
+    q2, i2 = fs.step(dq, torch.from_numpy(g['act'].astype(np.float32)).cuda())
+    assert q2.pos.is_cuda and i2.contact_pos.is_cuda
+    q3, _ = s.step(QP(dq.pos, dq.rot, dq.vel, dq.ang), torch.from_numpy(g['act'].astype(np.float32)).cuda())
+    assert torch.equal(q2.pos, q3.pos)
+  finally:
+    for k, v in saved.items():
+      if v is None:
+        sys.modules.pop(k, None)
+      else:
+        sys.modules[k] = v
