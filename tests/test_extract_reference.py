@@ -56,8 +56,12 @@ def test_shim_installed_into_the_reference_env(variant):
   metrics built by the reference's code from the QP / Info the shim returns) gives what the unpatched reference
   gives.  Backend here = the float64 oracle; on a GPU box it is the CUDA path (no reference tree there)."""
   import numpy as np
-  sys.path.insert(0, os.path.join(util.ROOT, 'oracle'))
-  import gen_golden_env as gg
+  path0 = list(sys.path)
+  try:
+    import gen_golden_env as gg      # (oracle/ is on sys.path: refsys above)
+  finally:
+    sys.path[:] = path0              # gen_golden_env puts oracle/ in front of the repo root: later tests that spawn
+                                     # processes (tests/test_shard_gloo.py) must keep resolving `oracle` as the package
   import brax_b200.shim as shim
   from brax_b200.extract import describe
   sysname, modname, clsname, kw = gg.VARIANTS[variant]
