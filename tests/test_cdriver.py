@@ -30,7 +30,7 @@ def _build(tmp_path):
 def _system_blob(desc, env, path):
   """bx_system_desc + its arrays as raw bytes (the layout IS the ABI)."""
   d, keep = desc.to_c(env)
-  bodies, joints, acts, forces, pairs, cenv, creset = keep
+  bodies, joints, acts, forces, pairs, cenv, creset = keep[:7]
   with open(path, 'wb') as f:
     f.write(bytes(d))
     for arr, cnt in ((bodies, d.num_bodies), (joints, d.num_joints), (acts, d.num_actuators),
