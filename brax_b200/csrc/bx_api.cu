@@ -975,6 +975,11 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   p.obs0 = nullptr;
   p.act_out = nullptr;
   p.friction = io->friction;
+  p.joint_offset = io->joint_offset;
+  // per-env joint sockets: [J][32] quads behind the friction values (16-byte aligned: + 16 bytes of slack)
+  const size_t jo_bytes = io->joint_offset ? 16 + static_cast<size_t>(s->h.nj) * BX_ENVS_PER_CTA * 16 : 0;
+  const size_t base_bytes = s->smem_bytes + jo_bytes;   // the tile without the policy's buffers
+  if (base_bytes > static_cast<size_t>(s->smem_optin)) return fail("the per-env joint offsets do not fit in shared memory beside the tile");
   size_t policy_smem = 0;
   bool policy_one_tile = false;   // the policy's buffers leave room for one tile per SM only
   if (io->policy) {
@@ -1006,23 +1011,26 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
     p.act_out = io->act_out;
     // the normalised obs is staged whole when that keeps the tile's occupancy, else in chunks of 128 / 64 /
     // 32 rows (two more barriers per chunk): the largest that still lets two tiles share an SM, or fits at all
-    const bool two_now = 2 * (s->smem_bytes + 1024) <= 233472;
+    const bool two_now = 2 * (base_bytes + 1024) <= 233472;
     const int cand[4] = {q.sizes[0], 128, 64, 32};
     int rows = 0;
     for (int pass = two_now ? 0 : 1; pass < 2 && !rows; pass++)
       for (int i = 0; i < 4 && !rows; i++) {
         if (cand[i] > q.sizes[0]) continue;
-        const size_t total = s->smem_bytes + BX_POLICY_SMEM(cand[i], hmax);
+        const size_t total = base_bytes + BX_POLICY_SMEM(cand[i], hmax);
         if (pass == 0 ? 2 * (total + 1024) <= 233472 : total <= static_cast<size_t>(s->smem_optin)) rows = cand[i];
       }
     if (!rows) return fail("the policy's activation buffers do not fit in shared memory beside the tile");
     p.pol.obs_rows = rows;
     policy_smem = BX_POLICY_SMEM(rows, hmax);
-    policy_one_tile = 2 * (s->smem_bytes + policy_smem + 1024) > 233472;
+    policy_one_tile = 2 * (base_bytes + policy_smem + 1024) > 233472;
   }
   p.h = s->h;
   // (float index behind the two mbarriers; 0 = off)
   p.h.fr_off = io->friction ? (s->h.n_quads * BX_QSTRIDE + s->h.n_fquads) * 4 + s->h.n_ints + 4 : 0;
+  p.h.jo_off = io->joint_offset && s->h.nj > 0
+                   ? s->h.n_quads * BX_QSTRIDE + s->h.n_fquads + ((s->h.n_ints * 4 + 16 + BX_FRICTION_SMEM + 15) >> 4)
+                   : 0;
   p.tab_i = s->d_tab_i;
   p.tab_f = s->d_tab_f;
   p.in[0] = io->pos; p.in[1] = io->rot; p.in[2] = io->vel; p.in[3] = io->ang; p.in[4] = io->act;
@@ -1087,9 +1095,11 @@ static int launch(const bx_system* s, int64_t num_envs, int32_t num_steps,
   // An explicit bx_system_configure / autotune choice is kept.
   // The same holds when the in-kernel policy's buffers leave room for one tile per SM only (humanoid).
   const int warps = (!s->warps_chosen && (tiles <= s->sm_count || policy_one_tile) && s->warps < 16) ? 16 : s->warps;
-  cudaError_t le = launch_variant(s->h.mode, s->jc, s->cc | (s->h.env_kind ? BX_CC_ENV : 0) | pdl,
+  // per-env joint sockets run the all-contact-features build of the system's joint class (BXF_JOINT_OFFSET, bx_kernels.cu)
+  const int jc = s->jc, cc = p.h.jo_off ? (BX_CC_MESH | BX_CC_JO) : s->cc;
+  cudaError_t le = launch_variant(s->h.mode, jc, cc | (s->h.env_kind ? BX_CC_ENV : 0) | pdl,
                                   static_cast<unsigned>(tiles), 32 * warps,
-                                  s->smem_bytes + policy_smem, stream, p, three);
+                                  base_bytes + policy_smem, stream, p, three);
   if (cur_dev != s->device) cudaSetDevice(cur_dev);
   g_launches.fetch_add(1);
   CUDA_OK(le);
@@ -1235,6 +1245,9 @@ static int host_args_ok(const bx_system* s, int64_t B, const bx_step_io* hio) {
   if (B <= 0) return fail("num_envs must be positive");
   if (hio->first_pos) return fail("auto-reset inputs are supported on the device path only (bx_step / bx_rollout)");
   if (hio->observe) return fail("observe is supported on the device path only (bx_step)");
+  if (hio->policy) return fail("the in-kernel policy is supported on the device path only (bx_rollout)");
+  if (hio->friction || hio->joint_offset)
+    return fail("per-env friction / joint offsets are supported on the device path only (bx_step / bx_rollout)");
   if (!hio->pos || !hio->rot || !hio->vel || !hio->ang || !hio->act || !hio->pos_o || !hio->rot_o ||
       !hio->vel_o || !hio->ang_o)
     return fail("QP / act pointers must not be NULL");
@@ -1477,6 +1490,9 @@ extern "C" int bx_step_host_static(const bx_system* s, int64_t B, const bx_step_
   if (B <= 0) return fail("num_envs must be positive");
   if (hio->first_pos) return fail("auto-reset inputs are supported on the device path only (bx_step / bx_rollout)");
   if (hio->observe) return fail("observe is supported on the device path only (bx_step)");
+  if (hio->policy) return fail("the in-kernel policy is supported on the device path only (bx_rollout)");
+  if (hio->friction || hio->joint_offset)
+    return fail("per-env friction / joint offsets are supported on the device path only (bx_step / bx_rollout)");
   if (!hio->pos || !hio->rot || !hio->vel || !hio->ang || !hio->act || !hio->pos_o || !hio->rot_o ||
       !hio->vel_o || !hio->ang_o)
     return fail("QP / act pointers must not be NULL");

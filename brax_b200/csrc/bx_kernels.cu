@@ -48,6 +48,22 @@ static bx_kernel_fn pick(int jc, int cc) {
 
 static bx_kernel_fn pick_any(int mode, int jc, int cc) {
   cc &= ~BX_CC_PDL;
+  if (cc & BX_CC_JO) {
+    // per-env joint sockets: one all-contact-features build per (mode, joint class, env epilogue); the joint class
+    // stays the system's own because the joint record's stride is a compile-time property of it (JQS)
+#ifdef BX_TU_MESH
+#define BX_KJ(MODE, JM, ENV) bx_step_kernel<MODE, (JM) | BXF_CC2 | BXF_COMMON | BXF_JOINT_OFFSET | ENV, BX_TU_MAXT, BX_TU_MINB>
+#define BX_KJ3(MODE, ENV)                                                                              \
+  (jc == BX_JC_REVOLUTE ? BX_KJ(MODE, BXF_JC0, ENV)                                                    \
+                        : (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL ? BX_KJ(MODE, BXF_JC1, ENV) : BX_KJ(MODE, BXF_JC2, ENV)))
+    if (cc & BX_CC_ENV) return mode == BX_MODE_PBD ? BX_KJ3(BX_MODE_PBD, BXF_ENV) : BX_KJ3(BX_MODE_LEGACY_SPRING, BXF_ENV);
+    return mode == BX_MODE_PBD ? BX_KJ3(BX_MODE_PBD, 0) : BX_KJ3(BX_MODE_LEGACY_SPRING, 0);
+#undef BX_KJ3
+#undef BX_KJ
+#else
+    return nullptr;
+#endif
+  }
   if (cc & BX_CC_ENV) {
     cc &= ~BX_CC_ENV;
     return mode == BX_MODE_PBD ? pick<BX_MODE_PBD, BXF_ENV>(jc, cc) : pick<BX_MODE_LEGACY_SPRING, BXF_ENV>(jc, cc);
@@ -80,11 +96,12 @@ cudaError_t BX_CAT(bx_set_smem_, BX_TU_NAME)(int bytes) {
   for (int mode = 0; mode < 2; mode++)
     for (int jc = 0; jc < BX_NUM_JC; jc++)
       for (int cc = 0; cc < BX_NUM_CC; cc++)
-        for (int env = 0; env < 2; env++) {
-          if (pick_any(mode, jc, cc | (env ? BX_CC_ENV : 0)) == nullptr) continue;
-          cudaError_t e = cudaFuncSetAttribute(pick_any(mode, jc, cc | (env ? BX_CC_ENV : 0)),
-                                               cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-          if (e != cudaSuccess) return e;
-        }
+        for (int env = 0; env < 2; env++)
+          for (int jo = 0; jo < 2; jo++) {
+            const int c2 = cc | (env ? BX_CC_ENV : 0) | (jo ? BX_CC_JO : 0);
+            if (pick_any(mode, jc, c2) == nullptr) continue;
+            cudaError_t e = cudaFuncSetAttribute(pick_any(mode, jc, c2), cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+            if (e != cudaSuccess) return e;
+          }
   return cudaSuccess;
 }

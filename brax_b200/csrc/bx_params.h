@@ -49,6 +49,7 @@ struct BxKernelParams {
   const float* obs0;           // [B,O] obs of the state passed in (policy launches)
   float* act_out;              // [T,B,A] actions the policy chose, or NULL
   const float* friction;       // [B] per-env collider friction (h.fr_off != 0), or NULL
+  const float* joint_offset;   // [B,J,3] per-env Joint parent_offset (h.jo_off != 0), or NULL
   int64_t num_envs;
   int32_t num_steps;  // >1: rollout, act is [T,B,A]
   // host path only (bx_step_host on mapped host memory): tile i starts i/grid of
@@ -68,6 +69,7 @@ enum {
   BXF_FUSED_CONTACTS = 2048,  // pbd, one-way colliders, <= 2 rows per body
   BXF_ENV = 4096,             // env epilogue compiled in (systems created with desc.env)
   BXF_CAPSULE_BOX = 8192,     // capsule against a triangulated box (capsule_mesh, colliders.py:822-849)
+  BXF_JOINT_OFFSET = 16384,   // per-env joint sockets (bx_step_io.joint_offset): all-contact-features builds of their own
   BXF_ALL = 2047
 };
 #define BX_CC_ENV 8  // or-ed into the contact class passed to bx_launch_*: env-epilogue build
@@ -75,6 +77,9 @@ enum {
 // launch): the CTAs of this launch may become resident, load the static tables and park at
 // griddepcontrol.wait while the previous kernel of the stream drains
 #define BX_CC_PDL 16
+// or-ed in as well: the launch carries per-env joint sockets -> the build with BXF_JOINT_OFFSET of the system's
+// joint class (contact class MESH = every contact feature; only in the translation units that hold the MESH class)
+#define BX_CC_JO 32
 // Kernel variants are instantiated per (dynamics mode, joint class, contact
 // class, launch bound).  Classes are the feature sets of the reference's envs (BX_CC_MESH: the
 // round-2 capsule-box collider on top of everything):

@@ -577,6 +577,10 @@ BXS void limit_angle(V3 n, V3 n_1, V3 n_2, float lo, float hi, float4 lcs, V3 ii
 // ---- phase J (pbd): Joint.apply for every joint -> per-joint delta slots -------
 // joints.py:79-100, Revolute :270-309, Spherical :332-386.  Slot of joint j:
 // quads JS+4j .. +3 = parent dpos, parent drot, child dpos, child drot.
+// BXF_JOINT_OFFSET builds: the joint sockets come from this env's own table (bx_step_io.joint_offset).  A build of
+// its own (all features, bx_kernels.cu) because every cheaper arrangement taxed all systems -- measured: a per-item
+// test of h.jo_off 1 %, a second inlined instantiation picked per launch 0.9 % (the step loop's code grows by a phase
+// that never runs: instruction cache), the same out of line 0.5-1 % (the call constrains register allocation).
 BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
   typedef Lay<BX_MODE_PBD> L;
   for (int j = c.warp; j < h.nj; j += c.nwarp) {
@@ -590,7 +594,12 @@ BXS void phase_joints_pbd(const Ctx& c, const BxHeader& h) {
     Q4 rp = ldq(c, L::BQ * bp + 2 * c.cur + 1), rc = ldq(c, L::BQ * bc + 2 * c.cur + 1);
     V3 ii_p = f3(bqp[BQ_INV_INERTIA]), ii_c = f3(bqc[BQ_INV_INERTIA]);
     const float4 mp = bqp[BQ_MASS], mc = bqc[BQ_MASS];
-    const float4 j0 = jq[JQ_OFF_P], j1 = jq[JQ_OFF_C];
+    float4 j0 = jq[JQ_OFF_P];
+    const float4 j1 = jq[JQ_OFF_C];
+    if constexpr ((BX_FEAT & BXF_JOINT_OFFSET) != 0) {   // this env's own socket (bx_step_io.joint_offset)
+      const float4 o = bx_smem[h.jo_off + j * BX_ENVS_PER_CTA + (threadIdx.x & 31)];
+      j0.x = o.x; j0.y = o.y; j0.z = o.z;
+    }
     const float4 ap0 = jq[JQ_AXIS_P];
     const M3 Rp = rotmat(rp), Rc = rotmat(rc);
     V3 wp = pos_p + mrot(Rp, f3(j0));
@@ -1269,7 +1278,12 @@ BXS void phase_joints_spring(const Ctx& c, const BxHeader& h) {
     Q4 rp = ldq(c, rp0 + 1), rc = ldq(c, rc0 + 1);
     V3 ang_p = ldv(c, rp0 + L::ANG), ang_c = ldv(c, rc0 + L::ANG);
     V3 ii_p = f3(bqp[BQ_INV_INERTIA]), ii_c = f3(bqc[BQ_INV_INERTIA]);
-    const float4 j0 = jq[JQ_OFF_P], j1 = jq[JQ_OFF_C];
+    float4 j0 = jq[JQ_OFF_P];
+    const float4 j1 = jq[JQ_OFF_C];
+    if constexpr ((BX_FEAT & BXF_JOINT_OFFSET) != 0) {   // this env's own socket (bx_step_io.joint_offset)
+      const float4 o = bx_smem[h.jo_off + j * BX_ENVS_PER_CTA + (threadIdx.x & 31)];
+      j0.x = o.x; j0.y = o.y; j0.z = o.z;
+    }
     const float stiffness = jq[JQ_AXIS_P + 1].w, spring_damp = jq[JQ_AXIS_P + 2].w;
     const float ang_damp = j0.w, ls = jq[JQ_AXIS_C].w;
     // QP.to_world base.py:112-125
@@ -1969,6 +1983,18 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
     const float f = l < nenv ? p.friction[env0 + l] : 1.f;
     smf[h.fr_off + l] = f * f;
   }
+  if ((BX_FEAT & BXF_JOINT_OFFSET) != 0 && h.jo_off) {
+    // per-env joint sockets: Joint.parent_offset of env `lane` for every joint, read by the joint phases
+    for (int i = threadIdx.x; i < h.nj * BX_ENVS_PER_CTA; i += blockDim.x) {
+      const int j = i / BX_ENVS_PER_CTA, l = i - j * BX_ENVS_PER_CTA;
+      float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (l < nenv) {
+        const float* src = p.joint_offset + ((env0 + l) * h.nj + j) * 3;
+        o = make_float4(src[0], src[1], src[2], 0.f);
+      }
+      bx_smem[h.jo_off + i] = o;
+    }
+  }
   if (!full) {
     // partial tile: give the idle env slots a benign state (identity rotations)
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -2042,7 +2068,8 @@ static __device__ __forceinline__ void run(const BxKernelParams& p) {
       // actions of this step from the policy: obs of the previous step (obs0 for the first; first_obs for
       // envs the auto-reset restarted at the end of the previous step)
       // (the policy's buffers start at the 16-byte boundary behind the mbarriers)
-      float* pbuf = reinterpret_cast<float*>(bx_smem + h.n_quads * QS + h.n_fquads + ((h.n_ints * 4 + 16 + BX_FRICTION_SMEM + 15) >> 4));
+      float* pbuf = reinterpret_cast<float*>(bx_smem + h.n_quads * QS + h.n_fquads + ((h.n_ints * 4 + 16 + BX_FRICTION_SMEM + 15) >> 4) +
+                                             (h.jo_off ? h.nj * BX_ENVS_PER_CTA : 0));
       const bool restarted = step > 0 && p.first[0] != nullptr && (threadIdx.x & 31) < nenv &&
                              sq[(h.q_env + EQ_S0) * QS + (threadIdx.x & 31)].y > 0.f;
       policy_forward<MODE>(c, h, p, pbuf, smf, step, env0, nenv, restarted);

@@ -141,6 +141,9 @@ struct BxHeader {
   // per-env collider friction (bx_step_io.friction): float index in shared memory of the tile's 32
   // friction[e]^2 values (behind the mbarriers), set per launch; 0 = the pair tables' friction
   int32_t fr_off;
+  // per-env joint sockets (bx_step_io.joint_offset): quad index in shared memory of the tile's [J][32] parent
+  // offsets (behind the friction values, in front of the policy's buffers), set per launch; 0 = the joint tables'
+  int32_t jo_off;
   // box_heightmap pairs: the height grids of the system, concatenated (device memory; NULL without one)
   const float* hm;
   BxSeg seg_in[BX_SEG_IN];

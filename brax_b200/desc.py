@@ -20,7 +20,7 @@ from typing import Any, Dict, List
 
 import numpy as np
 
-ABI_VERSION = 12
+ABI_VERSION = 13
 
 MODE = {'pbd': 0, 'legacy_spring': 1}
 JOINT_KIND = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,
@@ -113,7 +113,7 @@ class CStepIO(C.Structure):
       'actuator_ang', 'contact_pos', 'contact_normal', 'contact_penetration',
       'joint_angle', 'joint_velocity', 'obs', 'reward', 'done', 'metrics', 'env_rand',
       'first_pos', 'first_rot', 'first_vel', 'first_ang', 'first_obs', 'done_in', 'steps_in',
-      'steps_out', 'truncation', 'policy', 'obs0', 'act_out', 'friction')] + [('episode_length', C.c_float), ('observe', C.c_int32), ('action_repeat', C.c_int32)]
+      'steps_out', 'truncation', 'policy', 'obs0', 'act_out', 'friction', 'joint_offset')] + [('episode_length', C.c_float), ('observe', C.c_int32), ('action_repeat', C.c_int32)]
 
 
 POLICY_MAX_LAYERS = 8

@@ -181,6 +181,8 @@ class Env:
     self.keep_info = False
     # per-env collider friction [B] (CUDA tensor) or None: see `randomize_friction`
     self.friction = None
+    # per-env joint sockets [B,J,3] (CUDA tensor) or None: see `randomize_joints`
+    self.joint_offset = None
     self.sys = _system.load_system(system_name, device, env)
     self.observation_size = env.obs_size(self.sys.desc)
     self.action_size = self.sys.act_size
@@ -272,6 +274,17 @@ class Env:
     self.friction = friction
     return self
 
+  def randomize_joints(self, joint_offset):
+    """Domain randomisation over joint sockets, as `DomainRandomizationWrapper(env_fn, *joint_randomizer(env,
+    offsets, keys))` (experimental/tracing/randomizers.py:54-97): env e is stepped with `Joint.parent_offset` =
+    joint_offset[e, j] for joint j -- `self.sys.joint_offsets()` (the config's values) plus your per-env deltas on
+    the joints you select.  float32 CUDA tensor [B,J,3], or None to return to the config.  Applies to `step` and the
+    wrappers around this env; `reset` builds its pose from the config's sockets (the solver then pulls the joints
+    onto the randomised ones within the first steps), not from the randomised ones as the reference's vmapped
+    `default_qp` does."""
+    self.joint_offset = joint_offset
+    return self
+
   def host_io(self, batch: int):
     """Page-locked host tensors for `step(..., host_out=)`: 'action' [B,A] in, 'obs' [B,O],
     'reward' [B], 'done' [B], 'metrics' [B,M] out."""
@@ -283,7 +296,7 @@ class Env:
   def _launch(self, state: State, action, rand=None, auto_reset=None, host_out=None) -> State:
     torch_path = _system._is_torch(state.qp.pos)
     qp, info, eo = self.sys.step(state.qp, action, env=True, env_rand=rand, auto_reset=auto_reset,
-                                 info=self.keep_info or not torch_path, friction=self.friction,
+                                 info=self.keep_info or not torch_path, friction=self.friction, joint_offset=self.joint_offset,
                                  env_out=None if host_out is None else {k: host_out[k] for k in ('obs', 'reward', 'done', 'metrics')})
     names = self.env.metric_names()
     metrics = dict(state.metrics)
@@ -436,7 +449,7 @@ class EpisodeAutoReset:
     if rand is None and isinstance(self.env, _TargetEnv):
       rand = self.env._uniform(state.qp.pos, (int(actions.shape[0]) * self.action_repeat,) + tuple(state.qp.pos.shape[:-2]))
     qp, info, eo = self.sys.rollout(state.qp, actions, env=True, env_rand=rand, auto_reset=ar, info=False,
-                                    friction=self.env.friction)
+                                    friction=self.env.friction, joint_offset=self.env.joint_offset)
     names = self.env.env.metric_names()
     metrics = {k: eo['metrics'][-1, ..., i] for i, k in enumerate(names)}
     last = State(qp, eo['obs'][-1], eo['reward'][-1], eo['done'][-1], metrics,

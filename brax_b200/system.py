@@ -377,6 +377,11 @@ class System:
       arrs = [torch.from_numpy(a).to(device) for a in arrs]
     return QP(*arrs)
 
+  def joint_offsets(self):
+    """`Joint.parent_offset` of every joint as the descriptor holds it, float32 [J,3]: the base to which a joint
+    randomiser adds its per-env deltas (`joint_offset=` of `step` / `rollout`)."""
+    return np.asarray([j['off_p'] for j in self.desc.joints], np.float32).reshape(-1, 3)
+
   def observe(self, qp: QP, friction=None):
     """obs [B,O] of a state as `Env.reset` builds it: `_get_obs(qp, info)` with a zero Info and a
     zero action (envs/ant.py:203-204, humanoid.py:230-231, fetch.py:41-42, grasp.py:60-61) -- the
@@ -434,7 +439,8 @@ class System:
 
   # ---- the step ---------------------------------------------------------------
   def step(self, qp: QP, act, out: 'HostBuffers' = None, angle_vel: bool = False, env: bool = False,
-           env_rand=None, auto_reset: 'AutoReset' = None, info: bool = True, env_out=None, friction=None):
+           env_rand=None, auto_reset: 'AutoReset' = None, info: bool = True, env_out=None, friction=None,
+           joint_offset=None):
     """`System.step(qp, act) -> (qp, info)` (system.py:244-247).
 
     out: optional `HostBuffers` (host path only): results are written into its
@@ -458,7 +464,9 @@ class System:
     launch, no separate copies; synchronise the stream before reading the host tensors.
     friction: (torch path) float32 CUDA tensor [B]: per-env collider material friction -- the domain
     randomisation of experimental/tracing/randomizers.py:26-51 (every collider of env e has
-    material.friction = friction[e]; pair friction = friction[e]^2)."""
+    material.friction = friction[e]; pair friction = friction[e]^2).
+    joint_offset: (torch path) float32 CUDA tensor [B,J,3]: per-env `Joint.parent_offset` of every joint -- the
+    joint randomiser of experimental/tracing/randomizers.py:54-97 (`joint_offsets()` + your per-env deltas)."""
     if env and self.env is None:
       raise ValueError('this System was built without an EnvDesc')
     if auto_reset is not None and not env:
@@ -472,9 +480,10 @@ class System:
       if isinstance(act, np.ndarray):
         raise TypeError('qp is on the GPU, act is a numpy array: pass a CUDA (or page-locked) tensor')
     if _is_torch(qp.pos):
-      return self._step_torch(qp, act, 1, angle_vel, env, env_rand, auto_reset, info, env_out=env_out, friction=friction)
-    if env_out is not None or friction is not None:
-      raise ValueError('env_out / friction belong to the torch path')
+      return self._step_torch(qp, act, 1, angle_vel, env, env_rand, auto_reset, info, env_out=env_out, friction=friction,
+                              joint_offset=joint_offset)
+    if env_out is not None or friction is not None or joint_offset is not None:
+      raise ValueError('env_out / friction / joint_offset belong to the torch path')
     if auto_reset is not None:
       raise ValueError('auto_reset is supported with torch CUDA tensors only')
     return self._step_numpy(qp, act, out, angle_vel, env, env_rand)
@@ -506,7 +515,8 @@ class System:
     return int(h2d.value), int(d2h.value)
 
   def rollout(self, qp: QP, acts, env: bool = False, env_rand=None, auto_reset: 'AutoReset' = None,
-              info: bool = True, policy: 'Policy' = None, obs0=None, noise=None, steps: int = None, friction=None):
+              info: bool = True, policy: 'Policy' = None, obs0=None, noise=None, steps: int = None, friction=None,
+              joint_offset=None):
     """T steps in ONE launch; acts is [T, B, A] (torch CUDA).  Returns the final
     QP and the Info of the last step (lax.scan of System.step over actions); with
     env=True also the env epilogue of EVERY step: obs [T,B,O], reward / done [T,B],
@@ -523,8 +533,9 @@ class System:
       if not env or obs0 is None or steps is None:
         raise ValueError('a policy rollout needs env=True, obs0 and steps')
       return self._step_torch(qp, None, int(steps), False, True, env_rand, auto_reset, info,
-                              policy=(policy, obs0, noise), friction=friction)
-    return self._step_torch(qp, acts, int(acts.shape[0]), False, env, env_rand, auto_reset, info, friction=friction)
+                              policy=(policy, obs0, noise), friction=friction, joint_offset=joint_offset)
+    return self._step_torch(qp, acts, int(acts.shape[0]), False, env, env_rand, auto_reset, info, friction=friction,
+                            joint_offset=joint_offset)
 
   def _shapes(self, pos_shape):
     n = self.num_bodies
@@ -585,7 +596,8 @@ class System:
     io.action_repeat = 0
 
   def _step_torch(self, qp: QP, act, steps: int, av: bool = False, env: bool = False, env_rand=None,
-                  auto_reset=None, info: bool = True, observe: bool = False, env_out=None, policy=None, friction=None):
+                  auto_reset=None, info: bool = True, observe: bool = False, env_out=None, policy=None, friction=None,
+                  joint_offset=None):
     """env_rand: (fetch / grasp) uniforms of the target teleport, [B,3] or [T,B,3].
 
     Host cost per call is what bounds a plain Python stepping loop (the kernel takes ~57 us for
@@ -677,6 +689,13 @@ class System:
       io.friction = friction.data_ptr()
     elif io.friction:
       io.friction = None
+    if joint_offset is not None:
+      if not (_is_torch(joint_offset) and joint_offset.is_cuda):
+        raise ValueError('joint_offset must be a CUDA tensor [B,J,3]')
+      joint_offset = prep(joint_offset, b * len(self.desc.joints) * 3)
+      io.joint_offset = joint_offset.data_ptr()
+    elif io.joint_offset:
+      io.joint_offset = None
     if ext:
       for nm, cnt in (('obs', b * self.obs_size), ('reward', b), ('done', b), ('metrics', b * self.num_metrics)):
         t = env_out[nm]

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BX_ABI_VERSION 12
+#define BX_ABI_VERSION 13
 
 /* dynamics_mode (base.py:179-201) */
 #define BX_MODE_PBD 0
@@ -359,6 +359,11 @@ typedef struct bx_step_io {
    * friction[e] * friction[e] (colliders.py:277,315,392,459,596).  bx_step / bx_rollout / bx_state_rollout;
    * the host-buffer entry points (bx_step_host*) refuse it. */
   const float* friction;
+  /* Optional per-env joint sockets [B,J,3] (device; NULL = the descriptor's): Joint.parent_offset of every joint
+   * (bx_joint.off_p) for env e -- the joint domain randomisation of experimental/tracing/randomizers.py:54-97
+   * (joint_randomizer: parent_offset + offsets[e] on the selected joints, the config's value on the others).
+   * Device path only, like friction. */
+  const float* joint_offset;
   float episode_length;   /* EpisodeWrapper.episode_length; 0 = no episode limit */
   /* Non-zero (systems with desc.env, bx_step only): no physics -- the launch evaluates
    * info = System.info(qp) of the state passed in (system.py:327-340 / :378-390: the contact rows and

@@ -101,5 +101,88 @@ def main(only):
         name, time.time() - t0, len(FRICTION), T, FRICTION[0], FRICTION[-1], WARM + T, spread, 100 * active))
 
 
+JOINT_DELTAS = ((0.0, 0.0, 0.0), (0.02, -0.01, 0.015), (-0.03, 0.02, 0.0), (0.01, 0.03, -0.02))
+JOINT_SYSTEMS = {'ant': ('ant', '_SYSTEM_CONFIG'), 'ant_spring': ('ant', '_SYSTEM_CONFIG_SPRING'),
+                 'humanoid_spring': ('humanoid', '_SYSTEM_CONFIG_SPRING')}
+
+
+def joint_tree(config, delta, randomized):
+  """randomizers.py:73-93 with a scalar offset instead of the vmapped vector: parent_offset + delta on the
+  selected joints, the config's own value on the others."""
+  tree = {'joints': []}
+  for i, j in enumerate(config.joints):
+    d = delta if i in randomized else (0.0, 0.0, 0.0)
+    tree['joints'].append({'parent_offset': {'x': d[0] + j.parent_offset.x, 'y': d[1] + j.parent_offset.y,
+                                             'z': d[2] + j.parent_offset.z}})
+  return tree
+
+
+def main_joints(only):
+  """tests/golden/friction/<sys>_joints.npz: the joint randomiser (randomizers.py:54-97) through the reference's
+  own TracedConfig hook, one System per offset; every other joint is randomised.  Each variant starts from ITS OWN
+  `default_qp()` (the reference builds the pose from the randomised sockets), given a sliding velocity."""
+  brax = refsys.setup()
+  from brax.experimental.tracing.customize import TracedConfig
+  from brax_b200.extract import describe
+  os.makedirs(OUT, exist_ok=True)
+  for name, (env, var) in JOINT_SYSTEMS.items():
+    if only and name not in only:
+      continue
+    t0 = time.time()
+    config = refsys.parse(refsys.env_config_text(env, var))
+    rng = np.random.default_rng(13)
+    randomized = set(range(0, len(config.joints), 2))
+    acts = rng.uniform(-1, 1, (WARM + T, 64))
+    keys = ('pos', 'rot', 'vel', 'ang', 'act') + tuple('out_' + k for k in (
+        'pos', 'rot', 'vel', 'ang', 'contact_vel', 'contact_ang', 'joint_vel', 'joint_ang', 'actuator_vel', 'actuator_ang',
+        'contact_pos', 'contact_normal', 'contact_penetration'))
+    rec = {k: [] for k in keys}
+    offs = []
+    for delta in JOINT_DELTAS:
+      s = brax.System(config, post_process_fn=lambda c, d=delta: TracedConfig(c, joint_tree(c, d, randomized)))
+      desc = describe(s, name)
+      offs.append([j['off_p'] for j in desc.joints])
+      a = desc.act_size
+      qp = s.default_qp()
+      free = np.asarray([b['pos_mask'][0] for b in desc.bodies], np.float64)[:, None]
+      qp = qp.__class__(pos=qp.pos, rot=qp.rot, vel=np.asarray(qp.vel) + free * np.array([1.0, 0.3, 0.0]), ang=qp.ang)
+      per = {k: [] for k in keys}
+      for t in range(WARM + T):
+        act = acts[t, :a]
+        if t >= WARM:
+          for k in ('pos', 'rot', 'vel', 'ang'):
+            per[k].append(np.asarray(getattr(qp, k), np.float64))
+          per['act'].append(act.copy())
+        qp, info = s.step(qp, act)
+        if t >= WARM:
+          for k in ('pos', 'rot', 'vel', 'ang'):
+            per['out_' + k].append(np.asarray(getattr(qp, k), np.float64))
+          for k, v in _info_arrays(info).items():
+            per['out_' + k].append(v)
+      for k in keys:
+        rec[k].append(np.stack(per[k]))
+    out = {k: np.stack(v) for k, v in rec.items()}      # [V, T, ...]
+    out['joint_offset'] = np.asarray(offs)              # [V, J, 3] as extracted from the built Systems
+    base = out['joint_offset'][0]
+    # the descriptor lists the joints in the reference's joint-group order (by type), the config in file order:
+    # match them by their (parent, child) bodies
+    bidx = {b.name: i for i, b in enumerate(config.bodies)}
+    cfg_of = {(bidx[j.parent], bidx[j.child]): i for i, j in enumerate(config.joints)}
+    rand_desc = {k for k, j in enumerate(desc.joints) if cfg_of[(j['body_p'], j['body_c'])] in randomized}
+    out['randomized'] = np.asarray(sorted(rand_desc))
+    for v, d in enumerate(JOINT_DELTAS):
+      for j in range(base.shape[0]):
+        want = base[j] + (np.asarray(d) if j in rand_desc else 0.0)
+        assert np.allclose(out["joint_offset"][v, j], want, atol=1e-7), (v, j, out["joint_offset"][v, j], want)
+    np.savez_compressed(os.path.join(OUT, name + '_joints.npz'), **out)
+    print('%-16s %.0fs  variants=%d T=%d  %d of %d joints randomised  |pos(v0) - pos(v1)| = %.3e' % (
+        name, time.time() - t0, len(JOINT_DELTAS), T, len(randomized), base.shape[0],
+        np.abs(out['out_pos'][0, -1] - out['out_pos'][1, -1]).max()))
+
+
 if __name__ == '__main__':
-  main(sys.argv[1:])
+  args = [a for a in sys.argv[1:] if a != '--joints']
+  if '--joints' in sys.argv[1:]:
+    main_joints(args)
+  else:
+    main(args)

@@ -129,30 +129,54 @@ def with_collider_friction(desc, friction: float):
   return d
 
 
+def with_joint_offsets(desc, off_p):
+  """A copy of `desc` whose joints have parent_offset (`off_p`) = off_p[j] -- what experimental/tracing/
+  randomizers.py:54-97 (joint_randomizer) substitutes per env through TracedConfig."""
+  import copy
+  d = copy.copy(desc)
+  off_p = np.asarray(off_p, np.float64).reshape(len(desc.joints), 3)
+  d.joints = [dict(j, off_p=[float(x) for x in off_p[i]]) for i, j in enumerate(desc.joints)]
+  return d
+
+
 class FrictionOracle:
   """`Oracle.step` with per-env collider friction [B] (domain randomisation): env e is stepped by the
   oracle of `with_collider_friction(desc, friction[e])`, one Oracle per distinct value."""
 
-  def __init__(self, desc, friction, dtype=np.float32):
+  def __init__(self, desc, friction, dtype=np.float32, joint_offset=None):
+    """friction: [B] or None (the descriptor's); joint_offset: [B,J,3] or None -- per-env `Joint.parent_offset`."""
     self.desc, self.dtype = desc, np.dtype(dtype)
-    self.friction = np.asarray(friction).reshape(-1)   # (the caller's precision: float64 values stay exact)
+    self.joint_offset = None if joint_offset is None else np.asarray(joint_offset).reshape(-1, len(desc.joints) * 3)
+    b = len(friction) if friction is not None else self.joint_offset.shape[0]
+    self.friction = None if friction is None else np.asarray(friction).reshape(-1)   # (the caller's precision: float64 values stay exact)
+    # one key per env: (friction, offsets)
+    self._keys = [((None if self.friction is None else float(self.friction[e])),
+                   (None if self.joint_offset is None else tuple(float(x) for x in self.joint_offset[e]))) for e in range(b)]
     self._oracles = {}
 
   def step(self, pos, rot, vel, ang, act):
     ins = [np.asarray(x) for x in (pos, rot, vel, ang, act)]
     b = ins[0].shape[0]
-    assert self.friction.shape[0] == b
+    assert len(self._keys) == b
+    groups = {}
+    for e, k in enumerate(self._keys):
+      groups.setdefault(k, []).append(e)
     out = None
-    for f in np.unique(self.friction):
-      idx = np.nonzero(self.friction == f)[0]
-      o = self._oracles.get(float(f))
+    for k, idx in groups.items():
+      idx = np.asarray(idx)
+      o = self._oracles.get(k)
       if o is None:
-        o = self._oracles[float(f)] = Oracle(with_collider_friction(self.desc, float(f)), self.dtype)
+        d = self.desc
+        if k[0] is not None:
+          d = with_collider_friction(d, k[0])
+        if k[1] is not None:
+          d = with_joint_offsets(d, k[1])
+        o = self._oracles[k] = Oracle(d, self.dtype)
       part = o.step(*[x[idx] for x in ins])
       if out is None:
-        out = {k: np.empty((b,) + v.shape[1:], v.dtype) for k, v in part.items()}
-      for k, v in part.items():
-        out[k][idx] = v
+        out = {kk: np.empty((b,) + v.shape[1:], v.dtype) for kk, v in part.items()}
+      for kk, v in part.items():
+        out[kk][idx] = v
     return out
 
 

@@ -163,3 +163,107 @@ def test_gpu_env_randomize_friction():
   assert torch.equal(w1.qp.pos, rnd.qp.pos)
   env.randomize_friction(None)
   assert torch.equal(env.step(st, act).obs, plain.obs)
+
+
+# ------------------------------------------------------------------ per-env joint sockets (randomizers.py:54-97)
+JOINT_SYSTEMS = ('ant', 'ant_spring', 'humanoid_spring')
+
+
+def _golden_joints(name):
+  g = np.load(os.path.join(GOLD, name + '_joints.npz'))
+  v, t = g['pos'].shape[:2]
+  flat = {k: g[k].reshape((v * t,) + g[k].shape[2:]) for k in g.files if k not in ('joint_offset', 'randomized')}
+  off = np.repeat(g['joint_offset'], t, axis=0)          # [V*T, J, 3]
+  return g, flat, off
+
+
+@pytest.mark.parametrize('name', JOINT_SYSTEMS)
+def test_oracle_f64_reproduces_reference_steps_under_substituted_joint_offsets(name):
+  from oracle.oracle import FrictionOracle
+  g, flat, off = _golden_joints(name)
+  d = util.load_desc(name)
+  # variant 0 is the config itself; the others moved exactly the randomised joints
+  np.testing.assert_allclose(g['joint_offset'][0], [j['off_p'] for j in d.joints], atol=1e-7)
+  moved = np.abs(g['joint_offset'][1] - g['joint_offset'][0]).max(axis=1) > 1e-4
+  assert sorted(np.nonzero(moved)[0]) == sorted(g['randomized'])
+  o = FrictionOracle(d, None, np.float64, joint_offset=off)
+  out = o.step(*[flat[k] for k in util.QP_KEYS], flat['act'])
+  for k in util.QP_KEYS + util.INFO_KEYS:
+    if out[k].size:
+      np.testing.assert_allclose(out[k], flat['out_' + k], rtol=0, atol=1e-9 * max(1.0, np.abs(flat['out_' + k]).max()), err_msg=k)
+  assert np.abs(g['out_pos'][0, -1] - g['out_pos'][1, -1]).max() > 1e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', JOINT_SYSTEMS)
+def test_gpu_step_with_per_env_joint_offsets_on_reference_states(name):
+  torch = _torch()
+  from oracle.oracle import FrictionOracle
+  from brax_b200.system import QP
+  from tests.test_gpu_parity import _flat, _system, check_step
+  g, flat, off = _golden_joints(name)
+  s = _system(name)
+  assert np.allclose(s.joint_offsets(), g['joint_offset'][0], atol=1e-7)
+  ins = [flat[k].astype(np.float32) for k in util.QP_KEYS]
+  act = flat['act'].astype(np.float32)
+  qp = QP(*[torch.from_numpy(x).cuda() for x in ins])
+  off32 = off.astype(np.float32)
+  got = _flat(*s.step(qp, torch.from_numpy(act).cuda(), joint_offset=torch.from_numpy(off32).cuda()))
+  d = util.load_desc(name)
+  check_step(name, ins, act, got, oracles=(FrictionOracle(d, None, np.float32, joint_offset=off32),
+                                           FrictionOracle(d, None, np.float64, joint_offset=off32)))
+  # the lanes with the config's own sockets are bitwise the plain step; the others are not
+  plain = _flat(*s.step(qp, torch.from_numpy(act).cuda()))
+  t = g['pos'].shape[1]
+  assert np.array_equal(plain['pos'][:t], got['pos'][:t]) and np.array_equal(plain['vel'][:t], got['vel'][:t])
+  assert np.abs(plain['pos'][t:] - got['pos'][t:]).max() > 1e-4
+
+
+@pytest.mark.gpu
+def test_gpu_joint_offsets_with_friction_policy_and_rollout():
+  """Both per-env tables and the in-kernel policy share the launch's extra shared memory: T steps in one launch ==
+  T single launches; harvested ragged batch against the oracle per env."""
+  torch = _torch()
+  from oracle.oracle import FrictionOracle
+  from brax_b200 import envs
+  from brax_b200.system import Policy
+  from tests.test_gpu_parity import _flat, _harvest, _system, check_step
+  s = _system('humanoid')
+  d = util.load_desc('humanoid')
+  b = 333
+  qp, rng = _harvest(s, b, 20, 23)
+  base = s.joint_offsets()
+  deltas = np.float32([[0, 0, 0], [0.02, -0.01, 0.01], [-0.02, 0.015, 0.0]])
+  off = (base[None] + deltas[rng.integers(0, 3, b)][:, None, :] * (np.arange(base.shape[0]) % 2 == 0)[None, :, None]).astype(np.float32)
+  fr = rng.choice(np.float32([0.5, 1.0, 1.5]), b).astype(np.float32)
+  act = rng.uniform(-1, 1, (b, s.act_size)).astype(np.float32)
+  got = _flat(*s.step(qp, torch.from_numpy(act).cuda(), friction=torch.from_numpy(fr).cuda(),
+                      joint_offset=torch.from_numpy(off).cuda()))
+  ins = [getattr(qp, k).cpu().numpy() for k in util.QP_KEYS]
+  check_step('humanoid', ins, act, got, oracles=(FrictionOracle(d, fr, np.float32, joint_offset=off),
+                                                 FrictionOracle(d, fr, np.float64, joint_offset=off)))
+  # rollout == chained steps, bitwise
+  acts = torch.from_numpy(rng.uniform(-1, 1, (4, b, s.act_size)).astype(np.float32)).cuda()
+  kw = dict(friction=torch.from_numpy(fr).cuda(), joint_offset=torch.from_numpy(off).cuda())
+  qr, _ = s.rollout(qp, acts, **kw)
+  qc = qp
+  for t in range(4):
+    qc, _ = s.step(qc, acts[t], **kw)
+  assert torch.equal(qr.pos, qc.pos) and torch.equal(qr.ang, qc.ang)
+  # the env + in-kernel policy on top (ant: the tile keeps two per SM): the policy rollout == the acting loop
+  env = envs.create('ant')
+  no, na = env.observation_size, env.action_size
+  qpa, rng = _harvest(env.sys, 200, 5, 29)
+  offa = torch.from_numpy((env.sys.joint_offsets()[None] + rng.uniform(-0.02, 0.02, (200, 1, 3)).astype(np.float32))).cuda().contiguous()
+  env.randomize_joints(offa)
+  g = torch.Generator(device='cuda'); g.manual_seed(1)
+  params = [((torch.rand(no, 16, generator=g, device='cuda') - .5) * .3, torch.zeros(16, device='cuda')),
+            ((torch.rand(16, 2 * na, generator=g, device='cuda') - .5) * .3, torch.zeros(2 * na, device='cuda'))]
+  obs0 = env.sys.observe(qpa)
+  q2, _, eo = env.sys.rollout(qpa, None, env=True, policy=Policy(params, activation='tanh'), obs0=obs0, steps=3, info=False,
+                              joint_offset=offa)
+  st = envs.State(qpa, obs0, None, None)
+  for t in range(3):
+    st = env.step(st, eo['action'][t].contiguous())
+    assert torch.equal(st.obs, eo['obs'][t]), t
+  assert torch.equal(st.qp.pos, q2.pos)
