@@ -186,6 +186,8 @@ static float* const* io_outs(const bx_step_io* io) { return &io->pos_o; }
 static float** io_outs(bx_step_io* io) { return &io->pos_o; }
 
 // Flattens the description into the tables of bx_tables.h.
+static int joint_class(const bx_system_desc* d);
+
 static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<int32_t>* ti_out,
                            std::vector<float>* tf_out, int rows_per_item) {
   BxHeader& h = *hh;
@@ -273,9 +275,8 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
     quad(s.rot_mask[0], s.rot_mask[1], s.rot_mask[2], 0.f);
   }
   h.fo_joint = nquads();
-  bool rev_only = true;   // the revolute-only kernel variants read the 10-quad record (bx_step_kernel.cuh JQS)
-  for (int i = 0; i < nj; i++)
-    rev_only = rev_only && (d->joints[i].kind == BX_JOINT_REVOLUTE || d->joints[i].kind == BX_JOINT_SPRING_REVOLUTE);
+  // the revolute class's kernel variants read the 10-quad record (bx_step_kernel.cuh JQS)
+  const bool rev_only = joint_class(d) == BX_JC_REVOLUTE;
   for (int i = 0; i < nj; i++) {
     const bx_joint& s = d->joints[i];
     quad(s.off_p[0], s.off_p[1], s.off_p[2], s.angular_damping);
@@ -712,6 +713,22 @@ static void build_tables_g(const bx_system_desc* d, BxHeader* hh, std::vector<in
 
 static size_t tile_bytes(const BxHeader& h);
 
+// Joint (and actuator) class of a system: which kernel variants run it (bx_params.h).
+static int joint_class(const bx_system_desc* d) {
+  bool rev = false, other = false, sph_only = d->num_joints > 0, angle = false, torque = false;
+  for (int i = 0; i < d->num_joints; i++) {
+    const int k = d->joints[i].kind;
+    if (k == BX_JOINT_REVOLUTE || k == BX_JOINT_SPRING_REVOLUTE) rev = true; else other = true;
+    if (k != BX_JOINT_SPHERICAL) sph_only = false;
+  }
+  for (int i = 0; i < d->num_actuators; i++)
+    if (d->actuators[i].kind == BX_ACT_ANGLE) angle = true; else torque = true;
+  if (d->num_forces > 0 || (angle && torque)) return BX_JC_ALL;
+  if (!other) return angle ? BX_JC_ALL : BX_JC_REVOLUTE;
+  if (sph_only && !rev) return angle ? BX_JC_SPHERICAL_ANGLE : BX_JC_SPHERICAL;
+  return BX_JC_ALL;
+}
+
 // Rows per contact item: 1 (every row its own slot-list entry: most parallelism,
 // the reference's exact summation order) unless pairing the rows is what lets two
 // tiles share an SM (fetch: 8 box corners per collider).
@@ -800,13 +817,7 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
   std::vector<float> tf;
   build_tables(desc, &s->h, &ti, &tf);
   {
-    bool rev = false, other = false, sph_only = desc->num_joints > 0;
-    for (int i = 0; i < desc->num_joints; i++) {
-      const int k = desc->joints[i].kind;
-      if (k == BX_JOINT_REVOLUTE || k == BX_JOINT_SPRING_REVOLUTE) rev = true; else other = true;
-      if (k != BX_JOINT_SPHERICAL) sph_only = false;
-    }
-    s->jc = !other ? BX_JC_REVOLUTE : ((sph_only && !rev) ? BX_JC_SPHERICAL : BX_JC_ALL);
+    s->jc = joint_class(desc);
     // fused contact section: pbd, one-way plane colliders only, <= 2 rows per body
     std::vector<int> rows_of(desc->num_bodies, 0);
     int max_rows = 0;

@@ -22,11 +22,13 @@ static bx_kernel_fn pick(int jc, int cc) {
   if (MODE == BX_MODE_PBD && cc == BX_CC_PLANE_FUSED) {
     if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC0 | BXF_FUSED_CONTACTS);
     if (jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC0 | BXF_FUSED_CONTACTS);
+    if (jc == BX_JC_SPHERICAL_ANGLE) return BX_K(BXF_JC3, BXF_CC0 | BXF_FUSED_CONTACTS);
     return BX_K(BXF_JC2, BXF_CC0 | BXF_FUSED_CONTACTS);
   }
   if (cc != BX_CC_ALL && cc != BX_CC_MESH) {
     if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC0);
     if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC0);
+    if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL_ANGLE) return BX_K(BXF_JC3, BXF_CC0);
     return BX_K(BXF_JC2, BXF_CC0);
   }
   if (cc == BX_CC_MESH) {
@@ -35,6 +37,7 @@ static bx_kernel_fn pick(int jc, int cc) {
 #ifdef BX_TU_MESH
     if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC2);
     if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC2);
+    if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL_ANGLE) return BX_K(BXF_JC3, BXF_CC2);
     return BX_K(BXF_JC2, BXF_CC2);
 #else
     return nullptr;
@@ -42,6 +45,7 @@ static bx_kernel_fn pick(int jc, int cc) {
   }
   if (jc == BX_JC_REVOLUTE) return BX_K(BXF_JC0, BXF_CC1);
   if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL) return BX_K(BXF_JC1, BXF_CC1);
+  if (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL_ANGLE) return BX_K(BXF_JC3, BXF_CC1);
   return BX_K(BXF_JC2, BXF_CC1);
 #undef BX_K
 }
@@ -55,7 +59,9 @@ static bx_kernel_fn pick_any(int mode, int jc, int cc) {
 #define BX_KJ(MODE, JM, ENV) bx_step_kernel<MODE, (JM) | BXF_CC2 | BXF_COMMON | BXF_JOINT_OFFSET | ENV, BX_TU_MAXT, BX_TU_MINB>
 #define BX_KJ3(MODE, ENV)                                                                              \
   (jc == BX_JC_REVOLUTE ? BX_KJ(MODE, BXF_JC0, ENV)                                                    \
-                        : (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL ? BX_KJ(MODE, BXF_JC1, ENV) : BX_KJ(MODE, BXF_JC2, ENV)))
+                        : (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL                                \
+                               ? BX_KJ(MODE, BXF_JC1, ENV)                                             \
+                               : (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL_ANGLE ? BX_KJ(MODE, BXF_JC3, ENV) : BX_KJ(MODE, BXF_JC2, ENV))))
     if (cc & BX_CC_ENV) return mode == BX_MODE_PBD ? BX_KJ3(BX_MODE_PBD, BXF_ENV) : BX_KJ3(BX_MODE_LEGACY_SPRING, BXF_ENV);
     return mode == BX_MODE_PBD ? BX_KJ3(BX_MODE_PBD, 0) : BX_KJ3(BX_MODE_LEGACY_SPRING, 0);
 #undef BX_KJ3
