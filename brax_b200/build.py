@@ -5,6 +5,7 @@ GPU box with the snapshot.
 """
 import os
 import subprocess
+import time
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
@@ -44,17 +45,19 @@ def build(force: bool = False, verbose: bool = False, extra=(), out: str = None)
   jobs = [(common + ['-c', os.path.join(CSRC, 'bx_api.cu'), '-o', os.path.join(objdir, 'bx_api.o')])]
   objs = [os.path.join(objdir, 'bx_api.o'), os.path.join(objdir, 'bx_reset.o')]
   jobs.append(common + ['-c', os.path.join(CSRC, 'bx_reset.cu'), '-o', os.path.join(objdir, 'bx_reset.o')])
-  for maxt, minb in BOUNDS:
-    o = os.path.join(objdir, 'bx_kernels_%d.o' % maxt)
-    objs.append(o)
-    mesh = ['-DBX_TU_MESH=1'] if (maxt, minb) in MESH_BOUNDS else []
-    jobs.append(common + mesh + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-c',
-                                 os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
-  for name, maxt, minb in EXTRA_UNITS:
-    o = os.path.join(objdir, 'bx_kernels_%s.o' % name)
-    objs.append(o)
-    jobs.append(common + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-DBX_TU_NAME=%s' % name, '-c',
-                          os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
+  # one object per (launch bound, dynamics mode): independent nvcc jobs, run in parallel below
+  for mode in (0, 1):
+    for maxt, minb in BOUNDS:
+      o = os.path.join(objdir, 'bx_kernels_%d_m%d.o' % (maxt, mode))
+      objs.append(o)
+      mesh = ['-DBX_TU_MESH=1'] if (maxt, minb) in MESH_BOUNDS else []
+      jobs.append(common + mesh + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-DBX_TU_MODE=%d' % mode, '-c',
+                                   os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
+    for name, maxt, minb in EXTRA_UNITS:
+      o = os.path.join(objdir, 'bx_kernels_%s_m%d.o' % (name, mode))
+      objs.append(o)
+      jobs.append(common + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-DBX_TU_NAME=%s' % name,
+                            '-DBX_TU_MODE=%d' % mode, '-c', os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
   # incremental: an object is recompiled only if one of ITS sources is newer (same flags: the object
   # directory is keyed by the output name; `extra` flags force everything)
   kernel_deps = ['bx_kernels.cu', 'bx_step_kernel.cuh', 'bx_params.h', 'bx_math.cuh', 'bx_tables.h',
@@ -73,8 +76,21 @@ def build(force: bool = False, verbose: bool = False, extra=(), out: str = None)
     return all(os.path.getmtime(os.path.join(CSRC, d)) <= os.path.getmtime(o) for d in deps)
 
   jobs = [j for j in jobs if not fresh(j)]
-  procs = [subprocess.Popen(j) for j in jobs]
-  rcs = [p.wait() for p in procs]
+  # at most one nvcc per core at a time (the mesh-class objects are the long ones: they go first)
+  jobs.sort(key=lambda j: '-DBX_TU_MESH=1' not in j)
+  limit = max(1, os.cpu_count() or 1)
+  running, rcs = [], []
+  for j in jobs:
+    while len(running) >= limit:
+      done = [p for p in running if p.poll() is not None]
+      if not done:
+        time.sleep(0.2)
+        continue
+      for p in done:
+        running.remove(p)
+        rcs.append(p.returncode)
+    running.append(subprocess.Popen(j))
+  rcs += [p.wait() for p in running]
   if any(rcs):
     raise subprocess.CalledProcessError(max(rcs), 'nvcc')
   with open(stamp, 'w') as f:

@@ -1,11 +1,11 @@
-// bx_kernels.cu -- instantiates the step kernel for ONE launch bound
-// (compiled once per bound: -DBX_TU_MAXT=256|320|512 -DBX_TU_MINB=2|2|1) and
-// exports its launcher.  Variants: dynamics mode x joint class x contact class
+// bx_kernels.cu -- instantiates the step kernel for ONE launch bound and ONE dynamics mode
+// (compiled once per bound and mode: -DBX_TU_MAXT=256|320|512 -DBX_TU_MINB=2|2|1 -DBX_TU_MODE=0|1: the
+// build runs one nvcc per object in parallel) and exports its launcher.  Variants: dynamics mode x joint class x contact class
 // (bx_params.h); a system runs the variant that contains only its own features.
 #include "bx_step_kernel.cuh"
 
-#ifndef BX_TU_MAXT
-#error "compile with -DBX_TU_MAXT=<threads> -DBX_TU_MINB=<blocks per SM>"
+#if !defined(BX_TU_MAXT) || !defined(BX_TU_MODE)
+#error "compile with -DBX_TU_MAXT=<threads> -DBX_TU_MINB=<blocks per SM> -DBX_TU_MODE=<0 pbd | 1 legacy_spring>"
 #endif
 
 #define BX_CAT_(a, b) a##b
@@ -52,6 +52,7 @@ static bx_kernel_fn pick(int jc, int cc) {
 
 static bx_kernel_fn pick_any(int mode, int jc, int cc) {
   cc &= ~BX_CC_PDL;
+  if (mode != BX_TU_MODE) return nullptr;   // the other mode lives in the sibling object
   if (cc & BX_CC_JO) {
     // per-env joint sockets: one all-contact-features build per (mode, joint class, env epilogue); the joint class
     // stays the system's own because the joint record's stride is a compile-time property of it (JQS)
@@ -62,8 +63,8 @@ static bx_kernel_fn pick_any(int mode, int jc, int cc) {
                         : (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL                                \
                                ? BX_KJ(MODE, BXF_JC1, ENV)                                             \
                                : (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL_ANGLE ? BX_KJ(MODE, BXF_JC3, ENV) : BX_KJ(MODE, BXF_JC2, ENV))))
-    if (cc & BX_CC_ENV) return mode == BX_MODE_PBD ? BX_KJ3(BX_MODE_PBD, BXF_ENV) : BX_KJ3(BX_MODE_LEGACY_SPRING, BXF_ENV);
-    return mode == BX_MODE_PBD ? BX_KJ3(BX_MODE_PBD, 0) : BX_KJ3(BX_MODE_LEGACY_SPRING, 0);
+    if (cc & BX_CC_ENV) return BX_KJ3(BX_TU_MODE, BXF_ENV);
+    return BX_KJ3(BX_TU_MODE, 0);
 #undef BX_KJ3
 #undef BX_KJ
 #else
@@ -72,12 +73,13 @@ static bx_kernel_fn pick_any(int mode, int jc, int cc) {
   }
   if (cc & BX_CC_ENV) {
     cc &= ~BX_CC_ENV;
-    return mode == BX_MODE_PBD ? pick<BX_MODE_PBD, BXF_ENV>(jc, cc) : pick<BX_MODE_LEGACY_SPRING, BXF_ENV>(jc, cc);
+    return pick<BX_TU_MODE, BXF_ENV>(jc, cc);
   }
-  return mode == BX_MODE_PBD ? pick<BX_MODE_PBD, 0>(jc, cc) : pick<BX_MODE_LEGACY_SPRING, 0>(jc, cc);
+  return pick<BX_TU_MODE, 0>(jc, cc);
 }
 
-cudaError_t BX_CAT(bx_launch_, BX_TU_NAME)(int mode, int jc, int cc, unsigned grid, int threads,
+#define BX_TU_SUFFIX BX_CAT(BX_CAT(BX_TU_NAME, _m), BX_TU_MODE)
+cudaError_t BX_CAT(bx_launch_, BX_TU_SUFFIX)(int mode, int jc, int cc, unsigned grid, int threads,
                                            size_t smem, cudaStream_t stream,
                                            const BxKernelParams& p) {
   if (pick_any(mode, jc, cc) == nullptr) return cudaErrorInvalidDeviceFunction;
@@ -98,8 +100,8 @@ cudaError_t BX_CAT(bx_launch_, BX_TU_NAME)(int mode, int jc, int cc, unsigned gr
   return cudaLaunchKernelEx(&cfg, pick_any(mode, jc, cc), p);
 }
 
-cudaError_t BX_CAT(bx_set_smem_, BX_TU_NAME)(int bytes) {
-  for (int mode = 0; mode < 2; mode++)
+cudaError_t BX_CAT(bx_set_smem_, BX_TU_SUFFIX)(int bytes) {
+  for (int mode = BX_TU_MODE; mode <= BX_TU_MODE; mode++)
     for (int jc = 0; jc < BX_NUM_JC; jc++)
       for (int cc = 0; cc < BX_NUM_CC; cc++)
         for (int env = 0; env < 2; env++)
