@@ -45,19 +45,21 @@ def build(force: bool = False, verbose: bool = False, extra=(), out: str = None)
   jobs = [(common + ['-c', os.path.join(CSRC, 'bx_api.cu'), '-o', os.path.join(objdir, 'bx_api.o')])]
   objs = [os.path.join(objdir, 'bx_api.o'), os.path.join(objdir, 'bx_reset.o')]
   jobs.append(common + ['-c', os.path.join(CSRC, 'bx_reset.cu'), '-o', os.path.join(objdir, 'bx_reset.o')])
-  # one object per (launch bound, dynamics mode): independent nvcc jobs, run in parallel below
+  # one object per (launch bound, dynamics mode, env epilogue): independent nvcc jobs, run in parallel below
   for mode in (0, 1):
-    for maxt, minb in BOUNDS:
-      o = os.path.join(objdir, 'bx_kernels_%d_m%d.o' % (maxt, mode))
-      objs.append(o)
-      mesh = ['-DBX_TU_MESH=1'] if (maxt, minb) in MESH_BOUNDS else []
-      jobs.append(common + mesh + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-DBX_TU_MODE=%d' % mode, '-c',
+    for env in (0, 1):
+      tu = ['-DBX_TU_MODE=%d' % mode, '-DBX_TU_ENV=%d' % env]
+      for maxt, minb in BOUNDS:
+        o = os.path.join(objdir, 'bx_kernels_%d_m%de%d.o' % (maxt, mode, env))
+        objs.append(o)
+        mesh = ['-DBX_TU_MESH=1'] if (maxt, minb) in MESH_BOUNDS else []
+        jobs.append(common + mesh + tu + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-c',
+                                          os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
+      for name, maxt, minb in EXTRA_UNITS:
+        o = os.path.join(objdir, 'bx_kernels_%s_m%de%d.o' % (name, mode, env))
+        objs.append(o)
+        jobs.append(common + tu + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-DBX_TU_NAME=%s' % name, '-c',
                                    os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
-    for name, maxt, minb in EXTRA_UNITS:
-      o = os.path.join(objdir, 'bx_kernels_%s_m%d.o' % (name, mode))
-      objs.append(o)
-      jobs.append(common + ['-DBX_TU_MAXT=%d' % maxt, '-DBX_TU_MINB=%d' % minb, '-DBX_TU_NAME=%s' % name,
-                            '-DBX_TU_MODE=%d' % mode, '-c', os.path.join(CSRC, 'bx_kernels.cu'), '-o', o])
   # incremental: an object is recompiled only if one of ITS sources is newer (same flags: the object
   # directory is keyed by the output name; `extra` flags force everything)
   kernel_deps = ['bx_kernels.cu', 'bx_step_kernel.cuh', 'bx_params.h', 'bx_math.cuh', 'bx_tables.h',

@@ -1,11 +1,11 @@
-// bx_kernels.cu -- instantiates the step kernel for ONE launch bound and ONE dynamics mode
-// (compiled once per bound and mode: -DBX_TU_MAXT=256|320|512 -DBX_TU_MINB=2|2|1 -DBX_TU_MODE=0|1: the
-// build runs one nvcc per object in parallel) and exports its launcher.  Variants: dynamics mode x joint class x contact class
+// bx_kernels.cu -- instantiates the step kernel for ONE launch bound, ONE dynamics mode and with or without
+// the env epilogue (compiled once per combination: -DBX_TU_MAXT=256|320|512 -DBX_TU_MINB=2|2|1 -DBX_TU_MODE=0|1
+// -DBX_TU_ENV=0|1: the build runs one nvcc per object in parallel) and exports its launcher.  Variants: dynamics mode x joint class x contact class
 // (bx_params.h); a system runs the variant that contains only its own features.
 #include "bx_step_kernel.cuh"
 
-#if !defined(BX_TU_MAXT) || !defined(BX_TU_MODE)
-#error "compile with -DBX_TU_MAXT=<threads> -DBX_TU_MINB=<blocks per SM> -DBX_TU_MODE=<0 pbd | 1 legacy_spring>"
+#if !defined(BX_TU_MAXT) || !defined(BX_TU_MODE) || !defined(BX_TU_ENV)
+#error "compile with -DBX_TU_MAXT=<threads> -DBX_TU_MINB=<blocks per SM> -DBX_TU_MODE=<0 pbd | 1 legacy_spring> -DBX_TU_ENV=<0 | 1>"
 #endif
 
 #define BX_CAT_(a, b) a##b
@@ -52,33 +52,29 @@ static bx_kernel_fn pick(int jc, int cc) {
 
 static bx_kernel_fn pick_any(int mode, int jc, int cc) {
   cc &= ~BX_CC_PDL;
-  if (mode != BX_TU_MODE) return nullptr;   // the other mode lives in the sibling object
+  if (mode != BX_TU_MODE || ((cc & BX_CC_ENV) != 0) != (BX_TU_ENV != 0)) return nullptr;   // lives in a sibling object
   if (cc & BX_CC_JO) {
     // per-env joint sockets: one all-contact-features build per (mode, joint class, env epilogue); the joint class
     // stays the system's own because the joint record's stride is a compile-time property of it (JQS)
 #ifdef BX_TU_MESH
-#define BX_KJ(MODE, JM, ENV) bx_step_kernel<MODE, (JM) | BXF_CC2 | BXF_COMMON | BXF_JOINT_OFFSET | ENV, BX_TU_MAXT, BX_TU_MINB>
+#define BX_KJ(MODE, JM, ENV) bx_step_kernel<MODE, (JM) | BXF_CC2 | BXF_COMMON | BXF_JOINT_OFFSET | (ENV), BX_TU_MAXT, BX_TU_MINB>
 #define BX_KJ3(MODE, ENV)                                                                              \
   (jc == BX_JC_REVOLUTE ? BX_KJ(MODE, BXF_JC0, ENV)                                                    \
                         : (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL                                \
                                ? BX_KJ(MODE, BXF_JC1, ENV)                                             \
                                : (MODE == BX_MODE_PBD && jc == BX_JC_SPHERICAL_ANGLE ? BX_KJ(MODE, BXF_JC3, ENV) : BX_KJ(MODE, BXF_JC2, ENV))))
-    if (cc & BX_CC_ENV) return BX_KJ3(BX_TU_MODE, BXF_ENV);
-    return BX_KJ3(BX_TU_MODE, 0);
+    return BX_KJ3(BX_TU_MODE, BX_TU_ENV ? BXF_ENV : 0);
 #undef BX_KJ3
 #undef BX_KJ
 #else
     return nullptr;
 #endif
   }
-  if (cc & BX_CC_ENV) {
-    cc &= ~BX_CC_ENV;
-    return pick<BX_TU_MODE, BXF_ENV>(jc, cc);
-  }
-  return pick<BX_TU_MODE, 0>(jc, cc);
+  cc &= ~BX_CC_ENV;
+  return pick<BX_TU_MODE, BX_TU_ENV ? BXF_ENV : 0>(jc, cc);
 }
 
-#define BX_TU_SUFFIX BX_CAT(BX_CAT(BX_TU_NAME, _m), BX_TU_MODE)
+#define BX_TU_SUFFIX BX_CAT(BX_CAT(BX_CAT(BX_CAT(BX_TU_NAME, _m), BX_TU_MODE), e), BX_TU_ENV)
 cudaError_t BX_CAT(bx_launch_, BX_TU_SUFFIX)(int mode, int jc, int cc, unsigned grid, int threads,
                                            size_t smem, cudaStream_t stream,
                                            const BxKernelParams& p) {
@@ -104,7 +100,7 @@ cudaError_t BX_CAT(bx_set_smem_, BX_TU_SUFFIX)(int bytes) {
   for (int mode = BX_TU_MODE; mode <= BX_TU_MODE; mode++)
     for (int jc = 0; jc < BX_NUM_JC; jc++)
       for (int cc = 0; cc < BX_NUM_CC; cc++)
-        for (int env = 0; env < 2; env++)
+        for (int env = BX_TU_ENV; env <= BX_TU_ENV; env++)
           for (int jo = 0; jo < 2; jo++) {
             const int c2 = cc | (env ? BX_CC_ENV : 0) | (jo ? BX_CC_JO : 0);
             if (pick_any(mode, jc, c2) == nullptr) continue;

@@ -9,7 +9,28 @@
 
 #include <cuda_runtime.h>
 
+// BX_PACKED_V3 (default 1): component-wise V3 / Q4 arithmetic issues the packed FP32 instructions of sm_100
+// (FADD2 / FMUL2 / FFMA2 = add/mul/fma.rn.f32x2: two lanes per issue slot, each rounded like the scalar
+// instruction) on the (x, y) pair, the scalar one on z.  A product `v * s` / `a * b` is first an unevaluated
+// proxy (V3S / V3P) so that `c + v * s` still becomes ONE fused multiply-add per component -- the contraction
+// the compiler did on the scalar expression -- instead of a multiply and an add.
+#ifndef BX_PACKED_V3
+#define BX_PACKED_V3 1
+#endif
+#if BX_PACKED_V3
+struct V3S;
+struct V3P;
+struct V3 {
+  float x, y, z;
+  V3() = default;
+  __device__ __forceinline__ V3(const V3S& p);
+  __device__ __forceinline__ V3(const V3P& p);
+};
+struct V3S { V3 v; float s; };   // v * s
+struct V3P { V3 a, b; };         // a * b, component-wise
+#else
 struct V3 { float x, y, z; };
+#endif
 struct Q4 { float w, x, y, z; };
 
 #define BXD __device__ __forceinline__
@@ -63,12 +84,56 @@ BXD float bx_sqrt(float a) {
 }
 
 BXD V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+#if BX_PACKED_V3
+BXD float2 xy(V3 a) { return make_float2(a.x, a.y); }
+BXD float2 f2(float s) { return make_float2(s, s); }
+BXD V3 pk(float2 r, float z) { return v3(r.x, r.y, z); }
+BXD V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
+BXD V3 operator+(V3 a, V3 b) { return pk(__fadd2_rn(xy(a), xy(b)), a.z + b.z); }
+BXD V3 operator-(V3 a, V3 b) { return pk(__fadd2_rn(xy(a), xy(-b)), a.z - b.z); }
+// products: proxies, evaluated on conversion to V3
+BXD V3S operator*(V3 a, float s) { V3S r; r.v = a; r.s = s; return r; }
+BXD V3S operator*(float s, V3 a) { V3S r; r.v = a; r.s = s; return r; }
+BXD V3P operator*(V3 a, V3 b) { V3P r; r.a = a; r.b = b; return r; }
+BXD V3 ev(V3S p) { return pk(__fmul2_rn(xy(p.v), f2(p.s)), p.v.z * p.s); }
+BXD V3 ev(V3P p) { return pk(__fmul2_rn(xy(p.a), xy(p.b)), p.a.z * p.b.z); }
+BXD V3::V3(const V3S& p) { *this = ev(p); }
+BXD V3::V3(const V3P& p) { *this = ev(p); }
+BXD V3 fma3(V3 v, float s, V3 c) { return pk(__ffma2_rn(xy(v), f2(s), xy(c)), fmaf(v.z, s, c.z)); }
+BXD V3 fma3(V3 a, V3 b, V3 c) { return pk(__ffma2_rn(xy(a), xy(b), xy(c)), fmaf(a.z, b.z, c.z)); }
+BXD V3S operator-(V3S p) { p.s = -p.s; return p; }
+BXD V3P operator-(V3P p) { p.a = -p.a; return p; }
+// c + v * s and friends: one fused multiply-add per component
+BXD V3 operator+(V3 c, V3S p) { return fma3(p.v, p.s, c); }
+BXD V3 operator+(V3S p, V3 c) { return fma3(p.v, p.s, c); }
+BXD V3 operator-(V3 c, V3S p) { return fma3(p.v, -p.s, c); }
+BXD V3 operator-(V3S p, V3 c) { return fma3(p.v, p.s, -c); }
+BXD V3 operator+(V3S p, V3S q) { return fma3(p.v, p.s, ev(q)); }
+BXD V3 operator-(V3S p, V3S q) { return fma3(q.v, -q.s, ev(p)); }
+BXD V3 operator+(V3 c, V3P p) { return fma3(p.a, p.b, c); }
+BXD V3 operator+(V3P p, V3 c) { return fma3(p.a, p.b, c); }
+BXD V3 operator-(V3 c, V3P p) { return fma3(-p.a, p.b, c); }
+BXD V3 operator-(V3P p, V3 c) { return fma3(p.a, p.b, -c); }
+BXD V3 operator+(V3P p, V3P q) { return fma3(p.a, p.b, ev(q)); }
+BXD V3 operator+(V3S p, V3P q) { return fma3(p.v, p.s, ev(q)); }
+BXD V3 operator+(V3P p, V3S q) { return fma3(q.v, q.s, ev(p)); }
+// a product of a product: evaluate the inner one
+BXD V3S operator*(V3S p, float s) { return ev(p) * s; }
+BXD V3S operator*(float s, V3S p) { return ev(p) * s; }
+BXD V3S operator*(V3P p, float s) { return ev(p) * s; }
+BXD V3S operator*(float s, V3P p) { return ev(p) * s; }
+BXD V3P operator*(V3S p, V3 b) { return ev(p) * b; }
+BXD V3P operator*(V3 a, V3S p) { return a * ev(p); }
+BXD V3P operator*(V3P p, V3 b) { return ev(p) * b; }
+BXD V3P operator*(V3 a, V3P p) { return a * ev(p); }
+#else
 BXD V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
 BXD V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
 BXD V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
 BXD V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
 BXD V3 operator*(float s, V3 a) { return v3(s * a.x, s * a.y, s * a.z); }
 BXD V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
+#endif
 BXD V3 vdiv(V3 a, float s) {
   float r = bx_rcp(s);
   return v3(bx_mul_rcp(a.x, s, r), bx_mul_rcp(a.y, s, r), bx_mul_rcp(a.z, s, r));
@@ -100,8 +165,19 @@ BXD V3 cross(V3 a, V3 b) {
   return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
 }
 BXD Q4 q4(float w, float x, float y, float z) { Q4 r; r.w = w; r.x = x; r.y = y; r.z = z; return r; }
+#if BX_PACKED_V3
+BXD Q4 operator+(Q4 a, Q4 b) {
+  const float2 l = __fadd2_rn(make_float2(a.w, a.x), make_float2(b.w, b.x)), h = __fadd2_rn(make_float2(a.y, a.z), make_float2(b.y, b.z));
+  return q4(l.x, l.y, h.x, h.y);
+}
+BXD Q4 operator*(float s, Q4 a) {
+  const float2 l = __fmul2_rn(make_float2(a.w, a.x), make_float2(s, s)), h = __fmul2_rn(make_float2(a.y, a.z), make_float2(s, s));
+  return q4(l.x, l.y, h.x, h.y);
+}
+#else
 BXD Q4 operator+(Q4 a, Q4 b) { return q4(a.w + b.w, a.x + b.x, a.y + b.y, a.z + b.z); }
 BXD Q4 operator*(float s, Q4 a) { return q4(s * a.w, s * a.x, s * a.y, s * a.z); }
+#endif
 BXD Q4 qconj(Q4 q) { return q4(q.w, -q.x, -q.y, -q.z); }
 
 // math.py:25-40

@@ -102,23 +102,29 @@ enum { BX_CC_PLANE_FUSED = 0, BX_CC_PLANE = 1, BX_CC_ALL = 2, BX_CC_MESH = 3, BX
 #define BXF_CC1 (BXF_ONE_WAY | BXF_TWO_WAY | BXF_CAPSULE_PLANE | BXF_CAPSULE_CAPSULE | BXF_BOX_PLANE)
 #define BXF_CC2 (BXF_CC1 | BXF_CAPSULE_BOX)  // ... and capsule against a triangulated box
 
-// One object per launch bound and dynamics mode (bx_kernels.cu compiled with -DBX_TU_MAXT=.. -DBX_TU_MINB=..
-// -DBX_TU_MODE=0|1) exports a launcher and a shared-memory setter; bx_launch_<bound> picks the mode's.
+// One object per launch bound, dynamics mode and env-epilogue flag (bx_kernels.cu compiled with -DBX_TU_MAXT=..
+// -DBX_TU_MINB=.. -DBX_TU_MODE=0|1 -DBX_TU_ENV=0|1) exports a launcher and a shared-memory setter;
+// bx_launch_<bound> picks the object.
+#define BX_LAUNCHER_PROTO(sfx)                                                                          \
+  cudaError_t bx_launch_##sfx(int mode, int jc, int cc, unsigned grid, int threads, size_t smem,        \
+                              cudaStream_t stream, const BxKernelParams& p);                            \
+  cudaError_t bx_set_smem_##sfx(int bytes);
 #define BX_LAUNCHER_DECL(maxt)                                                                          \
-  cudaError_t bx_launch_##maxt##_m0(int mode, int jc, int cc, unsigned grid, int threads, size_t smem,  \
-                                    cudaStream_t stream, const BxKernelParams& p);                      \
-  cudaError_t bx_launch_##maxt##_m1(int mode, int jc, int cc, unsigned grid, int threads, size_t smem,  \
-                                    cudaStream_t stream, const BxKernelParams& p);                      \
-  cudaError_t bx_set_smem_##maxt##_m0(int bytes);                                                       \
-  cudaError_t bx_set_smem_##maxt##_m1(int bytes);                                                       \
+  BX_LAUNCHER_PROTO(maxt##_m0e0) BX_LAUNCHER_PROTO(maxt##_m0e1)                                         \
+  BX_LAUNCHER_PROTO(maxt##_m1e0) BX_LAUNCHER_PROTO(maxt##_m1e1)                                         \
   static inline cudaError_t bx_launch_##maxt(int mode, int jc, int cc, unsigned grid, int threads,      \
                                              size_t smem, cudaStream_t stream, const BxKernelParams& p) { \
-    return mode == 0 ? bx_launch_##maxt##_m0(mode, jc, cc, grid, threads, smem, stream, p)              \
-                     : bx_launch_##maxt##_m1(mode, jc, cc, grid, threads, smem, stream, p);             \
+    if (cc & BX_CC_ENV)                                                                                 \
+      return mode == 0 ? bx_launch_##maxt##_m0e1(mode, jc, cc, grid, threads, smem, stream, p)          \
+                       : bx_launch_##maxt##_m1e1(mode, jc, cc, grid, threads, smem, stream, p);         \
+    return mode == 0 ? bx_launch_##maxt##_m0e0(mode, jc, cc, grid, threads, smem, stream, p)            \
+                     : bx_launch_##maxt##_m1e0(mode, jc, cc, grid, threads, smem, stream, p);           \
   }                                                                                                     \
   static inline cudaError_t bx_set_smem_##maxt(int bytes) {                                             \
-    cudaError_t e = bx_set_smem_##maxt##_m0(bytes);                                                     \
-    return e != cudaSuccess ? e : bx_set_smem_##maxt##_m1(bytes);                                       \
+    cudaError_t e = bx_set_smem_##maxt##_m0e0(bytes);                                                   \
+    if (e == cudaSuccess) e = bx_set_smem_##maxt##_m0e1(bytes);                                         \
+    if (e == cudaSuccess) e = bx_set_smem_##maxt##_m1e0(bytes);                                         \
+    return e != cudaSuccess ? e : bx_set_smem_##maxt##_m1e1(bytes);                                     \
   }
 BX_LAUNCHER_DECL(256)
 BX_LAUNCHER_DECL(320)

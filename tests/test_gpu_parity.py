@@ -148,7 +148,10 @@ def check_step(name, ins, act, got, strict_frac=0.90, outlier_frac=OUTLIER_FRAC,
   pen, pen64 = ref['contact_penetration'], r64['contact_penetration']
   if pen.size:
     mism = (got['contact_penetration'] > 0) != (pen > 0)
-    hard = mism & (np.abs(pen) >= 1e-6) & (np.abs(pen64) >= 1e-6)
+    # ... and the kernel's flag differs from the float64 oracle's too: where the two ORACLES disagree a discrete
+    # decision flipped inside the float32 oracle (seen: ant_spring, kernel = float64 to 1e-8, float32 oracle 9 mm off)
+    # and the kernel siding with the float64 reference is not an error (the env still spends the outlier budget)
+    hard = mism & (np.abs(pen) >= 1e-6) & (np.abs(pen64) >= 1e-6) & ((got['contact_penetration'] > 0) != (pen64 > 0))
     assert not hard.any(), (name, 'contact flags', int(hard.sum()))
     # body-level flag: any(info.contact.vel != 0)  (SURVEY.md 8(c)).  The impulse of
     # an active contact is itself gated by float compares (normal-velocity sign,
