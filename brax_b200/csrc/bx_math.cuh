@@ -188,6 +188,15 @@ BXD V3 rotate(V3 v, Q4 q) {
   V3 r = 2.f * (uv * u) + (s * s - uu) * v;
   return r + (2.f * s) * cross(u, v);
 }
+// rotate((0, 0, 1), q) -- the plane normal of every plane contact row (colliders.py:672,749) -- without the terms
+// that multiply the zero components: the same operations, in the same order and with the same fused
+// multiply-adds `rotate` performs on the non-zero ones (adding the exact zeros changes nothing), 13 instead of ~25.
+BXD V3 rotate_z(Q4 q) {
+  const float uu = dot(v3(q.x, q.y, q.z), v3(q.x, q.y, q.z));
+  const float d = q.w * q.w - uu, s2 = 2.f * q.w;
+  const float zx = q.z * q.x, zy = q.z * q.y, zz = q.z * q.z;
+  return v3(fmaf(q.y, s2, 2.f * zx), fmaf(-q.x, s2, 2.f * zy), fmaf(zz, 2.f, d));
+}
 // math.py:130-145
 BXD Q4 quat_mul(Q4 u, Q4 v) {
   return q4(u.w * v.w - u.x * v.x - u.y * v.y - u.z * v.z,

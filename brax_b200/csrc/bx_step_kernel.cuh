@@ -913,7 +913,7 @@ BXS Contact contact_fn(const BxHeader& h, int kind, const float4* cq, const floa
     ct.pos = vdiv(best_a + best_b, 2.f);
     ct.vel = (va + cross(wa, ct.pos - pa)) - (vb + cross(wb, ct.pos - pb));
   } else {
-    V3 n = rotate(v3(0.f, 0.f, 1.f), rb);
+    V3 n = rotate_z(rb);
     V3 off = rotate(f3(cq[CQ_PTS]), ra);
     if (BXF_IS(kind == BX_PAIR_CAPSULE_PLANE, BXF_CAPSULE_PLANE, BXF_BOX_PLANE)) {
       ct.pos = (pa + off) - n * mat.z;
