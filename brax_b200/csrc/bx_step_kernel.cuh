@@ -86,6 +86,13 @@
 // Inside Kern<FEAT> the mask is the template parameter.
 #define BX_FEAT FEAT
 // "is x the case?" with the answer folded at compile time when the mask decides it
+// the env epilogue phases (once per step, after the substep loop): inlined (shared-memory loads instead of the
+// generic ones a separate function gets) unless -DBX_ENV_NOINLINE
+#ifdef BX_ENV_NOINLINE
+#define BX_ENV_INLINE __noinline__
+#else
+#define BX_ENV_INLINE __forceinline__
+#endif
 #define BXF_IS(cond, yes_mask, no_mask) \
   ((BX_FEAT & (no_mask)) == 0 ? true : ((BX_FEAT & (yes_mask)) == 0 ? false : (cond)))
 
@@ -1511,7 +1518,7 @@ BXS float env_map_act(const Ctx& c, const BxHeader& h, int i) {
 // (grasp.py:75-85): every warp maps its share of the action vector; the last warp maps the
 // three palm-target slots itself and moves the (frozen) palm towards the target.
 template <int MODE>
-static __device__ __noinline__ void phase_env_before(const Ctx c, const BxHeader& h) {
+static __device__ BX_ENV_INLINE void phase_env_before(const Ctx c, const BxHeader& h) {
   typedef Lay<MODE> L;
   const int po = MODE == BX_MODE_PBD ? 2 * c.cur : 0;
   const bool last = c.warp == c.nwarp - 1;
@@ -1548,7 +1555,7 @@ BXS float env_contact_flag(const Ctx& c, const BxHeader& h, int b) {
 // Fetch.step / Grasp.step after sys.step (fetch.py:55-122, grasp.py:88-186)
 // rand: this tile's [32,3] uniforms of the target teleport for this step, or nullptr
 template <int MODE>
-static __device__ __noinline__ void phase_env_ego(const Ctx c, const BxHeader& h, const float* rand, int nenv) {
+static __device__ BX_ENV_INLINE void phase_env_ego(const Ctx c, const BxHeader& h, const float* rand, int nenv) {
   typedef Lay<MODE> L;
   const int po = MODE == BX_MODE_PBD ? 2 * c.cur : 0;
   const V3 pref = ldv(c, L::BQ * h.env_ref + po);
@@ -1644,7 +1651,7 @@ static __device__ __noinline__ void phase_env_ego(const Ctx c, const BxHeader& h
   }
 }
 template <int MODE>
-static __device__ __noinline__ void phase_env(const Ctx c, const BxHeader& h) {
+static __device__ BX_ENV_INLINE void phase_env(const Ctx c, const BxHeader& h) {
   typedef Lay<MODE> L;
   const int po = MODE == BX_MODE_PBD ? 2 * c.cur : 0;
   const int E = h.q_env;
