@@ -43,11 +43,12 @@ struct bx_system {
   bx_reset_desc* d_reset;  // device copy of desc.reset (bx_default_qp), or NULL
   int reset_dof;
   float* d_hm;  // height grids of the box_heightmap pairs, concatenated in pair order, or NULL
+  BxResetMap reset_map;  // reset joint -> step joint (per-env joint sockets in bx_default_qp_offsets)
 };
 
 cudaError_t bx_reset_launch(const bx_reset_desc* d_tables, int nb, int64_t num_envs, const float* joint_angle,
-                            const float* joint_velocity, float* pos, float* rot, float* vel, float* ang,
-                            cudaStream_t stream);
+                            const float* joint_velocity, const float* joint_offset, const BxResetMap& map,
+                            float* pos, float* rot, float* vel, float* ang, cudaStream_t stream);
 
 static thread_local std::string g_err;
 static std::atomic<int64_t> g_launches{0};
@@ -916,6 +917,14 @@ extern "C" int bx_system_create(const bx_system_desc* desc, int device, bx_syste
     if ((e1 = cudaMemcpy(s->d_reset, desc->reset, sizeof(bx_reset_desc), cudaMemcpyHostToDevice)) != cudaSuccess)
       return drop("upload of reset tables failed", e1);
     s->reset_dof = desc->reset->num_dof;
+    // reset joints are listed in depth order, the step's joints in the reference's joint-group order: match by bodies
+    s->reset_map.num_joints = desc->num_joints;
+    for (int j = 0; j < desc->reset->num_joints && j < 64; j++) {
+      s->reset_map.step_joint[j] = -1;
+      for (int k = 0; k < desc->num_joints; k++)
+        if (desc->joints[k].body_p == desc->reset->joints[j].body_p && desc->joints[k].body_c == desc->reset->joints[j].body_c)
+          s->reset_map.step_joint[j] = k;
+    }
   }
   *out = s;
   return 0;
@@ -925,14 +934,23 @@ extern "C" int bx_system_num_joint_dof(const bx_system* s) { return s && s->d_re
 
 extern "C" int bx_default_qp(const bx_system* s, int64_t B, const float* joint_angle, const float* joint_velocity,
                              float* pos, float* rot, float* vel, float* ang, void* stream) {
+  return bx_default_qp_offsets(s, B, joint_angle, joint_velocity, nullptr, pos, rot, vel, ang, stream);
+}
+
+extern "C" int bx_default_qp_offsets(const bx_system* s, int64_t B, const float* joint_angle, const float* joint_velocity,
+                                     const float* joint_offset, float* pos, float* rot, float* vel, float* ang,
+                                     void* stream) {
   if (!s) return fail("system is NULL");
+  if (joint_offset)
+    for (int j = 0; s->d_reset && j < s->reset_map.num_joints && j < 64; j++)
+      if (s->reset_map.step_joint[j] < 0) return fail("bx_default_qp_offsets: a reset joint has no counterpart in desc.joints");
   if (!s->d_reset) return fail("bx_default_qp needs a system created with desc.reset");
   if (B <= 0) return fail("num_envs must be positive");
   if (!pos || !rot || !vel || !ang) return fail("QP pointers must not be NULL");
   if (s->reset_dof > 0 && (!joint_angle || !joint_velocity)) return fail("joint_angle / joint_velocity must not be NULL");
   CUDA_OK(cudaSetDevice(s->device));
-  CUDA_OK(bx_reset_launch(s->d_reset, s->h.nb, B, joint_angle, joint_velocity, pos, rot, vel, ang,
-                          static_cast<cudaStream_t>(stream)));
+  CUDA_OK(bx_reset_launch(s->d_reset, s->h.nb, B, joint_angle, joint_velocity, joint_offset, s->reset_map, pos, rot, vel,
+                          ang, static_cast<cudaStream_t>(stream)));
   g_launches.fetch_add(1);
   return 0;
 }

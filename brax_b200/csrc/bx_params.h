@@ -9,6 +9,12 @@
 #include "bx_tables.h"
 
 // bx_policy by value (include/brax_b200.h): the in-kernel MLP policy of a rollout
+// reset joint j (depth order of bx_reset_desc.joints) -> its index in bx_system_desc.joints: how the reset kernel
+// finds a joint's socket in a per-env joint_offset[B,J,3] array (bx_default_qp_offsets)
+struct BxResetMap {
+  int32_t num_joints;
+  int32_t step_joint[64];
+};
 #define BX_FRICTION_SMEM 128   // bytes behind the mbarriers: friction[e]^2 of the tile's 32 envs
 #define BX_POLICY_KBLOCK 32     // weight rows a warp stages per block (4 units wide)
 #define BX_POLICY_MAX_WARPS 16  // slices are laid out for the widest launch

@@ -9,12 +9,14 @@
 
 #include "../../include/brax_b200.h"
 #include "bx_math.cuh"
+#include "bx_params.h"
 
 #define ROW(r) sm[(r) * 32 + lane]
 
 __global__ void __launch_bounds__(32)
 bx_reset_kernel(const bx_reset_desc* __restrict__ gt, int nb, int64_t num_envs,
                 const float* __restrict__ joint_angle, const float* __restrict__ joint_velocity,
+                const float* __restrict__ joint_offset, BxResetMap map,
                 float* __restrict__ pos_o, float* __restrict__ rot_o, float* __restrict__ vel_o,
                 float* __restrict__ ang_o) {
   extern __shared__ float smem_all[];
@@ -59,7 +61,13 @@ bx_reset_kernel(const bx_reset_desc* __restrict__ gt, int nb, int64_t num_envs,
     const Q4 rp = body_rot(jt.body_p);
     const V3 pp = body_pos(jt.body_p);
     const Q4 wr = quat_mul(rp, lr);                                                     // :204
-    const V3 lp = v3(jt.off_p[0], jt.off_p[1], jt.off_p[2]) - rotate(v3(jt.off_c[0], jt.off_c[1], jt.off_c[2]), lr);
+    // this env's own socket when per-env joint offsets are given ([B,J,3] in the order of bx_system_desc.joints)
+    V3 op = v3(jt.off_p[0], jt.off_p[1], jt.off_p[2]);
+    if (joint_offset != nullptr) {
+      const float* o = joint_offset + (e * map.num_joints + map.step_joint[j]) * 3;
+      op = v3(o[0], o[1], o[2]);
+    }
+    const V3 lp = op - rotate(v3(jt.off_c[0], jt.off_c[1], jt.off_c[2]), lr);
     const V3 wp = pp + rotate(lp, rp);                                                  // :206
     const V3 wa = rotate(la, rp);                                                       // :207
     const int c = jt.body_c * 10;
@@ -93,8 +101,8 @@ bx_reset_kernel(const bx_reset_desc* __restrict__ gt, int nb, int64_t num_envs,
 }
 
 cudaError_t bx_reset_launch(const bx_reset_desc* d_tables, int nb, int64_t num_envs, const float* joint_angle,
-                            const float* joint_velocity, float* pos, float* rot, float* vel, float* ang,
-                            cudaStream_t stream) {
+                            const float* joint_velocity, const float* joint_offset, const BxResetMap& map,
+                            float* pos, float* rot, float* vel, float* ang, cudaStream_t stream) {
   const size_t smem = (sizeof(bx_reset_desc) + 15) / 16 * 16 + static_cast<size_t>(nb) * 10 * 32 * sizeof(float);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(bx_reset_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -102,6 +110,7 @@ cudaError_t bx_reset_launch(const bx_reset_desc* d_tables, int nb, int64_t num_e
     if (e != cudaSuccess) return e;
   }
   const unsigned grid = static_cast<unsigned>((num_envs + 31) / 32);
-  bx_reset_kernel<<<grid, 32, smem, stream>>>(d_tables, nb, num_envs, joint_angle, joint_velocity, pos, rot, vel, ang);
+  bx_reset_kernel<<<grid, 32, smem, stream>>>(d_tables, nb, num_envs, joint_angle, joint_velocity, joint_offset, map, pos,
+                                              rot, vel, ang);
   return cudaGetLastError();
 }

@@ -20,7 +20,7 @@ from typing import Any, Dict, List
 
 import numpy as np
 
-ABI_VERSION = 13
+ABI_VERSION = 14
 
 MODE = {'pbd': 0, 'legacy_spring': 1}
 JOINT_KIND = {'revolute': 0, 'spherical': 1, 'spring_revolute': 2,

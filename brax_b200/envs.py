@@ -240,7 +240,8 @@ class Env:
       joint_angle = torch.from_numpy(self.sys.default_angle()).to(dev) + noise()    # ant.py:202
     if joint_velocity is None:
       joint_velocity = noise()                                                      # ant.py:203
-    qp = self.sys.default_qp(joint_angle=joint_angle.reshape(b, nd), joint_velocity=joint_velocity.reshape(b, nd))
+    qp = self.sys.default_qp(joint_angle=joint_angle.reshape(b, nd), joint_velocity=joint_velocity.reshape(b, nd),
+                             joint_offset=self.joint_offset)
     qp = self._place_targets(qp, gen)
     obs = self.sys.observe(qp, self.friction)
     names = self.env.metric_names()
@@ -278,10 +279,9 @@ class Env:
     """Domain randomisation over joint sockets, as `DomainRandomizationWrapper(env_fn, *joint_randomizer(env,
     offsets, keys))` (experimental/tracing/randomizers.py:54-97): env e is stepped with `Joint.parent_offset` =
     joint_offset[e, j] for joint j -- `self.sys.joint_offsets()` (the config's values) plus your per-env deltas on
-    the joints you select.  float32 CUDA tensor [B,J,3], or None to return to the config.  Applies to `step` and the
-    wrappers around this env; `reset` builds its pose from the config's sockets (the solver then pulls the joints
-    onto the randomised ones within the first steps), not from the randomised ones as the reference's vmapped
-    `default_qp` does."""
+    the joints you select.  float32 CUDA tensor [B,J,3], or None to return to the config.  Applies to `step`, to
+    `reset` (the pose is built from the randomised sockets, as the reference's vmapped `default_qp` does:
+    bx_default_qp_offsets) and to the wrappers around this env."""
     self.joint_offset = joint_offset
     return self
 

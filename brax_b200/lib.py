@@ -17,7 +17,7 @@ SYMBOLS = ('bx_system_create', 'bx_system_destroy', 'bx_system_num_contacts',
            'bx_step_host', 'bx_rollout', 'bx_system_configure',
            'bx_system_autotune', 'bx_system_threads', 'bx_host_transfer_bytes',
            'bx_host_alloc', 'bx_host_free', 'bx_desc_tile_bytes',
-           'bx_launch_count', 'bx_last_error', 'bx_system_num_joint_dof', 'bx_default_qp',
+           'bx_launch_count', 'bx_last_error', 'bx_system_num_joint_dof', 'bx_default_qp', 'bx_default_qp_offsets',
            'bx_step_host_static', 'bx_static_scratch_bytes', 'bx_step_host_async', 'bx_host_wait', 'bx_state_create', 'bx_state_destroy',
            'bx_state_num_envs', 'bx_state_set', 'bx_state_get', 'bx_state_rollout')
 
@@ -47,6 +47,8 @@ def load():
     getattr(lib, f).restype = C.c_int
   lib.bx_default_qp.argtypes = [P, C.c_int64, P, P, P, P, P, P, P]
   lib.bx_default_qp.restype = C.c_int
+  lib.bx_default_qp_offsets.argtypes = [P, C.c_int64, P, P, P, P, P, P, P, P]
+  lib.bx_default_qp_offsets.restype = C.c_int
   lib.bx_step.argtypes = [P, C.c_int64, C.POINTER(_desc.CStepIO), P]
   lib.bx_step.restype = C.c_int
   lib.bx_step_host.argtypes = [P, C.c_int64, C.POINTER(_desc.CStepIO)]

@@ -358,7 +358,7 @@ class System:
     """D: length of the joint_angle / joint_velocity vectors `default_qp` takes."""
     return int(self.desc.reset['num_dof'])
 
-  def default_qp(self, batch: int = None, device=None, joint_angle=None, joint_velocity=None) -> QP:
+  def default_qp(self, batch: int = None, device=None, joint_angle=None, joint_velocity=None, joint_offset=None) -> QP:
     """`System.default_qp(joint_angle=..., joint_velocity=...)` (system.py:112-242).
 
     Without joint arguments: the default state as recorded at extraction time (numpy, or
@@ -367,7 +367,10 @@ class System:
     trees onto the xy plane in ONE kernel launch (bx_default_qp) -- what every env's reset
     calls with its noisy joint state (envs/ant.py:198-204)."""
     if joint_angle is not None or joint_velocity is not None:
-      return self._default_qp_torch(joint_angle, joint_velocity)
+      # joint_offset: per-env joint sockets [B,J,3] (see `step`): the randomised Systems' own default pose
+      return self._default_qp_torch(joint_angle, joint_velocity, joint_offset)
+    if joint_offset is not None:
+      raise ValueError('joint_offset needs joint_angle / joint_velocity (the torch path)')
     d = self.desc.default_qp
     arrs = [np.asarray(d[k], dtype=np.float32) for k in ('pos', 'rot', 'vel', 'ang')]
     if batch is not None:
@@ -397,7 +400,7 @@ class System:
     act = torch.zeros(shape, dtype=torch.float32, device=qp.pos.device)
     return self._step_torch(qp, act, 1, False, True, None, None, False, observe=True, friction=friction)[2]['obs']
 
-  def _default_qp_torch(self, joint_angle, joint_velocity) -> QP:
+  def _default_qp_torch(self, joint_angle, joint_velocity, joint_offset=None) -> QP:
     import torch
     if not self.desc.reset:
       raise ValueError('this descriptor carries no reset tables (SystemDesc.reset)')
@@ -419,8 +422,14 @@ class System:
     outs = [flat[:b * n * 3].view(b, n, 3), flat[b * n * 3:b * n * 7].view(b, n, 4),
             flat[b * n * 7:b * n * 10].view(b, n, 3), flat[b * n * 10:].view(b, n, 3)]
     stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-    rc = self._lib.bx_default_qp(self._h, b, ja.data_ptr() if nd else None, jv.data_ptr() if nd else None,
-                                 *[o.data_ptr() for o in outs], stream)
+    jo = None
+    if joint_offset is not None:
+      # per-env joint sockets [B,J,3] (`joint_offset=` of `step`): the pose the randomised System's default_qp builds
+      jo = joint_offset.to(f32).reshape(b, len(self.desc.joints), 3).contiguous()
+      if jo.device != dev:
+        raise ValueError('joint_offset must live on the device of joint_angle')
+    rc = self._lib.bx_default_qp_offsets(self._h, b, ja.data_ptr() if nd else None, jv.data_ptr() if nd else None,
+                                         None if jo is None else jo.data_ptr(), *[o.data_ptr() for o in outs], stream)
     if rc != 0:
       raise RuntimeError('bx_default_qp: ' + _lib.last_error())
     if not batched:

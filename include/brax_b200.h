@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define BX_ABI_VERSION 13
+#define BX_ABI_VERSION 14
 
 /* dynamics_mode (base.py:179-201) */
 #define BX_MODE_PBD 0
@@ -402,6 +402,12 @@ int bx_system_num_joint_dof(const bx_system* sys);
 int bx_default_qp(const bx_system* sys, int64_t num_envs, const float* joint_angle,
                   const float* joint_velocity, float* pos, float* rot, float* vel, float* ang,
                   void* stream);
+/* The same with per-env joint sockets: joint_offset [B,J,3] (device; NULL = bx_default_qp) is Joint.parent_offset of
+ * every joint of env e in the order of bx_system_desc.joints -- `default_qp` of the System each env builds under the
+ * joint domain randomisation (experimental/tracing/randomizers.py:54-97; system.py:199-206 reads parent_offset). */
+int bx_default_qp_offsets(const bx_system* sys, int64_t num_envs, const float* joint_angle,
+                          const float* joint_velocity, const float* joint_offset, float* pos, float* rot,
+                          float* vel, float* ang, void* stream);
 
 /* One System.step for B independent environments: ONE kernel launch on
  * `stream` (a cudaStream_t passed as void*; NULL = default stream).  No host

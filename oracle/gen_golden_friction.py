@@ -137,12 +137,20 @@ def main_joints(only):
         'pos', 'rot', 'vel', 'ang', 'contact_vel', 'contact_ang', 'joint_vel', 'joint_ang', 'actuator_vel', 'actuator_ang',
         'contact_pos', 'contact_normal', 'contact_penetration'))
     rec = {k: [] for k in keys}
-    offs = []
+    offs, resets = [], []
+    reset_rng = (rng.uniform(-0.3, 0.3, 64), rng.uniform(-0.5, 0.5, 64))
     for delta in JOINT_DELTAS:
       s = brax.System(config, post_process_fn=lambda c, d=delta: TracedConfig(c, joint_tree(c, d, randomized)))
       desc = describe(s, name)
       offs.append([j['off_p'] for j in desc.joints])
       a = desc.act_size
+      # the reset pose of this variant: default_qp(joint_angle, joint_velocity) with fixed random joint states
+      # (system.py:112-242 reads the randomised parent_offset, :199-206)
+      nd = len(s.default_angle())
+      ja = s.default_angle() + reset_rng[0][:nd]
+      rq = s.default_qp(joint_angle=ja, joint_velocity=reset_rng[1][:nd])
+      resets.append({k: np.asarray(getattr(rq, k), np.float64) for k in ('pos', 'rot', 'vel', 'ang')})
+      reset_in = (np.asarray(ja, np.float64), np.asarray(reset_rng[1][:nd], np.float64))
       qp = s.default_qp()
       free = np.asarray([b['pos_mask'][0] for b in desc.bodies], np.float64)[:, None]
       qp = qp.__class__(pos=qp.pos, rot=qp.rot, vel=np.asarray(qp.vel) + free * np.array([1.0, 0.3, 0.0]), ang=qp.ang)
@@ -163,6 +171,9 @@ def main_joints(only):
         rec[k].append(np.stack(per[k]))
     out = {k: np.stack(v) for k, v in rec.items()}      # [V, T, ...]
     out['joint_offset'] = np.asarray(offs)              # [V, J, 3] as extracted from the built Systems
+    for k in ('pos', 'rot', 'vel', 'ang'):
+      out['reset_' + k] = np.stack([r[k] for r in resets])      # [V, N, .] default_qp(joint_angle, joint_velocity)
+    out['reset_joint_angle'], out['reset_joint_velocity'] = reset_in
     base = out['joint_offset'][0]
     # the descriptor lists the joints in the reference's joint-group order (by type), the config in file order:
     # match them by their (parent, child) bodies

@@ -172,7 +172,8 @@ JOINT_SYSTEMS = ('ant', 'ant_spring', 'humanoid_spring')
 def _golden_joints(name):
   g = np.load(os.path.join(GOLD, name + '_joints.npz'))
   v, t = g['pos'].shape[:2]
-  flat = {k: g[k].reshape((v * t,) + g[k].shape[2:]) for k in g.files if k not in ('joint_offset', 'randomized')}
+  flat = {k: g[k].reshape((v * t,) + g[k].shape[2:]) for k in g.files
+          if k not in ('joint_offset', 'randomized') and not k.startswith('reset_')}
   off = np.repeat(g['joint_offset'], t, axis=0)          # [V*T, J, 3]
   return g, flat, off
 
@@ -267,3 +268,69 @@ def test_gpu_joint_offsets_with_friction_policy_and_rollout():
     st = env.step(st, eo['action'][t].contiguous())
     assert torch.equal(st.obs, eo['obs'][t]), t
   assert torch.equal(st.qp.pos, q2.pos)
+
+
+def _reset_desc_with_offsets(desc, off):
+  """`desc` with the reset tables' parent offsets replaced by off[J,3] (step-joint order): reset joints are matched
+  to the step's joints by their bodies, as bx_system_create does."""
+  import copy
+  d = copy.copy(desc)
+  d.reset = copy.deepcopy(desc.reset)
+  step = {(j['body_p'], j['body_c']): i for i, j in enumerate(desc.joints)}
+  for rj in d.reset['joints']:
+    rj['off_p'] = [float(x) for x in off[step[(rj['body_p'], rj['body_c'])]]]
+  return d
+
+
+@pytest.mark.parametrize('name', JOINT_SYSTEMS)
+def test_reset_oracle_reproduces_reference_default_qp_under_substituted_joint_offsets(name):
+  from oracle import reset_oracle
+  g, _, _ = _golden_joints(name)
+  desc = util.load_desc(name)
+  ja, jv = g['reset_joint_angle'][None], g['reset_joint_velocity'][None]
+  for v in range(g['joint_offset'].shape[0]):
+    got = reset_oracle.default_qp(_reset_desc_with_offsets(desc, g['joint_offset'][v]), ja, jv, np.float64)
+    for k in util.QP_KEYS:
+      np.testing.assert_allclose(got[k][0], g['reset_' + k][v], rtol=0, atol=1e-12, err_msg='%s variant %d' % (k, v))
+  assert np.abs(g['reset_pos'][1] - g['reset_pos'][0]).max() > 5e-3     # the sockets move the pose
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', JOINT_SYSTEMS)
+def test_gpu_default_qp_with_per_env_joint_offsets(name):
+  """bx_default_qp_offsets: ONE launch over envs with different sockets == the reference's default_qp of each variant."""
+  torch = _torch()
+  from tests.test_gpu_parity import _system
+  g, _, _ = _golden_joints(name)
+  s = _system(name)
+  nv = g['joint_offset'].shape[0]
+  reps = 40                                   # ragged: 160 envs = 5 tiles, variants interleaved
+  idx = np.arange(nv * reps) % nv
+  off = torch.from_numpy(g['joint_offset'][idx].astype(np.float32)).cuda()
+  ja = torch.from_numpy(np.tile(g['reset_joint_angle'].astype(np.float32), (nv * reps, 1))).cuda()
+  jv = torch.from_numpy(np.tile(g['reset_joint_velocity'].astype(np.float32), (nv * reps, 1))).cuda()
+  qp = s.default_qp(joint_angle=ja, joint_velocity=jv, joint_offset=off)
+  for k in util.QP_KEYS:
+    got = getattr(qp, k).cpu().numpy()
+    np.testing.assert_allclose(got, g['reset_' + k][idx], rtol=0, atol=2e-6, err_msg=k)
+  plain = s.default_qp(joint_angle=ja, joint_velocity=jv)
+  assert torch.equal(plain.pos[idx == 0], qp.pos[idx == 0])          # the config's lanes: bitwise the plain launch
+  assert float((plain.pos[idx == 1] - qp.pos[idx == 1]).abs().max()) > 5e-3
+
+
+@pytest.mark.gpu
+def test_gpu_env_reset_uses_randomised_joint_sockets():
+  torch = _torch()
+  from brax_b200 import envs
+  env = envs.create('ant')
+  b = 64
+  base = torch.from_numpy(env.sys.joint_offsets()).cuda()
+  off = (base[None] + torch.linspace(-0.03, 0.03, b, device='cuda')[:, None, None]).contiguous()
+  st0 = env.reset(b, device='cuda', seed=5)
+  env.randomize_joints(off)
+  st1 = env.reset(b, device='cuda', seed=5)
+  want = env.sys.default_qp(joint_angle=None, joint_velocity=torch.zeros(b, env.sys.num_joint_dof, device='cuda'), joint_offset=off)
+  assert st1.qp.pos.shape == st0.qp.pos.shape and float((st1.qp.pos - st0.qp.pos).abs().max()) > 5e-3
+  mid = b // 2      # linspace passes (almost) through 0 in the middle: nearly the config's pose there
+  assert float((st1.qp.pos[mid] - st0.qp.pos[mid]).abs().max()) < 2e-3
+  assert want.pos.shape == st1.qp.pos.shape
