@@ -399,13 +399,17 @@ def run_reference(args, desc):
   b = args.envs  # per-step bounded sample: one GPU's shard of the workload
   rng = np.random.default_rng(7)
   pos, rot, vel, ang = make_state(desc, b, 7)
-  acts = rng.uniform(-1, 1, (args.steps + args.warmup, b, desc.act_size)).astype(np.float32)
+  # at least 5 untimed steps whatever --warmup says: the OpenMP team, the page cache of the outputs and the host's
+  # clocks are up before the timed steps (a cold 3-step run reads 0.46 M env-steps/s instead of 0.67 M: the
+  # reference arm must not look slower than it is)
+  warm = max(args.warmup, 5)
+  acts = rng.uniform(-1, 1, (args.steps + warm, b, desc.act_size)).astype(np.float32)
   st = {'pos': pos, 'rot': rot, 'vel': vel, 'ang': ang}
-  for i in range(args.warmup):
+  for i in range(warm):
     st = o.step(st['pos'], st['rot'], st['vel'], st['ang'], acts[i], num_threads=cores)
   t0 = time.perf_counter()
   for i in range(args.steps):
-    st = o.step(st['pos'], st['rot'], st['vel'], st['ang'], acts[args.warmup + i], num_threads=cores)
+    st = o.step(st['pos'], st['rot'], st['vel'], st['ang'], acts[warm + i], num_threads=cores)
   el = time.perf_counter() - t0
   v = b * args.steps / el
   sample = '%s %d envs per step (one GPU shard), C oracle float32 + OpenMP' % (args.env, b)
