@@ -48,7 +48,7 @@ NCU_TRAFFIC = {
     # env: (bytes per launch, capture under profiles/).  Reads + writes seen at DRAM by one launch of the
     # bench workload under ncu (--set full, cache control on: the outputs of a launch stay in the 126 MB L2
     # until a later launch evicts them, so the figure is dominated by the cold input reads).
-    'ant': (4591616, 'profiles/r02_ncu_full_ant_step_kernel.csv (ant 8192 envs)'),
+    'ant': (4585984, 'profiles/r02_ncu_full_ant_step_kernel_final.csv (ant 8192 envs, final round-2 build)'),
     'humanoid': (5748992, 'profiles/r02_ncu_full_humanoid_step_kernel.csv (humanoid 8192 envs)'),
     'grasp': (4142848, 'profiles/r02_ncu_full_grasp_step_kernel.csv (grasp 4096 envs)'),
 }
